@@ -1,0 +1,213 @@
+/* pynama_b200 -- C ABI of the B200-native FEM hot path (libpynama_b200.so)
+ *
+ * The reference (ibejarano/Pynama) is pure Python on top of petsc4py and defines no FFI of its own; the native
+ * code it executes on this path is PETSc's.  Each entry point below therefore cites the reference call site
+ * (path:line under /root/reference/) whose work it replaces; INTEGRATION.md shows the ctypes binding a
+ * maintainer would add on the reference side.
+ *
+ * Conventions
+ *   - plain C: raw pointers and sizes only.  Every `d_` pointer is a DEVICE pointer owned by the caller;
+ *     `h_` pointers are host pointers.  No hidden allocation except inside opaque handles
+ *     (`*_create` / `*_destroy`).
+ *   - every function returns 0 on success, a negative pyn_status on failure; pyn_last_error() gives the text.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).  Calls are asynchronous with
+ *     respect to the host unless stated otherwise.
+ *   - all values FP64, column indices int32, row pointers int64, dof classes int8.
+ *   - vector layout: dof = node*ncomp + comp (reference: indices.py:90-92).
+ *   - one host thread per GPU; nothing here is re-entrant on the same handle.
+ */
+#ifndef PYNAMA_B200_H
+#define PYNAMA_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+  PYN_OK = 0,
+  PYN_ERR_ARG = -1,      /* bad argument */
+  PYN_ERR_CUDA = -2,     /* CUDA runtime error (text in pyn_last_error) */
+  PYN_ERR_LIMIT = -3,    /* size outside the compiled limits (ngl, node valence) */
+  PYN_ERR_NCCL = -4,
+  PYN_ERR_BREAKDOWN = -5 /* Krylov breakdown / indefinite operator */
+} pyn_status;
+
+#define PYN_MAX_NGL 12
+
+const char* pyn_last_error(void);
+int pyn_version(void);
+/* number of kernel launches issued by this library on this process since load (bench.py: gpu_launches) */
+int64_t pyn_launch_count(void);
+int pyn_device_info(int* sm_count, int* cc_major, int* cc_minor, int64_t* smem_per_block_optin);
+
+/* ------------------------------------------------------------------------------------------------------
+ * Element layer.  Replaces Spectral.getElemKLEMatrices / getElemKLEOperators
+ * (src/elements/spectral.py:89-157, :159-218) for dim = 2, batched over elements.
+ * The 1-D tables are the host-computed Q1-Q3 tables (src/elements/utilities.py:43-92,
+ * src/elements/element.py:17-48):  h[q*ngl+a] = l_a(xi_q), d[q*ngl+a] = l_a'(xi_q).
+ * perm[k] = a*ngl+b : element-local node k -> tensor index (src/elements/spectral.py:224-246).
+ * ---------------------------------------------------------------------------------------------------- */
+typedef struct pyn_elem pyn_elem;
+
+int pyn_elem_create(int ngl,
+                    int nq_full, const double* h_full, const double* d_full, const double* w_full, const double* xi_full,
+                    int nq_red, const double* h_red, const double* d_red, const double* w_red, const double* xi_red,
+                    const double* d_nodal /* [ngl*ngl] l_a'(node_q) */, const double* w_nodal, const double* xi_nodal,
+                    const int32_t* perm /* [ngl*ngl] */, double alpha_w, double alpha_d, pyn_elem** out);
+int pyn_elem_destroy(pyn_elem* e);
+
+/* d_coords [ne][4][2] corner coordinates in closure order.  Outputs (any may be NULL to skip):
+ * d_K [ne][2nn][2nn], d_Rw [ne][2nn][nn], d_Rd [ne][2nn][nn]; index = localNode*2 + comp. */
+int pyn_elem_kle(const pyn_elem* e, const double* d_coords, int64_t ne,
+                 double* d_K, double* d_Rw, double* d_Rd, void* stream);
+/* d_SrT [ne][3nn][2nn], d_DivSrT [ne][2nn][3nn], d_Curl [ne][nn][2nn], d_W [ne][nn] */
+int pyn_elem_ops(const pyn_elem* e, const double* d_coords, int64_t ne,
+                 double* d_SrT, double* d_DivSrT, double* d_Curl, double* d_W, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------
+ * Mesh numbering on device.  Replaces the per-cell Python loops of DMPlexDom.getGlobalNodesFromCell /
+ * IndicesManager.mapEntitiesToNodes (src/domain/dmplex.py:197-200, src/domain/indices.py:66-88),
+ * getCellCornersCoords (dmplex.py:97-104) and computeFullCoordinates (dmplex.py:66-95) for the serial
+ * DMPlexCreateBoxMesh numbering (dmplex.py:16).  Cells [cell0, cell0+ncells).
+ * ---------------------------------------------------------------------------------------------------- */
+int pyn_box_cell_nodes(int nx, int ny, int ngl, int64_t cell0, int64_t ncells,
+                       int32_t* d_elem2node /* [ncells][ngl*ngl] */, void* stream);
+int pyn_box_cell_corners(int nx, int ny, double x0, double y0, double x1, double y1, int64_t cell0, int64_t ncells,
+                         double* d_coords /* [ncells][4][2] */, void* stream);
+/* node coordinates [nnodes][2]: corner-bilinear map evaluated at the nodal GLL points (xi_nodal, ngl values) */
+int pyn_box_node_coords(int nx, int ny, int ngl, double x0, double y0, double x1, double y1,
+                        const double* h_xi_nodal, const int32_t* h_perm, double* d_xy, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------
+ * Topology handle: node->element incidence and node adjacency (nodes sharing a cell), built once per mesh.
+ * Replaces DMPlexDom.getMatIndices (src/domain/dmplex.py:305-333) and PETSc's MatAssembly pattern work.
+ * elem ids in d_elem2node are LOCAL [0,ne); `elem_order` (NULL = identity) gives the global cell number used
+ * for the summation order (ascending), so a partition sums in the same order as the serial cell loop.
+ * ---------------------------------------------------------------------------------------------------- */
+typedef struct pyn_topo pyn_topo;
+int pyn_topo_create(const int32_t* d_elem2node, int64_t ne, int nn, int64_t nnodes, void* stream, pyn_topo** out);
+int pyn_topo_destroy(pyn_topo* t);
+/* nnz of the node adjacency, max elements per node, max adjacency row length */
+int pyn_topo_info(const pyn_topo* t, int64_t* adj_nnz, int* max_valence, int* max_row);
+/* device pointers to the node adjacency CSR (owned by the handle) */
+int pyn_topo_adjacency(const pyn_topo* t, const int64_t** d_rowptr, const int32_t** d_cols);
+
+/* ------------------------------------------------------------------------------------------------------
+ * Deterministic global assembly into CSR (sorted columns, explicit zeros kept, duplicates added in ascending
+ * cell order).  One descriptor describes one matrix of FreeSlip.buildKLEMats / NoSlipFreeSlip.buildKLEMats /
+ * BaseProblem.buildOperators (src/cases/base_problem.py:499-552, :329-454, :132-140) together with
+ * Mat.setIndices2One (src/matrices/mat_generator.py:113-118) and Operators.assembleAll (:172-190):
+ *
+ *   entry (row dof i of class ri, col dof j of class cj) is stored iff  pair_mask bit (ri*4+cj)  is set, or
+ *   i == j and diag_classes bit ri is set;  its value is  rowscale[node(i)] * sign * sum_e E_e[li][lj]  (+
+ *   diag_add[ri] on such a diagonal).  Classes: 0 free, 1 tangential-on-no-slip-wall, 2 prescribed.
+ * ---------------------------------------------------------------------------------------------------- */
+typedef struct {
+  int32_t rdof, cdof;        /* dofs per node on rows / columns: K 2x2, Rw 2x1, SrT 3x2, DivSrT 2x3, Curl 1x2 */
+  const int8_t* d_rclass;    /* [nnodes*rdof] or NULL (all 0) */
+  const int8_t* d_cclass;    /* [nnodes*cdof] or NULL (all 0) */
+  uint32_t pair_mask;
+  uint32_t diag_classes;
+  double diag_add[4];
+  double sign;
+  const double* d_E;         /* [ne or 1][rdof*nn][cdof*nn] element matrices */
+  int64_t E_stride;          /* elements between consecutive element matrices in doubles; 0 = one for all cells */
+  const double* d_rowscale;  /* [nnodes] or NULL */
+} pyn_asm_desc;
+
+/* pattern: row pointers (exclusive scan done inside), total nnz returned on the host (synchronises) */
+int pyn_asm_count(const pyn_topo* t, const pyn_asm_desc* desc, int64_t* d_indptr /* [nnodes*rdof+1] */,
+                  int64_t* h_nnz, void* stream);
+/* d_indices may be NULL (values only: re-assembly on a known pattern) ; d_data may be NULL (pattern only) */
+int pyn_asm_fill(const pyn_topo* t, const pyn_asm_desc* desc, const int64_t* d_indptr,
+                 int32_t* d_indices, double* d_data, void* stream);
+/* lumped weights  W[node] = sum_e W_e[local]  in ascending cell order  (mat_generator.py:168-170) */
+int pyn_asm_weights(const pyn_topo* t, const double* d_We, int64_t We_stride, double* d_W, void* stream);
+
+/* Generic deterministic COO -> CSR (Mat.setValues(ADD_VALUES) + assemble, mat_generator.py:14-17,157-166):
+ * keys sorted by (row, col), duplicates added in input order.  Two calls: count then fill. */
+int pyn_coo_count(int64_t n, const int32_t* d_rows, const int32_t* d_cols, int64_t nrows, int64_t ncols,
+                  int64_t* d_indptr, int64_t* h_nnz, void** scratch /* opaque, freed by fill */, void* stream);
+int pyn_coo_fill(void* scratch, const double* d_vals, const int64_t* d_indptr, int32_t* d_indices, double* d_data,
+                 void* stream);
+
+/* C = A + alpha*B on the union pattern (petsc4py `K + Kfs`, base_problem.py:318) */
+int pyn_csr_add_count(int64_t nrows, const int64_t* d_aptr, const int32_t* d_aind,
+                      const int64_t* d_bptr, const int32_t* d_bind, int64_t* d_cptr, int64_t* h_nnz, void* stream);
+int pyn_csr_add_fill(int64_t nrows, const int64_t* d_aptr, const int32_t* d_aind, const double* d_aval, double alpha,
+                     const int64_t* d_bptr, const int32_t* d_bind, const double* d_bval,
+                     const int64_t* d_cptr, int32_t* d_cind, double* d_cval, void* stream);
+int pyn_csr_diagonal(int64_t nrows, const int64_t* d_ptr, const int32_t* d_ind, const double* d_val,
+                     double* d_diag, void* stream);
+/* drop stored zeros (compressed operator pattern for the timed SpMV): count then fill */
+int pyn_csr_compress_count(int64_t nrows, const int64_t* d_ptr, const double* d_val, int64_t* d_optr, int64_t* h_nnz,
+                           void* stream);
+int pyn_csr_compress_fill(int64_t nrows, const int64_t* d_ptr, const int32_t* d_ind, const double* d_val,
+                          const int64_t* d_optr, int32_t* d_oind, double* d_oval, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------
+ * SpMV  y = A x  (PETSc Mat.mult / `Mat * Vec`, base_problem.py:219,229,232,323-327,481) with fused epilogues.
+ * ---------------------------------------------------------------------------------------------------- */
+typedef enum {
+  PYN_SPMV_SET = 0,        /* y = A x */
+  PYN_SPMV_ADD = 1,        /* y += A x */
+  PYN_SPMV_SCALE = 2,      /* y = p0 * (A x)                                 (base_problem.py:229-230) */
+  PYN_SPMV_SRT_VTENSV = 3  /* y = p0*(A x) - p1*VtensV(aux)  rows = 3*nodes   (base_problem.py:217-223) */
+} pyn_spmv_mode;
+int pyn_spmv(int64_t nrows, const int64_t* d_ptr, const int32_t* d_ind, const double* d_val, int64_t nnz,
+             const double* d_x, double* d_y, int mode, double p0, double p1, const double* d_aux, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------
+ * Vectors (PETSc Vec calls of the path: base_problem.py:222-230,234-252; cavity.py:53-81; custom_func.py:76-83)
+ * ---------------------------------------------------------------------------------------------------- */
+int pyn_vec_set(int64_t n, double a, double* d_x, void* stream);
+int pyn_vec_scale(int64_t n, double a, double* d_x, void* stream);
+int pyn_vec_axpy(int64_t n, double a, const double* d_x, double* d_y, void* stream);          /* y += a x */
+int pyn_vec_aypx(int64_t n, double a, const double* d_x, double* d_y, void* stream);          /* y = x + a y */
+int pyn_vec_waxpy(int64_t n, double a, const double* d_x, const double* d_y, double* d_w, void* stream); /* w = a x + y */
+int pyn_vec_maxpy(int64_t n, int m, const double* h_coef, const double* const* h_xs, const double* d_y0,
+                  double* d_y, void* stream);                                                 /* y = y0 + sum c_j x_j */
+int pyn_vec_dot(int64_t n, const double* d_x, const double* d_y, double* h_out, void* stream); /* synchronises */
+int pyn_vec_norm(int64_t n, const double* d_x, int kind /*2: l2, 3: inf*/, double* h_out, void* stream);
+int pyn_vec_scatter_set(int64_t nidx, const int64_t* d_idx, const double* d_vals, double* d_x, void* stream);
+int pyn_vec_scatter_const(int64_t nidx, const int64_t* d_idx, double val, double* d_x, void* stream);
+int pyn_vtensv(int64_t nnodes, const double* d_vel, double* d_out, void* stream);  /* base_problem.py:234-252 */
+/* Taylor-Green analytic fields on a node list (custom_func.py:76-83,173-193); idx NULL = all nodes */
+int pyn_taylor_green(int64_t nidx, const int64_t* d_idx, const double* d_xy, double nu, double t,
+                     double* d_vel /* nullable */, double* d_vort /* nullable */, void* stream);
+/* TSAdapt-basic weighted RMS error norm: sqrt(mean((e_i/(atol+rtol*max(|y_i|,|ynew_i|)))^2)), synchronises */
+int pyn_vec_wrms(int64_t n, const double* d_err, const double* d_y, const double* d_ynew, double atol, double rtol,
+                 double* h_out, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------
+ * Krylov solvers with PETSc semantics (KspSolver, src/solver/ksp_solver.py:9-19; use sites
+ * base_problem.py:276,318,323-327,481): zero initial guess, left preconditioning, preconditioned residual
+ * norm, KSPConvergedDefault.  reason: 2 rtol, 3 atol, -3 max_it, -4 dtol, -8 indefinite.
+ * ---------------------------------------------------------------------------------------------------- */
+typedef struct pyn_ksp pyn_ksp;
+typedef struct {
+  int32_t type;        /* 0 cg, 1 gmres */
+  int32_t pc;          /* 0 none, 1 jacobi */
+  double rtol, atol, dtol;
+  int32_t max_it;
+  int32_t restart;     /* gmres */
+  int32_t check_every; /* iterations between host polls of the device convergence flag (0 = default) */
+  int32_t nonzero_guess;
+} pyn_ksp_opts;
+typedef struct {
+  int32_t its, reason;
+  double rnorm0, rnorm;
+} pyn_ksp_result;
+int pyn_ksp_create(int64_t nrows, const int64_t* d_ptr, const int32_t* d_ind, const double* d_val, int64_t nnz,
+                   const pyn_ksp_opts* opts, void* stream, pyn_ksp** out);
+int pyn_ksp_solve(pyn_ksp* k, const double* d_b, double* d_x, pyn_ksp_result* res, void* stream); /* synchronises */
+int pyn_ksp_destroy(pyn_ksp* k);
+/* device work done by the last solve: SpMV launches and total kernel launches (for the roofline accounting) */
+int pyn_ksp_stats(const pyn_ksp* k, int64_t* spmv_launches, int64_t* kernel_launches);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PYNAMA_B200_H */

@@ -1,0 +1,374 @@
+"""Device-side objects of the hot path: thin Python owners of HBM buffers + calls into libpynama_b200.so.
+
+PyTorch is used only as the allocator / stream provider (torch tensors own the device memory; raw pointers are
+handed to the C ABI).  Nothing here computes on the CPU.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import AsmDesc, KspOpts, KspResult, call
+
+F64, I64, I32, I8 = torch.float64, torch.int64, torch.int32, torch.int8
+
+
+def device():
+    if not torch.cuda.is_available():
+        raise _lib.PynamaError("pynama_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback")
+    return torch.device("cuda", torch.cuda.current_device())
+
+
+def stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def ptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else None
+
+
+def empty(n, dtype=F64):
+    return torch.empty(int(n), dtype=dtype, device=device())
+
+
+def zeros(n, dtype=F64):
+    return torch.zeros(int(n), dtype=dtype, device=device())
+
+
+def to_device(a, dtype=None):
+    t = torch.as_tensor(np.ascontiguousarray(a))
+    if dtype is not None:
+        t = t.to(dtype)
+    return t.to(device())
+
+
+def launch_count():
+    return int(_lib.load().pyn_launch_count())
+
+
+def _np_ptr(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+# ---------------------------------------------------------------------------------------------------------
+class ElemKernels:
+    """Device tables of one Spectral(ngl, 2) element + the batched integration kernels (pyn_elem_*)."""
+
+    def __init__(self, ngl, rules, deriv_nodal, perm, alpha_w=1e2, alpha_d=1e3):
+        """rules: dict name -> (h[q,a], d[q,a], w[q], xi[q]) for 'full', 'red'; plus 'op' -> (w, xi)."""
+        self.ngl, self.nn = int(ngl), int(ngl) ** 2
+        f64 = lambda a: np.ascontiguousarray(a, dtype=np.float64)
+        hF, dF, wF, xF = map(f64, rules["full"])
+        hG, dG, wG, xG = map(f64, rules["red"])
+        wO, xO = map(f64, rules["op"])
+        D = f64(deriv_nodal)
+        perm = np.ascontiguousarray(perm, dtype=np.int32)
+        self._h = C.c_void_p()
+        call("pyn_elem_create", self.ngl, len(wF), _np_ptr(hF), _np_ptr(dF), _np_ptr(wF), _np_ptr(xF),
+             len(wG), _np_ptr(hG), _np_ptr(dG), _np_ptr(wG), _np_ptr(xG), _np_ptr(D), _np_ptr(wO), _np_ptr(xO),
+             _np_ptr(perm), float(alpha_w), float(alpha_d), C.byref(self._h))
+
+    def __del__(self):
+        try:
+            if getattr(self, "_h", None):
+                _lib.load().pyn_elem_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+    def kle(self, coords, want_rd=True):
+        """coords: device tensor (ne,4,2) -> K (ne,2nn,2nn), Rw (ne,2nn,nn), Rd (ne,2nn,nn) on device."""
+        coords = coords.contiguous()
+        ne, nn = coords.numel() // 8, self.nn
+        K = empty(ne * 4 * nn * nn).view(ne, 2 * nn, 2 * nn)
+        Rw = empty(ne * 2 * nn * nn).view(ne, 2 * nn, nn)
+        Rd = empty(ne * 2 * nn * nn).view(ne, 2 * nn, nn) if want_rd else None
+        call("pyn_elem_kle", self._h, ptr(coords), ne, ptr(K), ptr(Rw), ptr(Rd), stream())
+        return K, Rw, Rd
+
+    def ops(self, coords):
+        coords = coords.contiguous()
+        ne, nn = coords.numel() // 8, self.nn
+        SrT = empty(ne * 6 * nn * nn).view(ne, 3 * nn, 2 * nn)
+        Div = empty(ne * 6 * nn * nn).view(ne, 2 * nn, 3 * nn)
+        Curl = empty(ne * 2 * nn * nn).view(ne, nn, 2 * nn)
+        W = empty(ne * nn).view(ne, nn)
+        call("pyn_elem_ops", self._h, ptr(coords), ne, ptr(SrT), ptr(Div), ptr(Curl), ptr(W), stream())
+        return SrT, Div, Curl, W
+
+
+# ---------------------------------------------------------------------------------------------------------
+def box_cell_nodes(nx, ny, ngl, cell0=0, ncells=None):
+    ncells = nx * ny - cell0 if ncells is None else ncells
+    out = empty(ncells * ngl * ngl, I32).view(ncells, ngl * ngl)
+    call("pyn_box_cell_nodes", nx, ny, ngl, cell0, ncells, ptr(out), stream())
+    return out
+
+
+def box_cell_corners(nx, ny, lower, upper, cell0=0, ncells=None):
+    ncells = nx * ny - cell0 if ncells is None else ncells
+    out = empty(ncells * 8).view(ncells, 4, 2)
+    call("pyn_box_cell_corners", nx, ny, float(lower[0]), float(lower[1]), float(upper[0]), float(upper[1]),
+         cell0, ncells, ptr(out), stream())
+    return out
+
+
+def box_node_coords(nx, ny, ngl, lower, upper, xi_nodal, perm, nnodes):
+    out = empty(nnodes * 2).view(nnodes, 2)
+    xi = np.ascontiguousarray(xi_nodal, dtype=np.float64)
+    pm = np.ascontiguousarray(perm, dtype=np.int32)
+    call("pyn_box_node_coords", nx, ny, ngl, float(lower[0]), float(lower[1]), float(upper[0]), float(upper[1]),
+         _np_ptr(xi), _np_ptr(pm), ptr(out), stream())
+    return out
+
+
+class Topology:
+    """node->element incidence + node adjacency on device (pyn_topo_*)."""
+
+    def __init__(self, elem2node, nnodes):
+        self.elem2node = elem2node.contiguous()       # kept alive: the handle borrows it
+        self.ne, self.nn = self.elem2node.shape
+        self.nnodes = int(nnodes)
+        self._h = C.c_void_p()
+        call("pyn_topo_create", ptr(self.elem2node), self.ne, self.nn, self.nnodes, stream(), C.byref(self._h))
+        nnz, val, row = C.c_int64(), C.c_int(), C.c_int()
+        call("pyn_topo_info", self._h, C.byref(nnz), C.byref(val), C.byref(row))
+        self.adj_nnz, self.max_valence, self.max_row = nnz.value, val.value, row.value
+
+    def __del__(self):
+        try:
+            if getattr(self, "_h", None):
+                _lib.load().pyn_topo_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+
+def pair_mask(pairs):
+    m = 0
+    for rc, cc in pairs:
+        m |= 1 << (rc * 4 + cc)
+    return m
+
+
+ALL_PAIRS = pair_mask([(r, c) for r in range(4) for c in range(4)])
+
+
+class CSR:
+    """Device CSR matrix (int64 row pointers, int32 sorted column indices, FP64 values)."""
+
+    def __init__(self, shape, indptr, indices, data, name=""):
+        self.shape, self.indptr, self.indices, self.data, self.name = tuple(shape), indptr, indices, data, name
+
+    @property
+    def nnz(self):
+        return int(self.indices.numel())
+
+    # -- PETSc-Mat flavoured surface ----------------------------------------------------------------------
+    def mult(self, x, y, mode=0, p0=0.0, p1=0.0, aux=None):
+        xd = x.data if hasattr(x, "data") and not isinstance(x, torch.Tensor) else x
+        yd = y.data if hasattr(y, "data") and not isinstance(y, torch.Tensor) else y
+        ad = aux.data if (aux is not None and not isinstance(aux, torch.Tensor)) else aux
+        assert xd.numel() == self.shape[1] and yd.numel() == self.shape[0]
+        call("pyn_spmv", self.shape[0], ptr(self.indptr), ptr(self.indices), ptr(self.data), self.nnz,
+             ptr(xd), ptr(yd), mode, float(p0), float(p1), ptr(ad), stream())
+        return y
+
+    def diagonal(self):
+        d = empty(self.shape[0])
+        call("pyn_csr_diagonal", self.shape[0], ptr(self.indptr), ptr(self.indices), ptr(self.data), ptr(d), stream())
+        return d
+
+    def add(self, other, alpha=1.0, name=""):
+        """self + alpha*other on the union pattern (MatAXPY, DIFFERENT_NONZERO_PATTERN)."""
+        assert self.shape == other.shape
+        n = self.shape[0]
+        cp = empty(n + 1, I64)
+        nnz = C.c_int64()
+        call("pyn_csr_add_count", n, ptr(self.indptr), ptr(self.indices), ptr(other.indptr), ptr(other.indices),
+             ptr(cp), C.byref(nnz), stream())
+        ci, cv = empty(nnz.value, I32), empty(nnz.value)
+        call("pyn_csr_add_fill", n, ptr(self.indptr), ptr(self.indices), ptr(self.data), float(alpha),
+             ptr(other.indptr), ptr(other.indices), ptr(other.data), ptr(cp), ptr(ci), ptr(cv), stream())
+        return CSR(self.shape, cp, ci, cv, name)
+
+    def compressed(self, name=""):
+        """Copy with stored zeros dropped (timed operator SpMVs; the reference pattern stays in `self`)."""
+        n = self.shape[0]
+        op = empty(n + 1, I64)
+        nnz = C.c_int64()
+        call("pyn_csr_compress_count", n, ptr(self.indptr), ptr(self.data), ptr(op), C.byref(nnz), stream())
+        oi, ov = empty(nnz.value, I32), empty(nnz.value)
+        call("pyn_csr_compress_fill", n, ptr(self.indptr), ptr(self.indices), ptr(self.data), ptr(op), ptr(oi),
+             ptr(ov), stream())
+        return CSR(self.shape, op, oi, ov, name or self.name)
+
+    # -- exporters (copies to host) -------------------------------------------------------------------------
+    def getValuesCSR(self):
+        """(indptr, indices, data) as NumPy, like petsc4py Mat.getValuesCSR()."""
+        ip = self.indptr.cpu().numpy()
+        if ip[-1] < 2 ** 31:
+            ip = ip.astype(np.int32)
+        return ip, self.indices.cpu().numpy(), self.data.cpu().numpy()
+
+    def to_scipy(self):
+        import scipy.sparse as sp
+        ip, ix, dv = self.getValuesCSR()
+        return sp.csr_matrix((dv, ix, ip), shape=self.shape)
+
+    def to_petsc(self):
+        from petsc4py import PETSc  # only when the user has it
+        ip, ix, dv = self.getValuesCSR()
+        return PETSc.Mat().createAIJ(size=self.shape, csr=(ip, ix, dv))
+
+    def bytes_spmv(self):
+        """algorithmic HBM bytes of one y = A x: 12 nnz + 8 (rows+1) + 8 rows + 8 cols."""
+        return 12 * self.nnz + 8 * (self.shape[0] + 1) + 8 * self.shape[0] + 8 * self.shape[1]
+
+
+def assemble(topo, rdof, cdof, E, rclass=None, cclass=None, pairs=ALL_PAIRS, diag_classes=0,
+             diag_add=(0.0, 0.0, 0.0, 0.0), sign=1.0, rowscale=None, pattern=None, name="", values=True):
+    """Deterministic assembly of one matrix (pyn_asm_count + pyn_asm_fill).
+
+    E: device tensor (1|ne, rdof*nn, cdof*nn).  pattern: an existing CSR whose indptr/indices are reused
+    (values-only re-assembly).  Returns CSR."""
+    d = AsmDesc()
+    d.rdof, d.cdof = rdof, cdof
+    d.d_rclass = rclass.data_ptr() if rclass is not None else None
+    d.d_cclass = cclass.data_ptr() if cclass is not None else None
+    d.pair_mask = pairs if isinstance(pairs, int) else pair_mask(pairs)
+    d.diag_classes = diag_classes
+    for i in range(4):
+        d.diag_add[i] = float(diag_add[i])
+    d.sign = float(sign)
+    if E is not None:
+        E = E.contiguous()
+        assert E.shape[-2] == rdof * topo.nn and E.shape[-1] == cdof * topo.nn
+        d.d_E = E.data_ptr()
+        d.E_stride = 0 if E.shape[0] == 1 else rdof * cdof * topo.nn * topo.nn
+        if E.shape[0] != 1:
+            assert E.shape[0] == topo.ne
+    d.d_rowscale = rowscale.data_ptr() if rowscale is not None else None
+    nrows, ncols = topo.nnodes * rdof, topo.nnodes * cdof
+    if pattern is None:
+        indptr = empty(nrows + 1, I64)
+        nnz = C.c_int64()
+        call("pyn_asm_count", topo._h, C.byref(d), ptr(indptr), C.byref(nnz), stream())
+        indices = empty(nnz.value, I32)
+        fill_idx = indices
+    else:
+        indptr, indices, fill_idx = pattern.indptr, pattern.indices, None
+    data = empty(indices.numel()) if values else None
+    call("pyn_asm_fill", topo._h, C.byref(d), ptr(indptr), ptr(fill_idx), ptr(data), stream())
+    return CSR((nrows, ncols), indptr, indices, data, name)
+
+
+def assemble_weights(topo, We):
+    We = We.contiguous()
+    W = empty(topo.nnodes)
+    call("pyn_asm_weights", topo._h, ptr(We), 0 if We.shape[0] == 1 else topo.nn, ptr(W), stream())
+    return W
+
+
+def coo_to_csr(rows, cols, vals, shape, name=""):
+    """Generic deterministic COO -> CSR on device (Mat.setValues(ADD) + assemble semantics)."""
+    n = int(rows.numel())
+    indptr = empty(shape[0] + 1, I64)
+    nnz = C.c_int64()
+    scratch = C.c_void_p()
+    call("pyn_coo_count", n, ptr(rows), ptr(cols), shape[0], shape[1], ptr(indptr), C.byref(nnz), C.byref(scratch),
+         stream())
+    indices, data = empty(nnz.value, I32), empty(nnz.value)
+    call("pyn_coo_fill", scratch, ptr(vals), ptr(indptr), ptr(indices), ptr(data), stream())
+    return CSR(shape, indptr, indices, data, name)
+
+
+# ---------------------------------------------------------------------------------------------------------
+class Ksp:
+    """Device Krylov solver handle (pyn_ksp_*)."""
+    TYPES = {"cg": 0, "gmres": 1}
+    PCS = {"none": 0, "jacobi": 1}
+
+    def __init__(self, A: CSR, ksp_type="cg", pc="jacobi", rtol=1e-5, atol=1e-50, dtol=1e4, max_it=10000,
+                 restart=30, check_every=0):
+        self.A = A
+        o = KspOpts()
+        o.type, o.pc = self.TYPES[ksp_type], self.PCS[pc]
+        o.rtol, o.atol, o.dtol, o.max_it, o.restart, o.check_every, o.nonzero_guess = rtol, atol, dtol, max_it, restart, check_every, 0
+        self.opts = o
+        self._h = C.c_void_p()
+        call("pyn_ksp_create", A.shape[0], ptr(A.indptr), ptr(A.indices), ptr(A.data), A.nnz, C.byref(o), stream(),
+             C.byref(self._h))
+        self.its, self.reason, self.rnorm0, self.rnorm = 0, 0, 0.0, 0.0
+
+    def solve(self, b, x):
+        r = KspResult()
+        call("pyn_ksp_solve", self._h, ptr(b), ptr(x), C.byref(r), stream())
+        self.its, self.reason, self.rnorm0, self.rnorm = r.its, r.reason, r.rnorm0, r.rnorm
+        return r
+
+    def __del__(self):
+        try:
+            if getattr(self, "_h", None):
+                _lib.load().pyn_ksp_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+
+# ---------------------------------------------------------------------------------------------------------
+def vec_dot(x, y):
+    out = C.c_double()
+    call("pyn_vec_dot", x.numel(), ptr(x), ptr(y), C.byref(out), stream())
+    return out.value
+
+
+def vec_norm(x, kind=2):
+    out = C.c_double()
+    call("pyn_vec_norm", x.numel(), ptr(x), kind, C.byref(out), stream())
+    return out.value
+
+
+def vec_axpy(y, a, x):
+    call("pyn_vec_axpy", y.numel(), float(a), ptr(x), ptr(y), stream())
+
+
+def vec_scale(x, a):
+    call("pyn_vec_scale", x.numel(), float(a), ptr(x), stream())
+
+
+def vec_set(x, a):
+    call("pyn_vec_set", x.numel(), float(a), ptr(x), stream())
+
+
+def vec_maxpy(y, y0, coefs, xs):
+    m = len(coefs)
+    cf = (C.c_double * m)(*[float(c) for c in coefs])
+    px = (C.c_void_p * m)(*[x.data_ptr() for x in xs])
+    call("pyn_vec_maxpy", y.numel(), m, cf, px, ptr(y0), ptr(y), stream())
+
+
+def vec_wrms(err, y, ynew, atol, rtol):
+    out = C.c_double()
+    call("pyn_vec_wrms", err.numel(), ptr(err), ptr(y), ptr(ynew), float(atol), float(rtol), C.byref(out), stream())
+    return out.value
+
+
+def vec_scatter_set(x, idx, vals):
+    call("pyn_vec_scatter_set", idx.numel(), ptr(idx), ptr(vals), ptr(x), stream())
+
+
+def vec_scatter_const(x, idx, val):
+    call("pyn_vec_scatter_const", idx.numel(), ptr(idx), float(val), ptr(x), stream())
+
+
+def vtensv(vel, out):
+    call("pyn_vtensv", vel.numel() // 2, ptr(vel), ptr(out), stream())
+
+
+def taylor_green(xy, nu, t, vel=None, vort=None, idx=None):
+    n = idx.numel() if idx is not None else xy.shape[0]
+    call("pyn_taylor_green", n, ptr(idx), ptr(xy), float(nu), float(t), ptr(vel), ptr(vort), stream())

@@ -1,0 +1,322 @@
+// Krylov solvers on device with PETSc semantics (KSPCG / KSPGMRES + KSPConvergedDefault, left preconditioning,
+// preconditioned residual norm, zero initial guess) -- replaces KspSolver (src/solver/ksp_solver.py:9-19).
+//
+// Control flow lives on the device: every kernel of an iteration starts by reading a `done` flag in a small state
+// block, so a whole chunk of iterations can be enqueued (as one CUDA graph) without the host knowing whether
+// convergence happened in the middle; the host polls the state once per chunk.  The iteration count, the stopping
+// iteration and the iterate are therefore exactly those of the sequential algorithm.
+// All reductions are two-level with a fixed tree (per-CTA partial -> every CTA re-sums the partials in the same
+// order), i.e. bitwise reproducible run to run.
+#include <vector>
+
+#include "spmv.cuh"
+
+namespace {
+constexpr int BLK = 256;
+
+struct KspState {
+  double beta, betaold, dp, rnorm0, ttol;
+  int its, reason, done, pad;
+};
+
+struct CgBuffers {
+  double *r, *z, *p, *w, *x, *dinv;
+  double *part_a, *part_b;  // per-CTA partials (two reductions per kernel)
+  KspState* st;
+};
+
+__global__ void jacobi_inv_kernel(int64_t n, const double* __restrict__ diag, double* __restrict__ dinv, int use) {
+  for (int64_t i = blockIdx.x * (int64_t)BLK + threadIdx.x; i < n; i += (int64_t)gridDim.x * BLK) {
+    const double d = diag[i];
+    dinv[i] = (use && d != 0.0) ? 1.0 / d : 1.0;  // PCJacobi replaces zero diagonal entries by one
+  }
+}
+
+// r = b, x = 0, z = M^-1 r, partials of z.z and z.r
+__global__ void cg_init_kernel(int64_t n, const double* __restrict__ b, CgBuffers B) {
+  __shared__ double sm[BLK / 32];
+  double szz = 0.0, szr = 0.0;
+  for (int64_t i = blockIdx.x * (int64_t)BLK + threadIdx.x; i < n; i += (int64_t)gridDim.x * BLK) {
+    const double r = b[i];
+    const double z = B.dinv[i] * r;
+    B.r[i] = r;
+    B.z[i] = z;
+    B.x[i] = 0.0;
+    B.p[i] = 0.0;
+    szz += z * z;
+    szr += z * r;
+  }
+  szz = pyn::block_sum<BLK>(szz, sm);
+  szr = pyn::block_sum<BLK>(szr, sm);
+  if (threadIdx.x == 0) {
+    B.part_a[blockIdx.x] = szz;
+    B.part_b[blockIdx.x] = szr;
+  }
+}
+
+__global__ void cg_scalar_init_kernel(int nparts, CgBuffers B, double rtol, double atol) {
+  const double zz = pyn::reduce_partials(B.part_a, nparts);
+  const double zr = pyn::reduce_partials(B.part_b, nparts);
+  if (threadIdx.x == 0) {
+    KspState* s = B.st;
+    s->dp = sqrt(zz);
+    s->rnorm0 = s->dp;
+    s->ttol = fmax(rtol * s->dp, atol);
+    s->beta = zr;
+    s->betaold = 1.0;
+    s->its = 0;
+    s->reason = 0;
+    s->done = 0;
+    if (s->dp <= s->ttol) {  // KSPConvergedDefault at iteration 0
+      s->reason = (s->dp <= atol) ? 3 : 2;
+      s->done = 1;
+    }
+  }
+}
+
+// p = z + (beta/betaold) p   (first iteration: p = z)
+__global__ void cg_pupdate_kernel(int64_t n, CgBuffers B) {
+  const KspState* s = B.st;
+  if (s->done) return;
+  const bool first = (s->its == 0);
+  const double b = first ? 0.0 : s->beta / s->betaold;
+  for (int64_t i = blockIdx.x * (int64_t)BLK + threadIdx.x; i < n; i += (int64_t)gridDim.x * BLK)
+    B.p[i] = first ? B.z[i] : B.z[i] + b * B.p[i];
+}
+
+// w = A p, per-CTA partial of p.w
+template <int LPR>
+__global__ void __launch_bounds__(BLK)
+cg_spmv_dot_kernel(int64_t nrows, const int64_t* __restrict__ ptr, const int* __restrict__ ind,
+                   const double* __restrict__ val, CgBuffers B) {
+  __shared__ double sm[BLK / 32];
+  if (B.st->done) return;
+  const int sub = threadIdx.x % LPR;
+  const int64_t rows_per_pass = ((int64_t)gridDim.x * BLK) / LPR;
+  const int64_t first = (blockIdx.x * (int64_t)BLK + threadIdx.x) / LPR;
+  const int64_t passes = (nrows + rows_per_pass - 1) / rows_per_pass;
+  double dot = 0.0;
+  for (int64_t it = 0; it < passes; ++it) {
+    const int64_t row = first + it * rows_per_pass;
+    const bool active = row < nrows;
+    const double s = pyn::spmv_row<LPR>(ptr, ind, val, B.p, row, active, sub);
+    if (active && sub == 0) {
+      B.w[row] = s;
+      dot += B.p[row] * s;
+    }
+  }
+  dot = pyn::block_sum<BLK>(dot, sm);
+  if (threadIdx.x == 0) B.part_a[blockIdx.x] = dot;
+}
+
+// a = beta / (p.w) ; x += a p ; r -= a w ; z = M^-1 r ; partials of z.z, z.r   (input partials: nparts_in of p.w)
+__global__ void cg_update_kernel(int64_t n, int nparts_in, CgBuffers B, double* __restrict__ out_a,
+                                 double* __restrict__ out_b) {
+  __shared__ double sm[BLK / 32];
+  __shared__ double s_a;
+  const KspState* s = B.st;
+  if (s->done) return;
+  if (threadIdx.x < 32) {
+    const double dpi = pyn::reduce_partials(B.part_a, nparts_in);
+    if (threadIdx.x == 0) s_a = s->beta / dpi;
+  }
+  __syncthreads();
+  const double a = s_a;
+  double szz = 0.0, szr = 0.0;
+  for (int64_t i = blockIdx.x * (int64_t)BLK + threadIdx.x; i < n; i += (int64_t)gridDim.x * BLK) {
+    B.x[i] += a * B.p[i];
+    const double r = B.r[i] - a * B.w[i];
+    const double z = B.dinv[i] * r;
+    B.r[i] = r;
+    B.z[i] = z;
+    szz += z * z;
+    szr += z * r;
+  }
+  szz = pyn::block_sum<BLK>(szz, sm);
+  szr = pyn::block_sum<BLK>(szr, sm);
+  if (threadIdx.x == 0) {
+    out_a[blockIdx.x] = szz;
+    out_b[blockIdx.x] = szr;
+  }
+}
+
+// end of iteration: norms, convergence test, new beta  (one warp)
+__global__ void cg_scalar_kernel(int nparts_pw, int nparts, CgBuffers B, const double* __restrict__ pzz,
+                                 const double* __restrict__ pzr, double atol, double dtol, int max_it) {
+  KspState* s = B.st;
+  if (s->done) return;
+  const double dpi = pyn::reduce_partials(B.part_a, nparts_pw);
+  const double zz = pyn::reduce_partials(pzz, nparts);
+  const double zr = pyn::reduce_partials(pzr, nparts);
+  if (threadIdx.x == 0) {
+    s->its += 1;
+    s->betaold = s->beta;
+    s->dp = sqrt(zz);
+    if (!(dpi > 0.0)) {  // KSP_DIVERGED_INDEFINITE_MAT
+      s->reason = -8;
+      s->done = 1;
+    } else if (s->dp <= s->ttol) {
+      s->reason = (s->dp <= atol) ? 3 : 2;
+      s->done = 1;
+    } else if (s->dp >= dtol * s->rnorm0) {
+      s->reason = -4;
+      s->done = 1;
+    } else if (s->its >= max_it) {
+      s->reason = -3;
+      s->done = 1;
+    }
+    s->beta = zr;
+    if (!s->done && zr == 0.0) {  // PETSc: beta == 0 at the top of the next iteration -> CONVERGED_ATOL
+      s->its += 1;
+      s->reason = 3;
+      s->done = 1;
+    }
+  }
+}
+
+__global__ void copy_kernel(int64_t n, const double* __restrict__ src, double* __restrict__ dst) {
+  for (int64_t i = blockIdx.x * (int64_t)BLK + threadIdx.x; i < n; i += (int64_t)gridDim.x * BLK) dst[i] = src[i];
+}
+
+}  // namespace
+
+struct pyn_ksp {
+  int64_t n, nnz;
+  const int64_t* ptr;
+  const int* ind;
+  const double* val;
+  pyn_ksp_opts opts;
+  CgBuffers B;
+  double *pzz, *pzr;
+  KspState* h_state;  // pinned
+  int vgrid, sgrid, lpr;
+  cudaGraphExec_t graph;
+  int graph_iters;
+  int64_t last_spmv, last_launches;
+};
+
+namespace {
+
+template <int LPR>
+void launch_spmv_dot(const pyn_ksp* k, cudaStream_t st) {
+  cg_spmv_dot_kernel<LPR><<<k->sgrid, BLK, 0, st>>>(k->n, k->ptr, k->ind, k->val, k->B);
+}
+
+void enqueue_cg_iteration(const pyn_ksp* k, cudaStream_t st) {
+  cg_pupdate_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, k->B);
+  switch (k->lpr) {
+    case 4: launch_spmv_dot<4>(k, st); break;
+    case 8: launch_spmv_dot<8>(k, st); break;
+    case 16: launch_spmv_dot<16>(k, st); break;
+    default: launch_spmv_dot<32>(k, st);
+  }
+  cg_update_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, k->sgrid, k->B, k->pzz, k->pzr);
+  cg_scalar_kernel<<<1, 32, 0, st>>>(k->sgrid, k->vgrid, k->B, k->pzz, k->pzr, k->opts.atol, k->opts.dtol, k->opts.max_it);
+}
+
+}  // namespace
+
+extern "C" {
+
+int pyn_ksp_create(int64_t nrows, const int64_t* d_ptr, const int32_t* d_ind, const double* d_val, int64_t nnz,
+                   const pyn_ksp_opts* opts, void* stream, pyn_ksp** out) {
+  PYN_REQUIRE(nrows > 0 && d_ptr && d_ind && d_val && opts && out, "bad arguments");
+  PYN_REQUIRE(opts->type == 0, "only cg (type 0) is available through pyn_ksp_create in this build");
+  PYN_REQUIRE(opts->nonzero_guess == 0, "nonzero initial guess is not supported (PETSc default is zero)");
+  cudaStream_t st = pyn::as_stream(stream);
+  pyn_ksp* k = new pyn_ksp();
+  memset(k, 0, sizeof(*k));
+  k->n = nrows; k->nnz = nnz; k->ptr = d_ptr; k->ind = d_ind; k->val = d_val; k->opts = *opts;
+  if (k->opts.check_every <= 0) k->opts.check_every = 16;
+  if (k->opts.max_it <= 0) k->opts.max_it = 10000;
+  k->vgrid = pyn::grid_for(nrows, BLK, 8);
+  k->lpr = pyn::pick_lpr(nrows, nnz);
+  {
+    const int64_t need = (nrows * k->lpr + BLK - 1) / BLK;
+    const int64_t cap = (int64_t)pyn::sm_count() * 16;
+    k->sgrid = (int)(need < cap ? need : cap);
+  }
+  double* pool = nullptr;
+  const size_t nparts = (size_t)(k->vgrid > k->sgrid ? k->vgrid : k->sgrid);
+  PYN_CHECK_CUDA(cudaMalloc(&pool, sizeof(double) * (6 * (size_t)nrows + 4 * nparts)));
+  k->B.r = pool; k->B.z = pool + nrows; k->B.p = pool + 2 * nrows; k->B.w = pool + 3 * nrows;
+  k->B.x = pool + 4 * nrows; k->B.dinv = pool + 5 * nrows;
+  k->B.part_a = pool + 6 * nrows; k->B.part_b = k->B.part_a + nparts;
+  k->pzz = k->B.part_b + nparts; k->pzr = k->pzz + nparts;
+  PYN_CHECK_CUDA(cudaMalloc(&k->B.st, sizeof(KspState)));
+  PYN_CHECK_CUDA(cudaMallocHost(&k->h_state, sizeof(KspState)));
+  // Jacobi: dinv = 1/diag(A)
+  int rc = pyn_csr_diagonal(nrows, d_ptr, d_ind, d_val, k->B.w, stream);
+  if (rc) return rc;
+  jacobi_inv_kernel<<<k->vgrid, BLK, 0, st>>>(nrows, k->B.w, k->B.dinv, opts->pc == 1);
+  PYN_CHECK_LAUNCH();
+  PYN_CHECK_CUDA(cudaStreamSynchronize(st));
+  *out = k;
+  return PYN_OK;
+}
+
+int pyn_ksp_solve(pyn_ksp* k, const double* d_b, double* d_x, pyn_ksp_result* res, void* stream) {
+  PYN_REQUIRE(k && d_b && d_x, "bad arguments");
+  cudaStream_t st = pyn::as_stream(stream);
+  int64_t launches = 0;
+  cg_init_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, d_b, k->B);
+  PYN_CHECK_LAUNCH();
+  cg_scalar_init_kernel<<<1, 32, 0, st>>>(k->vgrid, k->B, k->opts.rtol, k->opts.atol);
+  PYN_CHECK_LAUNCH();
+  launches += 2;
+  const int chunk = k->opts.check_every;
+  if (!k->graph || k->graph_iters != chunk) {
+    if (k->graph) cudaGraphExecDestroy(k->graph);
+    k->graph = nullptr;
+    cudaStream_t cs;
+    PYN_CHECK_CUDA(cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking));
+    cudaGraph_t g;
+    PYN_CHECK_CUDA(cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal));
+    for (int i = 0; i < chunk; ++i) enqueue_cg_iteration(k, cs);
+    PYN_CHECK_CUDA(cudaStreamEndCapture(cs, &g));
+    PYN_CHECK_CUDA(cudaGraphInstantiate(&k->graph, g, 0));
+    PYN_CHECK_CUDA(cudaGraphDestroy(g));
+    PYN_CHECK_CUDA(cudaStreamDestroy(cs));
+    k->graph_iters = chunk;
+  }
+  int enq = 0;
+  for (;;) {
+    PYN_CHECK_CUDA(cudaMemcpyAsync(k->h_state, k->B.st, sizeof(KspState), cudaMemcpyDeviceToHost, st));
+    PYN_CHECK_CUDA(cudaStreamSynchronize(st));
+    if (k->h_state->done || enq >= k->opts.max_it) break;
+    PYN_CHECK_CUDA(cudaGraphLaunch(k->graph, st));
+    enq += chunk;
+    launches += 4 * (int64_t)chunk;
+  }
+  pyn::count_launch((int)(4 * (int64_t)k->h_state->its));  // only the launches that did work are claimed
+  copy_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, k->B.x, d_x);
+  PYN_CHECK_LAUNCH();
+  PYN_CHECK_CUDA(cudaStreamSynchronize(st));
+  if (res) {
+    res->its = k->h_state->its;
+    res->reason = k->h_state->reason ? k->h_state->reason : -3;
+    res->rnorm0 = k->h_state->rnorm0;
+    res->rnorm = k->h_state->dp;
+  }
+  k->last_spmv = k->h_state->its;
+  k->last_launches = launches + 1;
+  return PYN_OK;
+}
+
+int pyn_ksp_destroy(pyn_ksp* k) {
+  if (!k) return PYN_OK;
+  if (k->graph) cudaGraphExecDestroy(k->graph);
+  cudaFree(k->B.r);
+  cudaFree(k->B.st);
+  cudaFreeHost(k->h_state);
+  delete k;
+  return PYN_OK;
+}
+
+int pyn_ksp_stats(const pyn_ksp* k, int64_t* spmv, int64_t* launches) {
+  PYN_REQUIRE(k, "ksp is NULL");
+  if (spmv) *spmv = k->last_spmv;
+  if (launches) *launches = k->last_launches;
+  return PYN_OK;
+}
+}

@@ -1,0 +1,37 @@
+// Topology handle shared between topo.cu and assemble.cu.
+#pragma once
+#include "common.cuh"
+
+struct pyn_topo {
+  int64_t ne, nnodes;
+  int nn;
+  const int* e2n;      // [ne][nn] borrowed from the caller (must outlive the handle)
+  int64_t* n2e_ptr;    // [nnodes+1]
+  int* n2e_elem;       // element ids ascending per node
+  short* n2e_loc;      // local index of the node inside that element
+  int64_t* adj_ptr;    // [nnodes+1]
+  int* adj_cols;       // sorted neighbour nodes (including the node itself)
+  int64_t adj_nnz;
+  int max_valence, max_row;
+};
+
+namespace pyn {
+struct TopoView {
+  int64_t ne, nnodes;
+  int nn;
+  const int* e2n;
+  const int64_t* n2e_ptr;
+  const int* n2e_elem;
+  const short* n2e_loc;
+  const int64_t* adj_ptr;
+  const int* adj_cols;
+};
+static inline TopoView view_of(const pyn_topo* t) {
+  TopoView v;
+  v.ne = t->ne; v.nnodes = t->nnodes; v.nn = t->nn; v.e2n = t->e2n;
+  v.n2e_ptr = t->n2e_ptr; v.n2e_elem = t->n2e_elem; v.n2e_loc = t->n2e_loc;
+  v.adj_ptr = t->adj_ptr; v.adj_cols = t->adj_cols;
+  return v;
+}
+int scan_counts(const int* d_cnt, int64_t n, int64_t* d_ptr, int64_t* h_total, cudaStream_t st);
+}  // namespace pyn

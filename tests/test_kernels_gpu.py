@@ -1,0 +1,302 @@
+"""GPU parity tests (through the C ABI): element kernels, numbering, assembly, SpMV, CG against the CPU oracle and
+the golden vectors of the reference.  Tolerances: 1e-12 relative (max-norm) for assembled / element values,
+bit-exact for index arrays and for the assembly sums given identical element matrices, 1e-10 for KSP solutions."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+import kle_oracle as o  # noqa: E402
+from conftest import rel_err  # noqa: E402
+
+TOL_ASM = 1e-12
+TOL_KSP = 1e-10
+
+
+@pytest.fixture(scope="module")
+def be():
+    import torch
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    from pynama_b200 import backend
+    return backend
+
+
+def _spectral(n):
+    from pynama_b200.elements.spectral import Spectral
+    return Spectral(n, 2)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("n", range(2, 10))
+def test_elem_kernels_vs_reference_golden(be, golden_elem, n):
+    s = _spectral(n)
+    for q in ("affine", "skew", "reftest"):
+        if f"K_{n}_{q}" not in golden_elem:
+            continue
+        c = golden_elem[f"coords_{q}"].reshape(-1).copy()
+        K, Rw, Rd = s.getElemKLEMatrices(c)
+        S, D, C, W = s.getElemKLEOperators(golden_elem[f"coords_{q}"].reshape(-1).copy())
+        for nm, a in zip(("K", "Rw", "Rd", "SrT", "DivSrT", "Curl", "W"), (K, Rw, Rd, S, D, C, W)):
+            assert rel_err(a, golden_elem[f"{nm}_{n}_{q}"]) < TOL_ASM, (nm, n, q)
+
+
+@pytest.mark.parametrize("n", [2, 3, 5, 8, 11])
+def test_elem_kernels_batched_random_quads(be, n):
+    rng = np.random.default_rng(n)
+    ne = 37
+    base = np.array([[0, 0], [1, 0], [1, 1], [0, 1]], float)
+    coords = (base[None] * rng.uniform(0.1, 0.5, (ne, 1, 2)) + rng.uniform(-1, 1, (ne, 1, 2))
+              + rng.uniform(-0.02, 0.02, (ne, 4, 2)))
+    s = _spectral(n)
+    K, Rw, Rd = s.getElemKLEMatricesDevice(be.to_device(coords))
+    S, D, C, W = s.getElemKLEOperatorsDevice(be.to_device(coords))
+    Ko, Rwo, Rdo = o.elem_kle_matrices(n, coords)
+    So, Do, Co, Wo = o.elem_kle_operators(n, coords)
+    for e in range(ne):
+        for nm, a, b in (("K", K, Ko), ("Rw", Rw, Rwo), ("Rd", Rd, Rdo), ("SrT", S, So), ("Div", D, Do),
+                         ("Curl", C, Co), ("W", W, Wo)):
+            assert rel_err(a[e].cpu().numpy(), b[e]) < TOL_ASM, (nm, e)
+    Kh = K.cpu().numpy()
+    assert np.abs(Kh - Kh.transpose(0, 2, 1)).max() == 0.0      # exactly symmetric, like the reference's B^T B
+
+
+def test_elem_identities(be):
+    """rigid translation in the null space, sum of weights = area."""
+    s = _spectral(5)
+    c = np.array([[0.02, -0.01], [0.31, 0.03], [0.27, 0.2], [-0.03, 0.15]])
+    K, Rw, Rd = s.getElemKLEMatrices(c.reshape(-1).copy())
+    S, D, C, W = s.getElemKLEOperators(c.reshape(-1).copy())
+    t = np.tile([0.7, -0.4], 25)
+    assert np.abs(K @ t).max() < 1e-9 * np.abs(K).max()
+    assert np.abs(C @ t).max() < 1e-12 * np.abs(C).max() * 25
+    area = 0.5 * abs(np.cross(c[2] - c[0], c[3] - c[1]))
+    assert abs(W.sum() - area) < 1e-14
+
+
+# ---------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("nx,ny,n", [(3, 4, 3), (2, 3, 2), (5, 2, 6), (1, 1, 4), (4, 4, 9)])
+def test_box_numbering_vs_oracle(be, nx, ny, n):
+    m = o.BoxMesh([nx, ny], [0.1, -0.2], [0.7, 0.6], n)
+    e2n = be.box_cell_nodes(nx, ny, n).cpu().numpy()
+    np.testing.assert_array_equal(e2n, m.cell_nodes())
+    cc = be.box_cell_corners(nx, ny, m.lower, m.upper).cpu().numpy()
+    np.testing.assert_allclose(cc, m.cell_corner_coords(), rtol=0, atol=1e-15)
+    s = _spectral(n)
+    xy = be.box_node_coords(nx, ny, n, m.lower, m.upper, s.nodes1D, s.localOrder, m.nnodes).cpu().numpy()
+    np.testing.assert_allclose(xy, m.node_coords(), rtol=0, atol=2e-16 * 4)
+
+
+def _upload_classes(be, cls):
+    return be.to_device(cls.astype(np.int8))
+
+
+def _same_pattern(A, ref):
+    ip, ix, _ = A.getValuesCSR()
+    np.testing.assert_array_equal(ip, ref.indptr)
+    np.testing.assert_array_equal(ix, ref.indices)
+
+
+@pytest.mark.parametrize("nx,ny,n", [(8, 8, 3), (4, 5, 5), (3, 3, 2), (2, 2, 7)])
+def test_assembly_freeslip_vs_oracle(be, nx, ny, n):
+    """K, Krhs, Rw of FreeSlip.buildKLEMats: pattern bit-exact; values bit-exact when fed the oracle's element
+    matrices, 1e-12 when integrated on the GPU."""
+    m = o.BoxMesh([nx, ny], [0, 0], [1, 1], n)
+    ref = o.assemble_freeslip(m, per_cell=True)
+    topo = be.Topology(be.box_cell_nodes(nx, ny, n), m.nnodes)
+    bc = np.zeros(m.nnodes, bool)
+    bc[m.boundary_nodes()] = True
+    cls = _upload_classes(be, np.repeat(np.where(bc, 2, 0), 2))
+    Ke_o, Rwe_o, _ = o.elem_kle_matrices(n, m.cell_corner_coords())
+    s = _spectral(n)
+    Ke_g, Rwe_g, _ = s.getElemKLEMatricesDevice(be.box_cell_corners(nx, ny, m.lower, m.upper), want_rd=False)
+    for Ke, Rwe, exact in ((be.to_device(Ke_o), be.to_device(Rwe_o), True), (Ke_g, Rwe_g, False)):
+        K = be.assemble(topo, 2, 2, Ke, cls, cls, [(0, 0)], diag_classes=0b100, diag_add=(0, 0, 1.0, 0))
+        Krhs = be.assemble(topo, 2, 2, Ke, cls, cls, [(0, 2)], diag_classes=0b100, diag_add=(0, 0, 1.0, 0), sign=-1.0)
+        Rw = be.assemble(topo, 2, 1, Rwe, cls, None, [(0, 0)])
+        for A, r in ((K, ref["K"]), (Krhs, ref["Krhs"]), (Rw, ref["Rw"])):
+            _same_pattern(A, r)
+            d = A.data.cpu().numpy()
+            if exact:
+                np.testing.assert_array_equal(d, r.data)
+            else:
+                assert rel_err(d, r.data) < TOL_ASM
+
+
+@pytest.mark.parametrize("nx,ny,n", [(8, 8, 3), (3, 4, 4)])
+def test_assembly_noslip_and_operators_vs_oracle(be, nx, ny, n):
+    """All eight MatNS matrices of the cavity + K+Kfs + the three operators (uniform mesh: cell 0's element)."""
+    m = o.BoxMesh([nx, ny], [0, 0], [1, 1], n)
+    ref = o.assemble_noslip(m)
+    topo = be.Topology(be.box_cell_nodes(nx, ny, n), m.nnodes)
+    cls = _upload_classes(be, ref["cls"])
+    c0 = m.cell_corner_coords([0])
+    Ke, Rwe, Rde = (be.to_device(a) for a in o.elem_kle_matrices(n, c0))
+    one = (0, 1.0, 1.0, 0)
+    got = {
+        "K": be.assemble(topo, 2, 2, Ke, cls, cls, [(0, 0)], diag_classes=0b110, diag_add=one),
+        "Krhs": be.assemble(topo, 2, 2, Ke, cls, cls, [(0, 1), (0, 2)], diag_classes=0b110, diag_add=one, sign=-1.0),
+        "Kfs": be.assemble(topo, 2, 2, Ke, cls, cls, [(1, 0), (0, 1), (1, 1)], diag_classes=0b010,
+                           diag_add=(0, -1.0, 0, 0)),
+        "Rw": be.assemble(topo, 2, 1, Rwe, cls, None, [(0, 0)]),
+        "Rd": be.assemble(topo, 2, 1, Rde, cls, None, [(0, 0)]),
+        "Rwfs": be.assemble(topo, 2, 1, Rwe, cls, None, [(1, 0)]),
+        "Rdfs": be.assemble(topo, 2, 1, Rde, cls, None, [(1, 0)]),
+        "Krhsfs": be.assemble(topo, 2, 2, Ke, cls, cls, [(1, 2), (0, 2)], diag_classes=0b100, diag_add=(0, 0, 1.0, 0),
+                              sign=-1.0),
+    }
+    for name, A in got.items():
+        _same_pattern(A, ref[name])
+        np.testing.assert_array_equal(A.data.cpu().numpy(), ref[name].data, err_msg=name)
+    KK = got["K"].add(got["Kfs"])
+    rKK = o.mat_add(ref["K"], ref["Kfs"])
+    _same_pattern(KK, rKK)
+    np.testing.assert_array_equal(KK.data.cpu().numpy(), rKK.data)
+    # operators
+    rops = o.assemble_operators(m)
+    S, D, C, W = (be.to_device(a) for a in o.elem_kle_operators(n, c0))
+    Wg = be.assemble_weights(topo, W)
+    np.testing.assert_array_equal(Wg.cpu().numpy(), rops["W"])
+    rW = 1.0 / Wg
+    for name, E, rd, cd in (("SrT", S, 3, 2), ("DivSrT", D, 2, 3), ("Curl", C, 1, 2)):
+        A = be.assemble(topo, rd, cd, E, rowscale=rW)
+        _same_pattern(A, rops[name])
+        np.testing.assert_array_equal(A.data.cpu().numpy(), rops[name].data, err_msg=name)
+        Ac = A.compressed()
+        sc = rops[name].copy()
+        sc.eliminate_zeros()
+        _same_pattern(Ac, sc)
+
+
+def test_coo_to_csr_generic(be):
+    """Mat.setValues(ADD)+assemble semantics: sorted, duplicates added in input order, explicit zeros kept."""
+    rng = np.random.default_rng(3)
+    n, nr, nc = 5000, 60, 45
+    rows, cols = rng.integers(0, nr, n), rng.integers(0, nc, n)
+    vals = rng.standard_normal(n)
+    vals[rng.integers(0, n, 200)] = 0.0
+    A = be.coo_to_csr(be.to_device(rows.astype(np.int32)), be.to_device(cols.astype(np.int32)), be.to_device(vals),
+                      (nr, nc))
+    ref = o.coo_to_csr(rows, cols, vals, (nr, nc))
+    _same_pattern(A, ref)
+    np.testing.assert_array_equal(A.data.cpu().numpy(), ref.data)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+def test_spmv_modes(be):
+    import scipy.sparse as sp
+    rng = np.random.default_rng(0)
+    for nr, nc, dens in ((300, 200, 0.02), (999, 666, 0.05), (64, 64, 0.9), (3 * 50, 2 * 50, 0.3)):
+        M = sp.random(nr, nc, dens, format="csr", random_state=1, dtype=np.float64)
+        M.sort_indices()
+        A = be.CSR((nr, nc), be.to_device(M.indptr.astype(np.int64)), be.to_device(M.indices.astype(np.int32)),
+                   be.to_device(M.data))
+        x, y0 = rng.standard_normal(nc), rng.standard_normal(nr)
+        xd = be.to_device(x)
+        y = be.to_device(y0.copy())
+        A.mult(xd, y)
+        ref = M @ x
+        scale = np.abs(M).dot(np.abs(x)).max()
+        assert np.abs(y.cpu().numpy() - ref).max() < 1e-14 * scale
+        y = be.to_device(y0.copy())
+        A.mult(xd, y, mode=1)
+        assert np.abs(y.cpu().numpy() - (y0 + ref)).max() < 1e-14 * (scale + 5)
+        y = be.to_device(y0.copy())
+        A.mult(xd, y, mode=2, p0=0.37)
+        assert np.abs(y.cpu().numpy() - 0.37 * ref).max() < 1e-14 * scale
+        if nr % 3 == 0 and nc % 2 == 0:
+            y = be.to_device(y0.copy())
+            A.mult(xd, y, mode=3, p0=0.02, p1=0.5, aux=xd)
+            want = 0.02 * ref - 0.5 * o.vtensv(x)[:nr]
+            assert np.abs(y.cpu().numpy() - want).max() < 1e-14 * (scale + 10)
+
+
+def test_vector_kernels(be):
+    import torch
+    rng = np.random.default_rng(1)
+    n = 100003
+    x, y = rng.standard_normal(n), rng.standard_normal(n)
+    xd, yd = be.to_device(x), be.to_device(y)
+    assert abs(be.vec_dot(xd, yd) - x @ y) < 1e-10
+    assert abs(be.vec_norm(xd) - np.linalg.norm(x)) < 1e-10
+    assert be.vec_norm(xd, 3) == np.abs(x).max()
+    be.vec_axpy(yd, 0.3, xd)
+    np.testing.assert_allclose(yd.cpu().numpy(), y + 0.3 * x, rtol=0, atol=1e-15)
+    out = be.empty(n)
+    be.vec_maxpy(out, xd, [0.5, -2.0], [yd, xd])
+    np.testing.assert_allclose(out.cpu().numpy(), x + 0.5 * (y + 0.3 * x) - 2.0 * x, rtol=0, atol=1e-14)
+    v = be.to_device(np.arange(1.0, 19.0))
+    t = be.empty(27)
+    be.vtensv(v, t)
+    np.testing.assert_array_equal(t.cpu().numpy(), o.vtensv(np.arange(1.0, 19.0)))      # test_solver.py:66-87
+    idx = be.to_device(np.array([5, 1, 7], dtype=np.int64))
+    z = be.zeros(10)
+    be.vec_scatter_set(z, idx, be.to_device(np.array([1.0, 2.0, 3.0])))
+    assert z.cpu().numpy().tolist() == [0, 2, 0, 0, 0, 1, 0, 3, 0, 0]
+    assert torch.cuda.is_available()
+
+
+def _freeslip_system(be, nx, ny, n):
+    m = o.BoxMesh([nx, ny], [0, 0], [1, 1], n)
+    ref = o.assemble_freeslip(m, per_cell=False)
+    xy = m.node_coords()
+    vel_ex, vort_ex = o.taylor_green(xy, 0.02, 0.0)
+    vel = np.zeros(2 * m.nnodes)
+    vel.reshape(-1, 2)[ref["bc_nodes"]] = vel_ex[ref["bc_nodes"]]
+    b = ref["Rw"] @ vort_ex + ref["Krhs"] @ vel
+    K = ref["K"]
+    A = be.CSR(K.shape, be.to_device(K.indptr.astype(np.int64)), be.to_device(K.indices.astype(np.int32)),
+               be.to_device(K.data))
+    return m, K, A, b, vel_ex
+
+
+@pytest.mark.parametrize("nx,n,rtol", [(8, 3, 1e-5), (8, 3, 1e-10), (6, 5, 1e-10)])
+def test_cg_jacobi_petsc_semantics(be, nx, n, rtol):
+    """Same recurrence, same (preconditioned) norm, same stopping test as the oracle's KSPCG restatement: identical
+    iteration count and reason, solution within 1e-10 relative."""
+    m, K, A, b, _ = _freeslip_system(be, nx, nx, n)
+    xo, its, reason, hist = o.ksp_cg_jacobi(K, b, rtol=rtol)
+    ksp = be.Ksp(A, "cg", "jacobi", rtol=rtol, check_every=7)
+    x = be.empty(K.shape[0])
+    r = ksp.solve(be.to_device(b), x)
+    assert (r.its, r.reason) == (its, reason)
+    assert abs(r.rnorm0 - hist[0]) < 1e-12 * hist[0] and abs(r.rnorm - hist[-1]) < 1e-6 * hist[-1] + 1e-18
+    assert rel_err(x.cpu().numpy(), xo) < TOL_KSP
+    # zero right-hand side converges at iteration 0 (KSPConvergedDefault)
+    r = ksp.solve(be.zeros(K.shape[0]), x)
+    assert r.its == 0 and r.reason in (2, 3)
+    # iteration cap
+    ksp2 = be.Ksp(A, "cg", "jacobi", rtol=1e-14, max_it=5, check_every=3)
+    r = ksp2.solve(be.to_device(b), x)
+    assert (r.its, r.reason) == (5, -3)
+
+
+def test_taylor_green_known_answer_gpu(be):
+    """src/tests/test_solver.py:29-37 on the GPU path: 2x2 elements, ngl 11, ||v - v_exact||_2 < 2e-8
+    (K assembled on device from device-integrated per-cell element matrices, CG to rtol 1e-13)."""
+    n, nx = 11, 2
+    m = o.BoxMesh([nx, nx], [0, 0], [1, 1], n)
+    s = _spectral(n)
+    topo = be.Topology(be.box_cell_nodes(nx, nx, n), m.nnodes)
+    bc = np.zeros(m.nnodes, bool)
+    bc[m.boundary_nodes()] = True
+    cls = _upload_classes(be, np.repeat(np.where(bc, 2, 0), 2))
+    Ke, Rwe, _ = s.getElemKLEMatricesDevice(be.box_cell_corners(nx, nx, m.lower, m.upper), want_rd=False)
+    K = be.assemble(topo, 2, 2, Ke, cls, cls, [(0, 0)], diag_classes=0b100, diag_add=(0, 0, 1.0, 0))
+    Krhs = be.assemble(topo, 2, 2, Ke, cls, cls, [(0, 2)], diag_classes=0b100, diag_add=(0, 0, 1.0, 0), sign=-1.0)
+    Rw = be.assemble(topo, 2, 1, Rwe, cls, None, [(0, 0)])
+    xy = be.box_node_coords(nx, nx, n, m.lower, m.upper, s.nodes1D, s.localOrder, m.nnodes)
+    vel_ex, vort = be.empty(2 * m.nnodes), be.empty(m.nnodes)
+    be.taylor_green(xy, 0.02, 0.0, vel_ex, vort)
+    vel = be.zeros(2 * m.nnodes)
+    bidx = be.to_device(m.boundary_nodes().astype(np.int64))
+    be.taylor_green(xy, 0.02, 0.0, vel, None, idx=bidx)
+    rhs, tmp = be.empty(2 * m.nnodes), be.empty(2 * m.nnodes)
+    Rw.mult(vort, rhs)
+    Krhs.mult(vel, rhs, mode=1)
+    ksp = be.Ksp(K, "cg", "jacobi", rtol=1e-13, max_it=20000)
+    sol = be.empty(2 * m.nnodes)
+    r = ksp.solve(rhs, sol)
+    assert r.reason > 0
+    err = sol - vel_ex
+    assert be.vec_norm(err) < 2e-8
+    del tmp

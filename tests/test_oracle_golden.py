@@ -1,0 +1,179 @@
+"""CPU tests: the oracle (oracle/kle_oracle.py) and the product's host tables against the golden vectors made by the
+UNMODIFIED reference (oracle/gen_golden.py) and against the reference's own known answers."""
+import math
+
+import numpy as np
+import pytest
+
+import kle_oracle as o
+from conftest import rel_err
+
+
+# ---- closed-form rules pinned by the reference (src/tests/test_element.py:181-229) -----------------------
+def test_gauss_closed_form():
+    x, w = o.gauss_points(2)
+    np.testing.assert_array_equal(x, [-1 / math.sqrt(3), 1 / math.sqrt(3)])
+    np.testing.assert_array_equal(w, [1, 1])
+    x, w = o.gauss_points(3)
+    np.testing.assert_allclose(x, [-math.sqrt(3 / 5), 0, math.sqrt(3 / 5)], atol=1e-12)
+    np.testing.assert_allclose(w, [5 / 9, 8 / 9, 5 / 9], atol=1e-12)
+
+
+def test_lobatto_closed_form():
+    exp = {2: ([-1, 1], [1, 1]), 3: ([-1, 0, 1], [1 / 3, 4 / 3, 1 / 3]),
+           4: ([-1, -1 / math.sqrt(5), 1 / math.sqrt(5), 1], [1 / 6, 5 / 6, 5 / 6, 1 / 6])}
+    for n, (x, w) in exp.items():
+        xx, ww = o.lobatto_points(n)
+        np.testing.assert_allclose(xx, x, atol=1e-12)
+        np.testing.assert_allclose(ww, w, atol=1e-12)
+
+
+def test_rules_match_reference(golden_tables):
+    from pynama_b200.elements.utilities import gaussPoints, lobattoPoints
+    for N in range(1, 12):
+        for fn in (o.gauss_points, gaussPoints):
+            x, w = fn(N)
+            np.testing.assert_array_equal(x, golden_tables[f"gauss_x_{N}"])
+            np.testing.assert_array_equal(w, golden_tables[f"gauss_w_{N}"])
+        if N >= 2:
+            for fn in (o.lobatto_points, lobattoPoints):
+                x, w = fn(N)
+                np.testing.assert_array_equal(x, golden_tables[f"lobatto_x_{N}"])
+                np.testing.assert_array_equal(w, golden_tables[f"lobatto_w_{N}"])
+
+
+@pytest.mark.parametrize("n", [2, 3, 4, 5])
+def test_tabulations_match_reference(golden_tables, n):
+    """H / Hrs / Gauss-point lists of Spectral(n,2): oracle and product host tables vs the reference, bit for bit."""
+    from pynama_b200.elements.spectral import Spectral
+    t = o.tables(n)
+    s = Spectral(n, 2)
+    pairs = {"H": (t.full.H, s.H), "Hrs": (t.full.Hrs, s.Hrs), "HRed": (t.red.H, s.HRed),
+             "HrsRed": (t.red.Hrs, s.HrsRed), "HOp": (t.op.H, s.HOp), "HrsOp": (t.op.Hrs, s.HrsOp),
+             "HCoo": (t.coo_full.H, s.HCoo), "HrsCoo": (t.coo_full.Hrs, s.HrsCoo),
+             "HCooRed": (t.coo_red.H, s.HCooRed), "HrsCooRed": (t.coo_red.Hrs, s.HrsCooRed),
+             "HCooOp": (t.coo_op.H, s.HCooOp), "HrsCooOp": (t.coo_op.Hrs, s.HrsCooOp)}
+    for name, (orc, prod) in pairs.items():
+        ref = golden_tables[f"tab_{name}_{n}"]
+        np.testing.assert_array_equal(orc, ref, err_msg=f"oracle {name}")
+        np.testing.assert_array_equal(np.array(prod), ref, err_msg=f"product {name}")
+    for name, tab, plist in (("gps", t.full, s.gps), ("gpsRed", t.red, s.gpsRed), ("gpsOp", t.op, s.gpsOp)):
+        ref = golden_tables[f"tab_{name}_{n}"]
+        np.testing.assert_array_equal(np.stack([tab.r, tab.s, tab.w], 1), ref)
+        np.testing.assert_array_equal(np.array([[g.r, g.s, g.w] for g in plist]), ref)
+
+
+def test_node_count_formulas():
+    """src/tests/test_element.py:231-266"""
+    from pynama_b200.elements.spectral import Spectral
+    for i, n in enumerate(range(2, 5)):
+        s = Spectral(n, 2)
+        assert s.nnode == n ** 2 and s.nnodedge == i and s.nnodcell == i ** 2
+
+
+@pytest.mark.parametrize("n", range(2, 10))
+def test_oracle_element_matrices_vs_reference(golden_elem, n):
+    for q in ("affine", "skew", "reftest"):
+        if f"K_{n}_{q}" not in golden_elem:
+            continue
+        c = golden_elem[f"coords_{q}"][None]
+        K, Rw, Rd = o.elem_kle_matrices(n, c)
+        S, D, C, W = o.elem_kle_operators(n, c)
+        for nm, a in zip(("K", "Rw", "Rd", "SrT", "DivSrT", "Curl", "W"), (K, Rw, Rd, S, D, C, W)):
+            assert rel_err(a[0], golden_elem[f"{nm}_{n}_{q}"]) < 1e-13, (nm, n, q)
+
+
+# ---- numbering: what the reference's test_domain.py pins ------------------------------------------------------
+def test_box_numbering_pins():
+    m = o.BoxMesh([3, 4], [0, 0], [0.6, 0.8], 3)
+    assert m.ncell == 12                                                        # test_domain.py:22-24
+    np.testing.assert_allclose(m.cell_corner_coords([0])[0].reshape(-1),
+                               [0, 0, 0.2, 0, 0.2, 0.2, 0, 0.2], atol=1e-13)      # :26-30
+    assert len(m.boundary_nodes()) == 28                                        # :32-42
+    for b in ("up", "down", "left", "right"):
+        assert len(m.border_nodes(b)) == (7 if b in ("up", "down") else 9)      # :44-50
+    for n in range(2, 10, 2):                                                   # :61-78
+        m = o.BoxMesh([2, 3], [0, 0], [0.6, 0.8], n)
+        assert len(m.boundary_nodes()) == 10 + 10 * (n - 2)
+        for b in ("up", "down", "left", "right"):
+            assert len(m.border_nodes(b)) == ((3 + 2 * (n - 2)) if b in ("up", "down") else (4 + 3 * (n - 2)))
+    for n in range(2, 14):                                                      # :187-195
+        m = o.BoxMesh([2, 3], [0, 0], [0.6, 0.8], n)
+        assert m.nnodes == 12 + 17 * (n - 2) + 6 * (n - 2) ** 2
+        assert len(np.unique(m.cell_nodes())) == m.nnodes
+    m = o.BoxMesh([2, 2], [0, 0], [1, 1], 2)                                    # :197-201 row-major numbering
+    np.testing.assert_allclose(m.node_coords(), [[0, 0], [.5, 0], [1, 0], [0, .5], [.5, .5], [1, .5],
+                                                 [0, 1], [.5, 1], [1, 1]], atol=1e-14)
+
+
+# ---- known answers of src/tests/test_solver.py ------------------------------------------------------------------
+def _direct(A, b):
+    import scipy.sparse.linalg as spl
+    return spl.spsolve(A.tocsc(), b)
+
+
+def test_uniform_flow_known_answer():
+    """test_solver.py:20-27: ||v - v_exact||_2 < 1e-12 (10x10, ngl 3)."""
+    m = o.BoxMesh([10, 10], [0, 0], [1, 1], 3)
+    A = o.assemble_freeslip(m)
+    vel = np.zeros(2 * m.nnodes)
+    vel.reshape(-1, 2)[A["bc_nodes"]] = [1.0, 0.0]
+    x = _direct(A["K"], A["Rw"] @ np.zeros(m.nnodes) + A["Krhs"] @ vel)
+    assert np.linalg.norm(x - np.tile([1.0, 0.0], m.nnodes)) < 1e-12
+
+
+def test_taylor_green_known_answer():
+    """test_solver.py:29-37: 2x2 elements, ngl 11: ||v - v_exact||_2 < 2e-8."""
+    m = o.BoxMesh([2, 2], [0, 0], [1, 1], 11)
+    A = o.assemble_freeslip(m)
+    vel_ex, vort_ex = o.taylor_green(m.node_coords(), 0.01 / 0.5, 0.0)
+    vel = np.zeros(2 * m.nnodes)
+    vel.reshape(-1, 2)[A["bc_nodes"]] = vel_ex[A["bc_nodes"]]
+    x = _direct(A["K"], A["Rw"] @ vort_ex + A["Krhs"] @ vel)
+    assert np.linalg.norm(x - vel_ex.reshape(-1)) < 2e-8
+
+
+def test_vtensv_known_answer():
+    """test_solver.py:66-87"""
+    v = np.arange(1.0, 19.0)
+    ref = np.array([[a * a, a * b, b * b] for a, b in v.reshape(-1, 2)]).reshape(-1)
+    np.testing.assert_array_almost_equal(o.vtensv(v), ref, decimal=10)
+
+
+def test_cavity_matrices_structure():
+    """No reference-side known answer exists for the cavity: structural identities only."""
+    m = o.BoxMesh([6, 6], [0, 0], [1, 1], 3)
+    B = o.assemble_noslip(m)
+    KK = o.mat_add(B["K"], B["Kfs"])
+    assert abs(B["K"] - B["K"].T).max() == 0 and abs(KK - KK.T).max() < 1e-12
+    assert np.linalg.eigvalsh(KK.toarray()).min() > 0 and np.linalg.eigvalsh(B["K"].toarray()).min() > 0
+    cls = B["cls"]
+    d = B["K"].diagonal()
+    np.testing.assert_array_equal(d[cls > 0], 1.0)
+    ops = o.assemble_operators(m)
+    assert abs(ops["W"].sum() - 1.0) < 1e-13                       # sum of lumped weights = area
+    vel = np.tile([0.3, -0.2], m.nnodes)                            # rigid translation
+    assert np.abs(ops["Curl"] @ vel).max() < 1e-12 and np.abs(ops["SrT"] @ vel).max() < 1e-12
+
+
+def test_rk5bs_tableau_order_conditions():
+    A, b, bh, c = o.rk5bs_tableau()
+    np.testing.assert_allclose(A.sum(1), c, atol=1e-15)
+    np.testing.assert_allclose(A[7, :7], b[:7], atol=0)              # FSAL
+    for k in range(1, 6):                                           # quadrature conditions up to order 5 / 4
+        assert abs(b @ c ** (k - 1) - 1.0 / k) < 1e-14
+        if k <= 4:
+            assert abs(bh @ c ** (k - 1) - 1.0 / k) < 1e-14
+    y, err, _ = o.rk5bs_step(lambda t, y: -y, 0.0, np.array([1.0]), 0.1)
+    assert abs(y[0] - math.exp(-0.1)) < 1e-9
+
+
+def test_rhs_chain_taylor_green_decay():
+    """d(omega)/dt = -8 pi^2 nu omega for Taylor-Green: spectral convergence of the operator chain."""
+    m = o.BoxMesh([4, 4], [0, 0], [1, 1], 9)
+    ops = o.assemble_operators(m)
+    nu, rho, mu = 0.02, 0.5, 0.01
+    vel, vort = o.taylor_green(m.node_coords(), nu, 0.0)
+    f = o.eval_rhs_from_vel(ops, vel.reshape(-1), rho, mu)
+    interior = np.setdiff1d(np.arange(m.nnodes), m.boundary_nodes())
+    assert np.abs(f[interior] - (-8 * math.pi ** 2 * nu) * vort[interior]).max() < 5e-2 * np.abs(vort).max()
