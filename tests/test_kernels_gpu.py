@@ -262,7 +262,10 @@ def test_cg_jacobi_petsc_semantics(be, nx, n, rtol):
     assert (r.its, r.reason) == (its, reason)
     assert abs(r.rnorm0 - hist[0]) < 1e-12 * hist[0]
     assert r.rnorm <= max(rtol * r.rnorm0, 1e-50) and 0.5 * hist[-1] < r.rnorm < 2.0 * hist[-1]
-    assert rel_err(x.cpu().numpy(), xo) < TOL_KSP
+    # 1e-10 at rtol <= 1e-10 (north_star).  At a looser rtol both iterates stop ~rtol away from the solution and CG's
+    # round-off amplification separates any two summation orders by ~4e-9 here (measured oracle-vs-row-permuted
+    # oracle, see DESIGN.md "KSP parity"), so the bound there is 1e-3 * rtol.
+    assert rel_err(x.cpu().numpy(), xo) < max(TOL_KSP, 1e-3 * rtol)
     # zero right-hand side converges at iteration 0 (KSPConvergedDefault)
     r = ksp.solve(be.zeros(K.shape[0]), x)
     assert r.its == 0 and r.reason in (2, 3)
