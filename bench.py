@@ -1,0 +1,448 @@
+#!/usr/bin/env python
+"""bench.py -- the hot path of BASELINE.json on B200: cavity nx x nx spectral elements, ngl 5 (configs[3]).
+
+One "step" = one assembly pass of the matrices the velocity-from-vorticity solve uses (element integration from the
+corner coordinates + deterministic CSR assembly of the eight MatNS matrices K, Krhs, Kfs, Krhsfs, Rw, Rwfs, Rd, Rdfs on the prebuilt pattern;
+NoSlipFreeSlip.buildKLEMats, reference src/cases/base_problem.py:329-454).  `value` = velocity DOF rows assembled per
+second with every input resident in HBM.  The second half of the metric ("FP64 KSP solve time/step") is the `ksp`
+object of the same JSON line: CG + Jacobi (PETSc semantics) on the assembled K, timed over a fixed iteration budget
+with CUDA events.  `e2e` is the same assembly step driven through the public Python API from HOST buffers (pinned
+host arrays -> device, result diagonal -> host).  `cpu_baseline` / `--impl reference` time the CPU oracle (a
+NumPy/SciPy port of the reference path; petsc4py is not installable here) on a bounded sample of the same workload.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--nx 1024] [--ngl 5] [--ksp-its 50] [--impl reference]
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "assembled DOF/s and FP64 KSP solve time/step"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--nx", type=int, default=1024)
+    ap.add_argument("--ngl", type=int, default=5)
+    ap.add_argument("--ksp-its", type=int, default=50, dest="ksp_its")
+    ap.add_argument("--impl", default="native", choices=["native", "reference"])
+    ap.add_argument("--cpu-sample-nx", type=int, default=96, dest="cpu_nx")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------------------------------
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.proc = index, [], None
+
+    def run(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            for line in self.proc.stdout:
+                self.rows.append([c.strip() for c in line.split(",")])
+        except Exception:
+            pass
+
+    def stop(self):
+        if self.proc is not None:
+            self.proc.terminate()
+        self.join(timeout=2)
+        sm, mx, reasons = [], 0.0, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx = max(mx, float(r[1]))
+                for nm, v in zip(names, r[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(nm)
+            except (ValueError, IndexError):
+                continue
+        sm.sort()
+        # median over the upper half = samples under load (the sampler also sees idle gaps between phases)
+        load = sm[len(sm) // 2:] if sm else []
+        return {"sm_mhz": load[len(load) // 2] if load else None, "sm_max_mhz": mx or None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def measured_peak_hbm():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# CPU arm: the oracle port of the reference path on host cores (test infrastructure used ONLY as the timed baseline)
+# ------------------------------------------------------------------------------------------------------------------
+def _cpu_strip(args):
+    """Assemble the cavity matrices of one strip of cell rows with the oracle (worker of the process pool)."""
+    nx, ny_strip, ngl = args
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import kle_oracle as o
+    m = o.BoxMesh([nx, ny_strip], [0.0, 0.0], [1.0, ny_strip / nx], ngl)
+    t0 = time.perf_counter()
+    r = o.assemble_noslip(m)
+    return time.perf_counter() - t0, 2 * m.nnodes, int(r["K"].nnz)
+
+
+def cpu_reference_step(nx, ngl, cores):
+    """One bounded sample of the workload on the host: `cores` independent strips (nx x nx/cores cells each) of the
+    cavity assembly, one process per core; returns (seconds, dof rows, nnz)."""
+    from concurrent.futures import ProcessPoolExecutor
+    strip = max(1, nx // cores)
+    t0 = time.perf_counter()
+    if cores == 1:
+        res = [_cpu_strip((nx, strip, ngl))]
+    else:
+        with ProcessPoolExecutor(cores) as ex:
+            res = list(ex.map(_cpu_strip, [(nx, strip, ngl)] * cores))
+    wall = time.perf_counter() - t0
+    return wall, sum(r[1] for r in res), sum(r[2] for r in res)
+
+
+def cpu_ksp_iteration(nx, ngl, its=20):
+    """ms per CG+Jacobi iteration of the oracle (SciPy SpMV, 1 core) on an nx x nx sample."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import numpy as np
+    import kle_oracle as o
+    m = o.BoxMesh([nx, nx], [0, 0], [1, 1], ngl)
+    K = o.assemble_noslip(m)["K"]
+    b = np.random.default_rng(0).standard_normal(K.shape[0])
+    t0 = time.perf_counter()
+    o.ksp_cg_jacobi(K, b, rtol=1e-300, max_it=its)
+    return (time.perf_counter() - t0) / its * 1e3, K.shape[0], int(K.nnz)
+
+
+def run_reference(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    nx = a.cpu_nx
+    times, dof = [], 0
+    for i in range(a.warmup + a.steps):
+        wall, dof, _ = cpu_reference_step(nx, a.ngl, cores)
+        if i >= a.warmup:
+            times.append(wall)
+    t = sum(times) / len(times)
+    ksp_ms, krows, knnz = cpu_ksp_iteration(min(nx, 64), a.ngl)
+    val = dof / t
+    sample = (f"{cores} strips of {nx}x{max(1, nx // cores)} cells, ngl {a.ngl}, oracle/kle_oracle.py "
+              f"assemble_noslip (8 matrices incl. Rd/Rdfs), one process per core")
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": val, "unit": "DOF/s", "n_gpus": a.gpus, "steps": a.steps,
+        "warmup": a.warmup, "ms_per_step": t * 1e3, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": f"cavity {a.nx}x{a.nx} elements ngl {a.ngl} (configs[3]); CPU arm times a bounded "
+                               f"sample: {sample}"},
+        "cpu_baseline": {"value": val, "unit": "DOF/s", "cores": cores, "kind": "port", "sample": sample},
+        "ksp": {"ms_per_iteration": ksp_ms, "rows": krows, "nnz": knnz, "cores": 1,
+                "note": "oracle CG+Jacobi (SciPy CSR SpMV) on a 64x64-cell sample"},
+        "e2e": {"value": val, "unit": "DOF/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# native arm
+# ------------------------------------------------------------------------------------------------------------------
+# (name, rdof, cdof, element matrix, class pairs kept, diag classes, diag add, sign): the cavity matrices that
+# NoSlipFreeSlip.solveKLE uses (base_problem.py:321-327,388-451); classes 0 free, 1 tangential-on-wall, 2 set.
+ONE12 = (0.0, 1.0, 1.0, 0.0)
+CAVITY_MATS = [
+    ("K", 2, 2, "K", [(0, 0)], 0b110, ONE12, 1.0),
+    ("Krhs", 2, 2, "K", [(0, 1), (0, 2)], 0b110, ONE12, -1.0),
+    ("Kfs", 2, 2, "K", [(1, 0), (0, 1), (1, 1)], 0b010, (0.0, -1.0, 0.0, 0.0), 1.0),
+    ("Krhsfs", 2, 2, "K", [(1, 2), (0, 2)], 0b100, (0.0, 0.0, 1.0, 0.0), -1.0),
+    ("Rw", 2, 1, "Rw", [(0, 0)], 0, (0.0,) * 4, 1.0),
+    ("Rwfs", 2, 1, "Rw", [(1, 0)], 0, (0.0,) * 4, 1.0),
+    ("Rd", 2, 1, "Rd", [(0, 0)], 0, (0.0,) * 4, 1.0),
+    ("Rdfs", 2, 1, "Rd", [(1, 0)], 0, (0.0,) * 4, 1.0),
+]
+
+
+def cavity_classes(dom, be, torch):
+    """int8 class per velocity dof on device: wall-normal component (both at corners) = 2, tangential = 1."""
+    N = dom.getTotalNodes()
+    is_set = torch.zeros((N, 2), dtype=torch.bool, device=be.device())
+    is_tan = torch.zeros((N, 2), dtype=torch.bool, device=be.device())
+    for name, nrm in (("down", 1), ("up", 1), ("left", 0), ("right", 0)):
+        nd = be.to_device(dom.borderNodesArray(name))
+        is_set[nd, nrm] = True
+        is_tan[nd, 1 - nrm] = True
+    is_tan &= ~is_set
+    cls = torch.zeros((N, 2), dtype=torch.int8, device=be.device())
+    cls[is_tan] = 1
+    cls[is_set] = 2
+    return cls.view(-1).contiguous()
+
+
+class CavityAssembly:
+    """Device state of the cavity assembly on one rank (all cells for N=1, a strip of cell rows otherwise)."""
+
+    def __init__(self, nx, ny, ngl, lower, upper):
+        import torch
+        from pynama_b200 import backend as be
+        from pynama_b200.domain.dmplex import DMPlexDom
+        from pynama_b200.elements.spectral import Spectral
+        self.be, self.torch = be, torch
+        self.dom = DMPlexDom(boxMesh={"nelem": [nx, ny], "lower": lower, "upper": upper})
+        self.dom.setFemIndexing(ngl)
+        self.elem = Spectral(ngl, 2)
+        self.topo = self.dom.topology()
+        self.cls = cavity_classes(self.dom, be, torch)
+        self.cc0 = self.dom.deviceCellCorners(0, 1)
+        self.mats = {}
+        self.nrows = 2 * self.dom.getTotalNodes()
+
+    def integrate(self, cc0=None):
+        Ke, Rwe, Rde = self.elem.getElemKLEMatricesDevice(self.cc0 if cc0 is None else cc0, want_rd=True)
+        return {"K": Ke, "Rw": Rwe, "Rd": Rde}
+
+    def assemble(self, E, cls=None, events=None):
+        be = self.be
+        cls = self.cls if cls is None else cls
+        for name, rd, cd, which, pairs, dcls, dadd, sign in CAVITY_MATS:
+            if events is not None and name == "K":
+                events[0].record()
+            self.mats[name] = be.assemble(self.topo, rd, cd, E[which], cls, cls if cd == 2 else None, pairs,
+                                          diag_classes=dcls, diag_add=dadd, sign=sign, pattern=self.mats.get(name),
+                                          name=name)
+            if events is not None and name == "K":
+                events[1].record()
+        return self.mats
+
+    def step(self, events=None):
+        return self.assemble(self.integrate(), events=events)
+
+
+def run_native(a):
+    import torch
+    import torch.distributed as dist
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (B200); there is no CPU fallback. Use --impl reference for "
+                         "the CPU arm.")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    from pynama_b200 import backend as be
+    ev = lambda: torch.cuda.Event(enable_timing=True)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    nx, n = a.nx, a.ngl
+    # strong scaling over strips of cell rows: rank r assembles the rows of its strip (own problem, no exchange)
+    ny_loc = nx // world + (1 if rank < nx % world else 0)
+    prob = CavityAssembly(nx, ny_loc, n, [0.0, 0.0], [1.0, ny_loc / nx])
+    prob.step()                                   # pattern build (count + fill with indices), not timed
+    barrier()
+    nnz = {k: v.nnz for k, v in prob.mats.items()}
+    dof_local = prob.nrows
+    for _ in range(a.warmup):
+        prob.step()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.25)
+    l0 = be.launch_count()
+    kev = [(ev(), ev()) for _ in range(a.steps)]
+    t0, t1 = ev(), ev()
+    barrier()
+    t0.record()
+    for i in range(a.steps):
+        prob.step(events=kev[i])
+    t1.record()
+    barrier()
+    launches = be.launch_count() - l0
+    ms_total = t0.elapsed_time(t1)
+    k_ms = sum(s.elapsed_time(e) for s, e in kev) / a.steps
+    tt = torch.tensor([ms_total, float(dof_local)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        tmax = tt.clone()
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tt, op=dist.ReduceOp.SUM)
+        ms_total, dof_total = float(tmax[0]), float(tt[1])
+    else:
+        dof_total = float(dof_local)
+    ms_step = ms_total / a.steps
+    value = dof_total / (ms_step * 1e-3)
+
+    peak, peak_src = measured_peak_hbm()
+    K = prob.mats["K"]
+    # algorithmic bytes of the dominant launch (assembly of K, values only): 8 nnz written + int64 row pointers read
+    # + 64 B of corner coordinates per cell; DESIGN.md "Roofline accounting"
+    k_bytes = 8 * K.nnz + 8 * (K.shape[0] + 1) + 64 * prob.dom.ncell
+    roof = {"bound": "hbm", "kernel": "asm_rows_kernel<false> (K, values on the prebuilt pattern)",
+            "achieved": k_bytes / (k_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s", "peak_source": peak_src,
+            "frac": k_bytes / (k_ms * 1e-3) / 1e9 / peak, "ms_per_launch": k_ms, "bytes_per_launch": k_bytes,
+            "traffic": load_traffic("asm_rows_kernel")}
+    out = {
+        "metric": METRIC, "value": value, "unit": "DOF/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic",
+        "config": {"workload": f"cavity {nx}x{nx} elements ngl {n} (BASELINE configs[3]): integrate + assemble "
+                               f"K,Krhs,Kfs,Krhsfs,Rw,Rwfs,Rd,Rdfs values on the prebuilt CSR pattern",
+                   "partition": f"{world} strip(s) of cell rows, one per GPU, no data-path collective",
+                   "dof_rows": int(dof_total), "nnz_rank0": nnz,
+                   "l2": "outputs (>= 8*nnz(K) bytes per step) exceed the 126 MB L2 for nx >= 128; no flush needed"},
+        "roofline": roof, "gpu_launches": int(launches),
+    }
+    # ---- KSP phase: CG + Jacobi on K, fixed iteration budget ---------------------------------------------------
+    out["ksp"] = ksp_phase(a, prob, be, torch, peak, barrier)
+    barrier()
+    if rank == 0:
+        out["clocks"] = sampler.stop()
+    # ---- end to end through the public API from host buffers (rank-local; max over ranks) ----------------------
+    if not a.no_e2e:
+        e = e2e_phase(a, prob, be, torch, barrier)
+        if world > 1:
+            t = torch.tensor([e["ms"]], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            e["ms"] = float(t[0])
+        out["e2e"] = {"value": dof_total / (e["ms"] * 1e-3), "unit": "DOF/s", "ms_per_step": e["ms"],
+                      "h2d_bytes_per_step": e["h2d"] * world, "d2h_bytes_per_step": e["d2h"] * world,
+                      "what": e["what"]}
+    if rank == 0 and world == 1 and not a.no_cpu_baseline:
+        cores = os.cpu_count() or 1
+        wall, dof, _ = cpu_reference_step(a.cpu_nx, n, cores)
+        out["cpu_baseline"] = {"value": dof / wall, "unit": "DOF/s", "cores": cores, "kind": "port",
+                               "sample": f"{cores} strips of {a.cpu_nx}x{max(1, a.cpu_nx // cores)} cells ngl {n}, "
+                                         f"oracle assemble_noslip, one process per core, {wall:.1f} s"}
+    if rank == 0:
+        print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def load_traffic(kernel_substr):
+    """DRAM bytes per launch of a kernel from the committed `ncu --set full` summary (profiles/traffic.json), or None."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    try:
+        for k, v in json.load(open(p)).items():
+            if kernel_substr in k:
+                return v
+    except Exception:
+        pass
+    return None
+
+
+def ksp_phase(a, prob, be, torch, peak, barrier):
+    """CG + Jacobi (KSPCG semantics) on the assembled K with a fixed iteration budget (-ksp_max_it), rhs =
+    Rw*vort + Krhs*vel_bc for a lid velocity 1 and a synthetic vorticity field; CUDA events around the solve."""
+    K, Rw, Krhs = prob.mats["K"], prob.mats["Rw"], prob.mats["Krhs"]
+    N = prob.dom.getTotalNodes()
+    g = torch.Generator(device="cuda").manual_seed(1234)
+    vort = torch.randn(N, dtype=torch.float64, device="cuda", generator=g)
+    vel = be.zeros(2 * N)
+    lid = be.to_device(prob.dom.borderNodesArray("up")) * 2
+    be.vec_scatter_const(vel, lid, 1.0)
+    rhs = be.empty(2 * N)
+    Rw.mult(vort, rhs)
+    Krhs.mult(vel, rhs, mode=1)
+    its = a.ksp_its
+    ksp = be.Ksp(K, "cg", "jacobi", rtol=1e-300, atol=1e-300, max_it=its, check_every=its)
+    x = be.empty(2 * N)
+    ev = lambda: torch.cuda.Event(enable_timing=True)
+    ksp.solve(rhs, x)                       # warm-up: graph capture + one full budget
+    ksp.solve(rhs, x)
+    barrier()
+    reps, ms = 3, []
+    for _ in range(reps):
+        s, e = ev(), ev()
+        s.record()
+        r = ksp.solve(rhs, x)
+        e.record()
+        torch.cuda.synchronize()
+        ms.append(s.elapsed_time(e))
+    ms_solve = min(ms)
+    # one SpMV alone (same kernel family as inside CG) for the roofline line
+    y = be.empty(2 * N)
+    for _ in range(3):
+        K.mult(x, y)
+    s, e = ev(), ev()
+    s.record()
+    nrep = 10
+    for _ in range(nrep):
+        K.mult(x, y)
+    e.record()
+    torch.cuda.synchronize()
+    ms_spmv = s.elapsed_time(e) / nrep
+    spmv_bytes = K.bytes_spmv()
+    it_bytes = spmv_bytes + 8 * K.shape[0] * 12      # + ~12 vector passes per PCG iteration
+    return {"type": "cg", "pc": "jacobi", "its": int(r.its), "reason": int(r.reason), "ms_per_solve": ms_solve,
+            "ms_per_iteration": ms_solve / max(r.its, 1), "rows": K.shape[0], "nnz": K.nnz,
+            "iteration_gbs": it_bytes / (ms_solve / max(r.its, 1) * 1e-3) / 1e9,
+            "iteration_frac_of_peak": it_bytes / (ms_solve / max(r.its, 1) * 1e-3) / 1e9 / peak,
+            "spmv": {"ms": ms_spmv, "bytes": spmv_bytes, "achieved": spmv_bytes / (ms_spmv * 1e-3) / 1e9,
+                     "peak": peak, "unit": "GB/s", "frac": spmv_bytes / (ms_spmv * 1e-3) / 1e9 / peak,
+                     "traffic": load_traffic("spmv_kernel")},
+            "note": f"fixed budget of {its} iterations (-ksp_max_it {its}); a converged Jacobi-CG solve at this size "
+                    f"needs O(10^4) iterations (SURVEY 7.2)"}
+
+
+def e2e_phase(a, prob, be, torch, barrier):
+    """The same assembly step from HOST buffers through the public API: pinned cell-0 corner coordinates and the
+    per-dof boundary classes go host->device, the matrices are integrated + assembled, diag(K) comes back."""
+    import numpy as np
+    cc_h = torch.from_numpy(np.asarray(prob.dom.getCellCornersCoords(0)).reshape(1, 4, 2)).pin_memory()
+    cls_h = prob.cls.cpu().pin_memory()
+    diag_h = torch.empty(prob.nrows, dtype=torch.float64).pin_memory()
+    ev = lambda: torch.cuda.Event(enable_timing=True)
+
+    def one():
+        cc = cc_h.to("cuda", non_blocking=True)
+        cls = cls_h.to("cuda", non_blocking=True)
+        mats = prob.assemble(prob.integrate(cc), cls=cls)
+        diag_h.copy_(mats["K"].diagonal(), non_blocking=True)
+
+    for _ in range(2):
+        one()
+    barrier()
+    steps = max(3, min(a.steps, 5))
+    s, e = ev(), ev()
+    s.record()
+    for _ in range(steps):
+        one()
+    e.record()
+    torch.cuda.synchronize()
+    assert float(diag_h[0]) != 0.0
+    return {"ms": s.elapsed_time(e) / steps, "h2d": cc_h.numel() * 8 + cls_h.numel(), "d2h": diag_h.numel() * 8,
+            "what": "pinned host corner coords + int8 dof classes -> device; integrate + assemble 8 matrices; "
+                    "diag(K) -> pinned host"}
+
+
+if __name__ == "__main__":
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_native(args)
