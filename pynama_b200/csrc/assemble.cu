@@ -24,86 +24,102 @@ struct DescView {
   const double* rowscale;
 };
 
-__device__ __forceinline__ int lower_bound_smem(const int* __restrict__ a, int n, int key) {
-  int lo = 0, hi = n;
-  while (lo < hi) {
-    const int mid = (lo + hi) >> 1;
-    if (a[mid] < key) lo = mid + 1; else hi = mid;
-  }
-  return lo;
-}
-
-template <bool COUNT>
-__global__ void __launch_bounds__(128)
-asm_rows_kernel(pyn::TopoView t, DescView d, int Lmax, int* __restrict__ rowcnt, const int64_t* __restrict__ indptr,
-                int* __restrict__ indices, double* __restrict__ data) {
-  extern __shared__ double smd[];
-  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, wpb = blockDim.x >> 5;
-  const int rd = d.rdof, cd = d.cdof, blk = rd * cd;
-  const int per_warp_dbl = COUNT ? (Lmax + 1) / 2 : Lmax * blk + (Lmax + 1) / 2;
-  double* acc = smd + (size_t)w * per_warp_dbl;
-  int* scols = COUNT ? (int*)acc : (int*)(acc + Lmax * blk);
+// One warp per mesh node (= RD consecutive matrix rows); lanes stride over the node's sorted adjacency row.  Every
+// lane owns whole output blocks: for adjacency position p it gathers, in ascending cell order, the RD x CD block of
+// each incident element that contains column node p (inverse position map of the topology handle), so there are no
+// shared-memory accumulators, no atomics and no intra-warp ordering hazards.  COUNT only counts kept entries.
+template <int RD, int CD, bool COUNT>
+__global__ void __launch_bounds__(256)
+asm_gather_kernel(pyn::TopoView t, DescView d, int* __restrict__ rowcnt, const int64_t* __restrict__ indptr,
+                  int* __restrict__ indices, double* __restrict__ data) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp0 = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
   const bool values = (!COUNT) && (data != nullptr);
-  const bool square = (rd == cd);
-
-  for (int64_t r = blockIdx.x * (int64_t)wpb + w; r < t.nnodes; r += (int64_t)gridDim.x * wpb) {
-    const int64_t a0 = t.adj_ptr[r];
-    const int L = (int)(t.adj_ptr[r + 1] - a0);
-    for (int i = lane; i < L; i += 32) scols[i] = t.adj_cols[a0 + i];
-    if (values)
-      for (int i = lane; i < L * blk; i += 32) acc[i] = 0.0;
-    __syncwarp();
-    if (values) {
-      const int64_t b0 = t.n2e_ptr[r];
-      const int deg = (int)(t.n2e_ptr[r + 1] - b0);
-      for (int k = 0; k < deg; ++k) {  // ascending cell order
-        const int e = t.n2e_elem[b0 + k];
-        const int lr = t.n2e_loc[b0 + k];
-        const double* Ee = d.E + (d.E_stride ? (int64_t)e * d.E_stride : 0) + (int64_t)lr * rd * (cd * t.nn);
-        const int* en = t.e2n + (int64_t)e * t.nn;
-        for (int l = lane; l < t.nn; l += 32) {
-          const int c = en[l];
-          const int p = lower_bound_smem(scols, L, c);
-          for (int a = 0; a < rd; ++a)
-            for (int b = 0; b < cd; ++b)
-              acc[(p * rd + a) * cd + b] += d.sign * Ee[(int64_t)a * (cd * t.nn) + l * cd + b];
-        }
-        __syncwarp();
-      }
+  const unsigned lt = (1u << lane) - 1u;
+  const int ldE = CD * t.nn;
+  for (int64_t r = warp0; r < t.nnodes; r += nwarps) {
+    const int64_t a0 = t.adj_ptr[r], b0 = t.n2e_ptr[r];
+    const int L = (int)(t.adj_ptr[r + 1] - a0), deg = (int)(t.n2e_ptr[r + 1] - b0);
+    const int64_t iv0 = values ? t.inv_ptr[r] : 0;
+    int my_e = 0, my_lr = 0;
+    if (values && lane < deg) {
+      my_e = t.n2e_elem[b0 + lane];
+      my_lr = t.n2e_loc[b0 + lane];
+    }
+    int rca[RD];
+    int64_t base[RD];
+    int running[RD];
+#pragma unroll
+    for (int a = 0; a < RD; ++a) {
+      rca[a] = d.rclass ? d.rclass[r * RD + a] : 0;
+      base[a] = COUNT ? 0 : indptr[r * RD + a];
+      running[a] = 0;
     }
     const double rs = (values && d.rowscale) ? d.rowscale[r] : 1.0;
-    for (int a = 0; a < rd; ++a) {
-      const int64_t row = r * rd + a;
-      const int rca = d.rclass ? d.rclass[row] : 0;
-      const bool dgrow = square && ((d.diag_classes >> rca) & 1u);
-      const int64_t base = COUNT ? 0 : indptr[row];
-      int running = 0;
-      const int tot = L * cd;
-      for (int t0 = 0; t0 < tot; t0 += 32) {
-        const int tt = t0 + lane;
-        const bool valid = tt < tot;
-        const int p = valid ? tt / cd : 0, b = valid ? tt % cd : 0;
-        const int c = scols[p];
-        const int cc = d.cclass ? d.cclass[(int64_t)c * cd + b] : 0;
-        const bool pa = (d.pair_mask >> (rca * 4 + cc)) & 1u;
-        const bool dg = dgrow && (c == r) && (a == b);
-        const bool keep = valid && (pa || dg);
-        const unsigned m = __ballot_sync(0xffffffffu, keep);
-        if (!COUNT && keep) {
-          const int64_t pos = base + running + __popc(m & ((1u << lane) - 1));
-          if (indices) indices[pos] = c * cd + b;
-          if (values) {
-            double v = pa ? acc[(p * rd + a) * cd + b] : 0.0;
-            if (d.rowscale) v = rs * v;
-            if (dg) v += d.diag_add[rca];
-            data[pos] = v;
+    for (int p0 = 0; p0 < L; p0 += 32) {
+      const int p = p0 + lane;
+      const bool valid = p < L;
+      const int c = valid ? t.adj_cols[a0 + p] : 0;
+      int cc[CD];
+#pragma unroll
+      for (int b = 0; b < CD; ++b) cc[b] = (valid && d.cclass) ? d.cclass[(int64_t)c * CD + b] : 0;
+      double v[RD][CD];
+#pragma unroll
+      for (int a = 0; a < RD; ++a)
+#pragma unroll
+        for (int b = 0; b < CD; ++b) v[a][b] = 0.0;
+      if (values) {
+        for (int k = 0; k < deg; ++k) {  // ascending cell order: the reference's serial cell loop
+          const int e = __shfl_sync(0xffffffffu, my_e, k), lr = __shfl_sync(0xffffffffu, my_lr, k);
+          const int l = valid ? (int)t.inv[iv0 + (int64_t)k * L + p] : 0xFF;
+          if (l != 0xFF) {
+            const double* Ee = d.E + (d.E_stride ? (int64_t)e * d.E_stride : 0) + (int64_t)lr * RD * ldE + l * CD;
+#pragma unroll
+            for (int a = 0; a < RD; ++a)
+#pragma unroll
+              for (int b = 0; b < CD; ++b) v[a][b] += d.sign * Ee[a * ldE + b];
           }
         }
-        running += __popc(m);
       }
-      if (COUNT && lane == 0) rowcnt[row] = running;
+#pragma unroll
+      for (int a = 0; a < RD; ++a) {
+        const bool dgrow = (RD == CD) && ((d.diag_classes >> rca[a]) & 1u);
+        bool keep[CD], pa[CD];
+        int before = 0, mine = 0, total = 0;
+#pragma unroll
+        for (int b = 0; b < CD; ++b) {
+          pa[b] = (d.pair_mask >> (rca[a] * 4 + cc[b])) & 1u;
+          const bool dg = dgrow && (c == r) && (a == b);
+          keep[b] = valid && (pa[b] || dg);
+          const unsigned m = __ballot_sync(0xffffffffu, keep[b]);
+          before += __popc(m & lt);
+          total += __popc(m);
+        }
+        if (!COUNT) {
+#pragma unroll
+          for (int b = 0; b < CD; ++b) {
+            if (keep[b]) {
+              const int64_t pos = base[a] + running[a] + before + mine;
+              if (indices) indices[pos] = c * CD + b;
+              if (values) {
+                double x = pa[b] ? v[a][b] : 0.0;
+                if (d.rowscale) x = rs * x;
+                if (dgrow && (c == r) && (a == b))
+                  x += (rca[a] == 0) ? d.diag_add[0] : (rca[a] == 1) ? d.diag_add[1] : (rca[a] == 2) ? d.diag_add[2] : d.diag_add[3];
+                data[pos] = x;
+              }
+              ++mine;
+            }
+          }
+        }
+        running[a] += total;
+      }
     }
-    __syncwarp();
+    if (COUNT && lane == 0) {
+#pragma unroll
+      for (int a = 0; a < RD; ++a) rowcnt[r * RD + a] = running[a];
+    }
   }
 }
 
@@ -240,6 +256,28 @@ int make_desc(const pyn_asm_desc* desc, DescView* v) {
 
 extern "C" {
 
+}  // extern "C"
+
+template <bool COUNT>
+static int launch_asm(const pyn_topo* t, const DescView& dv, int* cnt, const int64_t* indptr, int* indices, double* data,
+                      cudaStream_t st) {
+  const pyn::TopoView tv = pyn::view_of(t);
+  const int grid = pyn::grid_for(t->nnodes * 32, 256, 16);
+#define PYN_ASM_CASE(R, C)                                                                        \
+  if (dv.rdof == R && dv.cdof == C) {                                                             \
+    asm_gather_kernel<R, C, COUNT><<<grid, 256, 0, st>>>(tv, dv, cnt, indptr, indices, data);     \
+    PYN_CHECK_LAUNCH();                                                                           \
+    return PYN_OK;                                                                                \
+  }
+  PYN_ASM_CASE(2, 2) PYN_ASM_CASE(2, 1) PYN_ASM_CASE(1, 2) PYN_ASM_CASE(3, 2) PYN_ASM_CASE(2, 3)
+  PYN_ASM_CASE(1, 1) PYN_ASM_CASE(3, 3) PYN_ASM_CASE(1, 3) PYN_ASM_CASE(3, 1)
+#undef PYN_ASM_CASE
+  pyn::set_error("assembly: unsupported block shape %d x %d", dv.rdof, dv.cdof);
+  return PYN_ERR_ARG;
+}
+
+extern "C" {
+
 int pyn_asm_count(const pyn_topo* t, const pyn_asm_desc* desc, int64_t* d_indptr, int64_t* h_nnz, void* stream) {
   PYN_REQUIRE(t && d_indptr, "bad arguments");
   DescView dv;
@@ -249,12 +287,8 @@ int pyn_asm_count(const pyn_topo* t, const pyn_asm_desc* desc, int64_t* d_indptr
   const int64_t nrows = t->nnodes * dv.rdof;
   int* cnt = nullptr;
   PYN_CHECK_CUDA(cudaMallocAsync(&cnt, sizeof(int) * (nrows + 1), st));
-  const int wpb = 4;
-  const size_t smem = (size_t)wpb * ((t->max_row + 1) / 2) * sizeof(double);
-  asm_rows_kernel<true><<<pyn::grid_for(t->nnodes, wpb, 16), wpb * 32, smem, st>>>(pyn::view_of(t), dv, t->max_row, cnt,
-                                                                                   nullptr, nullptr, nullptr);
-  PYN_CHECK_LAUNCH();
-  rc = pyn::scan_counts(cnt, nrows, d_indptr, h_nnz, st);
+  rc = launch_asm<true>(t, dv, cnt, nullptr, nullptr, nullptr, st);
+  if (rc == PYN_OK) rc = pyn::scan_counts(cnt, nrows, d_indptr, h_nnz, st);
   PYN_CHECK_CUDA(cudaFreeAsync(cnt, st));
   return rc;
 }
@@ -266,18 +300,7 @@ int pyn_asm_fill(const pyn_topo* t, const pyn_asm_desc* desc, const int64_t* d_i
   int rc = make_desc(desc, &dv);
   if (rc) return rc;
   PYN_REQUIRE(d_data == nullptr || dv.E != nullptr, "element matrices missing");
-  const int wpb = 4;
-  const int blk = dv.rdof * dv.cdof;
-  const size_t smem = (size_t)wpb * ((size_t)t->max_row * blk + (t->max_row + 1) / 2) * sizeof(double);
-  if (smem > 227 * 1024) {
-    pyn::set_error("pyn_asm_fill: adjacency row length %d needs %zu B shared memory", t->max_row, smem);
-    return PYN_ERR_LIMIT;
-  }
-  PYN_CHECK_CUDA(cudaFuncSetAttribute(asm_rows_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  asm_rows_kernel<false><<<pyn::grid_for(t->nnodes, wpb, 16), wpb * 32, smem, pyn::as_stream(stream)>>>(
-      pyn::view_of(t), dv, t->max_row, nullptr, d_indptr, d_indices, d_data);
-  PYN_CHECK_LAUNCH();
-  return PYN_OK;
+  return launch_asm<false>(t, dv, nullptr, d_indptr, d_indices, d_data, pyn::as_stream(stream));
 }
 
 int pyn_asm_weights(const pyn_topo* t, const double* d_We, int64_t stride, double* d_W, void* stream) {

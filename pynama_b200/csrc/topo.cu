@@ -182,6 +182,39 @@ adjacency_kernel(pyn::TopoView t, int cap, int* __restrict__ rowlen, const int64
   }
 }
 
+// per node: valence * adjacency row length (size of its slice of the inverse position map)
+__global__ void inv_count_kernel(pyn::TopoView t, int* __restrict__ cnt) {
+  for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < t.nnodes; r += (int64_t)gridDim.x * blockDim.x)
+    cnt[r] = (int)(t.n2e_ptr[r + 1] - t.n2e_ptr[r]) * (int)(t.adj_ptr[r + 1] - t.adj_ptr[r]);
+}
+
+// one warp per node: inv[k][p] = local index in element k of adjacency column p (binary search of every element node
+// in the sorted adjacency row held in shared memory)
+__global__ void __launch_bounds__(128)
+inv_fill_kernel(pyn::TopoView t, int cap, uint8_t* __restrict__ inv) {
+  extern __shared__ int smi[];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, wpb = blockDim.x >> 5;
+  int* row = smi + w * cap;
+  for (int64_t r = blockIdx.x * (int64_t)wpb + w; r < t.nnodes; r += (int64_t)gridDim.x * wpb) {
+    const int64_t a0 = t.adj_ptr[r], b0 = t.n2e_ptr[r], o = t.inv_ptr[r];
+    const int L = (int)(t.adj_ptr[r + 1] - a0), deg = (int)(t.n2e_ptr[r + 1] - b0);
+    for (int i = lane; i < L; i += 32) row[i] = t.adj_cols[a0 + i];
+    for (int i = lane; i < deg * L; i += 32) inv[o + i] = 0xFF;
+    __syncwarp();
+    for (int i = lane; i < deg * t.nn; i += 32) {
+      const int k = i / t.nn, l = i % t.nn;
+      const int c = t.e2n[(int64_t)t.n2e_elem[b0 + k] * t.nn + l];
+      int lo = 0, hi = L;
+      while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (row[mid] < c) lo = mid + 1; else hi = mid;
+      }
+      inv[o + (int64_t)k * L + lo] = (uint8_t)l;
+    }
+    __syncwarp();
+  }
+}
+
 __global__ void int_to_i64_kernel(const int* __restrict__ in, int64_t n, int64_t* __restrict__ out) {
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
     out[i] = in[i];
@@ -324,6 +357,28 @@ int pyn_topo_create(const int32_t* d_e2n, int64_t ne, int nn, int64_t nnodes, vo
   TOPO_TRY(cuda_try(cudaMalloc(&t->adj_cols, sizeof(int) * t->adj_nnz), "malloc adj_cols"));
   adjacency_kernel<true><<<grid, 128, smem, st>>>(v, cap, nullptr, t->adj_ptr, t->adj_cols);
   pyn::count_launch();
+  // inverse position map for the gather assembly
+  if (nn > 254 || t->max_valence > 32) {
+    pyn::set_error("pyn_topo_create: %d nodes/element (max 254) or valence %d (max 32) outside the compiled limits", nn,
+                   t->max_valence);
+    pyn_topo_destroy(t); cudaFree(cnt);
+    return PYN_ERR_LIMIT;
+  }
+  v = pyn::view_of(t);
+  inv_count_kernel<<<pyn::grid_for(nnodes, 256), 256, 0, st>>>(v, cnt);
+  pyn::count_launch();
+  TOPO_TRY(cuda_try(cudaMalloc(&t->inv_ptr, sizeof(int64_t) * (nnodes + 1)), "malloc inv_ptr"));
+  TOPO_TRY(pyn::scan_counts(cnt, nnodes, t->inv_ptr, &t->inv_len, st));
+  TOPO_TRY(cuda_try(cudaMalloc(&t->inv, (size_t)(t->inv_len > 0 ? t->inv_len : 1)), "malloc inv"));
+  v = pyn::view_of(t);
+  {
+    int rcap = 32;
+    while (rcap < t->max_row) rcap <<= 1;
+    const size_t smem2 = (size_t)rcap * 4 * sizeof(int);
+    cudaFuncSetAttribute(inv_fill_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
+    inv_fill_kernel<<<grid, 128, smem2, st>>>(v, rcap, t->inv);
+    pyn::count_launch();
+  }
   TOPO_TRY(cuda_try(cudaStreamSynchronize(st), "sync"));
   TOPO_TRY(cuda_try(cudaGetLastError(), "kernels"));
   cudaFree(cnt);
@@ -334,7 +389,7 @@ int pyn_topo_create(const int32_t* d_e2n, int64_t ne, int nn, int64_t nnodes, vo
 
 int pyn_topo_destroy(pyn_topo* t) {
   if (!t) return PYN_OK;
-  cudaFree(t->n2e_ptr); cudaFree(t->n2e_elem); cudaFree(t->n2e_loc); cudaFree(t->adj_ptr); cudaFree(t->adj_cols);
+  cudaFree(t->n2e_ptr); cudaFree(t->n2e_elem); cudaFree(t->n2e_loc); cudaFree(t->adj_ptr); cudaFree(t->adj_cols); cudaFree(t->inv_ptr); cudaFree(t->inv);
   delete t;
   return PYN_OK;
 }

@@ -11,7 +11,10 @@ struct pyn_topo {
   short* n2e_loc;      // local index of the node inside that element
   int64_t* adj_ptr;    // [nnodes+1]
   int* adj_cols;       // sorted neighbour nodes (including the node itself)
-  int64_t adj_nnz;
+  int64_t* inv_ptr;    // [nnodes+1] offsets into `inv` (sum of valence * row length)
+  uint8_t* inv;        // inverse position map: inv[inv_ptr[r] + k*L + p] = local index, inside the k-th element of
+                       // node r, of the p-th adjacency column of r (0xFF: that column is not a node of the element)
+  int64_t adj_nnz, inv_len;
   int max_valence, max_row;
 };
 
@@ -25,12 +28,14 @@ struct TopoView {
   const short* n2e_loc;
   const int64_t* adj_ptr;
   const int* adj_cols;
+  const int64_t* inv_ptr;
+  const uint8_t* inv;
 };
 static inline TopoView view_of(const pyn_topo* t) {
   TopoView v;
   v.ne = t->ne; v.nnodes = t->nnodes; v.nn = t->nn; v.e2n = t->e2n;
   v.n2e_ptr = t->n2e_ptr; v.n2e_elem = t->n2e_elem; v.n2e_loc = t->n2e_loc;
-  v.adj_ptr = t->adj_ptr; v.adj_cols = t->adj_cols;
+  v.adj_ptr = t->adj_ptr; v.adj_cols = t->adj_cols; v.inv_ptr = t->inv_ptr; v.inv = t->inv;
   return v;
 }
 int scan_counts(const int* d_cnt, int64_t n, int64_t* d_ptr, int64_t* h_total, cudaStream_t st);

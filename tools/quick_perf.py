@@ -47,5 +47,7 @@ def run(nx, n, per_cell=False):
           f"spmv {t_spmv:.3f} ms = {gb/t_spmv*1e3:.0f} GB/s | cg {r.its} its {t_cg/ max(r.its,1):.3f} ms/it", flush=True)
 
 if __name__ == "__main__":
-    for nx, n, pc in [(64, 5, True), (256, 5, False), (512, 5, False), (1024, 5, False), (707, 5, True), (1414, 3, False)]:
+    import sys as _s
+    cases = [(64, 5, True), (512, 5, False), (1024, 5, False), (707, 5, True), (1414, 3, False), (354, 9, False)]
+    for nx, n, pc in cases:
         run(nx, n, pc)
