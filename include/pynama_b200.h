@@ -159,6 +159,15 @@ typedef enum {
 int pyn_spmv(int64_t nrows, const int64_t* d_ptr, const int32_t* d_ind, const double* d_val, int64_t nnz,
              const double* d_x, double* d_y, int mode, double p0, double p1, const double* d_aux, void* stream);
 
+/* Planned SpMV ("CSR-stream"): the plan cuts the matrix into chunks of consecutive non-zeros snapped to row
+ * boundaries, once per sparsity pattern; the kernel then streams values/indices fully coalesced whatever the row
+ * lengths.  Same result contract and modes as pyn_spmv.  `d_ptr` is borrowed and must outlive the plan. */
+typedef struct pyn_spmv_plan pyn_spmv_plan;
+int pyn_spmv_plan_create(int64_t nrows, const int64_t* d_ptr, int64_t nnz, void* stream, pyn_spmv_plan** out);
+int pyn_spmv_plan_destroy(pyn_spmv_plan* plan);
+int pyn_spmv_planned(const pyn_spmv_plan* plan, const int32_t* d_ind, const double* d_val, const double* d_x,
+                     double* d_y, int mode, double p0, double p1, const double* d_aux, void* stream);
+
 /* ------------------------------------------------------------------------------------------------------
  * Vectors (PETSc Vec calls of the path: base_problem.py:222-230,234-252; cavity.py:53-81; custom_func.py:76-83)
  * ---------------------------------------------------------------------------------------------------- */

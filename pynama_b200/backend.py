@@ -157,24 +157,53 @@ def pair_mask(pairs):
 ALL_PAIRS = pair_mask([(r, c) for r in range(4) for c in range(4)])
 
 
+class SpmvPlan:
+    """Owner of a pyn_spmv_plan handle (keeps the borrowed row-pointer tensor alive)."""
+
+    def __init__(self, nrows, indptr, nnz):
+        self.indptr = indptr
+        self.handle = C.c_void_p()
+        call("pyn_spmv_plan_create", nrows, ptr(indptr), nnz, stream(), C.byref(self.handle))
+
+    def __del__(self):
+        try:
+            if getattr(self, "handle", None):
+                _lib.load().pyn_spmv_plan_destroy(self.handle)
+                self.handle = None
+        except Exception:
+            pass
+
+
 class CSR:
     """Device CSR matrix (int64 row pointers, int32 sorted column indices, FP64 values)."""
 
     def __init__(self, shape, indptr, indices, data, name=""):
         self.shape, self.indptr, self.indices, self.data, self.name = tuple(shape), indptr, indices, data, name
+        self._plan = None
+
+    def plan(self):
+        """SpMV plan of this sparsity pattern (pyn_spmv_plan_create), built on first use and shared between the
+        matrices that share `indptr` (values-only re-assembly)."""
+        if self._plan is None:
+            self._plan = SpmvPlan(self.shape[0], self.indptr, self.nnz)
+        return self._plan.handle
 
     @property
     def nnz(self):
         return int(self.indices.numel())
 
     # -- PETSc-Mat flavoured surface ----------------------------------------------------------------------
-    def mult(self, x, y, mode=0, p0=0.0, p1=0.0, aux=None):
+    def mult(self, x, y, mode=0, p0=0.0, p1=0.0, aux=None, planned=True):
         xd = x.data if hasattr(x, "data") and not isinstance(x, torch.Tensor) else x
         yd = y.data if hasattr(y, "data") and not isinstance(y, torch.Tensor) else y
         ad = aux.data if (aux is not None and not isinstance(aux, torch.Tensor)) else aux
         assert xd.numel() == self.shape[1] and yd.numel() == self.shape[0]
-        call("pyn_spmv", self.shape[0], ptr(self.indptr), ptr(self.indices), ptr(self.data), self.nnz,
-             ptr(xd), ptr(yd), mode, float(p0), float(p1), ptr(ad), stream())
+        if planned:
+            call("pyn_spmv_planned", self.plan(), ptr(self.indices), ptr(self.data), ptr(xd), ptr(yd), mode,
+                 float(p0), float(p1), ptr(ad), stream())
+        else:       # plan-less CSR-vector kernel (one-off products)
+            call("pyn_spmv", self.shape[0], ptr(self.indptr), ptr(self.indices), ptr(self.data), self.nnz,
+                 ptr(xd), ptr(yd), mode, float(p0), float(p1), ptr(ad), stream())
         return y
 
     def diagonal(self):
@@ -263,7 +292,10 @@ def assemble(topo, rdof, cdof, E, rclass=None, cclass=None, pairs=ALL_PAIRS, dia
         indptr, indices, fill_idx = pattern.indptr, pattern.indices, None
     data = empty(indices.numel()) if values else None
     call("pyn_asm_fill", topo._h, C.byref(d), ptr(indptr), ptr(fill_idx), ptr(data), stream())
-    return CSR((nrows, ncols), indptr, indices, data, name)
+    out = CSR((nrows, ncols), indptr, indices, data, name)
+    if pattern is not None:
+        out._plan = pattern._plan
+    return out
 
 
 def assemble_weights(topo, We):

@@ -84,28 +84,25 @@ __global__ void cg_pupdate_kernel(int64_t n, CgBuffers B) {
     B.p[i] = first ? B.z[i] : B.z[i] + b * B.p[i];
 }
 
-// w = A p, per-CTA partial of p.w
-template <int LPR>
-__global__ void __launch_bounds__(BLK)
-cg_spmv_dot_kernel(int64_t nrows, const int64_t* __restrict__ ptr, const int* __restrict__ ind,
-                   const double* __restrict__ val, CgBuffers B) {
-  __shared__ double sm[BLK / 32];
-  if (B.st->done) return;
-  const int sub = threadIdx.x % LPR;
-  const int64_t rows_per_pass = ((int64_t)gridDim.x * BLK) / LPR;
-  const int64_t first = (blockIdx.x * (int64_t)BLK + threadIdx.x) / LPR;
-  const int64_t passes = (nrows + rows_per_pass - 1) / rows_per_pass;
-  double dot = 0.0;
-  for (int64_t it = 0; it < passes; ++it) {
-    const int64_t row = first + it * rows_per_pass;
-    const bool active = row < nrows;
-    const double s = pyn::spmv_row<LPR>(ptr, ind, val, B.p, row, active, sub);
-    if (active && sub == 0) {
-      B.w[row] = s;
-      dot += B.p[row] * s;
-    }
+// w = A p, per-CTA partial of p.w  (CSR-stream kernel, see spmv.cuh)
+struct CgDotEpi {
+  double* w;
+  const double* p;
+  double* dot;
+  __device__ __forceinline__ void operator()(int64_t row, double s) const {
+    w[row] = s;
+    *dot += p[row] * s;
   }
-  dot = pyn::block_sum<BLK>(dot, sm);
+};
+__global__ void __launch_bounds__(pyn::SP_BLK)
+cg_spmv_dot_kernel(pyn::SpmvPlanView P, const int* __restrict__ ind, const double* __restrict__ val, CgBuffers B) {
+  __shared__ pyn::SpmvSmem sm;
+  __shared__ double red[pyn::SP_BLK / 32];
+  if (B.st->done) return;
+  double dot = 0.0;
+  CgDotEpi epi{B.w, B.p, &dot};
+  for (int b = blockIdx.x; b < P.nblk; b += gridDim.x) pyn::spmv_stream_chunk(P, ind, val, B.p, b, sm, epi);
+  dot = pyn::block_sum<pyn::SP_BLK>(dot, red);
   if (threadIdx.x == 0) B.part_a[blockIdx.x] = dot;
 }
 
@@ -189,7 +186,8 @@ struct pyn_ksp {
   CgBuffers B;
   double *pzz, *pzr;
   KspState* h_state;  // pinned
-  int vgrid, sgrid, lpr;
+  int vgrid, sgrid;
+  pyn_spmv_plan* plan;
   cudaGraphExec_t graph;
   int graph_iters;
   int64_t last_spmv, last_launches;
@@ -197,19 +195,9 @@ struct pyn_ksp {
 
 namespace {
 
-template <int LPR>
-void launch_spmv_dot(const pyn_ksp* k, cudaStream_t st) {
-  cg_spmv_dot_kernel<LPR><<<k->sgrid, BLK, 0, st>>>(k->n, k->ptr, k->ind, k->val, k->B);
-}
-
 void enqueue_cg_iteration(const pyn_ksp* k, cudaStream_t st) {
   cg_pupdate_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, k->B);
-  switch (k->lpr) {
-    case 4: launch_spmv_dot<4>(k, st); break;
-    case 8: launch_spmv_dot<8>(k, st); break;
-    case 16: launch_spmv_dot<16>(k, st); break;
-    default: launch_spmv_dot<32>(k, st);
-  }
+  cg_spmv_dot_kernel<<<k->sgrid, pyn::SP_BLK, 0, st>>>(pyn::view_of(k->plan), k->ind, k->val, k->B);
   cg_update_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, k->sgrid, k->B, k->pzz, k->pzr);
   cg_scalar_kernel<<<1, 32, 0, st>>>(k->sgrid, k->vgrid, k->B, k->pzz, k->pzr, k->opts.atol, k->opts.dtol, k->opts.max_it);
 }
@@ -230,11 +218,13 @@ int pyn_ksp_create(int64_t nrows, const int64_t* d_ptr, const int32_t* d_ind, co
   if (k->opts.check_every <= 0) k->opts.check_every = 16;
   if (k->opts.max_it <= 0) k->opts.max_it = 10000;
   k->vgrid = pyn::grid_for(nrows, BLK, 8);
-  k->lpr = pyn::pick_lpr(nrows, nnz);
   {
-    const int64_t need = (nrows * k->lpr + BLK - 1) / BLK;
-    const int64_t cap = (int64_t)pyn::sm_count() * 16;
-    k->sgrid = (int)(need < cap ? need : cap);
+    int rc0 = pyn_spmv_plan_create(nrows, d_ptr, nnz, stream, &k->plan);
+    if (rc0) { delete k; return rc0; }
+    int occ = 0;
+    PYN_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, cg_spmv_dot_kernel, pyn::SP_BLK, 0));
+    const int64_t cap = (int64_t)pyn::sm_count() * (occ > 0 ? occ : 1);
+    k->sgrid = (int)(k->plan->nblk < cap ? k->plan->nblk : cap);
   }
   double* pool = nullptr;
   const size_t nparts = (size_t)(k->vgrid > k->sgrid ? k->vgrid : k->sgrid);
@@ -306,6 +296,7 @@ int pyn_ksp_solve(pyn_ksp* k, const double* d_b, double* d_x, pyn_ksp_result* re
 int pyn_ksp_destroy(pyn_ksp* k) {
   if (!k) return PYN_OK;
   if (k->graph) cudaGraphExecDestroy(k->graph);
+  pyn_spmv_plan_destroy(k->plan);
   cudaFree(k->B.r);
   cudaFree(k->B.st);
   cudaFreeHost(k->h_state);

@@ -47,7 +47,118 @@ int launch(int64_t nrows, const int64_t* ptr, const int* ind, const double* val,
   return PYN_OK;
 }
 
+// ---- CSR-stream kernel (planned) ------------------------------------------------------------------------------------
+struct ModeEpi {
+  double* y;
+  int mode;
+  double p0, p1;
+  const double* aux;
+  __device__ __forceinline__ void operator()(int64_t row, double s) const {
+    double out;
+    switch (mode) {
+      case PYN_SPMV_ADD: out = y[row] + s; break;
+      case PYN_SPMV_SCALE: out = p0 * s; break;
+      case PYN_SPMV_SRT_VTENSV: {
+        const int64_t k = row / 3;
+        const int c = (int)(row - 3 * k);
+        const double vx = aux[2 * k], vy = aux[2 * k + 1];
+        const double t = (c == 0) ? vx * vx : ((c == 1) ? vx * vy : vy * vy);
+        out = p0 * s + (-p1) * t;
+      } break;
+      default: out = s;
+    }
+    y[row] = out;
+  }
+};
+
+__global__ void __launch_bounds__(pyn::SP_BLK)
+spmv_stream_kernel(pyn::SpmvPlanView P, const int* __restrict__ ind, const double* __restrict__ val,
+                   const double* __restrict__ x, ModeEpi epi) {
+  __shared__ pyn::SpmvSmem sm;
+  for (int b = blockIdx.x; b < P.nblk; b += gridDim.x) pyn::spmv_stream_chunk(P, ind, val, x, b, sm, epi);
+}
+
+__global__ void plan_maxrow_kernel(int64_t nrows, const int64_t* __restrict__ ptr, int* __restrict__ out) {
+  int m = 0;
+  for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < nrows; r += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t len = ptr[r + 1] - ptr[r];
+    m = max(m, (int)min(len, (int64_t)0x7fffffff));
+  }
+  for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_down_sync(0xffffffffu, m, o));
+  if ((threadIdx.x & 31) == 0 && m > 0) atomicMax(out, m);
+}
+
+// blk_row[b] = first row whose first non-zero lies at or after b*chunk
+__global__ void plan_rows_kernel(int64_t nrows, const int64_t* __restrict__ ptr, int chunk, int nblk,
+                                 int* __restrict__ blk_row) {
+  for (int b = blockIdx.x * blockDim.x + threadIdx.x; b <= nblk; b += gridDim.x * blockDim.x) {
+    if (b == nblk) { blk_row[b] = (int)nrows; continue; }
+    const int64_t key = (int64_t)b * chunk;
+    int64_t lo = 0, hi = nrows;
+    while (lo < hi) {
+      const int64_t mid = (lo + hi) >> 1;
+      if (ptr[mid] < key) lo = mid + 1; else hi = mid;
+    }
+    blk_row[b] = (int)lo;
+  }
+}
+
 }  // namespace
+
+extern "C" int pyn_spmv_plan_create(int64_t nrows, const int64_t* d_ptr, int64_t nnz, void* stream,
+                                    pyn_spmv_plan** out) {
+  PYN_REQUIRE(nrows > 0 && nrows < 2147483647LL && d_ptr && nnz >= 0 && out, "bad arguments");
+  cudaStream_t st = pyn::as_stream(stream);
+  pyn_spmv_plan* p = new pyn_spmv_plan();
+  memset(p, 0, sizeof(*p));
+  p->nrows = nrows; p->nnz = nnz; p->ptr = d_ptr;
+  int* d_max = nullptr;
+  int maxrow = 0;
+  PYN_CHECK_CUDA(cudaMalloc(&d_max, sizeof(int)));
+  PYN_CHECK_CUDA(cudaMemsetAsync(d_max, 0, sizeof(int), st));
+  plan_maxrow_kernel<<<pyn::grid_for(nrows, 256), 256, 0, st>>>(nrows, d_ptr, d_max);
+  PYN_CHECK_LAUNCH();
+  PYN_CHECK_CUDA(cudaMemcpyAsync(&maxrow, d_max, sizeof(int), cudaMemcpyDeviceToHost, st));
+  PYN_CHECK_CUDA(cudaStreamSynchronize(st));
+  cudaFree(d_max);
+  // one pass of SP_U loads per thread covers SP_U*SP_BLK products: aim chunks at that, leaving room for the last row
+  const int pass = pyn::SP_U * pyn::SP_BLK;
+  int chunk = pass - maxrow;
+  if (chunk < pass / 2) chunk = pass / 2;
+  p->chunk = chunk;
+  const int64_t nb = nnz > 0 ? (nnz + chunk - 1) / chunk : 1;
+  PYN_REQUIRE(nb < 2147483647LL, "matrix too large for one SpMV plan");
+  p->nblk = (int)nb;
+  PYN_CHECK_CUDA(cudaMalloc(&p->blk_row, sizeof(int) * (nb + 1)));
+  plan_rows_kernel<<<pyn::grid_for(nb + 1, 256), 256, 0, st>>>(nrows, d_ptr, chunk, p->nblk, p->blk_row);
+  PYN_CHECK_LAUNCH();
+  int occ = 0;  // persistent grid: exactly the CTAs that are resident at once
+  PYN_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, spmv_stream_kernel, pyn::SP_BLK, 0));
+  const int64_t cap = (int64_t)pyn::sm_count() * (occ > 0 ? occ : 1);
+  p->grid = (int)(nb < cap ? nb : cap);
+  PYN_CHECK_CUDA(cudaStreamSynchronize(st));
+  *out = p;
+  return PYN_OK;
+}
+
+extern "C" int pyn_spmv_plan_destroy(pyn_spmv_plan* p) {
+  if (!p) return PYN_OK;
+  cudaFree(p->blk_row);
+  delete p;
+  return PYN_OK;
+}
+
+extern "C" int pyn_spmv_planned(const pyn_spmv_plan* p, const int32_t* d_ind, const double* d_val, const double* d_x,
+                                double* d_y, int mode, double p0, double p1, const double* d_aux, void* stream) {
+  PYN_REQUIRE(p && d_ind && d_val && d_x && d_y, "bad arguments");
+  PYN_REQUIRE(mode >= 0 && mode <= 3, "bad mode");
+  PYN_REQUIRE(mode != PYN_SPMV_SRT_VTENSV || (d_aux != nullptr && p->nrows % 3 == 0),
+              "SRT_VTENSV needs aux and 3 rows per node");
+  ModeEpi epi{d_y, mode, p0, p1, d_aux};
+  spmv_stream_kernel<<<p->grid, pyn::SP_BLK, 0, pyn::as_stream(stream)>>>(pyn::view_of(p), d_ind, d_val, d_x, epi);
+  PYN_CHECK_LAUNCH();
+  return PYN_OK;
+}
 
 extern "C" int pyn_spmv(int64_t nrows, const int64_t* d_ptr, const int32_t* d_ind, const double* d_val, int64_t nnz,
                         const double* d_x, double* d_y, int mode, double p0, double p1, const double* d_aux,
