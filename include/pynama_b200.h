@@ -104,6 +104,16 @@ int pyn_topo_adjacency(const pyn_topo* t, const int64_t** d_rowptr, const int32_
  *   i == j and diag_classes bit ri is set;  its value is  rowscale[node(i)] * sign * sum_e E_e[li][lj]  (+
  *   diag_add[ri] on such a diagonal).  Classes: 0 free, 1 tangential-on-no-slip-wall, 2 prescribed.
  * ---------------------------------------------------------------------------------------------------- */
+/* Boundary map (optional accelerator): the list of nodes that carry a non-zero row class or have a neighbour with
+ * a non-zero column class.  All other nodes ("interior") keep either every entry or none, need no class lookups
+ * and go through a streamlined kernel; boundary-only matrices (Krhs, Kfs, ...) touch only the listed nodes.
+ * The class arrays are borrowed and must be the ones later passed in the descriptor. */
+typedef struct pyn_bcmap pyn_bcmap;
+int pyn_bcmap_create(const pyn_topo* t, const int8_t* d_rclass, int rdof, const int8_t* d_cclass, int cdof,
+                     void* stream, pyn_bcmap** out);
+int pyn_bcmap_destroy(pyn_bcmap* m);
+int pyn_bcmap_info(const pyn_bcmap* m, int64_t* n_boundary_nodes);
+
 typedef struct {
   int32_t rdof, cdof;        /* dofs per node on rows / columns: K 2x2, Rw 2x1, SrT 3x2, DivSrT 2x3, Curl 1x2 */
   const int8_t* d_rclass;    /* [nnodes*rdof] or NULL (all 0) */
@@ -115,6 +125,7 @@ typedef struct {
   const double* d_E;         /* [ne or 1][rdof*nn][cdof*nn] element matrices */
   int64_t E_stride;          /* elements between consecutive element matrices in doubles; 0 = one for all cells */
   const double* d_rowscale;  /* [nnodes] or NULL */
+  const pyn_bcmap* bcmap;    /* NULL, or the map built from (d_rclass, rdof, d_cclass, cdof) */
 } pyn_asm_desc;
 
 /* pattern: row pointers (exclusive scan done inside), total nnz returned on the host (synchronises) */

@@ -21,7 +21,7 @@ class AsmDesc(C.Structure):
     """pyn_asm_desc"""
     _fields_ = [("rdof", c_i32), ("cdof", c_i32), ("d_rclass", c_vp), ("d_cclass", c_vp),
                 ("pair_mask", C.c_uint32), ("diag_classes", C.c_uint32), ("diag_add", c_f64 * 4),
-                ("sign", c_f64), ("d_E", c_vp), ("E_stride", c_i64), ("d_rowscale", c_vp)]
+                ("sign", c_f64), ("d_E", c_vp), ("E_stride", c_i64), ("d_rowscale", c_vp), ("bcmap", c_vp)]
 
 
 class KspOpts(C.Structure):
@@ -53,6 +53,9 @@ _SIGNATURES = {
     "pyn_topo_destroy": (C.c_int, [c_vp]),
     "pyn_topo_info": (C.c_int, [c_vp, P(c_i64), P(C.c_int), P(C.c_int)]),
     "pyn_topo_adjacency": (C.c_int, [c_vp, P(c_vp), P(c_vp)]),
+    "pyn_bcmap_create": (C.c_int, [c_vp, c_vp, C.c_int, c_vp, C.c_int, c_vp, P(c_vp)]),
+    "pyn_bcmap_destroy": (C.c_int, [c_vp]),
+    "pyn_bcmap_info": (C.c_int, [c_vp, P(c_i64)]),
     "pyn_asm_count": (C.c_int, [c_vp, P(AsmDesc), c_vp, P(c_i64), c_vp]),
     "pyn_asm_fill": (C.c_int, [c_vp, P(AsmDesc), c_vp, c_vp, c_vp, c_vp]),
     "pyn_asm_weights": (C.c_int, [c_vp, c_vp, c_i64, c_vp, c_vp]),

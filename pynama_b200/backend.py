@@ -147,6 +147,29 @@ class Topology:
             pass
 
 
+class BcMap:
+    """Boundary map of one (row classes, column classes) pair on a topology (pyn_bcmap_*): lets the assembly run its
+    streamlined interior kernel on every node without boundary influence and visit only the listed nodes for the
+    boundary-only matrices.  Holds the class tensors, which must not be modified afterwards."""
+
+    def __init__(self, topo, rclass=None, rdof=0, cclass=None, cdof=0):
+        self.topo, self.rclass, self.cclass = topo, rclass, cclass
+        self._h = C.c_void_p()
+        call("pyn_bcmap_create", topo._h, ptr(rclass), int(rdof if rclass is not None else 0), ptr(cclass),
+             int(cdof if cclass is not None else 0), stream(), C.byref(self._h))
+        n = C.c_int64()
+        call("pyn_bcmap_info", self._h, C.byref(n))
+        self.n_boundary = n.value
+
+    def __del__(self):
+        try:
+            if getattr(self, "_h", None):
+                _lib.load().pyn_bcmap_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+
 def pair_mask(pairs):
     m = 0
     for rc, cc in pairs:
@@ -259,7 +282,7 @@ class CSR:
 
 
 def assemble(topo, rdof, cdof, E, rclass=None, cclass=None, pairs=ALL_PAIRS, diag_classes=0,
-             diag_add=(0.0, 0.0, 0.0, 0.0), sign=1.0, rowscale=None, pattern=None, name="", values=True):
+             diag_add=(0.0, 0.0, 0.0, 0.0), sign=1.0, rowscale=None, pattern=None, name="", values=True, bcmap=None):
     """Deterministic assembly of one matrix (pyn_asm_count + pyn_asm_fill).
 
     E: device tensor (1|ne, rdof*nn, cdof*nn).  pattern: an existing CSR whose indptr/indices are reused
@@ -281,6 +304,9 @@ def assemble(topo, rdof, cdof, E, rclass=None, cclass=None, pairs=ALL_PAIRS, dia
         if E.shape[0] != 1:
             assert E.shape[0] == topo.ne
     d.d_rowscale = rowscale.data_ptr() if rowscale is not None else None
+    if bcmap is not None:
+        assert bcmap.topo is topo and bcmap.rclass is rclass and bcmap.cclass is cclass, "bcmap built for other classes"
+        d.bcmap = bcmap._h
     nrows, ncols = topo.nnodes * rdof, topo.nnodes * cdof
     if pattern is None:
         indptr = empty(nrows + 1, I64)

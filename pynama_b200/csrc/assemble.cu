@@ -22,6 +22,7 @@ struct DescView {
   const double* E;
   int64_t E_stride;
   const double* rowscale;
+  const uint8_t* flags;  // bcmap: 1 = boundary-affected node (NULL: no map)
 };
 
 // One warp per mesh node (= RD consecutive matrix rows); lanes stride over the node's sorted adjacency row.  Every
@@ -30,15 +31,17 @@ struct DescView {
 // shared-memory accumulators, no atomics and no intra-warp ordering hazards.  COUNT only counts kept entries.
 template <int RD, int CD, bool COUNT>
 __global__ void __launch_bounds__(256)
-asm_gather_kernel(pyn::TopoView t, DescView d, int* __restrict__ rowcnt, const int64_t* __restrict__ indptr,
-                  int* __restrict__ indices, double* __restrict__ data) {
+asm_gather_kernel(pyn::TopoView t, DescView d, const int* __restrict__ list, int64_t nlist, int* __restrict__ rowcnt,
+                  const int64_t* __restrict__ indptr, int* __restrict__ indices, double* __restrict__ data) {
   const int lane = threadIdx.x & 31;
   const int64_t warp0 = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
   const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
   const bool values = (!COUNT) && (data != nullptr);
   const unsigned lt = (1u << lane) - 1u;
   const int ldE = CD * t.nn;
-  for (int64_t r = warp0; r < t.nnodes; r += nwarps) {
+  const int64_t nwork = list ? nlist : t.nnodes;
+  for (int64_t wi = warp0; wi < nwork; wi += nwarps) {
+    const int64_t r = list ? (int64_t)list[wi] : wi;
     const int64_t a0 = t.adj_ptr[r], b0 = t.n2e_ptr[r];
     const int L = (int)(t.adj_ptr[r + 1] - a0), deg = (int)(t.n2e_ptr[r + 1] - b0);
     const int64_t iv0 = values ? t.inv_ptr[r] : 0;
@@ -121,6 +124,114 @@ asm_gather_kernel(pyn::TopoView t, DescView d, int* __restrict__ rowcnt, const i
       for (int a = 0; a < RD; ++a) rowcnt[r * RD + a] = running[a];
     }
   }
+}
+
+// Interior nodes (bcmap flag 0): every class is 0, so the node keeps either all its L*CD entries per row or none;
+// no class lookups, no compaction, positions are p*CD+b.  Launched only when the (free,free) pair is kept.
+template <int RD, int CD>
+__global__ void __launch_bounds__(256)
+asm_interior_kernel(pyn::TopoView t, DescView d, const int64_t* __restrict__ indptr, int* __restrict__ indices,
+                    double* __restrict__ data) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp0 = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  const int ldE = CD * t.nn;
+  for (int64_t r = warp0; r < t.nnodes; r += nwarps) {
+    if (d.flags[r]) continue;
+    const int64_t a0 = t.adj_ptr[r], b0 = t.n2e_ptr[r], iv0 = t.inv_ptr[r];
+    const int L = (int)(t.adj_ptr[r + 1] - a0), deg = (int)(t.n2e_ptr[r + 1] - b0);
+    int my_e = 0, my_lr = 0;
+    if (lane < deg) {
+      my_e = t.n2e_elem[b0 + lane];
+      my_lr = t.n2e_loc[b0 + lane];
+    }
+    int64_t base[RD];
+#pragma unroll
+    for (int a = 0; a < RD; ++a) base[a] = indptr[r * RD + a];
+    const double rs = d.rowscale ? d.rowscale[r] : 1.0;
+    for (int p0 = 0; p0 < L; p0 += 32) {
+      const int p = p0 + lane;
+      const bool valid = p < L;
+      double v[RD][CD];
+#pragma unroll
+      for (int a = 0; a < RD; ++a)
+#pragma unroll
+        for (int b = 0; b < CD; ++b) v[a][b] = 0.0;
+      if (data) {
+        for (int k = 0; k < deg; ++k) {  // ascending cell order
+          const int e = __shfl_sync(0xffffffffu, my_e, k), lr = __shfl_sync(0xffffffffu, my_lr, k);
+          const int l = valid ? (int)t.inv[iv0 + (int64_t)k * L + p] : 0xFF;
+          if (l != 0xFF) {
+            const double* Ee = d.E + (d.E_stride ? (int64_t)e * d.E_stride : 0) + (int64_t)lr * RD * ldE + l * CD;
+#pragma unroll
+            for (int a = 0; a < RD; ++a)
+#pragma unroll
+              for (int b = 0; b < CD; ++b) v[a][b] += d.sign * Ee[a * ldE + b];
+          }
+        }
+      }
+      if (!valid) continue;
+      if (data) {
+#pragma unroll
+        for (int a = 0; a < RD; ++a) {
+          double* o = data + base[a] + (int64_t)p * CD;
+#pragma unroll
+          for (int b = 0; b < CD; ++b)
+            if (d.rowscale) v[a][b] = rs * v[a][b];
+          if (CD == 2 && ((base[a] & 1) == 0)) {
+            *reinterpret_cast<double2*>(o) = make_double2(v[a][0], v[a][CD - 1]);
+          } else {
+#pragma unroll
+            for (int b = 0; b < CD; ++b) o[b] = v[a][b];
+          }
+        }
+      }
+      if (indices) {
+        const int c = t.adj_cols[a0 + p];
+#pragma unroll
+        for (int a = 0; a < RD; ++a)
+#pragma unroll
+          for (int b = 0; b < CD; ++b) indices[base[a] + (int64_t)p * CD + b] = c * CD + b;
+      }
+    }
+  }
+}
+
+// row lengths of the interior nodes: L*cdof when the (free,free) pair is kept, else 0
+__global__ void asm_interior_count_kernel(pyn::TopoView t, const uint8_t* __restrict__ flags, int rdof, int cdof,
+                                          int keep00, int* __restrict__ rowcnt) {
+  for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < t.nnodes; r += (int64_t)gridDim.x * blockDim.x) {
+    if (flags[r]) continue;
+    const int n = keep00 ? (int)(t.adj_ptr[r + 1] - t.adj_ptr[r]) * cdof : 0;
+    for (int a = 0; a < rdof; ++a) rowcnt[r * rdof + a] = n;
+  }
+}
+
+// bcmap: flag = node has a non-zero row class, or any adjacency column has a non-zero column class
+__global__ void bcmap_flags_kernel(pyn::TopoView t, const int8_t* __restrict__ rclass, int rdof,
+                                   const int8_t* __restrict__ cclass, int cdof, uint8_t* __restrict__ flags) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp0 = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t r = warp0; r < t.nnodes; r += nwarps) {
+    bool f = false;
+    if (rclass && lane < rdof) f = rclass[r * rdof + lane] != 0;
+    if (cclass) {
+      const int64_t a0 = t.adj_ptr[r];
+      const int L = (int)(t.adj_ptr[r + 1] - a0);
+      for (int p = lane; p < L; p += 32) {
+        const int64_t c = t.adj_cols[a0 + p];
+        for (int b = 0; b < cdof; ++b) f |= cclass[c * cdof + b] != 0;
+      }
+    }
+    const unsigned m = __ballot_sync(0xffffffffu, f);
+    if (lane == 0) flags[r] = m ? 1 : 0;
+  }
+}
+
+__global__ void iota_kernel(int64_t n, int* __restrict__ out) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    out[i] = (int)i;
 }
 
 __global__ void weights_kernel(pyn::TopoView t, const double* __restrict__ We, int64_t stride, double* __restrict__ W) {
@@ -249,6 +360,7 @@ int make_desc(const pyn_asm_desc* desc, DescView* v) {
   v->pair_mask = desc->pair_mask; v->diag_classes = desc->diag_classes;
   for (int i = 0; i < 4; ++i) v->diag_add[i] = desc->diag_add[i];
   v->sign = desc->sign; v->E = desc->d_E; v->E_stride = desc->E_stride; v->rowscale = desc->d_rowscale;
+  v->flags = desc->bcmap ? desc->bcmap->flags : nullptr;
   return PYN_OK;
 }
 
@@ -259,13 +371,32 @@ extern "C" {
 }  // extern "C"
 
 template <bool COUNT>
-static int launch_asm(const pyn_topo* t, const DescView& dv, int* cnt, const int64_t* indptr, int* indices, double* data,
-                      cudaStream_t st) {
+static int launch_asm(const pyn_topo* t, const DescView& dv, const int* list, int64_t nlist, int* cnt,
+                      const int64_t* indptr, int* indices, double* data, cudaStream_t st) {
+  const pyn::TopoView tv = pyn::view_of(t);
+  const int64_t nwork = list ? nlist : t->nnodes;
+  if (nwork == 0) return PYN_OK;
+  const int grid = pyn::grid_for(nwork * 32, 256, 16);
+#define PYN_ASM_CASE(R, C)                                                                                     \
+  if (dv.rdof == R && dv.cdof == C) {                                                                          \
+    asm_gather_kernel<R, C, COUNT><<<grid, 256, 0, st>>>(tv, dv, list, nlist, cnt, indptr, indices, data);     \
+    PYN_CHECK_LAUNCH();                                                                                        \
+    return PYN_OK;                                                                                             \
+  }
+  PYN_ASM_CASE(2, 2) PYN_ASM_CASE(2, 1) PYN_ASM_CASE(1, 2) PYN_ASM_CASE(3, 2) PYN_ASM_CASE(2, 3)
+  PYN_ASM_CASE(1, 1) PYN_ASM_CASE(3, 3) PYN_ASM_CASE(1, 3) PYN_ASM_CASE(3, 1)
+#undef PYN_ASM_CASE
+  pyn::set_error("assembly: unsupported block shape %d x %d", dv.rdof, dv.cdof);
+  return PYN_ERR_ARG;
+}
+
+static int launch_interior(const pyn_topo* t, const DescView& dv, const int64_t* indptr, int* indices, double* data,
+                           cudaStream_t st) {
   const pyn::TopoView tv = pyn::view_of(t);
   const int grid = pyn::grid_for(t->nnodes * 32, 256, 16);
 #define PYN_ASM_CASE(R, C)                                                                        \
   if (dv.rdof == R && dv.cdof == C) {                                                             \
-    asm_gather_kernel<R, C, COUNT><<<grid, 256, 0, st>>>(tv, dv, cnt, indptr, indices, data);     \
+    asm_interior_kernel<R, C><<<grid, 256, 0, st>>>(tv, dv, indptr, indices, data);               \
     PYN_CHECK_LAUNCH();                                                                           \
     return PYN_OK;                                                                                \
   }
@@ -276,7 +407,58 @@ static int launch_asm(const pyn_topo* t, const DescView& dv, int* cnt, const int
   return PYN_ERR_ARG;
 }
 
+// the interior fast path applies when a map is given and class-0 rows carry no forced diagonal
+static inline bool use_map(const pyn_asm_desc* desc) { return desc->bcmap != nullptr && !(desc->diag_classes & 1u); }
+
 extern "C" {
+
+int pyn_bcmap_create(const pyn_topo* t, const int8_t* d_rclass, int rdof, const int8_t* d_cclass, int cdof,
+                     void* stream, pyn_bcmap** out) {
+  PYN_REQUIRE(t && out && rdof >= 0 && rdof <= 3 && cdof >= 0 && cdof <= 3, "bad arguments");
+  cudaStream_t st = pyn::as_stream(stream);
+  pyn_bcmap* m = new pyn_bcmap();
+  memset(m, 0, sizeof(*m));
+  m->nnodes = t->nnodes;
+  PYN_CHECK_CUDA(cudaMalloc(&m->flags, (size_t)t->nnodes));
+  bcmap_flags_kernel<<<pyn::grid_for(t->nnodes * 32, 256, 16), 256, 0, st>>>(pyn::view_of(t), d_rclass, rdof, d_cclass,
+                                                                             cdof, m->flags);
+  PYN_CHECK_LAUNCH();
+  int *iota = nullptr, *sel = nullptr;
+  int64_t* d_n = nullptr;
+  PYN_CHECK_CUDA(cudaMalloc(&iota, sizeof(int) * t->nnodes));
+  PYN_CHECK_CUDA(cudaMalloc(&sel, sizeof(int) * t->nnodes));
+  PYN_CHECK_CUDA(cudaMalloc(&d_n, sizeof(int64_t)));
+  iota_kernel<<<pyn::grid_for(t->nnodes, 256), 256, 0, st>>>(t->nnodes, iota);
+  PYN_CHECK_LAUNCH();
+  void* tmp = nullptr;
+  size_t bytes = 0;
+  PYN_CHECK_CUDA(cub::DeviceSelect::Flagged(tmp, bytes, iota, m->flags, sel, d_n, t->nnodes, st));
+  PYN_CHECK_CUDA(cudaMalloc(&tmp, bytes));
+  PYN_CHECK_CUDA(cub::DeviceSelect::Flagged(tmp, bytes, iota, m->flags, sel, d_n, t->nnodes, st));
+  pyn::count_launch(2);
+  PYN_CHECK_CUDA(cudaMemcpyAsync(&m->nlist, d_n, sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+  PYN_CHECK_CUDA(cudaStreamSynchronize(st));
+  PYN_CHECK_CUDA(cudaMalloc(&m->list, sizeof(int) * (m->nlist > 0 ? m->nlist : 1)));
+  PYN_CHECK_CUDA(cudaMemcpyAsync(m->list, sel, sizeof(int) * m->nlist, cudaMemcpyDeviceToDevice, st));
+  PYN_CHECK_CUDA(cudaStreamSynchronize(st));
+  cudaFree(tmp); cudaFree(iota); cudaFree(sel); cudaFree(d_n);
+  *out = m;
+  return PYN_OK;
+}
+
+int pyn_bcmap_destroy(pyn_bcmap* m) {
+  if (!m) return PYN_OK;
+  cudaFree(m->flags);
+  cudaFree(m->list);
+  delete m;
+  return PYN_OK;
+}
+
+int pyn_bcmap_info(const pyn_bcmap* m, int64_t* n) {
+  PYN_REQUIRE(m, "bcmap is NULL");
+  if (n) *n = m->nlist;
+  return PYN_OK;
+}
 
 int pyn_asm_count(const pyn_topo* t, const pyn_asm_desc* desc, int64_t* d_indptr, int64_t* h_nnz, void* stream) {
   PYN_REQUIRE(t && d_indptr, "bad arguments");
@@ -287,7 +469,15 @@ int pyn_asm_count(const pyn_topo* t, const pyn_asm_desc* desc, int64_t* d_indptr
   const int64_t nrows = t->nnodes * dv.rdof;
   int* cnt = nullptr;
   PYN_CHECK_CUDA(cudaMallocAsync(&cnt, sizeof(int) * (nrows + 1), st));
-  rc = launch_asm<true>(t, dv, cnt, nullptr, nullptr, nullptr, st);
+  if (use_map(desc)) {
+    PYN_REQUIRE(desc->bcmap->nnodes == t->nnodes, "bcmap belongs to another topology");
+    asm_interior_count_kernel<<<pyn::grid_for(t->nnodes, 256), 256, 0, st>>>(pyn::view_of(t), dv.flags, dv.rdof, dv.cdof,
+                                                                             (int)(dv.pair_mask & 1u), cnt);
+    PYN_CHECK_LAUNCH();
+    rc = launch_asm<true>(t, dv, desc->bcmap->list, desc->bcmap->nlist, cnt, nullptr, nullptr, nullptr, st);
+  } else {
+    rc = launch_asm<true>(t, dv, nullptr, 0, cnt, nullptr, nullptr, nullptr, st);
+  }
   if (rc == PYN_OK) rc = pyn::scan_counts(cnt, nrows, d_indptr, h_nnz, st);
   PYN_CHECK_CUDA(cudaFreeAsync(cnt, st));
   return rc;
@@ -300,7 +490,16 @@ int pyn_asm_fill(const pyn_topo* t, const pyn_asm_desc* desc, const int64_t* d_i
   int rc = make_desc(desc, &dv);
   if (rc) return rc;
   PYN_REQUIRE(d_data == nullptr || dv.E != nullptr, "element matrices missing");
-  return launch_asm<false>(t, dv, nullptr, d_indptr, d_indices, d_data, pyn::as_stream(stream));
+  cudaStream_t st = pyn::as_stream(stream);
+  if (use_map(desc)) {
+    PYN_REQUIRE(desc->bcmap->nnodes == t->nnodes, "bcmap belongs to another topology");
+    if ((dv.pair_mask & 1u) && (d_data || d_indices)) {
+      rc = launch_interior(t, dv, d_indptr, d_indices, d_data, st);
+      if (rc) return rc;
+    }
+    return launch_asm<false>(t, dv, desc->bcmap->list, desc->bcmap->nlist, nullptr, d_indptr, d_indices, d_data, st);
+  }
+  return launch_asm<false>(t, dv, nullptr, 0, nullptr, d_indptr, d_indices, d_data, st);
 }
 
 int pyn_asm_weights(const pyn_topo* t, const double* d_We, int64_t stride, double* d_W, void* stream) {

@@ -18,6 +18,12 @@ struct pyn_topo {
   int max_valence, max_row;
 };
 
+struct pyn_bcmap {
+  int64_t nnodes, nlist;
+  uint8_t* flags;  // [nnodes] 1 = boundary-affected node
+  int* list;       // the flagged nodes, ascending
+};
+
 namespace pyn {
 struct TopoView {
   int64_t ne, nnodes;

@@ -110,10 +110,13 @@ def test_assembly_freeslip_vs_oracle(be, nx, ny, n):
     Ke_o, Rwe_o, _ = o.elem_kle_matrices(n, m.cell_corner_coords())
     s = _spectral(n)
     Ke_g, Rwe_g, _ = s.getElemKLEMatricesDevice(be.box_cell_corners(nx, ny, m.lower, m.upper), want_rd=False)
-    for Ke, Rwe, exact in ((be.to_device(Ke_o), be.to_device(Rwe_o), True), (Ke_g, Rwe_g, False)):
-        K = be.assemble(topo, 2, 2, Ke, cls, cls, [(0, 0)], diag_classes=0b100, diag_add=(0, 0, 1.0, 0))
-        Krhs = be.assemble(topo, 2, 2, Ke, cls, cls, [(0, 2)], diag_classes=0b100, diag_add=(0, 0, 1.0, 0), sign=-1.0)
-        Rw = be.assemble(topo, 2, 1, Rwe, cls, None, [(0, 0)])
+    maps = (be.BcMap(topo, cls, 2, cls, 2), be.BcMap(topo, cls, 2))
+    for Ke, Rwe, exact, mp in ((be.to_device(Ke_o), be.to_device(Rwe_o), True, (None, None)),
+                               (be.to_device(Ke_o), be.to_device(Rwe_o), True, maps), (Ke_g, Rwe_g, False, maps)):
+        K = be.assemble(topo, 2, 2, Ke, cls, cls, [(0, 0)], diag_classes=0b100, diag_add=(0, 0, 1.0, 0), bcmap=mp[0])
+        Krhs = be.assemble(topo, 2, 2, Ke, cls, cls, [(0, 2)], diag_classes=0b100, diag_add=(0, 0, 1.0, 0), sign=-1.0,
+                           bcmap=mp[0])
+        Rw = be.assemble(topo, 2, 1, Rwe, cls, None, [(0, 0)], bcmap=mp[1])
         for A, r in ((K, ref["K"]), (Krhs, ref["Krhs"]), (Rw, ref["Rw"])):
             _same_pattern(A, r)
             d = A.data.cpu().numpy()
@@ -133,21 +136,23 @@ def test_assembly_noslip_and_operators_vs_oracle(be, nx, ny, n):
     c0 = m.cell_corner_coords([0])
     Ke, Rwe, Rde = (be.to_device(a) for a in o.elem_kle_matrices(n, c0))
     one = (0, 1.0, 1.0, 0)
-    got = {
-        "K": be.assemble(topo, 2, 2, Ke, cls, cls, [(0, 0)], diag_classes=0b110, diag_add=one),
-        "Krhs": be.assemble(topo, 2, 2, Ke, cls, cls, [(0, 1), (0, 2)], diag_classes=0b110, diag_add=one, sign=-1.0),
-        "Kfs": be.assemble(topo, 2, 2, Ke, cls, cls, [(1, 0), (0, 1), (1, 1)], diag_classes=0b010,
-                           diag_add=(0, -1.0, 0, 0)),
-        "Rw": be.assemble(topo, 2, 1, Rwe, cls, None, [(0, 0)]),
-        "Rd": be.assemble(topo, 2, 1, Rde, cls, None, [(0, 0)]),
-        "Rwfs": be.assemble(topo, 2, 1, Rwe, cls, None, [(1, 0)]),
-        "Rdfs": be.assemble(topo, 2, 1, Rde, cls, None, [(1, 0)]),
-        "Krhsfs": be.assemble(topo, 2, 2, Ke, cls, cls, [(1, 2), (0, 2)], diag_classes=0b100, diag_add=(0, 0, 1.0, 0),
-                              sign=-1.0),
-    }
-    for name, A in got.items():
-        _same_pattern(A, ref[name])
-        np.testing.assert_array_equal(A.data.cpu().numpy(), ref[name].data, err_msg=name)
+    for m22, m21 in ((None, None), (be.BcMap(topo, cls, 2, cls, 2), be.BcMap(topo, cls, 2))):
+        got = {
+            "K": be.assemble(topo, 2, 2, Ke, cls, cls, [(0, 0)], diag_classes=0b110, diag_add=one, bcmap=m22),
+            "Krhs": be.assemble(topo, 2, 2, Ke, cls, cls, [(0, 1), (0, 2)], diag_classes=0b110, diag_add=one, sign=-1.0,
+                                bcmap=m22),
+            "Kfs": be.assemble(topo, 2, 2, Ke, cls, cls, [(1, 0), (0, 1), (1, 1)], diag_classes=0b010,
+                               diag_add=(0, -1.0, 0, 0), bcmap=m22),
+            "Rw": be.assemble(topo, 2, 1, Rwe, cls, None, [(0, 0)], bcmap=m21),
+            "Rd": be.assemble(topo, 2, 1, Rde, cls, None, [(0, 0)], bcmap=m21),
+            "Rwfs": be.assemble(topo, 2, 1, Rwe, cls, None, [(1, 0)], bcmap=m21),
+            "Rdfs": be.assemble(topo, 2, 1, Rde, cls, None, [(1, 0)], bcmap=m21),
+            "Krhsfs": be.assemble(topo, 2, 2, Ke, cls, cls, [(1, 2), (0, 2)], diag_classes=0b100,
+                                  diag_add=(0, 0, 1.0, 0), sign=-1.0, bcmap=m22),
+        }
+        for name, A in got.items():
+            _same_pattern(A, ref[name])
+            np.testing.assert_array_equal(A.data.cpu().numpy(), ref[name].data, err_msg=name)
     KK = got["K"].add(got["Kfs"])
     rKK = o.mat_add(ref["K"], ref["Kfs"])
     _same_pattern(KK, rKK)
@@ -158,8 +163,12 @@ def test_assembly_noslip_and_operators_vs_oracle(be, nx, ny, n):
     Wg = be.assemble_weights(topo, W)
     np.testing.assert_array_equal(Wg.cpu().numpy(), rops["W"])
     rW = 1.0 / Wg
+    nomap = be.BcMap(topo)
+    assert nomap.n_boundary == 0
     for name, E, rd, cd in (("SrT", S, 3, 2), ("DivSrT", D, 2, 3), ("Curl", C, 1, 2)):
-        A = be.assemble(topo, rd, cd, E, rowscale=rW)
+        A0 = be.assemble(topo, rd, cd, E, rowscale=rW)
+        A = be.assemble(topo, rd, cd, E, rowscale=rW, bcmap=nomap)
+        np.testing.assert_array_equal(A0.data.cpu().numpy(), A.data.cpu().numpy())
         _same_pattern(A, rops[name])
         np.testing.assert_array_equal(A.data.cpu().numpy(), rops[name].data, err_msg=name)
         Ac = A.compressed()

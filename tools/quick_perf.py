@@ -31,18 +31,22 @@ def run(nx, n, per_cell=False):
     cc = be.box_cell_corners(nx, nx, [0, 0], [1, 1], 0, nx * nx if per_cell else 1)
     t_el, (Ke, Rwe, _) = timed(lambda: s.getElemKLEMatricesDevice(cc, want_rd=False), 2)
     t0 = time.time()
-    K = be.assemble(topo, 2, 2, Ke, cls, cls, [(0, 0)], diag_classes=0b100, diag_add=(0, 0, 1.0, 0))
+    mp = be.BcMap(topo, cls, 2, cls, 2)
+    torch.cuda.synchronize()
+    t_map = time.time() - t0
+    t0 = time.time()
+    K = be.assemble(topo, 2, 2, Ke, cls, cls, [(0, 0)], diag_classes=0b100, diag_add=(0, 0, 1.0, 0), bcmap=mp)
     torch.cuda.synchronize()
     t_first = time.time() - t0
     t_fill, _ = timed(lambda: be.assemble(topo, 2, 2, Ke, cls, cls, [(0, 0)], diag_classes=0b100,
-                                          diag_add=(0, 0, 1.0, 0), pattern=K))
+                                          diag_add=(0, 0, 1.0, 0), pattern=K, bcmap=mp))
     x, y = torch.randn(2 * nnodes, dtype=torch.float64, device="cuda"), be.empty(2 * nnodes)
     t_spmv, _ = timed(lambda: K.mult(x, y), 5)
     gb = K.bytes_spmv() / 1e9
     ksp = be.Ksp(K, "cg", "jacobi", rtol=1e-30, max_it=64, check_every=64)
     sol = be.empty(2 * nnodes)
     t_cg, r = timed(lambda: ksp.solve(y, sol), 2)
-    print(f"nx={nx} n={n} nodes={nnodes} adj_nnz={topo.adj_nnz} Knnz={K.nnz} | topo {t_topo*1e3:.1f} ms | elem({cc.shape[0]}) {t_el:.2f} ms | "
+    print(f"nx={nx} n={n} nodes={nnodes} adj_nnz={topo.adj_nnz} Knnz={K.nnz} | topo {t_topo*1e3:.1f} ms bcmap {t_map*1e3:.1f} ms ({mp.n_boundary}) | elem({cc.shape[0]}) {t_el:.2f} ms | "
           f"asm first {t_first*1e3:.1f} ms, values-only {t_fill:.2f} ms = {8*K.nnz/t_fill/1e6:.0f} GB/s(vals) {2*nnodes/t_fill/1e6:.2f} GDOF/s | "
           f"spmv {t_spmv:.3f} ms = {gb/t_spmv*1e3:.0f} GB/s | cg {r.its} its {t_cg/ max(r.its,1):.3f} ms/it", flush=True)
 
