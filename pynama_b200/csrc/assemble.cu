@@ -128,72 +128,104 @@ asm_gather_kernel(pyn::TopoView t, DescView d, const int* __restrict__ list, int
 
 // Interior nodes (bcmap flag 0): every class is 0, so the node keeps either all its L*CD entries per row or none;
 // no class lookups, no compaction, positions are p*CD+b.  Launched only when the (free,free) pair is kept.
-template <int RD, int CD>
+//
+// A CTA takes ASM_NB consecutive nodes: their headers (row pointers, incidence lists, output bases) are staged in
+// shared memory with one coalesced round of loads, then the CTA's threads share the nodes' adjacency positions --
+// which are contiguous in the adjacency CSR -- one output block per thread and step.  Every thread's work is then a
+// short independent chain (inverse-map byte -> element-matrix entries from L1 -> coalesced store), so the kernel is
+// limited by the store stream instead of by per-node latency.
+constexpr int ASM_NB = 32;     // nodes per CTA batch
+constexpr int ASM_MAXDEG = 8;  // nodes with more incident elements are routed to the generic kernel by the bcmap
+
+template <int RD, int CD, bool VEC>
 __global__ void __launch_bounds__(256)
 asm_interior_kernel(pyn::TopoView t, DescView d, const int64_t* __restrict__ indptr, int* __restrict__ indices,
                     double* __restrict__ data) {
-  const int lane = threadIdx.x & 31;
-  const int64_t warp0 = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
-  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  __shared__ int64_t s_adj[ASM_NB + 1], s_inv[ASM_NB], s_base[ASM_NB * RD], s_eoff[ASM_NB * ASM_MAXDEG];
+  __shared__ int s_n2e[ASM_NB + 1];
+  __shared__ double s_rs[ASM_NB];
+  __shared__ uint8_t s_flag[ASM_NB];
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
   const int ldE = CD * t.nn;
-  for (int64_t r = warp0; r < t.nnodes; r += nwarps) {
-    if (d.flags[r]) continue;
-    const int64_t a0 = t.adj_ptr[r], b0 = t.n2e_ptr[r], iv0 = t.inv_ptr[r];
-    const int L = (int)(t.adj_ptr[r + 1] - a0), deg = (int)(t.n2e_ptr[r + 1] - b0);
-    int my_e = 0, my_lr = 0;
-    if (lane < deg) {
-      my_e = t.n2e_elem[b0 + lane];
-      my_lr = t.n2e_loc[b0 + lane];
+  const int64_t nbatch = (t.nnodes + ASM_NB - 1) / ASM_NB;
+  for (int64_t batch = blockIdx.x; batch < nbatch; batch += gridDim.x) {
+    const int64_t r0 = batch * ASM_NB;
+    const int nb = (int)min((int64_t)ASM_NB, t.nnodes - r0);
+    const int64_t e0 = t.n2e_ptr[r0];
+    if (tid <= nb) {
+      s_adj[tid] = t.adj_ptr[r0 + tid];
+      s_n2e[tid] = (int)(t.n2e_ptr[r0 + tid] - e0);
     }
-    int64_t base[RD];
-#pragma unroll
-    for (int a = 0; a < RD; ++a) base[a] = indptr[r * RD + a];
-    const double rs = d.rowscale ? d.rowscale[r] : 1.0;
-    for (int p0 = 0; p0 < L; p0 += 32) {
-      const int p = p0 + lane;
-      const bool valid = p < L;
-      double v[RD][CD];
-#pragma unroll
-      for (int a = 0; a < RD; ++a)
-#pragma unroll
-        for (int b = 0; b < CD; ++b) v[a][b] = 0.0;
-      if (data) {
-        for (int k = 0; k < deg; ++k) {  // ascending cell order
-          const int e = __shfl_sync(0xffffffffu, my_e, k), lr = __shfl_sync(0xffffffffu, my_lr, k);
-          const int l = valid ? (int)t.inv[iv0 + (int64_t)k * L + p] : 0xFF;
-          if (l != 0xFF) {
-            const double* Ee = d.E + (d.E_stride ? (int64_t)e * d.E_stride : 0) + (int64_t)lr * RD * ldE + l * CD;
-#pragma unroll
-            for (int a = 0; a < RD; ++a)
-#pragma unroll
-              for (int b = 0; b < CD; ++b) v[a][b] += d.sign * Ee[a * ldE + b];
-          }
-        }
+    if (tid < nb) {
+      s_inv[tid] = t.inv_ptr[r0 + tid];
+      s_flag[tid] = d.flags[r0 + tid];
+      s_rs[tid] = d.rowscale ? d.rowscale[r0 + tid] : 1.0;
+    }
+    if (tid >= 64 && tid < 64 + nb * RD) s_base[tid - 64] = indptr[r0 * RD + (tid - 64)];
+    __syncthreads();
+    {  // element-matrix row offsets of every (node, incident element): 8 threads per node
+      const int j = tid >> 3, k = tid & 7;
+      if (j < nb && !s_flag[j] && k < s_n2e[j + 1] - s_n2e[j]) {
+        const int64_t q = e0 + s_n2e[j] + k;
+        s_eoff[j * ASM_MAXDEG + k] = (d.E_stride ? (int64_t)t.n2e_elem[q] * d.E_stride : 0) +
+                                     (int64_t)t.n2e_loc[q] * RD * ldE;
       }
-      if (!valid) continue;
-      if (data) {
-#pragma unroll
-        for (int a = 0; a < RD; ++a) {
-          double* o = data + base[a] + (int64_t)p * CD;
-#pragma unroll
-          for (int b = 0; b < CD; ++b)
-            if (d.rowscale) v[a][b] = rs * v[a][b];
-          if (CD == 2 && ((base[a] & 1) == 0)) {
-            *reinterpret_cast<double2*>(o) = make_double2(v[a][0], v[a][CD - 1]);
-          } else {
-#pragma unroll
-            for (int b = 0; b < CD; ++b) o[b] = v[a][b];
-          }
-        }
-      }
-      if (indices) {
-        const int c = t.adj_cols[a0 + p];
+    }
+    __syncthreads();
+    for (int j = w; j < nb; j += 8) {  // one warp per node, lanes over its adjacency positions
+      if (s_flag[j]) continue;
+      const int L = (int)(s_adj[j + 1] - s_adj[j]), deg = s_n2e[j + 1] - s_n2e[j];
+      const uint8_t* ivj = t.inv + s_inv[j];
+      const double rs = s_rs[j];
+      for (int p = lane; p < L; p += 32) {
+        double v[RD][CD];
 #pragma unroll
         for (int a = 0; a < RD; ++a)
 #pragma unroll
-          for (int b = 0; b < CD; ++b) indices[base[a] + (int64_t)p * CD + b] = c * CD + b;
+          for (int b = 0; b < CD; ++b) v[a][b] = 0.0;
+        if (data) {
+          for (int k = 0; k < deg; ++k) {  // ascending cell order
+            const int l = ivj[k * L + p];
+            if (l != 0xFF) {
+              const double* Ee = d.E + s_eoff[j * ASM_MAXDEG + k] + l * CD;
+#pragma unroll
+              for (int a = 0; a < RD; ++a) {
+                if (VEC) {  // CD == 2, 16-byte aligned element matrices
+                  const double2 e2 = *reinterpret_cast<const double2*>(Ee + a * ldE);
+                  v[a][0] += d.sign * e2.x;
+                  v[a][CD - 1] += d.sign * e2.y;
+                } else {
+#pragma unroll
+                  for (int b = 0; b < CD; ++b) v[a][b] += d.sign * Ee[a * ldE + b];
+                }
+              }
+            }
+          }
+#pragma unroll
+          for (int a = 0; a < RD; ++a) {
+            const int64_t base = s_base[j * RD + a];
+            double* o = data + base + p * CD;
+#pragma unroll
+            for (int b = 0; b < CD; ++b)
+              if (d.rowscale) v[a][b] = rs * v[a][b];
+            if (CD == 2 && ((base & 1) == 0)) {
+              *reinterpret_cast<double2*>(o) = make_double2(v[a][0], v[a][CD - 1]);
+            } else {
+#pragma unroll
+              for (int b = 0; b < CD; ++b) o[b] = v[a][b];
+            }
+          }
+        }
+        if (indices) {
+          const int c = t.adj_cols[s_adj[j] + p];
+#pragma unroll
+          for (int a = 0; a < RD; ++a)
+#pragma unroll
+            for (int b = 0; b < CD; ++b) indices[s_base[j * RD + a] + p * CD + b] = c * CD + b;
+        }
       }
     }
+    __syncthreads();
   }
 }
 
@@ -214,8 +246,8 @@ __global__ void bcmap_flags_kernel(pyn::TopoView t, const int8_t* __restrict__ r
   const int64_t warp0 = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
   const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
   for (int64_t r = warp0; r < t.nnodes; r += nwarps) {
-    bool f = false;
-    if (rclass && lane < rdof) f = rclass[r * rdof + lane] != 0;
+    bool f = (t.n2e_ptr[r + 1] - t.n2e_ptr[r]) > ASM_MAXDEG;  // high-valence nodes take the generic kernel
+    if (rclass && lane < rdof) f = f || (rclass[r * rdof + lane] != 0);
     if (cclass) {
       const int64_t a0 = t.adj_ptr[r];
       const int L = (int)(t.adj_ptr[r + 1] - a0);
@@ -393,10 +425,14 @@ static int launch_asm(const pyn_topo* t, const DescView& dv, const int* list, in
 static int launch_interior(const pyn_topo* t, const DescView& dv, const int64_t* indptr, int* indices, double* data,
                            cudaStream_t st) {
   const pyn::TopoView tv = pyn::view_of(t);
-  const int grid = pyn::grid_for(t->nnodes * 32, 256, 16);
+  const int grid = pyn::grid_for((t->nnodes + ASM_NB - 1) / ASM_NB * 256, 256, 8);
+  const bool vec = ((reinterpret_cast<uintptr_t>(dv.E) & 15) == 0) && ((dv.E_stride & 1) == 0);
 #define PYN_ASM_CASE(R, C)                                                                        \
   if (dv.rdof == R && dv.cdof == C) {                                                             \
-    asm_interior_kernel<R, C><<<grid, 256, 0, st>>>(tv, dv, indptr, indices, data);               \
+    if (C == 2 && vec)                                                                            \
+      asm_interior_kernel<R, C, (C == 2)><<<grid, 256, 0, st>>>(tv, dv, indptr, indices, data);   \
+    else                                                                                          \
+      asm_interior_kernel<R, C, false><<<grid, 256, 0, st>>>(tv, dv, indptr, indices, data);      \
     PYN_CHECK_LAUNCH();                                                                           \
     return PYN_OK;                                                                                \
   }
