@@ -136,12 +136,14 @@ asm_gather_kernel(pyn::TopoView t, DescView d, const int* __restrict__ list, int
 // limited by the store stream instead of by per-node latency.
 constexpr int ASM_NB = 32;     // nodes per CTA batch
 constexpr int ASM_MAXDEG = 8;  // nodes with more incident elements are routed to the generic kernel by the bcmap
+constexpr int ASM_IVCAP = 12288;  // bytes of the inverse position map staged in shared memory per batch
 
 template <int RD, int CD, bool VEC>
 __global__ void __launch_bounds__(256)
 asm_interior_kernel(pyn::TopoView t, DescView d, const int64_t* __restrict__ indptr, int* __restrict__ indices,
                     double* __restrict__ data) {
-  __shared__ int64_t s_adj[ASM_NB + 1], s_inv[ASM_NB], s_base[ASM_NB * RD], s_eoff[ASM_NB * ASM_MAXDEG];
+  __shared__ int64_t s_adj[ASM_NB + 1], s_inv[ASM_NB + 1], s_base[ASM_NB * RD], s_eoff[ASM_NB * ASM_MAXDEG];
+  __shared__ __align__(16) uint8_t s_ivb[ASM_IVCAP + 32];
   __shared__ int s_n2e[ASM_NB + 1];
   __shared__ double s_rs[ASM_NB];
   __shared__ uint8_t s_flag[ASM_NB];
@@ -155,14 +157,24 @@ asm_interior_kernel(pyn::TopoView t, DescView d, const int64_t* __restrict__ ind
     if (tid <= nb) {
       s_adj[tid] = t.adj_ptr[r0 + tid];
       s_n2e[tid] = (int)(t.n2e_ptr[r0 + tid] - e0);
+      s_inv[tid] = t.inv_ptr[r0 + tid];
     }
     if (tid < nb) {
-      s_inv[tid] = t.inv_ptr[r0 + tid];
       s_flag[tid] = d.flags[r0 + tid];
       s_rs[tid] = d.rowscale ? d.rowscale[r0 + tid] : 1.0;
     }
     if (tid >= 64 && tid < 64 + nb * RD) s_base[tid - 64] = indptr[r0 * RD + (tid - 64)];
     __syncthreads();
+    // the batch's slice of the inverse position map is contiguous: stage it with 16-byte loads (aligned superset)
+    const uint8_t* ivsrc = t.inv + s_inv[0];
+    const int mis = (int)(reinterpret_cast<uintptr_t>(ivsrc) & 15);
+    const int64_t ivlen = s_inv[nb] - s_inv[0];
+    const bool staged = ivlen + mis <= ASM_IVCAP;
+    if (staged && data) {
+      const uint4* src = reinterpret_cast<const uint4*>(ivsrc - mis);
+      const int n16 = (int)((ivlen + mis + 15) >> 4);
+      for (int i = tid; i < n16; i += 256) reinterpret_cast<uint4*>(s_ivb)[i] = src[i];
+    }
     {  // element-matrix row offsets of every (node, incident element): 8 threads per node
       const int j = tid >> 3, k = tid & 7;
       if (j < nb && !s_flag[j] && k < s_n2e[j + 1] - s_n2e[j]) {
@@ -175,7 +187,7 @@ asm_interior_kernel(pyn::TopoView t, DescView d, const int64_t* __restrict__ ind
     for (int j = w; j < nb; j += 8) {  // one warp per node, lanes over its adjacency positions
       if (s_flag[j]) continue;
       const int L = (int)(s_adj[j + 1] - s_adj[j]), deg = s_n2e[j + 1] - s_n2e[j];
-      const uint8_t* ivj = t.inv + s_inv[j];
+      const uint8_t* ivj = staged ? s_ivb + mis + (int)(s_inv[j] - s_inv[0]) : t.inv + s_inv[j];
       const double rs = s_rs[j];
       for (int p = lane; p < L; p += 32) {
         double v[RD][CD];

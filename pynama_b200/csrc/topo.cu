@@ -369,7 +369,7 @@ int pyn_topo_create(const int32_t* d_e2n, int64_t ne, int nn, int64_t nnodes, vo
   pyn::count_launch();
   TOPO_TRY(cuda_try(cudaMalloc(&t->inv_ptr, sizeof(int64_t) * (nnodes + 1)), "malloc inv_ptr"));
   TOPO_TRY(pyn::scan_counts(cnt, nnodes, t->inv_ptr, &t->inv_len, st));
-  TOPO_TRY(cuda_try(cudaMalloc(&t->inv, (size_t)(t->inv_len > 0 ? t->inv_len : 1)), "malloc inv"));
+  TOPO_TRY(cuda_try(cudaMalloc(&t->inv, (size_t)t->inv_len + 32), "malloc inv"));
   v = pyn::view_of(t);
   {
     int rcap = 32;
