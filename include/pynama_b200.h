@@ -188,7 +188,7 @@ int pyn_vec_axpy(int64_t n, double a, const double* d_x, double* d_y, void* stre
 int pyn_vec_aypx(int64_t n, double a, const double* d_x, double* d_y, void* stream);          /* y = x + a y */
 int pyn_vec_waxpy(int64_t n, double a, const double* d_x, const double* d_y, double* d_w, void* stream); /* w = a x + y */
 int pyn_vec_maxpy(int64_t n, int m, const double* h_coef, const double* const* h_xs, const double* d_y0,
-                  double* d_y, void* stream);                                                 /* y = y0 + sum c_j x_j */
+                  double* d_y, void* stream);                          /* y = y0 + sum c_j x_j ; y0 NULL = 0 */
 int pyn_vec_dot(int64_t n, const double* d_x, const double* d_y, double* h_out, void* stream); /* synchronises */
 int pyn_vec_norm(int64_t n, const double* d_x, int kind /*2: l2, 3: inf*/, double* h_out, void* stream);
 int pyn_vec_scatter_set(int64_t nidx, const int64_t* d_idx, const double* d_vals, double* d_x, void* stream);

@@ -658,3 +658,105 @@ def rk5bs_step(f, t, y, dt, k1=None):
             y5 = y5 + (dt * b[j]) * k[j]
         err = err + (dt * (b[j] - bh[j])) * k[j]
     return y5, err, k[7]
+
+
+# --------------------------------------------------------------------------------------------------------
+# R1  case-level flows: boundary vectors and the velocity-from-vorticity solves
+# --------------------------------------------------------------------------------------------------------
+def direct_solve(A, b):
+    """Stand-in for the reference's default `preonly` + `lu` (src/solver/ksp_solver.py:13-16): SuperLU."""
+    import scipy.sparse.linalg as spla
+    return spla.spsolve(A.tocsc(), b)
+
+
+def cavity_wall_vectors(mesh, moving=(("up", (1.0, 0.0)),)):
+    """Cavity.applyBoundaryConditions / applyBoundaryConditionsFS (src/cases/cavity.py:53-81) as data:
+    returns vel_bc[2N] (zero except the moving walls' tangential component) and (dofs, values) assigned to velFS
+    after the free-slip solve, in assignment order (moving walls first, then the static walls' tangential dofs)."""
+    normal = {"down": 1, "up": 1, "left": 0, "right": 0}
+    vel = np.zeros(2 * mesh.nnodes)
+    fs_d, fs_v = [], []
+    moving = dict(moving)
+    for name, v in moving.items():
+        tang = 1 - normal[name]
+        d = mesh.border_nodes(name) * 2 + tang
+        vel[d] = v[tang]
+        fs_d.append(d)
+        fs_v.append(np.full(len(d), float(v[tang])))
+    for name in ("left", "right", "up", "down"):          # NoSlipWalls side order (common/nswalls.py:13)
+        if name in moving:
+            continue
+        d = mesh.border_nodes(name) * 2 + (1 - normal[name])
+        fs_d.append(d)
+        fs_v.append(np.zeros(len(d)))
+    return vel, np.concatenate(fs_d), np.concatenate(fs_v)
+
+
+def solve_kle_noslip(mats, ops, vel_bc, fs_dofs, fs_vals, vort, solve=direct_solve, solve_fs=None, KFS=None):
+    """NoSlipFreeSlip.solveKLE (src/cases/base_problem.py:321-327)."""
+    KFS = mat_add(mats["K"], mats["Kfs"]) if KFS is None else KFS
+    solve_fs = solve if solve_fs is None else solve_fs
+    rhs1 = mats["Rw"] @ vort + mats["Rwfs"] @ vort + mats["Krhsfs"] @ vel_bc
+    vel_fs = solve_fs(KFS, rhs1)
+    vel_fs = vel_fs.copy()
+    vel_fs[fs_dofs] = fs_vals
+    vort2 = ops["Curl"] @ vel_fs
+    vel = solve(mats["K"], mats["Rw"] @ vort2 + mats["Krhs"] @ vel_bc)
+    return vel, vel_fs, vort2
+
+
+def solve_kle_freeslip(mats, vel_bc, vort, solve=direct_solve):
+    """FreeSlip.solveKLE (src/cases/base_problem.py:479-481)."""
+    return solve(mats["K"], mats["Rw"] @ vort + mats["Krhs"] @ vel_bc)
+
+
+def rk_fixed_steps(f, t0, y0, dt, nsteps, post=None):
+    """nsteps of RK5BS with a fixed step and FSAL reuse (TSRK with -ts_adapt_type none)."""
+    t, y, k1 = t0, y0.copy(), None
+    for _ in range(nsteps):
+        y, _, k1 = rk5bs_step(f, t, y, dt, k1)
+        t += dt
+        if post is not None:
+            y = post(t, y)
+    return t, y
+
+
+def wrms(err, y, ynew, atol, rtol):
+    """TSErrorWeightedNorm (NORM_2): sqrt(mean((e_i / (atol + rtol*max(|y_i|,|ynew_i|)))^2))."""
+    tol = atol + rtol * np.maximum(np.abs(y), np.abs(ynew))
+    return math.sqrt(np.mean((err / tol) ** 2))
+
+
+def rk_adaptive(f, t0, y0, t_end, dt0=0.1, atol=1e-4, rtol=1e-4, max_steps=5000, safety=0.9, reject_safety=0.5,
+                clip=(0.1, 10.0)):
+    """TSRK 5bs + TSAdapt basic + MATCHSTEP restated (SURVEY 8a''): returns t, y, accepted step sizes, rejections."""
+    def match(tn, h):
+        hmax = t_end - tn
+        if tn < t_end and t_end < tn + h * 1.01:
+            return hmax
+        if tn < t_end and t_end < tn + h * 2.0:
+            return hmax / 2
+        return h
+    t, y, k1, dt = t0, y0.copy(), None, dt0
+    if t + dt > t_end:
+        dt = t_end - t
+    hs, nrej, steps = [], 0, 0
+    while t < t_end and steps < max_steps:
+        prev_rejected = False
+        while True:
+            y5, err, k8 = rk5bs_step(f, t, y, dt, k1)
+            k1 = f(t, y) if k1 is None else k1
+            e = wrms(err, y5, y5 - err, atol, rtol)
+            accept = e <= 1.0
+            s = safety * (reject_safety if (prev_rejected and not accept) else 1.0)
+            fac = clip[1] if e == 0.0 else min(max(s * e ** (-1.0 / 5.0), clip[0]), clip[1])
+            if accept:
+                break
+            nrej += 1
+            prev_rejected = True
+            dt = match(t, dt * fac)
+        hs.append(dt)
+        t, y, k1 = t + dt, y5, k8
+        steps += 1
+        dt = match(t, dt * fac)
+    return t, y, hs, nrej

@@ -41,7 +41,7 @@ class Wall(object):
             raise Exception("Velocity not valid")
         self.velocity = np.array([vel[d] for d in moving])
         self.velDofs = moving
-        self.staticDofs = [d for d in self.staticDofs if d not in moving]
+        self.staticDofs[:] = [d for d in self.staticDofs if d not in moving]   # in place: callers hold the list
 
     def getWallVelocity(self):
         if self.velocity is not None:

@@ -28,7 +28,7 @@ struct MaxpyArgs {
 __global__ void maxpy_kernel(int64_t n, const __grid_constant__ MaxpyArgs a, const double* __restrict__ y0,
                              double* __restrict__ y) {
   for (int64_t i = blockIdx.x * (int64_t)BLK + threadIdx.x; i < n; i += (int64_t)gridDim.x * BLK) {
-    double s = y0[i];
+    double s = y0 ? y0[i] : 0.0;
 #pragma unroll
     for (int j = 0; j < 8; ++j)
       if (j < a.m) s += a.c[j] * a.x[j][i];
@@ -150,7 +150,7 @@ int pyn_vec_waxpy(int64_t n, double a, const double* x, const double* y, double*
 }
 int pyn_vec_maxpy(int64_t n, int m, const double* h_coef, const double* const* h_xs, const double* y0, double* y,
                   void* stream) {
-  PYN_REQUIRE(m >= 0 && m <= 8 && y0 && y, "maxpy supports at most 8 vectors");
+  PYN_REQUIRE(m >= 0 && m <= 8 && y, "maxpy supports at most 8 vectors");
   MaxpyArgs a;
   a.m = m;
   for (int j = 0; j < 8; ++j) {

@@ -1,0 +1,145 @@
+"""`KspSolver`: the linear solver of the velocity-from-vorticity problem (reference: src/solver/ksp_solver.py:9-19;
+use sites src/cases/base_problem.py:276,318,323-327,481).
+
+Same surface -- `KspSolver()`, `createSolver(mat, comm)`, `solver(b, x)` -- and the same precedence of settings: the
+reference's defaults (`preonly` + `lu`) first, then whatever the options database says (`-ksp_type`, `-pc_type`,
+`-ksp_rtol`, `-ksp_atol`, `-ksp_divtol`, `-ksp_max_it`, `-ksp_gmres_restart`), then `setOperators` / `setUp`.
+The iterations run on the device (csrc/ksp.cu) with PETSc's semantics: zero initial guess, left preconditioning,
+preconditioned residual norm, KSPConvergedDefault.
+
+`preonly` + `lu` (a sparse direct factorisation) has no device counterpart in this build; it is served by
+Jacobi-preconditioned CG driven to `DIRECT_RTOL` followed by `DIRECT_REFINE` passes of iterative refinement
+(r = b - A x, A d = r, x += d), i.e. "solve to round-off" like a direct solver would, and says so in the log.  Parity statements about KSP are made for `-ksp_type cg -pc_type jacobi` at matched tolerances.
+"""
+import logging
+
+from .. import backend as be
+from ..common.options import Options
+
+
+class ConvergedReason:
+    CONVERGED_RTOL, CONVERGED_ATOL, CONVERGED_ITS = 2, 3, 4
+    DIVERGED_MAX_IT, DIVERGED_DTOL, DIVERGED_BREAKDOWN, DIVERGED_INDEFINITE_MAT = -3, -4, -5, -8
+
+
+class KspSolver(object):
+    DIRECT_RTOL = 1e-10          # stand-in for preonly + lu: CG to this tolerance ...
+    DIRECT_REFINE = 2            # ... then this many passes of iterative refinement
+    DIRECT_MAX_IT = 200000
+
+    def __init__(self):
+        self.logger = None
+        self._ksp = None
+        self._direct = False
+        self._type, self._pc = "preonly", "lu"
+        self.rtol, self.atol, self.divtol, self.max_it = 1e-5, 1e-50, 1e4, 10000
+        self.restart = 30
+        self.check_every = 0
+        self.its, self.reason, self.rnorm = 0, 0, 0.0
+        self.history = []
+
+    # -- petsc4py KSP surface used by the reference -------------------------------------------------------------
+    def create(self, comm=None):
+        self.comm = comm
+        return self
+
+    def setType(self, t):
+        self._type = t
+
+    def getType(self):
+        return self._type
+
+    def setPCType(self, t):
+        self._pc = t
+
+    def setTolerances(self, rtol=None, atol=None, divtol=None, max_it=None):
+        if rtol is not None:
+            self.rtol = rtol
+        if atol is not None:
+            self.atol = atol
+        if divtol is not None:
+            self.divtol = divtol
+        if max_it is not None:
+            self.max_it = max_it
+
+    def getTolerances(self):
+        return self.rtol, self.atol, self.divtol, self.max_it
+
+    def setFromOptions(self):
+        o = Options()
+        self._type = o.getString("ksp_type", self._type)
+        self._pc = o.getString("pc_type", self._pc)
+        self.rtol = o.getReal("ksp_rtol", self.rtol)
+        self.atol = o.getReal("ksp_atol", self.atol)
+        self.divtol = o.getReal("ksp_divtol", self.divtol)
+        self.max_it = o.getInt("ksp_max_it", self.max_it)
+        self.restart = o.getInt("ksp_gmres_restart", self.restart)
+        self.check_every = o.getInt("ksp_check_every", self.check_every)
+
+    def setOperators(self, mat):
+        self.mat = mat
+
+    def getOperators(self):
+        return self.mat, self.mat
+
+    def setUp(self):
+        ksp_type, pc = self._type, self._pc
+        rtol, max_it = self.rtol, self.max_it
+        if ksp_type == "preonly":
+            if pc not in ("lu", "cholesky"):
+                raise Exception(f"KSP preonly with PC {pc} is not available on the device path")
+            self.logger.info("preonly+lu requested: served by device CG+Jacobi to rtol %g (no sparse direct "
+                             "factorisation on the device path)", self.DIRECT_RTOL)
+            ksp_type, pc, rtol, max_it = "cg", "jacobi", self.DIRECT_RTOL, self.DIRECT_MAX_IT
+            self._direct = True
+        if ksp_type not in be.Ksp.TYPES:
+            raise Exception(f"KSP type {ksp_type} is not available on the device path (cg, gmres)")
+        if pc not in be.Ksp.PCS:
+            raise Exception(f"PC type {pc} is not available on the device path (none, jacobi)")
+        csr = self.mat.csr if hasattr(self.mat, "csr") else self.mat
+        self._ksp = be.Ksp(csr, ksp_type, pc, rtol=rtol, atol=self.atol, dtol=self.divtol, max_it=max_it,
+                           restart=self.restart, check_every=self.check_every)
+
+    def createSolver(self, mat, comm=None):
+        self.logger = logging.getLogger("KSP Solver")
+        self.logger.debug("setupKSP")
+        self.create(comm)
+        self.setType('preonly')
+        self.setPCType('lu')
+        self.setFromOptions()
+        self.setOperators(mat)
+        self.setUp()
+
+    def solve(self, b, x):
+        r = self._ksp.solve(b.data, x.data)
+        if self._direct and r.reason > 0:
+            csr = self._ksp.A
+            if getattr(self, "_res", None) is None or self._res.numel() != b.data.numel():
+                self._res, self._cor = be.empty(b.data.numel()), be.empty(b.data.numel())
+            for _ in range(self.DIRECT_REFINE):
+                csr.mult(x.data, self._res)                       # A x
+                be.vec_maxpy(self._res, b.data, [-1.0], [self._res])   # r = b - A x
+                rr = self._ksp.solve(self._res, self._cor)
+                if rr.reason < 0:
+                    break
+                be.vec_axpy(x.data, 1.0, self._cor)
+        self.its, self.reason, self.rnorm = r.its, r.reason, r.rnorm
+        self.history.append((r.its, r.reason))
+        if r.reason < 0:
+            self.logger.warning("KSP did not converge: reason %d after %d iterations (rnorm %.3e)", r.reason, r.its,
+                                r.rnorm)
+        return r
+
+    __call__ = solve
+
+    def getIterationNumber(self):
+        return self.its
+
+    def getConvergedReason(self):
+        return self.reason
+
+    def getResidualNorm(self):
+        return self.rnorm
+
+    def destroy(self):
+        self._ksp = None

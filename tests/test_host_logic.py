@@ -1,0 +1,163 @@
+"""CPU tests of the host-side mirror of the reference interface: wall bookkeeping (assertions of the reference's
+src/tests/test_nswalls.py), the options database, the preallocation helpers (src/tests/test_mat.py:15-25), the RK
+tableaus, the dof classification against the oracle, and the box-mesh queries of DMPlexDom against the reference's
+src/tests/test_domain.py.  None of this needs a GPU (no kernel is launched)."""
+from fractions import Fraction as F
+
+import numpy as np
+import pytest
+
+import kle_oracle as o
+from pynama_b200.common.nswalls import NoSlipWalls
+from pynama_b200.common.options import Options
+
+
+# ---- src/tests/test_nswalls.py -----------------------------------------------------------------------------------------
+def _box(dim=2):
+    lower = np.random.default_rng(0).random(dim)
+    return lower, lower + np.random.default_rng(1).random(dim)
+
+
+def test_walls_with_velocity():
+    lower, upper = _box()
+    ns = NoSlipWalls(lower, upper)
+    ns.setWallVelocity("up", [1, 0])
+    ns.setWallVelocity("down", [2, 0])
+    assert set(ns.getWallsWithVelocity()) == {"up", "down"}
+    assert set(ns.getStaticWalls()) == {"left", "right"}
+    vel, dofs = ns.getWallVelocity("up")
+    assert len(vel) == 1 and vel[0] == 1 and list(dofs) == [0]
+    vel, dofs = ns.getWallVelocity("down")
+    assert vel[0] == 2 and dofs[0] == 0
+    ns2 = NoSlipWalls(lower, upper)
+    ns2.setWallVelocity("left", [0, 1])
+    ns2.setWallVelocity("right", [0, 2])
+    assert set(ns2.getWallsWithVelocity()) == {"left", "right"}
+    vel, dofs = ns2.getWallVelocity("right")
+    assert vel[0] == 2 and dofs[0] == 1
+
+
+def test_ignore_velocity_normal():
+    lower, upper = _box()
+    ns = NoSlipWalls(lower, upper)
+    ns.setWallVelocity("up", [0, 3])        # purely normal: ignored
+    ns.setWallVelocity("left", [4, 0])
+    ns.setWallVelocity("nowhere", [1, 0])
+    ns.setWallVelocity("down", [1, 0, 0])   # wrong dimension
+    assert list(ns.getWallsWithVelocity()) == []
+    assert set(ns.getStaticWalls()) == {"left", "right", "up", "down"}
+
+
+def test_normals_static_dofs_and_names():
+    lower, upper = _box()
+    ns = NoSlipWalls(lower, upper)
+    for wall, normal in (("left", 0), ("right", 0), ("up", 1), ("down", 1)):
+        assert ns.getWalletNormalBySideName(wall) == normal
+        assert list(ns.getStaticDofsByName(wall)) == [1 - normal]
+    held = ns.getStaticDofsByName("up")
+    ns.setWallVelocity("up", [5, 0])
+    assert len(held) == 0                    # the list handed out earlier is updated in place (test_nswalls.py:127-133)
+    assert set(NoSlipWalls(lower, upper, exclude=["left"]).getWallsNames()) == {"right", "up", "down"}
+    assert len(NoSlipWalls(lower, upper)) == 4
+    lo3, up3 = _box(3)
+    ns3 = NoSlipWalls(lo3, up3)
+    assert set(ns3.getWallsNames()) == {"left", "right", "up", "down", "front", "back"}
+    ns3.setWallVelocity("up", [1, 0, 5])
+    vel, dofs = ns3.getWallVelocity("up")
+    assert list(vel) == [1, 5] and list(dofs) == [0, 2]
+    assert ns3.getWalletNormalBySideName("front") == 2
+
+
+# ---- options database ----------------------------------------------------------------------------------------------------
+def test_options_database():
+    Options.init(["prog", "-case", "cavity", "-ksp_rtol", "1e-8", "-ts_dt", "-0.5", "-flag", "-ksp_max_it", "77"])
+    opt = Options()
+    assert opt.getString("case") == "cavity" and opt.getReal("ksp_rtol") == 1e-8 and opt.getInt("ksp_max_it") == 77
+    assert opt.getReal("ts_dt") == -0.5 and opt.hasName("flag") and not opt.hasName("pc_type")
+    assert opt.getString("pc_type", "lu") == "lu"
+    Options.clear()
+    assert not Options().hasName("case")
+
+
+# ---- src/tests/test_mat.py:15-25 -------------------------------------------------------------------------------------------
+def test_create_nnz_helpers():
+    from pynama_b200.matrices.mat_generator import Mat
+    mat = Mat(2)
+    d, off = np.array([9, 15, 25, 9]), np.array([0, 2, 0, 1])
+    for i in range(1, 3):
+        for j in range(1, 3):
+            d_ref, o_ref = mat.createNonZeroIndex(d, off, i, j)
+            d_test, o_test = mat.createNNZWithArray(d, off, i, j)
+            np.testing.assert_array_equal(d_ref, d_test)
+            np.testing.assert_array_equal(o_ref, o_test)
+
+
+# ---- RK tableaus -------------------------------------------------------------------------------------------------------------
+def test_rk_tableaus_consistent():
+    from pynama_b200.solver.ts_solver import RK_TABLEAUS
+    A, b, bh, c = o.rk5bs_tableau()
+    t = RK_TABLEAUS["5bs"]
+    np.testing.assert_array_equal(np.array(t["A"]), A)
+    np.testing.assert_array_equal(t["b"], b)
+    np.testing.assert_array_equal(t["bh"], bh)
+    assert t["fsal"] and t["s"] == 8 and t["order"] == 5
+    for name, tab in RK_TABLEAUS.items():
+        A, b, c = np.array(tab["A"]), np.array(tab["b"]), np.array(tab["c"])
+        assert abs(b.sum() - 1) < 1e-15 and np.allclose(A.sum(1), c, atol=1e-15)
+        p = tab["order"]
+        if p >= 2:
+            assert abs(b @ c - 0.5) < 1e-14
+        if p >= 3:
+            assert abs(b @ c ** 2 - 1 / 3) < 1e-14 and abs(b @ (A @ c) - 1 / 6) < 1e-14
+        if p >= 4:
+            assert abs(b @ c ** 3 - 0.25) < 1e-14
+        if tab["bh"] is not None:
+            assert abs(sum(tab["bh"]) - 1) < 1e-14
+    assert RK_TABLEAUS["5dp"]["fsal"] and RK_TABLEAUS["3bs"]["fsal"] and not RK_TABLEAUS["4"]["fsal"]
+
+
+# ---- dof classes and borders vs the oracle --------------------------------------------------------------------------------------
+@pytest.mark.parametrize("nx,ny,n", [(8, 8, 3), (3, 5, 4), (2, 2, 2)])
+def test_noslip_classes_and_borders_vs_oracle(nx, ny, n):
+    from pynama_b200.domain.dmplex import DMPlexDom
+    from pynama_b200.matrices.mat_ns import noSlipDofClasses
+    dom = DMPlexDom(boxMesh={"nelem": [nx, ny], "lower": [0, 0], "upper": [1, 1]})
+    dom.setFemIndexing(n)
+    m = o.BoxMesh([nx, ny], [0, 0], [1, 1], n)
+    for name in dom.getBordersNames():
+        np.testing.assert_array_equal(dom.borderNodesArray(name), m.border_nodes(name))
+    dom.setBoundaryCondition([], ["left", "right", "up", "down"])
+    cls = noSlipDofClasses(dom, dom.getGlobalIndicesNoSlip(), dom.getGlobalIndicesDirichlet())
+    np.testing.assert_array_equal(cls, o.dof_classes_noslip(m))
+    # a Dirichlet (free-slip-listed) border: every component set
+    dom2 = DMPlexDom(boxMesh={"nelem": [nx, ny], "lower": [0, 0], "upper": [1, 1]})
+    dom2.setFemIndexing(n)
+    dom2.setBoundaryCondition(["left"], ["right", "up", "down"])
+    cls2 = noSlipDofClasses(dom2, dom2.getGlobalIndicesNoSlip(), dom2.getGlobalIndicesDirichlet()).reshape(-1, 2)
+    assert (cls2[m.border_nodes("left")] == 2).all()
+    np.testing.assert_array_equal(np.array(dom.cellNodesArray()), m.cell_nodes())
+
+
+# ---- src/tests/test_domain.py ----------------------------------------------------------------------------------------------------
+def test_domain_pins_of_the_reference():
+    from pynama_b200.domain.dmplex import DMPlexDom
+    dom = DMPlexDom(boxMesh={"nelem": [2, 2], "lower": [0, 0], "upper": [0.6, 0.8]})
+    assert (dom.cellStart, dom.cellEnd) == (0, 4)                                   # test_domain.py:22-24
+    np.testing.assert_allclose(dom.getCellCornersCoords(0), [0, 0, 0.3, 0, 0.3, 0.4, 0, 0.4], atol=1e-15)   # :26-30
+    for ngl in range(2, 9):                                                         # :32-78 border node counts
+        dom.setFemIndexing(ngl)
+        for name, cells in (("up", 2), ("down", 2), ("left", 2), ("right", 2)):
+            assert len(dom.getBorderNodes(name)) == cells * (ngl - 1) + 1
+        assert len(dom.getBordersNodes()) == 8 * (ngl - 1)
+    dom23 = DMPlexDom(boxMesh={"nelem": [2, 3], "lower": [0, 0], "upper": [1, 1]})
+    for ngl in range(2, 14):                                                        # :187-195
+        dom23.setFemIndexing(ngl)
+        assert dom23.getTotalNodes() == 12 + 17 * (ngl - 2) + 6 * (ngl - 2) ** 2
+        seen = set()
+        for c in range(6):
+            seen |= set(dom23.getGlobalNodesFromCell(c))
+        assert seen == set(range(dom23.getTotalNodes()))
+    dom23.setFemIndexing(2)                                                         # :197-201 row-major numbering
+    assert dom23.getGlobalNodesFromCell(0) == [0, 1, 4, 3]
+    assert dom23.getGlobalNodesFromCell(3) == [4, 5, 8, 7]
+    assert dom23.getVelocityIndex([3, 5]) == [6, 7, 10, 11] and dom23.getSrtIndex([1]) == [3, 4, 5]
