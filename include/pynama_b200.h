@@ -79,6 +79,11 @@ int pyn_box_cell_corners(int nx, int ny, double x0, double y0, double x1, double
 /* node coordinates [nnodes][2]: corner-bilinear map evaluated at the nodal GLL points (xi_nodal, ngl values) */
 int pyn_box_node_coords(int nx, int ny, int ngl, double x0, double y0, double x1, double y1,
                         const double* h_xi_nodal, const int32_t* h_perm, double* d_xy, void* stream);
+/* same for a strip of cell rows [fy0, fy0+ny_local) of the global nx x ny_global mesh, in the strip's own (local)
+ * box numbering; coordinates are computed with the global mesh spacing so they are bit-identical to the serial ones */
+int pyn_box_node_coords_strip(int nx, int ny_global, int64_t fy0, int ny_local, int ngl, double x0, double y0,
+                              double x1, double y1, const double* h_xi_nodal, const int32_t* h_perm, double* d_xy,
+                              void* stream);
 
 /* ------------------------------------------------------------------------------------------------------
  * Topology handle: node->element incidence and node adjacency (nodes sharing a cell), built once per mesh.
@@ -226,6 +231,31 @@ int pyn_ksp_solve(pyn_ksp* k, const double* d_b, double* d_x, pyn_ksp_result* re
 int pyn_ksp_destroy(pyn_ksp* k);
 /* device work done by the last solve: SpMV launches and total kernel launches (for the roofline accounting) */
 int pyn_ksp_stats(const pyn_ksp* k, int64_t* spmv_launches, int64_t* kernel_launches);
+
+/* ------------------------------------------------------------------------------------------------------
+ * Multi-GPU: one process per GPU, the mesh cut into strips of cell rows (the reference: DMPlex.distribute(),
+ * src/domain/dmplex.py:29; MatStash / VecScatter / MPI_Allreduce inside PETSc).  NCCL is bound at run time.
+ *   - pyn_comm: NCCL communicator.  Rank 0 makes the 128-byte id, the host side broadcasts it (torch.distributed).
+ *   - pyn_halo: per neighbour, the local node ids to send (owned nodes the neighbour holds as ghosts) and to receive
+ *     into (ghost nodes), both ordered by global node id; one grouped ncclSend/ncclRecv per exchange.
+ *   - pyn_ksp_set_dist: CG then refreshes the ghosts of the search direction before every SpMV and all-reduces its
+ *     three scalars; `d_owned_rows` (1 = row owned by this rank) masks the right-hand side.
+ * ---------------------------------------------------------------------------------------------------- */
+typedef struct pyn_comm pyn_comm;
+typedef struct pyn_halo pyn_halo;
+int pyn_comm_unique_id(char* id128);
+int pyn_comm_create(const char* id128, int rank, int world, pyn_comm** out);
+int pyn_comm_destroy(pyn_comm* c);
+int pyn_comm_info(const pyn_comm* c, int* rank, int* world, int* nccl_version);
+int pyn_comm_allreduce_sum(const pyn_comm* c, double* d_buf, int n, void* stream);
+int pyn_halo_create(const pyn_comm* c, int nnbr, const int32_t* h_nbr_rank, const int64_t* h_send_cnt,
+                    const int64_t* const* d_send_idx, const int64_t* h_recv_cnt, const int64_t* const* d_recv_idx,
+                    pyn_halo** out);
+int pyn_halo_destroy(pyn_halo* h);
+/* d_vec: local vector with ncomp (1..3) dofs per node; ghost entries are overwritten with their owners' values */
+int pyn_halo_exchange(const pyn_halo* h, double* d_vec, int ncomp, void* stream);
+int64_t pyn_halo_bytes(const pyn_halo* h, int ncomp);
+int pyn_ksp_set_dist(pyn_ksp* k, const pyn_comm* comm, const pyn_halo* halo, int ncomp, const uint8_t* d_owned_rows);
 
 #ifdef __cplusplus
 }

@@ -87,6 +87,18 @@ _SIGNATURES = {
     "pyn_ksp_solve": (C.c_int, [c_vp, c_vp, c_vp, P(KspResult), c_vp]),
     "pyn_ksp_destroy": (C.c_int, [c_vp]),
     "pyn_ksp_stats": (C.c_int, [c_vp, P(c_i64), P(c_i64)]),
+    "pyn_box_node_coords_strip": (C.c_int, [C.c_int, C.c_int, c_i64, C.c_int, C.c_int, c_f64, c_f64, c_f64, c_f64, c_vp,
+                                            c_vp, c_vp, c_vp]),
+    "pyn_comm_unique_id": (C.c_int, [c_vp]),
+    "pyn_comm_create": (C.c_int, [c_vp, C.c_int, C.c_int, P(c_vp)]),
+    "pyn_comm_destroy": (C.c_int, [c_vp]),
+    "pyn_comm_info": (C.c_int, [c_vp, P(C.c_int), P(C.c_int), P(C.c_int)]),
+    "pyn_comm_allreduce_sum": (C.c_int, [c_vp, c_vp, C.c_int, c_vp]),
+    "pyn_halo_create": (C.c_int, [c_vp, C.c_int, P(c_i32), P(c_i64), P(c_vp), P(c_i64), P(c_vp), P(c_vp)]),
+    "pyn_halo_destroy": (C.c_int, [c_vp]),
+    "pyn_halo_exchange": (C.c_int, [c_vp, c_vp, C.c_int, c_vp]),
+    "pyn_halo_bytes": (c_i64, [c_vp, C.c_int]),
+    "pyn_ksp_set_dist": (C.c_int, [c_vp, c_vp, c_vp, C.c_int, c_vp]),
 }
 
 EXPORTED_SYMBOLS = tuple(_SIGNATURES)

@@ -9,6 +9,7 @@
 // order), i.e. bitwise reproducible run to run.
 #include <vector>
 
+#include "dist.cuh"
 #include "spmv.cuh"
 
 namespace {
@@ -33,11 +34,12 @@ __global__ void jacobi_inv_kernel(int64_t n, const double* __restrict__ diag, do
 }
 
 // r = b, x = 0, z = M^-1 r, partials of z.z and z.r
-__global__ void cg_init_kernel(int64_t n, const double* __restrict__ b, CgBuffers B) {
+__global__ void cg_init_kernel(int64_t n, const double* __restrict__ b, CgBuffers B,
+                               const uint8_t* __restrict__ owned) {
   __shared__ double sm[BLK / 32];
   double szz = 0.0, szr = 0.0;
   for (int64_t i = blockIdx.x * (int64_t)BLK + threadIdx.x; i < n; i += (int64_t)gridDim.x * BLK) {
-    const double r = b[i];
+    const double r = (owned && !owned[i]) ? 0.0 : b[i];  // rows of ghost nodes belong to another rank
     const double z = B.dinv[i] * r;
     B.r[i] = r;
     B.z[i] = z;
@@ -54,9 +56,21 @@ __global__ void cg_init_kernel(int64_t n, const double* __restrict__ b, CgBuffer
   }
 }
 
-__global__ void cg_scalar_init_kernel(int nparts, CgBuffers B, double rtol, double atol) {
-  const double zz = pyn::reduce_partials(B.part_a, nparts);
-  const double zr = pyn::reduce_partials(B.part_b, nparts);
+// partial sums -> scalars (multi-GPU: the scalars are then all-reduced over the ranks)
+__global__ void cg_reduce_kernel(int nparts, const double* __restrict__ pa, const double* __restrict__ pb,
+                                 double* __restrict__ out) {
+  const double a = pyn::reduce_partials(pa, nparts);
+  const double b = pb ? pyn::reduce_partials(pb, nparts) : 0.0;
+  if (threadIdx.x == 0) {
+    out[0] = a;
+    if (pb) out[1] = b;
+  }
+}
+
+// g (multi-GPU only): global sums [p.w, z.z, z.r] produced by cg_reduce_kernel + all-reduce
+__global__ void cg_scalar_init_kernel(int nparts, CgBuffers B, double rtol, double atol, const double* __restrict__ g) {
+  const double zz = g ? g[1] : pyn::reduce_partials(B.part_a, nparts);
+  const double zr = g ? g[2] : pyn::reduce_partials(B.part_b, nparts);
   if (threadIdx.x == 0) {
     KspState* s = B.st;
     s->dp = sqrt(zz);
@@ -108,13 +122,13 @@ cg_spmv_dot_kernel(pyn::SpmvPlanView P, const int* __restrict__ ind, const doubl
 
 // a = beta / (p.w) ; x += a p ; r -= a w ; z = M^-1 r ; partials of z.z, z.r   (input partials: nparts_in of p.w)
 __global__ void cg_update_kernel(int64_t n, int nparts_in, CgBuffers B, double* __restrict__ out_a,
-                                 double* __restrict__ out_b) {
+                                 double* __restrict__ out_b, const double* __restrict__ g) {
   __shared__ double sm[BLK / 32];
   __shared__ double s_a;
   const KspState* s = B.st;
   if (s->done) return;
   if (threadIdx.x < 32) {
-    const double dpi = pyn::reduce_partials(B.part_a, nparts_in);
+    const double dpi = g ? g[0] : pyn::reduce_partials(B.part_a, nparts_in);
     if (threadIdx.x == 0) s_a = s->beta / dpi;
   }
   __syncthreads();
@@ -139,12 +153,13 @@ __global__ void cg_update_kernel(int64_t n, int nparts_in, CgBuffers B, double* 
 
 // end of iteration: norms, convergence test, new beta  (one warp)
 __global__ void cg_scalar_kernel(int nparts_pw, int nparts, CgBuffers B, const double* __restrict__ pzz,
-                                 const double* __restrict__ pzr, double atol, double dtol, int max_it) {
+                                 const double* __restrict__ pzr, double atol, double dtol, int max_it,
+                                 const double* __restrict__ g) {
   KspState* s = B.st;
   if (s->done) return;
-  const double dpi = pyn::reduce_partials(B.part_a, nparts_pw);
-  const double zz = pyn::reduce_partials(pzz, nparts);
-  const double zr = pyn::reduce_partials(pzr, nparts);
+  const double dpi = g ? g[0] : pyn::reduce_partials(B.part_a, nparts_pw);
+  const double zz = g ? g[1] : pyn::reduce_partials(pzz, nparts);
+  const double zr = g ? g[2] : pyn::reduce_partials(pzr, nparts);
   if (threadIdx.x == 0) {
     s->its += 1;
     s->betaold = s->beta;
@@ -191,15 +206,39 @@ struct pyn_ksp {
   cudaGraphExec_t graph;
   int graph_iters;
   int64_t last_spmv, last_launches;
+  // multi-GPU (pyn_ksp_set_dist): communicator, halo plan of the unknown (ncomp dofs per node), owned-row mask
+  const pyn_comm* comm;
+  const pyn_halo* halo;
+  int halo_comp;
+  const uint8_t* owned;
+  double* gsum;  // [p.w, z.z, z.r]
 };
 
 namespace {
 
-void enqueue_cg_iteration(const pyn_ksp* k, cudaStream_t st) {
+int enqueue_cg_iteration(const pyn_ksp* k, cudaStream_t st) {
+  const bool dist = k->comm && k->comm->world > 1;
+  const double* g = dist ? k->gsum : nullptr;
   cg_pupdate_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, k->B);
+  if (dist) {  // ghost entries of p <- their owners (MPIAIJ MatMult's VecScatter in the reference)
+    int rc = pyn::halo_exchange(k->halo, k->B.p, k->halo_comp, st);
+    if (rc) return rc;
+  }
   cg_spmv_dot_kernel<<<k->sgrid, pyn::SP_BLK, 0, st>>>(pyn::view_of(k->plan), k->ind, k->val, k->B);
-  cg_update_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, k->sgrid, k->B, k->pzz, k->pzr);
-  cg_scalar_kernel<<<1, 32, 0, st>>>(k->sgrid, k->vgrid, k->B, k->pzz, k->pzr, k->opts.atol, k->opts.dtol, k->opts.max_it);
+  if (dist) {
+    cg_reduce_kernel<<<1, 32, 0, st>>>(k->sgrid, k->B.part_a, nullptr, k->gsum);
+    int rc = pyn::comm_allreduce_sum(k->comm, k->gsum, 1, st);
+    if (rc) return rc;
+  }
+  cg_update_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, k->sgrid, k->B, k->pzz, k->pzr, g);
+  if (dist) {
+    cg_reduce_kernel<<<1, 32, 0, st>>>(k->vgrid, k->pzz, k->pzr, k->gsum + 1);
+    int rc = pyn::comm_allreduce_sum(k->comm, k->gsum + 1, 2, st);
+    if (rc) return rc;
+  }
+  cg_scalar_kernel<<<1, 32, 0, st>>>(k->sgrid, k->vgrid, k->B, k->pzz, k->pzr, k->opts.atol, k->opts.dtol,
+                                     k->opts.max_it, g);
+  return PYN_OK;
 }
 
 }  // namespace
@@ -249,9 +288,16 @@ int pyn_ksp_solve(pyn_ksp* k, const double* d_b, double* d_x, pyn_ksp_result* re
   PYN_REQUIRE(k && d_b && d_x, "bad arguments");
   cudaStream_t st = pyn::as_stream(stream);
   int64_t launches = 0;
-  cg_init_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, d_b, k->B);
+  const bool dist = k->comm && k->comm->world > 1;
+  cg_init_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, d_b, k->B, dist ? k->owned : nullptr);
   PYN_CHECK_LAUNCH();
-  cg_scalar_init_kernel<<<1, 32, 0, st>>>(k->vgrid, k->B, k->opts.rtol, k->opts.atol);
+  if (dist) {
+    cg_reduce_kernel<<<1, 32, 0, st>>>(k->vgrid, k->B.part_a, k->B.part_b, k->gsum + 1);
+    PYN_CHECK_LAUNCH();
+    int rc = pyn::comm_allreduce_sum(k->comm, k->gsum + 1, 2, st);
+    if (rc) return rc;
+  }
+  cg_scalar_init_kernel<<<1, 32, 0, st>>>(k->vgrid, k->B, k->opts.rtol, k->opts.atol, dist ? k->gsum : nullptr);
   PYN_CHECK_LAUNCH();
   launches += 2;
   const int chunk = k->opts.check_every;
@@ -262,8 +308,10 @@ int pyn_ksp_solve(pyn_ksp* k, const double* d_b, double* d_x, pyn_ksp_result* re
     PYN_CHECK_CUDA(cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking));
     cudaGraph_t g;
     PYN_CHECK_CUDA(cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal));
-    for (int i = 0; i < chunk; ++i) enqueue_cg_iteration(k, cs);
+    int erc = PYN_OK;
+    for (int i = 0; i < chunk && erc == PYN_OK; ++i) erc = enqueue_cg_iteration(k, cs);
     PYN_CHECK_CUDA(cudaStreamEndCapture(cs, &g));
+    if (erc != PYN_OK) { cudaGraphDestroy(g); cudaStreamDestroy(cs); return erc; }
     PYN_CHECK_CUDA(cudaGraphInstantiate(&k->graph, g, 0));
     PYN_CHECK_CUDA(cudaGraphDestroy(g));
     PYN_CHECK_CUDA(cudaStreamDestroy(cs));
@@ -278,7 +326,7 @@ int pyn_ksp_solve(pyn_ksp* k, const double* d_b, double* d_x, pyn_ksp_result* re
     enq += chunk;
     launches += 4 * (int64_t)chunk;
   }
-  pyn::count_launch((int)(4 * (int64_t)k->h_state->its));  // only the launches that did work are claimed
+  pyn::count_launch((int)((dist ? 6 : 4) * (int64_t)k->h_state->its));  // only the launches that did work are claimed
   copy_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, k->B.x, d_x);
   PYN_CHECK_LAUNCH();
   PYN_CHECK_CUDA(cudaStreamSynchronize(st));
@@ -299,8 +347,18 @@ int pyn_ksp_destroy(pyn_ksp* k) {
   pyn_spmv_plan_destroy(k->plan);
   cudaFree(k->B.r);
   cudaFree(k->B.st);
+  cudaFree(k->gsum);
   cudaFreeHost(k->h_state);
   delete k;
+  return PYN_OK;
+}
+
+int pyn_ksp_set_dist(pyn_ksp* k, const pyn_comm* comm, const pyn_halo* halo, int ncomp, const uint8_t* d_owned_rows) {
+  PYN_REQUIRE(k && comm, "bad arguments");
+  PYN_REQUIRE(comm->world == 1 || (halo && ncomp >= 1 && ncomp <= PYN_HALO_MAX_COMP), "halo plan required for world > 1");
+  k->comm = comm; k->halo = halo; k->halo_comp = ncomp; k->owned = d_owned_rows;
+  if (!k->gsum) PYN_CHECK_CUDA(cudaMalloc(&k->gsum, 4 * sizeof(double)));
+  if (k->graph) { cudaGraphExecDestroy(k->graph); k->graph = nullptr; }  // re-capture with the collectives
   return PYN_OK;
 }
 

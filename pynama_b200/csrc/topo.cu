@@ -52,7 +52,7 @@ struct XiPerm {
 };
 
 __global__ void box_node_coords_kernel(int nx, int ny, int n, double x0, double y0, double hx, double hy,
-                                       const __grid_constant__ XiPerm tp, const int* __restrict__ e2n_unused,
+                                       const __grid_constant__ XiPerm tp, int64_t fy_off,
                                        double* __restrict__ xy) {
   // one thread per (cell, local node); later cells overwrite shared nodes with the same value up to rounding,
   // so to stay deterministic only the LAST cell containing a node (reference: INSERT in cell order) writes it.
@@ -92,7 +92,7 @@ __global__ void box_node_coords_kernel(int nx, int ny, int n, double x0, double 
     const double r = tp.xi[p / n], s = tp.xi[p % n];
     // bilinear map with corner k at (+1,+1),(-1,+1),(-1,-1),(+1,-1) and corners (xa,ya),(xb,ya),(xb,yb),(xa,yb)
     const double xa = x0 + hx * (double)fx, xb = x0 + hx * (double)(fx + 1);
-    const double ya = y0 + hy * (double)fy, yb = y0 + hy * (double)(fy + 1);
+    const double ya = y0 + hy * (double)(fy + fy_off), yb = y0 + hy * (double)(fy + fy_off + 1);
     const double rp = (r + 1.0) * 0.5, rm = (1.0 - r) * 0.5, sp = (s + 1.0) * 0.5, sm_ = (1.0 - s) * 0.5;
     const double N0 = rp * sp, N1 = rm * sp, N2 = rm * sm_, N3 = rp * sm_;
     xy[2 * node] = N0 * xa + N1 * xb + N2 * xb + N3 * xa;
@@ -281,7 +281,20 @@ int pyn_box_node_coords(int nx, int ny, int ngl, double x0, double y0, double x1
   for (int i = 0; i < ngl; ++i) tp.xi[i] = h_xi[i];
   for (int i = 0; i < ngl * ngl; ++i) tp.perm[i] = h_perm[i];
   box_node_coords_kernel<<<pyn::grid_for((int64_t)nx * ny * ngl * ngl, 256), 256, 0, pyn::as_stream(stream)>>>(
-      nx, ny, ngl, x0, y0, (x1 - x0) / nx, (y1 - y0) / ny, tp, nullptr, d_xy);
+      nx, ny, ngl, x0, y0, (x1 - x0) / nx, (y1 - y0) / ny, tp, 0, d_xy);
+  PYN_CHECK_LAUNCH();
+  return PYN_OK;
+}
+
+int pyn_box_node_coords_strip(int nx, int ny_global, int64_t fy0, int ny_local, int ngl, double x0, double y0, double x1,
+                              double y1, const double* h_xi, const int32_t* h_perm, double* d_xy, void* stream) {
+  PYN_REQUIRE(nx > 0 && ny_global > 0 && ny_local > 0 && fy0 >= 0 && fy0 + ny_local <= ny_global && ngl >= 2 &&
+                  ngl <= PYN_MAX_NGL && h_xi && h_perm && d_xy, "bad arguments");
+  XiPerm tp;
+  for (int i = 0; i < ngl; ++i) tp.xi[i] = h_xi[i];
+  for (int i = 0; i < ngl * ngl; ++i) tp.perm[i] = h_perm[i];
+  box_node_coords_kernel<<<pyn::grid_for((int64_t)nx * ny_local * ngl * ngl, 256), 256, 0, pyn::as_stream(stream)>>>(
+      nx, ny_local, ngl, x0, y0, (x1 - x0) / nx, (y1 - y0) / ny_global, tp, fy0, d_xy);
   PYN_CHECK_LAUNCH();
   return PYN_OK;
 }

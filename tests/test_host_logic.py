@@ -161,3 +161,23 @@ def test_domain_pins_of_the_reference():
     assert dom23.getGlobalNodesFromCell(0) == [0, 1, 4, 3]
     assert dom23.getGlobalNodesFromCell(3) == [4, 5, 8, 7]
     assert dom23.getVelocityIndex([3, 5]) == [6, 7, 10, 11] and dom23.getSrtIndex([1]) == [3, 4, 5]
+
+
+# ---- the C ABI ----------------------------------------------------------------------------------------------------------------
+def test_library_exports_every_declared_symbol():
+    """libpynama_b200.so loads without a GPU and exports every function include/pynama_b200.h declares; the ctypes
+    table of pynama_b200/_lib.py covers all of them (no compute call is made here)."""
+    import ctypes
+    import os
+    import re
+    from conftest import ROOT
+    from pynama_b200 import _lib
+    hdr = open(os.path.join(ROOT, "include", "pynama_b200.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    declared = set(re.findall(r"\b(pyn_[a-z0-9_]+)\s*\(", hdr))
+    assert len(declared) >= 60
+    lib = ctypes.CDLL(_lib.LIB_PATH)
+    for name in sorted(declared):
+        assert hasattr(lib, name), f"{name} declared in the header but not exported"
+    assert declared == set(_lib.EXPORTED_SYMBOLS), declared ^ set(_lib.EXPORTED_SYMBOLS)
+    assert _lib.load().pyn_version() >= 100
