@@ -116,12 +116,17 @@ def box_cell_corners(nx, ny, lower, upper, cell0=0, ncells=None):
     return out
 
 
-def box_node_coords(nx, ny, ngl, lower, upper, xi_nodal, perm, nnodes):
+def box_node_coords(nx, ny, ngl, lower, upper, xi_nodal, perm, nnodes, strip=None):
+    """strip = (ny_global, fy0): `ny` cell rows starting at row fy0 of the global mesh, local numbering."""
     out = empty(nnodes * 2).view(nnodes, 2)
     xi = np.ascontiguousarray(xi_nodal, dtype=np.float64)
     pm = np.ascontiguousarray(perm, dtype=np.int32)
-    call("pyn_box_node_coords", nx, ny, ngl, float(lower[0]), float(lower[1]), float(upper[0]), float(upper[1]),
-         _np_ptr(xi), _np_ptr(pm), ptr(out), stream())
+    if strip is None or strip == (ny, 0):
+        call("pyn_box_node_coords", nx, ny, ngl, float(lower[0]), float(lower[1]), float(upper[0]), float(upper[1]),
+             _np_ptr(xi), _np_ptr(pm), ptr(out), stream())
+    else:
+        call("pyn_box_node_coords_strip", nx, int(strip[0]), int(strip[1]), ny, ngl, float(lower[0]), float(lower[1]),
+             float(upper[0]), float(upper[1]), _np_ptr(xi), _np_ptr(pm), ptr(out), stream())
     return out
 
 

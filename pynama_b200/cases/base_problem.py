@@ -37,6 +37,7 @@ class _Comm(object):
 
     def __init__(self):
         self.rank, self.size = 0, 1
+        self.dist = None            # pynama_b200.dist.DistContext once the mesh has been partitioned
         try:
             import torch.distributed as dist
             if dist.is_available() and dist.is_initialized():
@@ -86,7 +87,14 @@ class BaseProblem(object):
         if "box-mesh" in domain:
             self.logger.info("Creating dom with box Mesh")
             self.meshType = "box-mesh"
-            self.dom = DMPlexDom(boxMesh=domain.get('box-mesh'), **self.opts)
+            ngl = self.opts['ngl'] if "ngl" in self.opts else domain['ngl']
+            if self.comm.size > 1:      # one strip of cell rows per GPU (domain/partition.py)
+                from ..domain.partition import StripPartition
+                faces = self.opts['nelem'] if 'nelem' in self.opts else domain['box-mesh']['nelem']
+                part = StripPartition(faces[0], faces[1], ngl, self.comm.rank, self.comm.size)
+                self.dom = DMPlexDom(boxMesh=domain.get('box-mesh'), partition=part, **self.opts)
+            else:
+                self.dom = DMPlexDom(boxMesh=domain.get('box-mesh'), **self.opts)
         elif "gmsh-file" in domain:
             raise Exception("gmsh meshes are outside the B200 hot path (SURVEY.md 8f item 2)")
         self.dim = self.dom.getDimension()
@@ -94,6 +102,10 @@ class BaseProblem(object):
         self.dim_s = 3 if self.dim == 2 else 6
         self.ngl = self.opts['ngl'] if "ngl" in self.opts else domain['ngl']
         self.dom.setFemIndexing(self.ngl)
+        if self.dom.partition is not None:
+            from ..dist import DistContext
+            self.comm.dist = DistContext(self.dom.partition)
+            self.logger.info(self.dom.partition.describe())
         if not self.comm.rank:
             self.logger.info("DMPlex dom created")
 
@@ -205,8 +217,16 @@ class BaseProblem(object):
         op = self.operator.spmv
         op["SrT"].csr.mult(self.vel.data, self._Aux1.data, mode=SPMV_SRT_VTENSV, p0=2.0 * self.mu, p1=self.rho,
                            aux=self.vel.data)
+        self._halo(self._Aux1, self.dim_s)
         op["DivSrT"].csr.mult(self._Aux1.data, self._rhs.data, mode=SPMV_SCALE, p0=1 / self.rho)
+        self._halo(self._rhs, self.dim)
         op["Curl"].csr.mult(self._rhs.data, f.data)
+
+    def _halo(self, vec, ncomp):
+        """Multi-GPU: refresh the ghost entries of a product result before it is multiplied again (the products only
+        fill owned rows).  No-op on one GPU."""
+        if self.comm.dist is not None:
+            self.comm.dist.exchange(vec, ncomp)
 
     def computeVtensV(self, vec=None):
         """Node-wise convective tensor [vx^2, vx vy, vy^2] into `_VtensV` (base_problem.py:234-252).  The time loop
@@ -288,6 +308,7 @@ class NoSlipFreeSlip(BaseProblem):
         rhs = Rw w' + Krhs v_bc -> vel.  Six SpMV launches (accumulating in place, same order of additions) and two
         device Krylov solves."""
         self.applyBoundaryConditions()
+        self._halo(vort, self.dim_w)
         m, b = self.mat, self._kleRhs.data
         m.Rw.csr.mult(vort.data, b)
         m.Rwfs.csr.mult(vort.data, b, mode=SPMV_ADD)
@@ -295,6 +316,7 @@ class NoSlipFreeSlip(BaseProblem):
         self.solverFS(self._kleRhs, self.velFS)
         self.applyBoundaryConditionsFS()
         self.operator.spmv["Curl"].csr.mult(self.velFS.data, self._vortFS.data)
+        self._halo(self._vortFS, self.dim_w)
         m.Rw.csr.mult(self._vortFS.data, b)
         m.Krhs.csr.mult(self.vel.data, b, mode=SPMV_ADD)
         self.solver(self._kleRhs, self.vel)
@@ -336,6 +358,7 @@ class FreeSlip(BaseProblem):
     def _solveVelocity(self, vort):
         """solver(Rw w + Krhs v_bc, vel)  (base_problem.py:481)"""
         b = self._kleRhs.data
+        self._halo(vort, self.dim_w)
         self.mat.Rw.csr.mult(vort.data, b)
         self.mat.Krhs.csr.mult(self.vel.data, b, mode=SPMV_ADD)
         self.solver(self._kleRhs, self.vel)

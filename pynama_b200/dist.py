@@ -1,0 +1,107 @@
+"""Multi-GPU context of one rank: NCCL communicator + halo-exchange plan + ownership masks on the device.
+
+`torch.distributed` (one process per GPU, launched by torchrun) is used for the rendezvous only -- it carries the
+128-byte NCCL id from rank 0 to the others; every data-path collective (halo exchange of interface-node dofs,
+all-reduce of the Krylov / time-step scalars) goes through the library's own communicator (csrc/dist.cu), so that CG
+can issue them from inside its captured iteration graph.  In the reference these are PETSc's VecScatter and
+MPI_Allreduce."""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib
+from . import backend as be
+from ._lib import call
+from .domain.partition import StripPartition
+
+
+def world_info():
+    """(rank, world) of the torch.distributed job, (0, 1) when there is none."""
+    import torch.distributed as dist
+    if dist.is_available() and dist.is_initialized():
+        return dist.get_rank(), dist.get_world_size()
+    return 0, 1
+
+
+class DistContext(object):
+    def __init__(self, partition: StripPartition):
+        import torch.distributed as dist
+        self.part = partition
+        self.rank, self.world = partition.rank, partition.world
+        ident = C.create_string_buffer(128)
+        if self.world > 1:
+            if self.rank == 0:
+                call("pyn_comm_unique_id", ident)
+            box = [bytes(ident.raw)]
+            dist.broadcast_object_list(box, src=0)
+            ident = C.create_string_buffer(box[0], 128)
+        self._comm = C.c_void_p()
+        call("pyn_comm_create", ident, self.rank, self.world, C.byref(self._comm))
+        own = partition.owned_mask()
+        self.n_owned = int(own.sum())
+        self.owned = be.to_device(own.astype(np.uint8))
+        self._owned_rows = {1: self.owned}
+        # halo plan
+        lists = partition.halo_lists()
+        self._idx = [(be.to_device(s), be.to_device(r)) for _, s, r in lists]      # kept alive: the plan borrows them
+        n = len(lists)
+        nbr = (C.c_int32 * max(n, 1))(*[q for q, _, _ in lists])
+        scnt = (C.c_int64 * max(n, 1))(*[len(s) for _, s, _ in lists])
+        rcnt = (C.c_int64 * max(n, 1))(*[len(r) for _, _, r in lists])
+        sidx = (C.c_void_p * max(n, 1))(*[t[0].data_ptr() for t in self._idx])
+        ridx = (C.c_void_p * max(n, 1))(*[t[1].data_ptr() for t in self._idx])
+        self._halo = C.c_void_p()
+        call("pyn_halo_create", self._comm, n, nbr, scnt, sidx, rcnt, ridx, C.byref(self._halo))
+        self._scal = be.empty(4)
+
+    def owned_rows(self, ncomp):
+        """uint8 per dof (node*ncomp + c): 1 when the node is owned."""
+        if ncomp not in self._owned_rows:
+            self._owned_rows[ncomp] = self.owned.repeat_interleave(ncomp).contiguous()
+        return self._owned_rows[ncomp]
+
+    def exchange(self, vec, ncomp):
+        """Refresh the ghost entries of a local vector (tensor or Vec) with their owners' values."""
+        t = vec.data if not isinstance(vec, torch.Tensor) else vec
+        if self.world > 1:
+            call("pyn_halo_exchange", self._halo, be.ptr(t), int(ncomp), be.stream())
+        return vec
+
+    def halo_bytes(self, ncomp):
+        return int(_lib.load().pyn_halo_bytes(self._halo, int(ncomp)))
+
+    def allreduce_sum(self, values):
+        """Sum a few host scalars over the ranks (device all-reduce through the library communicator)."""
+        vals = [float(v) for v in values]
+        if self.world == 1:
+            return vals
+        self._scal[:len(vals)] = torch.tensor(vals, dtype=torch.float64)
+        call("pyn_comm_allreduce_sum", self._comm, be.ptr(self._scal), len(vals), be.stream())
+        return self._scal[:len(vals)].cpu().tolist()
+
+    def attach(self, ksp, ncomp=2):
+        """Make a backend.Ksp distributed (halo exchange of the search direction + all-reduced scalars)."""
+        call("pyn_ksp_set_dist", ksp._h, self._comm, self._halo, int(ncomp), be.ptr(self.owned_rows(ncomp)))
+        ksp._dist = self         # keep the context alive as long as the solver
+
+    def gather_owned(self, vec, ncomp):
+        """(global dof ids, values) of the owned entries of a local vector -- for comparisons in the serial numbering."""
+        t = vec.data if not isinstance(vec, torch.Tensor) else vec
+        own = self.part.owned_mask()
+        l2g = self.part.local_to_global()[own]
+        vals = t.view(-1, ncomp)[be.to_device(np.flatnonzero(own))].cpu().numpy()
+        dofs = (l2g[:, None] * ncomp + np.arange(ncomp)).reshape(-1)
+        return dofs, vals.reshape(-1)
+
+    def __del__(self):
+        try:
+            lib = _lib.load()
+            if getattr(self, "_halo", None):
+                lib.pyn_halo_destroy(self._halo)
+                self._halo = None
+            if getattr(self, "_comm", None):
+                lib.pyn_comm_destroy(self._comm)
+                self._comm = None
+        except Exception:
+            pass

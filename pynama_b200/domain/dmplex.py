@@ -41,6 +41,13 @@ class DMPlexDom(object):
         self.lower = [float(lower[0]), float(lower[1])]
         self.upper = [float(upper[0]), float(upper[1])]
         self.comm = kwargs.get('comm', None)
+        # multi-GPU: this object describes the rank's strip (its cell rows + one ghost row) in local numbering;
+        # geometry and the physical borders stay those of the global mesh (domain/partition.py)
+        self.partition = kwargs.get('partition', None)
+        self.ny_global, self.fy0 = self.ny, 0
+        if self.partition is not None:
+            assert (self.partition.nx, self.partition.ny) == (self.nx, self.ny)
+            self.ny, self.fy0 = self.partition.ny_local, self.partition.fy0
         self.logger = logging.getLogger("[0] Class")
         self.dim_w, self.dim_s = 1, 3
         self.namingConvention = ["down", "right", "up", "left"]
@@ -171,8 +178,8 @@ class DMPlexDom(object):
         if cell + self.cellStart >= self.cellEnd:
             raise Exception('elem parameter must be in local numbering!')
         hx = (self.upper[0] - self.lower[0]) / self.nx
-        hy = (self.upper[1] - self.lower[1]) / self.ny
-        fx, fy = cell % self.nx, cell // self.nx
+        hy = (self.upper[1] - self.lower[1]) / self.ny_global
+        fx, fy = cell % self.nx, cell // self.nx + self.fy0
         x0, x1 = self.lower[0] + hx * fx, self.lower[0] + hx * (fx + 1)
         y0, y1 = self.lower[1] + hy * fy, self.lower[1] + hy * (fy + 1)
         return np.array([x0, y0, x1, y0, x1, y1, x0, y1], dtype=float)
@@ -181,7 +188,7 @@ class DMPlexDom(object):
         """Coordinates of every GLL node (dmplex.py:66-95) -- one CUDA kernel instead of the cells x nodes loop."""
         from .. import backend as be
         xy = be.box_node_coords(self.nx, self.ny, self.ngl, self.lower, self.upper, spElem.nodes1D,
-                                spElem.localOrder, self.nnodes)
+                                spElem.localOrder, self.nnodes, strip=(self.ny_global, self.fy0))
         self._dev["xy"] = xy
         self.fullCoordVec = Vec(data=xy.view(-1), name='NodeCoordinates')
         self.nodes = list(range(self.nnodes))
@@ -203,7 +210,14 @@ class DMPlexDom(object):
 
     def deviceCellCorners(self, cell0=0, ncells=None):
         from .. import backend as be
-        return be.box_cell_corners(self.nx, self.ny, self.lower, self.upper, cell0, ncells)
+        ncells = self.ncell - cell0 if ncells is None else ncells
+        return be.box_cell_corners(self.nx, self.ny_global, self.lower, self.upper, cell0 + self.fy0 * self.nx, ncells)
+
+    def ownedNodeMask(self):
+        """bool per local node: owned by this rank (all True without a partition)."""
+        if self.partition is None:
+            return np.ones(self.nnodes, dtype=bool)
+        return self.partition.owned_mask()
 
     def deviceNodeCoords(self):
         return self._dev["xy"]
@@ -225,6 +239,9 @@ class DMPlexDom(object):
         """nodes on the closure of a border's faces; "Face Sets" 1 down, 2 right, 3 up, 4 left (dmplex.py:160-171)."""
         nx, ny, m = self.nx, self.ny, self.ngl - 2
         k = np.arange(m)
+        if self.partition is not None and ((name == "down" and self.fy0 > 0) or
+                                           (name == "up" and self.partition.ghost_above)):
+            return np.zeros(0, dtype=np.int64)          # that physical border lies in another rank's strip
         if name in ("down", "up"):
             vy = 0 if name == "down" else ny
             verts = self.off_vert + vy * (nx + 1) + np.arange(nx + 1)

@@ -25,6 +25,17 @@ from ..petsc_like import Vec
 
 # dof classes used by the assembly descriptors (include/pynama_b200.h: pyn_asm_desc)
 FREE, TANGENT, SET = 0, 1, 2
+NOT_OWNED = 3      # multi-GPU: row of a ghost node -- belongs to another rank, no entry is stored
+
+
+def rowClasses(dom, colClasses, ncomp):
+    """Row classes of a (possibly partitioned) mesh: the column classes with the rows of ghost nodes marked
+    NOT_OWNED.  `colClasses` is a host int8 array (or None = all FREE); returns a host array or None."""
+    if dom.partition is None:
+        return colClasses
+    own = np.repeat(dom.ownedNodeMask(), ncomp)
+    base = np.zeros(own.size, dtype=np.int8) if colClasses is None else colClasses
+    return np.where(own, base, NOT_OWNED).astype(np.int8)
 
 
 def _rank(comm):
@@ -115,17 +126,19 @@ class Mat(object):
         N = dom.getTotalNodes()
         cls_np = np.zeros(N, dtype=np.int8)
         cls_np[np.array(sorted(self.globalNodesDIR), dtype=np.int64)] = SET
-        cls = be.to_device(np.repeat(cls_np, self.dim))
+        cls_host = np.repeat(cls_np, self.dim)
+        cls = be.to_device(cls_host)
+        rcls = cls if dom.partition is None else be.to_device(rowClasses(dom, cls_host, self.dim))
         corners = dom.deviceCellCorners(0, None if perCell else 1)
         Ke, Rwe, _ = elemType.getElemKLEMatricesDevice(corners, want_rd=False)
-        m22, m21 = be.BcMap(topo, cls, 2, cls, 2), be.BcMap(topo, cls, 2)
+        m22, m21 = be.BcMap(topo, rcls, 2, cls, 2), be.BcMap(topo, rcls, 2)
         one = (0.0, 0.0, 1.0, 0.0)
-        self._install("K", be.assemble(topo, 2, 2, Ke, cls, cls, [(FREE, FREE)], diag_classes=1 << SET, diag_add=one,
+        self._install("K", be.assemble(topo, 2, 2, Ke, rcls, cls, [(FREE, FREE)], diag_classes=1 << SET, diag_add=one,
                                        bcmap=m22))
-        self._install("Krhs", be.assemble(topo, 2, 2, Ke, cls, cls, [(FREE, SET)], diag_classes=1 << SET,
+        self._install("Krhs", be.assemble(topo, 2, 2, Ke, rcls, cls, [(FREE, SET)], diag_classes=1 << SET,
                                           diag_add=one, sign=-1.0, bcmap=m22))
-        self._install("Rw", be.assemble(topo, 2, 1, Rwe, cls, None, [(FREE, FREE)], bcmap=m21))
-        self.dofClasses = cls
+        self._install("Rw", be.assemble(topo, 2, 1, Rwe, rcls, None, [(FREE, FREE)], bcmap=m21))
+        self.dofClasses, self.rowClasses = cls, rcls
         self._unit_diagonals_folded = True
 
 
@@ -192,13 +205,15 @@ class Operators(Mat):
         Wg = be.assemble_weights(topo, W)
         self.weights = Wg
         rW = Wg.reciprocal()
-        nomap = be.BcMap(topo)
         if compressed is None:
             compressed = N > 2_000_000
         self.spmv = {}
         for name, E, rd, cd in (("SrT", S, self.dim_s, self.dim), ("DivSrT", D, self.dim, self.dim_s),
                                 ("Curl", C, self.dim_w, self.dim)):
-            full = be.assemble(topo, rd, cd, E, rowscale=rW, bcmap=nomap, name=name)
+            rc = rowClasses(dom, None, rd)              # multi-GPU: no rows for ghost nodes
+            rc = None if rc is None else be.to_device(rc)
+            bmap = be.BcMap(topo, rc, rd)
+            full = be.assemble(topo, rd, cd, E, rclass=rc, pairs=[(FREE, FREE)], rowscale=rW, bcmap=bmap, name=name)
             small = full.compressed(name)
             self.spmv[name] = DeviceMat.fromCSR(small, name)
             m = getattr(self, name)

@@ -16,7 +16,7 @@ post-assembly loops; the assembly kernel evaluates it for the whole mesh in one 
 import numpy as np
 
 from .. import backend as be
-from .mat_generator import FREE, SET, TANGENT, Mat
+from .mat_generator import FREE, SET, TANGENT, Mat, rowClasses
 
 # name: (cdof, element matrix, kept (row class, column class) pairs, classes whose diagonal entry is stored,
 #        value added on that diagonal per class, sign)
@@ -86,16 +86,21 @@ class MatNS(Mat):
         pattern rewrites values only."""
         topo = dom.topology()
         if classes is None:
-            classes = be.to_device(noSlipDofClasses(dom, self.globalIndicesNS, self.globalIndicesDIR))
+            host = noSlipDofClasses(dom, self.globalIndicesNS, self.globalIndicesDIR)
+            classes = be.to_device(host)
+            self.rowClasses = classes if dom.partition is None else be.to_device(rowClasses(dom, host, 2))
+        elif getattr(self, "dofClasses", None) is not classes:
+            self.rowClasses = classes if dom.partition is None else \
+                be.to_device(rowClasses(dom, classes.cpu().numpy(), 2))
         if getattr(self, "dofClasses", None) is not classes:
             self.dofClasses = classes
-            self._maps = (be.BcMap(topo, classes, 2, classes, 2), be.BcMap(topo, classes, 2))
+            self._maps = (be.BcMap(topo, self.rowClasses, 2, classes, 2), be.BcMap(topo, self.rowClasses, 2))
         Ke, Rwe, Rde = elemType.getElemKLEMatricesDevice(dom.deviceCellCorners(0, 1), want_rd=True)
         E = {"K": Ke, "Rw": Rwe, "Rd": Rde}
         for name in (names or NS_DESCRIPTORS):
             cd, which, pairs, dcls, dadd, sign = NS_DESCRIPTORS[name]
             m = getattr(self, name)
-            csr = be.assemble(topo, 2, cd, E[which], classes, classes if cd == 2 else None, pairs, diag_classes=dcls,
+            csr = be.assemble(topo, 2, cd, E[which], self.rowClasses, classes if cd == 2 else None, pairs, diag_classes=dcls,
                               diag_add=dadd, sign=sign, pattern=m.csr, name=name,
                               bcmap=self._maps[0] if cd == 2 else self._maps[1])
             m.csr, m.shape = csr, csr.shape

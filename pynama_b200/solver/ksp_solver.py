@@ -99,6 +99,9 @@ class KspSolver(object):
         csr = self.mat.csr if hasattr(self.mat, "csr") else self.mat
         self._ksp = be.Ksp(csr, ksp_type, pc, rtol=rtol, atol=self.atol, dtol=self.divtol, max_it=max_it,
                            restart=self.restart, check_every=self.check_every)
+        dist = getattr(self.comm, "dist", None)
+        if dist is not None:       # multi-GPU: halo exchange of the search direction + all-reduced scalars
+            dist.attach(self._ksp, ncomp=csr.shape[0] // dist.part.nnodes)
 
     def createSolver(self, mat, comm=None):
         self.logger = logging.getLogger("KSP Solver")

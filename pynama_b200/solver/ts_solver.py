@@ -242,6 +242,14 @@ class TsSolver(object):
                 be.vec_maxpy(Y.data, X.data, [cf for cf, _ in coef], [v.data for _, v in coef])       # y5
                 be.vec_maxpy(w["y4"].data, Y.data, [-1.0], [w["err"].data])                           # y4
                 enorm = be.vec_wrms(w["err"].data, Y.data, w["y4"].data, self.atol, self.rtol)
+                dist = getattr(self.comm, "dist", None)
+                if dist is not None and dist.world > 1:
+                    # the RHS is zero on ghost entries, so they add nothing: sum the squares over the ranks and
+                    # normalise by the global size (TSErrorWeightedNorm does an MPI_Allreduce here)
+                    n_loc = X.getSize()
+                    n_glob = dist.part.nnodes_global * (n_loc // dist.part.nnodes)
+                    (ssq,) = dist.allreduce_sum([enorm * enorm * n_loc])
+                    enorm = (ssq / n_glob) ** 0.5
                 accept = enorm <= 1.0
                 # TSAdaptChoose_Basic: "the last attempt also failed, shorten more aggressively"
                 safety = self.safety * (self.reject_safety if (after_reject and not accept) else 1.0)
