@@ -169,78 +169,53 @@ def run_reference(a):
 # ------------------------------------------------------------------------------------------------------------------
 # native arm
 # ------------------------------------------------------------------------------------------------------------------
-# (name, rdof, cdof, element matrix, class pairs kept, diag classes, diag add, sign): the cavity matrices that
-# NoSlipFreeSlip.solveKLE uses (base_problem.py:321-327,388-451); classes 0 free, 1 tangential-on-wall, 2 set.
-ONE12 = (0.0, 1.0, 1.0, 0.0)
-CAVITY_MATS = [
-    ("K", 2, 2, "K", [(0, 0)], 0b110, ONE12, 1.0),
-    ("Krhs", 2, 2, "K", [(0, 1), (0, 2)], 0b110, ONE12, -1.0),
-    ("Kfs", 2, 2, "K", [(1, 0), (0, 1), (1, 1)], 0b010, (0.0, -1.0, 0.0, 0.0), 1.0),
-    ("Krhsfs", 2, 2, "K", [(1, 2), (0, 2)], 0b100, (0.0, 0.0, 1.0, 0.0), -1.0),
-    ("Rw", 2, 1, "Rw", [(0, 0)], 0, (0.0,) * 4, 1.0),
-    ("Rwfs", 2, 1, "Rw", [(1, 0)], 0, (0.0,) * 4, 1.0),
-    ("Rd", 2, 1, "Rd", [(0, 0)], 0, (0.0,) * 4, 1.0),
-    ("Rdfs", 2, 1, "Rd", [(1, 0)], 0, (0.0,) * 4, 1.0),
-]
-
-
-def cavity_classes(dom, be, torch):
-    """int8 class per velocity dof on device: wall-normal component (both at corners) = 2, tangential = 1."""
-    N = dom.getTotalNodes()
-    is_set = torch.zeros((N, 2), dtype=torch.bool, device=be.device())
-    is_tan = torch.zeros((N, 2), dtype=torch.bool, device=be.device())
-    for name, nrm in (("down", 1), ("up", 1), ("left", 0), ("right", 0)):
-        nd = be.to_device(dom.borderNodesArray(name))
-        is_set[nd, nrm] = True
-        is_tan[nd, 1 - nrm] = True
-    is_tan &= ~is_set
-    cls = torch.zeros((N, 2), dtype=torch.int8, device=be.device())
-    cls[is_tan] = 1
-    cls[is_set] = 2
-    return cls.view(-1).contiguous()
+def cavity_config(nx, ngl):
+    """cases/cavity.yaml with the mesh of BASELINE configs[3] and Re = 100 (rho 1, mu 0.01, lid `up: [1, 0]`)."""
+    return {"name": "Cavity", "material-properties": {"rho": 1.0, "mu": 0.01},
+            "domain": {"ngl": ngl, "box-mesh": {"nelem": [nx, nx], "lower": [0, 0], "upper": [1, 1]}},
+            "time-solver": {"max-steps": 1, "start-time": 0, "end-time": 1},
+            "boundary-conditions": {"no-slip": {"up": [1, 0]}}}
 
 
 class CavityAssembly:
-    """Device state of the cavity assembly on one rank (all cells for N=1, a strip of cell rows otherwise)."""
+    """The cavity through the drop-in classes (pynama_b200.cases.cavity.Cavity): on N ranks every rank holds its strip
+    of cell rows (domain/partition.py) and assembles the rows of the nodes it owns.  One step = element integration +
+    values of the eight MatNS matrices on the prebuilt pattern (NoSlipFreeSlip.buildKLEMats)."""
+    NAMES = ("K", "Krhs", "Kfs", "Krhsfs", "Rw", "Rwfs", "Rd", "Rdfs")
 
-    def __init__(self, nx, ny, ngl, lower, upper):
-        import torch
+    def __init__(self, nx, ngl):
         from pynama_b200 import backend as be
-        from pynama_b200.domain.dmplex import DMPlexDom
-        from pynama_b200.elements.spectral import Spectral
-        self.be, self.torch = be, torch
-        self.dom = DMPlexDom(boxMesh={"nelem": [nx, ny], "lower": lower, "upper": upper})
-        self.dom.setFemIndexing(ngl)
-        self.elem = Spectral(ngl, 2)
-        self.topo = self.dom.topology()
-        self.cls = cavity_classes(self.dom, be, torch)
-        self.cc0 = self.dom.deviceCellCorners(0, 1)
-        self.maps = {}
-        self.mats = {}
-        self.nrows = 2 * self.dom.getTotalNodes()
+        from pynama_b200.cases.cavity import Cavity
+        from pynama_b200.common.options import Options
+        Options.clear()
+        for k, v in (("ksp_type", "cg"), ("pc_type", "jacobi")):
+            Options.setValue(k, v)
+        self.be = be
+        self.fem = Cavity(cavity_config(nx, ngl), case="cavity")
+        fem = self.fem
+        fem.setUpGeneral()
+        fem.setUpBoundaryConditions()
+        fem.setUpEmptyMats()
+        fem.buildKLEMats()                      # pattern build (count + fill with indices): not timed
+        self.dom, self.mat = fem.dom, fem.mat
+        own = fem.dom.ownedNodeMask()
+        self.dof_owned = 2 * int(own.sum())
+        self.nrows = 2 * fem.dom.getTotalNodes()
 
-    def integrate(self, cc0=None):
-        Ke, Rwe, Rde = self.elem.getElemKLEMatricesDevice(self.cc0 if cc0 is None else cc0, want_rd=True)
-        return {"K": Ke, "Rw": Rwe, "Rd": Rde}
+    @property
+    def mats(self):
+        return {n: getattr(self.mat, n).csr for n in self.NAMES}
 
-    def assemble(self, E, cls=None, events=None):
-        be = self.be
-        cls = self.cls if cls is None else cls
-        if id(cls) not in self.maps:   # boundary maps of this class array (rebuilt when the classes are re-uploaded)
-            self.maps = {id(cls): (be.BcMap(self.topo, cls, 2, cls, 2), be.BcMap(self.topo, cls, 2))}
-        m22, m21 = self.maps[id(cls)]
-        for name, rd, cd, which, pairs, dcls, dadd, sign in CAVITY_MATS:
-            if events is not None and name == "K":
-                events[0].record()
-            self.mats[name] = be.assemble(self.topo, rd, cd, E[which], cls, cls if cd == 2 else None, pairs,
-                                          diag_classes=dcls, diag_add=dadd, sign=sign, pattern=self.mats.get(name),
-                                          name=name, bcmap=m22 if cd == 2 else m21)
-            if events is not None and name == "K":
-                events[1].record()
+    def step(self, events=None, classes=None, row_classes=None, corners=None):
+        m, fem = self.mat, self.fem
+        if events is not None:
+            events[0].record()
+        m.assembleFromMesh(fem.dom, fem.elemType, names=("K",), classes=classes if classes is not None else m.dofClasses,
+                           rowClassesDev=row_classes, corners=corners)
+        if events is not None:
+            events[1].record()
+        m.assembleFromMesh(fem.dom, fem.elemType, names=self.NAMES[1:], classes=m.dofClasses, corners=corners)
         return self.mats
-
-    def step(self, events=None):
-        return self.assemble(self.integrate(), events=events)
 
 
 def run_native(a):
@@ -263,13 +238,13 @@ def run_native(a):
         torch.cuda.synchronize()
 
     nx, n = a.nx, a.ngl
-    # strong scaling over strips of cell rows: rank r assembles the rows of its strip (own problem, no exchange)
-    ny_loc = nx // world + (1 if rank < nx % world else 0)
-    prob = CavityAssembly(nx, ny_loc, n, [0.0, 0.0], [1.0, ny_loc / nx])
-    prob.step()                                   # pattern build (count + fill with indices), not timed
+    # strong scaling: the fixed nx x nx mesh is cut into `world` strips of cell rows, one per GPU; a rank assembles the
+    # rows of the nodes it owns (complete thanks to one ghost row of cells: no matrix entry crosses NVLink)
+    prob = CavityAssembly(nx, n)
+    prob.step()
     barrier()
     nnz = {k: v.nnz for k, v in prob.mats.items()}
-    dof_local = prob.nrows
+    dof_local = prob.dof_owned
     for _ in range(a.warmup):
         prob.step()
     barrier()
@@ -315,13 +290,19 @@ def run_native(a):
         "data": "synthetic",
         "config": {"workload": f"cavity {nx}x{nx} elements ngl {n} (BASELINE configs[3]): integrate + assemble "
                                f"K,Krhs,Kfs,Krhsfs,Rw,Rwfs,Rd,Rdfs values on the prebuilt CSR pattern",
-                   "partition": f"{world} strip(s) of cell rows, one per GPU, no data-path collective",
+                   "partition": f"{world} strip(s) of cell rows of the one {nx}x{nx} mesh, one per GPU; assembly needs no "
+                                f"collective, CG exchanges interface dofs + 3 scalars per iteration over NCCL",
                    "dof_rows": int(dof_total), "nnz_rank0": nnz,
                    "l2": "outputs (>= 8*nnz(K) bytes per step) exceed the 126 MB L2 for nx >= 128; no flush needed"},
         "roofline": roof, "gpu_launches": int(launches),
     }
     # ---- KSP phase: CG + Jacobi on K, fixed iteration budget ---------------------------------------------------
     out["ksp"] = ksp_phase(a, prob, be, torch, peak, barrier)
+    if world > 1:
+        t = torch.tensor([out["ksp"]["ms_per_solve"]], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        out["ksp"]["ms_per_solve"] = float(t[0])
+        out["ksp"]["ms_per_iteration"] = float(t[0]) / max(out["ksp"]["its"], 1)
     barrier()
     if rank == 0:
         out["clocks"] = sampler.stop()
@@ -344,7 +325,9 @@ def run_native(a):
     if rank == 0:
         print(json.dumps(out), flush=True)
     if world > 1:
-        dist.destroy_process_group()
+        barrier()
+        sys.stdout.flush()
+        os._exit(0)      # skip destructors: NCCL communicators captured in CUDA graphs are not torn down rank by rank
 
 
 def load_traffic(kernel_substr):
@@ -361,19 +344,27 @@ def load_traffic(kernel_substr):
 
 def ksp_phase(a, prob, be, torch, peak, barrier):
     """CG + Jacobi (KSPCG semantics) on the assembled K with a fixed iteration budget (-ksp_max_it), rhs =
-    Rw*vort + Krhs*vel_bc for a lid velocity 1 and a synthetic vorticity field; CUDA events around the solve."""
+    Rw*vort + Krhs*vel_bc for the lid velocity and a synthetic vorticity field; CUDA events around the solve.  On N
+    ranks the solve is the distributed one (halo exchange of the search direction + 3 all-reduced scalars per
+    iteration); times are rank-local here and maxed over ranks by the caller."""
     K, Rw, Krhs = prob.mats["K"], prob.mats["Rw"], prob.mats["Krhs"]
     N = prob.dom.getTotalNodes()
+    dc = prob.fem.comm.dist
     g = torch.Generator(device="cuda").manual_seed(1234)
     vort = torch.randn(N, dtype=torch.float64, device="cuda", generator=g)
+    if dc is not None:
+        dc.exchange(vort, 1)
     vel = be.zeros(2 * N)
-    lid = be.to_device(prob.dom.borderNodesArray("up")) * 2
-    be.vec_scatter_const(vel, lid, 1.0)
+    lid = prob.dom.borderNodesArray("up")
+    if len(lid):
+        be.vec_scatter_const(vel, be.to_device(lid) * 2, 1.0)
     rhs = be.empty(2 * N)
     Rw.mult(vort, rhs)
     Krhs.mult(vel, rhs, mode=1)
     its = a.ksp_its
     ksp = be.Ksp(K, "cg", "jacobi", rtol=1e-300, atol=1e-300, max_it=its, check_every=its)
+    if dc is not None:
+        dc.attach(ksp, 2)
     x = be.empty(2 * N)
     ev = lambda: torch.cuda.Event(enable_timing=True)
     ksp.solve(rhs, x)                       # warm-up: graph capture + one full budget
@@ -381,6 +372,7 @@ def ksp_phase(a, prob, be, torch, peak, barrier):
     barrier()
     reps, ms = 3, []
     for _ in range(reps):
+        barrier()
         s, e = ev(), ev()
         s.record()
         r = ksp.solve(rhs, x)
@@ -402,15 +394,19 @@ def ksp_phase(a, prob, be, torch, peak, barrier):
     ms_spmv = s.elapsed_time(e) / nrep
     spmv_bytes = K.bytes_spmv()
     it_bytes = spmv_bytes + 8 * K.shape[0] * 12      # + ~12 vector passes per PCG iteration
-    return {"type": "cg", "pc": "jacobi", "its": int(r.its), "reason": int(r.reason), "ms_per_solve": ms_solve,
-            "ms_per_iteration": ms_solve / max(r.its, 1), "rows": K.shape[0], "nnz": K.nnz,
-            "iteration_gbs": it_bytes / (ms_solve / max(r.its, 1) * 1e-3) / 1e9,
-            "iteration_frac_of_peak": it_bytes / (ms_solve / max(r.its, 1) * 1e-3) / 1e9 / peak,
-            "spmv": {"ms": ms_spmv, "bytes": spmv_bytes, "achieved": spmv_bytes / (ms_spmv * 1e-3) / 1e9,
-                     "peak": peak, "unit": "GB/s", "frac": spmv_bytes / (ms_spmv * 1e-3) / 1e9 / peak,
-                     "traffic": load_traffic("spmv_kernel")},
-            "note": f"fixed budget of {its} iterations (-ksp_max_it {its}); a converged Jacobi-CG solve at this size "
-                    f"needs O(10^4) iterations (SURVEY 7.2)"}
+    out = {"type": "cg", "pc": "jacobi", "its": int(r.its), "reason": int(r.reason), "ms_per_solve": ms_solve,
+           "ms_per_iteration": ms_solve / max(r.its, 1), "rows": K.shape[0], "nnz": K.nnz,
+           "iteration_gbs": it_bytes / (ms_solve / max(r.its, 1) * 1e-3) / 1e9,
+           "iteration_frac_of_peak": it_bytes / (ms_solve / max(r.its, 1) * 1e-3) / 1e9 / peak,
+           "spmv": {"ms": ms_spmv, "bytes": spmv_bytes, "achieved": spmv_bytes / (ms_spmv * 1e-3) / 1e9,
+                    "peak": peak, "unit": "GB/s", "frac": spmv_bytes / (ms_spmv * 1e-3) / 1e9 / peak,
+                    "traffic": load_traffic("spmv_kernel")},
+           "note": f"fixed budget of {its} iterations (-ksp_max_it {its}); rows/nnz/GB/s are rank 0's strip; a converged "
+                   f"Jacobi-CG solve at this size needs O(10^4) iterations (SURVEY 7.2)"}
+    if dc is not None:
+        out["halo_bytes_per_iteration"] = dc.halo_bytes(2)
+    del ksp
+    return out
 
 
 def e2e_phase(a, prob, be, torch, barrier):
@@ -418,14 +414,17 @@ def e2e_phase(a, prob, be, torch, barrier):
     per-dof boundary classes go host->device, the matrices are integrated + assembled, diag(K) comes back."""
     import numpy as np
     cc_h = torch.from_numpy(np.asarray(prob.dom.getCellCornersCoords(0)).reshape(1, 4, 2)).pin_memory()
-    cls_h = prob.cls.cpu().pin_memory()
+    host_c, host_r = prob.mat.hostDofClasses(prob.dom)
+    cls_h = torch.from_numpy(host_c).pin_memory()
+    rcls_h = torch.from_numpy(host_r).pin_memory() if prob.dom.partition is not None else None
     diag_h = torch.empty(prob.nrows, dtype=torch.float64).pin_memory()
     ev = lambda: torch.cuda.Event(enable_timing=True)
 
     def one():
         cc = cc_h.to("cuda", non_blocking=True)
         cls = cls_h.to("cuda", non_blocking=True)
-        mats = prob.assemble(prob.integrate(cc), cls=cls)
+        rcls = rcls_h.to("cuda", non_blocking=True) if rcls_h is not None else None
+        mats = prob.step(classes=cls, row_classes=rcls, corners=cc)
         diag_h.copy_(mats["K"].diagonal(), non_blocking=True)
 
     for _ in range(2):
@@ -439,7 +438,8 @@ def e2e_phase(a, prob, be, torch, barrier):
     e.record()
     torch.cuda.synchronize()
     assert float(diag_h[0]) != 0.0
-    return {"ms": s.elapsed_time(e) / steps, "h2d": cc_h.numel() * 8 + cls_h.numel(), "d2h": diag_h.numel() * 8,
+    h2d = cc_h.numel() * 8 + cls_h.numel() + (rcls_h.numel() if rcls_h is not None else 0)
+    return {"ms": s.elapsed_time(e) / steps, "h2d": h2d, "d2h": diag_h.numel() * 8,
             "what": "pinned host corner coords + int8 dof classes -> device; integrate + assemble 8 matrices; "
                     "diag(K) -> pinned host"}
 

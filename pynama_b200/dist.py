@@ -94,14 +94,16 @@ class DistContext(object):
         dofs = (l2g[:, None] * ncomp + np.arange(ncomp)).reshape(-1)
         return dofs, vals.reshape(-1)
 
-    def __del__(self):
-        try:
-            lib = _lib.load()
-            if getattr(self, "_halo", None):
-                lib.pyn_halo_destroy(self._halo)
-                self._halo = None
-            if getattr(self, "_comm", None):
-                lib.pyn_comm_destroy(self._comm)
-                self._comm = None
-        except Exception:
-            pass
+    def close(self):
+        """Release the halo plan and the NCCL communicator.  Collective in spirit: call it on every rank, after the
+        solvers that were attached to this context are gone, and before torch.distributed is shut down.  It is NOT
+        called from __del__: tearing NCCL down from a garbage-collector callback at interpreter exit (other ranks may
+        already be gone, captured graphs may still hold NCCL nodes) can block forever."""
+        lib = _lib.load()
+        torch.cuda.synchronize()
+        if getattr(self, "_halo", None):
+            lib.pyn_halo_destroy(self._halo)
+            self._halo = None
+        if getattr(self, "_comm", None):
+            lib.pyn_comm_destroy(self._comm)
+            self._comm = None

@@ -80,22 +80,32 @@ class MatNS(Mat):
         self.mats = [self.K, self.Rw, self.Rd, self.Krhs, self.Kfs, self.Rwfs, self.Rdfs, self.Krhsfs]
 
     # -- B200 path --------------------------------------------------------------------------------------------
-    def assembleFromMesh(self, dom, elemType, names=None, classes=None):
+    def hostDofClasses(self, dom):
+        """(column classes, row classes) as host int8 arrays; they differ only on a partitioned mesh, where the rows
+        of ghost nodes are marked NOT_OWNED."""
+        host = noSlipDofClasses(dom, self.globalIndicesNS, self.globalIndicesDIR)
+        return host, rowClasses(dom, host, 2)
+
+    def assembleFromMesh(self, dom, elemType, names=None, classes=None, rowClassesDev=None, corners=None):
         """NoSlipFreeSlip.buildKLEMats for the whole mesh on the device (cell 0's element matrices for every cell,
         base_problem.py:333-334).  `names` restricts the matrices (default: all eight); re-assembly on an existing
-        pattern rewrites values only."""
+        pattern rewrites values only.  `classes` / `rowClassesDev` (device int8, from `hostDofClasses`) and `corners`
+        (device (1,4,2) corner coordinates of cell 0) let a caller feed the inputs from host buffers."""
         topo = dom.topology()
         if classes is None:
-            host = noSlipDofClasses(dom, self.globalIndicesNS, self.globalIndicesDIR)
+            host, hostRows = self.hostDofClasses(dom)
             classes = be.to_device(host)
-            self.rowClasses = classes if dom.partition is None else be.to_device(rowClasses(dom, host, 2))
-        elif getattr(self, "dofClasses", None) is not classes:
-            self.rowClasses = classes if dom.partition is None else \
-                be.to_device(rowClasses(dom, classes.cpu().numpy(), 2))
+            rowClassesDev = classes if dom.partition is None else be.to_device(hostRows)
         if getattr(self, "dofClasses", None) is not classes:
-            self.dofClasses = classes
+            if rowClassesDev is None:
+                if dom.partition is not None:
+                    raise Exception("partitioned mesh: pass rowClassesDev together with classes")
+                rowClassesDev = classes
+            self.dofClasses, self.rowClasses = classes, rowClassesDev
             self._maps = (be.BcMap(topo, self.rowClasses, 2, classes, 2), be.BcMap(topo, self.rowClasses, 2))
-        Ke, Rwe, Rde = elemType.getElemKLEMatricesDevice(dom.deviceCellCorners(0, 1), want_rd=True)
+        if corners is None:
+            corners = dom.deviceCellCorners(0, 1)
+        Ke, Rwe, Rde = elemType.getElemKLEMatricesDevice(corners, want_rd=True)
         E = {"K": Ke, "Rw": Rwe, "Rd": Rde}
         for name in (names or NS_DESCRIPTORS):
             cd, which, pairs, dcls, dadd, sign = NS_DESCRIPTORS[name]
