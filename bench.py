@@ -280,10 +280,10 @@ def run_native(a):
     # algorithmic bytes of the dominant launch (assembly of K, values only): 8 nnz written + int64 row pointers read
     # + 64 B of corner coordinates per cell; DESIGN.md "Roofline accounting"
     k_bytes = 8 * K.nnz + 8 * (K.shape[0] + 1) + 64 * prob.dom.ncell
-    roof = {"bound": "hbm", "kernel": "asm_interior_kernel<2,2> + boundary list (K, values on the prebuilt pattern)",
+    roof = {"bound": "hbm", "kernel": "asm_stream_kernel<2,2> (+ asm_template_kernel, boundary list): K values on the prebuilt pattern",
             "achieved": k_bytes / (k_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s", "peak_source": peak_src,
             "frac": k_bytes / (k_ms * 1e-3) / 1e9 / peak, "ms_per_launch": k_ms, "bytes_per_launch": k_bytes,
-            "traffic": load_traffic("asm_interior_kernel<2, 2>") if world == 1 else None}
+            "traffic": load_traffic("asm_stream_kernel<2, 2>") if world == 1 else None}
     out = {
         "metric": METRIC, "value": value, "unit": "DOF/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",

@@ -139,6 +139,11 @@ int pyn_asm_count(const pyn_topo* t, const pyn_asm_desc* desc, int64_t* d_indptr
 /* d_indices may be NULL (values only: re-assembly on a known pattern) ; d_data may be NULL (pattern only) */
 int pyn_asm_fill(const pyn_topo* t, const pyn_asm_desc* desc, const int64_t* d_indptr,
                  int32_t* d_indices, double* d_data, void* stream);
+/* Row templates (uniform meshes): when one element matrix serves every cell (E_stride == 0) and the topology found
+ * few distinct row signatures, a values-only pyn_asm_fill computes each distinct interior row once and streams it to all
+ * the nodes that share it (bit-identical to the gather kernel).  pyn_asm_set_templates(0) forces the gather kernel. */
+int pyn_asm_set_templates(int enabled);
+int pyn_topo_signatures(const pyn_topo* t, int* nsig, int64_t* template_slots);
 /* lumped weights  W[node] = sum_e W_e[local]  in ascending cell order  (mat_generator.py:168-170) */
 int pyn_asm_weights(const pyn_topo* t, const double* d_We, int64_t We_stride, double* d_W, void* stream);
 

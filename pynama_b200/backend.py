@@ -142,6 +142,9 @@ class Topology:
         nnz, val, row = C.c_int64(), C.c_int(), C.c_int()
         call("pyn_topo_info", self._h, C.byref(nnz), C.byref(val), C.byref(row))
         self.adj_nnz, self.max_valence, self.max_row = nnz.value, val.value, row.value
+        ns, slots = C.c_int(), C.c_int64()
+        call("pyn_topo_signatures", self._h, C.byref(ns), C.byref(slots))
+        self.nsig, self.sig_slots = ns.value, slots.value      # distinct row signatures (0: templates unavailable)
 
     def __del__(self):
         try:
@@ -173,6 +176,11 @@ class BcMap:
                 self._h = None
         except Exception:
             pass
+
+
+def set_templates(enabled):
+    """Enable/disable the row-template fast path of the values-only assembly (pyn_asm_set_templates)."""
+    call("pyn_asm_set_templates", 1 if enabled else 0)
 
 
 def pair_mask(pairs):
@@ -287,11 +295,13 @@ class CSR:
 
 
 def assemble(topo, rdof, cdof, E, rclass=None, cclass=None, pairs=ALL_PAIRS, diag_classes=0,
-             diag_add=(0.0, 0.0, 0.0, 0.0), sign=1.0, rowscale=None, pattern=None, name="", values=True, bcmap=None):
+             diag_add=(0.0, 0.0, 0.0, 0.0), sign=1.0, rowscale=None, pattern=None, name="", values=True, bcmap=None,
+             inplace=False):
     """Deterministic assembly of one matrix (pyn_asm_count + pyn_asm_fill).
 
     E: device tensor (1|ne, rdof*nn, cdof*nn).  pattern: an existing CSR whose indptr/indices are reused
-    (values-only re-assembly).  Returns CSR."""
+    (values-only re-assembly); with `inplace` its value array is overwritten and `pattern` itself is returned (no
+    allocation at all -- what a re-assembly inside a time loop wants).  Returns CSR."""
     d = AsmDesc()
     d.rdof, d.cdof = rdof, cdof
     d.d_rclass = rclass.data_ptr() if rclass is not None else None
@@ -321,6 +331,9 @@ def assemble(topo, rdof, cdof, E, rclass=None, cclass=None, pairs=ALL_PAIRS, dia
         fill_idx = indices
     else:
         indptr, indices, fill_idx = pattern.indptr, pattern.indices, None
+    if inplace and pattern is not None and pattern.data is not None:
+        call("pyn_asm_fill", topo._h, C.byref(d), ptr(indptr), None, ptr(pattern.data), stream())
+        return pattern
     data = empty(indices.numel()) if values else None
     call("pyn_asm_fill", topo._h, C.byref(d), ptr(indptr), ptr(fill_idx), ptr(data), stream())
     out = CSR((nrows, ncols), indptr, indices, data, name)

@@ -241,6 +241,95 @@ asm_interior_kernel(pyn::TopoView t, DescView d, const int64_t* __restrict__ ind
   }
 }
 
+// ---- uniform-mesh fast path: one template per row signature, streamed to every node that carries it ----------------
+// With ONE element matrix for all cells (E_stride == 0: the reference integrates cell 0 only, base_problem.py:333,133)
+// the rows of an interior node depend only on its signature (topo.cuh).  asm_template_kernel computes the RD x (L*CD)
+// block of each signature with exactly the arithmetic of asm_interior_kernel (same order of additions -> same bits);
+// asm_stream_kernel then writes it to every unflagged node: a pure store stream, bounded by HBM write bandwidth.
+template <int RD, int CD>
+__global__ void __launch_bounds__(128)
+asm_template_kernel(pyn::TopoView t, DescView d, double* __restrict__ T) {
+  const int lane = threadIdx.x & 31;
+  const int ldE = CD * t.nn;
+  for (int s = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); s < t.nsig; s += gridDim.x * (blockDim.x >> 5)) {
+    const int64_t r = t.sig_rep[s];
+    const int64_t b0 = t.n2e_ptr[r];
+    const int L = (int)(t.adj_ptr[r + 1] - t.adj_ptr[r]), deg = (int)(t.n2e_ptr[r + 1] - b0);
+    const uint8_t* iv = t.inv + t.inv_ptr[r];
+    double* out = T + t.sig_ptr[s] * (RD * CD);
+    for (int p = lane; p < L; p += 32) {
+      double v[RD][CD];
+#pragma unroll
+      for (int a = 0; a < RD; ++a)
+#pragma unroll
+        for (int b = 0; b < CD; ++b) v[a][b] = 0.0;
+      for (int k = 0; k < deg; ++k) {  // ascending cell order
+        const int l = iv[k * L + p];
+        if (l != 0xFF) {
+          const double* Ee = d.E + (int64_t)t.n2e_loc[b0 + k] * RD * ldE + l * CD;
+#pragma unroll
+          for (int a = 0; a < RD; ++a)
+#pragma unroll
+            for (int b = 0; b < CD; ++b) v[a][b] += d.sign * Ee[a * ldE + b];
+        }
+      }
+#pragma unroll
+      for (int a = 0; a < RD; ++a)
+#pragma unroll
+        for (int b = 0; b < CD; ++b) out[(a * L + p) * CD + b] = v[a][b];
+    }
+  }
+}
+
+constexpr int ASM_SB = 64;  // nodes per CTA batch of the stream kernel
+template <int RD, int CD>
+__global__ void __launch_bounds__(256)
+asm_stream_kernel(pyn::TopoView t, DescView d, const int64_t* __restrict__ indptr, const double* __restrict__ T,
+                  double* __restrict__ data) {
+  __shared__ int64_t s_base[ASM_SB], s_src[ASM_SB];
+  __shared__ int s_len[ASM_SB];
+  __shared__ double s_rs[ASM_SB];
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  const int64_t nbatch = (t.nnodes + ASM_SB - 1) / ASM_SB;
+  for (int64_t batch = blockIdx.x; batch < nbatch; batch += gridDim.x) {
+    const int64_t r0 = batch * ASM_SB;
+    const int nb = (int)min((int64_t)ASM_SB, t.nnodes - r0);
+    if (tid < nb) {
+      const int64_t r = r0 + tid;
+      const bool skip = d.flags[r] != 0;
+      const int L = (int)(t.adj_ptr[r + 1] - t.adj_ptr[r]);
+      s_len[tid] = skip ? 0 : L * (RD * CD);        // the RD rows of an interior node are contiguous in the CSR data
+      s_base[tid] = indptr[r * RD];
+      s_src[tid] = t.sig_ptr[t.sig_id[r]] * (RD * CD);
+      s_rs[tid] = d.rowscale ? d.rowscale[r] : 1.0;
+    }
+    __syncthreads();
+    for (int j = w; j < nb; j += 8) {
+      const int n = s_len[j];
+      if (n == 0) continue;
+      const double* src = T + s_src[j];
+      double* dst = data + s_base[j];
+      const double rs = s_rs[j];
+      if (((s_base[j] | s_src[j] | n) & 1) == 0) {      // 16-byte aligned on both sides: double2 stores
+        const double2* s2 = reinterpret_cast<const double2*>(src);
+        double2* d2 = reinterpret_cast<double2*>(dst);
+        for (int i = lane; i < (n >> 1); i += 32) {
+          double2 v = __ldg(s2 + i);
+          if (d.rowscale) { v.x = rs * v.x; v.y = rs * v.y; }
+          d2[i] = v;
+        }
+      } else {
+        for (int i = lane; i < n; i += 32) {
+          double v = __ldg(src + i);
+          if (d.rowscale) v = rs * v;
+          dst[i] = v;
+        }
+      }
+    }
+    __syncthreads();
+  }
+}
+
 // row lengths of the interior nodes: L*cdof when the (free,free) pair is kept, else 0
 __global__ void asm_interior_count_kernel(pyn::TopoView t, const uint8_t* __restrict__ flags, int rdof, int cdof,
                                           int keep00, int* __restrict__ rowcnt) {
@@ -455,7 +544,40 @@ static int launch_interior(const pyn_topo* t, const DescView& dv, const int64_t*
   return PYN_ERR_ARG;
 }
 
+// values-only assembly of the interior nodes through row templates (needs signatures and one element matrix)
+static int launch_templates(const pyn_topo* t, const DescView& dv, const int64_t* indptr, double* data, cudaStream_t st) {
+  const pyn::TopoView tv = pyn::view_of(t);
+  pyn_topo* tm = const_cast<pyn_topo*>(t);   // scratch owned by the handle (one host thread per handle)
+  if (!tm->sig_tmpl) PYN_CHECK_CUDA(cudaMalloc(&tm->sig_tmpl, sizeof(double) * (size_t)t->sig_slots * 9));
+  double* T = tm->sig_tmpl;
+  const int tgrid = (t->nsig + 3) / 4;
+  const int sgrid = pyn::grid_for((t->nnodes + ASM_SB - 1) / ASM_SB * 256, 256, 8);
+  bool done = false;
+#define PYN_ASM_CASE(R, C)                                                                        \
+  if (!done && dv.rdof == R && dv.cdof == C) {                                                    \
+    asm_template_kernel<R, C><<<tgrid, 128, 0, st>>>(tv, dv, T);                                  \
+    pyn::count_launch();                                                                          \
+    asm_stream_kernel<R, C><<<sgrid, 256, 0, st>>>(tv, dv, indptr, T, data);                      \
+    pyn::count_launch();                                                                          \
+    done = true;                                                                                  \
+  }
+  PYN_ASM_CASE(2, 2) PYN_ASM_CASE(2, 1) PYN_ASM_CASE(1, 2) PYN_ASM_CASE(3, 2) PYN_ASM_CASE(2, 3)
+  PYN_ASM_CASE(1, 1) PYN_ASM_CASE(3, 3) PYN_ASM_CASE(1, 3) PYN_ASM_CASE(3, 1)
+#undef PYN_ASM_CASE
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    pyn::set_error("template assembly: %s", cudaGetErrorString(e));
+    return PYN_ERR_CUDA;
+  }
+  if (!done) {
+    pyn::set_error("assembly: unsupported block shape %d x %d", dv.rdof, dv.cdof);
+    return PYN_ERR_ARG;
+  }
+  return PYN_OK;
+}
+
 // the interior fast path applies when a map is given and class-0 rows carry no forced diagonal
+static bool g_no_templates = false;  // pyn_asm_set_templates(0): force the generic gather kernel (tests, comparisons)
 static inline bool use_map(const pyn_asm_desc* desc) { return desc->bcmap != nullptr && !(desc->diag_classes & 1u); }
 
 extern "C" {
@@ -542,12 +664,26 @@ int pyn_asm_fill(const pyn_topo* t, const pyn_asm_desc* desc, const int64_t* d_i
   if (use_map(desc)) {
     PYN_REQUIRE(desc->bcmap->nnodes == t->nnodes, "bcmap belongs to another topology");
     if ((dv.pair_mask & 1u) && (d_data || d_indices)) {
-      rc = launch_interior(t, dv, d_indptr, d_indices, d_data, st);
+      // values on a known pattern, one element matrix for all cells, repetitive mesh: stream the row templates
+      const bool tmpl = d_data && !d_indices && dv.E_stride == 0 && t->nsig > 0 && !g_no_templates;
+      rc = tmpl ? launch_templates(t, dv, d_indptr, d_data, st) : launch_interior(t, dv, d_indptr, d_indices, d_data, st);
       if (rc) return rc;
     }
     return launch_asm<false>(t, dv, desc->bcmap->list, desc->bcmap->nlist, nullptr, d_indptr, d_indices, d_data, st);
   }
   return launch_asm<false>(t, dv, nullptr, 0, nullptr, d_indptr, d_indices, d_data, st);
+}
+
+int pyn_asm_set_templates(int enabled) {
+  g_no_templates = !enabled;
+  return PYN_OK;
+}
+
+int pyn_topo_signatures(const pyn_topo* t, int* nsig, int64_t* slots) {
+  PYN_REQUIRE(t, "topo is NULL");
+  if (nsig) *nsig = t->nsig;
+  if (slots) *slots = t->sig_slots;
+  return PYN_OK;
 }
 
 int pyn_asm_weights(const pyn_topo* t, const double* d_We, int64_t stride, double* d_W, void* stream) {

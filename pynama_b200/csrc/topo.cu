@@ -244,6 +244,124 @@ int scan_counts(const int* d_cnt, int64_t n, int64_t* d_ptr, int64_t* h_total, c
   PYN_CHECK_CUDA(cudaFreeAsync(tmp64, st));
   return PYN_OK;
 }
+
+// ---- row signatures ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint64_t sig_mix(uint64_t h, uint64_t v) {
+  h ^= v;
+  h *= 0x100000001b3ULL;   // FNV-1a step on 64-bit words
+  h ^= h >> 29;
+  return h;
+}
+__global__ void sig_hash_kernel(pyn::TopoView t, uint64_t* __restrict__ key, int* __restrict__ node) {
+  for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < t.nnodes; r += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t b0 = t.n2e_ptr[r];
+    const int deg = (int)(t.n2e_ptr[r + 1] - b0), L = (int)(t.adj_ptr[r + 1] - t.adj_ptr[r]);
+    uint64_t h = sig_mix(0xcbf29ce484222325ULL, ((uint64_t)deg << 32) | (uint32_t)L);
+    for (int k = 0; k < deg; ++k) h = sig_mix(h, (uint64_t)(uint16_t)t.n2e_loc[b0 + k] + 0x9e37ULL * (k + 1));
+    const uint8_t* iv = t.inv + t.inv_ptr[r];
+    const int len = deg * L;
+    uint64_t w = 0;
+    for (int i = 0; i < len; ++i) {
+      w = (w << 8) | iv[i];
+      if ((i & 7) == 7) { h = sig_mix(h, w); w = 0; }
+    }
+    h = sig_mix(h, w + 0x51ULL);
+    key[r] = h;
+    node[r] = (int)r;
+  }
+}
+__global__ void sig_heads_kernel(int64_t n, const uint64_t* __restrict__ key, int* __restrict__ head) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    head[i] = (i == 0 || key[i] != key[i - 1]) ? 1 : 0;
+}
+// gid = inclusive scan of heads - 1 ; the sort is stable, so the head of a group is its lowest-numbered node
+__global__ void sig_assign_kernel(int64_t n, const int* __restrict__ head, const int64_t* __restrict__ scan,
+                                  const int* __restrict__ node, int* __restrict__ sig_id, int* __restrict__ rep) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int g = (int)(scan[i + 1] - 1);
+    sig_id[node[i]] = g;
+    if (head[i]) rep[g] = node[i];
+  }
+}
+// exact comparison with the representative (a hash collision disables the fast path for this mesh)
+__global__ void sig_verify_kernel(pyn::TopoView t, const int* __restrict__ sig_id, const int* __restrict__ rep,
+                                  int* __restrict__ bad) {
+  for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < t.nnodes; r += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t q = rep[sig_id[r]];
+    if (q == r) continue;
+    const int64_t b0 = t.n2e_ptr[r], c0 = t.n2e_ptr[q];
+    const int deg = (int)(t.n2e_ptr[r + 1] - b0), L = (int)(t.adj_ptr[r + 1] - t.adj_ptr[r]);
+    bool same = deg == (int)(t.n2e_ptr[q + 1] - c0) && L == (int)(t.adj_ptr[q + 1] - t.adj_ptr[q]);
+    if (same) {
+      for (int k = 0; k < deg; ++k) same &= t.n2e_loc[b0 + k] == t.n2e_loc[c0 + k];
+      const uint8_t *a = t.inv + t.inv_ptr[r], *b = t.inv + t.inv_ptr[q];
+      for (int i = 0; i < deg * L && same; ++i) same = a[i] == b[i];
+    }
+    if (!same) atomicAdd(bad, 1);
+  }
+}
+__global__ void sig_len_kernel(int nsig, pyn::TopoView t, const int* __restrict__ rep, int* __restrict__ len) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nsig; i += gridDim.x * blockDim.x)
+    len[i] = (int)(t.adj_ptr[rep[i] + 1] - t.adj_ptr[rep[i]]);
+}
+
+// Builds sig_id / sig_rep / sig_ptr; leaves nsig = 0 when the mesh has too many distinct rows to make templates pay.
+int build_signatures(pyn_topo* t, cudaStream_t st) {
+  const int64_t n = t->nnodes;
+  t->nsig = 0;
+  if (n >= 2147483647LL) return PYN_OK;
+  uint64_t *key = nullptr, *key2 = nullptr;
+  int *node = nullptr, *node2 = nullptr, *head = nullptr, *bad = nullptr, *len = nullptr;
+  int64_t* scan = nullptr;
+  void* tmp = nullptr;
+  size_t bytes = 0;
+  int rc = PYN_OK;
+  auto fail = [&](const char* what, cudaError_t e) {
+    pyn::set_error("build_signatures: %s: %s", what, cudaGetErrorString(e));
+    rc = PYN_ERR_CUDA;
+  };
+  cudaError_t e;
+  const pyn::TopoView v = pyn::view_of(t);
+  do {
+    if ((e = cudaMalloc(&key, 8 * n)) || (e = cudaMalloc(&key2, 8 * n)) || (e = cudaMalloc(&node, 4 * n)) ||
+        (e = cudaMalloc(&node2, 4 * n)) || (e = cudaMalloc(&head, 4 * (n + 1))) || (e = cudaMalloc(&scan, 8 * (n + 1))) ||
+        (e = cudaMalloc(&bad, 4)) || (e = cudaMalloc(&t->sig_id, 4 * n))) { fail("malloc", e); break; }
+    sig_hash_kernel<<<pyn::grid_for(n, 128, 32), 128, 0, st>>>(v, key, node);
+    pyn::count_launch();
+    cub::DeviceRadixSort::SortPairs(tmp, bytes, key, key2, node, node2, n, 0, 64, st);
+    if ((e = cudaMalloc(&tmp, bytes))) { fail("malloc sort", e); break; }
+    cub::DeviceRadixSort::SortPairs(tmp, bytes, key, key2, node, node2, n, 0, 64, st);
+    pyn::count_launch();
+    sig_heads_kernel<<<pyn::grid_for(n, 256), 256, 0, st>>>(n, key2, head);
+    pyn::count_launch();
+    int64_t nsig64 = 0;
+    rc = pyn::scan_counts(head, n, scan, &nsig64, st);
+    if (rc) break;
+    if (nsig64 > 4096 || nsig64 * 8 > n) break;      // not a repetitive mesh: keep the generic kernels
+    const int nsig = (int)nsig64;
+    if ((e = cudaMalloc(&t->sig_rep, 4 * nsig)) || (e = cudaMalloc(&t->sig_ptr, 8 * (nsig + 1))) ||
+        (e = cudaMalloc(&len, 4 * (nsig + 1)))) { fail("malloc rep", e); break; }
+    sig_assign_kernel<<<pyn::grid_for(n, 256), 256, 0, st>>>(n, head, scan, node2, t->sig_id, t->sig_rep);
+    pyn::count_launch();
+    cudaMemsetAsync(bad, 0, 4, st);
+    sig_verify_kernel<<<pyn::grid_for(n, 128, 32), 128, 0, st>>>(v, t->sig_id, t->sig_rep, bad);
+    pyn::count_launch();
+    int h_bad = 0;
+    if ((e = cudaMemcpyAsync(&h_bad, bad, 4, cudaMemcpyDeviceToHost, st)) || (e = cudaStreamSynchronize(st))) {
+      fail("verify", e);
+      break;
+    }
+    if (h_bad) break;                                  // hash collision: no templates for this mesh
+    sig_len_kernel<<<pyn::grid_for(nsig, 256), 256, 0, st>>>(nsig, v, t->sig_rep, len);
+    pyn::count_launch();
+    rc = pyn::scan_counts(len, nsig, t->sig_ptr, &t->sig_slots, st);
+    if (rc) break;
+    t->nsig = nsig;
+  } while (0);
+  cudaFree(key); cudaFree(key2); cudaFree(node); cudaFree(node2); cudaFree(head); cudaFree(scan); cudaFree(bad);
+  cudaFree(len); cudaFree(tmp);
+  return rc;
+}
 }  // namespace pyn
 
 extern "C" {
@@ -395,6 +513,7 @@ int pyn_topo_create(const int32_t* d_e2n, int64_t ne, int nn, int64_t nnodes, vo
   TOPO_TRY(cuda_try(cudaStreamSynchronize(st), "sync"));
   TOPO_TRY(cuda_try(cudaGetLastError(), "kernels"));
   cudaFree(cnt);
+  TOPO_TRY(pyn::build_signatures(t, st));
 #undef TOPO_TRY
   *out = t;
   return PYN_OK;
@@ -403,6 +522,7 @@ int pyn_topo_create(const int32_t* d_e2n, int64_t ne, int nn, int64_t nnodes, vo
 int pyn_topo_destroy(pyn_topo* t) {
   if (!t) return PYN_OK;
   cudaFree(t->n2e_ptr); cudaFree(t->n2e_elem); cudaFree(t->n2e_loc); cudaFree(t->adj_ptr); cudaFree(t->adj_cols); cudaFree(t->inv_ptr); cudaFree(t->inv);
+  cudaFree(t->sig_id); cudaFree(t->sig_rep); cudaFree(t->sig_ptr); cudaFree(t->sig_tmpl);
   delete t;
   return PYN_OK;
 }

@@ -16,6 +16,15 @@ struct pyn_topo {
                        // node r, of the p-th adjacency column of r (0xFF: that column is not a node of the element)
   int64_t adj_nnz, inv_len;
   int max_valence, max_row;
+  // Row signatures (uniform-mesh fast path of the assembly).  Two nodes whose incidence lists (local indices inside
+  // their elements) and inverse position maps are byte-identical get identical rows from ONE element matrix, so the
+  // rows are computed once per signature ("template") and streamed to every node that carries it.
+  int* sig_id;        // [nnodes] signature of each node
+  int nsig;           // 0 = signatures not available (irregular mesh or hash collision)
+  int* sig_rep;       // [nsig] representative (lowest-numbered) node
+  int64_t* sig_ptr;   // [nsig+1] offsets of the templates in adjacency slots
+  int64_t sig_slots;
+  double* sig_tmpl;    // [sig_slots * 9] scratch for the row templates of the matrix being assembled (lazy)
 };
 
 struct pyn_bcmap {
@@ -36,12 +45,17 @@ struct TopoView {
   const int* adj_cols;
   const int64_t* inv_ptr;
   const uint8_t* inv;
+  const int* sig_id;
+  const int* sig_rep;
+  const int64_t* sig_ptr;
+  int nsig;
 };
 static inline TopoView view_of(const pyn_topo* t) {
   TopoView v;
   v.ne = t->ne; v.nnodes = t->nnodes; v.nn = t->nn; v.e2n = t->e2n;
   v.n2e_ptr = t->n2e_ptr; v.n2e_elem = t->n2e_elem; v.n2e_loc = t->n2e_loc;
   v.adj_ptr = t->adj_ptr; v.adj_cols = t->adj_cols; v.inv_ptr = t->inv_ptr; v.inv = t->inv;
+  v.sig_id = t->sig_id; v.sig_rep = t->sig_rep; v.sig_ptr = t->sig_ptr; v.nsig = t->nsig;
   return v;
 }
 int scan_counts(const int* d_cnt, int64_t n, int64_t* d_ptr, int64_t* h_total, cudaStream_t st);

@@ -111,7 +111,7 @@ class MatNS(Mat):
             cd, which, pairs, dcls, dadd, sign = NS_DESCRIPTORS[name]
             m = getattr(self, name)
             csr = be.assemble(topo, 2, cd, E[which], self.rowClasses, classes if cd == 2 else None, pairs, diag_classes=dcls,
-                              diag_add=dadd, sign=sign, pattern=m.csr, name=name,
+                              diag_add=dadd, sign=sign, pattern=m.csr, inplace=True, name=name,
                               bcmap=self._maps[0] if cd == 2 else self._maps[1])
             m.csr, m.shape = csr, csr.shape
         self._unit_diagonals_folded = True

@@ -177,6 +177,52 @@ def test_assembly_noslip_and_operators_vs_oracle(be, nx, ny, n):
         _same_pattern(Ac, sc)
 
 
+@pytest.mark.parametrize("nx,ny,n", [(8, 8, 3), (6, 5, 5), (5, 7, 2), (3, 3, 8)])
+def test_template_assembly_is_bit_identical(be, nx, ny, n):
+    """Values-only re-assembly on a known pattern takes the row-template stream kernels on uniform meshes; it must
+    reproduce the gather kernels bit for bit (all cavity matrices, operators with their 1/W row scaling), and the
+    per-cell path (one element matrix per cell) must keep using the gather kernel."""
+    m = o.BoxMesh([nx, ny], [0, 0], [1, 1], n)
+    ref = o.assemble_noslip(m)
+    topo = be.Topology(be.box_cell_nodes(nx, ny, n), m.nnodes)
+    # a handful of node types (interior, edge, vertex x borders); tiny meshes have too few repeats and keep nsig = 0
+    assert topo.nsig <= 4096 and (topo.nsig > 0 or nx * ny < 40), topo.nsig
+    cls = _upload_classes(be, ref["cls"])
+    c0 = m.cell_corner_coords([0])
+    Ke, Rwe, Rde = (be.to_device(a) for a in o.elem_kle_matrices(n, c0))
+    m22, m21 = be.BcMap(topo, cls, 2, cls, 2), be.BcMap(topo, cls, 2)
+    one = (0, 1.0, 1.0, 0)
+    specs = {"K": (2, Ke, [(0, 0)], 0b110, one, 1.0), "Krhs": (2, Ke, [(0, 1), (0, 2)], 0b110, one, -1.0),
+             "Kfs": (2, Ke, [(1, 0), (0, 1), (1, 1)], 0b010, (0, -1.0, 0, 0), 1.0),
+             "Rw": (1, Rwe, [(0, 0)], 0, (0,) * 4, 1.0), "Rd": (1, Rde, [(0, 0)], 0, (0,) * 4, 1.0),
+             "mRw": (1, Rwe, [(0, 0)], 0, (0,) * 4, -1.0)}
+    for name, (cd, E, pairs, dcls, dadd, sign) in specs.items():
+        kw = dict(diag_classes=dcls, diag_add=dadd, sign=sign, bcmap=m22 if cd == 2 else m21)
+        A = be.assemble(topo, 2, cd, E, cls, cls if cd == 2 else None, pairs, **kw)                 # gather (+indices)
+        B = be.assemble(topo, 2, cd, E, cls, cls if cd == 2 else None, pairs, pattern=A, **kw)      # templates
+        be.set_templates(False)
+        Cm = be.assemble(topo, 2, cd, E, cls, cls if cd == 2 else None, pairs, pattern=A, **kw)     # gather, values only
+        be.set_templates(True)
+        np.testing.assert_array_equal(B.data.cpu().numpy(), A.data.cpu().numpy(), err_msg=name)
+        np.testing.assert_array_equal(Cm.data.cpu().numpy(), A.data.cpu().numpy(), err_msg=name)
+        if name in ref:
+            np.testing.assert_array_equal(B.data.cpu().numpy(), ref[name].data, err_msg=name)
+    S, D, Cu, W = (be.to_device(a) for a in o.elem_kle_operators(n, c0))
+    rW = 1.0 / be.assemble_weights(topo, W)
+    nomap = be.BcMap(topo)
+    rops = o.assemble_operators(m)
+    for name, E, rd, cd in (("SrT", S, 3, 2), ("DivSrT", D, 2, 3), ("Curl", Cu, 1, 2)):
+        A = be.assemble(topo, rd, cd, E, rowscale=rW, bcmap=nomap)
+        B = be.assemble(topo, rd, cd, E, rowscale=rW, bcmap=nomap, pattern=A)
+        np.testing.assert_array_equal(B.data.cpu().numpy(), A.data.cpu().numpy(), err_msg=name)
+        np.testing.assert_array_equal(B.data.cpu().numpy(), rops[name].data, err_msg=name)
+    # per-cell element matrices: signatures do not apply, values still right
+    Kall = be.to_device(o.elem_kle_matrices(n, m.cell_corner_coords())[0])
+    A = be.assemble(topo, 2, 2, Kall, cls, cls, [(0, 0)], diag_classes=0b110, diag_add=one, bcmap=m22)
+    B = be.assemble(topo, 2, 2, Kall, cls, cls, [(0, 0)], diag_classes=0b110, diag_add=one, bcmap=m22, pattern=A)
+    np.testing.assert_array_equal(B.data.cpu().numpy(), A.data.cpu().numpy())
+
+
 def test_coo_to_csr_generic(be):
     """Mat.setValues(ADD)+assemble semantics: sorted, duplicates added in input order, explicit zeros kept."""
     rng = np.random.default_rng(3)
