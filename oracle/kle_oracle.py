@@ -760,3 +760,71 @@ def rk_adaptive(f, t0, y0, t_end, dt0=0.1, atol=1e-4, rtol=1e-4, max_steps=5000,
         steps += 1
         dt = match(t, dt * fac)
     return t, y, hs, nrej
+
+
+# --------------------------------------------------------------------------------------------------------
+# S1b  KSP: restarted GMRES with PETSc semantics (restated from the KSPGMRES documentation)
+# --------------------------------------------------------------------------------------------------------
+def ksp_gmres(A, b, rtol=1e-5, atol=1e-50, dtol=1e4, max_it=10000, restart=30, jacobi=True):
+    """Left-preconditioned GMRES(restart), zero initial guess, classical Gram-Schmidt without refinement, residual
+    norm from the Givens recurrence, KSPConvergedDefault; the true preconditioned residual is formed and tested at the
+    top of every cycle (src/solver/ksp_solver.py:9-19 with -ksp_type gmres).  Returns x, its, reason, history."""
+    n = A.shape[0]
+    dinv = 1.0 / A.diagonal() if jacobi else np.ones(n)
+    x = np.zeros(n)
+    its, reason, hist, m = 0, 0, [], restart
+    rnorm0 = ttol = None
+    while not reason:
+        r = dinv * (b - A @ x) if its else dinv * b
+        beta = math.sqrt(r @ r)
+        if rnorm0 is None:
+            rnorm0, ttol = beta, max(rtol * beta, atol)
+            hist.append(beta)
+        if beta <= ttol:
+            reason = 3 if beta <= atol else 2
+            break
+        if beta >= dtol * rnorm0:
+            reason = -4
+            break
+        if its >= max_it:
+            reason = -3
+            break
+        V = [r / beta]
+        H = np.zeros((m + 1, m))
+        cs, sn, g = np.zeros(m), np.zeros(m), np.zeros(m + 1)
+        g[0] = beta
+        k = 0
+        for j in range(m):
+            w = dinv * (A @ V[j])
+            h = np.array([V[i] @ w for i in range(j + 1)])
+            for i in range(j + 1):
+                w = w - h[i] * V[i]
+            hn = math.sqrt(w @ w)
+            V.append(w / hn if hn > 0 else w)
+            H[:j + 1, j], H[j + 1, j] = h, hn
+            for i in range(j):
+                t = cs[i] * H[i, j] + sn[i] * H[i + 1, j]
+                H[i + 1, j] = -sn[i] * H[i, j] + cs[i] * H[i + 1, j]
+                H[i, j] = t
+            den = math.hypot(H[j, j], H[j + 1, j])
+            cs[j], sn[j] = H[j, j] / den, H[j + 1, j] / den
+            H[j, j], H[j + 1, j] = den, 0.0
+            g[j + 1], g[j] = -sn[j] * g[j], cs[j] * g[j]
+            rn = abs(g[j + 1])
+            its += 1
+            k = j + 1
+            hist.append(rn)
+            if rn <= ttol:
+                reason = 3 if rn <= atol else 2
+            elif hn == 0.0:
+                reason = 2
+            elif rn >= dtol * rnorm0:
+                reason = -4
+            elif its >= max_it:
+                reason = -3
+            if reason:
+                break
+        y = np.linalg.solve(np.triu(H[:k, :k]), g[:k]) if k else np.zeros(0)
+        for i in range(k):
+            x = x + y[i] * V[i]
+    return x, its, reason, hist

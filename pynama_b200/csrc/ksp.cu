@@ -11,20 +11,12 @@
 
 #include "dist.cuh"
 #include "spmv.cuh"
+#include "ksp.cuh"
 
 namespace {
 constexpr int BLK = 256;
 
-struct KspState {
-  double beta, betaold, dp, rnorm0, ttol;
-  int its, reason, done, pad;
-};
 
-struct CgBuffers {
-  double *r, *z, *p, *w, *x, *dinv;
-  double *part_a, *part_b;  // per-CTA partials (two reductions per kernel)
-  KspState* st;
-};
 
 __global__ void jacobi_inv_kernel(int64_t n, const double* __restrict__ diag, double* __restrict__ dinv, int use) {
   for (int64_t i = blockIdx.x * (int64_t)BLK + threadIdx.x; i < n; i += (int64_t)gridDim.x * BLK) {
@@ -192,27 +184,8 @@ __global__ void copy_kernel(int64_t n, const double* __restrict__ src, double* _
 
 }  // namespace
 
-struct pyn_ksp {
-  int64_t n, nnz;
-  const int64_t* ptr;
-  const int* ind;
-  const double* val;
-  pyn_ksp_opts opts;
-  CgBuffers B;
-  double *pzz, *pzr;
-  KspState* h_state;  // pinned
-  int vgrid, sgrid;
-  pyn_spmv_plan* plan;
-  cudaGraphExec_t graph;
-  int graph_iters;
-  int64_t last_spmv, last_launches;
-  // multi-GPU (pyn_ksp_set_dist): communicator, halo plan of the unknown (ncomp dofs per node), owned-row mask
-  const pyn_comm* comm;
-  const pyn_halo* halo;
-  int halo_comp;
-  const uint8_t* owned;
-  double* gsum;  // [p.w, z.z, z.r]
-};
+#include "ksp.cuh"
+
 
 namespace {
 
@@ -248,7 +221,7 @@ extern "C" {
 int pyn_ksp_create(int64_t nrows, const int64_t* d_ptr, const int32_t* d_ind, const double* d_val, int64_t nnz,
                    const pyn_ksp_opts* opts, void* stream, pyn_ksp** out) {
   PYN_REQUIRE(nrows > 0 && d_ptr && d_ind && d_val && opts && out, "bad arguments");
-  PYN_REQUIRE(opts->type == 0, "only cg (type 0) is available through pyn_ksp_create in this build");
+  PYN_REQUIRE(opts->type == 0 || opts->type == 1, "ksp type must be 0 (cg) or 1 (gmres)");
   PYN_REQUIRE(opts->nonzero_guess == 0, "nonzero initial guess is not supported (PETSc default is zero)");
   cudaStream_t st = pyn::as_stream(stream);
   pyn_ksp* k = new pyn_ksp();
@@ -287,6 +260,7 @@ int pyn_ksp_create(int64_t nrows, const int64_t* d_ptr, const int32_t* d_ind, co
 int pyn_ksp_solve(pyn_ksp* k, const double* d_b, double* d_x, pyn_ksp_result* res, void* stream) {
   PYN_REQUIRE(k && d_b && d_x, "bad arguments");
   cudaStream_t st = pyn::as_stream(stream);
+  if (k->opts.type == 1) return pyn::gmres_solve(k, d_b, d_x, res, st);
   int64_t launches = 0;
   const bool dist = k->comm && k->comm->world > 1;
   cg_init_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, d_b, k->B, dist ? k->owned : nullptr);
@@ -348,6 +322,7 @@ int pyn_ksp_destroy(pyn_ksp* k) {
   cudaFree(k->B.r);
   cudaFree(k->B.st);
   cudaFree(k->gsum);
+  pyn::gmres_free(k->gm);
   cudaFreeHost(k->h_state);
   delete k;
   return PYN_OK;

@@ -1,0 +1,44 @@
+// Krylov solver handle shared by ksp.cu (CG, handle life cycle) and gmres.cu.
+#pragma once
+#include "dist.cuh"
+#include "spmv.cuh"
+
+struct KspState {
+  double beta, betaold, dp, rnorm0, ttol;
+  int its, reason, done, pad;
+};
+
+struct CgBuffers {
+  double *r, *z, *p, *w, *x, *dinv;
+  double *part_a, *part_b;  // per-CTA partials (two reductions per kernel)
+  KspState* st;
+};
+
+struct pyn_ksp {
+  int64_t n, nnz;
+  const int64_t* ptr;
+  const int* ind;
+  const double* val;
+  pyn_ksp_opts opts;
+  CgBuffers B;
+  double *pzz, *pzr;
+  KspState* h_state;  // pinned
+  int vgrid, sgrid;
+  pyn_spmv_plan* plan;
+  cudaGraphExec_t graph;
+  int graph_iters;
+  int64_t last_spmv, last_launches;
+  // multi-GPU (pyn_ksp_set_dist): communicator, halo plan of the unknown (ncomp dofs per node), owned-row mask
+  const pyn_comm* comm;
+  const pyn_halo* halo;
+  int halo_comp;
+  const uint8_t* owned;
+  double* gsum;  // [p.w, z.z, z.r]
+  struct pyn_gmres* gm;  // GMRES work space (lazy)
+};
+
+struct pyn_gmres;
+namespace pyn {
+int gmres_solve(pyn_ksp* k, const double* d_b, double* d_x, pyn_ksp_result* res, cudaStream_t st);
+void gmres_free(pyn_gmres* g);
+}  // namespace pyn

@@ -334,6 +334,31 @@ def test_cg_jacobi_petsc_semantics(be, nx, n, rtol):
     assert (r.its, r.reason) == (5, -3)
 
 
+@pytest.mark.parametrize("nx,n,rtol,restart,pc", [(8, 3, 1e-8, 30, "jacobi"), (6, 4, 1e-10, 30, "jacobi"),
+                                                   (6, 4, 1e-6, 7, "jacobi"), (5, 3, 1e-8, 30, "none")])
+def test_gmres_petsc_semantics(be, nx, n, rtol, restart, pc):
+    """Restarted GMRES (classical Gram-Schmidt, left PC, Givens residual) against the oracle's restatement of KSPGMRES:
+    same iteration count / reason up to round-off sensitivity, solution within 1e-10 relative at tight rtol."""
+    m, K, A, b, _ = _freeslip_system(be, nx, nx, n)
+    xo, its, reason, hist = o.ksp_gmres(K, b, rtol=rtol, restart=restart, jacobi=(pc == "jacobi"), max_it=4000)
+    ksp = be.Ksp(A, "gmres", pc, rtol=rtol, restart=restart, max_it=4000)
+    x = be.empty(K.shape[0])
+    r = ksp.solve(be.to_device(b), x)
+    # classical Gram-Schmidt without refinement loses orthogonality at round-off level, and a short restart multiplies
+    # the effect: the count moves by a few percent between two summation orders of the same algorithm
+    assert r.reason == reason and abs(r.its - its) <= max(2, its // 10), (r.its, its, r.reason, reason)
+    assert abs(r.rnorm0 - hist[0]) < 1e-12 * hist[0]
+    xs = o.direct_solve(K, b)
+    # both stop ~rtol away from the exact solution; they agree with each other much more closely than that
+    assert rel_err(x.cpu().numpy(), xo) < max(TOL_KSP, 1e-2 * rtol) * (1 if r.its == its else 50)
+    assert rel_err(x.cpu().numpy(), xs) < 1e3 * rtol
+    r = ksp.solve(be.zeros(K.shape[0]), x)
+    assert r.its == 0 and r.reason in (2, 3)
+    ksp2 = be.Ksp(A, "gmres", pc, rtol=1e-14, restart=4, max_it=9)
+    r = ksp2.solve(be.to_device(b), x)
+    assert (r.its, r.reason) == (9, -3)
+
+
 def test_taylor_green_known_answer_gpu(be):
     """src/tests/test_solver.py:29-37 on the GPU path: 2x2 elements, ngl 11, ||v - v_exact||_2 < 2e-8
     (K assembled on device from device-integrated per-cell element matrices, CG to rtol 1e-13)."""
