@@ -189,6 +189,20 @@ int pyn_spmv_plan_destroy(pyn_spmv_plan* plan);
 int pyn_spmv_planned(const pyn_spmv_plan* plan, const int32_t* d_ind, const double* d_val, const double* d_x,
                      double* d_y, int mode, double p0, double p1, const double* d_aux, void* stream);
 
+/* Template operator (uniform meshes): the same y = A x without streaming the matrix values.  Built from the
+ * descriptor a matrix was assembled with (one element matrix for all cells, boundary map, row signatures available)
+ * plus the assembled CSR, whose rows are used for the boundary-affected nodes only; interior nodes multiply with their
+ * row template through the node adjacency: 4 B of HBM per adjacency slot instead of 12 B per stored entry.  The CSR
+ * may be any matrix that equals the descriptor's matrix on the interior rows (e.g. K + Kfs for K).  All arrays are
+ * borrowed.  Same modes as pyn_spmv. */
+typedef struct pyn_tmat pyn_tmat;
+int pyn_tmat_create(const pyn_topo* t, const pyn_asm_desc* desc, const int64_t* d_indptr, const int32_t* d_indices,
+                    const double* d_data, void* stream, pyn_tmat** out);
+int pyn_tmat_destroy(pyn_tmat* m);
+int pyn_tmat_mult(const pyn_tmat* m, const double* d_x, double* d_y, int mode, double p0, double p1, const double* d_aux,
+                  void* stream);
+int64_t pyn_tmat_bytes(const pyn_tmat* m);
+
 /* ------------------------------------------------------------------------------------------------------
  * Vectors (PETSc Vec calls of the path: base_problem.py:222-230,234-252; cavity.py:53-81; custom_func.py:76-83)
  * ---------------------------------------------------------------------------------------------------- */
@@ -236,6 +250,8 @@ int pyn_ksp_solve(pyn_ksp* k, const double* d_b, double* d_x, pyn_ksp_result* re
 int pyn_ksp_destroy(pyn_ksp* k);
 /* device work done by the last solve: SpMV launches and total kernel launches (for the roofline accounting) */
 int pyn_ksp_stats(const pyn_ksp* k, int64_t* spmv_launches, int64_t* kernel_launches);
+/* CG applies the operator through the template operator instead of the CSR stream (NULL: back to the CSR) */
+int pyn_ksp_set_tmat(pyn_ksp* k, const pyn_tmat* m);
 
 /* ------------------------------------------------------------------------------------------------------
  * Multi-GPU: one process per GPU, the mesh cut into strips of cell rows (the reference: DMPlex.distribute(),

@@ -100,6 +100,11 @@ _SIGNATURES = {
     "pyn_halo_destroy": (C.c_int, [c_vp]),
     "pyn_halo_exchange": (C.c_int, [c_vp, c_vp, C.c_int, c_vp]),
     "pyn_halo_bytes": (c_i64, [c_vp, C.c_int]),
+    "pyn_tmat_create": (C.c_int, [c_vp, P(AsmDesc), c_vp, c_vp, c_vp, c_vp, P(c_vp)]),
+    "pyn_tmat_destroy": (C.c_int, [c_vp]),
+    "pyn_tmat_mult": (C.c_int, [c_vp, c_vp, c_vp, C.c_int, c_f64, c_f64, c_vp, c_vp]),
+    "pyn_tmat_bytes": (c_i64, [c_vp]),
+    "pyn_ksp_set_tmat": (C.c_int, [c_vp, c_vp]),
     "pyn_ksp_set_dist": (C.c_int, [c_vp, c_vp, c_vp, C.c_int, c_vp]),
 }
 

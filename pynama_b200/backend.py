@@ -210,12 +210,65 @@ class SpmvPlan:
             pass
 
 
+class TMat:
+    """Template operator (pyn_tmat_*): y = A x of a matrix assembled from one element matrix on a repetitive mesh,
+    without streaming its values.  `asm` is the assembly record (CSR._asm) whose descriptor defines the interior rows, `csr` the
+    matrix whose stored rows serve the boundary-affected nodes (the same object unless e.g. csr = K + Kfs)."""
+
+    def __init__(self, asm, csr):
+        topo, desc, keep = asm
+        self._keep = (topo, desc, keep, csr.indptr, csr.indices, csr.data)
+        self.handle = C.c_void_p()
+        call("pyn_tmat_create", topo._h, C.byref(desc), ptr(csr.indptr), ptr(csr.indices), ptr(csr.data), stream(),
+             C.byref(self.handle))
+        self.bytes = int(_lib.load().pyn_tmat_bytes(self.handle))
+
+    def __del__(self):
+        try:
+            if getattr(self, "handle", None):
+                _lib.load().pyn_tmat_destroy(self.handle)
+                self.handle = None
+        except Exception:
+            pass
+
+
+def templates_eligible(csr):
+    """Can `csr` (as returned by assemble) be applied through row templates?"""
+    a = getattr(csr, "_asm", None)
+    if a is None:
+        return False
+    topo, desc, _ = a
+    return bool(topo.nsig > 0 and desc.E_stride == 0 and desc.bcmap and (desc.pair_mask & 1) and desc.d_E and
+                not (desc.diag_classes & 1))
+
+
 class CSR:
     """Device CSR matrix (int64 row pointers, int32 sorted column indices, FP64 values)."""
 
     def __init__(self, shape, indptr, indices, data, name=""):
         self.shape, self.indptr, self.indices, self.data, self.name = tuple(shape), indptr, indices, data, name
         self._plan = None
+        self._asm = None          # (topology, descriptor, keep-alive refs) when produced by assemble()
+        self._tmat = None         # template operator, built on first use when enabled
+        self._tmat_asm = None     # assembly record the templates come from (own or another matrix's), None = off
+
+    def enable_templates(self, like=None):
+        """Apply this matrix through row templates from now on (products and CG).  `like`: another assembled CSR that
+        equals this matrix on the interior rows and carries the descriptor (e.g. K for K + Kfs).  Returns False --
+        and keeps the CSR stream -- when the matrix is not eligible (per-cell element matrices, irregular mesh)."""
+        src = like if like is not None else self
+        if not templates_eligible(src):
+            return False
+        self._tmat_asm, self._tmat = src._asm, None     # only the record is kept: `like` itself may be freed
+        return True
+
+    def disable_templates(self):
+        self._tmat_asm = self._tmat = None
+
+    def tmat(self):
+        if self._tmat is None and self._tmat_asm is not None:
+            self._tmat = TMat(self._tmat_asm, self)
+        return self._tmat
 
     def plan(self):
         """SpMV plan of this sparsity pattern (pyn_spmv_plan_create), built on first use and shared between the
@@ -234,7 +287,10 @@ class CSR:
         yd = y.data if hasattr(y, "data") and not isinstance(y, torch.Tensor) else y
         ad = aux.data if (aux is not None and not isinstance(aux, torch.Tensor)) else aux
         assert xd.numel() == self.shape[1] and yd.numel() == self.shape[0]
-        if planned:
+        tm = self.tmat() if planned else None
+        if tm is not None:
+            call("pyn_tmat_mult", tm.handle, ptr(xd), ptr(yd), mode, float(p0), float(p1), ptr(ad), stream())
+        elif planned:
             call("pyn_spmv_planned", self.plan(), ptr(self.indices), ptr(self.data), ptr(xd), ptr(yd), mode,
                  float(p0), float(p1), ptr(ad), stream())
         else:       # plan-less CSR-vector kernel (one-off products)
@@ -289,8 +345,12 @@ class CSR:
         ip, ix, dv = self.getValuesCSR()
         return PETSc.Mat().createAIJ(size=self.shape, csr=(ip, ix, dv))
 
-    def bytes_spmv(self):
-        """algorithmic HBM bytes of one y = A x: 12 nnz + 8 (rows+1) + 8 rows + 8 cols."""
+    def bytes_spmv(self, templates=None):
+        """algorithmic HBM bytes of one y = A x.  CSR stream (SURVEY 8d): 12 nnz + 8 (rows+1) + 8 rows + 8 cols;
+        template operator: 4 per adjacency slot + 8 per node + the vectors."""
+        tm = self.tmat() if (templates is None or templates) else None
+        if tm is not None and templates is not False:
+            return tm.bytes
         return 12 * self.nnz + 8 * (self.shape[0] + 1) + 8 * self.shape[0] + 8 * self.shape[1]
 
 
@@ -331,14 +391,23 @@ def assemble(topo, rdof, cdof, E, rclass=None, cclass=None, pairs=ALL_PAIRS, dia
         fill_idx = indices
     else:
         indptr, indices, fill_idx = pattern.indptr, pattern.indices, None
+    keep = (E, rclass, cclass, rowscale, bcmap)
     if inplace and pattern is not None and pattern.data is not None:
         call("pyn_asm_fill", topo._h, C.byref(d), ptr(indptr), None, ptr(pattern.data), stream())
+        own = pattern._tmat_asm is pattern._asm
+        pattern._asm = (topo, d, keep)
+        if own:
+            pattern._tmat_asm = pattern._asm
+        pattern._tmat = None          # templates (if enabled) are rebuilt from the new element matrix on next use
         return pattern
     data = empty(indices.numel()) if values else None
     call("pyn_asm_fill", topo._h, C.byref(d), ptr(indptr), ptr(fill_idx), ptr(data), stream())
     out = CSR((nrows, ncols), indptr, indices, data, name)
+    out._asm = (topo, d, keep)
     if pattern is not None:
         out._plan = pattern._plan
+        if pattern._tmat_asm is not None and pattern._tmat_asm is pattern._asm:
+            out._tmat_asm = out._asm
     return out
 
 
@@ -379,6 +448,9 @@ class Ksp:
         call("pyn_ksp_create", A.shape[0], ptr(A.indptr), ptr(A.indices), ptr(A.data), A.nnz, C.byref(o), stream(),
              C.byref(self._h))
         self.its, self.reason, self.rnorm0, self.rnorm = 0, 0, 0.0, 0.0
+        self._tm = A.tmat() if ksp_type == "cg" else None      # template operator for w = A p when enabled on A
+        if self._tm is not None:
+            call("pyn_ksp_set_tmat", self._h, self._tm.handle)
 
     def solve(self, b, x):
         r = KspResult()

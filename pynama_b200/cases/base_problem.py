@@ -299,7 +299,11 @@ class NoSlipFreeSlip(BaseProblem):
     def setUpSolver(self):
         super().setUpSolver()
         self.solverFS = KspSolver()
-        self.solverFS.createSolver(self.mat.K + self.mat.Kfs, self.comm)
+        KFS = self.mat.K + self.mat.Kfs
+        # Kfs only touches boundary-affected rows, so K + Kfs keeps K's row templates on the interior
+        if self.mat.K.csr._tmat_asm is not None:
+            KFS.csr.enable_templates(like=self.mat.K.csr)
+        self.solverFS.createSolver(KFS, self.comm)
         self.velFS = self.vel.copy()
         self._vortFS = self.vort.duplicate()
 

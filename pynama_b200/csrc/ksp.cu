@@ -112,6 +112,50 @@ cg_spmv_dot_kernel(pyn::SpmvPlanView P, const int* __restrict__ ind, const doubl
   if (threadIdx.x == 0) B.part_a[blockIdx.x] = dot;
 }
 
+// the same product through the template operator (tmat.cuh): interior nodes by row templates, flagged rows by CSR
+template <int RD, int CD>
+__global__ void __launch_bounds__(256)
+cg_tmat_interior_kernel(pyn::TmatView m, CgBuffers B, int part_off) {
+  __shared__ double red[256 / 32];
+  if (B.st->done) return;
+  const int lane = threadIdx.x & 31;
+  const int64_t w0 = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5, nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  double dot = 0.0;
+  for (int64_t r = w0; r < m.nnodes; r += nw) {
+    if (m.flags[r]) continue;
+    double acc[RD];
+    pyn::tmat_node<RD, CD>(m, r, lane, B.p, acc);
+    if (lane == 0) {
+#pragma unroll
+      for (int a = 0; a < RD; ++a) {
+        B.w[r * RD + a] = acc[a];
+        dot += B.p[r * RD + a] * acc[a];
+      }
+    }
+  }
+  dot = pyn::block_sum<256>(dot, red);
+  if (threadIdx.x == 0) B.part_a[part_off + blockIdx.x] = dot;
+}
+__global__ void __launch_bounds__(256)
+cg_tmat_boundary_kernel(pyn::TmatView m, int rd, CgBuffers B) {
+  __shared__ double red[256 / 32];
+  if (B.st->done) return;
+  const int lane = threadIdx.x & 31;
+  const int64_t w0 = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5, nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  const int64_t nrows = m.nlist * rd;
+  double dot = 0.0;
+  for (int64_t i = w0; i < nrows; i += nw) {
+    const int64_t row = (int64_t)m.list[i / rd] * rd + (i % rd);
+    const double s = pyn::spmv_row<32>(m.ptr, m.ind, m.val, B.p, row, true, lane);
+    if (lane == 0) {
+      B.w[row] = s;
+      dot += B.p[row] * s;
+    }
+  }
+  dot = pyn::block_sum<256>(dot, red);
+  if (threadIdx.x == 0) B.part_a[blockIdx.x] = dot;
+}
+
 // a = beta / (p.w) ; x += a p ; r -= a w ; z = M^-1 r ; partials of z.z, z.r   (input partials: nparts_in of p.w)
 __global__ void cg_update_kernel(int64_t n, int nparts_in, CgBuffers B, double* __restrict__ out_a,
                                  double* __restrict__ out_b, const double* __restrict__ g) {
@@ -197,19 +241,30 @@ int enqueue_cg_iteration(const pyn_ksp* k, cudaStream_t st) {
     int rc = pyn::halo_exchange(k->halo, k->B.p, k->halo_comp, st);
     if (rc) return rc;
   }
-  cg_spmv_dot_kernel<<<k->sgrid, pyn::SP_BLK, 0, st>>>(pyn::view_of(k->plan), k->ind, k->val, k->B);
+  int npw = k->sgrid;   // number of per-CTA partials of p.w
+  if (k->tmat) {
+    const pyn::TmatView tv = pyn::view_of(k->tmat);
+    const int gb = k->tmat->nlist > 0 ? k->tmat->grid_bnd : 0, gi = k->tmat->grid_int;
+    if (gb) cg_tmat_boundary_kernel<<<gb, 256, 0, st>>>(tv, k->tmat->rdof, k->B);
+    if (k->tmat->rdof == 2) cg_tmat_interior_kernel<2, 2><<<gi, 256, 0, st>>>(tv, k->B, gb);
+    else if (k->tmat->rdof == 1) cg_tmat_interior_kernel<1, 1><<<gi, 256, 0, st>>>(tv, k->B, gb);
+    else cg_tmat_interior_kernel<3, 3><<<gi, 256, 0, st>>>(tv, k->B, gb);
+    npw = gb + gi;
+  } else {
+    cg_spmv_dot_kernel<<<k->sgrid, pyn::SP_BLK, 0, st>>>(pyn::view_of(k->plan), k->ind, k->val, k->B);
+  }
   if (dist) {
-    cg_reduce_kernel<<<1, 32, 0, st>>>(k->sgrid, k->B.part_a, nullptr, k->gsum);
+    cg_reduce_kernel<<<1, 32, 0, st>>>(npw, k->B.part_a, nullptr, k->gsum);
     int rc = pyn::comm_allreduce_sum(k->comm, k->gsum, 1, st);
     if (rc) return rc;
   }
-  cg_update_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, k->sgrid, k->B, k->pzz, k->pzr, g);
+  cg_update_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, npw, k->B, k->pzz, k->pzr, g);
   if (dist) {
     cg_reduce_kernel<<<1, 32, 0, st>>>(k->vgrid, k->pzz, k->pzr, k->gsum + 1);
     int rc = pyn::comm_allreduce_sum(k->comm, k->gsum + 1, 2, st);
     if (rc) return rc;
   }
-  cg_scalar_kernel<<<1, 32, 0, st>>>(k->sgrid, k->vgrid, k->B, k->pzz, k->pzr, k->opts.atol, k->opts.dtol,
+  cg_scalar_kernel<<<1, 32, 0, st>>>(npw, k->vgrid, k->B, k->pzz, k->pzr, k->opts.atol, k->opts.dtol,
                                      k->opts.max_it, g);
   return PYN_OK;
 }
@@ -239,7 +294,8 @@ int pyn_ksp_create(int64_t nrows, const int64_t* d_ptr, const int32_t* d_ind, co
     k->sgrid = (int)(k->plan->nblk < cap ? k->plan->nblk : cap);
   }
   double* pool = nullptr;
-  const size_t nparts = (size_t)(k->vgrid > k->sgrid ? k->vgrid : k->sgrid);
+  size_t nparts = (size_t)(k->vgrid > k->sgrid ? k->vgrid : k->sgrid);
+  if (nparts < (size_t)pyn::sm_count() * 10) nparts = (size_t)pyn::sm_count() * 10;   // room for the template operator's grids
   PYN_CHECK_CUDA(cudaMalloc(&pool, sizeof(double) * (6 * (size_t)nrows + 4 * nparts)));
   k->B.r = pool; k->B.z = pool + nrows; k->B.p = pool + 2 * nrows; k->B.w = pool + 3 * nrows;
   k->B.x = pool + 4 * nrows; k->B.dinv = pool + 5 * nrows;
@@ -334,6 +390,17 @@ int pyn_ksp_set_dist(pyn_ksp* k, const pyn_comm* comm, const pyn_halo* halo, int
   k->comm = comm; k->halo = halo; k->halo_comp = ncomp; k->owned = d_owned_rows;
   if (!k->gsum) PYN_CHECK_CUDA(cudaMalloc(&k->gsum, 4 * sizeof(double)));
   if (k->graph) { cudaGraphExecDestroy(k->graph); k->graph = nullptr; }  // re-capture with the collectives
+  return PYN_OK;
+}
+
+int pyn_ksp_set_tmat(pyn_ksp* k, const pyn_tmat* m) {
+  PYN_REQUIRE(k, "ksp is NULL");
+  if (m) {
+    PYN_REQUIRE(m->rdof == m->cdof && m->topo->nnodes * m->rdof == k->n, "template operator does not match the system");
+    PYN_REQUIRE(k->opts.type == 0, "the template operator is wired into CG only");
+  }
+  k->tmat = m;
+  if (k->graph) { cudaGraphExecDestroy(k->graph); k->graph = nullptr; }
   return PYN_OK;
 }
 

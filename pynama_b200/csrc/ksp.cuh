@@ -2,6 +2,7 @@
 #pragma once
 #include "dist.cuh"
 #include "spmv.cuh"
+#include "tmat.cuh"
 
 struct KspState {
   double beta, betaold, dp, rnorm0, ttol;
@@ -35,6 +36,7 @@ struct pyn_ksp {
   const uint8_t* owned;
   double* gsum;  // [p.w, z.z, z.r]
   struct pyn_gmres* gm;  // GMRES work space (lazy)
+  const pyn_tmat* tmat;  // template operator used for w = A p instead of the CSR stream (pyn_ksp_set_tmat)
 };
 
 struct pyn_gmres;

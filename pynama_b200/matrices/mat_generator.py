@@ -38,6 +38,13 @@ def rowClasses(dom, colClasses, ncomp):
     return np.where(own, base, NOT_OWNED).astype(np.int8)
 
 
+def templatesWanted():
+    """`-mat_templates 0` keeps every product on the CSR stream; default: row templates wherever a matrix is eligible
+    (one element matrix for all cells on a repetitive mesh -- csrc/tmat.cuh)."""
+    from ..common.options import Options
+    return str(Options().getString("mat_templates", "1")).lower() not in ("0", "false", "no", "off")
+
+
 def _rank(comm):
     return getattr(comm, "rank", 0)
 
@@ -116,6 +123,8 @@ class Mat(object):
         m = getattr(self, name)
         m.csr, m.shape = csr, csr.shape
         csr.name = name
+        if templatesWanted():
+            csr.enable_templates()
 
     def assembleFromMesh(self, dom, elemType, perCell=True):
         """FreeSlip.buildKLEMats (src/cases/base_problem.py:499-552) for the whole mesh on the device: element
@@ -215,6 +224,10 @@ class Operators(Mat):
             bmap = be.BcMap(topo, rc, rd)
             full = be.assemble(topo, rd, cd, E, rclass=rc, pairs=[(FREE, FREE)], rowscale=rW, bcmap=bmap, name=name)
             small = full.compressed(name)
+            if templatesWanted():
+                # interior rows through the row templates of the full block (4 B per adjacency slot); the squeezed
+                # CSR only serves the rows of flagged (ghost) nodes, where both matrices agree
+                small.enable_templates(like=full)
             self.spmv[name] = DeviceMat.fromCSR(small, name)
             m = getattr(self, name)
             m.csr, m.shape = (small if compressed else full), full.shape

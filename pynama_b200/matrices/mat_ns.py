@@ -16,7 +16,7 @@ post-assembly loops; the assembly kernel evaluates it for the whole mesh in one 
 import numpy as np
 
 from .. import backend as be
-from .mat_generator import FREE, SET, TANGENT, Mat, rowClasses
+from .mat_generator import FREE, SET, TANGENT, Mat, rowClasses, templatesWanted
 
 # name: (cdof, element matrix, kept (row class, column class) pairs, classes whose diagonal entry is stored,
 #        value added on that diagonal per class, sign)
@@ -114,4 +114,6 @@ class MatNS(Mat):
                               diag_add=dadd, sign=sign, pattern=m.csr, inplace=True, name=name,
                               bcmap=self._maps[0] if cd == 2 else self._maps[1])
             m.csr, m.shape = csr, csr.shape
+            if templatesWanted():
+                csr.enable_templates()
         self._unit_diagonals_folded = True
