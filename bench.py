@@ -362,50 +362,78 @@ def ksp_phase(a, prob, be, torch, peak, barrier):
     Rw.mult(vort, rhs)
     Krhs.mult(vel, rhs, mode=1)
     its = a.ksp_its
-    ksp = be.Ksp(K, "cg", "jacobi", rtol=1e-300, atol=1e-300, max_it=its, check_every=its)
-    if dc is not None:
-        dc.attach(ksp, 2)
     x = be.empty(2 * N)
+    y = be.empty(2 * N)
     ev = lambda: torch.cuda.Event(enable_timing=True)
-    ksp.solve(rhs, x)                       # warm-up: graph capture + one full budget
-    ksp.solve(rhs, x)
-    barrier()
-    reps, ms = 3, []
-    for _ in range(reps):
+
+    def time_cg():
+        ksp = be.Ksp(K, "cg", "jacobi", rtol=1e-300, atol=1e-300, max_it=its, check_every=its)
+        if dc is not None:
+            dc.attach(ksp, 2)
+        ksp.solve(rhs, x)                       # warm-up: graph capture + one full budget
+        ksp.solve(rhs, x)
         barrier()
+        ms = []
+        for _ in range(3):
+            barrier()
+            s, e = ev(), ev()
+            s.record()
+            r = ksp.solve(rhs, x)
+            e.record()
+            torch.cuda.synchronize()
+            ms.append(s.elapsed_time(e))
+        del ksp
+        return min(ms), r
+
+    def time_mult():
+        for _ in range(3):
+            K.mult(x, y)
         s, e = ev(), ev()
         s.record()
-        r = ksp.solve(rhs, x)
+        nrep = 10
+        for _ in range(nrep):
+            K.mult(x, y)
         e.record()
         torch.cuda.synchronize()
-        ms.append(s.elapsed_time(e))
-    ms_solve = min(ms)
-    # one SpMV alone (same kernel family as inside CG) for the roofline line
-    y = be.empty(2 * N)
-    for _ in range(3):
-        K.mult(x, y)
-    s, e = ev(), ev()
-    s.record()
-    nrep = 10
-    for _ in range(nrep):
-        K.mult(x, y)
-    e.record()
-    torch.cuda.synchronize()
-    ms_spmv = s.elapsed_time(e) / nrep
-    spmv_bytes = K.bytes_spmv()
-    it_bytes = spmv_bytes + 8 * K.shape[0] * 12      # + ~12 vector passes per PCG iteration
-    out = {"type": "cg", "pc": "jacobi", "its": int(r.its), "reason": int(r.reason), "ms_per_solve": ms_solve,
-           "ms_per_iteration": ms_solve / max(r.its, 1), "rows": K.shape[0], "nnz": K.nnz,
-           "iteration_gbs": it_bytes / (ms_solve / max(r.its, 1) * 1e-3) / 1e9,
-           "iteration_frac_of_peak": it_bytes / (ms_solve / max(r.its, 1) * 1e-3) / 1e9 / peak,
-           "spmv": {"ms": ms_spmv, "bytes": spmv_bytes, "achieved": spmv_bytes / (ms_spmv * 1e-3) / 1e9,
-                    "peak": peak, "unit": "GB/s", "frac": spmv_bytes / (ms_spmv * 1e-3) / 1e9 / peak,
-                    "traffic": load_traffic("spmv_kernel")},
+        return s.elapsed_time(e) / nrep
+
+    def leg(kernel, traffic_key):
+        """one operator variant: CG with the fixed budget + the bare product y = K x, against the HBM roofline"""
+        ms_solve, r = time_cg()
+        ms_mult = time_mult()
+        nbytes = K.bytes_spmv()
+        it_bytes = nbytes + 8 * K.shape[0] * 12      # + ~12 vector passes per PCG iteration (SURVEY 8d)
+        ms_it = ms_solve / max(r.its, 1)
+        return r, {"kernel": kernel, "ms_per_solve": ms_solve, "ms_per_iteration": ms_it,
+                   "iteration_bytes": it_bytes, "iteration_gbs": it_bytes / (ms_it * 1e-3) / 1e9,
+                   "iteration_frac_of_peak": it_bytes / (ms_it * 1e-3) / 1e9 / peak,
+                   "spmv": {"ms": ms_mult, "bytes": nbytes, "achieved": nbytes / (ms_mult * 1e-3) / 1e9, "peak": peak,
+                            "unit": "GB/s", "frac": nbytes / (ms_mult * 1e-3) / 1e9 / peak,
+                            "traffic": load_traffic(traffic_key)}}
+
+    # (1) the assembled CSR streamed from HBM: the north_star's "vectorised, coalesced CSR SpMV"
+    saved = K._tmat_asm
+    K.disable_templates()
+    r, csr_leg = leg("cg_spmv_dot_kernel / spmv_stream_kernel (CSR stream, 12 B per stored entry)", "spmv_kernel")
+    # (2) the element operator the case classes use on uniform meshes (csrc/tmat.cuh): same operator, matrix-free
+    eop_leg = None
+    if saved is not None or K.enable_templates():
+        if saved is not None:
+            K._tmat_asm = saved
+        r, eop_leg = leg("eop_apply_kernel + cg_tmat_interior_kernel (element operator: element products with the "
+                         "element matrix in shared memory + per-node gather)", "eop_kernel")
+    best = eop_leg or csr_leg
+    out = {"type": "cg", "pc": "jacobi", "its": int(r.its), "reason": int(r.reason),
+           "ms_per_solve": best["ms_per_solve"], "ms_per_iteration": best["ms_per_iteration"],
+           "rows": K.shape[0], "nnz": K.nnz, "operator": "element operator" if eop_leg else "csr stream",
+           "iteration_gbs": csr_leg["iteration_gbs"], "iteration_frac_of_peak": csr_leg["iteration_frac_of_peak"],
+           "spmv": csr_leg["spmv"], "csr_stream": csr_leg, "element_operator": eop_leg,
            "note": f"fixed budget of {its} iterations (-ksp_max_it {its}); rows/nnz/GB/s are rank 0's strip; a converged "
-                   f"Jacobi-CG solve at this size needs O(10^4) iterations (SURVEY 7.2)"}
+                   f"Jacobi-CG solve at this size needs O(10^4) iterations (SURVEY 7.2).  ms_per_solve / "
+                   f"ms_per_iteration are the default path of the case classes (`operator`); spmv / iteration_gbs "
+                   f"are the CSR-stream leg (HBM-bound kernel the roofline applies to)"}
     if dc is not None:
         out["halo_bytes_per_iteration"] = dc.halo_bytes(2)
-    del ksp
     return out
 
 

@@ -189,12 +189,15 @@ int pyn_spmv_plan_destroy(pyn_spmv_plan* plan);
 int pyn_spmv_planned(const pyn_spmv_plan* plan, const int32_t* d_ind, const double* d_val, const double* d_x,
                      double* d_y, int mode, double p0, double p1, const double* d_aux, void* stream);
 
-/* Template operator (uniform meshes): the same y = A x without streaming the matrix values.  Built from the
- * descriptor a matrix was assembled with (one element matrix for all cells, boundary map, row signatures available)
- * plus the assembled CSR, whose rows are used for the boundary-affected nodes only; interior nodes multiply with their
- * row template through the node adjacency: 4 B of HBM per adjacency slot instead of 12 B per stored entry.  The CSR
- * may be any matrix that equals the descriptor's matrix on the interior rows (e.g. K + Kfs for K).  All arrays are
- * borrowed.  Same modes as pyn_spmv. */
+/* Element ("template") operator for uniform meshes: the same y = A x without streaming the matrix values -- the
+ * matrix-free form of MatMult on the matrices of base_problem.py:329-454,499-552 / mat_generator.py:157-190.  Built
+ * from the descriptor a matrix was assembled with (ONE element matrix for all cells, boundary map) plus the assembled
+ * CSR, whose rows serve the boundary-affected nodes only.  Interior nodes: phase 1 multiplies the element matrix
+ * (resident in shared memory) with the gathered dofs of every element, phase 2 sums the element results per node in
+ * ascending cell order (deterministic, no atomics).  The CSR may be any matrix that equals the descriptor's matrix on
+ * the interior rows (e.g. K + Kfs for K).  The descriptor's element matrix is copied, everything else is borrowed.
+ * Same modes as pyn_spmv.  pyn_tmat_supported: 1 when an element matrix of rdof*nn x cdof*nn fits the kernel's shared
+ * memory budget (ngl <= 7 for K), else the caller keeps the CSR stream. */
 typedef struct pyn_tmat pyn_tmat;
 int pyn_tmat_create(const pyn_topo* t, const pyn_asm_desc* desc, const int64_t* d_indptr, const int32_t* d_indices,
                     const double* d_data, void* stream, pyn_tmat** out);
@@ -202,6 +205,7 @@ int pyn_tmat_destroy(pyn_tmat* m);
 int pyn_tmat_mult(const pyn_tmat* m, const double* d_x, double* d_y, int mode, double p0, double p1, const double* d_aux,
                   void* stream);
 int64_t pyn_tmat_bytes(const pyn_tmat* m);
+int pyn_tmat_supported(int nn, int rdof, int cdof);
 
 /* ------------------------------------------------------------------------------------------------------
  * Vectors (PETSc Vec calls of the path: base_problem.py:222-230,234-252; cavity.py:53-81; custom_func.py:76-83)

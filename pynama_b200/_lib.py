@@ -104,6 +104,7 @@ _SIGNATURES = {
     "pyn_tmat_destroy": (C.c_int, [c_vp]),
     "pyn_tmat_mult": (C.c_int, [c_vp, c_vp, c_vp, C.c_int, c_f64, c_f64, c_vp, c_vp]),
     "pyn_tmat_bytes": (c_i64, [c_vp]),
+    "pyn_tmat_supported": (C.c_int, [C.c_int, C.c_int, C.c_int]),
     "pyn_ksp_set_tmat": (C.c_int, [c_vp, c_vp]),
     "pyn_ksp_set_dist": (C.c_int, [c_vp, c_vp, c_vp, C.c_int, c_vp]),
 }

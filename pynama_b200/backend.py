@@ -211,8 +211,8 @@ class SpmvPlan:
 
 
 class TMat:
-    """Template operator (pyn_tmat_*): y = A x of a matrix assembled from one element matrix on a repetitive mesh,
-    without streaming its values.  `asm` is the assembly record (CSR._asm) whose descriptor defines the interior rows, `csr` the
+    """Element ("template") operator (pyn_tmat_*): y = A x of a matrix assembled from one element matrix on a
+    repetitive mesh, matrix-free (element products + per-node gather), without streaming its values.  `asm` is the assembly record (CSR._asm) whose descriptor defines the interior rows, `csr` the
     matrix whose stored rows serve the boundary-affected nodes (the same object unless e.g. csr = K + Kfs)."""
 
     def __init__(self, asm, csr):
@@ -232,14 +232,19 @@ class TMat:
             pass
 
 
+def tmat_supported(nn, rdof, cdof):
+    """Does an element matrix of rdof*nn x cdof*nn fit the element operator's shared-memory budget?"""
+    return bool(_lib.load().pyn_tmat_supported(int(nn), int(rdof), int(cdof)))
+
+
 def templates_eligible(csr):
     """Can `csr` (as returned by assemble) be applied through row templates?"""
     a = getattr(csr, "_asm", None)
     if a is None:
         return False
     topo, desc, _ = a
-    return bool(topo.nsig > 0 and desc.E_stride == 0 and desc.bcmap and (desc.pair_mask & 1) and desc.d_E and
-                not (desc.diag_classes & 1))
+    return bool(desc.E_stride == 0 and desc.bcmap and (desc.pair_mask & 1) and desc.d_E and
+                not (desc.diag_classes & 1) and _lib.load().pyn_tmat_supported(topo.nn, desc.rdof, desc.cdof))
 
 
 class CSR:
@@ -347,7 +352,7 @@ class CSR:
 
     def bytes_spmv(self, templates=None):
         """algorithmic HBM bytes of one y = A x.  CSR stream (SURVEY 8d): 12 nnz + 8 (rows+1) + 8 rows + 8 cols;
-        template operator: 4 per adjacency slot + 8 per node + the vectors."""
+        element operator: see pyn_tmat_bytes (x, connectivity, element results written + read, y)."""
         tm = self.tmat() if (templates is None or templates) else None
         if tm is not None and templates is not False:
             return tm.bytes

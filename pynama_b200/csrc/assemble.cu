@@ -331,19 +331,6 @@ asm_stream_kernel(pyn::TopoView t, DescView d, const int64_t* __restrict__ indpt
   }
 }
 
-// [sig][a][p][b] (assembly layout: rows contiguous) -> [sig][p][a][b] (operator layout: one block per adjacency slot)
-__global__ void tmat_layout_kernel(pyn::TopoView t, int rd, int cd, const double* __restrict__ src,
-                                   double* __restrict__ dst) {
-  for (int s = blockIdx.x; s < t.nsig; s += gridDim.x) {
-    const int64_t o = t.sig_ptr[s] * rd * cd;
-    const int L = (int)(t.sig_ptr[s + 1] - t.sig_ptr[s]);
-    for (int i = threadIdx.x; i < L * rd * cd; i += blockDim.x) {
-      const int b = i % cd, a = (i / cd) % rd, p = i / (cd * rd);
-      dst[o + i] = src[o + (a * L + p) * cd + b];
-    }
-  }
-}
-
 // row lengths of the interior nodes: L*cdof when the (free,free) pair is kept, else 0
 __global__ void asm_interior_count_kernel(pyn::TopoView t, const uint8_t* __restrict__ flags, int rdof, int cdof,
                                           int keep00, int* __restrict__ rowcnt) {
@@ -706,41 +693,18 @@ int pyn_tmat_create(const pyn_topo* t, const pyn_asm_desc* desc, const int64_t* 
   DescView dv;
   int rc = make_desc(desc, &dv);
   if (rc) return rc;
-  PYN_REQUIRE(t->nsig > 0, "template operator: the topology has no row signatures (irregular mesh)");
-  PYN_REQUIRE(dv.E && dv.E_stride == 0, "template operator: needs ONE element matrix for all cells (E_stride == 0)");
-  PYN_REQUIRE(use_map(desc) && (dv.pair_mask & 1u), "template operator: needs a boundary map and the (free,free) pair");
+  PYN_REQUIRE(dv.E && dv.E_stride == 0, "element operator: needs ONE element matrix for all cells (E_stride == 0)");
+  PYN_REQUIRE(use_map(desc) && (dv.pair_mask & 1u), "element operator: needs a boundary map and the (free,free) pair");
+  PYN_REQUIRE(!(dv.diag_classes & 1u), "element operator: a diagonal rule on free dofs is not supported");
   PYN_REQUIRE(desc->bcmap->nnodes == t->nnodes, "bcmap belongs to another topology");
-  cudaStream_t st = pyn::as_stream(stream);
+  PYN_REQUIRE(pyn_tmat_supported(t->nn, dv.rdof, dv.cdof), "element operator: element matrix too large for shared memory");
   pyn_tmat* m = new pyn_tmat();
   memset(m, 0, sizeof(*m));
   m->topo = t; m->rdof = dv.rdof; m->cdof = dv.cdof;
   m->flags = desc->bcmap->flags; m->list = desc->bcmap->list; m->nlist = desc->bcmap->nlist;
   m->rowscale = dv.rowscale; m->ptr = d_indptr; m->ind = d_indices; m->val = d_data;
-  const size_t len = (size_t)t->sig_slots * dv.rdof * dv.cdof;
-  double* tmp = nullptr;
-  PYN_CHECK_CUDA(cudaMalloc(&m->T, sizeof(double) * len));
-  PYN_CHECK_CUDA(cudaMalloc(&tmp, sizeof(double) * len));
-  const pyn::TopoView tv = pyn::view_of(t);
-  const int tgrid = (t->nsig + 3) / 4;
-  bool done = false;
-#define PYN_ASM_CASE(R, C)                                                   \
-  if (!done && dv.rdof == R && dv.cdof == C) {                               \
-    asm_template_kernel<R, C><<<tgrid, 128, 0, st>>>(tv, dv, tmp);           \
-    done = true;                                                             \
-  }
-  PYN_ASM_CASE(2, 2) PYN_ASM_CASE(2, 1) PYN_ASM_CASE(1, 2) PYN_ASM_CASE(3, 2) PYN_ASM_CASE(2, 3)
-  PYN_ASM_CASE(1, 1) PYN_ASM_CASE(3, 3) PYN_ASM_CASE(1, 3) PYN_ASM_CASE(3, 1)
-#undef PYN_ASM_CASE
-  pyn::count_launch();
-  tmat_layout_kernel<<<t->nsig, 128, 0, st>>>(tv, dv.rdof, dv.cdof, tmp, m->T);
-  PYN_CHECK_LAUNCH();
-  PYN_CHECK_CUDA(cudaStreamSynchronize(st));
-  cudaFree(tmp);
-  // persistent grids: one warp per node / per flagged row
-  const int64_t need_i = (t->nnodes * 32 + 255) / 256, need_b = (m->nlist * dv.rdof * 32 + 255) / 256;
-  const int64_t cap_i = (int64_t)pyn::sm_count() * 8, cap_b = (int64_t)pyn::sm_count() * 2;
-  m->grid_int = (int)(need_i < cap_i ? need_i : cap_i);
-  m->grid_bnd = (int)(need_b < cap_b ? (need_b > 0 ? need_b : 1) : cap_b);
+  rc = pyn::tmat_init(m, dv.E, dv.sign, pyn::as_stream(stream));
+  if (rc) { pyn_tmat_destroy(m); return rc; }
   *out = m;
   return PYN_OK;
 }

@@ -112,25 +112,22 @@ cg_spmv_dot_kernel(pyn::SpmvPlanView P, const int* __restrict__ ind, const doubl
   if (threadIdx.x == 0) B.part_a[blockIdx.x] = dot;
 }
 
-// the same product through the template operator (tmat.cuh): interior nodes by row templates, flagged rows by CSR
-template <int RD, int CD>
+// the same product through the element operator (tmat.cuh): phase 1 is pyn::tmat_apply on p; here phase 2 (gather
+// per un-flagged node, one thread each) and the flagged rows from the CSR, both with the p.w partials fused
+template <int RD>
 __global__ void __launch_bounds__(256)
 cg_tmat_interior_kernel(pyn::TmatView m, CgBuffers B, int part_off) {
   __shared__ double red[256 / 32];
   if (B.st->done) return;
-  const int lane = threadIdx.x & 31;
-  const int64_t w0 = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5, nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
   double dot = 0.0;
-  for (int64_t r = w0; r < m.nnodes; r += nw) {
+  for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < m.nnodes; r += (int64_t)gridDim.x * blockDim.x) {
     if (m.flags[r]) continue;
     double acc[RD];
-    pyn::tmat_node<RD, CD>(m, r, lane, B.p, acc);
-    if (lane == 0) {
+    pyn::eop_gather_node<RD>(m, r, acc);
 #pragma unroll
-      for (int a = 0; a < RD; ++a) {
-        B.w[r * RD + a] = acc[a];
-        dot += B.p[r * RD + a] * acc[a];
-      }
+    for (int a = 0; a < RD; ++a) {
+      B.w[r * RD + a] = acc[a];
+      dot += B.p[r * RD + a] * acc[a];
     }
   }
   dot = pyn::block_sum<256>(dot, red);
@@ -245,10 +242,12 @@ int enqueue_cg_iteration(const pyn_ksp* k, cudaStream_t st) {
   if (k->tmat) {
     const pyn::TmatView tv = pyn::view_of(k->tmat);
     const int gb = k->tmat->nlist > 0 ? k->tmat->grid_bnd : 0, gi = k->tmat->grid_int;
+    int rc = pyn::tmat_apply(k->tmat, k->B.p, &k->B.st->done, st);
+    if (rc) return rc;
     if (gb) cg_tmat_boundary_kernel<<<gb, 256, 0, st>>>(tv, k->tmat->rdof, k->B);
-    if (k->tmat->rdof == 2) cg_tmat_interior_kernel<2, 2><<<gi, 256, 0, st>>>(tv, k->B, gb);
-    else if (k->tmat->rdof == 1) cg_tmat_interior_kernel<1, 1><<<gi, 256, 0, st>>>(tv, k->B, gb);
-    else cg_tmat_interior_kernel<3, 3><<<gi, 256, 0, st>>>(tv, k->B, gb);
+    if (k->tmat->rdof == 2) cg_tmat_interior_kernel<2><<<gi, 256, 0, st>>>(tv, k->B, gb);
+    else if (k->tmat->rdof == 1) cg_tmat_interior_kernel<1><<<gi, 256, 0, st>>>(tv, k->B, gb);
+    else cg_tmat_interior_kernel<3><<<gi, 256, 0, st>>>(tv, k->B, gb);
     npw = gb + gi;
   } else {
     cg_spmv_dot_kernel<<<k->sgrid, pyn::SP_BLK, 0, st>>>(pyn::view_of(k->plan), k->ind, k->val, k->B);

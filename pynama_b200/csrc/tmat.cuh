@@ -1,7 +1,17 @@
-// Template operator: y = A x for a matrix assembled from ONE element matrix on a repetitive mesh, without streaming
-// its values.  Interior nodes multiply with the row template of their signature (topo.cuh) through the node adjacency
-// -- 4 bytes of HBM per adjacency slot instead of 12 bytes per stored entry --, boundary-affected nodes (the bcmap
-// list) use their rows of the assembled CSR.  Same matrix, same result up to summation order.
+// Element operator ("template operator" of the C ABI, pyn_tmat_*): y = A x for a matrix assembled from ONE element
+// matrix E on a repetitive mesh, WITHOUT streaming its stored values.
+//
+//   phase 1 (eop_apply_kernel, tmat.cu): Ye[e][:] = E . x[dofs(e)] for every element -- a batched dense product
+//            [NR x NC] . [NC x ne] with E resident in shared memory, 128 elements per tile, each thread an 8-row x
+//            4-element register block; HBM traffic = x once + 4 B/element-node of connectivity + Ye written once.
+//   phase 2 (eop_gather_node, below): row node r sums Ye[e][loc_e(r)] over its incident elements in ascending cell
+//            order (the reference's cell loop order, base_problem.py:499-552), scaled by rowscale[r] -- a deterministic
+//            gather, no atomics.
+//   boundary-affected nodes (bcmap list) take their rows from the assembled CSR (one warp per row).
+//
+// Algorithmic HBM bytes per product (K at 1024^2 x ngl 5: 1.6 GB against 29.8 GB of the CSR stream):
+//   8 cols + 4 ne nn + 2 * 8 ne NR + 8 (nnodes+1) + 6 ne nn + 8 rows.
+// Same operator, same result up to summation order (sum over elements of row sums instead of row sum of sums).
 #pragma once
 #include "spmv.cuh"
 #include "topo.cuh"
@@ -9,7 +19,9 @@
 struct pyn_tmat {
   const pyn_topo* topo;      // borrowed
   int rdof, cdof;
-  double* T;                 // [sig_slots][rdof][cdof]: per adjacency slot the block of the template (owned)
+  int NR, NC, NRP;           // element matrix rows / cols, rows padded to a multiple of EO_R
+  double* Et;                // owned: sign * E transposed, [NC][NRP], zero padded
+  double* Ye;                // owned scratch [ne][NR]
   const uint8_t* flags;      // borrowed from the bcmap: 1 = row comes from the CSR
   const int* list;           // flagged nodes
   int64_t nlist;
@@ -17,18 +29,26 @@ struct pyn_tmat {
   const int64_t* ptr;        // assembled CSR (borrowed): used for the flagged rows only
   const int* ind;
   const double* val;
-  int grid_int, grid_bnd;    // persistent grids of the two kernels
+  size_t smem;               // dynamic shared memory of eop_apply_kernel
+  int grid_apply, grid_int, grid_bnd;   // persistent grids: phase 1, phase 2, flagged rows
 };
 
 namespace pyn {
 
+constexpr int EO_THREADS = 128;  // threads per CTA of phase 1
+constexpr int EO_TE = 128;       // elements per tile
+constexpr int EO_R = 8;          // rows per register block
+constexpr int EO_Q = 4;          // elements per register block (per lane)
+
 struct TmatView {
-  int64_t nnodes;
-  const int64_t* adj_ptr;
-  const int* adj_cols;
-  const int* sig_id;
-  const int64_t* sig_ptr;
-  const double* T;
+  int64_t nnodes, ne;
+  int nn, NR, NC, NRP;
+  const int* e2n;
+  const int64_t* n2e_ptr;
+  const int* n2e_elem;
+  const short* n2e_loc;
+  const double* Et;
+  double* Ye;
   const uint8_t* flags;
   const int* list;
   int64_t nlist;
@@ -39,45 +59,42 @@ struct TmatView {
 };
 static inline TmatView view_of(const pyn_tmat* m) {
   TmatView v;
-  v.nnodes = m->topo->nnodes; v.adj_ptr = m->topo->adj_ptr; v.adj_cols = m->topo->adj_cols;
-  v.sig_id = m->topo->sig_id; v.sig_ptr = m->topo->sig_ptr; v.T = m->T; v.flags = m->flags; v.list = m->list;
-  v.nlist = m->nlist; v.rowscale = m->rowscale; v.ptr = m->ptr; v.ind = m->ind; v.val = m->val;
+  v.nnodes = m->topo->nnodes; v.ne = m->topo->ne; v.nn = m->topo->nn; v.NR = m->NR; v.NC = m->NC; v.NRP = m->NRP;
+  v.e2n = m->topo->e2n; v.n2e_ptr = m->topo->n2e_ptr; v.n2e_elem = m->topo->n2e_elem; v.n2e_loc = m->topo->n2e_loc;
+  v.Et = m->Et; v.Ye = m->Ye; v.flags = m->flags; v.list = m->list; v.nlist = m->nlist; v.rowscale = m->rowscale;
+  v.ptr = m->ptr; v.ind = m->ind; v.val = m->val;
   return v;
 }
 
-// One warp computes the RD rows of interior node r; the sums are valid in lane 0.
-template <int RD, int CD>
-__device__ __forceinline__ void tmat_node(const TmatView& m, int64_t r, int lane, const double* __restrict__ x,
-                                          double (&acc)[RD]) {
-  const int64_t a0 = m.adj_ptr[r];
-  const int L = (int)(m.adj_ptr[r + 1] - a0);
-  const double* Ts = m.T + m.sig_ptr[m.sig_id[r]] * (RD * CD);
-  const double rs = m.rowscale ? m.rowscale[r] : 1.0;
+// phase 1 on `st` (defined in tmat.cu); `done` (nullable): device flag, non-zero = skip (CG convergence flag)
+int tmat_apply(const pyn_tmat* m, const double* d_x, const int* d_done, cudaStream_t st);
+// allocations and launch shapes of a handle whose topo / rdof / cdof / bcmap / CSR fields are set (pyn_tmat_create)
+int tmat_init(pyn_tmat* m, const double* d_E, double sign, cudaStream_t st);
+
+// phase 2 for one un-flagged node: acc[a] = rowscale[r] * sum over incident elements (ascending) of Ye[e][loc*RD + a]
+template <int RD>
+__device__ __forceinline__ void eop_gather_node(const TmatView& m, int64_t r, double (&acc)[RD]) {
+  const int64_t b0 = m.n2e_ptr[r], b1 = m.n2e_ptr[r + 1];
 #pragma unroll
   for (int a = 0; a < RD; ++a) acc[a] = 0.0;
-  for (int p = lane; p < L; p += 32) {
-    const int c = ld_stream(m.adj_cols + a0 + p);
-    double xv[CD];
-    if (CD == 2) {
-      const double2 t = *reinterpret_cast<const double2*>(x + (int64_t)c * 2);
-      xv[0] = t.x;
-      xv[CD - 1] = t.y;
+  for (int64_t k = b0; k < b1; ++k) {
+    const int e = ld_stream(m.n2e_elem + k);
+    const int loc = m.n2e_loc[k];
+    const double* p = m.Ye + (int64_t)e * m.NR + loc * RD;
+    if (RD == 2) {
+      const double2 t = *reinterpret_cast<const double2*>(p);   // NR and loc*2 are even
+      acc[0] += t.x;
+      acc[RD - 1] += t.y;
     } else {
 #pragma unroll
-      for (int b = 0; b < CD; ++b) xv[b] = x[(int64_t)c * CD + b];
+      for (int a = 0; a < RD; ++a) acc[a] += p[a];
     }
-    const double* Tb = Ts + p * (RD * CD);
-#pragma unroll
-    for (int a = 0; a < RD; ++a)
-#pragma unroll
-      for (int b = 0; b < CD; ++b) {
-        double tv = __ldg(Tb + a * CD + b);
-        if (m.rowscale) tv = rs * tv;          // the assembled entry is rowscale * template
-        acc[a] += tv * xv[b];
-      }
   }
+  if (m.rowscale) {
+    const double rs = m.rowscale[r];
 #pragma unroll
-  for (int a = 0; a < RD; ++a) acc[a] = warp_sum(acc[a]);
+    for (int a = 0; a < RD; ++a) acc[a] = rs * acc[a];
+  }
 }
 
 }  // namespace pyn
