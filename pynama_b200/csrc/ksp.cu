@@ -116,41 +116,36 @@ cg_spmv_dot_kernel(pyn::SpmvPlanView P, const int* __restrict__ ind, const doubl
 // per un-flagged node, one thread each) and the flagged rows from the CSR, both with the p.w partials fused
 template <int RD>
 __global__ void __launch_bounds__(256)
-cg_tmat_interior_kernel(pyn::TmatView m, CgBuffers B, int part_off) {
+cg_tmat_interior_kernel(pyn::TmatView m, CgBuffers B) {
   __shared__ double red[256 / 32];
   if (B.st->done) return;
   double dot = 0.0;
   for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < m.nnodes; r += (int64_t)gridDim.x * blockDim.x) {
-    if (m.flags[r]) continue;
     double acc[RD];
-    pyn::eop_gather_node<RD>(m, r, acc);
+    if (m.flags[r]) {   // row written by cg_tmat_boundary_kernel (launched before): only its share of p.w is due
 #pragma unroll
-    for (int a = 0; a < RD; ++a) {
-      B.w[r * RD + a] = acc[a];
-      dot += B.p[r * RD + a] * acc[a];
+      for (int a = 0; a < RD; ++a) acc[a] = B.w[r * RD + a];
+    } else {
+      pyn::eop_gather_node<RD>(m, r, acc);
+#pragma unroll
+      for (int a = 0; a < RD; ++a) B.w[r * RD + a] = acc[a];
     }
-  }
-  dot = pyn::block_sum<256>(dot, red);
-  if (threadIdx.x == 0) B.part_a[part_off + blockIdx.x] = dot;
-}
-__global__ void __launch_bounds__(256)
-cg_tmat_boundary_kernel(pyn::TmatView m, int rd, CgBuffers B) {
-  __shared__ double red[256 / 32];
-  if (B.st->done) return;
-  const int lane = threadIdx.x & 31;
-  const int64_t w0 = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5, nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
-  const int64_t nrows = m.nlist * rd;
-  double dot = 0.0;
-  for (int64_t i = w0; i < nrows; i += nw) {
-    const int64_t row = (int64_t)m.list[i / rd] * rd + (i % rd);
-    const double s = pyn::spmv_row<32>(m.ptr, m.ind, m.val, B.p, row, true, lane);
-    if (lane == 0) {
-      B.w[row] = s;
-      dot += B.p[row] * s;
-    }
+#pragma unroll
+    for (int a = 0; a < RD; ++a) dot += B.p[r * RD + a] * acc[a];
   }
   dot = pyn::block_sum<256>(dot, red);
   if (threadIdx.x == 0) B.part_a[blockIdx.x] = dot;
+}
+// flagged rows from the CSR, one warp per row, one row per warp (the list is short: full-width grid, no partials)
+__global__ void __launch_bounds__(256)
+cg_tmat_boundary_kernel(pyn::TmatView m, int rd, CgBuffers B) {
+  if (B.st->done) return;
+  const int lane = threadIdx.x & 31;
+  const int64_t i = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  if (i >= m.nlist * rd) return;
+  const int64_t row = (int64_t)m.list[i / rd] * rd + (i % rd);
+  const double s = pyn::spmv_row<32>(m.ptr, m.ind, m.val, B.p, row, true, lane);
+  if (lane == 0) B.w[row] = s;
 }
 
 // a = beta / (p.w) ; x += a p ; r -= a w ; z = M^-1 r ; partials of z.z, z.r   (input partials: nparts_in of p.w)
@@ -245,10 +240,10 @@ int enqueue_cg_iteration(const pyn_ksp* k, cudaStream_t st) {
     int rc = pyn::tmat_apply(k->tmat, k->B.p, &k->B.st->done, st);
     if (rc) return rc;
     if (gb) cg_tmat_boundary_kernel<<<gb, 256, 0, st>>>(tv, k->tmat->rdof, k->B);
-    if (k->tmat->rdof == 2) cg_tmat_interior_kernel<2><<<gi, 256, 0, st>>>(tv, k->B, gb);
-    else if (k->tmat->rdof == 1) cg_tmat_interior_kernel<1><<<gi, 256, 0, st>>>(tv, k->B, gb);
-    else cg_tmat_interior_kernel<3><<<gi, 256, 0, st>>>(tv, k->B, gb);
-    npw = gb + gi;
+    if (k->tmat->rdof == 2) cg_tmat_interior_kernel<2><<<gi, 256, 0, st>>>(tv, k->B);
+    else if (k->tmat->rdof == 1) cg_tmat_interior_kernel<1><<<gi, 256, 0, st>>>(tv, k->B);
+    else cg_tmat_interior_kernel<3><<<gi, 256, 0, st>>>(tv, k->B);
+    npw = gi;
   } else {
     cg_spmv_dot_kernel<<<k->sgrid, pyn::SP_BLK, 0, st>>>(pyn::view_of(k->plan), k->ind, k->val, k->B);
   }
@@ -294,7 +289,7 @@ int pyn_ksp_create(int64_t nrows, const int64_t* d_ptr, const int32_t* d_ind, co
   }
   double* pool = nullptr;
   size_t nparts = (size_t)(k->vgrid > k->sgrid ? k->vgrid : k->sgrid);
-  if (nparts < (size_t)pyn::sm_count() * 10) nparts = (size_t)pyn::sm_count() * 10;   // room for the template operator's grids
+  if (nparts < (size_t)pyn::sm_count() * 16) nparts = (size_t)pyn::sm_count() * 16;   // room for the template operator's grids
   PYN_CHECK_CUDA(cudaMalloc(&pool, sizeof(double) * (6 * (size_t)nrows + 4 * nparts)));
   k->B.r = pool; k->B.z = pool + nrows; k->B.p = pool + 2 * nrows; k->B.w = pool + 3 * nrows;
   k->B.x = pool + 4 * nrows; k->B.dinv = pool + 5 * nrows;

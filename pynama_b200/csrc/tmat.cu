@@ -1,12 +1,13 @@
 // Element operator kernels (see tmat.cuh): y = A x with fused epilogues, same modes as pyn_spmv.
+#include <stdlib.h>
+
 #include "tmat.cuh"
 
 namespace {
 
 using pyn::EO_Q;
-using pyn::EO_R;
 using pyn::EO_TE;
-using pyn::EO_THREADS;
+constexpr int EO_MAXW = 5;   // warps per CTA of phase 1 (<= 160 threads x 3 CTAs per SM caps the registers at 136)
 
 struct ModeEpi {
   double* y;
@@ -31,97 +32,127 @@ struct ModeEpi {
   }
 };
 
-// E (row major [NR][NC]) -> sign * E^T, rows padded to NRP with zeros
-__global__ void eop_transpose_kernel(int NR, int NC, int NRP, double sign, const double* __restrict__ E,
+// E (row major [NR][NC]) -> sign * E^T as [NCP][NRP], zero padded
+__global__ void eop_transpose_kernel(int NR, int NC, int NRP, int NCP, double sign, const double* __restrict__ E,
                                      double* __restrict__ Et) {
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < NC * NRP; i += gridDim.x * blockDim.x) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < NCP * NRP; i += gridDim.x * blockDim.x) {
     const int k = i / NRP, r = i - k * NRP;
-    Et[i] = (r < NR) ? sign * E[r * NC + k] : 0.0;
+    Et[i] = (r < NR && k < NC) ? sign * E[r * NC + k] : 0.0;
   }
 }
 
 // Phase 1.  Persistent CTAs; E^T stays in shared memory for the life of the CTA.  Per tile of 128 elements:
-//   gather   lane <-> element (conflict-free smem stores), warps split the local nodes; x through the read-only path
-//   compute  work item = 8 rows x (4 elements per lane); per k: 2 LDS.128 of X + 4 broadcast LDS.128 of E^T feed 32 DFMA
-//   store    each thread writes its 8 consecutive rows of 4 elements (64 B runs of the element-major Ye)
-template <int CD>
-__global__ void __launch_bounds__(EO_THREADS)
+//   gather   threads walk the tile's (element, local node) pairs in memory order: connectivity reads are coalesced,
+//            the x loads of neighbouring local nodes fall into the same lines, X lands element-major in shared memory
+//   compute  work item = R rows x 4 elements per lane (elements lane, lane+32, ...); per pair of k: 4 LDS.128 of X +
+//            R broadcast LDS.128 of E^T feed 8R DFMA.  Items are dealt round-robin to the warps; R and the CTA width
+//            are picked per matrix shape so that no warp idles (K at ngl 5: R = 10, 5 warps, 5 items)
+//   store    each thread writes its R consecutive rows of 4 elements (runs of 8R bytes of the element-major Ye)
+template <int CD, int R>
+__global__ void __launch_bounds__(EO_MAXW * 32, 3)
 eop_apply_kernel(pyn::TmatView m, const double* __restrict__ x, const int* __restrict__ done) {
   extern __shared__ __align__(16) double sm[];
   if (done && *done) return;
-  const int NR = m.NR, NC = m.NC, NRP = m.NRP, nn = m.nn;
-  double* Et = sm;                  // [NC][NRP]
-  double* Xs = sm + NC * NRP;       // [NC][EO_TE]
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  for (int i = tid; i < NC * NRP; i += EO_THREADS) Et[i] = m.Et[i];
+  const int NR = m.NR, NC = m.NC, NRP = m.NRP, NCP = m.NCP, nn = m.nn;
+  double* Et = sm;                  // [NCP][NRP]
+  double* Xs = sm + NCP * NRP;      // [EO_TE][NCP]
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nthr = blockDim.x, nwarps = nthr >> 5;
+  for (int i = tid; i < NCP * NRP; i += nthr) Et[i] = m.Et[i];
+  for (int i = tid; i < EO_TE * (NCP - NC); i += nthr) {   // pad columns of X: zero for the life of the CTA
+    const int el = i / (NCP - NC);
+    Xs[el * NCP + NC + (i - el * (NCP - NC))] = 0.0;
+  }
   const int64_t ntiles = (m.ne + EO_TE - 1) / EO_TE;
-  const int nitems = NRP / EO_R;
+  const int nitems = NRP / R;
   const bool vec_store = (NR & 1) == 0;
+  constexpr int U = (CD == 3) ? 12 : 20;
   for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     const int64_t e0 = tile * EO_TE;
+    const int64_t rem = m.ne - e0;
+    const int npairs = (int)(rem < EO_TE ? rem : EO_TE) * nn;
+    const int* en = m.e2n + e0 * nn;
     __syncthreads();   // the previous tile's products are done (and E^T is in place)
-    for (int j = warp; j < nn; j += EO_THREADS / 32) {
+    // U independent connectivity loads, then U independent x loads, then the shared-memory stores: two memory round
+    // trips per batch instead of two per pair (the gather is latency-bound; the accumulators are not live here)
+    for (int base = tid; base < EO_TE * nn; base += U * nthr) {
+      int nd[U];
 #pragma unroll
-      for (int q = 0; q < EO_TE / 32; ++q) {
-        const int el = q * 32 + lane;
-        const int64_t e = e0 + el;
-        double v[CD];
+      for (int u = 0; u < U; ++u) {
+        const int i = base + u * nthr;
+        nd[u] = (i < npairs) ? pyn::ld_stream(en + i) : -1;
+      }
+      double v[U][CD];
 #pragma unroll
-        for (int b = 0; b < CD; ++b) v[b] = 0.0;
-        if (e < m.ne) {
-          const int64_t node = m.e2n[e * nn + j];
+      for (int u = 0; u < U; ++u) {
+#pragma unroll
+        for (int b = 0; b < CD; ++b) v[u][b] = 0.0;
+        if (nd[u] >= 0) {
           if (CD == 2) {
-            const double2 t = __ldg(reinterpret_cast<const double2*>(x + node * 2));
-            v[0] = t.x;
-            v[CD - 1] = t.y;
+            const double2 t = __ldg(reinterpret_cast<const double2*>(x) + nd[u]);
+            v[u][0] = t.x;
+            v[u][CD - 1] = t.y;
           } else {
 #pragma unroll
-            for (int b = 0; b < CD; ++b) v[b] = __ldg(x + node * CD + b);
+            for (int b = 0; b < CD; ++b) v[u][b] = __ldg(x + (int64_t)nd[u] * CD + b);
           }
         }
+      }
 #pragma unroll
-        for (int b = 0; b < CD; ++b) Xs[(j * CD + b) * EO_TE + el] = v[b];
+      for (int u = 0; u < U; ++u) {
+        const int i = base + u * nthr;
+        if (i < EO_TE * nn) {
+          const int el = (int)__umulhi((unsigned)i, m.nn_magic), j = i - el * nn;
+          double* xs = Xs + el * NCP + j * CD;
+          if (CD == 2) {
+            *reinterpret_cast<double2*>(xs) = make_double2(v[u][0], v[u][CD - 1]);   // NCP and j*2 are even
+          } else {
+#pragma unroll
+            for (int b = 0; b < CD; ++b) xs[b] = v[u][b];
+          }
+        }
       }
     }
     __syncthreads();
-    for (int item = warp; item < nitems; item += EO_THREADS / 32) {
-      const int i0 = item * EO_R;
-      double acc[EO_R][EO_Q];
+    for (int item = warp; item < nitems; item += nwarps) {
+      const int i0 = item * R;
+      double acc[R][EO_Q];
 #pragma unroll
-      for (int r = 0; r < EO_R; ++r)
+      for (int r = 0; r < R; ++r)
 #pragma unroll
         for (int q = 0; q < EO_Q; ++q) acc[r][q] = 0.0;
-      const double* xp = Xs + EO_Q * lane;
+      const double* xp = Xs + lane * NCP;
       const double* ep = Et + i0;
-#pragma unroll 2
-      for (int k = 0; k < NC; ++k) {
-        const double2 xa = *reinterpret_cast<const double2*>(xp + k * EO_TE);
-        const double2 xb = *reinterpret_cast<const double2*>(xp + k * EO_TE + 2);
-        const double xv[EO_Q] = {xa.x, xa.y, xb.x, xb.y};
-        double ev[EO_R];
+      for (int k = 0; k < NCP; k += 2) {
+        double2 xv[EO_Q];
 #pragma unroll
-        for (int r = 0; r < EO_R; r += 2) {
-          const double2 t = *reinterpret_cast<const double2*>(ep + k * NRP + r);
-          ev[r] = t.x;
-          ev[r + 1] = t.y;
+        for (int q = 0; q < EO_Q; ++q) xv[q] = *reinterpret_cast<const double2*>(xp + q * 32 * NCP + k);
+#pragma unroll
+        for (int kk = 0; kk < 2; ++kk) {
+          double ev[R];
+#pragma unroll
+          for (int r = 0; r < R; r += 2) {
+            const double2 t = *reinterpret_cast<const double2*>(ep + (k + kk) * NRP + r);
+            ev[r] = t.x;
+            ev[r + 1] = t.y;
+          }
+#pragma unroll
+          for (int r = 0; r < R; ++r)
+#pragma unroll
+            for (int q = 0; q < EO_Q; ++q) acc[r][q] = fma(ev[r], kk ? xv[q].y : xv[q].x, acc[r][q]);
         }
-#pragma unroll
-        for (int r = 0; r < EO_R; ++r)
-#pragma unroll
-          for (int q = 0; q < EO_Q; ++q) acc[r][q] = fma(ev[r], xv[q], acc[r][q]);
       }
 #pragma unroll
       for (int q = 0; q < EO_Q; ++q) {
-        const int64_t e = e0 + EO_Q * lane + q;
+        const int64_t e = e0 + lane + 32 * q;
         if (e >= m.ne) continue;
         double* yp = m.Ye + e * NR + i0;
         if (vec_store) {
 #pragma unroll
-          for (int r = 0; r < EO_R; r += 2)
+          for (int r = 0; r < R; r += 2)
             if (i0 + r < NR) *reinterpret_cast<double2*>(yp + r) = make_double2(acc[r][q], acc[r + 1][q]);
         } else {
 #pragma unroll
-          for (int r = 0; r < EO_R; ++r)
+          for (int r = 0; r < R; ++r)
             if (i0 + r < NR) yp[r] = acc[r][q];
         }
       }
@@ -141,59 +172,101 @@ __global__ void __launch_bounds__(256) eop_gather_kernel(pyn::TmatView m, ModeEp
   }
 }
 
-// rows of the flagged nodes from the assembled CSR: one warp per row
+// rows of the flagged nodes from the assembled CSR: one warp per row, one row per warp (full-width grid)
 __global__ void __launch_bounds__(256)
 tmat_boundary_kernel(pyn::TmatView m, int rd, const double* __restrict__ x, ModeEpi epi) {
   const int lane = threadIdx.x & 31;
-  const int64_t w0 = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5, nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
-  const int64_t nrows = m.nlist * rd;
-  for (int64_t i = w0; i < nrows; i += nw) {
-    const int64_t row = (int64_t)m.list[i / rd] * rd + (i % rd);
-    const double s = pyn::spmv_row<32>(m.ptr, m.ind, m.val, x, row, true, lane);
-    if (lane == 0) epi(row, s);
-  }
+  const int64_t i = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  if (i >= m.nlist * rd) return;
+  const int64_t row = (int64_t)m.list[i / rd] * rd + (i % rd);
+  const double s = pyn::spmv_row<32>(m.ptr, m.ind, m.val, x, row, true, lane);
+  if (lane == 0) epi(row, s);
 }
 
-size_t eop_smem(int NC, int NRP) { return sizeof(double) * ((size_t)NC * NRP + (size_t)NC * EO_TE); }
+// launch shape for an element matrix with NR rows: rows per register block R (8 or 10), warps per CTA W (2..5) and the
+// padded sizes; minimises the idle fraction  1 - NR / (R * W * rounds)  (ties: wider CTA, then R = 8)
+struct EopShape {
+  int R, W, NRP, NCP;
+  size_t smem;
+};
+EopShape eop_shape(int NR, int NC) {
+  EopShape best{8, 4, 0, 0, 0};
+  double best_eff = -1.0;
+  for (int R : {8, 10}) {
+    const int items = (NR + R - 1) / R;
+    for (int W = EO_MAXW; W >= 2; --W) {
+      const int rounds = (items + W - 1) / W;
+      const double eff = (double)NR / ((double)R * W * rounds);
+      if (eff > best_eff + 1e-9) { best_eff = eff; best.R = R; best.W = W; }
+    }
+  }
+  best.NRP = (NR + best.R - 1) / best.R * best.R;
+  int ncp = (NC + 1) / 2 * 2;          // even, and NCP/2 odd: the LDS.128 reads of X are then bank-conflict free
+  if ((ncp / 2) % 2 == 0) ncp += 2;
+  best.NCP = ncp;
+  best.smem = sizeof(double) * ((size_t)best.NCP * best.NRP + (size_t)EO_TE * best.NCP);
+  return best;
+}
 constexpr size_t EO_SMEM_MAX = 227 * 1024;
+
+template <int CD, int R>
+int eop_launch(const pyn_tmat* m, const double* d_x, const int* d_done, cudaStream_t st) {
+  eop_apply_kernel<CD, R><<<m->grid_apply, 32 * m->W, m->smem, st>>>(pyn::view_of(m), d_x, d_done);
+  PYN_CHECK_LAUNCH();
+  return PYN_OK;
+}
+template <int CD, int R>
+int eop_prepare(pyn_tmat* m) {
+  int occ = 0;
+  PYN_CHECK_CUDA(cudaFuncSetAttribute(eop_apply_kernel<CD, R>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)EO_SMEM_MAX));
+  if (!getenv("PYN_EO_NO_CARVEOUT"))
+    PYN_CHECK_CUDA(cudaFuncSetAttribute(eop_apply_kernel<CD, R>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                        (int)cudaSharedmemCarveoutMaxShared));
+  PYN_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, eop_apply_kernel<CD, R>, 32 * m->W, m->smem));
+  const int64_t ntiles = (m->topo->ne + EO_TE - 1) / EO_TE;
+  const int64_t cap = (int64_t)pyn::sm_count() * (occ > 0 ? occ : 1);
+  m->grid_apply = (int)(ntiles < cap ? ntiles : cap);
+  return PYN_OK;
+}
+#define PYN_EO_DISPATCH(FN, ...)                                                     \
+  do {                                                                               \
+    if (m->R == 8) {                                                                 \
+      if (m->cdof == 1) return FN<1, 8>(__VA_ARGS__);                                \
+      if (m->cdof == 2) return FN<2, 8>(__VA_ARGS__);                                \
+      return FN<3, 8>(__VA_ARGS__);                                                  \
+    }                                                                                \
+    if (m->cdof == 1) return FN<1, 10>(__VA_ARGS__);                                 \
+    if (m->cdof == 2) return FN<2, 10>(__VA_ARGS__);                                 \
+    return FN<3, 10>(__VA_ARGS__);                                                   \
+  } while (0)
+int eop_prepare_any(pyn_tmat* m) { PYN_EO_DISPATCH(eop_prepare, m); }
 
 }  // namespace
 
 namespace pyn {
 
 int tmat_apply(const pyn_tmat* m, const double* d_x, const int* d_done, cudaStream_t st) {
-  const TmatView v = view_of(m);
-  if (m->cdof == 1) eop_apply_kernel<1><<<m->grid_apply, EO_THREADS, m->smem, st>>>(v, d_x, d_done);
-  else if (m->cdof == 2) eop_apply_kernel<2><<<m->grid_apply, EO_THREADS, m->smem, st>>>(v, d_x, d_done);
-  else eop_apply_kernel<3><<<m->grid_apply, EO_THREADS, m->smem, st>>>(v, d_x, d_done);
-  PYN_CHECK_LAUNCH();
-  return PYN_OK;
+  PYN_EO_DISPATCH(eop_launch, m, d_x, d_done, st);
 }
 
 // called by pyn_tmat_create (assemble.cu, which owns the descriptor logic): element matrix, scratch, launch shapes
 int tmat_init(pyn_tmat* m, const double* d_E, double sign, cudaStream_t st) {
   const pyn_topo* t = m->topo;
   m->NR = m->rdof * t->nn; m->NC = m->cdof * t->nn;
-  m->NRP = (m->NR + EO_R - 1) / EO_R * EO_R;
-  m->smem = eop_smem(m->NC, m->NRP);
+  const EopShape sh = eop_shape(m->NR, m->NC);
+  m->R = sh.R; m->W = sh.W; m->NRP = sh.NRP; m->NCP = sh.NCP; m->smem = sh.smem;
   PYN_REQUIRE(m->smem <= EO_SMEM_MAX, "element operator: the element matrix does not fit in shared memory");
-  PYN_CHECK_CUDA(cudaMalloc(&m->Et, sizeof(double) * (size_t)m->NC * m->NRP));
+  PYN_CHECK_CUDA(cudaMalloc(&m->Et, sizeof(double) * (size_t)m->NCP * m->NRP));
   PYN_CHECK_CUDA(cudaMalloc(&m->Ye, sizeof(double) * (size_t)t->ne * m->NR));
-  eop_transpose_kernel<<<(m->NC * m->NRP + 255) / 256, 256, 0, st>>>(m->NR, m->NC, m->NRP, sign, d_E, m->Et);
+  eop_transpose_kernel<<<(m->NCP * m->NRP + 255) / 256, 256, 0, st>>>(m->NR, m->NC, m->NRP, m->NCP, sign, d_E, m->Et);
   PYN_CHECK_LAUNCH();
-  int occ = 0;
-#define PYN_EO_ATTR(CD)                                                                                            \
-  PYN_CHECK_CUDA(cudaFuncSetAttribute(eop_apply_kernel<CD>, cudaFuncAttributeMaxDynamicSharedMemorySize,           \
-                                      (int)EO_SMEM_MAX));                                                          \
-  PYN_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, eop_apply_kernel<CD>, EO_THREADS, m->smem));
-  if (m->cdof == 1) { PYN_EO_ATTR(1) } else if (m->cdof == 2) { PYN_EO_ATTR(2) } else { PYN_EO_ATTR(3) }
-#undef PYN_EO_ATTR
-  const int64_t ntiles = (t->ne + EO_TE - 1) / EO_TE;
-  const int64_t cap_a = (int64_t)sm_count() * (occ > 0 ? occ : 1);
-  m->grid_apply = (int)(ntiles < cap_a ? ntiles : cap_a);
+  int rc = eop_prepare_any(m);
+  if (rc) return rc;
   m->grid_int = grid_for(t->nnodes, 256, 8);
-  const int64_t need_b = (m->nlist * m->rdof * 32 + 255) / 256, cap_b = (int64_t)sm_count() * 2;
-  m->grid_bnd = (int)(need_b < cap_b ? (need_b > 0 ? need_b : 1) : cap_b);
+  const int64_t need_b = (m->nlist * m->rdof * 32 + 255) / 256;
+  PYN_REQUIRE(need_b < 0x7fffffff, "element operator: boundary list too long");
+  m->grid_bnd = (int)(need_b > 0 ? need_b : 1);
   PYN_CHECK_CUDA(cudaStreamSynchronize(st));
   return PYN_OK;
 }
@@ -204,8 +277,7 @@ extern "C" {
 
 int pyn_tmat_supported(int nn, int rdof, int cdof) {
   if (nn < 1 || rdof < 1 || rdof > 3 || cdof < 1 || cdof > 3) return 0;
-  const int NR = rdof * nn, NC = cdof * nn, NRP = (NR + EO_R - 1) / EO_R * EO_R;
-  return eop_smem(NC, NRP) <= EO_SMEM_MAX ? 1 : 0;
+  return eop_shape(rdof * nn, cdof * nn).smem <= EO_SMEM_MAX ? 1 : 0;
 }
 
 int pyn_tmat_destroy(pyn_tmat* m) {

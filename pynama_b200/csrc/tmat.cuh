@@ -2,8 +2,8 @@
 // matrix E on a repetitive mesh, WITHOUT streaming its stored values.
 //
 //   phase 1 (eop_apply_kernel, tmat.cu): Ye[e][:] = E . x[dofs(e)] for every element -- a batched dense product
-//            [NR x NC] . [NC x ne] with E resident in shared memory, 128 elements per tile, each thread an 8-row x
-//            4-element register block; HBM traffic = x once + 4 B/element-node of connectivity + Ye written once.
+//            [NR x NC] . [NC x ne] with E resident in shared memory, 128 elements per tile, each thread an R-row x
+//            4-element register block (R = 8 | 10); HBM traffic = x once + 4 B/element-node of connectivity + Ye written once.
 //   phase 2 (eop_gather_node, below): row node r sums Ye[e][loc_e(r)] over its incident elements in ascending cell
 //            order (the reference's cell loop order, base_problem.py:499-552), scaled by rowscale[r] -- a deterministic
 //            gather, no atomics.
@@ -19,8 +19,9 @@
 struct pyn_tmat {
   const pyn_topo* topo;      // borrowed
   int rdof, cdof;
-  int NR, NC, NRP;           // element matrix rows / cols, rows padded to a multiple of EO_R
-  double* Et;                // owned: sign * E transposed, [NC][NRP], zero padded
+  int NR, NC, NRP, NCP;      // element matrix rows / cols; rows padded to a multiple of R, cols to 2*odd
+  int R, W;                  // rows per register block (8 | 10), warps per CTA of phase 1
+  double* Et;                // owned: sign * E transposed, [NCP][NRP], zero padded
   double* Ye;                // owned scratch [ne][NR]
   const uint8_t* flags;      // borrowed from the bcmap: 1 = row comes from the CSR
   const int* list;           // flagged nodes
@@ -35,14 +36,13 @@ struct pyn_tmat {
 
 namespace pyn {
 
-constexpr int EO_THREADS = 128;  // threads per CTA of phase 1
 constexpr int EO_TE = 128;       // elements per tile
-constexpr int EO_R = 8;          // rows per register block
 constexpr int EO_Q = 4;          // elements per register block (per lane)
 
 struct TmatView {
   int64_t nnodes, ne;
-  int nn, NR, NC, NRP;
+  int nn, NR, NC, NRP, NCP;
+  unsigned nn_magic;   // ceil(2^32 / nn): i / nn == __umulhi(i, nn_magic) for i * nn < 2^32
   const int* e2n;
   const int64_t* n2e_ptr;
   const int* n2e_elem;
@@ -59,7 +59,8 @@ struct TmatView {
 };
 static inline TmatView view_of(const pyn_tmat* m) {
   TmatView v;
-  v.nnodes = m->topo->nnodes; v.ne = m->topo->ne; v.nn = m->topo->nn; v.NR = m->NR; v.NC = m->NC; v.NRP = m->NRP;
+  v.nnodes = m->topo->nnodes; v.ne = m->topo->ne; v.nn = m->topo->nn; v.NR = m->NR; v.NC = m->NC; v.NRP = m->NRP; v.NCP = m->NCP;
+  v.nn_magic = (unsigned)((0x100000000ull + (unsigned)v.nn - 1) / (unsigned)v.nn);
   v.e2n = m->topo->e2n; v.n2e_ptr = m->topo->n2e_ptr; v.n2e_elem = m->topo->n2e_elem; v.n2e_loc = m->topo->n2e_loc;
   v.Et = m->Et; v.Ye = m->Ye; v.flags = m->flags; v.list = m->list; v.nlist = m->nlist; v.rowscale = m->rowscale;
   v.ptr = m->ptr; v.ind = m->ind; v.val = m->val;
