@@ -160,6 +160,132 @@ eop_apply_kernel(pyn::TmatView m, const double* __restrict__ x, const int* __res
   }
 }
 
+// ---- Phase 1 on the FP64 tensor cores ------------------------------------------------------------------------------
+// The SIMT kernel above is co-limited by the FP64 pipe and the shared-memory pipe (every DFMA needs an operand from
+// shared memory; ncu: fp64 32 %, LSU 48 %, the rest barrier / gather latency).  This variant computes the same
+// Ye = E . X with mma.sync.m8n8k4.f64 (DMMA): A = 8 rows x 4 cols of E (pre-arranged fragment-major in shared memory,
+// one conflict-free LDS.64 per fragment), B = 4 cols x 8 elements of X, D = 8 rows x 8 elements -- 256 FMA for two
+// operand loads.  Every WARP is autonomous: it owns stages of 8 elements, gathers them asynchronously (cp.async
+// straight into its private double buffer, connectivity prefetched one stage ahead into registers) and multiplies
+// the previous stage meanwhile, MB row blocks at a time.  No CTA barrier after the prologue: the 24 warps of an SM
+// drift apart and keep the DMMA pipe fed while others wait on memory.
+constexpr int EM_NE = 8;      // elements per warp stage (one DMMA n-block)
+constexpr int EM_PMAX = 16;   // (element, node) pairs gathered per lane and stage, at most (kernel variants: 8, 16)
+constexpr int EM_W = 8;       // warps per CTA
+
+__global__ void eop_fragment_kernel(int NR, int NC, int RB, int KB, double sign, const double* __restrict__ E,
+                                    double* __restrict__ Af) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < RB * KB * 32; i += gridDim.x * blockDim.x) {
+    const int l = i & 31, f = i >> 5, kb = f % KB, rb = f / KB;
+    const int r = rb * 8 + (l >> 2), k = kb * 4 + (l & 3);
+    Af[i] = (r < NR && k < NC) ? sign * E[r * NC + k] : 0.0;
+  }
+}
+
+__device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+               : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
+template <int BYTES>
+__device__ __forceinline__ void cp_async_zfill(double* smem_dst, const double* gsrc, bool valid) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  const int n = valid ? BYTES : 0;   // src-size 0: the destination is zero-filled
+  asm volatile("cp.async.ca.shared.global [%0], [%1], %2, %3;" ::"r"(d), "l"(gsrc), "n"(BYTES), "r"(n) : "memory");
+}
+
+template <int CD, int PMAX, int MB>
+__global__ void __launch_bounds__(EM_W * 32, 3)
+eop_apply_mma_kernel(pyn::TmatView m, const double* __restrict__ x, const int* __restrict__ done, int RB, int KB) {
+  extern __shared__ __align__(16) double sm[];
+  if (done && *done) return;
+  const int NR = m.NR, NC = m.NC, NCP = m.NCP, nn = m.nn;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  double* Af = sm;                                                // [RB][KB][32]
+  double* Xw = sm + RB * KB * 32 + warp * (2 * EM_NE * NCP);      // this warp's [2][EM_NE][NCP]
+  for (int i = tid; i < RB * KB * 32; i += EM_W * 32) Af[i] = m.Et[i];
+  for (int i = lane; i < 2 * EM_NE * (NCP - NC); i += 32) {        // pad columns of X: zero for the life of the CTA
+    const int el = i / (NCP - NC);
+    Xw[el * NCP + NC + (i - el * (NCP - NC))] = 0.0;
+  }
+  __syncthreads();
+  const int64_t nstages = (m.ne + EM_NE - 1) / EM_NE;
+  const int npt = EM_NE * nn;             // pairs per stage
+  int idx[PMAX];
+  auto load_idx = [&](int64_t stage) {
+    const int64_t e0 = stage * EM_NE;
+    const int64_t rem = m.ne - e0;
+    const int npairs = rem <= 0 ? 0 : (int)(rem < EM_NE ? rem : EM_NE) * nn;
+    const int* en = m.e2n + e0 * nn;
+#pragma unroll
+    for (int u = 0; u < PMAX; ++u) {
+      const int i = lane + u * 32;
+      idx[u] = (i < npairs) ? pyn::ld_stream(en + i) : -1;
+    }
+  };
+  auto issue = [&](int buf) {
+    double* X = Xw + buf * (EM_NE * NCP);
+#pragma unroll
+    for (int u = 0; u < PMAX; ++u) {
+      const int i = lane + u * 32;
+      if (i < npt) {
+        const int el = (int)__umulhi((unsigned)i, m.nn_magic), j = i - el * nn;
+        double* dst = X + el * NCP + j * CD;
+        const bool ok = idx[u] >= 0;
+        const double* src = x + (ok ? (int64_t)idx[u] * CD : 0);
+        if (CD == 2) {
+          cp_async_zfill<16>(dst, src, ok);
+        } else {
+#pragma unroll
+          for (int b = 0; b < CD; ++b) cp_async_zfill<8>(dst + b, src + b, ok);
+        }
+      }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  const int64_t G = (int64_t)gridDim.x * EM_W;
+  int64_t stage = (int64_t)blockIdx.x * EM_W + warp;
+  load_idx(stage);
+  issue(0);
+  load_idx(stage + G);
+  int buf = 0;
+  for (; stage < nstages; stage += G, buf ^= 1) {
+    __syncwarp();                         // the products of the previous stage no longer read buf ^ 1
+    if (stage + G < nstages) {
+      issue(buf ^ 1);                     // stage t+1 streams in while stage t is multiplied
+      load_idx(stage + 2 * G);
+      asm volatile("cp.async.wait_group 1;" ::: "memory");
+    } else {
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+    }
+    __syncwarp();                         // every lane's copies of stage t have landed
+    const double* bp = Xw + buf * (EM_NE * NCP) + (lane >> 2) * NCP + (lane & 3);
+    const int64_t e0 = stage * EM_NE + (lane & 3) * 2;
+    for (int rb0 = 0; rb0 < RB; rb0 += MB) {
+      double acc[MB][2];
+#pragma unroll
+      for (int i = 0; i < MB; ++i) acc[i][0] = acc[i][1] = 0.0;
+      const double* ap = Af + rb0 * KB * 32 + lane;
+#pragma unroll 2
+      for (int kb = 0; kb < KB; ++kb) {
+        const double b = bp[kb * 4];
+        double a[MB];
+#pragma unroll
+        for (int i = 0; i < MB; ++i) a[i] = (rb0 + i < RB) ? ap[(i * KB + kb) * 32] : 0.0;
+#pragma unroll
+        for (int i = 0; i < MB; ++i) dmma884(acc[i][0], acc[i][1], a[i], b);
+      }
+#pragma unroll
+      for (int i = 0; i < MB; ++i) {
+        const int row = (rb0 + i) * 8 + (lane >> 2);
+        if (row < NR) {
+          if (e0 < m.ne) m.Ye[e0 * NR + row] = acc[i][0];
+          if (e0 + 1 < m.ne) m.Ye[(e0 + 1) * NR + row] = acc[i][1];
+        }
+      }
+    }
+  }
+}
+
 // Phase 2: one thread per un-flagged node
 template <int RD>
 __global__ void __launch_bounds__(256) eop_gather_kernel(pyn::TmatView m, ModeEpi epi) {
@@ -209,6 +335,54 @@ EopShape eop_shape(int NR, int NC) {
 }
 constexpr size_t EO_SMEM_MAX = 227 * 1024;
 
+// DMMA variant: row blocks, k blocks, padded columns (NCP = 4 mod 8: conflict-free B fragments), row blocks per pass
+// MB (3..7: least padding, then the larger), shared memory
+struct MmaShape {
+  int RB, KB, NCP, MB, P;
+  size_t smem;
+  bool ok;
+};
+MmaShape mma_shape(int nn, int NR, int NC) {
+  MmaShape s;
+  s.RB = (NR + 7) / 8;
+  int ncp = (NC + 3) / 4 * 4;
+  if (ncp % 8 == 0) ncp += 4;
+  s.NCP = ncp; s.KB = ncp / 4;
+  s.MB = 3;
+  int best = 1 << 30;
+  for (int MB = 7; MB >= 3; --MB) {
+    const int waste = (s.RB + MB - 1) / MB * MB - s.RB;
+    if (waste < best) { best = waste; s.MB = MB; }
+  }
+  s.P = (EM_NE * nn + 31) / 32;
+  s.smem = sizeof(double) * ((size_t)s.RB * s.KB * 32 + (size_t)EM_W * 2 * EM_NE * s.NCP);
+  s.ok = s.smem <= EO_SMEM_MAX && s.P <= EM_PMAX;
+  return s;
+}
+template <int CD, int PMAX, int MB>
+int mma_launch(const pyn_tmat* m, const double* d_x, const int* d_done, cudaStream_t st) {
+  eop_apply_mma_kernel<CD, PMAX, MB><<<m->grid_apply, 32 * EM_W, m->smem, st>>>(pyn::view_of(m), d_x, d_done, m->RB,
+                                                                                 m->KB);
+  PYN_CHECK_LAUNCH();
+  return PYN_OK;
+}
+template <int CD, int PMAX, int MB>
+int mma_prepare(pyn_tmat* m) {
+  int occ = 0;
+  PYN_CHECK_CUDA(cudaFuncSetAttribute(eop_apply_mma_kernel<CD, PMAX, MB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)EO_SMEM_MAX));
+  PYN_CHECK_CUDA(cudaFuncSetAttribute(eop_apply_mma_kernel<CD, PMAX, MB>,
+                                      cudaFuncAttributePreferredSharedMemoryCarveout,
+                                      (int)cudaSharedmemCarveoutMaxShared));
+  PYN_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, eop_apply_mma_kernel<CD, PMAX, MB>, 32 * EM_W,
+                                                               m->smem));
+  const int64_t nstages = (m->topo->ne + EM_NE - 1) / EM_NE;
+  const int64_t need = (nstages + EM_W - 1) / EM_W;
+  const int64_t cap = (int64_t)pyn::sm_count() * (occ > 0 ? occ : 1);
+  m->grid_apply = (int)(need < cap ? need : cap);
+  return PYN_OK;
+}
+
 template <int CD, int R>
 int eop_launch(const pyn_tmat* m, const double* d_x, const int* d_done, cudaStream_t st) {
   eop_apply_kernel<CD, R><<<m->grid_apply, 32 * m->W, m->smem, st>>>(pyn::view_of(m), d_x, d_done);
@@ -241,12 +415,34 @@ int eop_prepare(pyn_tmat* m) {
     return FN<3, 10>(__VA_ARGS__);                                                   \
   } while (0)
 int eop_prepare_any(pyn_tmat* m) { PYN_EO_DISPATCH(eop_prepare, m); }
+// DMMA variant: PMAX = 8 when a lane gathers at most 8 pairs per stage (fewer registers), else 16; MB = 3..7
+#define PYN_EM_CASE(FN, CDV, PV, ...)                                                \
+  switch (m->MB) {                                                                   \
+    case 3: return FN<CDV, PV, 3>(__VA_ARGS__);                                      \
+    case 4: return FN<CDV, PV, 4>(__VA_ARGS__);                                      \
+    case 5: return FN<CDV, PV, 5>(__VA_ARGS__);                                      \
+    case 6: return FN<CDV, PV, 6>(__VA_ARGS__);                                      \
+    default: return FN<CDV, PV, 7>(__VA_ARGS__);                                     \
+  }
+#define PYN_EM_DISPATCH(FN, ...)                                                     \
+  do {                                                                               \
+    if (m->P <= 8) {                                                                 \
+      if (m->cdof == 1) { PYN_EM_CASE(FN, 1, 8, __VA_ARGS__) }                       \
+      if (m->cdof == 2) { PYN_EM_CASE(FN, 2, 8, __VA_ARGS__) }                       \
+      PYN_EM_CASE(FN, 3, 8, __VA_ARGS__)                                             \
+    }                                                                                \
+    if (m->cdof == 1) { PYN_EM_CASE(FN, 1, 16, __VA_ARGS__) }                        \
+    if (m->cdof == 2) { PYN_EM_CASE(FN, 2, 16, __VA_ARGS__) }                        \
+    PYN_EM_CASE(FN, 3, 16, __VA_ARGS__)                                              \
+  } while (0)
+int mma_prepare_any(pyn_tmat* m) { PYN_EM_DISPATCH(mma_prepare, m); }
 
 }  // namespace
 
 namespace pyn {
 
 int tmat_apply(const pyn_tmat* m, const double* d_x, const int* d_done, cudaStream_t st) {
+  if (m->mma) PYN_EM_DISPATCH(mma_launch, m, d_x, d_done, st);
   PYN_EO_DISPATCH(eop_launch, m, d_x, d_done, st);
 }
 
@@ -254,14 +450,27 @@ int tmat_apply(const pyn_tmat* m, const double* d_x, const int* d_done, cudaStre
 int tmat_init(pyn_tmat* m, const double* d_E, double sign, cudaStream_t st) {
   const pyn_topo* t = m->topo;
   m->NR = m->rdof * t->nn; m->NC = m->cdof * t->nn;
-  const EopShape sh = eop_shape(m->NR, m->NC);
-  m->R = sh.R; m->W = sh.W; m->NRP = sh.NRP; m->NCP = sh.NCP; m->smem = sh.smem;
-  PYN_REQUIRE(m->smem <= EO_SMEM_MAX, "element operator: the element matrix does not fit in shared memory");
-  PYN_CHECK_CUDA(cudaMalloc(&m->Et, sizeof(double) * (size_t)m->NCP * m->NRP));
+  const MmaShape ms = mma_shape(t->nn, m->NR, m->NC);
+  m->mma = ms.ok && !getenv("PYN_EO_SIMT");      // PYN_EO_SIMT=1: keep the DFMA kernel (A/B measurements)
   PYN_CHECK_CUDA(cudaMalloc(&m->Ye, sizeof(double) * (size_t)t->ne * m->NR));
-  eop_transpose_kernel<<<(m->NCP * m->NRP + 255) / 256, 256, 0, st>>>(m->NR, m->NC, m->NRP, m->NCP, sign, d_E, m->Et);
-  PYN_CHECK_LAUNCH();
-  int rc = eop_prepare_any(m);
+  int rc;
+  if (m->mma) {
+    m->RB = ms.RB; m->KB = ms.KB; m->NCP = ms.NCP; m->W = EM_W; m->MB = ms.MB; m->P = ms.P; m->smem = ms.smem;
+    m->NRP = ms.RB * 8;
+    const int len = m->RB * m->KB * 32;
+    PYN_CHECK_CUDA(cudaMalloc(&m->Et, sizeof(double) * (size_t)len));
+    eop_fragment_kernel<<<(len + 255) / 256, 256, 0, st>>>(m->NR, m->NC, m->RB, m->KB, sign, d_E, m->Et);
+    PYN_CHECK_LAUNCH();
+    rc = mma_prepare_any(m);
+  } else {
+    const EopShape sh = eop_shape(m->NR, m->NC);
+    m->R = sh.R; m->W = sh.W; m->NRP = sh.NRP; m->NCP = sh.NCP; m->smem = sh.smem;
+    PYN_REQUIRE(m->smem <= EO_SMEM_MAX, "element operator: the element matrix does not fit in shared memory");
+    PYN_CHECK_CUDA(cudaMalloc(&m->Et, sizeof(double) * (size_t)m->NCP * m->NRP));
+    eop_transpose_kernel<<<(m->NCP * m->NRP + 255) / 256, 256, 0, st>>>(m->NR, m->NC, m->NRP, m->NCP, sign, d_E, m->Et);
+    PYN_CHECK_LAUNCH();
+    rc = eop_prepare_any(m);
+  }
   if (rc) return rc;
   m->grid_int = grid_for(t->nnodes, 256, 8);
   const int64_t need_b = (m->nlist * m->rdof * 32 + 255) / 256;
@@ -277,7 +486,7 @@ extern "C" {
 
 int pyn_tmat_supported(int nn, int rdof, int cdof) {
   if (nn < 1 || rdof < 1 || rdof > 3 || cdof < 1 || cdof > 3) return 0;
-  return eop_shape(rdof * nn, cdof * nn).smem <= EO_SMEM_MAX ? 1 : 0;
+  return (mma_shape(nn, rdof * nn, cdof * nn).ok || eop_shape(rdof * nn, cdof * nn).smem <= EO_SMEM_MAX) ? 1 : 0;
 }
 
 int pyn_tmat_destroy(pyn_tmat* m) {
