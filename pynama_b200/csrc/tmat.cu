@@ -169,9 +169,10 @@ eop_apply_kernel(pyn::TmatView m, const double* __restrict__ x, const int* __res
 // straight into its private double buffer, connectivity prefetched one stage ahead into registers) and multiplies
 // the previous stage meanwhile, MB row blocks at a time.  No CTA barrier after the prologue: the 24 warps of an SM
 // drift apart and keep the DMMA pipe fed while others wait on memory.
-constexpr int EM_NE = 8;      // elements per warp stage (one DMMA n-block)
+constexpr int EM_NBW = 2;     // DMMA n-blocks (8 elements each) per warp stage: every A fragment feeds EM_NBW DMMAs
+constexpr int EM_NE = 8 * EM_NBW;   // elements per warp stage
 constexpr int EM_PMAX = 16;   // (element, node) pairs gathered per lane and stage, at most (kernel variants: 8, 16)
-constexpr int EM_W = 8;       // warps per CTA
+constexpr int EM_W = 4;       // warps per CTA
 
 __global__ void eop_fragment_kernel(int NR, int NC, int RB, int KB, double sign, const double* __restrict__ E,
                                     double* __restrict__ Af) {
@@ -261,25 +262,35 @@ eop_apply_mma_kernel(pyn::TmatView m, const double* __restrict__ x, const int* _
     const double* bp = Xw + buf * (EM_NE * NCP) + (lane >> 2) * NCP + (lane & 3);
     const int64_t e0 = stage * EM_NE + (lane & 3) * 2;
     for (int rb0 = 0; rb0 < RB; rb0 += MB) {
-      double acc[MB][2];
+      double acc[MB][EM_NBW][2];
 #pragma unroll
-      for (int i = 0; i < MB; ++i) acc[i][0] = acc[i][1] = 0.0;
+      for (int i = 0; i < MB; ++i)
+#pragma unroll
+        for (int nb = 0; nb < EM_NBW; ++nb) acc[i][nb][0] = acc[i][nb][1] = 0.0;
       const double* ap = Af + rb0 * KB * 32 + lane;
 #pragma unroll 2
       for (int kb = 0; kb < KB; ++kb) {
-        const double b = bp[kb * 4];
+        double b[EM_NBW];
+#pragma unroll
+        for (int nb = 0; nb < EM_NBW; ++nb) b[nb] = bp[nb * 8 * NCP + kb * 4];
         double a[MB];
 #pragma unroll
         for (int i = 0; i < MB; ++i) a[i] = (rb0 + i < RB) ? ap[(i * KB + kb) * 32] : 0.0;
 #pragma unroll
-        for (int i = 0; i < MB; ++i) dmma884(acc[i][0], acc[i][1], a[i], b);
+        for (int i = 0; i < MB; ++i)
+#pragma unroll
+          for (int nb = 0; nb < EM_NBW; ++nb) dmma884(acc[i][nb][0], acc[i][nb][1], a[i], b[nb]);
       }
 #pragma unroll
       for (int i = 0; i < MB; ++i) {
         const int row = (rb0 + i) * 8 + (lane >> 2);
         if (row < NR) {
-          if (e0 < m.ne) m.Ye[e0 * NR + row] = acc[i][0];
-          if (e0 + 1 < m.ne) m.Ye[(e0 + 1) * NR + row] = acc[i][1];
+#pragma unroll
+          for (int nb = 0; nb < EM_NBW; ++nb) {
+            const int64_t e = e0 + nb * 8;
+            if (e < m.ne) m.Ye[e * NR + row] = acc[i][nb][0];
+            if (e + 1 < m.ne) m.Ye[(e + 1) * NR + row] = acc[i][nb][1];
+          }
         }
       }
     }
