@@ -414,14 +414,14 @@ def ksp_phase(a, prob, be, torch, peak, barrier):
     # (1) the assembled CSR streamed from HBM: the north_star's "vectorised, coalesced CSR SpMV"
     saved = K._tmat_asm
     K.disable_templates()
-    r, csr_leg = leg("cg_spmv_dot_kernel / spmv_stream_kernel (CSR stream, 12 B per stored entry)", "spmv_kernel")
+    r, csr_leg = leg("cg_spmv_dot_kernel / spmv_stream_kernel (CSR stream, 12 B per stored entry)", "cg_spmv_dot_kernel")
     # (2) the element operator the case classes use on uniform meshes (csrc/tmat.cuh): same operator, matrix-free
     eop_leg = None
     if saved is not None or K.enable_templates():
         if saved is not None:
             K._tmat_asm = saved
-        r, eop_leg = leg("eop_apply_kernel + cg_tmat_interior_kernel (element operator: element products with the "
-                         "element matrix in shared memory + per-node gather)", "eop_kernel")
+        r, eop_leg = leg("eop_apply_mma_kernel + cg_tmat_interior_kernel (element operator: element products with the "
+                         "element matrix in shared memory + per-node gather)", "eop_product")
     best = eop_leg or csr_leg
     out = {"type": "cg", "pc": "jacobi", "its": int(r.its), "reason": int(r.reason),
            "ms_per_solve": best["ms_per_solve"], "ms_per_iteration": best["ms_per_iteration"],
