@@ -80,14 +80,26 @@ __global__ void cg_scalar_init_kernel(int nparts, CgBuffers B, double rtol, doub
   }
 }
 
-// p = z + (beta/betaold) p   (first iteration: p = z)
+// p = z + (beta/betaold) p   (first iteration: p = z); 16-byte accesses (the work vectors are 16-byte aligned)
 __global__ void cg_pupdate_kernel(int64_t n, CgBuffers B) {
   const KspState* s = B.st;
   if (s->done) return;
   const bool first = (s->its == 0);
   const double b = first ? 0.0 : s->beta / s->betaold;
-  for (int64_t i = blockIdx.x * (int64_t)BLK + threadIdx.x; i < n; i += (int64_t)gridDim.x * BLK)
-    B.p[i] = first ? B.z[i] : B.z[i] + b * B.p[i];
+  const int64_t n2 = n >> 1;
+  const double2* z2 = reinterpret_cast<const double2*>(B.z);
+  double2* p2 = reinterpret_cast<double2*>(B.p);
+  for (int64_t i = blockIdx.x * (int64_t)BLK + threadIdx.x; i < n2; i += (int64_t)gridDim.x * BLK) {
+    const double2 z = z2[i];
+    double2 p = z;
+    if (!first) {
+      const double2 q = p2[i];
+      p.x = z.x + b * q.x;
+      p.y = z.y + b * q.y;
+    }
+    p2[i] = p;
+  }
+  if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) B.p[n - 1] = first ? B.z[n - 1] : B.z[n - 1] + b * B.p[n - 1];
 }
 
 // w = A p, per-CTA partial of p.w  (CSR-stream kernel, see spmv.cuh)
@@ -162,7 +174,32 @@ __global__ void cg_update_kernel(int64_t n, int nparts_in, CgBuffers B, double* 
   __syncthreads();
   const double a = s_a;
   double szz = 0.0, szr = 0.0;
-  for (int64_t i = blockIdx.x * (int64_t)BLK + threadIdx.x; i < n; i += (int64_t)gridDim.x * BLK) {
+  const int64_t n2 = n >> 1;
+  double2* x2 = reinterpret_cast<double2*>(B.x);
+  double2* r2 = reinterpret_cast<double2*>(B.r);
+  double2* z2 = reinterpret_cast<double2*>(B.z);
+  const double2* p2 = reinterpret_cast<const double2*>(B.p);
+  const double2* w2 = reinterpret_cast<const double2*>(B.w);
+  const double2* d2 = reinterpret_cast<const double2*>(B.dinv);
+  for (int64_t i = blockIdx.x * (int64_t)BLK + threadIdx.x; i < n2; i += (int64_t)gridDim.x * BLK) {
+    const double2 p = p2[i], w = w2[i], d = d2[i];
+    double2 x = x2[i], r = r2[i], z;
+    x.x += a * p.x;
+    x.y += a * p.y;
+    r.x -= a * w.x;
+    r.y -= a * w.y;
+    z.x = d.x * r.x;
+    z.y = d.y * r.y;
+    x2[i] = x;
+    r2[i] = r;
+    z2[i] = z;
+    szz += z.x * z.x;
+    szr += z.x * r.x;
+    szz += z.y * z.y;
+    szr += z.y * r.y;
+  }
+  if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
+    const int64_t i = n - 1;
     B.x[i] += a * B.p[i];
     const double r = B.r[i] - a * B.w[i];
     const double z = B.dinv[i] * r;
@@ -290,10 +327,11 @@ int pyn_ksp_create(int64_t nrows, const int64_t* d_ptr, const int32_t* d_ind, co
   double* pool = nullptr;
   size_t nparts = (size_t)(k->vgrid > k->sgrid ? k->vgrid : k->sgrid);
   if (nparts < (size_t)pyn::sm_count() * 16) nparts = (size_t)pyn::sm_count() * 16;   // room for the template operator's grids
-  PYN_CHECK_CUDA(cudaMalloc(&pool, sizeof(double) * (6 * (size_t)nrows + 4 * nparts)));
-  k->B.r = pool; k->B.z = pool + nrows; k->B.p = pool + 2 * nrows; k->B.w = pool + 3 * nrows;
-  k->B.x = pool + 4 * nrows; k->B.dinv = pool + 5 * nrows;
-  k->B.part_a = pool + 6 * nrows; k->B.part_b = k->B.part_a + nparts;
+  const size_t ld = ((size_t)nrows + 1) & ~(size_t)1;   // even stride: every work vector stays 16-byte aligned
+  PYN_CHECK_CUDA(cudaMalloc(&pool, sizeof(double) * (6 * ld + 4 * nparts)));
+  k->B.r = pool; k->B.z = pool + ld; k->B.p = pool + 2 * ld; k->B.w = pool + 3 * ld;
+  k->B.x = pool + 4 * ld; k->B.dinv = pool + 5 * ld;
+  k->B.part_a = pool + 6 * ld; k->B.part_b = k->B.part_a + nparts;
   k->pzz = k->B.part_b + nparts; k->pzr = k->pzz + nparts;
   PYN_CHECK_CUDA(cudaMalloc(&k->B.st, sizeof(KspState)));
   PYN_CHECK_CUDA(cudaMallocHost(&k->h_state, sizeof(KspState)));
