@@ -341,31 +341,43 @@ __global__ void asm_interior_count_kernel(pyn::TopoView t, const uint8_t* __rest
   }
 }
 
-// bcmap: flag = node has a non-zero row class, or any adjacency column has a non-zero column class
-__global__ void bcmap_flags_kernel(pyn::TopoView t, const int8_t* __restrict__ rclass, int rdof,
-                                   const int8_t* __restrict__ cclass, int cdof, uint8_t* __restrict__ flags) {
-  const int lane = threadIdx.x & 31;
-  const int64_t warp0 = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
-  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
-  for (int64_t r = warp0; r < t.nnodes; r += nwarps) {
-    bool f = (t.n2e_ptr[r + 1] - t.n2e_ptr[r]) > ASM_MAXDEG;  // high-valence nodes take the generic kernel
-    if (rclass && lane < rdof) f = f || (rclass[r * rdof + lane] != 0);
-    if (cclass) {
-      const int64_t a0 = t.adj_ptr[r];
-      const int L = (int)(t.adj_ptr[r + 1] - a0);
-      for (int p = lane; p < L; p += 32) {
-        const int64_t c = t.adj_cols[a0 + p];
-        for (int b = 0; b < cdof; ++b) f |= cclass[c * cdof + b] != 0;
-      }
-    }
-    const unsigned m = __ballot_sync(0xffffffffu, f);
-    if (lane == 0) flags[r] = m ? 1 : 0;
+// A device scalar is handed to the host through mapped pinned memory (a store from a one-thread kernel), not through
+// a device->host memcpy: a memcpy would queue on the copy engine behind whatever bulk download another stream has in
+// flight (bench.py's end-to-end step downloads 268 MB on a second stream) and stall this stream for milliseconds.
+__global__ void publish_i64_kernel(const int64_t* __restrict__ src, volatile int64_t* dst) { *dst = *src; }
+int read_device_i64(const int64_t* d_src, int64_t* out, cudaStream_t st) {
+  static int64_t* h_box = nullptr;     // one host thread per GPU (include/pynama_b200.h)
+  static int64_t* d_box = nullptr;
+  if (!h_box) {
+    PYN_CHECK_CUDA(cudaHostAlloc(&h_box, sizeof(int64_t), cudaHostAllocMapped));
+    PYN_CHECK_CUDA(cudaHostGetDevicePointer(&d_box, h_box, 0));
   }
+  publish_i64_kernel<<<1, 1, 0, st>>>(d_src, d_box);
+  PYN_CHECK_LAUNCH();
+  PYN_CHECK_CUDA(cudaStreamSynchronize(st));
+  *out = *h_box;
+  return PYN_OK;
 }
 
-__global__ void iota_kernel(int64_t n, int* __restrict__ out) {
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
-    out[i] = (int)i;
+// bcmap: flag = node has a non-zero row class, or any adjacency column has a non-zero column class.  The node
+// adjacency is symmetric, so the second condition is scattered from the (few) nodes that carry a non-zero column
+// class instead of being searched from every node: O(nodes + boundary * row length) instead of O(adjacency).
+__global__ void bcmap_own_kernel(pyn::TopoView t, const int8_t* __restrict__ rclass, int rdof, uint8_t* __restrict__ flags) {
+  for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < t.nnodes; r += (int64_t)gridDim.x * blockDim.x) {
+    bool f = (t.n2e_ptr[r + 1] - t.n2e_ptr[r]) > ASM_MAXDEG;  // high-valence nodes take the generic kernel
+    if (rclass)
+      for (int a = 0; a < rdof; ++a) f = f || (rclass[r * rdof + a] != 0);
+    flags[r] = f ? 1 : 0;
+  }
+}
+__global__ void bcmap_scatter_kernel(pyn::TopoView t, const int8_t* __restrict__ cclass, int cdof,
+                                     uint8_t* __restrict__ flags) {
+  for (int64_t c = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; c < t.nnodes; c += (int64_t)gridDim.x * blockDim.x) {
+    bool nz = false;
+    for (int b = 0; b < cdof; ++b) nz = nz || (cclass[c * cdof + b] != 0);
+    if (!nz) continue;
+    for (int64_t q = t.adj_ptr[c]; q < t.adj_ptr[c + 1]; ++q) flags[t.adj_cols[q]] = 1;   // all writers store 1
+  }
 }
 
 __global__ void weights_kernel(pyn::TopoView t, const double* __restrict__ We, int64_t stride, double* __restrict__ W) {
@@ -590,37 +602,44 @@ int pyn_bcmap_create(const pyn_topo* t, const int8_t* d_rclass, int rdof, const 
   pyn_bcmap* m = new pyn_bcmap();
   memset(m, 0, sizeof(*m));
   m->nnodes = t->nnodes;
-  PYN_CHECK_CUDA(cudaMalloc(&m->flags, (size_t)t->nnodes));
-  bcmap_flags_kernel<<<pyn::grid_for(t->nnodes * 32, 256, 16), 256, 0, st>>>(pyn::view_of(t), d_rclass, rdof, d_cclass,
-                                                                             cdof, m->flags);
+  m->st = st;
+  PYN_CHECK_CUDA(cudaMallocAsync(&m->flags, (size_t)t->nnodes, st));
+  const pyn::TopoView tv = pyn::view_of(t);
+  bcmap_own_kernel<<<pyn::grid_for(t->nnodes, 256), 256, 0, st>>>(tv, d_rclass, rdof, m->flags);
   PYN_CHECK_LAUNCH();
-  int *iota = nullptr, *sel = nullptr;
+  if (d_cclass && cdof > 0) {
+    bcmap_scatter_kernel<<<pyn::grid_for(t->nnodes, 256), 256, 0, st>>>(tv, d_cclass, cdof, m->flags);
+    PYN_CHECK_LAUNCH();
+  }
+  // ascending list of the flagged nodes: stream-ordered temporaries, one host read-back (the list length)
+  int* sel = nullptr;
   int64_t* d_n = nullptr;
-  PYN_CHECK_CUDA(cudaMalloc(&iota, sizeof(int) * t->nnodes));
-  PYN_CHECK_CUDA(cudaMalloc(&sel, sizeof(int) * t->nnodes));
-  PYN_CHECK_CUDA(cudaMalloc(&d_n, sizeof(int64_t)));
-  iota_kernel<<<pyn::grid_for(t->nnodes, 256), 256, 0, st>>>(t->nnodes, iota);
-  PYN_CHECK_LAUNCH();
   void* tmp = nullptr;
   size_t bytes = 0;
-  PYN_CHECK_CUDA(cub::DeviceSelect::Flagged(tmp, bytes, iota, m->flags, sel, d_n, t->nnodes, st));
-  PYN_CHECK_CUDA(cudaMalloc(&tmp, bytes));
-  PYN_CHECK_CUDA(cub::DeviceSelect::Flagged(tmp, bytes, iota, m->flags, sel, d_n, t->nnodes, st));
+  cub::CountingInputIterator<int> ids(0);
+  PYN_CHECK_CUDA(cub::DeviceSelect::Flagged(tmp, bytes, ids, m->flags, sel, d_n, t->nnodes, st));
+  PYN_CHECK_CUDA(cudaMallocAsync(&sel, sizeof(int) * t->nnodes, st));
+  PYN_CHECK_CUDA(cudaMallocAsync(&d_n, sizeof(int64_t), st));
+  PYN_CHECK_CUDA(cudaMallocAsync(&tmp, bytes, st));
+  PYN_CHECK_CUDA(cub::DeviceSelect::Flagged(tmp, bytes, ids, m->flags, sel, d_n, t->nnodes, st));
   pyn::count_launch(2);
-  PYN_CHECK_CUDA(cudaMemcpyAsync(&m->nlist, d_n, sizeof(int64_t), cudaMemcpyDeviceToHost, st));
-  PYN_CHECK_CUDA(cudaStreamSynchronize(st));
-  PYN_CHECK_CUDA(cudaMalloc(&m->list, sizeof(int) * (m->nlist > 0 ? m->nlist : 1)));
+  {
+    const int rc = read_device_i64(d_n, &m->nlist, st);
+    if (rc) return rc;
+  }
+  PYN_CHECK_CUDA(cudaMallocAsync(&m->list, sizeof(int) * (m->nlist > 0 ? m->nlist : 1), st));
   PYN_CHECK_CUDA(cudaMemcpyAsync(m->list, sel, sizeof(int) * m->nlist, cudaMemcpyDeviceToDevice, st));
-  PYN_CHECK_CUDA(cudaStreamSynchronize(st));
-  cudaFree(tmp); cudaFree(iota); cudaFree(sel); cudaFree(d_n);
+  PYN_CHECK_CUDA(cudaFreeAsync(tmp, st));
+  PYN_CHECK_CUDA(cudaFreeAsync(sel, st));
+  PYN_CHECK_CUDA(cudaFreeAsync(d_n, st));
   *out = m;
   return PYN_OK;
 }
 
 int pyn_bcmap_destroy(pyn_bcmap* m) {
   if (!m) return PYN_OK;
-  cudaFree(m->flags);
-  cudaFree(m->list);
+  cudaFreeAsync(m->flags, m->st);   // stream-ordered: no device-wide synchronisation, the pool keeps the memory
+  cudaFreeAsync(m->list, m->st);
   delete m;
   return PYN_OK;
 }

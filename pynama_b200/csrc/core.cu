@@ -21,6 +21,13 @@ void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 int sm_count() {
   if (g_sm_count == 0) {
     int dev = 0, n = 0;
+    // temporaries come from the stream-ordered allocator (cudaMallocAsync); keep what it frees in the pool instead of
+    // handing it back to the driver at every synchronisation (unmapping and remapping costs milliseconds per step)
+    cudaMemPool_t pool;
+    if (cudaGetDevice(&dev) == cudaSuccess && cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+      unsigned long long keep = ~0ull;
+      cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+    }
     if (cudaGetDevice(&dev) == cudaSuccess &&
         cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && n > 0)
       g_sm_count = n;

@@ -31,6 +31,7 @@ struct pyn_bcmap {
   int64_t nnodes, nlist;
   uint8_t* flags;  // [nnodes] 1 = boundary-affected node
   int* list;       // the flagged nodes, ascending
+  cudaStream_t st; // stream the buffers were allocated on (stream-ordered allocator) and are released on
 };
 
 namespace pyn {
