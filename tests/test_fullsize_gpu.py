@@ -1,0 +1,146 @@
+"""Parity at BASELINE.json's full size (configs[3]: cavity 1024x1024 elements, ngl 5 -- 33.6 M velocity dofs, 2.41 G
+stored entries in K), where the CPU oracle cannot go: size-independent properties of the reference's matrices
+(NoSlipFreeSlip.buildKLEMats, base_problem.py:329-454).  Each identity below was first checked on the oracle's small
+meshes (6x5 cells, ngl 4: residuals 2e-12 on entries of size 3e3):
+
+  * rigid translations are in the null space of the element stiffness, and the constrained columns are
+    moved to Krhs with the opposite sign while both matrices get unit diagonals on constrained dofs, hence
+    (K - Krhs) t = 0 and (K + Kfs - Krhsfs) t = 0 for every constant velocity field t, on EVERY row;
+  * K is symmetric: x.(K y) = y.(K x);
+  * the product is linear, the element operator and the CSR stream are the same operator;
+  * the assembly is deterministic: two runs, and the row-template stream vs the generic gather kernel, give the same
+    bits; the pattern is a valid CSR with strictly increasing columns per row.
+"""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+from conftest import ROOT
+
+pytestmark = pytest.mark.gpu
+
+NX, NGL = 1024, 5
+
+
+@pytest.fixture(scope="module")
+def prob():
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("needs a GPU")
+    free, _ = torch.cuda.mem_get_info()
+    if free < 120 * 2 ** 30:
+        pytest.skip("needs ~100 GB of device memory")
+    if ROOT not in sys.path:
+        sys.path.insert(0, ROOT)
+    from bench import CavityAssembly
+    p = CavityAssembly(NX, NGL)
+    p.step()
+    yield p
+    del p
+    torch.cuda.empty_cache()
+
+
+def _rel(a, b):
+    import torch
+    return float((a - b).abs().max() / b.abs().max())
+
+
+def test_pattern_is_valid_csr_at_full_size(prob):
+    import torch
+    K = prob.mats["K"]
+    n = K.shape[0]
+    assert n == 2 * (NX * (NGL - 1) + 1) ** 2 == 33570818
+    ip, ix = K.indptr, K.indices
+    assert int(ip[0]) == 0 and int(ip[-1]) == K.nnz == 2412610692
+    assert bool((ip[1:] >= ip[:-1]).all())
+    assert int(ix.min()) >= 0 and int(ix.max()) < K.shape[1]
+    # strictly increasing columns inside every row, checked in slabs of rows to bound the temporaries
+    slab = n // 8 + 1
+    for r0 in range(0, n, slab):
+        r1 = min(n, r0 + slab)
+        a, b = int(ip[r0]), int(ip[r1])
+        d = ix[a + 1:b] - ix[a:b - 1]
+        starts = ip[r0 + 1:r1] - a - 1          # positions in d that straddle two rows
+        starts = starts[(starts >= 0) & (starts < d.numel())]
+        d[starts] = 1
+        assert bool((d > 0).all())
+        del d
+
+
+def test_translation_null_space_at_full_size(prob):
+    import torch
+    be = prob.be
+    m = prob.mats
+    n = m["K"].shape[0]
+    for tx, ty in ((1.0, 0.0), (0.0, 1.0), (0.7, -0.3)):
+        t = torch.empty(n, dtype=torch.float64, device="cuda")
+        t[0::2], t[1::2] = tx, ty
+        y, z = be.empty(n), be.empty(n)
+        m["K"].mult(t, y)
+        scale = float(y.abs().max())
+        m["Krhs"].mult(t, z)
+        assert scale > 1.0 and float((y - z).abs().max()) < 1e-12 * scale, (tx, ty)
+        # free-slip stage: (K + Kfs - Krhsfs) t = 0
+        m["Kfs"].mult(t, y, mode=1)
+        m["Krhsfs"].mult(t, z)
+        assert float((y - z).abs().max()) < 1e-12 * scale, (tx, ty)
+
+
+def test_symmetry_linearity_and_operator_equivalence_at_full_size(prob):
+    import torch
+    be = prob.be
+    K = prob.mats["K"]
+    n = K.shape[0]
+    g = torch.Generator(device="cuda").manual_seed(11)
+    x = torch.randn(n, dtype=torch.float64, device="cuda", generator=g)
+    y = torch.randn(n, dtype=torch.float64, device="cuda", generator=g)
+    saved = K._tmat_asm
+    K.disable_templates()
+    Kx, Ky, Kz = be.empty(n), be.empty(n), be.empty(n)
+    K.mult(x, Kx)
+    K.mult(y, Ky)
+    s1, s2 = float(torch.dot(y, Kx)), float(torch.dot(x, Ky))
+    assert abs(s1 - s2) < 1e-12 * float(torch.linalg.vector_norm(y) * torch.linalg.vector_norm(Kx))
+    K.mult(2.5 * x - 0.75 * y, Kz)
+    assert _rel(Kz, 2.5 * Kx - 0.75 * Ky) < 1e-13
+    # the matrix-free element operator (csrc/tmat.cu) is the same operator
+    if saved is not None:
+        K._tmat_asm = saved
+    assert K.enable_templates() or saved is not None
+    K.mult(x, Kz)
+    assert _rel(Kz, Kx) < 1e-13
+    # ... also inside CG: ten iterations from the same right-hand side through either operator
+    b = Kx
+    xs = []
+    for use in (False, True):
+        if use:
+            K.enable_templates()
+        else:
+            K.disable_templates()
+        ksp = be.Ksp(K, "cg", "jacobi", rtol=1e-300, atol=1e-300, max_it=10, check_every=10)
+        assert (ksp._tm is not None) == use
+        sol = be.empty(n)
+        r = ksp.solve(b, sol)
+        assert r.its == 10
+        xs.append(sol.clone())
+        del ksp
+    assert _rel(xs[1], xs[0]) < 1e-10
+
+
+def test_assembly_is_deterministic_at_full_size(prob):
+    import torch
+    be = prob.be
+    K = prob.mats["K"]
+    first = K.data.clone()
+    prob.step()
+    assert torch.equal(prob.mats["K"].data, first)              # run to run
+    be.set_templates(False)                                      # generic gather kernels instead of the template stream
+    try:
+        prob.step()
+        assert torch.equal(prob.mats["K"].data, first)
+    finally:
+        be.set_templates(True)
+    d = prob.mats["K"].diagonal()
+    assert float(d.min()) > 0.0                                  # SPD after the unit diagonals on constrained dofs
