@@ -35,6 +35,8 @@ def parse_args():
     ap.add_argument("--nx", type=int, default=1024)
     ap.add_argument("--ngl", type=int, default=5)
     ap.add_argument("--ksp-its", type=int, default=50, dest="ksp_its")
+    ap.add_argument("--ksp-converge", type=float, default=0.0, dest="ksp_converge", metavar="RTOL",
+                    help="also run one CG+Jacobi solve to this rtol (PETSc default 1e-5) and report its / seconds")
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--cpu-sample-nx", type=int, default=96, dest="cpu_nx")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -434,6 +436,20 @@ def ksp_phase(a, prob, be, torch, peak, barrier):
                    f"are the CSR-stream leg (HBM-bound kernel the roofline applies to)"}
     if dc is not None:
         out["halo_bytes_per_iteration"] = dc.halo_bytes(2)
+    if a.ksp_converge > 0:
+        # time to solution of the reference's solve (KSPConvergedDefault, zero initial guess) with the default operator
+        ksp = be.Ksp(K, "cg", "jacobi", rtol=a.ksp_converge, max_it=1000000, check_every=200)
+        if dc is not None:
+            dc.attach(ksp, 2)
+        barrier()
+        s, e = ev(), ev()
+        s.record()
+        r = ksp.solve(rhs, x)
+        e.record()
+        torch.cuda.synchronize()
+        out["converged"] = {"rtol": a.ksp_converge, "its": int(r.its), "reason": int(r.reason),
+                            "seconds": s.elapsed_time(e) * 1e-3, "operator": out["operator"]}
+        del ksp
     return out
 
 
