@@ -372,8 +372,13 @@ int pyn_ksp_solve(pyn_ksp* k, const double* d_b, double* d_x, pyn_ksp_result* re
     PYN_CHECK_CUDA(cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal));
     int erc = PYN_OK;
     for (int i = 0; i < chunk && erc == PYN_OK; ++i) erc = enqueue_cg_iteration(k, cs);
+    if (erc != PYN_OK) {   // keep the message of the launch that failed, not the one of the aborted capture
+      cudaStreamEndCapture(cs, &g);
+      cudaGetLastError();
+      cudaStreamDestroy(cs);
+      return erc;
+    }
     PYN_CHECK_CUDA(cudaStreamEndCapture(cs, &g));
-    if (erc != PYN_OK) { cudaGraphDestroy(g); cudaStreamDestroy(cs); return erc; }
     PYN_CHECK_CUDA(cudaGraphInstantiate(&k->graph, g, 0));
     PYN_CHECK_CUDA(cudaGraphDestroy(g));
     PYN_CHECK_CUDA(cudaStreamDestroy(cs));
