@@ -282,7 +282,8 @@ asm_template_kernel(pyn::TopoView t, DescView d, double* __restrict__ T) {
   }
 }
 
-constexpr int ASM_SB = 64;  // nodes per CTA batch of the stream kernel
+constexpr int ASM_SB = 256;  // nodes per CTA batch of the stream kernel
+constexpr int ASM_SG = ASM_SB / 8;   // consecutive nodes per warp
 template <int RD, int CD>
 __global__ void __launch_bounds__(256)
 asm_stream_kernel(pyn::TopoView t, DescView d, const int64_t* __restrict__ indptr, const double* __restrict__ T,
@@ -305,25 +306,51 @@ asm_stream_kernel(pyn::TopoView t, DescView d, const int64_t* __restrict__ indpt
       s_rs[tid] = d.rowscale ? d.rowscale[r] : 1.0;
     }
     __syncthreads();
-    for (int j = w; j < nb; j += 8) {
-      const int n = s_len[j];
-      if (n == 0) continue;
-      const double* src = T + s_src[j];
-      double* dst = data + s_base[j];
-      const double rs = s_rs[j];
-      if (((s_base[j] | s_src[j] | n) & 1) == 0) {      // 16-byte aligned on both sides: double2 stores
-        const double2* s2 = reinterpret_cast<const double2*>(src);
-        double2* d2 = reinterpret_cast<double2*>(dst);
-        for (int i = lane; i < (n >> 1); i += 32) {
-          double2 v = __ldg(s2 + i);
-          if (d.rowscale) { v.x = rs * v.x; v.y = rs * v.y; }
+    // a warp takes ASM_SG consecutive nodes.  When their rows are equally long, adjacent in the CSR data and 16-byte
+    // aligned (runs of cell-interior or edge nodes: almost always), the group is ONE contiguous destination range:
+    // full-warp double2 stores, the source template found by a division -- short rows no longer leave lanes idle.
+    const int j0 = w * ASM_SG, cnt = min(ASM_SG, nb - j0);
+    if (cnt > 0) {
+      const int n0 = s_len[j0];
+      bool okl = true;
+      if (lane < cnt) {
+        const int j = j0 + lane;
+        okl = s_len[j] == n0 && s_base[j] == s_base[j0] + (int64_t)lane * n0 && ((s_src[j] | s_base[j0] | n0) & 1) == 0;
+      }
+      const bool uniform = n0 > 0 && __all_sync(0xffffffffu, okl);
+      if (uniform) {
+        const int n2 = n0 >> 1, total2 = cnt * n2;
+        const unsigned magic = (unsigned)((0x100000000ull + (unsigned)n2 - 1) / (unsigned)n2);
+        const double2* T2 = reinterpret_cast<const double2*>(T);
+        double2* d2 = reinterpret_cast<double2*>(data + s_base[j0]);
+        for (int i = lane; i < total2; i += 32) {
+          const int jj = (int)__umulhi((unsigned)i, magic), k = i - jj * n2;
+          double2 v = __ldg(T2 + (s_src[j0 + jj] >> 1) + k);
+          if (d.rowscale) { const double rs = s_rs[j0 + jj]; v.x = rs * v.x; v.y = rs * v.y; }
           d2[i] = v;
         }
       } else {
-        for (int i = lane; i < n; i += 32) {
-          double v = __ldg(src + i);
-          if (d.rowscale) v = rs * v;
-          dst[i] = v;
+        for (int j = j0; j < j0 + cnt; ++j) {
+          const int n = s_len[j];
+          if (n == 0) continue;
+          const double* src = T + s_src[j];
+          double* dst = data + s_base[j];
+          const double rs = s_rs[j];
+          if (((s_base[j] | s_src[j] | n) & 1) == 0) {      // 16-byte aligned on both sides: double2 stores
+            const double2* s2 = reinterpret_cast<const double2*>(src);
+            double2* d2 = reinterpret_cast<double2*>(dst);
+            for (int i = lane; i < (n >> 1); i += 32) {
+              double2 v = __ldg(s2 + i);
+              if (d.rowscale) { v.x = rs * v.x; v.y = rs * v.y; }
+              d2[i] = v;
+            }
+          } else {
+            for (int i = lane; i < n; i += 32) {
+              double v = __ldg(src + i);
+              if (d.rowscale) v = rs * v;
+              dst[i] = v;
+            }
+          }
         }
       }
     }
