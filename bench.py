@@ -484,7 +484,7 @@ def e2e_phase(a, prob, be, torch, barrier):
         one(i)
     main.wait_stream(side)
     barrier()
-    steps = max(3, min(a.steps, 5))
+    steps = max(3, min(a.steps, 20))
     s, e = ev(), ev()
     s.record()
     for i in range(steps):

@@ -162,6 +162,12 @@ int pyn_csr_add_fill(int64_t nrows, const int64_t* d_aptr, const int32_t* d_aind
                      const int64_t* d_cptr, int32_t* d_cind, double* d_cval, void* stream);
 int pyn_csr_diagonal(int64_t nrows, const int64_t* d_ptr, const int32_t* d_ind, const double* d_val,
                      double* d_diag, void* stream);
+/* The same for a pattern that is re-used (values-only re-assembly): pyn_csr_diag_offsets finds, once, the offset of the
+ * diagonal entry inside every row (-1: the row stores none); pyn_csr_diagonal_at then gathers diag[r] =
+ * val[ptr[r] + off[r]] without searching. */
+int pyn_csr_diag_offsets(int64_t nrows, const int64_t* d_ptr, const int32_t* d_ind, int32_t* d_off, void* stream);
+int pyn_csr_diagonal_at(int64_t nrows, const int64_t* d_ptr, const int32_t* d_off, const double* d_val, double* d_diag,
+                        void* stream);
 /* drop stored zeros (compressed operator pattern for the timed SpMV): count then fill */
 int pyn_csr_compress_count(int64_t nrows, const int64_t* d_ptr, const double* d_val, int64_t* d_optr, int64_t* h_nnz,
                            void* stream);

@@ -66,6 +66,8 @@ _SIGNATURES = {
     "pyn_csr_add_count": (C.c_int, [c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, P(c_i64), c_vp]),
     "pyn_csr_add_fill": (C.c_int, [c_i64, c_vp, c_vp, c_vp, c_f64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "pyn_csr_diagonal": (C.c_int, [c_i64, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "pyn_csr_diag_offsets": (C.c_int, [c_i64, c_vp, c_vp, c_vp, c_vp]),
+    "pyn_csr_diagonal_at": (C.c_int, [c_i64, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "pyn_csr_compress_count": (C.c_int, [c_i64, c_vp, c_vp, c_vp, P(c_i64), c_vp]),
     "pyn_csr_compress_fill": (C.c_int, [c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "pyn_spmv": (C.c_int, [c_i64, c_vp, c_vp, c_vp, c_i64, c_vp, c_vp, C.c_int, c_f64, c_f64, c_vp, c_vp]),

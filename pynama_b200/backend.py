@@ -253,6 +253,7 @@ class CSR:
     def __init__(self, shape, indptr, indices, data, name=""):
         self.shape, self.indptr, self.indices, self.data, self.name = tuple(shape), indptr, indices, data, name
         self._plan = None
+        self._diag_off = None     # [offsets of the diagonal entries] (a shared cell: see diagonal())
         self._asm = None          # (topology, descriptor, keep-alive refs) when produced by assemble()
         self._tmat = None         # template operator, built on first use when enabled
         self._tmat_asm = None     # assembly record the templates come from (own or another matrix's), None = off
@@ -304,8 +305,17 @@ class CSR:
         return y
 
     def diagonal(self):
+        """diag(A) (MatGetDiagonal).  The offset of the diagonal entry inside every row is found once per sparsity
+        pattern and shared by the matrices re-assembled on it; later calls are a plain gather."""
         d = empty(self.shape[0])
-        call("pyn_csr_diagonal", self.shape[0], ptr(self.indptr), ptr(self.indices), ptr(self.data), ptr(d), stream())
+        if self._diag_off is None:
+            self._diag_off = [None]
+        if self._diag_off[0] is None:
+            off = empty(self.shape[0], I32)
+            call("pyn_csr_diag_offsets", self.shape[0], ptr(self.indptr), ptr(self.indices), ptr(off), stream())
+            self._diag_off[0] = off
+        call("pyn_csr_diagonal_at", self.shape[0], ptr(self.indptr), ptr(self._diag_off[0]), ptr(self.data), ptr(d),
+             stream())
         return d
 
     def add(self, other, alpha=1.0, name=""):
@@ -411,6 +421,9 @@ def assemble(topo, rdof, cdof, E, rclass=None, cclass=None, pairs=ALL_PAIRS, dia
     out._asm = (topo, d, keep)
     if pattern is not None:
         out._plan = pattern._plan
+        if pattern._diag_off is None:
+            pattern._diag_off = [None]
+        out._diag_off = pattern._diag_off
         if pattern._tmat_asm is not None and pattern._tmat_asm is pattern._asm:
             out._tmat_asm = out._asm
     return out

@@ -460,6 +460,26 @@ __global__ void csr_diag_kernel(int64_t nrows, const int64_t* __restrict__ p, co
   }
 }
 
+__global__ void csr_diag_offsets_kernel(int64_t nrows, const int64_t* __restrict__ p, const int* __restrict__ ind,
+                                        int* __restrict__ off) {
+  for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < nrows; r += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t b = p[r], e = p[r + 1];
+    int64_t lo = b, hi = e;
+    while (lo < hi) {
+      const int64_t mid = (lo + hi) >> 1;
+      if (ind[mid] < r) lo = mid + 1; else hi = mid;
+    }
+    off[r] = (lo < e && ind[lo] == r) ? (int)(lo - b) : -1;
+  }
+}
+__global__ void csr_diag_at_kernel(int64_t nrows, const int64_t* __restrict__ p, const int* __restrict__ off,
+                                   const double* __restrict__ val, double* __restrict__ diag) {
+  for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < nrows; r += (int64_t)gridDim.x * blockDim.x) {
+    const int o = off[r];
+    diag[r] = o >= 0 ? val[p[r] + o] : 0.0;
+  }
+}
+
 template <bool COUNT>
 __global__ void csr_compress_kernel(int64_t nrows, const int64_t* __restrict__ p, const int* __restrict__ ind,
                                     const double* __restrict__ val, int* __restrict__ cnt,
@@ -789,6 +809,21 @@ int pyn_csr_add_fill(int64_t nrows, const int64_t* ap, const int32_t* ai, const 
 int pyn_csr_diagonal(int64_t nrows, const int64_t* p, const int32_t* ind, const double* val, double* diag, void* stream) {
   PYN_REQUIRE(nrows > 0 && p && ind && val && diag, "bad arguments");
   csr_diag_kernel<<<pyn::grid_for(nrows, 256), 256, 0, pyn::as_stream(stream)>>>(nrows, p, ind, val, diag);
+  PYN_CHECK_LAUNCH();
+  return PYN_OK;
+}
+
+int pyn_csr_diag_offsets(int64_t nrows, const int64_t* p, const int32_t* ind, int32_t* off, void* stream) {
+  PYN_REQUIRE(nrows > 0 && p && ind && off, "bad arguments");
+  csr_diag_offsets_kernel<<<pyn::grid_for(nrows, 256), 256, 0, pyn::as_stream(stream)>>>(nrows, p, ind, off);
+  PYN_CHECK_LAUNCH();
+  return PYN_OK;
+}
+
+int pyn_csr_diagonal_at(int64_t nrows, const int64_t* p, const int32_t* off, const double* val, double* diag,
+                        void* stream) {
+  PYN_REQUIRE(nrows > 0 && p && off && val && diag, "bad arguments");
+  csr_diag_at_kernel<<<pyn::grid_for(nrows, 256), 256, 0, pyn::as_stream(stream)>>>(nrows, p, off, val, diag);
   PYN_CHECK_LAUNCH();
   return PYN_OK;
 }

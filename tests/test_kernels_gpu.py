@@ -455,3 +455,32 @@ def test_taylor_green_known_answer_gpu(be):
     err = sol - vel_ex
     assert be.vec_norm(err) < 2e-8
     del tmp
+
+
+def test_diagonal_cached_offsets(be):
+    """CSR.diagonal() (offsets found once per pattern, then a gather) equals the searching kernel and the oracle, also
+    after a values-only re-assembly on the same pattern and for rows without a stored diagonal."""
+    import torch
+    from pynama_b200 import _lib
+    m = o.BoxMesh([7, 6], [0, 0], [1, 1], 4)
+    ref = o.assemble_noslip(m)
+    topo = be.Topology(be.box_cell_nodes(7, 6, 4), m.nnodes)
+    cls = _upload_classes(be, ref["cls"])
+    Ke = be.to_device(o.elem_kle_matrices(4, m.cell_corner_coords([0]))[0])
+    m22 = be.BcMap(topo, cls, 2, cls, 2)
+    for name, kw in (("K", dict(pairs=[(0, 0)], diag_classes=0b110, diag_add=(0, 1.0, 1.0, 0))),
+                     ("Krhs", dict(pairs=[(0, 1), (0, 2)], diag_classes=0b110, diag_add=(0, 1.0, 1.0, 0), sign=-1.0))):
+        A = be.assemble(topo, 2, 2, Ke, cls, cls, bcmap=m22, **kw)
+        want = ref[name].diagonal()
+        d1 = A.diagonal().cpu().numpy()
+        d0 = be.empty(A.shape[0])
+        _lib.call("pyn_csr_diagonal", A.shape[0], be.ptr(A.indptr), be.ptr(A.indices), be.ptr(A.data), be.ptr(d0),
+                  be.stream())
+        assert np.array_equal(d1, d0.cpu().numpy())
+        assert np.allclose(d1, want, rtol=1e-12, atol=0)
+        B = be.assemble(topo, 2, 2, 2.0 * Ke, cls, cls, bcmap=m22, pattern=A, **kw)
+        assert B._diag_off is A._diag_off and A._diag_off[0] is not None
+        dB = B.diagonal().cpu().numpy()
+        if name == "K":
+            free = np.asarray(ref["cls"]).reshape(-1) == 0
+            assert np.allclose(dB[free], 2.0 * want[free], rtol=1e-12)
