@@ -143,6 +143,12 @@ int pyn_asm_fill(const pyn_topo* t, const pyn_asm_desc* desc, const int64_t* d_i
  * few distinct row signatures, a values-only pyn_asm_fill computes each distinct interior row once and streams it to all
  * the nodes that share it (bit-identical to the gather kernel).  pyn_asm_set_templates(0) forces the gather kernel. */
 int pyn_asm_set_templates(int enabled);
+/* A values-only pyn_asm_fill runs its boundary-list kernel on a side stream of the topology handle, overlapped with the
+ * interior rows, and joins it before returning.  pyn_asm_defer_join(1) postpones that join so that a batch of fills
+ * (the eight matrices of base_problem.py:329-454) overlaps as a whole; the caller then MUST call pyn_asm_join(t, stream)
+ * before anything reads the matrices, and pyn_asm_defer_join(0) afterwards. */
+int pyn_asm_defer_join(int enabled);
+int pyn_asm_join(const pyn_topo* t, void* stream);
 int pyn_topo_signatures(const pyn_topo* t, int* nsig, int64_t* template_slots);
 /* lumped weights  W[node] = sum_e W_e[local]  in ascending cell order  (mat_generator.py:168-170) */
 int pyn_asm_weights(const pyn_topo* t, const double* d_We, int64_t We_stride, double* d_W, void* stream);

@@ -59,6 +59,8 @@ _SIGNATURES = {
     "pyn_asm_count": (C.c_int, [c_vp, P(AsmDesc), c_vp, P(c_i64), c_vp]),
     "pyn_asm_fill": (C.c_int, [c_vp, P(AsmDesc), c_vp, c_vp, c_vp, c_vp]),
     "pyn_asm_set_templates": (C.c_int, [C.c_int]),
+    "pyn_asm_defer_join": (C.c_int, [C.c_int]),
+    "pyn_asm_join": (C.c_int, [c_vp, c_vp]),
     "pyn_topo_signatures": (C.c_int, [c_vp, P(C.c_int), P(c_i64)]),
     "pyn_asm_weights": (C.c_int, [c_vp, c_vp, c_i64, c_vp, c_vp]),
     "pyn_coo_count": (C.c_int, [c_i64, c_vp, c_vp, c_i64, c_i64, c_vp, P(c_i64), P(c_vp), c_vp]),

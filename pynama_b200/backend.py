@@ -178,6 +178,23 @@ class BcMap:
             pass
 
 
+class assembly_batch:
+    """`with assembly_batch(topo): ...` -- the values-only assemble() calls inside run their boundary-list kernels on
+    the topology's side stream and are joined once at the end (pyn_asm_defer_join / pyn_asm_join)."""
+
+    def __init__(self, topo):
+        self.topo = topo
+
+    def __enter__(self):
+        call("pyn_asm_defer_join", 1)
+        return self
+
+    def __exit__(self, *exc):
+        call("pyn_asm_defer_join", 0)
+        call("pyn_asm_join", self.topo._h, stream())
+        return False
+
+
 def set_templates(enabled):
     """Enable/disable the row-template fast path of the values-only assembly (pyn_asm_set_templates)."""
     call("pyn_asm_set_templates", 1 if enabled else 0)

@@ -1,3 +1,4 @@
+#include <stdlib.h>
 // Deterministic global assembly into CSR.
 //
 // Row-gather formulation (no atomics): one warp owns one mesh node = `rdof` consecutive matrix rows.  It walks the
@@ -637,6 +638,7 @@ static int launch_templates(const pyn_topo* t, const DescView& dv, const int64_t
 }
 
 // the interior fast path applies when a map is given and class-0 rows carry no forced diagonal
+static bool g_defer_join = false;    // pyn_asm_defer_join(1): a batch of fills joins the side stream once (pyn_asm_join)
 static bool g_no_templates = false;  // pyn_asm_set_templates(0): force the generic gather kernel (tests, comparisons)
 static inline bool use_map(const pyn_asm_desc* desc) { return desc->bcmap != nullptr && !(desc->diag_classes & 1u); }
 
@@ -720,6 +722,39 @@ int pyn_asm_count(const pyn_topo* t, const pyn_asm_desc* desc, int64_t* d_indptr
   return rc;
 }
 
+// boundary-list kernel of a values-only fill on the topology's side stream, ordered after the caller's stream so far
+static int fork_boundary(const pyn_topo* t, const DescView& dv, const int* list, int64_t nlist, const int64_t* indptr,
+                         double* data, cudaStream_t st) {
+  pyn_topo* tm = const_cast<pyn_topo*>(t);   // one host thread per handle
+  if (!tm->side) {
+    PYN_CHECK_CUDA(cudaStreamCreateWithFlags(&tm->side, cudaStreamNonBlocking));
+    PYN_CHECK_CUDA(cudaEventCreateWithFlags(&tm->ev_fork, cudaEventDisableTiming));
+    PYN_CHECK_CUDA(cudaEventCreateWithFlags(&tm->ev_join, cudaEventDisableTiming));
+  }
+  PYN_CHECK_CUDA(cudaEventRecord(tm->ev_fork, st));
+  PYN_CHECK_CUDA(cudaStreamWaitEvent(tm->side, tm->ev_fork, 0));
+  const int rc = launch_asm<false>(t, dv, list, nlist, nullptr, indptr, nullptr, data, tm->side);
+  if (rc) return rc;
+  PYN_CHECK_CUDA(cudaEventRecord(tm->ev_join, tm->side));
+  tm->pending = 1;
+  return PYN_OK;
+}
+
+int pyn_asm_join(const pyn_topo* t, void* stream) {
+  PYN_REQUIRE(t, "topo is NULL");
+  pyn_topo* tm = const_cast<pyn_topo*>(t);
+  if (tm->pending) {
+    PYN_CHECK_CUDA(cudaStreamWaitEvent(pyn::as_stream(stream), tm->ev_join, 0));
+    tm->pending = 0;
+  }
+  return PYN_OK;
+}
+
+int pyn_asm_defer_join(int enabled) {
+  g_defer_join = enabled != 0;
+  return PYN_OK;
+}
+
 int pyn_asm_fill(const pyn_topo* t, const pyn_asm_desc* desc, const int64_t* d_indptr, int32_t* d_indices,
                  double* d_data, void* stream) {
   PYN_REQUIRE(t && d_indptr, "bad arguments");
@@ -733,8 +768,21 @@ int pyn_asm_fill(const pyn_topo* t, const pyn_asm_desc* desc, const int64_t* d_i
     if ((dv.pair_mask & 1u) && (d_data || d_indices)) {
       // values on a known pattern, one element matrix for all cells, repetitive mesh: stream the row templates
       const bool tmpl = d_data && !d_indices && dv.E_stride == 0 && t->nsig > 0 && !g_no_templates;
+      // values-only re-assembly: the boundary list goes to the side stream first, so that it overlaps the interior
+      // rows written on the caller's stream (disjoint rows; both read the same element matrix)
+      const bool overlap = d_data && !d_indices && desc->bcmap->nlist > 0 && !getenv("PYN_ASM_NO_OVERLAP");
+      if (overlap) {
+        rc = fork_boundary(t, dv, desc->bcmap->list, desc->bcmap->nlist, d_indptr, d_data, st);
+        if (rc) return rc;
+      }
       rc = tmpl ? launch_templates(t, dv, d_indptr, d_data, st) : launch_interior(t, dv, d_indptr, d_indices, d_data, st);
       if (rc) return rc;
+      if (overlap) return g_defer_join ? PYN_OK : pyn_asm_join(t, stream);
+    } else if (d_data && !d_indices && desc->bcmap->nlist > 0 && !getenv("PYN_ASM_NO_OVERLAP")) {
+      // boundary-only matrix inside a batch: side stream as well, joined with the batch
+      rc = fork_boundary(t, dv, desc->bcmap->list, desc->bcmap->nlist, d_indptr, d_data, st);
+      if (rc) return rc;
+      return g_defer_join ? PYN_OK : pyn_asm_join(t, stream);
     }
     return launch_asm<false>(t, dv, desc->bcmap->list, desc->bcmap->nlist, nullptr, d_indptr, d_indices, d_data, st);
   }

@@ -25,6 +25,11 @@ struct pyn_topo {
   int64_t* sig_ptr;   // [nsig+1] offsets of the templates in adjacency slots
   int64_t sig_slots;
   double* sig_tmpl;    // [sig_slots * 9] scratch for the row templates of the matrix being assembled (lazy)
+  // Side stream of the values-only assembly: the boundary-list kernels (short, dependent-latency bound) run there
+  // while the caller's stream writes the interior rows.  `pending`: side work not yet joined (pyn_asm_join).
+  cudaStream_t side;
+  cudaEvent_t ev_fork, ev_join;
+  int pending;
 };
 
 struct pyn_bcmap {

@@ -107,13 +107,14 @@ class MatNS(Mat):
             corners = dom.deviceCellCorners(0, 1)
         Ke, Rwe, Rde = elemType.getElemKLEMatricesDevice(corners, want_rd=True)
         E = {"K": Ke, "Rw": Rwe, "Rd": Rde}
-        for name in (names or NS_DESCRIPTORS):
-            cd, which, pairs, dcls, dadd, sign = NS_DESCRIPTORS[name]
-            m = getattr(self, name)
-            csr = be.assemble(topo, 2, cd, E[which], self.rowClasses, classes if cd == 2 else None, pairs, diag_classes=dcls,
-                              diag_add=dadd, sign=sign, pattern=m.csr, inplace=True, name=name,
-                              bcmap=self._maps[0] if cd == 2 else self._maps[1])
-            m.csr, m.shape = csr, csr.shape
-            if templatesWanted():
-                csr.enable_templates()
+        with be.assembly_batch(topo):     # boundary-list kernels of all matrices overlap the interior streams
+            for name in (names or NS_DESCRIPTORS):
+                cd, which, pairs, dcls, dadd, sign = NS_DESCRIPTORS[name]
+                m = getattr(self, name)
+                csr = be.assemble(topo, 2, cd, E[which], self.rowClasses, classes if cd == 2 else None, pairs,
+                                  diag_classes=dcls, diag_add=dadd, sign=sign, pattern=m.csr, inplace=True, name=name,
+                                  bcmap=self._maps[0] if cd == 2 else self._maps[1])
+                m.csr, m.shape = csr, csr.shape
+                if templatesWanted():
+                    csr.enable_templates()
         self._unit_diagonals_folded = True
