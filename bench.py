@@ -212,11 +212,11 @@ class CavityAssembly:
         m, fem = self.mat, self.fem
         if events is not None:
             events[0].record()
-        m.assembleFromMesh(fem.dom, fem.elemType, names=("K",), classes=classes if classes is not None else m.dofClasses,
-                           rowClassesDev=row_classes, corners=corners)
-        if events is not None:
-            events[1].record()
-        m.assembleFromMesh(fem.dom, fem.elemType, names=self.NAMES[1:], classes=m.dofClasses, corners=corners)
+        # one element integration, then the eight matrices; events[1] closes the K launches (template + stream on this
+        # stream; K's boundary list runs beside them on the side stream)
+        m.assembleFromMesh(fem.dom, fem.elemType, names=self.NAMES, classes=classes if classes is not None else m.dofClasses,
+                           rowClassesDev=row_classes, corners=corners,
+                           after={"K": events[1].record} if events is not None else None)
         return self.mats
 
 

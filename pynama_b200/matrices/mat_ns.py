@@ -86,11 +86,12 @@ class MatNS(Mat):
         host = noSlipDofClasses(dom, self.globalIndicesNS, self.globalIndicesDIR)
         return host, rowClasses(dom, host, 2)
 
-    def assembleFromMesh(self, dom, elemType, names=None, classes=None, rowClassesDev=None, corners=None):
+    def assembleFromMesh(self, dom, elemType, names=None, classes=None, rowClassesDev=None, corners=None, after=None):
         """NoSlipFreeSlip.buildKLEMats for the whole mesh on the device (cell 0's element matrices for every cell,
         base_problem.py:333-334).  `names` restricts the matrices (default: all eight); re-assembly on an existing
         pattern rewrites values only.  `classes` / `rowClassesDev` (device int8, from `hostDofClasses`) and `corners`
-        (device (1,4,2) corner coordinates of cell 0) let a caller feed the inputs from host buffers."""
+        (device (1,4,2) corner coordinates of cell 0) let a caller feed the inputs from host buffers.  `after`:
+        optional {name: callable}, called right after that matrix's kernels are enqueued (timing events)."""
         topo = dom.topology()
         if classes is None:
             host, hostRows = self.hostDofClasses(dom)
@@ -117,4 +118,6 @@ class MatNS(Mat):
                 m.csr, m.shape = csr, csr.shape
                 if templatesWanted():
                     csr.enable_templates()
+                if after and name in after:
+                    after[name]()
         self._unit_diagonals_folded = True
