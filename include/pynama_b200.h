@@ -245,6 +245,8 @@ int pyn_vec_wrms(int64_t n, const double* d_err, const double* d_y, const double
  * Krylov solvers with PETSc semantics (KspSolver, src/solver/ksp_solver.py:9-19; use sites
  * base_problem.py:276,318,323-327,481): zero initial guess, left preconditioning, preconditioned residual
  * norm, KSPConvergedDefault.  reason: 2 rtol, 3 atol, -3 max_it, -4 dtol, -8 indefinite.
+ * nonzero_guess (CG; PETSc's -ksp_initial_guess_nonzero): d_x holds x0 on entry, r0 = b - A x0, and rtol is
+ * measured against |M^-1 b| (the initial residual when b = 0), as KSPConvergedDefault does.
  * ---------------------------------------------------------------------------------------------------- */
 typedef struct pyn_ksp pyn_ksp;
 typedef struct {
@@ -254,7 +256,7 @@ typedef struct {
   int32_t max_it;
   int32_t restart;     /* gmres */
   int32_t check_every; /* iterations between host polls of the device convergence flag (0 = default) */
-  int32_t nonzero_guess;
+  int32_t nonzero_guess; /* cg only: start from the contents of d_x */
 } pyn_ksp_opts;
 typedef struct {
   int32_t its, reason;

@@ -543,18 +543,28 @@ def assemble_operators(mesh):
 # --------------------------------------------------------------------------------------------------------
 # S1  KSP: CG + Jacobi with PETSc semantics (restated from PETSc KSPCG / KSPConvergedDefault docs)
 # --------------------------------------------------------------------------------------------------------
-def ksp_cg_jacobi(A, b, rtol=1e-5, atol=1e-50, dtol=1e4, max_it=10000, jacobi=True):
+def ksp_cg_jacobi(A, b, rtol=1e-5, atol=1e-50, dtol=1e4, max_it=10000, jacobi=True, x0=None):
     """Left-preconditioned CG, zero initial guess, monitored norm ||M^-1 r||_2, default convergence test
     rnorm <= max(rtol*rnorm0, atol) (src/solver/ksp_solver.py:9-19 with -ksp_type cg -pc_type jacobi).
-    Returns x, iterations, reason (2 rtol, 3 atol, -3 its, -4 dtol), residual history."""
+    x0 (-ksp_initial_guess_nonzero): r0 = b - A x0 and, as in KSPConvergedDefault, rnorm0 = ||M^-1 b|| (the initial
+    residual if b = 0).  Returns x, iterations, reason (2 rtol, 3 atol, -3 its, -4 dtol), residual history."""
     n = A.shape[0]
     dinv = 1.0 / A.diagonal() if jacobi else np.ones(n)
-    x = np.zeros(n)
-    r = b.copy()
+    if x0 is None:
+        x = np.zeros(n)
+        r = b.copy()
+    else:
+        x = np.array(x0, dtype=float)
+        r = b - A @ x
     z = dinv * r
     dp = math.sqrt(z @ z)
     hist = [dp]
-    ttol = max(rtol * dp, atol)
+    rnorm0 = dp
+    if x0 is not None:
+        zb = dinv * b
+        snorm = math.sqrt(zb @ zb)
+        rnorm0 = snorm if snorm > 0.0 else dp
+    ttol = max(rtol * rnorm0, atol)
     if dp <= ttol:
         return x, 0, (3 if dp <= atol else 2), hist
     beta = z @ r
@@ -579,7 +589,7 @@ def ksp_cg_jacobi(A, b, rtol=1e-5, atol=1e-50, dtol=1e4, max_it=10000, jacobi=Tr
         if dp <= ttol:
             reason = 3 if dp <= atol else 2
             break
-        if dp >= dtol * hist[0]:
+        if dp >= dtol * rnorm0:
             reason = -4
             break
         beta = z @ r

@@ -473,11 +473,14 @@ class Ksp:
     PCS = {"none": 0, "jacobi": 1}
 
     def __init__(self, A: CSR, ksp_type="cg", pc="jacobi", rtol=1e-5, atol=1e-50, dtol=1e4, max_it=10000,
-                 restart=30, check_every=0):
+                 restart=30, check_every=0, nonzero_guess=False):
+        if nonzero_guess and ksp_type != "cg":
+            raise Exception("-ksp_initial_guess_nonzero is available with -ksp_type cg on the device path")
         self.A = A
         o = KspOpts()
         o.type, o.pc = self.TYPES[ksp_type], self.PCS[pc]
-        o.rtol, o.atol, o.dtol, o.max_it, o.restart, o.check_every, o.nonzero_guess = rtol, atol, dtol, max_it, restart, check_every, 0
+        o.rtol, o.atol, o.dtol, o.max_it, o.restart, o.check_every = rtol, atol, dtol, max_it, restart, check_every
+        o.nonzero_guess = 1 if nonzero_guess else 0
         self.opts = o
         self._h = C.c_void_p()
         call("pyn_ksp_create", A.shape[0], ptr(A.indptr), ptr(A.indices), ptr(A.data), A.nnz, C.byref(o), stream(),

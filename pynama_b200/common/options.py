@@ -53,6 +53,20 @@ class Options(object):
     def getReal(self, key, default=None):
         return float(Options._db[key]) if key in Options._db else default
 
+    def getBool(self, key, default=None):
+        """PETSc spelling: a bare `-flag` is true; otherwise 1/0, true/false, yes/no, on/off."""
+        if key not in Options._db:
+            return default
+        v = Options._db[key]
+        if isinstance(v, bool):
+            return v
+        s = str(v).strip().lower()
+        if s in ("1", "true", "yes", "on"):
+            return True
+        if s in ("0", "false", "no", "off"):
+            return False
+        raise Exception(f"option -{key}: cannot read '{v}' as a boolean")
+
 
 def _is_number(s):
     try:

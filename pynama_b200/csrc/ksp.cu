@@ -1,5 +1,5 @@
 // Krylov solvers on device with PETSc semantics (KSPCG / KSPGMRES + KSPConvergedDefault, left preconditioning,
-// preconditioned residual norm, zero initial guess) -- replaces KspSolver (src/solver/ksp_solver.py:9-19).
+// preconditioned residual norm, zero or (CG) nonzero initial guess) -- replaces KspSolver (src/solver/ksp_solver.py:9-19).
 //
 // Control flow lives on the device: every kernel of an iteration starts by reading a `done` flag in a small state
 // block, so a whole chunk of iterations can be enqueued (as one CUDA graph) without the host knowing whether
@@ -59,15 +59,55 @@ __global__ void cg_reduce_kernel(int nparts, const double* __restrict__ pa, cons
   }
 }
 
-// g (multi-GPU only): global sums [p.w, z.z, z.r] produced by cg_reduce_kernel + all-reduce
-__global__ void cg_scalar_init_kernel(int nparts, CgBuffers B, double rtol, double atol, const double* __restrict__ g) {
+// nonzero initial guess (-ksp_initial_guess_nonzero): clear the flags of the previous solve so the product kernels run
+__global__ void cg_reset_kernel(KspState* s) {
+  s->done = 0;
+  s->its = 0;
+  s->reason = 0;
+}
+
+// ... then, with p = x0 and w = A p:  r = b - w, x = x0, z = M^-1 r; partials of z.z, z.r and |M^-1 b|^2 (KSPCG:
+// KSP_MatMult + VecAYPX; KSPConvergedDefault measures rtol against the preconditioned right-hand side in this case)
+__global__ void cg_init_guess_kernel(int64_t n, const double* __restrict__ b, CgBuffers B,
+                                     const uint8_t* __restrict__ owned, double* __restrict__ part_c) {
+  __shared__ double sm[BLK / 32];
+  double szz = 0.0, szr = 0.0, sbb = 0.0;
+  for (int64_t i = blockIdx.x * (int64_t)BLK + threadIdx.x; i < n; i += (int64_t)gridDim.x * BLK) {
+    const bool mine = !(owned && !owned[i]);
+    const double bi = mine ? b[i] : 0.0;
+    const double r = mine ? bi - B.w[i] : 0.0;
+    const double d = B.dinv[i];
+    const double z = d * r, zb = d * bi;
+    B.r[i] = r;
+    B.z[i] = z;
+    B.x[i] = B.p[i];
+    szz += z * z;
+    szr += z * r;
+    sbb += zb * zb;
+  }
+  szz = pyn::block_sum<BLK>(szz, sm);
+  szr = pyn::block_sum<BLK>(szr, sm);
+  sbb = pyn::block_sum<BLK>(sbb, sm);
+  if (threadIdx.x == 0) {
+    B.part_a[blockIdx.x] = szz;
+    B.part_b[blockIdx.x] = szr;
+    part_c[blockIdx.x] = sbb;
+  }
+}
+
+// g (multi-GPU only): global sums [p.w, z.z, z.r, |M^-1 b|^2] produced by cg_reduce_kernel + all-reduce
+// part_c (nonzero initial guess only): partials of |M^-1 b|^2
+__global__ void cg_scalar_init_kernel(int nparts, CgBuffers B, double rtol, double atol, const double* __restrict__ g,
+                                      const double* __restrict__ part_c) {
   const double zz = g ? g[1] : pyn::reduce_partials(B.part_a, nparts);
   const double zr = g ? g[2] : pyn::reduce_partials(B.part_b, nparts);
+  double bb = -1.0;
+  if (part_c) bb = g ? g[3] : pyn::reduce_partials(part_c, nparts);
   if (threadIdx.x == 0) {
     KspState* s = B.st;
     s->dp = sqrt(zz);
-    s->rnorm0 = s->dp;
-    s->ttol = fmax(rtol * s->dp, atol);
+    s->rnorm0 = bb > 0.0 ? sqrt(bb) : s->dp;   // zero right-hand side with a nonzero guess: the initial residual
+    s->ttol = fmax(rtol * s->rnorm0, atol);
     s->beta = zr;
     s->betaold = 1.0;
     s->its = 0;
@@ -262,10 +302,9 @@ __global__ void copy_kernel(int64_t n, const double* __restrict__ src, double* _
 
 namespace {
 
-int enqueue_cg_iteration(const pyn_ksp* k, cudaStream_t st) {
+// w = A p (+ per-CTA partials of p.w in part_a, *npw of them); ghost entries of p fetched first on N ranks
+int enqueue_cg_product(const pyn_ksp* k, cudaStream_t st, int* npw_out) {
   const bool dist = k->comm && k->comm->world > 1;
-  const double* g = dist ? k->gsum : nullptr;
-  cg_pupdate_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, k->B);
   if (dist) {  // ghost entries of p <- their owners (MPIAIJ MatMult's VecScatter in the reference)
     int rc = pyn::halo_exchange(k->halo, k->B.p, k->halo_comp, st);
     if (rc) return rc;
@@ -283,6 +322,19 @@ int enqueue_cg_iteration(const pyn_ksp* k, cudaStream_t st) {
     npw = gi;
   } else {
     cg_spmv_dot_kernel<<<k->sgrid, pyn::SP_BLK, 0, st>>>(pyn::view_of(k->plan), k->ind, k->val, k->B);
+  }
+  *npw_out = npw;
+  return PYN_OK;
+}
+
+int enqueue_cg_iteration(const pyn_ksp* k, cudaStream_t st) {
+  const bool dist = k->comm && k->comm->world > 1;
+  const double* g = dist ? k->gsum : nullptr;
+  cg_pupdate_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, k->B);
+  int npw = 0;
+  {
+    int rc = enqueue_cg_product(k, st, &npw);
+    if (rc) return rc;
   }
   if (dist) {
     cg_reduce_kernel<<<1, 32, 0, st>>>(npw, k->B.part_a, nullptr, k->gsum);
@@ -308,7 +360,7 @@ int pyn_ksp_create(int64_t nrows, const int64_t* d_ptr, const int32_t* d_ind, co
                    const pyn_ksp_opts* opts, void* stream, pyn_ksp** out) {
   PYN_REQUIRE(nrows > 0 && d_ptr && d_ind && d_val && opts && out, "bad arguments");
   PYN_REQUIRE(opts->type == 0 || opts->type == 1, "ksp type must be 0 (cg) or 1 (gmres)");
-  PYN_REQUIRE(opts->nonzero_guess == 0, "nonzero initial guess is not supported (PETSc default is zero)");
+  PYN_REQUIRE(opts->nonzero_guess == 0 || opts->type == 0, "nonzero initial guess is wired into CG only");
   cudaStream_t st = pyn::as_stream(stream);
   pyn_ksp* k = new pyn_ksp();
   memset(k, 0, sizeof(*k));
@@ -351,15 +403,28 @@ int pyn_ksp_solve(pyn_ksp* k, const double* d_b, double* d_x, pyn_ksp_result* re
   if (k->opts.type == 1) return pyn::gmres_solve(k, d_b, d_x, res, st);
   int64_t launches = 0;
   const bool dist = k->comm && k->comm->world > 1;
-  cg_init_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, d_b, k->B, dist ? k->owned : nullptr);
+  const bool guess = k->opts.nonzero_guess != 0;
+  if (guess) {   // r0 = b - A x0 with the contents of d_x (KSPSetInitialGuessNonzero)
+    cg_reset_kernel<<<1, 1, 0, st>>>(k->B.st);
+    copy_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, d_x, k->B.p);
+    int npw = 0;
+    int rc = enqueue_cg_product(k, st, &npw);
+    if (rc) return rc;
+    cg_init_guess_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, d_b, k->B, dist ? k->owned : nullptr, k->pzz);
+    launches += 4;
+  } else {
+    cg_init_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, d_b, k->B, dist ? k->owned : nullptr);
+  }
   PYN_CHECK_LAUNCH();
   if (dist) {
     cg_reduce_kernel<<<1, 32, 0, st>>>(k->vgrid, k->B.part_a, k->B.part_b, k->gsum + 1);
+    if (guess) cg_reduce_kernel<<<1, 32, 0, st>>>(k->vgrid, k->pzz, nullptr, k->gsum + 3);
     PYN_CHECK_LAUNCH();
-    int rc = pyn::comm_allreduce_sum(k->comm, k->gsum + 1, 2, st);
+    int rc = pyn::comm_allreduce_sum(k->comm, k->gsum + 1, guess ? 3 : 2, st);
     if (rc) return rc;
   }
-  cg_scalar_init_kernel<<<1, 32, 0, st>>>(k->vgrid, k->B, k->opts.rtol, k->opts.atol, dist ? k->gsum : nullptr);
+  cg_scalar_init_kernel<<<1, 32, 0, st>>>(k->vgrid, k->B, k->opts.rtol, k->opts.atol, dist ? k->gsum : nullptr,
+                                          guess ? k->pzz : nullptr);
   PYN_CHECK_LAUNCH();
   launches += 2;
   const int chunk = k->opts.check_every;

@@ -3,8 +3,9 @@ use sites src/cases/base_problem.py:276,318,323-327,481).
 
 Same surface -- `KspSolver()`, `createSolver(mat, comm)`, `solver(b, x)` -- and the same precedence of settings: the
 reference's defaults (`preonly` + `lu`) first, then whatever the options database says (`-ksp_type`, `-pc_type`,
-`-ksp_rtol`, `-ksp_atol`, `-ksp_divtol`, `-ksp_max_it`, `-ksp_gmres_restart`), then `setOperators` / `setUp`.
-The iterations run on the device (csrc/ksp.cu) with PETSc's semantics: zero initial guess, left preconditioning,
+`-ksp_rtol`, `-ksp_atol`, `-ksp_divtol`, `-ksp_max_it`, `-ksp_gmres_restart`, `-ksp_initial_guess_nonzero`), then `setOperators` / `setUp`.
+The iterations run on the device (csrc/ksp.cu) with PETSc's semantics: zero initial guess (or, for CG, the contents
+of `x` under `-ksp_initial_guess_nonzero`: r0 = b - A x0, rtol measured against |M^-1 b|), left preconditioning,
 preconditioned residual norm, KSPConvergedDefault.
 
 `preonly` + `lu` (a sparse direct factorisation) has no device counterpart in this build; it is served by
@@ -35,6 +36,7 @@ class KspSolver(object):
         self.rtol, self.atol, self.divtol, self.max_it = 1e-5, 1e-50, 1e4, 10000
         self.restart = 30
         self.check_every = 0
+        self.guess_nonzero = False
         self.its, self.reason, self.rnorm = 0, 0, 0.0
         self.history = []
 
@@ -62,6 +64,12 @@ class KspSolver(object):
         if max_it is not None:
             self.max_it = max_it
 
+    def setInitialGuessNonzero(self, flag):
+        self.guess_nonzero = bool(flag)
+
+    def getInitialGuessNonzero(self):
+        return self.guess_nonzero
+
     def getTolerances(self):
         return self.rtol, self.atol, self.divtol, self.max_it
 
@@ -75,6 +83,7 @@ class KspSolver(object):
         self.max_it = o.getInt("ksp_max_it", self.max_it)
         self.restart = o.getInt("ksp_gmres_restart", self.restart)
         self.check_every = o.getInt("ksp_check_every", self.check_every)
+        self.guess_nonzero = o.getBool("ksp_initial_guess_nonzero", self.guess_nonzero)
 
     def setOperators(self, mat):
         self.mat = mat
@@ -98,7 +107,8 @@ class KspSolver(object):
             raise Exception(f"PC type {pc} is not available on the device path (none, jacobi)")
         csr = self.mat.csr if hasattr(self.mat, "csr") else self.mat
         self._ksp = be.Ksp(csr, ksp_type, pc, rtol=rtol, atol=self.atol, dtol=self.divtol, max_it=max_it,
-                           restart=self.restart, check_every=self.check_every)
+                           restart=self.restart, check_every=self.check_every,
+                           nonzero_guess=self.guess_nonzero and not self._direct)
         dist = getattr(self.comm, "dist", None)
         if dist is not None:       # multi-GPU: halo exchange of the search direction + all-reduced scalars
             dist.attach(self._ksp, ncomp=csr.shape[0] // dist.part.nnodes)

@@ -75,6 +75,11 @@ def test_options_database():
     assert opt.getString("case") == "cavity" and opt.getReal("ksp_rtol") == 1e-8 and opt.getInt("ksp_max_it") == 77
     assert opt.getReal("ts_dt") == -0.5 and opt.hasName("flag") and not opt.hasName("pc_type")
     assert opt.getString("pc_type", "lu") == "lu"
+    assert opt.getBool("flag") is True and opt.getBool("absent", False) is False
+    Options.setValue("ksp_initial_guess_nonzero", "false")
+    assert opt.getBool("ksp_initial_guess_nonzero") is False
+    Options.setValue("ksp_initial_guess_nonzero", "1")
+    assert opt.getBool("ksp_initial_guess_nonzero") is True
     Options.clear()
     assert not Options().hasName("case")
 

@@ -287,6 +287,16 @@ def test_template_operator_matches_csr(be, nx, ny, n):
         r = ksp.solve(be.to_device(b), x)
         assert r.reason == reason and abs(r.its - its) <= max(1, its // 50), (r.its, its)
         assert rel_err(x.cpu().numpy(), xo) < TOL_KSP * (1 if r.its == its else 20)
+        # ... and from a nonzero initial guess (r0 = b - A x0 through the element operator)
+        x0 = xo * (1.0 + 1e-4 * np.random.default_rng(2).standard_normal(xo.size))
+        xg, itg, reasong, histg = o.ksp_cg_jacobi(Aref, b, rtol=1e-11, x0=x0)
+        kg = be.Ksp(A, "cg", "jacobi", rtol=1e-11, check_every=9, nonzero_guess=True)
+        assert kg._tm is not None
+        x = be.to_device(x0)
+        r = kg.solve(be.to_device(b), x)
+        assert 0 < itg < its and r.reason == reasong and abs(r.its - itg) <= max(1, itg // 50), (r.its, itg, its)
+        assert abs(r.rnorm0 - hist[0]) < 1e-12 * hist[0]
+        assert rel_err(x.cpu().numpy(), xg) < TOL_KSP * (1 if r.its == itg else 20)
 
 
 def test_coo_to_csr_generic(be):
@@ -398,6 +408,39 @@ def test_cg_jacobi_petsc_semantics(be, nx, n, rtol):
     ksp2 = be.Ksp(A, "cg", "jacobi", rtol=1e-14, max_it=5, check_every=3)
     r = ksp2.solve(be.to_device(b), x)
     assert (r.its, r.reason) == (5, -3)
+
+
+@pytest.mark.parametrize("nx,n,rtol", [(8, 3, 1e-10), (6, 5, 1e-10), (8, 4, 1e-6)])
+def test_cg_nonzero_initial_guess(be, nx, n, rtol):
+    """-ksp_initial_guess_nonzero: r0 = b - A x0 from the contents of x, rtol measured against |M^-1 b|
+    (KSPConvergedDefault), same iterate as the oracle (CSR stream here; through the element operator in
+    test_template_operator_matches_csr)."""
+    m, K, A, b, _ = _freeslip_system(be, nx, nx, n)
+    xs = o.direct_solve(K, b)
+    rng = np.random.default_rng(5)
+    x0 = xs * (1.0 + 1e-3 * rng.standard_normal(xs.size))           # a close guess, like the previous RK stage's
+    xo, its, reason, hist = o.ksp_cg_jacobi(K, b, rtol=rtol, x0=x0)
+    xz, its_zero, _, hist_zero = o.ksp_cg_jacobi(K, b, rtol=rtol)
+    assert its > 0          # (white noise on the guess is a rough error: not necessarily fewer iterations than from zero)
+    ksp = be.Ksp(A, "cg", "jacobi", rtol=rtol, check_every=5, nonzero_guess=True)
+    x = be.to_device(x0)
+    r = ksp.solve(be.to_device(b), x)
+    assert r.reason == reason and abs(r.its - its) <= max(1, its // 50), (r.its, its)
+    assert abs(r.rnorm0 - hist_zero[0]) < 1e-12 * hist_zero[0]      # |M^-1 b|, not the initial residual
+    assert r.rnorm <= max(rtol * hist_zero[0], 1e-50)
+    assert rel_err(x.cpu().numpy(), xo) < max(TOL_KSP, 1e-3 * rtol) * (1 if r.its == its else 20)
+    # an exact guess stops at iteration 0 and leaves x untouched; b = 0 falls back to the initial residual
+    x = be.to_device(xs)
+    keep = x.clone()
+    r = be.Ksp(A, "cg", "jacobi", rtol=1e-6, nonzero_guess=True).solve(be.to_device(b), x)
+    assert r.its == 0 and r.reason == 2 and bool((x == keep).all())
+    x = be.to_device(x0)
+    r = ksp.solve(be.zeros(K.shape[0]), x)
+    xb, itb, reasonb, histb = o.ksp_cg_jacobi(K, np.zeros_like(b), rtol=rtol, x0=x0)
+    assert r.reason == reasonb and abs(r.its - itb) <= max(1, itb // 50)
+    assert abs(r.rnorm0 - histb[0]) < 1e-10 * histb[0]
+    with pytest.raises(Exception):
+        be.Ksp(A, "gmres", "jacobi", nonzero_guess=True)
 
 
 @pytest.mark.parametrize("nx,n,rtol,restart,pc", [(8, 3, 1e-8, 30, "jacobi"), (6, 4, 1e-10, 30, "jacobi"),

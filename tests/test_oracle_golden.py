@@ -177,3 +177,24 @@ def test_rhs_chain_taylor_green_decay():
     f = o.eval_rhs_from_vel(ops, vel.reshape(-1), rho, mu)
     interior = np.setdiff1d(np.arange(m.nnodes), m.boundary_nodes())
     assert np.abs(f[interior] - (-8 * math.pi ** 2 * nu) * vort[interior]).max() < 5e-2 * np.abs(vort).max()
+
+
+def test_cg_initial_guess_nonzero_semantics():
+    """KSPCG with -ksp_initial_guess_nonzero (restated): r0 = b - A x0, the relative tolerance is measured against the
+    preconditioned right-hand side (KSPConvergedDefault), so a close guess saves iterations and an exact one stops at
+    iteration 0; with b = 0 the initial residual is the yardstick.  x0 = 0 reproduces the default path bit for bit."""
+    m = o.BoxMesh([8, 8], [0, 0], [1, 1], 4)
+    ref = o.assemble_freeslip(m, per_cell=False)
+    K = ref["K"]
+    b = ref["Rw"] @ np.random.default_rng(0).standard_normal(m.nnodes)
+    xs = o.direct_solve(K, b)
+    x0 = xs * (1 + 1e-3 * np.random.default_rng(5).standard_normal(xs.size))
+    xa, ita, ra, ha = o.ksp_cg_jacobi(K, b, rtol=1e-10)
+    xg, itg, rg, hg = o.ksp_cg_jacobi(K, b, rtol=1e-10, x0=x0)
+    assert (ra, rg) == (2, 2) and 0 < itg < ita
+    assert rel_err(xg, xs) < 1e-8 and hg[-1] <= 1e-10 * ha[0]
+    xz, itz, rz, hz = o.ksp_cg_jacobi(K, b, rtol=1e-10, x0=np.zeros_like(b))
+    assert itz == ita and np.array_equal(xz, xa)
+    assert o.ksp_cg_jacobi(K, b, rtol=1e-6, x0=xs)[1:3] == (0, 2)
+    xb, itb, rb, hb = o.ksp_cg_jacobi(K, np.zeros_like(b), rtol=1e-6, x0=x0)
+    assert rb == 2 and itb > 0 and hb[-1] <= 1e-6 * hb[0] and np.abs(xb).max() < 1e-4 * np.abs(x0).max()
