@@ -245,7 +245,7 @@ int pyn_vec_wrms(int64_t n, const double* d_err, const double* d_y, const double
  * Krylov solvers with PETSc semantics (KspSolver, src/solver/ksp_solver.py:9-19; use sites
  * base_problem.py:276,318,323-327,481): zero initial guess, left preconditioning, preconditioned residual
  * norm, KSPConvergedDefault.  reason: 2 rtol, 3 atol, -3 max_it, -4 dtol, -8 indefinite.
- * nonzero_guess (CG; PETSc's -ksp_initial_guess_nonzero): d_x holds x0 on entry, r0 = b - A x0, and rtol is
+ * nonzero_guess (PETSc's -ksp_initial_guess_nonzero): d_x holds x0 on entry, r0 = b - A x0, and rtol is
  * measured against |M^-1 b| (the initial residual when b = 0), as KSPConvergedDefault does.
  * ---------------------------------------------------------------------------------------------------- */
 typedef struct pyn_ksp pyn_ksp;
@@ -256,7 +256,7 @@ typedef struct {
   int32_t max_it;
   int32_t restart;     /* gmres */
   int32_t check_every; /* iterations between host polls of the device convergence flag (0 = default) */
-  int32_t nonzero_guess; /* cg only: start from the contents of d_x */
+  int32_t nonzero_guess; /* start from the contents of d_x */
 } pyn_ksp_opts;
 typedef struct {
   int32_t its, reason;
@@ -268,7 +268,7 @@ int pyn_ksp_solve(pyn_ksp* k, const double* d_b, double* d_x, pyn_ksp_result* re
 int pyn_ksp_destroy(pyn_ksp* k);
 /* device work done by the last solve: SpMV launches and total kernel launches (for the roofline accounting) */
 int pyn_ksp_stats(const pyn_ksp* k, int64_t* spmv_launches, int64_t* kernel_launches);
-/* CG applies the operator through the template operator instead of the CSR stream (NULL: back to the CSR) */
+/* CG and GMRES apply the operator through the template operator instead of the CSR stream (NULL: back to the CSR) */
 int pyn_ksp_set_tmat(pyn_ksp* k, const pyn_tmat* m);
 
 /* ------------------------------------------------------------------------------------------------------

@@ -775,20 +775,26 @@ def rk_adaptive(f, t0, y0, t_end, dt0=0.1, atol=1e-4, rtol=1e-4, max_steps=5000,
 # --------------------------------------------------------------------------------------------------------
 # S1b  KSP: restarted GMRES with PETSc semantics (restated from the KSPGMRES documentation)
 # --------------------------------------------------------------------------------------------------------
-def ksp_gmres(A, b, rtol=1e-5, atol=1e-50, dtol=1e4, max_it=10000, restart=30, jacobi=True):
+def ksp_gmres(A, b, rtol=1e-5, atol=1e-50, dtol=1e4, max_it=10000, restart=30, jacobi=True, x0=None):
     """Left-preconditioned GMRES(restart), zero initial guess, classical Gram-Schmidt without refinement, residual
     norm from the Givens recurrence, KSPConvergedDefault; the true preconditioned residual is formed and tested at the
-    top of every cycle (src/solver/ksp_solver.py:9-19 with -ksp_type gmres).  Returns x, its, reason, history."""
+    top of every cycle (src/solver/ksp_solver.py:9-19 with -ksp_type gmres).  x0 (-ksp_initial_guess_nonzero): first
+    residual from x0, rtol measured against ||M^-1 b|| (KSPConvergedDefault).  Returns x, its, reason, history."""
     n = A.shape[0]
     dinv = 1.0 / A.diagonal() if jacobi else np.ones(n)
-    x = np.zeros(n)
+    x = np.zeros(n) if x0 is None else np.array(x0, dtype=float)
     its, reason, hist, m = 0, 0, [], restart
     rnorm0 = ttol = None
     while not reason:
-        r = dinv * (b - A @ x) if its else dinv * b
+        r = dinv * (b - A @ x) if (its or x0 is not None) else dinv * b
         beta = math.sqrt(r @ r)
         if rnorm0 is None:
-            rnorm0, ttol = beta, max(rtol * beta, atol)
+            rnorm0 = beta
+            if x0 is not None:
+                zb = dinv * b
+                snorm = math.sqrt(zb @ zb)
+                rnorm0 = snorm if snorm > 0.0 else beta
+            ttol = max(rtol * rnorm0, atol)
             hist.append(beta)
         if beta <= ttol:
             reason = 3 if beta <= atol else 2

@@ -474,8 +474,6 @@ class Ksp:
 
     def __init__(self, A: CSR, ksp_type="cg", pc="jacobi", rtol=1e-5, atol=1e-50, dtol=1e4, max_it=10000,
                  restart=30, check_every=0, nonzero_guess=False):
-        if nonzero_guess and ksp_type != "cg":
-            raise Exception("-ksp_initial_guess_nonzero is available with -ksp_type cg on the device path")
         self.A = A
         o = KspOpts()
         o.type, o.pc = self.TYPES[ksp_type], self.PCS[pc]
@@ -486,7 +484,7 @@ class Ksp:
         call("pyn_ksp_create", A.shape[0], ptr(A.indptr), ptr(A.indices), ptr(A.data), A.nnz, C.byref(o), stream(),
              C.byref(self._h))
         self.its, self.reason, self.rnorm0, self.rnorm = 0, 0, 0.0, 0.0
-        self._tm = A.tmat() if ksp_type == "cg" else None      # template operator for w = A p when enabled on A
+        self._tm = A.tmat()                                     # element operator for w = A p when enabled on A
         if self._tm is not None:
             call("pyn_ksp_set_tmat", self._h, self._tm.handle)
 

@@ -1,5 +1,5 @@
 // Restarted GMRES on device with PETSc's KSPGMRES semantics (-ksp_type gmres; KspSolver, src/solver/ksp_solver.py:9-19):
-// left preconditioning (Jacobi or none), zero initial guess, restart 30 by default, CLASSICAL Gram-Schmidt without
+// left preconditioning (Jacobi or none), zero (or given: nonzero_guess) initial guess, restart 30 by default, CLASSICAL Gram-Schmidt without
 // refinement (all projections from the same vector), residual norm from the Givens recurrence, KSPConvergedDefault on the
 // preconditioned residual; at the top of every cycle the true preconditioned residual is formed and tested.
 //
@@ -40,6 +40,11 @@ gmres_spmv_kernel(pyn::SpmvPlanView P, const int* __restrict__ ind, const double
                   const double* __restrict__ x, PcEpi epi) {
   __shared__ pyn::SpmvSmem sm;
   for (int b = blockIdx.x; b < P.nblk; b += gridDim.x) pyn::spmv_stream_chunk(P, ind, val, x, b, sm, epi);
+}
+
+// the same epilogue after a product through the element operator (pyn_tmat_mult wrote w = A v)
+__global__ void gmres_pc_kernel(int64_t n, PcEpi epi) {
+  for (int64_t i = blockIdx.x * (int64_t)BLK + threadIdx.x; i < n; i += (int64_t)gridDim.x * BLK) epi(i, epi.w[i]);
 }
 
 // r = M^-1 b (zero initial guess), x = 0
@@ -175,6 +180,7 @@ int gmres_solve(pyn_ksp* k, const double* d_b, double* d_x, pyn_ksp_result* res,
   const double* dinv = k->B.dinv;
   const pyn::SpmvPlanView P = pyn::view_of(k->plan);
   auto Vj = [&](int j) { return g->V + (size_t)n * j; };
+  int rc;
 
   // dots[0..cnt) = <v_j, w> for j < cnt (v == NULL: <w, w>), all-reduced over the ranks; optionally copied to the host
   auto multi_dot = [&](int first, int cnt, const double* w, bool self, double* d_out) -> int {
@@ -199,31 +205,52 @@ int gmres_solve(pyn_ksp* k, const double* d_b, double* d_x, pyn_ksp_result* res,
     return PYN_OK;
   };
 
+  // epi.w = M^-1 (A v)  or  M^-1 (b - A v): CSR stream with the epilogue fused, or element operator + one vector pass
+  auto product = [&](const double* v, const PcEpi& epi) -> int {
+    if (dist && (rc = pyn::halo_exchange(k->halo, const_cast<double*>(v), k->halo_comp, st))) return rc;
+    if (k->tmat) {
+      if ((rc = pyn_tmat_mult(k->tmat, v, epi.w, PYN_SPMV_SET, 0.0, 0.0, nullptr, st))) return rc;
+      gmres_pc_kernel<<<k->vgrid, BLK, 0, st>>>(n, epi);
+      launches += 3;
+    } else {
+      gmres_spmv_kernel<<<k->sgrid, pyn::SP_BLK, 0, st>>>(P, k->ind, k->val, v, epi);
+    }
+    GM_LAUNCH_CHECK();
+    return PYN_OK;
+  };
+
   const double rtol = k->opts.rtol, atol = k->opts.atol, dtol = k->opts.dtol;
   const int max_it = k->opts.max_it;
+  const bool guess = k->opts.nonzero_guess != 0;
+  double bnorm = 0.0;
   std::vector<double> H((size_t)(m + 1) * m, 0.0), cs(m, 0.0), sn(m, 0.0), gg(m + 1, 0.0), y(m, 0.0);
   int its = 0, reason = 0;
   double rnorm0 = 0.0, rnorm = 0.0, ttol = 0.0;
   bool first = true;
-  int rc;
 
   while (!reason) {
     // ---- residual of the cycle: V0 = M^-1 (b - A x) ------------------------------------------------------------
     if (first) {
       gmres_init_kernel<<<k->vgrid, BLK, 0, st>>>(n, d_b, dinv, owned, Vj(0), g->x);
       GM_LAUNCH_CHECK();
-    } else {
-      if (dist && (rc = pyn::halo_exchange(k->halo, g->x, k->halo_comp, st))) return rc;
-      PcEpi epi{Vj(0), dinv, d_b, owned};
-      gmres_spmv_kernel<<<k->sgrid, pyn::SP_BLK, 0, st>>>(P, k->ind, k->val, g->x, epi);
+    }
+    if (first && guess) {   // -ksp_initial_guess_nonzero: |M^-1 b| is the yardstick of rtol, x0 = contents of d_x
+      if ((rc = multi_dot(0, 1, Vj(0), true, g->dots))) return rc;
+      if ((rc = fetch(1))) return rc;
+      bnorm = sqrt(g->h_dots[0]);
+      gmres_copy_kernel<<<k->vgrid, BLK, 0, st>>>(n, d_x, g->x);
       GM_LAUNCH_CHECK();
+    }
+    if (!first || guess) {
+      PcEpi epi{Vj(0), dinv, d_b, owned};
+      if ((rc = product(g->x, epi))) return rc;
     }
     if ((rc = multi_dot(0, 1, Vj(0), true, g->dots))) return rc;
     if ((rc = fetch(1))) return rc;
     const double beta = sqrt(g->h_dots[0]);
     rnorm = beta;
     if (first) {
-      rnorm0 = beta;
+      rnorm0 = (guess && bnorm > 0.0) ? bnorm : beta;
       ttol = fmax(rtol * rnorm0, atol);
       first = false;
     }
@@ -237,10 +264,8 @@ int gmres_solve(pyn_ksp* k, const double* d_b, double* d_x, pyn_ksp_result* res,
     int j = 0;
     for (; j < m; ++j) {
       // ---- w = M^-1 A v_j -----------------------------------------------------------------------------------
-      if (dist && (rc = pyn::halo_exchange(k->halo, Vj(j), k->halo_comp, st))) return rc;
       PcEpi epi{g->w, dinv, nullptr, owned};
-      gmres_spmv_kernel<<<k->sgrid, pyn::SP_BLK, 0, st>>>(P, k->ind, k->val, Vj(j), epi);
-      GM_LAUNCH_CHECK();
+      if ((rc = product(Vj(j), epi))) return rc;
       // ---- classical Gram-Schmidt: h_i = <v_i, w> for all i <= j from the same w, then one projection ----------
       if ((rc = multi_dot(0, j + 1, g->w, false, g->dots))) return rc;
       for (int j0 = 0; j0 <= j; j0 += MD) {

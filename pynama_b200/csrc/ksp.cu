@@ -1,5 +1,5 @@
 // Krylov solvers on device with PETSc semantics (KSPCG / KSPGMRES + KSPConvergedDefault, left preconditioning,
-// preconditioned residual norm, zero or (CG) nonzero initial guess) -- replaces KspSolver (src/solver/ksp_solver.py:9-19).
+// preconditioned residual norm, zero or given initial guess) -- replaces KspSolver (src/solver/ksp_solver.py:9-19).
 //
 // Control flow lives on the device: every kernel of an iteration starts by reading a `done` flag in a small state
 // block, so a whole chunk of iterations can be enqueued (as one CUDA graph) without the host knowing whether
@@ -360,7 +360,6 @@ int pyn_ksp_create(int64_t nrows, const int64_t* d_ptr, const int32_t* d_ind, co
                    const pyn_ksp_opts* opts, void* stream, pyn_ksp** out) {
   PYN_REQUIRE(nrows > 0 && d_ptr && d_ind && d_val && opts && out, "bad arguments");
   PYN_REQUIRE(opts->type == 0 || opts->type == 1, "ksp type must be 0 (cg) or 1 (gmres)");
-  PYN_REQUIRE(opts->nonzero_guess == 0 || opts->type == 0, "nonzero initial guess is wired into CG only");
   cudaStream_t st = pyn::as_stream(stream);
   pyn_ksp* k = new pyn_ksp();
   memset(k, 0, sizeof(*k));
@@ -499,7 +498,6 @@ int pyn_ksp_set_tmat(pyn_ksp* k, const pyn_tmat* m) {
   PYN_REQUIRE(k, "ksp is NULL");
   if (m) {
     PYN_REQUIRE(m->rdof == m->cdof && m->topo->nnodes * m->rdof == k->n, "template operator does not match the system");
-    PYN_REQUIRE(k->opts.type == 0, "the template operator is wired into CG only");
   }
   k->tmat = m;
   if (k->graph) { cudaGraphExecDestroy(k->graph); k->graph = nullptr; }

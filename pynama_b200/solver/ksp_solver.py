@@ -4,7 +4,7 @@ use sites src/cases/base_problem.py:276,318,323-327,481).
 Same surface -- `KspSolver()`, `createSolver(mat, comm)`, `solver(b, x)` -- and the same precedence of settings: the
 reference's defaults (`preonly` + `lu`) first, then whatever the options database says (`-ksp_type`, `-pc_type`,
 `-ksp_rtol`, `-ksp_atol`, `-ksp_divtol`, `-ksp_max_it`, `-ksp_gmres_restart`, `-ksp_initial_guess_nonzero`), then `setOperators` / `setUp`.
-The iterations run on the device (csrc/ksp.cu) with PETSc's semantics: zero initial guess (or, for CG, the contents
+The iterations run on the device (csrc/ksp.cu) with PETSc's semantics: zero initial guess (or the contents
 of `x` under `-ksp_initial_guess_nonzero`: r0 = b - A x0, rtol measured against |M^-1 b|), left preconditioning,
 preconditioned residual norm, KSPConvergedDefault.
 
