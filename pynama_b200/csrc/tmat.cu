@@ -1,6 +1,8 @@
 // Element operator kernels (see tmat.cuh): y = A x with fused epilogues, same modes as pyn_spmv.
 #include <stdlib.h>
 
+#include <vector>
+
 #include "tmat.cuh"
 
 namespace {
@@ -64,7 +66,6 @@ eop_apply_kernel(pyn::TmatView m, const double* __restrict__ x, const int* __res
   }
   const int64_t ntiles = (m.ne + EO_TE - 1) / EO_TE;
   const int nitems = NRP / R;
-  const bool vec_store = (NR & 1) == 0;
   constexpr int U = (CD == 3) ? 12 : 20;
   for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     const int64_t e0 = tile * EO_TE;
@@ -145,16 +146,12 @@ eop_apply_kernel(pyn::TmatView m, const double* __restrict__ x, const int* __res
       for (int q = 0; q < EO_Q; ++q) {
         const int64_t e = e0 + lane + 32 * q;
         if (e >= m.ne) continue;
-        double* yp = m.Ye + e * NR + i0;
-        if (vec_store) {
 #pragma unroll
-          for (int r = 0; r < R; r += 2)
-            if (i0 + r < NR) *reinterpret_cast<double2*>(yp + r) = make_double2(acc[r][q], acc[r + 1][q]);
-        } else {
-#pragma unroll
-          for (int r = 0; r < R; ++r)
-            if (i0 + r < NR) yp[r] = acc[r][q];
-        }
+        for (int r = 0; r < R; ++r)
+          if (i0 + r < NR) {
+            const int2 rm = __ldg(m.rowmap + i0 + r);
+            m.Ye[rm.x + e * rm.y] = acc[r][q];
+          }
       }
     }
   }
@@ -285,11 +282,14 @@ eop_apply_mma_kernel(pyn::TmatView m, const double* __restrict__ x, const int* _
       for (int i = 0; i < MB; ++i) {
         const int row = (rb0 + i) * 8 + (lane >> 2);
         if (row < NR) {
+          int bx, by;   // volatile: re-read from L1 per stage instead of living in 2*MB registers for the whole kernel
+          asm volatile("ld.global.nc.v2.s32 {%0,%1}, [%2];" : "=r"(bx), "=r"(by) : "l"(m.rowmap + row));
+          double* yp = m.Ye + bx;
 #pragma unroll
           for (int nb = 0; nb < EM_NBW; ++nb) {
             const int64_t e = e0 + nb * 8;
-            if (e < m.ne) m.Ye[e * NR + row] = acc[i][nb][0];
-            if (e + 1 < m.ne) m.Ye[(e + 1) * NR + row] = acc[i][nb][1];
+            if (e < m.ne) yp[e * by] = acc[i][nb][0];
+            if (e + 1 < m.ne) yp[(e + 1) * by] = acc[i][nb][1];
           }
         }
       }
@@ -463,7 +463,35 @@ int tmat_init(pyn_tmat* m, const double* d_E, double sign, cudaStream_t st) {
   m->NR = m->rdof * t->nn; m->NC = m->cdof * t->nn;
   const MmaShape ms = mma_shape(t->nn, m->NR, m->NC);
   m->mma = ms.ok && !getenv("PYN_EO_SIMT");      // PYN_EO_SIMT=1: keep the DFMA kernel (A/B measurements)
-  PYN_CHECK_CUDA(cudaMalloc(&m->Ye, sizeof(double) * (size_t)t->ne * m->NR));
+  {
+    // Row map of Ye: one dense array per node kind for square 2-D elements in the reference's local order (4 vertices,
+    // 4 x (n-2) edge nodes, (n-2)^2 interior nodes); anything else, or PYN_EO_AOS=1, keeps element-major records.
+    const int nn = t->nn, rd = m->rdof;
+    int n = 1;
+    while (n * n < nn) ++n;
+    std::vector<int> first;   // first local node of every kind, then nn
+    if (n * n == nn && n >= 3 && !getenv("PYN_EO_AOS") && (int64_t)t->ne * m->NR + 64 * 8 < 0x7fffffff) {
+      first.push_back(0);
+      for (int k = 0; k <= 4; ++k) first.push_back(4 + k * (n - 2));
+    } else {
+      first.push_back(0);
+    }
+    first.push_back(nn);
+    std::vector<int2> map((size_t)m->NR);
+    int64_t base = 0;
+    for (size_t g = 0; g + 1 < first.size(); ++g) {
+      const int stride = (first[g + 1] - first[g]) * rd;
+      for (int l = first[g]; l < first[g + 1]; ++l)
+        for (int a = 0; a < rd; ++a) map[(size_t)l * rd + a] = make_int2((int)base + (l - first[g]) * rd + a, stride);
+      base += (int64_t)t->ne * stride;
+      base = (base + 15) & ~(int64_t)15;     // every array starts on a 128-byte line
+    }
+    PYN_REQUIRE(first.size() == 2 || base < 0x7fffffff, "element operator: row map overflow");
+    PYN_CHECK_CUDA(cudaMalloc(&m->Ye, sizeof(double) * (size_t)base));
+    PYN_CHECK_CUDA(cudaMalloc(&m->rowmap, sizeof(int2) * map.size()));
+    PYN_CHECK_CUDA(cudaMemcpyAsync(m->rowmap, map.data(), sizeof(int2) * map.size(), cudaMemcpyHostToDevice, st));
+    PYN_CHECK_CUDA(cudaStreamSynchronize(st));   // `map` is pageable host memory going out of scope
+  }
   int rc;
   if (m->mma) {
     m->RB = ms.RB; m->KB = ms.KB; m->NCP = ms.NCP; m->W = EM_W; m->MB = ms.MB; m->P = ms.P; m->smem = ms.smem;
@@ -504,6 +532,7 @@ int pyn_tmat_destroy(pyn_tmat* m) {
   if (!m) return PYN_OK;
   cudaFree(m->Et);
   cudaFree(m->Ye);
+  cudaFree(m->rowmap);
   delete m;
   return PYN_OK;
 }

@@ -8,6 +8,11 @@
 //            order (the reference's cell loop order, base_problem.py:499-552), scaled by rowscale[r] -- a deterministic
 //            gather, no atomics.
 //   boundary-affected nodes (bcmap list) take their rows from the assembled CSR (one warp per row).
+//   Layout of Ye (rowmap): the rows of an element are split by the KIND of their node -- the 4 vertices, each of the 4
+//   edges, the cell interior (the reference's element-local order, indices.py:66-88) -- and every kind is its own dense
+//   array over the elements.  Phase 2 walks the nodes in global order, which is kind by kind (cell interiors, vertices,
+//   edges: dmplex.py:42-61), so each of its passes reads one dense array instead of 16-byte pieces scattered in
+//   element-major records (DRAM sectors fully used: 1.85 -> ~1.1 GB moved per product at cfg 4).
 //
 // Algorithmic HBM bytes per product (K at 1024^2 x ngl 5: 1.6 GB against 29.8 GB of the CSR stream):
 //   8 cols + 4 ne nn + 2 * 8 ne NR + 8 (nnodes+1) + 6 ne nn + 8 rows.
@@ -24,7 +29,8 @@ struct pyn_tmat {
   int mma, RB, KB, MB, P;    // DMMA variant of phase 1: 8-row blocks, 4-column blocks (Et then holds the fragments),
                              // row blocks per pass, gathered pairs per lane and stage
   double* Et;                // owned: sign * E transposed, [NCP][NRP], zero padded
-  double* Ye;                // owned scratch [ne][NR]
+  double* Ye;                // owned scratch: NR values per element, laid out by rowmap
+  int2* rowmap;              // owned [NR]: Ye index of (element e, row i) = rowmap[i].x + e * rowmap[i].y
   const uint8_t* flags;      // borrowed from the bcmap: 1 = row comes from the CSR
   const int* list;           // flagged nodes
   int64_t nlist;
@@ -51,6 +57,7 @@ struct TmatView {
   const short* n2e_loc;
   const double* Et;
   double* Ye;
+  const int2* rowmap;
   const uint8_t* flags;
   const int* list;
   int64_t nlist;
@@ -64,7 +71,7 @@ static inline TmatView view_of(const pyn_tmat* m) {
   v.nnodes = m->topo->nnodes; v.ne = m->topo->ne; v.nn = m->topo->nn; v.NR = m->NR; v.NC = m->NC; v.NRP = m->NRP; v.NCP = m->NCP;
   v.nn_magic = (unsigned)((0x100000000ull + (unsigned)v.nn - 1) / (unsigned)v.nn);
   v.e2n = m->topo->e2n; v.n2e_ptr = m->topo->n2e_ptr; v.n2e_elem = m->topo->n2e_elem; v.n2e_loc = m->topo->n2e_loc;
-  v.Et = m->Et; v.Ye = m->Ye; v.flags = m->flags; v.list = m->list; v.nlist = m->nlist; v.rowscale = m->rowscale;
+  v.Et = m->Et; v.Ye = m->Ye; v.rowmap = m->rowmap; v.flags = m->flags; v.list = m->list; v.nlist = m->nlist; v.rowscale = m->rowscale;
   v.ptr = m->ptr; v.ind = m->ind; v.val = m->val;
   return v;
 }
@@ -83,9 +90,10 @@ __device__ __forceinline__ void eop_gather_node(const TmatView& m, int64_t r, do
   for (int64_t k = b0; k < b1; ++k) {
     const int e = ld_stream(m.n2e_elem + k);
     const int loc = m.n2e_loc[k];
-    const double* p = m.Ye + (int64_t)e * m.NR + loc * RD;
+    const int2 rm = __ldg(m.rowmap + loc * RD);
+    const double* p = m.Ye + rm.x + (int64_t)e * rm.y;
     if (RD == 2) {
-      const double2 t = *reinterpret_cast<const double2*>(p);   // NR and loc*2 are even
+      const double2 t = *reinterpret_cast<const double2*>(p);   // bases and strides of the row map are even
       acc[0] += t.x;
       acc[RD - 1] += t.y;
     } else {
