@@ -278,18 +278,25 @@ eop_apply_mma_kernel(pyn::TmatView m, const double* __restrict__ x, const int* _
 #pragma unroll
           for (int nb = 0; nb < EM_NBW; ++nb) dmma884(acc[i][nb][0], acc[i][nb][1], a[i], b[nb]);
       }
+      // row map entries of this pass: MB independent loads issued back to back (one exposed latency per pass; L1 is a
+      // few kB next to the shared-memory carve-out and the gathers run through it, so these come from L2).  volatile:
+      // re-read per pass instead of living in 2*MB registers across the DMMA loop
+      int bx[MB], by[MB];
+#pragma unroll
+      for (int i = 0; i < MB; ++i) {
+        const int row = (rb0 + i) * 8 + (lane >> 2);
+        asm volatile("ld.global.nc.v2.s32 {%0,%1}, [%2];" : "=r"(bx[i]), "=r"(by[i]) : "l"(m.rowmap + (row < NR ? row : 0)));
+      }
 #pragma unroll
       for (int i = 0; i < MB; ++i) {
         const int row = (rb0 + i) * 8 + (lane >> 2);
         if (row < NR) {
-          int bx, by;   // volatile: re-read from L1 per stage instead of living in 2*MB registers for the whole kernel
-          asm volatile("ld.global.nc.v2.s32 {%0,%1}, [%2];" : "=r"(bx), "=r"(by) : "l"(m.rowmap + row));
-          double* yp = m.Ye + bx;
+          double* yp = m.Ye + bx[i];
 #pragma unroll
           for (int nb = 0; nb < EM_NBW; ++nb) {
             const int64_t e = e0 + nb * 8;
-            if (e < m.ne) yp[e * by] = acc[i][nb][0];
-            if (e + 1 < m.ne) yp[(e + 1) * by] = acc[i][nb][1];
+            if (e < m.ne) yp[e * by[i]] = acc[i][nb][0];
+            if (e + 1 < m.ne) yp[(e + 1) * by[i]] = acc[i][nb][1];
           }
         }
       }
