@@ -64,6 +64,7 @@ __global__ void cg_reset_kernel(KspState* s) {
   s->done = 0;
   s->its = 0;
   s->reason = 0;
+  s->pend = 0;
 }
 
 // ... then, with p = x0 and w = A p:  r = b - w, x = x0, z = M^-1 r; partials of z.z, z.r and |M^-1 b|^2 (KSPCG:
@@ -113,6 +114,8 @@ __global__ void cg_scalar_init_kernel(int nparts, CgBuffers B, double rtol, doub
     s->its = 0;
     s->reason = 0;
     s->done = 0;
+    s->pend = 0;
+    s->alpha = 0.0;
     if (s->dp <= s->ttol) {  // KSPConvergedDefault at iteration 0
       s->reason = (s->dp <= atol) ? 3 : 2;
       s->done = 1;
@@ -120,26 +123,43 @@ __global__ void cg_scalar_init_kernel(int nparts, CgBuffers B, double rtol, doub
   }
 }
 
-// p = z + (beta/betaold) p   (first iteration: p = z); 16-byte accesses (the work vectors are 16-byte aligned)
+// x += alpha_prev p (the previous iteration's step, deferred to here because p is read anyway: one vector pass less
+// per iteration than updating x next to r), then p = z + (beta/betaold) p   (first iteration: p = z).
+// 16-byte accesses (the work vectors are 16-byte aligned)
 __global__ void cg_pupdate_kernel(int64_t n, CgBuffers B) {
   const KspState* s = B.st;
   if (s->done) return;
   const bool first = (s->its == 0);
   const double b = first ? 0.0 : s->beta / s->betaold;
+  const double a = s->alpha;
   const int64_t n2 = n >> 1;
   const double2* z2 = reinterpret_cast<const double2*>(B.z);
   double2* p2 = reinterpret_cast<double2*>(B.p);
+  double2* x2 = reinterpret_cast<double2*>(B.x);
   for (int64_t i = blockIdx.x * (int64_t)BLK + threadIdx.x; i < n2; i += (int64_t)gridDim.x * BLK) {
     const double2 z = z2[i];
     double2 p = z;
     if (!first) {
       const double2 q = p2[i];
+      double2 x = x2[i];
+      x.x += a * q.x;
+      x.y += a * q.y;
+      x2[i] = x;
       p.x = z.x + b * q.x;
       p.y = z.y + b * q.y;
     }
     p2[i] = p;
   }
-  if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) B.p[n - 1] = first ? B.z[n - 1] : B.z[n - 1] + b * B.p[n - 1];
+  if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
+    const int64_t i = n - 1;
+    if (first) {
+      B.p[i] = B.z[i];
+    } else {
+      const double q = B.p[i];
+      B.x[i] += a * q;
+      B.p[i] = B.z[i] + b * q;
+    }
+  }
 }
 
 // w = A p, per-CTA partial of p.w  (CSR-stream kernel, see spmv.cuh)
@@ -200,7 +220,8 @@ cg_tmat_boundary_kernel(pyn::TmatView m, int rd, CgBuffers B) {
   if (lane == 0) B.w[row] = s;
 }
 
-// a = beta / (p.w) ; x += a p ; r -= a w ; z = M^-1 r ; partials of z.z, z.r   (input partials: nparts_in of p.w)
+// a = beta / (p.w) ; r -= a w ; z = M^-1 r ; partials of z.z, z.r   (input partials: nparts_in of p.w);
+// x += a p is left to the next cg_pupdate_kernel / cg_finish_kernel (state: alpha, pend)
 __global__ void cg_update_kernel(int64_t n, int nparts_in, CgBuffers B, double* __restrict__ out_a,
                                  double* __restrict__ out_b, const double* __restrict__ g) {
   __shared__ double sm[BLK / 32];
@@ -215,22 +236,17 @@ __global__ void cg_update_kernel(int64_t n, int nparts_in, CgBuffers B, double* 
   const double a = s_a;
   double szz = 0.0, szr = 0.0;
   const int64_t n2 = n >> 1;
-  double2* x2 = reinterpret_cast<double2*>(B.x);
   double2* r2 = reinterpret_cast<double2*>(B.r);
   double2* z2 = reinterpret_cast<double2*>(B.z);
-  const double2* p2 = reinterpret_cast<const double2*>(B.p);
   const double2* w2 = reinterpret_cast<const double2*>(B.w);
   const double2* d2 = reinterpret_cast<const double2*>(B.dinv);
   for (int64_t i = blockIdx.x * (int64_t)BLK + threadIdx.x; i < n2; i += (int64_t)gridDim.x * BLK) {
-    const double2 p = p2[i], w = w2[i], d = d2[i];
-    double2 x = x2[i], r = r2[i], z;
-    x.x += a * p.x;
-    x.y += a * p.y;
+    const double2 w = w2[i], d = d2[i];
+    double2 r = r2[i], z;
     r.x -= a * w.x;
     r.y -= a * w.y;
     z.x = d.x * r.x;
     z.y = d.y * r.y;
-    x2[i] = x;
     r2[i] = r;
     z2[i] = z;
     szz += z.x * z.x;
@@ -240,7 +256,6 @@ __global__ void cg_update_kernel(int64_t n, int nparts_in, CgBuffers B, double* 
   }
   if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
     const int64_t i = n - 1;
-    B.x[i] += a * B.p[i];
     const double r = B.r[i] - a * B.w[i];
     const double z = B.dinv[i] * r;
     B.r[i] = r;
@@ -267,6 +282,8 @@ __global__ void cg_scalar_kernel(int nparts_pw, int nparts, CgBuffers B, const d
   const double zr = g ? g[2] : pyn::reduce_partials(pzr, nparts);
   if (threadIdx.x == 0) {
     s->its += 1;
+    s->alpha = s->beta / dpi;   // the same quotient cg_update_kernel used
+    s->pend = 1;
     s->betaold = s->beta;
     s->dp = sqrt(zz);
     if (!(dpi > 0.0)) {  // KSP_DIVERGED_INDEFINITE_MAT
@@ -288,6 +305,18 @@ __global__ void cg_scalar_kernel(int nparts_pw, int nparts, CgBuffers B, const d
       s->reason = 3;
       s->done = 1;
     }
+  }
+}
+
+// solution out: x plus the step of the last iteration that no p-update has applied yet
+__global__ void cg_finish_kernel(int64_t n, CgBuffers B, double* __restrict__ dst) {
+  const KspState* s = B.st;
+  const bool pend = s->pend != 0;
+  const double a = s->alpha;
+  for (int64_t i = blockIdx.x * (int64_t)BLK + threadIdx.x; i < n; i += (int64_t)gridDim.x * BLK) {
+    double x = B.x[i];
+    if (pend) x += a * B.p[i];
+    dst[i] = x;
   }
 }
 
@@ -458,7 +487,7 @@ int pyn_ksp_solve(pyn_ksp* k, const double* d_b, double* d_x, pyn_ksp_result* re
     launches += 4 * (int64_t)chunk;
   }
   pyn::count_launch((int)((dist ? 6 : 4) * (int64_t)k->h_state->its));  // only the launches that did work are claimed
-  copy_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, k->B.x, d_x);
+  cg_finish_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, k->B, d_x);
   PYN_CHECK_LAUNCH();
   PYN_CHECK_CUDA(cudaStreamSynchronize(st));
   if (res) {

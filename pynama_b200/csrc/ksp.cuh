@@ -6,7 +6,8 @@
 
 struct KspState {
   double beta, betaold, dp, rnorm0, ttol;
-  int its, reason, done, pad;
+  double alpha;   // CG: step length of the last iteration; x += alpha p is applied by the NEXT p-update (or the finish)
+  int its, reason, done, pend;   // pend: that update of x is still outstanding
 };
 
 struct CgBuffers {
