@@ -466,18 +466,34 @@ def e2e_phase(a, prob, be, torch, barrier):
     rcls_h = torch.from_numpy(host_r).pin_memory() if prob.dom.partition is not None else None
     diag_h = [torch.empty(prob.nrows, dtype=torch.float64).pin_memory() for _ in range(2)]
     ev = lambda: torch.cuda.Event(enable_timing=True)
-    main, side = torch.cuda.current_stream(), torch.cuda.Stream()
+    main, side, up = torch.cuda.current_stream(), torch.cuda.Stream(), torch.cuda.Stream()
+    hold = [None, None]         # inputs + boundary maps of the last two steps (released on `up`, see below)
+    assembled = [None, None]    # event: the assembly that read them has finished
 
     def one(i):
-        cc = cc_h.to("cuda", non_blocking=True)
-        cls = cls_h.to("cuda", non_blocking=True)
-        rcls = rcls_h.to("cuda", non_blocking=True) if rcls_h is not None else None
+        # Three streams, two buffers each way.  `up`: this step's inputs host -> device and their boundary maps (the
+        # one scalar the map construction reads back synchronises only this stream); `main`: integration + assembly +
+        # diagonal; `side`: the result device -> host.  Step i+1's upload overlaps step i's assembly, step i's download
+        # overlaps step i+1's assembly; every step still pays its own H2D, kernels and D2H.
+        with torch.cuda.stream(up):
+            if assembled[i & 1] is not None:
+                up.wait_event(assembled[i & 1])     # step i-2 no longer reads the buffers released just below
+            cc = cc_h.to("cuda", non_blocking=True)
+            cls = cls_h.to("cuda", non_blocking=True)
+            rcls = rcls_h.to("cuda", non_blocking=True) if rcls_h is not None else None
+            maps = prob.mat.prepareBoundaryMaps(prob.dom, cls, rcls)
+            hold[i & 1] = (cc, cls, rcls, maps)
+            ready = torch.cuda.Event()
+            ready.record(up)
+        main.wait_event(ready)
+        for t in (cc, cls, rcls):
+            if t is not None:
+                t.record_stream(main)
         mats = prob.step(classes=cls, row_classes=rcls, corners=cc)
         d = mats["K"].diagonal()
-        # the result goes home on a second stream into one of two pinned buffers: the copy of step i overlaps the
-        # host->device copies and kernels of step i+1 (every step still pays its own H2D, kernels and D2H)
         done = torch.cuda.Event()
         done.record(main)
+        assembled[i & 1] = done
         side.wait_event(done)
         with torch.cuda.stream(side):
             diag_h[i & 1].copy_(d, non_blocking=True)
@@ -499,7 +515,8 @@ def e2e_phase(a, prob, be, torch, barrier):
     h2d = cc_h.numel() * 8 + cls_h.numel() + (rcls_h.numel() if rcls_h is not None else 0)
     return {"ms": s.elapsed_time(e) / steps, "h2d": h2d, "d2h": diag_h[0].numel() * 8,
             "what": "pinned host corner coords + int8 dof classes -> device; integrate + assemble 8 matrices; "
-                    "diag(K) -> pinned host (second stream, two buffers: overlaps the next step)"}
+                    "diag(K) -> pinned host; uploads (+ boundary maps) and downloads on their own streams, two buffers "
+                    "each way: they overlap the neighbouring steps' assembly"}
 
 
 if __name__ == "__main__":

@@ -86,6 +86,22 @@ class MatNS(Mat):
         host = noSlipDofClasses(dom, self.globalIndicesNS, self.globalIndicesDIR)
         return host, rowClasses(dom, host, 2)
 
+    def prepareBoundaryMaps(self, dom, classes, rowClassesDev=None):
+        """Boundary maps (flags + list of the boundary-affected nodes, csrc/assemble.cu pyn_bcmap_create) of a set of
+        device dof classes; a no-op when `classes` is the object already prepared.  Runs on the CURRENT stream and
+        reads one scalar back, so a caller that streams its inputs can call it on an upload stream ahead of
+        `assembleFromMesh` (bench.py end-to-end phase) instead of stalling the assembly stream."""
+        if getattr(self, "dofClasses", None) is classes:
+            return self._maps
+        if rowClassesDev is None:
+            if dom.partition is not None:
+                raise Exception("partitioned mesh: pass rowClassesDev together with classes")
+            rowClassesDev = classes
+        topo = dom.topology()
+        self.dofClasses, self.rowClasses = classes, rowClassesDev
+        self._maps = (be.BcMap(topo, self.rowClasses, 2, classes, 2), be.BcMap(topo, self.rowClasses, 2))
+        return self._maps
+
     def assembleFromMesh(self, dom, elemType, names=None, classes=None, rowClassesDev=None, corners=None, after=None):
         """NoSlipFreeSlip.buildKLEMats for the whole mesh on the device (cell 0's element matrices for every cell,
         base_problem.py:333-334).  `names` restricts the matrices (default: all eight); re-assembly on an existing
@@ -97,13 +113,7 @@ class MatNS(Mat):
             host, hostRows = self.hostDofClasses(dom)
             classes = be.to_device(host)
             rowClassesDev = classes if dom.partition is None else be.to_device(hostRows)
-        if getattr(self, "dofClasses", None) is not classes:
-            if rowClassesDev is None:
-                if dom.partition is not None:
-                    raise Exception("partitioned mesh: pass rowClassesDev together with classes")
-                rowClassesDev = classes
-            self.dofClasses, self.rowClasses = classes, rowClassesDev
-            self._maps = (be.BcMap(topo, self.rowClasses, 2, classes, 2), be.BcMap(topo, self.rowClasses, 2))
+        self.prepareBoundaryMaps(dom, classes, rowClassesDev)
         if corners is None:
             corners = dom.deviceCellCorners(0, 1)
         Ke, Rwe, Rde = elemType.getElemKLEMatricesDevice(corners, want_rd=True)
