@@ -283,6 +283,7 @@ asm_template_kernel(pyn::TopoView t, DescView d, double* __restrict__ T) {
   }
 }
 
+__device__ int g_stream_warp_only = 0;   // PYN_ASM_WARP_ONLY=1: keep the per-warp streaming only (A/B measurements)
 constexpr int ASM_SB = 256;  // nodes per CTA batch of the stream kernel
 constexpr int ASM_SG = ASM_SB / 8;   // consecutive nodes per warp
 template <int RD, int CD>
@@ -310,6 +311,31 @@ asm_stream_kernel(pyn::TopoView t, DescView d, const int64_t* __restrict__ indpt
     // a warp takes ASM_SG consecutive nodes.  When their rows are equally long, adjacent in the CSR data and 16-byte
     // aligned (runs of cell-interior or edge nodes: almost always), the group is ONE contiguous destination range:
     // full-warp double2 stores, the source template found by a division -- short rows no longer leave lanes idle.
+    // Whole batch uniform (the common case away from the walls and from the borders between node kinds): the CTA
+    // streams the batch's one contiguous destination range with all 256 threads, so that at any instant its 8 warps
+    // store 4 kB of ADJACENT addresses -- the access order of a plain fill, which is what HBM write-back likes.
+    bool oka = true;
+    if (tid < nb) {
+      const int n00 = s_len[0];
+      oka = n00 > 0 && s_len[tid] == n00 && s_base[tid] == s_base[0] + (int64_t)tid * n00 &&
+            ((s_src[tid] | s_base[0] | n00) & 1) == 0;
+    }
+    const bool cta_uniform = __syncthreads_and(oka) && !g_stream_warp_only;
+    if (cta_uniform) {
+      const int n2 = s_len[0] >> 1, total2 = nb * n2;
+      const unsigned magic = (unsigned)((0x100000000ull + (unsigned)n2 - 1) / (unsigned)n2);
+      const double2* T2 = reinterpret_cast<const double2*>(T);
+      double2* d2 = reinterpret_cast<double2*>(data + s_base[0]);
+#pragma unroll 4
+      for (int i = tid; i < total2; i += ASM_SB) {
+        const int jj = (int)__umulhi((unsigned)i, magic), k = i - jj * n2;
+        double2 v = __ldg(T2 + (s_src[jj] >> 1) + k);
+        if (d.rowscale) { const double rs = s_rs[jj]; v.x = rs * v.x; v.y = rs * v.y; }
+        d2[i] = v;
+      }
+      __syncthreads();
+      continue;
+    }
     const int j0 = w * ASM_SG, cnt = min(ASM_SG, nb - j0);
     if (cnt > 0) {
       const int n0 = s_len[j0];
@@ -612,8 +638,19 @@ static int launch_templates(const pyn_topo* t, const DescView& dv, const int64_t
   if (!tm->sig_tmpl) PYN_CHECK_CUDA(cudaMalloc(&tm->sig_tmpl, sizeof(double) * (size_t)t->sig_slots * 9));
   double* T = tm->sig_tmpl;
   const int tgrid = (t->nsig + 3) / 4;
-  const int sgrid = pyn::grid_for((t->nnodes + ASM_SB - 1) / ASM_SB * 256, 256, 8);
+  // One CTA per batch, NOT a persistent grid: CTAs are dispatched in batch order and start staggered, so the stores in
+  // flight sweep the array like a plain fill.  Persistent CTAs stay in lock-step at addresses one batch stride apart and
+  // lose ~20 % of the write bandwidth (tools/microbench/store_patterns*.cu: 6.2 vs 7.6 TB/s).  PYN_ASM_PERSISTENT=1: A/B.
+  const int64_t nbatch_s = (t->nnodes + ASM_SB - 1) / ASM_SB;
+  static const bool persistent_grid = getenv("PYN_ASM_PERSISTENT") != nullptr;
+  const int sgrid = persistent_grid || nbatch_s > 0x7fffffff ? pyn::grid_for(nbatch_s * 256, 256, 8) : (int)nbatch_s;
   bool done = false;
+  static const bool warp_only_set = [] {
+    const int v = getenv("PYN_ASM_WARP_ONLY") ? 1 : 0;
+    if (v) cudaMemcpyToSymbol(g_stream_warp_only, &v, sizeof(v));
+    return true;
+  }();
+  (void)warp_only_set;
 #define PYN_ASM_CASE(R, C)                                                                        \
   if (!done && dv.rdof == R && dv.cdof == C) {                                                    \
     asm_template_kernel<R, C><<<tgrid, 128, 0, st>>>(tv, dv, T);                                  \
