@@ -35,7 +35,7 @@ struct PcEpi {
     w[row] = dinv[row] * r;
   }
 };
-__global__ void __launch_bounds__(pyn::SP_BLK)
+__global__ void __launch_bounds__(pyn::SP_BLK, 6)
 gmres_spmv_kernel(pyn::SpmvPlanView P, const int* __restrict__ ind, const double* __restrict__ val,
                   const double* __restrict__ x, PcEpi epi) {
   __shared__ pyn::SpmvSmem sm;

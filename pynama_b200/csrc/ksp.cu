@@ -172,7 +172,7 @@ struct CgDotEpi {
     *dot += p[row] * s;
   }
 };
-__global__ void __launch_bounds__(pyn::SP_BLK)
+__global__ void __launch_bounds__(pyn::SP_BLK, 6)
 cg_spmv_dot_kernel(pyn::SpmvPlanView P, const int* __restrict__ ind, const double* __restrict__ val, CgBuffers B) {
   __shared__ pyn::SpmvSmem sm;
   __shared__ double red[pyn::SP_BLK / 32];

@@ -71,7 +71,7 @@ struct ModeEpi {
   }
 };
 
-__global__ void __launch_bounds__(pyn::SP_BLK)
+__global__ void __launch_bounds__(pyn::SP_BLK, 6)
 spmv_stream_kernel(pyn::SpmvPlanView P, const int* __restrict__ ind, const double* __restrict__ val,
                    const double* __restrict__ x, ModeEpi epi) {
   __shared__ pyn::SpmvSmem sm;
