@@ -460,7 +460,7 @@ def e2e_phase(a, prob, be, torch, barrier):
     """The same assembly step from HOST buffers through the public API: pinned cell-0 corner coordinates and the
     per-dof boundary classes go host->device, the matrices are integrated + assembled, diag(K) comes back."""
     import numpy as np
-    cc_h = torch.from_numpy(np.asarray(prob.dom.getCellCornersCoords(0)).reshape(1, 4, 2)).pin_memory()
+    cc_h = torch.from_numpy(prob.dom.templateCellCorners()).pin_memory()
     host_c, host_r = prob.mat.hostDofClasses(prob.dom)
     cls_h = torch.from_numpy(host_c).pin_memory()
     rcls_h = torch.from_numpy(host_r).pin_memory() if prob.dom.partition is not None else None

@@ -105,6 +105,8 @@ class BaseProblem(object):
         if self.dom.partition is not None:
             from ..dist import DistContext
             self.comm.dist = DistContext(self.dom.partition)
+            from .. import petsc_like
+            petsc_like.set_dist(self.comm.dist)      # Vec.norm / Vec.dot become global (owned entries, all-reduced)
             self.logger.info(self.dom.partition.describe())
         if not self.comm.rank:
             self.logger.info("DMPlex dom created")

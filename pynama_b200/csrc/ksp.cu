@@ -230,7 +230,8 @@ __global__ void cg_update_kernel(int64_t n, int nparts_in, CgBuffers B, double* 
   if (s->done) return;
   if (threadIdx.x < 32) {
     const double dpi = g ? g[0] : pyn::reduce_partials(B.part_a, nparts_in);
-    if (threadIdx.x == 0) s_a = s->beta / dpi;
+    // indefinite operator (p.w <= 0): take no step, so that r, z and x keep the last good iterate (PETSc returns it)
+    if (threadIdx.x == 0) s_a = (dpi > 0.0) ? s->beta / dpi : 0.0;
   }
   __syncthreads();
   const double a = s_a;
@@ -282,8 +283,8 @@ __global__ void cg_scalar_kernel(int nparts_pw, int nparts, CgBuffers B, const d
   const double zr = g ? g[2] : pyn::reduce_partials(pzr, nparts);
   if (threadIdx.x == 0) {
     s->its += 1;
-    s->alpha = s->beta / dpi;   // the same quotient cg_update_kernel used
-    s->pend = 1;
+    s->alpha = (dpi > 0.0) ? s->beta / dpi : 0.0;   // the same quotient cg_update_kernel used
+    s->pend = (dpi > 0.0) ? 1 : 0;
     s->betaold = s->beta;
     s->dp = sqrt(zz);
     if (!(dpi > 0.0)) {  // KSP_DIVERGED_INDEFINITE_MAT

@@ -25,8 +25,8 @@ struct MaxpyArgs {
   double c[8];
   int m;
 };
-__global__ void maxpy_kernel(int64_t n, const __grid_constant__ MaxpyArgs a, const double* __restrict__ y0,
-                             double* __restrict__ y) {
+// y0, y and the x_j may alias (in-place updates X = X + sum c_j K_j, r = b - r): no __restrict__ here
+__global__ void maxpy_kernel(int64_t n, const __grid_constant__ MaxpyArgs a, const double* y0, double* y) {
   for (int64_t i = blockIdx.x * (int64_t)BLK + threadIdx.x; i < n; i += (int64_t)gridDim.x * BLK) {
     double s = y0 ? y0[i] : 0.0;
 #pragma unroll

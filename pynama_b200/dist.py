@@ -80,6 +80,15 @@ class DistContext(object):
         call("pyn_comm_allreduce_sum", self._comm, be.ptr(self._scal), len(vals), be.stream())
         return self._scal[:len(vals)].cpu().tolist()
 
+    def allreduce_max(self, value):
+        """Max of one host scalar over the ranks (rendezvous-layer collective: off the hot path)."""
+        if self.world == 1:
+            return float(value)
+        import torch.distributed as dist
+        t = torch.tensor([float(value)], dtype=torch.float64, device=self.owned.device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t[0])
+
     def attach(self, ksp, ncomp=2):
         """Make a backend.Ksp distributed (halo exchange of the search direction + all-reduced scalars)."""
         call("pyn_ksp_set_dist", ksp._h, self._comm, self._halo, int(ncomp), be.ptr(self.owned_rows(ncomp)))

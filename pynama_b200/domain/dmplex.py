@@ -213,6 +213,20 @@ class DMPlexDom(object):
         ncells = self.ncell - cell0 if ncells is None else ncells
         return be.box_cell_corners(self.nx, self.ny_global, self.lower, self.upper, cell0 + self.fy0 * self.nx, ncells)
 
+    def templateCellCorners(self):
+        """Host (1,4,2) corner coordinates of GLOBAL cell 0: the one element the reference integrates when it reuses
+        cell 0's matrices for every cell (base_problem.py:133,333).  Every rank of a partition uses the same cell, so
+        the element matrices -- and with them the assembled rows -- are bit-identical to the serial ones."""
+        hx = (self.upper[0] - self.lower[0]) / self.nx
+        hy = (self.upper[1] - self.lower[1]) / self.ny_global
+        x0, x1 = self.lower[0] + hx * 0, self.lower[0] + hx * 1
+        y0, y1 = self.lower[1] + hy * 0, self.lower[1] + hy * 1
+        return np.array([x0, y0, x1, y0, x1, y1, x0, y1], dtype=float).reshape(1, 4, 2)
+
+    def deviceTemplateCorners(self):
+        from .. import backend as be
+        return be.box_cell_corners(self.nx, self.ny_global, self.lower, self.upper, 0, 1)
+
     def ownedNodeMask(self):
         """bool per local node: owned by this rank (all True without a partition)."""
         if self.partition is None:
@@ -239,9 +253,11 @@ class DMPlexDom(object):
         """nodes on the closure of a border's faces; "Face Sets" 1 down, 2 right, 3 up, 4 left (dmplex.py:160-171)."""
         nx, ny, m = self.nx, self.ny, self.ngl - 2
         k = np.arange(m)
+        # a strip holds a physical border only where its local mesh (ghost row included) reaches the global one: the
+        # ghost row of the last-but-one rank IS the top cell row when the last strip has a single row
         if self.partition is not None and ((name == "down" and self.fy0 > 0) or
-                                           (name == "up" and self.partition.ghost_above)):
-            return np.zeros(0, dtype=np.int64)          # that physical border lies in another rank's strip
+                                           (name == "up" and self.fy0 + self.ny < self.ny_global)):
+            return np.zeros(0, dtype=np.int64)          # that physical border lies outside this rank's local mesh
         if name in ("down", "up"):
             vy = 0 if name == "down" else ny
             verts = self.off_vert + vy * (nx + 1) + np.arange(nx + 1)
@@ -292,8 +308,8 @@ class DMPlexDom(object):
         nodes, normals = [], []
         fx, fy = cell % self.nx, cell // self.nx
         pts, _ = self.getTransitiveClosure(cell)
-        touch = {"down": (fy == 0, pts[1], 1), "right": (fx == self.nx - 1, pts[2], 0),
-                 "up": (fy == self.ny - 1, pts[3], 1), "left": (fx == 0, pts[4], 0)}
+        touch = {"down": (fy + self.fy0 == 0, pts[1], 1), "right": (fx == self.nx - 1, pts[2], 0),
+                 "up": (fy + self.fy0 == self.ny_global - 1, pts[3], 1), "left": (fx == 0, pts[4], 0)}
         for faceName in self.namingConvention:
             on, edge, normal = touch[faceName]
             if on:

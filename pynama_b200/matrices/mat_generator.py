@@ -138,7 +138,7 @@ class Mat(object):
         cls_host = np.repeat(cls_np, self.dim)
         cls = be.to_device(cls_host)
         rcls = cls if dom.partition is None else be.to_device(rowClasses(dom, cls_host, self.dim))
-        corners = dom.deviceCellCorners(0, None if perCell else 1)
+        corners = dom.deviceCellCorners(0, None) if perCell else dom.deviceTemplateCorners()
         Ke, Rwe, _ = elemType.getElemKLEMatricesDevice(corners, want_rd=False)
         m22, m21 = be.BcMap(topo, rcls, 2, cls, 2), be.BcMap(topo, rcls, 2)
         one = (0.0, 0.0, 1.0, 0.0)
@@ -210,7 +210,7 @@ class Operators(Mat):
         `self.spmv[...]` always holds zero-squeezed copies, which is what the time loop multiplies with."""
         topo = dom.topology()
         N = dom.getTotalNodes()
-        S, D, C, W = elemType.getElemKLEOperatorsDevice(dom.deviceCellCorners(0, 1))
+        S, D, C, W = elemType.getElemKLEOperatorsDevice(dom.deviceTemplateCorners())
         Wg = be.assemble_weights(topo, W)
         self.weights = Wg
         rW = Wg.reciprocal()

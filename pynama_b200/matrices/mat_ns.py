@@ -115,7 +115,7 @@ class MatNS(Mat):
             rowClassesDev = classes if dom.partition is None else be.to_device(hostRows)
         self.prepareBoundaryMaps(dom, classes, rowClassesDev)
         if corners is None:
-            corners = dom.deviceCellCorners(0, 1)
+            corners = dom.deviceTemplateCorners()
         Ke, Rwe, Rde = elemType.getElemKLEMatricesDevice(corners, want_rd=True)
         E = {"K": Ke, "Rw": Rwe, "Rd": Rde}
         with be.assembly_batch(topo):     # boundary-list kernels of all matrices overlap the interior streams

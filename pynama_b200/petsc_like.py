@@ -10,8 +10,31 @@ from . import backend as be
 
 
 class NormType:
-    NORM_1, NORM_2, NORM_INFINITY = 0, 2, 3
-    N1, N2, INFINITY = 0, 2, 3
+    """petsc4py.PETSc.NormType values."""
+    NORM_1, NORM_2, NORM_FROBENIUS, NORM_INFINITY = 0, 1, 2, 3
+    N1, N2, FROBENIUS, FRB, INFINITY, INF = 0, 1, 2, 2, 3, 3
+
+
+# Multi-GPU: set by the case layer (cases/base_problem.py setUpDomain) to the rank's DistContext.  Norms and dot products
+# of vectors laid out on the partitioned mesh (size = local nodes x ncomp) then count owned entries only and are summed /
+# maxed over the ranks, like PETSc's parallel Vec.
+_DIST = None
+
+
+def set_dist(ctx):
+    global _DIST
+    _DIST = ctx
+
+
+def _owned_view(t):
+    """(tensor restricted to owned entries, dist context) or (t, None) when the vector is not a partitioned field."""
+    d = _DIST
+    if d is None or d.world == 1:
+        return t, None
+    n = t.numel()
+    if n == 0 or n % d.part.nnodes:
+        return t, None
+    return t * d.owned_rows(n // d.part.nnodes).to(t.dtype), d
 
 
 class Vec(object):
@@ -113,12 +136,23 @@ class Vec(object):
         self.data.reciprocal_()
 
     def dot(self, other):
-        return be.vec_dot(self.data, other.data)
+        t, d = _owned_view(self.data)
+        v = be.vec_dot(t, other.data)
+        return d.allreduce_sum([v])[0] if d is not None else v
 
-    def norm(self, norm_type=2):
-        if norm_type in (2, 3):
-            return be.vec_norm(self.data, norm_type)
-        return float(self.data.abs().sum().item())
+    def norm(self, norm_type=NormType.NORM_2):
+        """petsc4py semantics: 0 = 1-norm, 1 and 2 (Frobenius) = 2-norm, 3 = max norm; global over the ranks."""
+        t, d = _owned_view(self.data)
+        if norm_type in (NormType.NORM_2, NormType.NORM_FROBENIUS):
+            v = be.vec_norm(t, 2)
+            return float(np.sqrt(d.allreduce_sum([v * v])[0])) if d is not None else v
+        if norm_type == NormType.NORM_INFINITY:
+            v = be.vec_norm(t, 3)
+            return d.allreduce_max(v) if d is not None else v
+        if norm_type == NormType.NORM_1:
+            v = float(t.abs().sum().item())
+            return d.allreduce_sum([v])[0] if d is not None else v
+        raise Exception(f"unknown norm type {norm_type}")
 
     def max(self):
         v, i = torch.max(self.data, 0)

@@ -37,6 +37,7 @@ class KspSolver(object):
         self.restart = 30
         self.check_every = 0
         self.guess_nonzero = False
+        self.error_if_not_converged = False
         self.its, self.reason, self.rnorm = 0, 0, 0.0
         self.history = []
 
@@ -84,6 +85,7 @@ class KspSolver(object):
         self.restart = o.getInt("ksp_gmres_restart", self.restart)
         self.check_every = o.getInt("ksp_check_every", self.check_every)
         self.guess_nonzero = o.getBool("ksp_initial_guess_nonzero", self.guess_nonzero)
+        self.error_if_not_converged = o.getBool("ksp_error_if_not_converged", self.error_if_not_converged)
 
     def setOperators(self, mat):
         self.mat = mat
@@ -134,13 +136,18 @@ class KspSolver(object):
                 be.vec_maxpy(self._res, b.data, [-1.0], [self._res])   # r = b - A x
                 rr = self._ksp.solve(self._res, self._cor)
                 if rr.reason < 0:
+                    r = rr          # a failed refinement pass fails the "direct" solve
                     break
                 be.vec_axpy(x.data, 1.0, self._cor)
         self.its, self.reason, self.rnorm = r.its, r.reason, r.rnorm
         self.history.append((r.its, r.reason))
         if r.reason < 0:
-            self.logger.warning("KSP did not converge: reason %d after %d iterations (rnorm %.3e)", r.reason, r.its,
-                                r.rnorm)
+            msg = f"KSP did not converge: reason {r.reason} after {r.its} iterations (rnorm {r.rnorm:.3e})"
+            # the reference's default is a direct solve (exact or an error): its iterative stand-in must not hand an
+            # unconverged velocity to the time loop; an iterative KSP only raises under -ksp_error_if_not_converged
+            if self._direct or self.error_if_not_converged:
+                raise Exception(msg)
+            self.logger.warning(msg)
         return r
 
     __call__ = solve

@@ -12,14 +12,17 @@ class Paraviewer:
         self.saveDir = saveDir if os.environ.get("PYNAMA_SAVE") else None
         if self.saveDir:
             os.makedirs(self.saveDir, exist_ok=True)
+        # one file set per rank of a partitioned run (every rank holds its strip + ghosts in local numbering)
+        size = getattr(comm, "size", 1)
+        self._tag = f"-r{getattr(comm, 'rank', 0):02d}" if size > 1 else ""
 
     def saveMesh(self, coords, name="mesh"):
         if self.saveDir:
-            np.savez(os.path.join(self.saveDir, name + ".npz"), coords=coords.getArray())
+            np.savez(os.path.join(self.saveDir, name + self._tag + ".npz"), coords=coords.getArray())
 
     def saveData(self, step, time, *vecs):
         if self.saveDir:
-            np.savez(os.path.join(self.saveDir, f"step-{step:05d}.npz"), time=time,
+            np.savez(os.path.join(self.saveDir, f"step-{step:05d}{self._tag}.npz"), time=time,
                      **{(v.getName() or f"vec{i}"): v.getArray() for i, v in enumerate(vecs)})
 
     def saveVec(self, vec, timeStep=None):

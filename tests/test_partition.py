@@ -139,3 +139,27 @@ def test_distributed_cg_emulation_gloo_world2():
     assert res[0][1] == res[1][1]                       # same iteration count on both ranks
     for rank, its, err, gerr in res:
         assert err < 1e-9 and gerr < 1e-9, res          # owned entries AND ghost entries of x hold the solution
+
+
+@pytest.mark.parametrize("nx,ny,n,world", [(4, 4, 3, 4), (3, 5, 4, 4), (4, 6, 3, 2), (2, 8, 5, 8), (3, 9, 2, 8)])
+def test_partition_dof_classes_match_serial(nx, ny, n, world):
+    """Boundary classes of every rank's local mesh (ghost row included) equal the serial classes of the same nodes --
+    in particular when the ghost row of the last-but-one rank is the top cell row of the global mesh (1-row strips)."""
+    from pynama_b200.matrices.mat_ns import noSlipDofClasses
+    box = {"nelem": [nx, ny], "lower": [0, 0], "upper": [1, 1]}
+    gdom = DMPlexDom(boxMesh=box)
+    gdom.setFemIndexing(n)
+    gdom.setBoundaryCondition([], ["up", "down", "left", "right"])
+    serial = noSlipDofClasses(gdom, gdom.getGlobalIndicesNoSlip(), gdom.getGlobalIndicesDirichlet()).reshape(-1, 2)
+    for r in range(world):
+        p = StripPartition(nx, ny, n, r, world)
+        ldom = DMPlexDom(boxMesh=box, partition=p)
+        ldom.setFemIndexing(n)
+        ldom.setBoundaryCondition([], ["up", "down", "left", "right"])
+        local = noSlipDofClasses(ldom, ldom.getGlobalIndicesNoSlip(), ldom.getGlobalIndicesDirichlet()).reshape(-1, 2)
+        np.testing.assert_array_equal(local, serial[p.local_to_global()], err_msg=f"rank {r}")
+        # the per-cell wall query agrees with the global one for the top and bottom cell rows of the local mesh
+        for c in (0, ldom.ncell - 1):
+            _, normals = ldom.getBorderNodesWithNormal(c, ldom.getBordersNodes())
+            _, gnormals = gdom.getBorderNodesWithNormal(c + p.cell0, gdom.getBordersNodes())
+            assert normals == gnormals
