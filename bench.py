@@ -41,6 +41,8 @@ def parse_args():
     ap.add_argument("--cpu-sample-nx", type=int, default=192, dest="cpu_nx")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-time-loop", action="store_true", dest="no_time_loop")
+    ap.add_argument("--pc", default="jacobi", help="-pc_type of the converged solves in the time-loop phase")
     return ap.parse_args()
 
 
@@ -188,21 +190,51 @@ class CavityAssembly:
     values of the eight MatNS matrices on the prebuilt pattern (NoSlipFreeSlip.buildKLEMats)."""
     NAMES = ("K", "Krhs", "Kfs", "Krhsfs", "Rw", "Rwfs", "Rd", "Rdfs")
 
-    def __init__(self, nx, ngl):
+    def __init__(self, nx, ngl, **extra_options):
         from pynama_b200 import backend as be
         from pynama_b200.cases.cavity import Cavity
         from pynama_b200.common.options import Options
         Options.clear()
         for k, v in (("ksp_type", "cg"), ("pc_type", "jacobi")):
             Options.setValue(k, v)
+        import torch
         self.be = be
+        for k, v in extra_options.items():
+            Options.setValue(k, v)
+
+        def lap(t0=[None]):
+            torch.cuda.synchronize()
+            t1 = time.perf_counter()
+            dt, t0[0] = (None if t0[0] is None else (t1 - t0[0]) * 1e3), t1
+            return dt
+
+        lap()
         self.fem = Cavity(cavity_config(nx, ngl), case="cavity")
         fem = self.fem
         fem.setUpGeneral()
         fem.setUpBoundaryConditions()
         fem.setUpEmptyMats()
-        fem.buildKLEMats()                      # pattern build (count + fill with indices): not timed
+        fem.dom.topology()
+        t_topo = lap()
+        fem.buildKLEMats()                      # pattern build (count + index fill) + first assembly of the values
+        t_first = lap()
         self.dom, self.mat = fem.dom, fem.mat
+        # the same values through the generic (non-template) kernels on the now existing pattern: what the first
+        # assembly spends on values; the difference to `t_first` is the pattern build (counts, scans, index fill)
+        be.set_templates(False)
+        self.step()
+        lap()
+        self.step()
+        t_generic = lap()
+        be.set_templates(True)
+        self.setup = {"topology_ms": t_topo, "pattern_build_ms": max(t_first - t_generic, 0.0),
+                      "first_assembly_ms": t_first, "generic_values_ms": t_generic,
+                      "note": "once per mesh, outside the timed step: topology = mesh numbering, node->element "
+                              "incidence, adjacency, inverse maps, row signatures; first_assembly = "
+                              "NoSlipFreeSlip.buildKLEMats from nothing (pattern counts + index fill + values of the "
+                              "8 matrices, generic gather kernels); generic_values = the values alone through the "
+                              "generic kernels; pattern_build = the difference.  Host wall clock around "
+                              "synchronised launches."}
         own = fem.dom.ownedNodeMask()
         self.dof_owned = 2 * int(own.sum())
         self.nrows = 2 * fem.dom.getTotalNodes()
@@ -245,7 +277,7 @@ def run_native(a):
     nx, n = a.nx, a.ngl
     # strong scaling: the fixed nx x nx mesh is cut into `world` strips of cell rows, one per GPU; a rank assembles the
     # rows of the nodes it owns (complete thanks to one ghost row of cells: no matrix entry crosses NVLink)
-    prob = CavityAssembly(nx, n)
+    prob = CavityAssembly(nx, n, pc_type=a.pc, ksp_max_it=200000, ksp_check_every=50)
     prob.step()
     barrier()
     nnz = {k: v.nnz for k, v in prob.mats.items()}
@@ -311,6 +343,15 @@ def run_native(a):
     barrier()
     if rank == 0:
         out["clocks"] = sampler.stop()
+    out["setup"] = prob.setup
+    if not a.no_time_loop:
+        tl = time_loop_phase(a, prob, be, torch, peak, barrier, world)
+        out["time_loop"] = tl
+        out["rhs_chain"] = tl["rhs_chain"]
+        out["ksp"]["converged"] = dict(tl["solve_kle"]["no_slip_solve"], rtol=tl["rtol"], pc=tl["pc"],
+                                       seconds_per_time_step=tl["seconds_per_time_step"],
+                                       note="the K solve of Cavity.solveKLE (second stage); a time step is 14 such "
+                                            "solves + 7 RHS chains (time_loop)")
     # ---- end to end through the public API from host buffers (rank-local; max over ranks) ----------------------
     if not a.no_e2e:
         e = e2e_phase(a, prob, be, torch, barrier)
@@ -333,6 +374,125 @@ def run_native(a):
         barrier()
         sys.stdout.flush()
         os._exit(0)      # skip destructors: NCCL communicators captured in CUDA graphs are not torn down rank by rank
+
+
+def time_loop_phase(a, prob, be, torch, peak, barrier, world):
+    """The per-time-step half of the metric through the case class (Cavity): operators, the two-stage solveKLE
+    (free-slip solve, wall vorticity, no-slip solve: src/cases/base_problem.py:321-327) to the KSP's own tolerance,
+    the RHS chain Curl (1/rho) DivSrT (2 mu SrT v - rho v(x)v) (base_problem.py:212-232), and the same solve driven from
+    HOST buffers (vorticity in, velocity out).  One RK 5(4) step = 7 evalRHS = 14 solves + 7 chains."""
+    import torch.distributed as dist
+    fem = prob.fem
+    ev = lambda: torch.cuda.Event(enable_timing=True)
+    N = prob.dom.getTotalNodes()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    fem.buildOperators()
+    fem.collectCornerNodes()
+    fem._bcDevice = None
+    fem.setUpSolver()
+    torch.cuda.synchronize()
+    t_ops = (time.perf_counter() - t0) * 1e3
+    dc = fem.comm.dist
+    g = torch.Generator(device="cuda").manual_seed(1234)
+    # a smooth synthetic vorticity field of the cavity's magnitude (the time loop solves for fields like this one, not
+    # for white noise): omega = 4 sin(pi x) sin(pi y) + lid shear layer
+    xy = fem.dom.fullCoordVec.data.view(-1, 2)
+    w = 4.0 * torch.sin(torch.pi * xy[:, 0]) * torch.sin(torch.pi * xy[:, 1]) + 20.0 * torch.exp(-40.0 * (1.0 - xy[:, 1]))
+    fem.vort.data.copy_(w)
+    recs = []
+    for sv in (fem.solverFS, fem.solver):
+        inner = sv._ksp.solve
+
+        def timed(b, x, _inner=inner, _sv=sv):
+            s, e = ev(), ev()
+            s.record()
+            r = _inner(b, x)
+            e.record()
+            torch.cuda.synchronize()
+            recs.append({"its": int(r.its), "reason": int(r.reason), "seconds": s.elapsed_time(e) * 1e-3})
+            return r
+        sv._ksp.solve = timed
+
+    def maxr(x):
+        if world > 1:
+            t = torch.tensor([x], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t[0])
+        return x
+
+    # ---- solveKLE: device resident ----
+    if a.pc != "jacobi":
+        fem.solveKLE(0.0, fem.vort)           # warm-up (graph capture, hierarchy set-up) when a solve is cheap
+    del recs[:]
+    barrier()
+    s, e = ev(), ev()
+    s.record()
+    fem.solveKLE(0.0, fem.vort)
+    e.record()
+    barrier()
+    t_kle = maxr(s.elapsed_time(e) * 1e-3)
+    fs, ns = recs[0], recs[1]
+    # ---- RHS chain: the three operator products of evalRHS with their fused epilogues ----
+    op = fem.operator.spmv
+
+    def chain():
+        op["SrT"].csr.mult(fem.vel.data, fem._Aux1.data, mode=3, p0=2.0 * fem.mu, p1=fem.rho, aux=fem.vel.data)
+        fem._halo(fem._Aux1, fem.dim_s)
+        op["DivSrT"].csr.mult(fem._Aux1.data, fem._rhs.data, mode=2, p0=1 / fem.rho)
+        fem._halo(fem._rhs, fem.dim)
+        op["Curl"].csr.mult(fem._rhs.data, f.data)
+
+    f = fem.vort.duplicate()
+    for _ in range(3):
+        chain()
+    barrier()
+    s, e = ev(), ev()
+    nrep = 10
+    s.record()
+    for _ in range(nrep):
+        chain()
+    e.record()
+    barrier()
+    t_chain = maxr(s.elapsed_time(e) / nrep)
+    # algorithmic bytes: each product's own accounting (element operator: x, connectivity, element results, y;
+    # CSR stream: 12 B per stored entry of the zero-squeezed operator + vectors) + v read again by the fused v(x)v
+    chain_bytes = sum(op[k].csr.bytes_spmv() for k in ("SrT", "DivSrT", "Curl")) + 8 * 2 * N
+    csr_bytes = sum(op[k].csr.bytes_spmv(templates=False) for k in ("SrT", "DivSrT", "Curl")) + 8 * 2 * N
+    # ---- the same solve end to end from host buffers: vorticity host -> device, solveKLE, velocity device -> host
+    w_h = fem.vort.data.cpu().pin_memory()
+    v_h = torch.empty(2 * N, dtype=torch.float64).pin_memory()
+    barrier()
+    s, e = ev(), ev()
+    s.record()
+    fem.vort.data.copy_(w_h, non_blocking=True)
+    fem.solveKLE(0.0, fem.vort)
+    v_h.copy_(fem.vel.data, non_blocking=True)
+    e.record()
+    barrier()
+    t_e2e = maxr(s.elapsed_time(e) * 1e-3)
+    assert bool(torch.isfinite(v_h).all())
+    n_rhs = 7
+    per_step = n_rhs * (t_kle + t_chain * 1e-3)
+    out = {
+        "ksp_type": "cg", "pc": a.pc, "rtol": fem.solver.rtol, "operators_setup_ms": t_ops,
+        "solve_kle": {"seconds": t_kle, "free_slip_solve": fs, "no_slip_solve": ns,
+                      "what": "Cavity.solveKLE: 6 SpMV + KSP on K+Kfs + Curl + KSP on K, zero initial guess, "
+                              "KSPConvergedDefault at the stated rtol"},
+        "rhs_chain": {"ms": t_chain, "bytes": chain_bytes, "achieved": chain_bytes / (t_chain * 1e-3) / 1e9,
+                      "peak": peak, "unit": "GB/s", "frac": chain_bytes / (t_chain * 1e-3) / 1e9 / peak,
+                      "csr_stream_bytes": csr_bytes,
+                      "what": "SrT (+ v(x)v, 2 mu / -rho epilogue), DivSrT (1/rho), Curl on the zero-squeezed "
+                              "operators; interior rows through the element operator, bytes = that path's own "
+                              "accounting; csr_stream_bytes = what the CSR stream of the same operators would move"},
+        "seconds_per_time_step": per_step,
+        "time_step": f"RK 5(4) Bogacki-Shampine, FSAL: {n_rhs} evalRHS per accepted step = {2 * n_rhs} KSP solves + "
+                     f"{n_rhs} RHS chains (measured solveKLE + chain, times {n_rhs})",
+        "e2e_solve": {"seconds": t_e2e, "h2d_bytes": 8 * N * world, "d2h_bytes": 16 * N * world,
+                      "what": "pinned host vorticity -> device, Cavity.solveKLE, velocity -> pinned host"},
+    }
+    return out
+
 
 
 def load_traffic(kernel_substr):
@@ -407,7 +567,7 @@ def ksp_phase(a, prob, be, torch, peak, barrier):
         ms_solve, r = time_cg()
         ms_mult = time_mult()
         nbytes = K.bytes_spmv()
-        it_bytes = nbytes + 8 * K.shape[0] * 12      # + ~12 vector passes per PCG iteration
+        it_bytes = nbytes + 8 * K.shape[0] * 10      # + 10 vector passes per PCG iteration (csrc/ksp.cu; SURVEY 8d: 12)
         ms_it = ms_solve / max(r.its, 1)
         return r, {"kernel": kernel, "ms_per_solve": ms_solve, "ms_per_iteration": ms_it,
                    "iteration_bytes": it_bytes, "iteration_gbs": it_bytes / (ms_it * 1e-3) / 1e9,
