@@ -251,7 +251,7 @@ int pyn_vec_wrms(int64_t n, const double* d_err, const double* d_y, const double
 typedef struct pyn_ksp pyn_ksp;
 typedef struct {
   int32_t type;        /* 0 cg, 1 gmres */
-  int32_t pc;          /* 0 none, 1 jacobi */
+  int32_t pc;          /* 0 none, 1 jacobi, 2 multigrid V-cycle (cg only; attach with pyn_ksp_set_mg) */
   double rtol, atol, dtol;
   int32_t max_it;
   int32_t restart;     /* gmres */
@@ -270,6 +270,27 @@ int pyn_ksp_destroy(pyn_ksp* k);
 int pyn_ksp_stats(const pyn_ksp* k, int64_t* spmv_launches, int64_t* kernel_launches);
 /* CG and GMRES apply the operator through the template operator instead of the CSR stream (NULL: back to the CSR) */
 int pyn_ksp_set_tmat(pyn_ksp* k, const pyn_tmat* m);
+
+/* ------------------------------------------------------------------------------------------------------
+ * Geometric p/h-multigrid V-cycle as the preconditioner of CG (`-pc_type mg`; SURVEY 8f-1: the reference's answer to
+ * the cost of the solve is a factor-once LU, src/solver/ksp_solver.py:13-16).  The caller (pynama_b200/solver/
+ * multigrid.py) builds the levels -- the rediscretised K of the same mesh at lower orders, then of bilinear elements on
+ * meshes coarsened by two -- with the library's own integration / assembly kernels and hands over, per level: the
+ * operator (element operator and/or planned CSR), 1/diag on the unknowns (0 on prescribed dofs), an upper bound of
+ * the spectrum of D^-1 A; per level pair: interpolation P and restriction R = P^T as planned CSR; and the dense
+ * inverse of the coarsest operator.  Smoother: Chebyshev of `degree` on [lmax / ratio, lmax], before and after the
+ * coarse correction (symmetric cycle).  Everything is borrowed; work vectors are allocated on first use.
+ * ---------------------------------------------------------------------------------------------------- */
+typedef struct pyn_mg pyn_mg;
+int pyn_mg_create(int nlevels, int degree, double ratio, pyn_mg** out);
+int pyn_mg_set_level(pyn_mg* g, int level, int64_t n, const pyn_tmat* tmat, const pyn_spmv_plan* plan,
+                     const int32_t* d_ind, const double* d_val, const double* d_dinv, double lmax);
+int pyn_mg_set_transfer(pyn_mg* g, int level, const pyn_spmv_plan* Pplan, const int32_t* d_Pind, const double* d_Pval,
+                        const pyn_spmv_plan* Rplan, const int32_t* d_Rind, const double* d_Rval);
+int pyn_mg_set_coarse_inverse(pyn_mg* g, const double* d_Ainv);   /* [n_c][n_c], row major; NULL: smoother only */
+int pyn_mg_apply(pyn_mg* g, const double* d_r, double* d_z, void* stream);   /* z = V(r); 0 on prescribed dofs */
+int pyn_mg_destroy(pyn_mg* g);
+int pyn_ksp_set_mg(pyn_ksp* k, pyn_mg* g);
 
 /* ------------------------------------------------------------------------------------------------------
  * Multi-GPU: one process per GPU, the mesh cut into strips of cell rows (the reference: DMPlex.distribute(),

@@ -543,25 +543,26 @@ def assemble_operators(mesh):
 # --------------------------------------------------------------------------------------------------------
 # S1  KSP: CG + Jacobi with PETSc semantics (restated from PETSc KSPCG / KSPConvergedDefault docs)
 # --------------------------------------------------------------------------------------------------------
-def ksp_cg_jacobi(A, b, rtol=1e-5, atol=1e-50, dtol=1e4, max_it=10000, jacobi=True, x0=None):
+def ksp_cg_jacobi(A, b, rtol=1e-5, atol=1e-50, dtol=1e4, max_it=10000, jacobi=True, x0=None, pc=None):
     """Left-preconditioned CG, zero initial guess, monitored norm ||M^-1 r||_2, default convergence test
     rnorm <= max(rtol*rnorm0, atol) (src/solver/ksp_solver.py:9-19 with -ksp_type cg -pc_type jacobi).
     x0 (-ksp_initial_guess_nonzero): r0 = b - A x0 and, as in KSPConvergedDefault, rnorm0 = ||M^-1 b|| (the initial
     residual if b = 0).  Returns x, iterations, reason (2 rtol, 3 atol, -3 its, -4 dtol), residual history."""
     n = A.shape[0]
     dinv = 1.0 / A.diagonal() if jacobi else np.ones(n)
+    apply_pc = pc if pc is not None else (lambda v: dinv * v)      # pc: callable z = M^-1 r (e.g. MultigridPC)
     if x0 is None:
         x = np.zeros(n)
         r = b.copy()
     else:
         x = np.array(x0, dtype=float)
         r = b - A @ x
-    z = dinv * r
+    z = apply_pc(r)
     dp = math.sqrt(z @ z)
     hist = [dp]
     rnorm0 = dp
     if x0 is not None:
-        zb = dinv * b
+        zb = apply_pc(b)
         snorm = math.sqrt(zb @ zb)
         rnorm0 = snorm if snorm > 0.0 else dp
     ttol = max(rtol * rnorm0, atol)
@@ -583,7 +584,7 @@ def ksp_cg_jacobi(A, b, rtol=1e-5, atol=1e-50, dtol=1e4, max_it=10000, jacobi=Tr
         a = beta / dpi
         x = x + a * p
         r = r - a * w
-        z = dinv * r
+        z = apply_pc(r)
         dp = math.sqrt(z @ z)
         hist.append(dp)
         if dp <= ttol:
@@ -594,6 +595,141 @@ def ksp_cg_jacobi(A, b, rtol=1e-5, atol=1e-50, dtol=1e4, max_it=10000, jacobi=Tr
             break
         beta = z @ r
     return x, its, reason, hist
+
+
+# --------------------------------------------------------------------------------------------------------
+# 8f-1  geometric p/h-multigrid V-cycle as CG's preconditioner (`-pc_type mg`)
+#
+# Not a restatement of reference code (the reference's answer to the cost of the solve is PETSc's factor-once LU,
+# src/solver/ksp_solver.py:13-16): this is the CPU statement of the algorithm in pynama_b200/solver/multigrid.py +
+# csrc/mg.cu -- same level sequence, same rediscretised operators (this oracle's assemblies), same interpolation, same
+# Chebyshev recurrence, exact coarse solve -- so that the device cycle can be checked against it.
+# --------------------------------------------------------------------------------------------------------
+def mg_coarsening_sequence(nx, ny, ngl, coarse_cells=1024):
+    seq = [(nx, ny, ngl)]
+    n = ngl
+    while n > 2:
+        n = (n - 1) // 2 + 1
+        seq.append((nx, ny, n))
+    while nx % 2 == 0 and ny % 2 == 0 and (nx // 2) * (ny // 2) >= 4 and nx * ny > coarse_cells:
+        nx, ny = nx // 2, ny // 2
+        seq.append((nx, ny, 2))
+    while nx * ny > coarse_cells:
+        nx, ny = max(2, (nx + 1) // 2), max(2, (ny + 1) // 2)
+        seq.append((nx, ny, 2))
+    return seq
+
+
+def mg_node_interpolation(mc, mf):
+    """P [Nf x Nc]: the coarse mesh's tensor-product Lagrange basis at the fine mesh's node coordinates."""
+    xy = mf.node_coords()
+    hx = (mc.upper[0] - mc.lower[0]) / mc.nx
+    hy = (mc.upper[1] - mc.lower[1]) / mc.ny
+    fx = np.clip(np.floor((xy[:, 0] - mc.lower[0]) / hx - 1e-9).astype(int), 0, mc.nx - 1)
+    fy = np.clip(np.floor((xy[:, 1] - mc.lower[1]) / hy - 1e-9).astype(int), 0, mc.ny - 1)
+    r = 1.0 - 2.0 * (xy[:, 0] - (mc.lower[0] + hx * fx)) / hx      # x = x0 + (1 - r) hx / 2
+    s = 1.0 - 2.0 * (xy[:, 1] - (mc.lower[1] + hy * fy)) / hy
+    n = mc.ngl
+    nodes, _ = lobatto_points(n)
+
+    def lag(pts):
+        h = np.ones((len(pts), n))
+        for a in range(n):
+            for m in range(n):
+                if m != a:
+                    h[:, a] *= (pts - nodes[m]) / (nodes[a] - nodes[m])
+        return h
+    H = np.einsum("qa,qb->qab", lag(r), lag(s)).reshape(len(r), n * n)[:, local_order(n)]
+    cn = mc.cell_nodes()[fy * mc.nx + fx]
+    rows = np.repeat(np.arange(mf.nnodes), n * n)
+    keep = np.abs(H.reshape(-1)) > 1e-12
+    return sp.csr_matrix((H.reshape(-1)[keep], (rows[keep], cn.reshape(-1)[keep])), shape=(mf.nnodes, mc.nnodes))
+
+
+class MultigridPC:
+    """z = V(r): Chebyshev(degree) on [lmax/ratio, lmax] of D^-1 A before and after the coarse correction, coarse levels
+    rediscretised, exact coarsest solve; Jacobi on the prescribed dofs (identity rows).  kind: "K" | "KFS" for the
+    cavity (assemble_noslip), "freeslip" for the all-Dirichlet cases (assemble_freeslip)."""
+
+    def __init__(self, nx, ny, ngl, kind="K", lower=(0, 0), upper=(1, 1), degree=3, ratio=10.0, coarse_cells=1024,
+                 power_its=30, fine=None, lmax=None):
+        """fine: use this matrix as the level-0 operator; lmax: per-level spectral bounds to use instead of this
+        class's own power iteration (its start vector differs from the device's, so the bounds agree to ~1e-3 only)."""
+        import scipy.sparse.linalg as spl
+        self.degree, self.ratio = degree, ratio
+        self.levels = []
+        for i, (hx, hy, p) in enumerate(mg_coarsening_sequence(nx, ny, ngl, coarse_cells)):
+            m = BoxMesh([hx, hy], lower, upper, p)
+            if kind == "freeslip":
+                A = fine if (i == 0 and fine is not None) else assemble_freeslip(m, per_cell=False)["K"]
+                bc = np.zeros(m.nnodes, bool)
+                bc[m.boundary_nodes()] = True
+                free = ~np.repeat(bc, 2)
+            else:
+                r = assemble_noslip(m)
+                A = r["K"] if kind == "K" else mat_add(r["K"], r["Kfs"])
+                free = (r["cls"] == 0) if kind == "K" else (r["cls"] < 2)
+                if i == 0 and fine is not None:
+                    A = fine
+            A = sp.csr_matrix(A)
+            L = dict(m=m, A=A, free=free, dinv=np.where(free, 1.0 / A.diagonal(), 0.0))
+            x = np.random.default_rng(0).standard_normal(A.shape[0]) * free
+            lam = 1.0
+            for _ in range(power_its):
+                y = L["dinv"] * (A @ x)
+                lam = np.linalg.norm(y) / np.linalg.norm(x)
+                x = y / np.linalg.norm(y)
+            L["lmax"] = 1.1 * lam if lmax is None else float(lmax[i])
+            if self.levels:
+                f = self.levels[-1]
+                P = sp.kron(mg_node_interpolation(m, f["m"]), sp.identity(2)).tocsr()
+                P = (sp.diags(f["free"].astype(float)) @ P @ sp.diags(free.astype(float))).tocsr()
+                f["P"], f["R"] = P, P.T.tocsr()
+            self.levels.append(L)
+        c = self.levels[-1]
+        idx = np.flatnonzero(c["free"])
+        c["lu"] = (idx, spl.splu(sp.csc_matrix(c["A"][idx][:, idx])))
+        self.jac = 1.0 / self.levels[0]["A"].diagonal()
+
+    def _smooth(self, L, b, x, r, fresh, want_resid):
+        lmax = L["lmax"]
+        lmin = lmax / self.ratio
+        theta, delta = 0.5 * (lmax + lmin), 0.5 * (lmax - lmin)
+        sigma = theta / delta
+        rho = 1.0 / sigma
+        A, dinv = L["A"], L["dinv"]
+        d = dinv * (b if fresh else r) / theta
+        x = d.copy() if fresh else x + d
+        if fresh:
+            r = b.copy()
+        for _ in range(1, self.degree):
+            r = r - A @ d
+            rho_new = 1.0 / (2.0 * sigma - rho)
+            d = rho_new * rho * d + (2.0 * rho_new / delta) * (dinv * r)
+            x = x + d
+            rho = rho_new
+        if want_resid:
+            r = r - A @ d
+        return x, r
+
+    def _cycle(self, l, b):
+        L = self.levels[l]
+        if l == len(self.levels) - 1:
+            idx, lu = L["lu"]
+            x = np.zeros_like(b)
+            x[idx] = lu.solve(b[idx])
+            return x
+        x, r = self._smooth(L, b, None, None, True, True)
+        e = L["P"] @ self._cycle(l + 1, L["R"] @ r)
+        x = x + e
+        r = r - L["A"] @ e
+        x, _ = self._smooth(L, b, x, r, False, False)
+        return x
+
+    def __call__(self, r):
+        free = self.levels[0]["free"]
+        z = self._cycle(0, r)
+        return np.where(free, z, self.jac * r)
 
 
 # --------------------------------------------------------------------------------------------------------

@@ -110,6 +110,13 @@ _SIGNATURES = {
     "pyn_tmat_bytes": (c_i64, [c_vp]),
     "pyn_tmat_supported": (C.c_int, [C.c_int, C.c_int, C.c_int]),
     "pyn_ksp_set_tmat": (C.c_int, [c_vp, c_vp]),
+    "pyn_mg_create": (C.c_int, [C.c_int, C.c_int, c_f64, P(c_vp)]),
+    "pyn_mg_set_level": (C.c_int, [c_vp, C.c_int, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_f64]),
+    "pyn_mg_set_transfer": (C.c_int, [c_vp, C.c_int, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "pyn_mg_set_coarse_inverse": (C.c_int, [c_vp, c_vp]),
+    "pyn_mg_apply": (C.c_int, [c_vp, c_vp, c_vp, c_vp]),
+    "pyn_mg_destroy": (C.c_int, [c_vp]),
+    "pyn_ksp_set_mg": (C.c_int, [c_vp, c_vp]),
     "pyn_ksp_set_dist": (C.c_int, [c_vp, c_vp, c_vp, C.c_int, c_vp]),
 }
 

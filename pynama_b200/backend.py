@@ -470,7 +470,7 @@ def coo_to_csr(rows, cols, vals, shape, name=""):
 class Ksp:
     """Device Krylov solver handle (pyn_ksp_*)."""
     TYPES = {"cg": 0, "gmres": 1}
-    PCS = {"none": 0, "jacobi": 1}
+    PCS = {"none": 0, "jacobi": 1, "mg": 2}
 
     def __init__(self, A: CSR, ksp_type="cg", pc="jacobi", rtol=1e-5, atol=1e-50, dtol=1e4, max_it=10000,
                  restart=30, check_every=0, nonzero_guess=False):

@@ -259,6 +259,8 @@ class BaseProblem(object):
     def setUpSolver(self):
         self.solver = KspSolver()
         self.solver.createSolver(self.mat.K, self.comm)
+        if self.solver.wantsMultigrid():
+            self.solver.setUpMultigrid(self, "K")
         self.vel = self.mat.K.createVecRight()
         self.vel.setName("velocity")
         self.vort = self.mat.Rw.createVecRight()
@@ -306,6 +308,8 @@ class NoSlipFreeSlip(BaseProblem):
         if self.mat.K.csr._tmat_asm is not None:
             KFS.csr.enable_templates(like=self.mat.K.csr)
         self.solverFS.createSolver(KFS, self.comm)
+        if self.solverFS.wantsMultigrid():
+            self.solverFS.setUpMultigrid(self, "KFS")
         self.velFS = self.vel.copy()
         self._vortFS = self.vort.duplicate()
 

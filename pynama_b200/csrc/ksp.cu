@@ -272,6 +272,59 @@ __global__ void cg_update_kernel(int64_t n, int nparts_in, CgBuffers B, double* 
   }
 }
 
+// ---- CG with a general (multigrid) preconditioner: z = M^-1 r is a sequence of launches between these kernels ----
+// r = b, x = 0, p = 0
+__global__ void cg_mg_init_kernel(int64_t n, const double* __restrict__ b, CgBuffers B) {
+  for (int64_t i = blockIdx.x * (int64_t)BLK + threadIdx.x; i < n; i += (int64_t)gridDim.x * BLK) {
+    B.r[i] = b[i];
+    B.x[i] = 0.0;
+    B.p[i] = 0.0;
+  }
+}
+// nonzero initial guess, with p = x0 and w = A p:  r = b - w, x = x0
+__global__ void cg_mg_init_guess_kernel(int64_t n, const double* __restrict__ b, CgBuffers B) {
+  for (int64_t i = blockIdx.x * (int64_t)BLK + threadIdx.x; i < n; i += (int64_t)gridDim.x * BLK) {
+    B.r[i] = b[i] - B.w[i];
+    B.x[i] = B.p[i];
+  }
+}
+// a = beta / (p.w) ; r -= a w
+__global__ void cg_mg_rupdate_kernel(int64_t n, int nparts_in, CgBuffers B) {
+  __shared__ double s_a;
+  const KspState* s = B.st;
+  if (s->done) return;
+  if (threadIdx.x < 32) {
+    const double dpi = pyn::reduce_partials(B.part_a, nparts_in);
+    if (threadIdx.x == 0) s_a = (dpi > 0.0) ? s->beta / dpi : 0.0;
+  }
+  __syncthreads();
+  const double a = s_a;
+  for (int64_t i = blockIdx.x * (int64_t)BLK + threadIdx.x; i < n; i += (int64_t)gridDim.x * BLK) B.r[i] -= a * B.w[i];
+}
+// the cycle left z on the unknowns (mask != 0) and 0 on prescribed dofs: those rows are identity rows, Jacobi there;
+// partials of z.z and z.src  (src = r, or b when |M^-1 b| is wanted)
+__global__ void cg_mg_zdot_kernel(int64_t n, const double* __restrict__ mask, const double* __restrict__ src, CgBuffers B,
+                                  double* __restrict__ out_a, double* __restrict__ out_b) {
+  __shared__ double sm[BLK / 32];
+  double szz = 0.0, szr = 0.0;
+  for (int64_t i = blockIdx.x * (int64_t)BLK + threadIdx.x; i < n; i += (int64_t)gridDim.x * BLK) {
+    const double r = src[i];
+    double z = B.z[i];
+    if (mask[i] == 0.0) {
+      z = B.dinv[i] * r;
+      B.z[i] = z;
+    }
+    szz += z * z;
+    szr += z * r;
+  }
+  szz = pyn::block_sum<BLK>(szz, sm);
+  szr = pyn::block_sum<BLK>(szr, sm);
+  if (threadIdx.x == 0) {
+    out_a[blockIdx.x] = szz;
+    if (out_b) out_b[blockIdx.x] = szr;
+  }
+}
+
 // end of iteration: norms, convergence test, new beta  (one warp)
 __global__ void cg_scalar_kernel(int nparts_pw, int nparts, CgBuffers B, const double* __restrict__ pzz,
                                  const double* __restrict__ pzr, double atol, double dtol, int max_it,
@@ -371,6 +424,12 @@ int enqueue_cg_iteration(const pyn_ksp* k, cudaStream_t st) {
     int rc = pyn::comm_allreduce_sum(k->comm, k->gsum, 1, st);
     if (rc) return rc;
   }
+  if (k->mg) {   // z = V-cycle(r): r -= a w, the cycle's launches, then the Jacobi rows + the two dot products
+    cg_mg_rupdate_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, npw, k->B);
+    int rc = pyn::mg_apply(k->mg, k->B.r, k->B.z, st);
+    if (rc) return rc;
+    cg_mg_zdot_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, k->mg->L[0].dinv, k->B.r, k->B, k->pzz, k->pzr);
+  } else
   cg_update_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, npw, k->B, k->pzz, k->pzr, g);
   if (dist) {
     cg_reduce_kernel<<<1, 32, 0, st>>>(k->vgrid, k->pzz, k->pzr, k->gsum + 1);
@@ -390,11 +449,12 @@ int pyn_ksp_create(int64_t nrows, const int64_t* d_ptr, const int32_t* d_ind, co
                    const pyn_ksp_opts* opts, void* stream, pyn_ksp** out) {
   PYN_REQUIRE(nrows > 0 && d_ptr && d_ind && d_val && opts && out, "bad arguments");
   PYN_REQUIRE(opts->type == 0 || opts->type == 1, "ksp type must be 0 (cg) or 1 (gmres)");
+  PYN_REQUIRE(opts->pc >= 0 && opts->pc <= 2 && !(opts->pc == 2 && opts->type != 0), "pc must be 0 (none), 1 (jacobi) or 2 (mg, cg only)");
   cudaStream_t st = pyn::as_stream(stream);
   pyn_ksp* k = new pyn_ksp();
   memset(k, 0, sizeof(*k));
   k->n = nrows; k->nnz = nnz; k->ptr = d_ptr; k->ind = d_ind; k->val = d_val; k->opts = *opts;
-  if (k->opts.check_every <= 0) k->opts.check_every = 16;
+  if (k->opts.check_every <= 0) k->opts.check_every = opts->pc == 2 ? 2 : 16;
   if (k->opts.max_it <= 0) k->opts.max_it = 10000;
   k->vgrid = pyn::grid_for(nrows, BLK, 8);
   {
@@ -419,7 +479,7 @@ int pyn_ksp_create(int64_t nrows, const int64_t* d_ptr, const int32_t* d_ind, co
   // Jacobi: dinv = 1/diag(A)
   int rc = pyn_csr_diagonal(nrows, d_ptr, d_ind, d_val, k->B.w, stream);
   if (rc) return rc;
-  jacobi_inv_kernel<<<k->vgrid, BLK, 0, st>>>(nrows, k->B.w, k->B.dinv, opts->pc == 1);
+  jacobi_inv_kernel<<<k->vgrid, BLK, 0, st>>>(nrows, k->B.w, k->B.dinv, opts->pc >= 1);
   PYN_CHECK_LAUNCH();
   PYN_CHECK_CUDA(cudaStreamSynchronize(st));
   *out = k;
@@ -430,17 +490,33 @@ int pyn_ksp_solve(pyn_ksp* k, const double* d_b, double* d_x, pyn_ksp_result* re
   PYN_REQUIRE(k && d_b && d_x, "bad arguments");
   cudaStream_t st = pyn::as_stream(stream);
   if (k->opts.type == 1) return pyn::gmres_solve(k, d_b, d_x, res, st);
+  PYN_REQUIRE(k->opts.pc != 2 || k->mg, "pc mg: attach the hierarchy first (pyn_ksp_set_mg)");
   int64_t launches = 0;
   const bool dist = k->comm && k->comm->world > 1;
   const bool guess = k->opts.nonzero_guess != 0;
+  if (k->mg) PYN_REQUIRE(!dist, "the multigrid preconditioner runs on one GPU (use -pc_type jacobi on a partitioned mesh)");
   if (guess) {   // r0 = b - A x0 with the contents of d_x (KSPSetInitialGuessNonzero)
     cg_reset_kernel<<<1, 1, 0, st>>>(k->B.st);
     copy_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, d_x, k->B.p);
     int npw = 0;
     int rc = enqueue_cg_product(k, st, &npw);
     if (rc) return rc;
+    if (k->mg) {   // |M^-1 b| first (KSPConvergedDefault's reference norm), then z = M^-1 r0
+      rc = pyn::mg_apply(k->mg, d_b, k->B.z, st);
+      if (rc) return rc;
+      cg_mg_zdot_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, k->mg->L[0].dinv, d_b, k->B, k->pzz, nullptr);
+      cg_mg_init_guess_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, d_b, k->B);
+      rc = pyn::mg_apply(k->mg, k->B.r, k->B.z, st);
+      if (rc) return rc;
+      cg_mg_zdot_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, k->mg->L[0].dinv, k->B.r, k->B, k->B.part_a, k->B.part_b);
+    } else
     cg_init_guess_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, d_b, k->B, dist ? k->owned : nullptr, k->pzz);
     launches += 4;
+  } else if (k->mg) {
+    cg_mg_init_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, d_b, k->B);
+    int rc = pyn::mg_apply(k->mg, k->B.r, k->B.z, st);
+    if (rc) return rc;
+    cg_mg_zdot_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, k->mg->L[0].dinv, k->B.r, k->B, k->B.part_a, k->B.part_b);
   } else {
     cg_init_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, d_b, k->B, dist ? k->owned : nullptr);
   }
@@ -530,6 +606,15 @@ int pyn_ksp_set_tmat(pyn_ksp* k, const pyn_tmat* m) {
     PYN_REQUIRE(m->rdof == m->cdof && m->topo->nnodes * m->rdof == k->n, "template operator does not match the system");
   }
   k->tmat = m;
+  if (k->graph) { cudaGraphExecDestroy(k->graph); k->graph = nullptr; }
+  return PYN_OK;
+}
+
+int pyn_ksp_set_mg(pyn_ksp* k, pyn_mg* g) {
+  PYN_REQUIRE(k, "ksp is NULL");
+  PYN_REQUIRE(k->opts.type == 0, "the multigrid preconditioner is available for cg");
+  if (g) PYN_REQUIRE(g->L[0].n == k->n, "multigrid hierarchy does not match the system");
+  k->mg = g;
   if (k->graph) { cudaGraphExecDestroy(k->graph); k->graph = nullptr; }
   return PYN_OK;
 }

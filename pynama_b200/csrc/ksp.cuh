@@ -3,6 +3,7 @@
 #include "dist.cuh"
 #include "spmv.cuh"
 #include "tmat.cuh"
+#include "mg.cuh"
 
 struct KspState {
   double beta, betaold, dp, rnorm0, ttol;
@@ -38,6 +39,7 @@ struct pyn_ksp {
   double* gsum;  // [p.w, z.z, z.r]
   struct pyn_gmres* gm;  // GMRES work space (lazy)
   const pyn_tmat* tmat;  // template operator used for w = A p instead of the CSR stream (pyn_ksp_set_tmat)
+  pyn_mg* mg;            // multigrid preconditioner (pc == 2, pyn_ksp_set_mg); borrowed
 };
 
 struct pyn_gmres;

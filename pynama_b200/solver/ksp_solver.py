@@ -11,6 +11,10 @@ preconditioned residual norm, KSPConvergedDefault.
 `preonly` + `lu` (a sparse direct factorisation) has no device counterpart in this build; it is served by
 Jacobi-preconditioned CG driven to `DIRECT_RTOL` followed by `DIRECT_REFINE` passes of iterative refinement
 (r = b - A x, A d = r, x += d), i.e. "solve to round-off" like a direct solver would, and says so in the log.  Parity statements about KSP are made for `-ksp_type cg -pc_type jacobi` at matched tolerances.
+
+`-pc_type mg` preconditions CG with a geometric p/h-multigrid V-cycle (solver/multigrid.py, csrc/mg.cu):
+rediscretised K on the same mesh at lower orders and on coarsened bilinear meshes, Chebyshev smoothing
+(`-pc_mg_degree`, `-pc_mg_ratio`), dense coarse inverse (`-pc_mg_coarse_cells`).
 """
 import logging
 
@@ -86,6 +90,9 @@ class KspSolver(object):
         self.check_every = o.getInt("ksp_check_every", self.check_every)
         self.guess_nonzero = o.getBool("ksp_initial_guess_nonzero", self.guess_nonzero)
         self.error_if_not_converged = o.getBool("ksp_error_if_not_converged", self.error_if_not_converged)
+        self.mg_degree = o.getInt("pc_mg_degree", 3)                 # Chebyshev smoother degree
+        self.mg_ratio = o.getReal("pc_mg_ratio", 10.0)               # ... on [lmax / ratio, lmax]
+        self.mg_coarse_cells = o.getInt("pc_mg_coarse_cells", 1024)  # coarsest mesh: dense inverse
 
     def setOperators(self, mat):
         self.mat = mat
@@ -106,7 +113,7 @@ class KspSolver(object):
         if ksp_type not in be.Ksp.TYPES:
             raise Exception(f"KSP type {ksp_type} is not available on the device path (cg, gmres)")
         if pc not in be.Ksp.PCS:
-            raise Exception(f"PC type {pc} is not available on the device path (none, jacobi)")
+            raise Exception(f"PC type {pc} is not available on the device path (none, jacobi, mg)")
         csr = self.mat.csr if hasattr(self.mat, "csr") else self.mat
         self._ksp = be.Ksp(csr, ksp_type, pc, rtol=rtol, atol=self.atol, dtol=self.divtol, max_it=max_it,
                            restart=self.restart, check_every=self.check_every,
@@ -114,6 +121,20 @@ class KspSolver(object):
         dist = getattr(self.comm, "dist", None)
         if dist is not None:       # multi-GPU: halo exchange of the search direction + all-reduced scalars
             dist.attach(self._ksp, ncomp=csr.shape[0] // dist.part.nnodes)
+
+    def wantsMultigrid(self):
+        return self._ksp is not None and self._ksp.opts.pc == be.Ksp.PCS["mg"] and getattr(self._ksp, "_mg", None) is None
+
+    def setUpMultigrid(self, fem, kind):
+        """`-pc_type mg`: build the V-cycle levels of this solve from the case (solver/multigrid.py) and attach them.
+        The case layer calls this right after createSolver (the hierarchy needs the mesh and the boundary classes, which
+        the reference's createSolver(mat, comm) signature does not carry)."""
+        from .multigrid import Hierarchy
+        h = Hierarchy(fem, kind, self._ksp.A, degree=self.mg_degree, ratio=self.mg_ratio,
+                      coarse_cells=self.mg_coarse_cells)
+        h.attach(self._ksp)
+        self.logger.info("multigrid: %s", h.describe())
+        return h
 
     def createSolver(self, mat, comm=None):
         self.logger = logging.getLogger("KSP Solver")

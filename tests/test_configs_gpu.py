@@ -105,8 +105,17 @@ def test_taylor_green_64_solve_and_rhs_vs_oracle(tg64):
     # the analytic field: spectral accuracy of the discretisation at this resolution
     assert np.abs(fem.vel.getArray() - vel_ex.reshape(-1)).max() < 1e-6
     fv = fem.vort.duplicate()
-    fem.evalRHS(fem.ts, 0.0, fem.vort, fv)
     f_o = o.eval_rhs_from_vel(ops, x_o, fem.rho, fem.mu)
-    assert rel_err(fv.getArray(), f_o) < 1e-8
+    # the operator chain alone on the oracle's velocity (Curl . DivSrT . SrT amplifies a velocity difference by
+    # ~(1/h_min)^3 ~ 5e7 on this mesh, so the solve is taken out of this comparison) ...
+    solve = fem.solveKLE
+    fem.solveKLE = lambda *a, **k: None
+    fem.vel.setArray(x_o)
+    fem.evalRHS(fem.ts, 0.0, fem.vort, fv)
+    fem.solveKLE = solve
+    assert rel_err(fv.getArray(), f_o) < 1e-11
+    # ... and evalRHS as the time loop calls it (solve included)
+    fem.evalRHS(fem.ts, 0.0, fem.vort, fv)
+    assert rel_err(fv.getArray(), f_o) < 1e-5
     interior = np.setdiff1d(np.arange(m.nnodes), bc)
     assert np.abs(fv.getArray()[interior] + 8 * math.pi ** 2 * nu * w0[interior]).max() < 1e-3 * np.abs(w0).max()
