@@ -42,6 +42,9 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-time-loop", action="store_true", dest="no_time_loop")
+    ap.add_argument("--workload", default="cavity", choices=["cavity", "percell"],
+                    help="cavity: configs[3] (default); percell: FreeSlip, element matrices of every cell (configs[1]/[2])")
+    ap.add_argument("--fused", default=None, help="percell: -mat_fused 0|1 (fused integrate+assemble kernel)")
     ap.add_argument("--pc", default="jacobi", help="-pc_type of the converged solves in the time-loop phase")
     return ap.parse_args()
 
@@ -495,6 +498,109 @@ def time_loop_phase(a, prob, be, torch, peak, barrier, world):
 
 
 
+# ------------------------------------------------------------------------------------------------------------------
+# per-cell workload (BASELINE configs[1]/[2]): FreeSlip.buildKLEMats integrates EVERY cell (base_problem.py:503-506)
+# ------------------------------------------------------------------------------------------------------------------
+def elem_flops(n):
+    """FP64 operations of one sum-factorised element integration (csrc/elem.cu), K and Rw: step 1 builds 16 + 8 T
+    arrays (2 flop per multiply-add over the q2 index, plus the table product), step 2 contracts q1 for the n^4 (i, j)
+    pairs.  nqF = n (full rule), nqG = n - 1 (reduced)."""
+    nqF, nqG, nn = n, n - 1, n * n
+    step1 = 3 * (4 * nqF * nn * nqF + 12 * nqG * nn * nqG) + 3 * (4 * nqF * nn * nqF + 4 * nqG * nn * nqG)
+    step2_k = nn * nn * (nqF * 12 + nqG * 36)
+    step2_r = nn * nn * (nqF * 10 + nqG * 10)
+    return step1 + step2_k + step2_r
+
+
+def run_percell(a):
+    """One step = integrate K_e, Rw_e of every cell from its corner coordinates + assemble K, Krhs, Rw (values on the
+    prebuilt pattern) through the reference's case class (CustomFuncCase -> FreeSlip.buildKLEMats)."""
+    import torch
+    import yaml
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (B200); there is no CPU fallback.")
+    torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
+    from pynama_b200 import backend as be
+    from pynama_b200.cases.custom_func import CustomFuncCase
+    from pynama_b200.common.options import Options
+    Options.clear()
+    for k, v in (("ksp_type", "cg"), ("pc_type", "jacobi")):
+        Options.setValue(k, v)
+    if a.fused is not None:
+        Options.setValue("mat_fused", a.fused)
+    with open(os.path.join(ROOT, "pynama_b200", "cases", "taylor-green.yaml")) as f:
+        cfg = yaml.load(f, Loader=yaml.Loader)
+    nx, n = a.nx, a.ngl
+    fem = CustomFuncCase(cfg, case="taylor-green", ngl=n, nelem=[nx, nx])
+    fem.setUpGeneral()
+    fem.setUpBoundaryConditions()
+    fem.setUpEmptyMats()
+    fem.buildKLEMats()
+    torch.cuda.synchronize()
+    ev = lambda: torch.cuda.Event(enable_timing=True)
+    names = ("elem", "K", "Krhs", "Rw")
+
+    def step(events=None):
+        after = None
+        if events is not None:
+            events[0].record()
+            after = {nm: events[i + 1].record for i, nm in enumerate(names)}
+        fem.mat.assembleFromMesh(fem.dom, fem.elemType, perCell=True, after=after)
+
+    for _ in range(a.warmup):
+        step()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(0)
+    sampler.start()
+    time.sleep(0.25)
+    l0 = be.launch_count()
+    evs = [[ev() for _ in range(len(names) + 1)] for _ in range(a.steps)]
+    t0, t1 = ev(), ev()
+    t0.record()
+    for i in range(a.steps):
+        step(evs[i])
+    t1.record()
+    torch.cuda.synchronize()
+    launches = be.launch_count() - l0
+    clocks = sampler.stop()
+    ms_step = t0.elapsed_time(t1) / a.steps
+    phase = {nm: sum(e[i].elapsed_time(e[i + 1]) for e in evs) / a.steps for i, nm in enumerate(names)}
+    peak, peak_src = measured_peak_hbm()
+    K, Rw, Krhs = fem.mat.K.csr, fem.mat.Rw.csr, fem.mat.Krhs.csr
+    ne, nn = fem.dom.ncell, n * n
+    dof = K.shape[0]
+    fused = bool(getattr(fem.mat, "fusedAssembly", False))
+    elem_bytes = 64 * ne + (0 if fused else 8 * ne * (4 * nn * nn + 2 * nn * nn))
+    k_bytes = 8 * K.nnz + 8 * (K.shape[0] + 1) + 64 * ne
+    fl = elem_flops(n) * ne
+    t_k = phase["K"] + (phase["elem"] if fused else 0.0)
+    out = {
+        "metric": METRIC, "value": dof / (ms_step * 1e-3), "unit": "DOF/s", "n_gpus": 1, "steps": a.steps,
+        "warmup": a.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic",
+        "config": {"workload": f"per-cell: Taylor-Green {nx}x{nx} elements ngl {n} (BASELINE configs[1]/[2]): "
+                               f"getElemKLEMatrices for EVERY cell + K, Krhs, Rw values on the prebuilt pattern "
+                               f"(FreeSlip.buildKLEMats, base_problem.py:499-552)",
+                   "dof_rows": dof, "cells": ne, "nnz": {"K": K.nnz, "Krhs": Krhs.nnz, "Rw": Rw.nnz},
+                   "fused_integrate_assemble": fused,
+                   "l2": "outputs exceed the 126 MB L2; no flush needed"},
+        "phases_ms": phase,
+        "integration": {"kernel": "elem_kle_kernel (K_e, Rw_e of every cell)", "ms": phase["elem"], "flop": fl,
+                        "tflops": fl / (phase["elem"] * 1e-3) / 1e12 if phase["elem"] > 0 else None,
+                        "bytes": elem_bytes, "gbs": elem_bytes / (phase["elem"] * 1e-3) / 1e9 if phase["elem"] > 0 else None,
+                        "hbm_frac": elem_bytes / (phase["elem"] * 1e-3) / 1e9 / peak if phase["elem"] > 0 else None,
+                        "flop_per_byte": fl / elem_bytes,
+                        "fp64_peak_tflops": 37.0, "fp64_frac": fl / (phase["elem"] * 1e-3) / 1e12 / 37.0 if phase["elem"] > 0 else None},
+        "roofline": {"bound": "hbm", "kernel": "K from corner coordinates: " + ("fused integrate+assemble" if fused else
+                                                                             "asm_interior_kernel<2,2> on materialised K_e"),
+                     "achieved": k_bytes / (t_k * 1e-3) / 1e9, "peak": peak, "unit": "GB/s", "peak_source": peak_src,
+                     "frac": k_bytes / (t_k * 1e-3) / 1e9 / peak, "ms_per_launch": t_k, "bytes_per_launch": k_bytes,
+                     "traffic": None},
+        "gpu_launches": int(launches), "clocks": clocks,
+    }
+    print(json.dumps(out), flush=True)
+
+
 def load_traffic(kernel_substr):
     """DRAM bytes per launch of a kernel from the committed `ncu --set full` summary (profiles/traffic.json), or None."""
     p = os.path.join(ROOT, "profiles", "traffic.json")
@@ -683,5 +789,7 @@ if __name__ == "__main__":
     args = parse_args()
     if args.impl == "reference":
         run_reference(args)
+    elif args.workload == "percell":
+        run_percell(args)
     else:
         run_native(args)

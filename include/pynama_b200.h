@@ -62,6 +62,15 @@ int pyn_elem_destroy(pyn_elem* e);
  * d_K [ne][2nn][2nn], d_Rw [ne][2nn][nn], d_Rd [ne][2nn][nn]; index = localNode*2 + comp. */
 int pyn_elem_kle(const pyn_elem* e, const double* d_coords, int64_t ne,
                  double* d_K, double* d_Rw, double* d_Rd, void* stream);
+/* Affine elements (parallelograms: every box mesh of the reference): the same quadrature in closed form -- 17
+ * coefficients per element and six 1-D matrices (csrc/elem_affine.cuh, SURVEY 8a').  pyn_elem_affine_coef writes
+ * d_coef [ne][18] and returns the number of NON-affine elements (synchronises when h_nonaffine is given): zero means the
+ * mesh can take pyn_elem_kle_affine (materialised element matrices, same layout as pyn_elem_kle, equal to it to
+ * round-off) or the fused integrate-and-assemble kernels (pyn_asm_desc.d_coef), which are bit-identical to each other. */
+int pyn_elem_affine_coef(const pyn_elem* e, const double* d_coords, int64_t ne, double* d_coef, int64_t* h_nonaffine,
+                         void* stream);
+int pyn_elem_kle_affine(const pyn_elem* e, const double* d_coef, int64_t ne, double* d_K, double* d_Rw, double* d_Rd,
+                        void* stream);
 /* d_SrT [ne][3nn][2nn], d_DivSrT [ne][2nn][3nn], d_Curl [ne][nn][2nn], d_W [ne][nn] */
 int pyn_elem_ops(const pyn_elem* e, const double* d_coords, int64_t ne,
                  double* d_SrT, double* d_DivSrT, double* d_Curl, double* d_W, void* stream);
@@ -131,6 +140,11 @@ typedef struct {
   int64_t E_stride;          /* elements between consecutive element matrices in doubles; 0 = one for all cells */
   const double* d_rowscale;  /* [nnodes] or NULL */
   const pyn_bcmap* bcmap;    /* NULL, or the map built from (d_rclass, rdof, d_cclass, cdof) */
+  /* fused integrate-and-assemble on affine elements: when d_coef is set (pyn_elem_affine_coef) the entries of K_e
+   * (which 0, 2x2 blocks), Rw_e (1) or Rd_e (2; 2x1 blocks) are evaluated while the rows are written and d_E is ignored */
+  const double* d_coef;      /* [ne][18] or NULL */
+  const pyn_elem* elem;      /* element handle the coefficients were computed with */
+  int32_t which;
 } pyn_asm_desc;
 
 /* pattern: row pointers (exclusive scan done inside), total nnz returned on the host (synchronises) */

@@ -21,7 +21,8 @@ class AsmDesc(C.Structure):
     """pyn_asm_desc"""
     _fields_ = [("rdof", c_i32), ("cdof", c_i32), ("d_rclass", c_vp), ("d_cclass", c_vp),
                 ("pair_mask", C.c_uint32), ("diag_classes", C.c_uint32), ("diag_add", c_f64 * 4),
-                ("sign", c_f64), ("d_E", c_vp), ("E_stride", c_i64), ("d_rowscale", c_vp), ("bcmap", c_vp)]
+                ("sign", c_f64), ("d_E", c_vp), ("E_stride", c_i64), ("d_rowscale", c_vp), ("bcmap", c_vp),
+                ("d_coef", c_vp), ("elem", c_vp), ("which", c_i32)]
 
 
 class KspOpts(C.Structure):
@@ -45,6 +46,8 @@ _SIGNATURES = {
                                   c_vp, c_vp, c_vp, c_vp, c_f64, c_f64, P(c_vp)]),
     "pyn_elem_destroy": (C.c_int, [c_vp]),
     "pyn_elem_kle": (C.c_int, [c_vp, c_vp, c_i64, c_vp, c_vp, c_vp, c_vp]),
+    "pyn_elem_affine_coef": (C.c_int, [c_vp, c_vp, c_i64, c_vp, P(c_i64), c_vp]),
+    "pyn_elem_kle_affine": (C.c_int, [c_vp, c_vp, c_i64, c_vp, c_vp, c_vp, c_vp]),
     "pyn_elem_ops": (C.c_int, [c_vp, c_vp, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "pyn_box_cell_nodes": (C.c_int, [C.c_int, C.c_int, C.c_int, c_i64, c_i64, c_vp, c_vp]),
     "pyn_box_cell_corners": (C.c_int, [C.c_int, C.c_int, c_f64, c_f64, c_f64, c_f64, c_i64, c_i64, c_vp, c_vp]),

@@ -89,6 +89,25 @@ class ElemKernels:
         call("pyn_elem_kle", self._h, ptr(coords), ne, ptr(K), ptr(Rw), ptr(Rd), stream())
         return K, Rw, Rd
 
+    def affine_coef(self, coords):
+        """coords (ne,4,2) -> (coef (ne,18) on device, number of non-affine elements): the closed-form coefficients
+        of csrc/elem_affine.cuh.  Synchronises (one scalar)."""
+        coords = coords.contiguous()
+        ne = coords.numel() // 8
+        coef = empty(ne * 18).view(ne, 18)
+        bad = C.c_int64()
+        call("pyn_elem_affine_coef", self._h, ptr(coords), ne, ptr(coef), C.byref(bad), stream())
+        return coef, bad.value
+
+    def kle_affine(self, coef, want_rd=True):
+        """Materialised K, Rw, Rd of affine elements from their coefficients (same layout as kle())."""
+        ne, nn = coef.shape[0], self.nn
+        K = empty(ne * 4 * nn * nn).view(ne, 2 * nn, 2 * nn)
+        Rw = empty(ne * 2 * nn * nn).view(ne, 2 * nn, nn)
+        Rd = empty(ne * 2 * nn * nn).view(ne, 2 * nn, nn) if want_rd else None
+        call("pyn_elem_kle_affine", self._h, ptr(coef), ne, ptr(K), ptr(Rw), ptr(Rd), stream())
+        return K, Rw, Rd
+
     def ops(self, coords):
         coords = coords.contiguous()
         ne, nn = coords.numel() // 8, self.nn
@@ -208,6 +227,16 @@ def pair_mask(pairs):
 
 
 ALL_PAIRS = pair_mask([(r, c) for r in range(4) for c in range(4)])
+
+
+class AffineSource:
+    """Element matrices that are never materialised: `assemble(..., E=AffineSource(kernels, coef, which))` evaluates
+    the entries of K_e ("K"), Rw_e ("Rw") or Rd_e ("Rd") of affine elements from their coefficients while it writes the
+    CSR rows (fused integrate-and-assemble, csrc/assemble.cu asm_interior_affine_kernel)."""
+    WHICH = {"K": 0, "Rw": 1, "Rd": 2}
+
+    def __init__(self, kernels, coef, which):
+        self.kernels, self.coef, self.which = kernels, coef.contiguous(), self.WHICH[which]
 
 
 class SpmvPlan:
@@ -403,7 +432,12 @@ def assemble(topo, rdof, cdof, E, rclass=None, cclass=None, pairs=ALL_PAIRS, dia
     for i in range(4):
         d.diag_add[i] = float(diag_add[i])
     d.sign = float(sign)
-    if E is not None:
+    if isinstance(E, AffineSource):
+        assert E.coef.shape[0] == topo.ne and E.kernels.nn == topo.nn and rowscale is None
+        assert (rdof, cdof) == ((2, 2) if E.which == 0 else (2, 1))
+        d.d_coef, d.elem, d.which = E.coef.data_ptr(), E.kernels._h, E.which
+        d.E_stride = 1
+    elif E is not None:
         E = E.contiguous()
         assert E.shape[-2] == rdof * topo.nn and E.shape[-1] == cdof * topo.nn
         d.d_E = E.data_ptr()

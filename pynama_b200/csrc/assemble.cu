@@ -11,6 +11,7 @@
 #include "common.cuh"
 #include "topo.cuh"
 #include "tmat.cuh"
+#include "elem.cuh"
 
 namespace {
 
@@ -25,13 +26,29 @@ struct DescView {
   int64_t E_stride;
   const double* rowscale;
   const uint8_t* flags;  // bcmap: 1 = boundary-affected node (NULL: no map)
+  // fused integrate-and-assemble on affine elements (elem_affine.cuh): entries are evaluated from the per-element
+  // coefficients instead of being read from materialised element matrices (coef == NULL: E is used)
+  const double* coef;    // [ne][PYN_AFF_NCOEF]
+  pyn::AffTables aff;
+  int which;             // 0 K (2x2 blocks), 1 Rw, 2 Rd (2x1 blocks)
 };
+
+// element block (rows of local node lr, columns of local node l) of element e from the affine closed form
+template <int RD, int CD>
+__device__ __forceinline__ void affine_entry(const DescView& d, const pyn::AffTables& T, const double* __restrict__ cf,
+                                             int lr, int l, double (&v)[RD][CD]) {
+  if constexpr (RD == 2 && CD == 2) {
+    pyn::affine_block_K(T, cf, lr, l, v);
+  } else if constexpr (RD == 2 && CD == 1) {
+    pyn::affine_block_R(T, cf, d.which, lr, l, v);
+  }
+}
 
 // One warp per mesh node (= RD consecutive matrix rows); lanes stride over the node's sorted adjacency row.  Every
 // lane owns whole output blocks: for adjacency position p it gathers, in ascending cell order, the RD x CD block of
 // each incident element that contains column node p (inverse position map of the topology handle), so there are no
 // shared-memory accumulators, no atomics and no intra-warp ordering hazards.  COUNT only counts kept entries.
-template <int RD, int CD, bool COUNT>
+template <int RD, int CD, bool COUNT, bool AFF = false>
 __global__ void __launch_bounds__(256)
 asm_gather_kernel(pyn::TopoView t, DescView d, const int* __restrict__ list, int64_t nlist, int* __restrict__ rowcnt,
                   const int64_t* __restrict__ indptr, int* __restrict__ indices, double* __restrict__ data) {
@@ -79,11 +96,20 @@ asm_gather_kernel(pyn::TopoView t, DescView d, const int* __restrict__ list, int
           const int e = __shfl_sync(0xffffffffu, my_e, k), lr = __shfl_sync(0xffffffffu, my_lr, k);
           const int l = valid ? (int)t.inv[iv0 + (int64_t)k * L + p] : 0xFF;
           if (l != 0xFF) {
+            if constexpr (AFF) {
+              double blk[RD][CD];
+              affine_entry<RD, CD>(d, d.aff, d.coef + (int64_t)e * PYN_AFF_NCOEF, lr, l, blk);
+#pragma unroll
+              for (int a = 0; a < RD; ++a)
+#pragma unroll
+                for (int b = 0; b < CD; ++b) v[a][b] += d.sign * blk[a][b];
+            } else {
             const double* Ee = d.E + (d.E_stride ? (int64_t)e * d.E_stride : 0) + (int64_t)lr * RD * ldE + l * CD;
 #pragma unroll
             for (int a = 0; a < RD; ++a)
 #pragma unroll
               for (int b = 0; b < CD; ++b) v[a][b] += d.sign * Ee[a * ldE + b];
+            }
           }
         }
       }
@@ -240,6 +266,138 @@ asm_interior_kernel(pyn::TopoView t, DescView d, const int64_t* __restrict__ ind
       }
     }
     __syncthreads();
+  }
+}
+
+// ---- fused integrate-and-assemble, interior nodes, affine elements --------------------------------------------------
+// Same batching and the same order of additions as asm_interior_kernel (ascending cell order per entry), but the
+// element entries are EVALUATED from the element's 17 coefficients and the six 1-D matrices held in shared memory
+// (elem_affine.cuh) instead of being read from a materialised element matrix: the only HBM traffic left is the CSR rows
+// written once, the row pointers, 1 B per (adjacency slot, incident element) of the inverse position map and 144 B of
+// coefficients per element.  A lane keeps up to AFF_Q adjacency positions of its node in registers and walks the
+// node's elements in the outer loop, so the coefficients are loaded once per (node, element).
+constexpr int AFF_Q = 4;   // adjacency positions per lane and pass (128 per warp)
+
+template <int CD>
+__global__ void __launch_bounds__(256)
+asm_interior_affine_kernel(pyn::TopoView t, DescView d, const int64_t* __restrict__ indptr, int* __restrict__ indices,
+                           double* __restrict__ data) {
+  constexpr int RD = 2;
+  __shared__ int64_t s_adj[ASM_NB + 1], s_inv[ASM_NB + 1], s_base[ASM_NB * RD];
+  __shared__ int s_el[ASM_NB * ASM_MAXDEG], s_lr[ASM_NB * ASM_MAXDEG];
+  __shared__ __align__(16) uint8_t s_ivb[ASM_IVCAP + 32];
+  __shared__ int s_n2e[ASM_NB + 1];
+  __shared__ uint8_t s_flag[ASM_NB];
+  __shared__ double s_tab[6 * PYN_MAX_NGL * PYN_MAX_NGL];
+  __shared__ int s_perm[PYN_MAX_NGL * PYN_MAX_NGL];
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  const int n2 = d.aff.n * d.aff.n;
+  for (int i = tid; i < 6 * n2; i += 256) s_tab[i] = d.aff.SF[i];   // SF MF CF SG MG CG are contiguous
+  for (int i = tid; i < n2; i += 256) s_perm[i] = d.aff.perm[i];
+  pyn::AffTables T = d.aff;
+  T.SF = s_tab; T.MF = s_tab + n2; T.CF = s_tab + 2 * n2; T.SG = s_tab + 3 * n2; T.MG = s_tab + 4 * n2;
+  T.CG = s_tab + 5 * n2; T.perm = s_perm;
+  const int64_t nbatch = (t.nnodes + ASM_NB - 1) / ASM_NB;
+  for (int64_t batch = blockIdx.x; batch < nbatch; batch += gridDim.x) {
+    const int64_t r0 = batch * ASM_NB;
+    const int nb = (int)min((int64_t)ASM_NB, t.nnodes - r0);
+    const int64_t e0 = t.n2e_ptr[r0];
+    __syncthreads();
+    if (tid <= nb) {
+      s_adj[tid] = t.adj_ptr[r0 + tid];
+      s_n2e[tid] = (int)(t.n2e_ptr[r0 + tid] - e0);
+      s_inv[tid] = t.inv_ptr[r0 + tid];
+    }
+    if (tid < nb) s_flag[tid] = d.flags[r0 + tid];
+    if (tid >= 64 && tid < 64 + nb * RD) s_base[tid - 64] = indptr[r0 * RD + (tid - 64)];
+    __syncthreads();
+    const uint8_t* ivsrc = t.inv + s_inv[0];
+    const int mis = (int)(reinterpret_cast<uintptr_t>(ivsrc) & 15);
+    const int64_t ivlen = s_inv[nb] - s_inv[0];
+    const bool staged = ivlen + mis <= ASM_IVCAP;
+    if (staged && data) {
+      const uint4* src = reinterpret_cast<const uint4*>(ivsrc - mis);
+      const int n16 = (int)((ivlen + mis + 15) >> 4);
+      for (int i = tid; i < n16; i += 256) reinterpret_cast<uint4*>(s_ivb)[i] = src[i];
+    }
+    {  // (element, local row) of every (node, incident element): 8 threads per node
+      const int j = tid >> 3, k = tid & 7;
+      if (j < nb && !s_flag[j] && k < s_n2e[j + 1] - s_n2e[j]) {
+        const int64_t q = e0 + s_n2e[j] + k;
+        s_el[j * ASM_MAXDEG + k] = t.n2e_elem[q];
+        s_lr[j * ASM_MAXDEG + k] = t.n2e_loc[q];
+      }
+    }
+    __syncthreads();
+    for (int j = w; j < nb; j += 8) {  // one warp per node
+      if (s_flag[j]) continue;
+      const int L = (int)(s_adj[j + 1] - s_adj[j]), deg = s_n2e[j + 1] - s_n2e[j];
+      const uint8_t* ivj = staged ? s_ivb + mis + (int)(s_inv[j] - s_inv[0]) : t.inv + s_inv[j];
+      if (data) {
+        for (int pc = 0; pc < L; pc += 32 * AFF_Q) {
+          double v[AFF_Q][RD][CD];
+#pragma unroll
+          for (int q = 0; q < AFF_Q; ++q)
+#pragma unroll
+            for (int a = 0; a < RD; ++a)
+#pragma unroll
+              for (int b = 0; b < CD; ++b) v[q][a][b] = 0.0;
+          for (int k = 0; k < deg; ++k) {  // ascending cell order
+            const int lr = s_lr[j * ASM_MAXDEG + k];
+            const double* cg = d.coef + (int64_t)s_el[j * ASM_MAXDEG + k] * PYN_AFF_NCOEF;
+            double cf[PYN_AFF_NCOEF];
+            if (CD == 2) {
+#pragma unroll
+              for (int i = 0; i < 13; ++i) cf[i] = __ldg(cg + i);
+            } else {
+#pragma unroll
+              for (int i = 13; i < 17; ++i) cf[i] = __ldg(cg + i);
+            }
+#pragma unroll
+            for (int q = 0; q < AFF_Q; ++q) {
+              const int p = pc + q * 32 + lane;
+              if (p < L) {
+                const int l = ivj[k * L + p];
+                if (l != 0xFF) {
+                  double blk[RD][CD];
+                  affine_entry<RD, CD>(d, T, cf, lr, l, blk);
+#pragma unroll
+                  for (int a = 0; a < RD; ++a)
+#pragma unroll
+                    for (int b = 0; b < CD; ++b) v[q][a][b] += d.sign * blk[a][b];
+                }
+              }
+            }
+          }
+#pragma unroll
+          for (int q = 0; q < AFF_Q; ++q) {
+            const int p = pc + q * 32 + lane;
+            if (p < L) {
+#pragma unroll
+              for (int a = 0; a < RD; ++a) {
+                const int64_t base = s_base[j * RD + a];
+                double* o = data + base + p * CD;
+                if (CD == 2 && ((base & 1) == 0)) {
+                  *reinterpret_cast<double2*>(o) = make_double2(v[q][a][0], v[q][a][CD - 1]);
+                } else {
+#pragma unroll
+                  for (int b = 0; b < CD; ++b) o[b] = v[q][a][b];
+                }
+              }
+            }
+          }
+        }
+      }
+      if (indices) {
+        for (int p = lane; p < L; p += 32) {
+          const int c = t.adj_cols[s_adj[j] + p];
+#pragma unroll
+          for (int a = 0; a < RD; ++a)
+#pragma unroll
+            for (int b = 0; b < CD; ++b) indices[s_base[j * RD + a] + p * CD + b] = c * CD + b;
+        }
+      }
+    }
   }
 }
 
@@ -581,6 +739,16 @@ int make_desc(const pyn_asm_desc* desc, DescView* v) {
   for (int i = 0; i < 4; ++i) v->diag_add[i] = desc->diag_add[i];
   v->sign = desc->sign; v->E = desc->d_E; v->E_stride = desc->E_stride; v->rowscale = desc->d_rowscale;
   v->flags = desc->bcmap ? desc->bcmap->flags : nullptr;
+  v->coef = nullptr; v->which = 0;
+  memset(&v->aff, 0, sizeof(v->aff));
+  if (desc->d_coef) {   // fused integrate-and-assemble on affine elements
+    PYN_REQUIRE(desc->elem != nullptr, "affine assembly: element handle missing");
+    PYN_REQUIRE(desc->rdof == 2 && ((desc->which == 0 && desc->cdof == 2) || ((desc->which == 1 || desc->which == 2) && desc->cdof == 1)),
+                "affine assembly: K (2x2) or Rw / Rd (2x1) blocks only");
+    PYN_REQUIRE(desc->d_rowscale == nullptr, "affine assembly: no row scaling");
+    v->coef = desc->d_coef; v->which = desc->which; v->aff = pyn::aff_tables(desc->elem);
+    v->E = nullptr; v->E_stride = 1;   // per-cell by nature: the row-template shortcut does not apply
+  }
   return PYN_OK;
 }
 
@@ -597,6 +765,13 @@ static int launch_asm(const pyn_topo* t, const DescView& dv, const int* list, in
   const int64_t nwork = list ? nlist : t->nnodes;
   if (nwork == 0) return PYN_OK;
   const int grid = pyn::grid_for(nwork * 32, 256, 16);
+  if (dv.coef && !COUNT) {
+    PYN_REQUIRE(tv.nn == dv.aff.n * dv.aff.n, "affine assembly: element handle of another order");
+    if (dv.cdof == 2) asm_gather_kernel<2, 2, COUNT, true><<<grid, 256, 0, st>>>(tv, dv, list, nlist, cnt, indptr, indices, data);
+    else asm_gather_kernel<2, 1, COUNT, true><<<grid, 256, 0, st>>>(tv, dv, list, nlist, cnt, indptr, indices, data);
+    PYN_CHECK_LAUNCH();
+    return PYN_OK;
+  }
 #define PYN_ASM_CASE(R, C)                                                                                     \
   if (dv.rdof == R && dv.cdof == C) {                                                                          \
     asm_gather_kernel<R, C, COUNT><<<grid, 256, 0, st>>>(tv, dv, list, nlist, cnt, indptr, indices, data);     \
@@ -614,6 +789,13 @@ static int launch_interior(const pyn_topo* t, const DescView& dv, const int64_t*
                            cudaStream_t st) {
   const pyn::TopoView tv = pyn::view_of(t);
   const int grid = pyn::grid_for((t->nnodes + ASM_NB - 1) / ASM_NB * 256, 256, 8);
+  if (dv.coef) {
+    PYN_REQUIRE(tv.nn == dv.aff.n * dv.aff.n, "affine assembly: element handle of another order");
+    if (dv.cdof == 2) asm_interior_affine_kernel<2><<<grid, 256, 0, st>>>(tv, dv, indptr, indices, data);
+    else asm_interior_affine_kernel<1><<<grid, 256, 0, st>>>(tv, dv, indptr, indices, data);
+    PYN_CHECK_LAUNCH();
+    return PYN_OK;
+  }
   const bool vec = ((reinterpret_cast<uintptr_t>(dv.E) & 15) == 0) && ((dv.E_stride & 1) == 0);
 #define PYN_ASM_CASE(R, C)                                                                        \
   if (dv.rdof == R && dv.cdof == C) {                                                             \
@@ -798,7 +980,7 @@ int pyn_asm_fill(const pyn_topo* t, const pyn_asm_desc* desc, const int64_t* d_i
   DescView dv;
   int rc = make_desc(desc, &dv);
   if (rc) return rc;
-  PYN_REQUIRE(d_data == nullptr || dv.E != nullptr, "element matrices missing");
+  PYN_REQUIRE(d_data == nullptr || dv.E != nullptr || dv.coef != nullptr, "element matrices missing");
   cudaStream_t st = pyn::as_stream(stream);
   if (use_map(desc)) {
     PYN_REQUIRE(desc->bcmap->nnodes == t->nnodes, "bcmap belongs to another topology");

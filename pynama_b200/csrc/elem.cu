@@ -9,14 +9,7 @@
 //
 // One CTA per element (grid-stride).  All FP64.
 #include "common.cuh"
-
-struct pyn_elem {
-  int n, nqF, nqG;
-  double alpha_w, alpha_d;
-  double* d_tab;  // hF dF wF xiF hG dG wG xiG D wO xiO (device)
-  int* d_perm;    // nn
-  int off_hF, off_dF, off_wF, off_xF, off_hG, off_dG, off_wG, off_xG, off_D, off_wO, off_xO, tab_len;
-};
+#include "elem.cuh"
 
 namespace {
 
@@ -298,6 +291,64 @@ elem_ops_kernel(pyn_elem E, const double* __restrict__ coords, int64_t ne, doubl
   }
 }
 
+// ---- affine elements: closed form (elem_affine.cuh) ---------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+elem_affine_coef_kernel(int64_t ne, const double* __restrict__ coords, double aw, double ad, double* __restrict__ coef,
+                        unsigned long long* __restrict__ nonaffine) {
+  const int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (e >= ne) return;
+  double c[8], out[PYN_AFF_NCOEF];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) c[k] = coords[e * 8 + k];
+  const bool ok = pyn::affine_coefficients(c, aw, ad, out);
+#pragma unroll
+  for (int k = 0; k < PYN_AFF_NCOEF; ++k) coef[e * PYN_AFF_NCOEF + k] = out[k];
+  if (!ok) atomicAdd(nonaffine, 1ull);
+}
+
+// materialised K_e / Rw_e / Rd_e from the coefficients: one thread per (element, local node pair)
+__global__ void __launch_bounds__(256)
+elem_kle_affine_kernel(pyn::AffTables T, const double* __restrict__ coef, int64_t ne, double* __restrict__ Kout,
+                       double* __restrict__ Rwout, double* __restrict__ Rdout) {
+  extern __shared__ double sm[];
+  const int n = T.n, nn = n * n, n2 = n * n;
+  double* tab = sm;
+  int* perm = (int*)(tab + 6 * n2);
+  for (int i = threadIdx.x; i < 6 * n2; i += blockDim.x) tab[i] = T.SF[i];   // the six matrices are contiguous
+  for (int i = threadIdx.x; i < nn; i += blockDim.x) perm[i] = T.perm[i];
+  __syncthreads();
+  pyn::AffTables S = T;
+  S.SF = tab; S.MF = tab + n2; S.CF = tab + 2 * n2; S.SG = tab + 3 * n2; S.MG = tab + 4 * n2; S.CG = tab + 5 * n2;
+  S.perm = perm;
+  const int64_t tot = ne * (int64_t)nn * nn;
+  for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < tot; idx += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t e = idx / (nn * nn);
+    const int ij = (int)(idx - e * (int64_t)nn * nn), i = ij / nn, j = ij - i * nn;
+    const double* cf = coef + e * PYN_AFF_NCOEF;
+    if (Kout) {
+      double v[2][2];
+      pyn::affine_block_K(S, cf, i, j, v);
+      double* row0 = Kout + e * (int64_t)(4 * nn) * nn + (int64_t)(2 * i) * (2 * nn) + 2 * j;
+      *reinterpret_cast<double2*>(row0) = make_double2(v[0][0], v[0][1]);
+      *reinterpret_cast<double2*>(row0 + 2 * nn) = make_double2(v[1][0], v[1][1]);
+    }
+    if (Rwout) {
+      double v[2][1];
+      pyn::affine_block_R(S, cf, 1, i, j, v);
+      double* o = Rwout + e * (int64_t)(2 * nn) * nn + (int64_t)(2 * i) * nn + j;
+      o[0] = v[0][0];
+      o[nn] = v[1][0];
+    }
+    if (Rdout) {
+      double v[2][1];
+      pyn::affine_block_R(S, cf, 2, i, j, v);
+      double* o = Rdout + e * (int64_t)(2 * nn) * nn + (int64_t)(2 * i) * nn + j;
+      o[0] = v[0][0];
+      o[nn] = v[1][0];
+    }
+  }
+}
+
 }  // namespace
 
 extern "C" {
@@ -313,6 +364,7 @@ int pyn_elem_create(int ngl, int nqF, const double* hF, const double* dF, const 
   }
   PYN_REQUIRE(nqF >= 1 && nqF <= PYN_MAX_NGL && nqG >= 1 && nqG <= PYN_MAX_NGL, "bad quadrature size");
   pyn_elem* e = new pyn_elem();
+  memset(e, 0, sizeof(*e));
   e->n = ngl;
   e->nqF = nqF;
   e->nqG = nqG;
@@ -337,6 +389,32 @@ int pyn_elem_create(int ngl, int nqF, const double* hF, const double* dF, const 
   delete[] host;
   if (err == cudaSuccess) err = cudaMalloc(&e->d_perm, sizeof(int) * n * n);
   if (err == cudaSuccess) err = cudaMemcpy(e->d_perm, perm, sizeof(int) * n * n, cudaMemcpyHostToDevice);
+  {  // the six 1-D matrices of the affine closed form (elem_affine.cuh): S, M symmetric by construction
+    const int n2 = n * n;
+    double* a = new double[6 * n2];
+    auto fill = [&](double* S, double* M, double* C, int nq, const double* h, const double* d, const double* w) {
+      for (int i = 0; i < n; ++i)
+        for (int j = 0; j < n; ++j) {
+          double cs = 0.0;
+          for (int q = 0; q < nq; ++q) cs += w[q] * h[q * n + i] * d[q * n + j];
+          C[i * n + j] = cs;
+          if (j < i) continue;
+          double ss = 0.0, ms = 0.0;
+          for (int q = 0; q < nq; ++q) {
+            ss += w[q] * d[q * n + i] * d[q * n + j];
+            ms += w[q] * h[q * n + i] * h[q * n + j];
+          }
+          S[i * n + j] = S[j * n + i] = ss;
+          M[i * n + j] = M[j * n + i] = ms;
+        }
+    };
+    fill(a, a + n2, a + 2 * n2, nqF, hF, dF, wF);
+    fill(a + 3 * n2, a + 4 * n2, a + 5 * n2, nqG, hG, dG, wG);
+    if (err == cudaSuccess) err = cudaMalloc(&e->d_aff, sizeof(double) * 6 * n2);
+    if (err == cudaSuccess) err = cudaMemcpy(e->d_aff, a, sizeof(double) * 6 * n2, cudaMemcpyHostToDevice);
+    delete[] a;
+  }
+  if (err == cudaSuccess) err = cudaMalloc(&e->d_count, sizeof(unsigned long long));
   if (err != cudaSuccess) {
     pyn::set_error("pyn_elem_create: %s", cudaGetErrorString(err));
     delete e;
@@ -350,6 +428,8 @@ int pyn_elem_destroy(pyn_elem* e) {
   if (!e) return PYN_OK;
   cudaFree(e->d_tab);
   cudaFree(e->d_perm);
+  cudaFree(e->d_aff);
+  cudaFree(e->d_count);
   delete e;
   return PYN_OK;
 }
@@ -388,6 +468,38 @@ int pyn_elem_ops(const pyn_elem* e, const double* d_coords, int64_t ne, double* 
   int grid = pyn::sm_count() * 8;
   if (grid > ne) grid = (int)ne;
   elem_ops_kernel<<<grid, 256, smem, pyn::as_stream(stream)>>>(*e, d_coords, ne, d_SrT, d_Div, d_Curl, d_W);
+  PYN_CHECK_LAUNCH();
+  return PYN_OK;
+}
+
+int pyn_elem_affine_coef(const pyn_elem* e, const double* d_coords, int64_t ne, double* d_coef, int64_t* h_nonaffine,
+                         void* stream) {
+  PYN_REQUIRE(e && d_coords && d_coef && ne >= 0, "bad arguments");
+  cudaStream_t st = pyn::as_stream(stream);
+  if (h_nonaffine) *h_nonaffine = 0;
+  if (ne == 0) return PYN_OK;
+  PYN_CHECK_CUDA(cudaMemsetAsync(e->d_count, 0, sizeof(unsigned long long), st));
+  elem_affine_coef_kernel<<<(unsigned)((ne + 255) / 256), 256, 0, st>>>(ne, d_coords, e->alpha_w, e->alpha_d, d_coef,
+                                                                          e->d_count);
+  PYN_CHECK_LAUNCH();
+  if (h_nonaffine) {   // the caller decides the path from this count: one scalar read-back
+    unsigned long long c = 0;
+    PYN_CHECK_CUDA(cudaMemcpyAsync(&c, e->d_count, sizeof(c), cudaMemcpyDeviceToHost, st));
+    PYN_CHECK_CUDA(cudaStreamSynchronize(st));
+    *h_nonaffine = (int64_t)c;
+  }
+  return PYN_OK;
+}
+
+int pyn_elem_kle_affine(const pyn_elem* e, const double* d_coef, int64_t ne, double* d_K, double* d_Rw, double* d_Rd,
+                        void* stream) {
+  PYN_REQUIRE(e && d_coef && ne >= 0, "bad arguments");
+  if (ne == 0) return PYN_OK;
+  const int nn = e->n * e->n;
+  const size_t smem = sizeof(double) * 6 * nn + sizeof(int) * nn;
+  const int64_t tot = ne * (int64_t)nn * nn;
+  elem_kle_affine_kernel<<<pyn::grid_for(tot, 256, 16), 256, smem, pyn::as_stream(stream)>>>(pyn::aff_tables(e), d_coef, ne,
+                                                                                            d_K, d_Rw, d_Rd);
   PYN_CHECK_LAUNCH();
   return PYN_OK;
 }

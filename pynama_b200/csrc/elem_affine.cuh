@@ -1,0 +1,119 @@
+// Closed-form element matrices on AFFINE quadrilaterals (parallelograms: every box / stretched / sheared mesh of the
+// reference), shared by the integration kernels (elem.cu) and the fused integrate-and-assemble kernels (assemble.cu).
+//
+// On an affine element the Jacobian of the bilinear 4-corner map is constant, so the per-point geometric factors of
+// Spectral.getElemKLEMatrices (src/elements/spectral.py:89-157) leave the quadrature sums and every block of K, Rw, Rd
+// becomes a short combination of Kronecker products of six 1-D matrices (SURVEY 8a', here for a general parallelogram):
+//     M^R[a,c] = sum_q w_q h_a(q) h_c(q)    S^R[a,c] = sum_q w_q h_a'(q) h_c'(q)    C^R[a,c] = sum_q w_q h_a(q) h_c'(q)
+// for the rule R in {F = full, G = reduced}, with 17 per-element coefficients (13 for K, 4 for Rw / Rd).  It is the SAME
+// quadrature as the general kernel, summed in a different order (<= 1e-14 relative apart); what makes it worth having is
+// that an entry costs ~6 multiply-adds instead of a contraction over the quadrature points, so the element matrix
+// never has to exist in memory: the assembly kernels evaluate the entries they need while they write the CSR rows.
+//
+// Every operation is an explicit round-to-nearest intrinsic: the materialising kernel (elem_kle_affine_kernel) and the
+// fused assembly kernels therefore produce bit-identical entries whatever the compiler does around the inlined code.
+#pragma once
+#include "common.cuh"
+
+constexpr int PYN_AFF_NCOEF = 18;   // per element: 13 (K) + 4 (Rw, Rd) + 1 pad (16-byte rows)
+
+namespace pyn {
+
+struct AffTables {   // device pointers (or shared-memory copies) of the six n x n matrices + the local -> tensor map
+  const double *SF, *MF, *CF, *SG, *MG, *CG;
+  const int* perm;   // [nn]: element-local node -> a*n+b
+  int n;
+  double alpha_w, alpha_d;
+};
+
+// coefficients of one element from its corner coordinates (closure order); returns false when the element is not
+// affine (relative bilinear term above 1e-13: such elements take the general sum-factorised kernel)
+__device__ __forceinline__ bool affine_coefficients(const double* __restrict__ c, double aw, double ad,
+                                                    double* __restrict__ out) {
+  // local corner k sits at (r,s) = (+1,+1), (-1,+1), (-1,-1), (+1,-1)   (spectral.py:226)
+  const double xr = 0.25 * (c[0] - c[2] - c[4] + c[6]), xs = 0.25 * (c[0] + c[2] - c[4] - c[6]);
+  const double yr = 0.25 * (c[1] - c[3] - c[5] + c[7]), ys = 0.25 * (c[1] + c[3] - c[5] - c[7]);
+  const double bx = 0.25 * (c[0] - c[2] + c[4] - c[6]), by = 0.25 * (c[1] - c[3] + c[5] - c[7]);
+  const double size = fabs(xr) + fabs(xs) + fabs(yr) + fabs(ys);
+  const double det = xr * ys - yr * xs;
+  const double inv = 1.0 / det;
+  const double mxr = ys * inv, mxs = -yr * inv, myr = -xs * inv, mys = xr * inv;
+  out[0] = det * (mxr * mxr + myr * myr);            // grad.grad  rr | rs | ss
+  out[1] = det * (mxr * mxs + myr * mys);
+  out[2] = det * (mxs * mxs + mys * mys);
+  out[3] = det * (ad * mxr * mxr + aw * myr * myr);  // uu: ad x x^T + aw y y^T
+  out[4] = det * (ad * mxr * mxs + aw * myr * mys);
+  out[5] = det * (ad * mxs * mxs + aw * mys * mys);
+  out[6] = det * (ad * myr * myr + aw * mxr * mxr);  // vv: ad y y^T + aw x x^T
+  out[7] = det * (ad * myr * mys + aw * mxr * mxs);
+  out[8] = det * (ad * mys * mys + aw * mxs * mxs);
+  out[9] = det * (ad * mxr * myr - aw * myr * mxr);  // uv: ad x y^T - aw y x^T   rr | rs | sr | ss
+  out[10] = det * (ad * mxr * mys - aw * myr * mxs);
+  out[11] = det * (ad * mxs * myr - aw * mys * mxr);
+  out[12] = det * (ad * mxs * mys - aw * mys * mxs);
+  out[13] = det * mxr;                               // first-order blocks (Rw, Rd)
+  out[14] = det * mxs;
+  out[15] = det * myr;
+  out[16] = det * mys;
+  out[17] = 0.0;
+  return (fabs(bx) + fabs(by)) <= 1e-13 * size;
+}
+
+__device__ __forceinline__ double aff_mul(double a, double b) { return __dmul_rn(a, b); }
+__device__ __forceinline__ double aff_fma(double a, double b, double c) { return __fma_rn(a, b, c); }
+
+// 2 x 2 block of K_e between local nodes i (rows) and j (columns): [[uu, uv], [vu, vv]]
+__device__ __forceinline__ void affine_block_K(const AffTables& T, const double* __restrict__ cf, int i, int j,
+                                               double (&v)[2][2]) {
+  const int n = T.n, pi = T.perm[i], pj = T.perm[j];
+  const int a = pi / n, b = pi - a * n, c = pj / n, d = pj - c * n;
+  const int ac = a * n + c, ca = c * n + a, bd = b * n + d, db = d * n + b;
+  // full rule: the vector Laplacian part, identical on uu and vv; the mixed pair is summed un-fused (bitwise symmetric)
+  const double cfca = T.CF[ca], cfbd = T.CF[bd], cfac = T.CF[ac], cfdb = T.CF[db];
+  double gr = aff_mul(cf[0], aff_mul(T.SF[ac], T.MF[bd]));
+  gr = aff_fma(cf[1], __dadd_rn(aff_mul(cfca, cfbd), aff_mul(cfac, cfdb)), gr);
+  gr = aff_fma(cf[2], aff_mul(T.MF[ac], T.SF[bd]), gr);
+  // reduced rule: penalty terms
+  const double sm = aff_mul(T.SG[ac], T.MG[bd]), ms = aff_mul(T.MG[ac], T.SG[bd]);
+  const double c1 = aff_mul(T.CG[ca], T.CG[bd]), c2 = aff_mul(T.CG[ac], T.CG[db]);
+  const double cs = __dadd_rn(c1, c2);
+  double kuu = aff_mul(cf[3], sm);
+  kuu = aff_fma(cf[4], cs, kuu);
+  kuu = aff_fma(cf[5], ms, kuu);
+  double kvv = aff_mul(cf[6], sm);
+  kvv = aff_fma(cf[7], cs, kvv);
+  kvv = aff_fma(cf[8], ms, kvv);
+  // uv and vu = uv^T: the same four products with the two mixed coefficients exchanged; the mixed pair is again
+  // summed un-fused so that K_e[i][j] (uv) and K_e[j][i] (vu seen from the other node) carry the same bits
+  double kuv = aff_mul(cf[9], sm);
+  kuv = __dadd_rn(kuv, __dadd_rn(aff_mul(cf[10], c1), aff_mul(cf[11], c2)));
+  kuv = aff_fma(cf[12], ms, kuv);
+  double kvu = aff_mul(cf[9], sm);
+  kvu = __dadd_rn(kvu, __dadd_rn(aff_mul(cf[11], c1), aff_mul(cf[10], c2)));
+  kvu = aff_fma(cf[12], ms, kvu);
+  v[0][0] = __dadd_rn(gr, kuu);
+  v[0][1] = kuv;
+  v[1][0] = kvu;
+  v[1][1] = __dadd_rn(gr, kvv);
+}
+
+// 2 x 1 block of Rw_e (which == 1) or Rd_e (which == 2) between local nodes i (velocity rows) and j (scalar column)
+__device__ __forceinline__ void affine_block_R(const AffTables& T, const double* __restrict__ cf, int which, int i,
+                                               int j, double (&v)[2][1]) {
+  const int n = T.n, pi = T.perm[i], pj = T.perm[j];
+  const int a = pi / n, b = pi - a * n, c = pj / n, d = pj - c * n;
+  const int ac = a * n + c, ca = c * n + a, bd = b * n + d, db = d * n + b;
+  const double f1 = aff_mul(T.CF[ac], T.MF[bd]), f2 = aff_mul(T.MF[ac], T.CF[bd]);   // test phi, trial gradient
+  const double g1 = aff_mul(T.CG[ca], T.MG[bd]), g2 = aff_mul(T.MG[ac], T.CG[db]);   // test gradient, trial phi
+  const double Ax = aff_fma(cf[14], f2, aff_mul(cf[13], f1)), Ay = aff_fma(cf[16], f2, aff_mul(cf[15], f1));
+  const double Cx = aff_fma(cf[14], g2, aff_mul(cf[13], g1)), Cy = aff_fma(cf[16], g2, aff_mul(cf[15], g1));
+  if (which == 1) {        // Rw = int dv . curl(w) + alpha_w int curl(dv) w      (spectral.py:140-147)
+    v[0][0] = aff_fma(-T.alpha_w, Cy, Ay);
+    v[1][0] = aff_fma(T.alpha_w, Cx, -Ax);
+  } else {                 // Rd = - int dv . grad(D) + alpha_d int div(dv) D
+    v[0][0] = aff_fma(T.alpha_d, Cx, -Ax);
+    v[1][0] = aff_fma(T.alpha_d, Cy, -Ay);
+  }
+}
+
+}  // namespace pyn

@@ -107,6 +107,10 @@ class Spectral(Element):
         """Batched: coords device tensor (ne,4,2) -> device tensors K (ne,2nn,2nn), Rw, Rd (ne,2nn,nn)."""
         return self.kernels().kle(coords, want_rd)
 
+    def getAffineCoefficientsDevice(self, coords):
+        """(coef (ne,18) device tensor, number of non-affine elements) -- csrc/elem_affine.cuh."""
+        return self.kernels().affine_coef(coords)
+
     def getElemKLEOperatorsDevice(self, coords):
         return self.kernels().ops(coords)
 

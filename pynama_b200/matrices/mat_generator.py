@@ -45,6 +45,13 @@ def templatesWanted():
     return str(Options().getString("mat_templates", "1")).lower() not in ("0", "false", "no", "off")
 
 
+def fusedWanted():
+    """`-mat_fused 0` materialises the element matrices of a per-cell assembly; default: fused integrate-and-assemble
+    whenever every element is affine."""
+    from ..common.options import Options
+    return str(Options().getString("mat_fused", "1")).lower() not in ("0", "false", "no", "off")
+
+
 def _rank(comm):
     return getattr(comm, "rank", 0)
 
@@ -126,27 +133,59 @@ class Mat(object):
         if templatesWanted():
             csr.enable_templates()
 
-    def assembleFromMesh(self, dom, elemType, perCell=True):
+    def assembleFromMesh(self, dom, elemType, perCell=True, corners=None, elementMatrices=None, after=None):
         """FreeSlip.buildKLEMats (src/cases/base_problem.py:499-552) for the whole mesh on the device: element
         matrices of every cell (perCell, :505-506) or of cell 0 only, then K (free x free, explicit zero + 1 on the
         diagonal of constrained dofs), Krhs (-K_e[free, set], + 1 on constrained diagonals), Rw (free rows).
-        Rd stays empty, as in the reference."""
+        Rd stays empty, as in the reference.  A second call on the same mesh rewrites the values on the existing
+        pattern.  `corners`: device (ne,4,2) corner coordinates (default: the box mesh's); `elementMatrices`: (Ke, Rwe)
+        already integrated; `after`: {"elem" | matrix name: callable} called after that stage is enqueued (timing)."""
         topo = dom.topology()
-        N = dom.getTotalNodes()
-        cls_np = np.zeros(N, dtype=np.int8)
-        cls_np[np.array(sorted(self.globalNodesDIR), dtype=np.int64)] = SET
-        cls_host = np.repeat(cls_np, self.dim)
-        cls = be.to_device(cls_host)
-        rcls = cls if dom.partition is None else be.to_device(rowClasses(dom, cls_host, self.dim))
-        corners = dom.deviceCellCorners(0, None) if perCell else dom.deviceTemplateCorners()
-        Ke, Rwe, _ = elemType.getElemKLEMatricesDevice(corners, want_rd=False)
-        m22, m21 = be.BcMap(topo, rcls, 2, cls, 2), be.BcMap(topo, rcls, 2)
+        if getattr(self, "_asmState", None) is None or self._asmState[0] is not topo:
+            N = dom.getTotalNodes()
+            cls_np = np.zeros(N, dtype=np.int8)
+            cls_np[np.array(sorted(self.globalNodesDIR), dtype=np.int64)] = SET
+            cls_host = np.repeat(cls_np, self.dim)
+            cls = be.to_device(cls_host)
+            rcls = cls if dom.partition is None else be.to_device(rowClasses(dom, cls_host, self.dim))
+            self._asmState = (topo, cls, rcls, be.BcMap(topo, rcls, 2, cls, 2), be.BcMap(topo, rcls, 2))
+            first = True
+        else:
+            first = False          # values-only re-assembly on the existing pattern (same mesh, same classes)
+        _, cls, rcls, m22, m21 = self._asmState
+        if corners is None:
+            corners = dom.deviceCellCorners(0, None) if perCell else dom.deviceTemplateCorners()
+        self.fusedAssembly = False
+        if elementMatrices is None:
+            Ke = None
+            if perCell and fusedWanted():
+                # affine elements (every box mesh): 17 coefficients per element, entries evaluated inside the assembly
+                # kernels -- the element matrices are never written to memory (csrc/elem_affine.cuh)
+                coef, nonaffine = elemType.getAffineCoefficientsDevice(corners)
+                if nonaffine == 0:
+                    kern = elemType.kernels()
+                    Ke, Rwe = be.AffineSource(kern, coef, "K"), be.AffineSource(kern, coef, "Rw")
+                    self.fusedAssembly = True
+            if Ke is None:
+                Ke, Rwe, _ = elemType.getElemKLEMatricesDevice(corners, want_rd=False)
+        else:
+            Ke, Rwe = elementMatrices
+        if after and "elem" in after:
+            after["elem"]()
         one = (0.0, 0.0, 1.0, 0.0)
-        self._install("K", be.assemble(topo, 2, 2, Ke, rcls, cls, [(FREE, FREE)], diag_classes=1 << SET, diag_add=one,
-                                       bcmap=m22))
-        self._install("Krhs", be.assemble(topo, 2, 2, Ke, rcls, cls, [(FREE, SET)], diag_classes=1 << SET,
-                                          diag_add=one, sign=-1.0, bcmap=m22))
-        self._install("Rw", be.assemble(topo, 2, 1, Rwe, rcls, None, [(FREE, FREE)], bcmap=m21))
+        for name, cd, E, ccls, pairs, dcls, dadd, sign, bmap in (
+                ("K", 2, Ke, cls, [(FREE, FREE)], 1 << SET, one, 1.0, m22),
+                ("Krhs", 2, Ke, cls, [(FREE, SET)], 1 << SET, one, -1.0, m22),
+                ("Rw", 1, Rwe, None, [(FREE, FREE)], 0, (0.0,) * 4, 1.0, m21)):
+            if first:
+                self._install(name, be.assemble(topo, 2, cd, E, rcls, ccls, pairs, diag_classes=dcls, diag_add=dadd,
+                                                sign=sign, bcmap=bmap))
+            else:
+                m = getattr(self, name)
+                m.csr = be.assemble(topo, 2, cd, E, rcls, ccls, pairs, diag_classes=dcls, diag_add=dadd, sign=sign,
+                                    bcmap=bmap, pattern=m.csr, inplace=True, name=name)
+            if after and name in after:
+                after[name]()
         self.dofClasses, self.rowClasses = cls, rcls
         self._unit_diagonals_folded = True
 

