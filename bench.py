@@ -280,7 +280,7 @@ def run_native(a):
     nx, n = a.nx, a.ngl
     # strong scaling: the fixed nx x nx mesh is cut into `world` strips of cell rows, one per GPU; a rank assembles the
     # rows of the nodes it owns (complete thanks to one ghost row of cells: no matrix entry crosses NVLink)
-    prob = CavityAssembly(nx, n, pc_type=a.pc, ksp_max_it=200000, ksp_check_every=50)
+    prob = CavityAssembly(nx, n, pc_type=a.pc, ksp_max_it=200000, **({"ksp_check_every": 50} if a.pc == "jacobi" else {}))
     prob.step()
     barrier()
     nnz = {k: v.nnz for k, v in prob.mats.items()}

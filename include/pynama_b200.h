@@ -326,6 +326,17 @@ int pyn_halo_create(const pyn_comm* c, int nnbr, const int32_t* h_nbr_rank, cons
                     const int64_t* const* d_send_idx, const int64_t* h_recv_cnt, const int64_t* const* d_recv_idx,
                     pyn_halo** out);
 int pyn_halo_destroy(pyn_halo* h);
+/* Peer memory: one region per rank, mapped by every other rank of the box through CUDA IPC (NVLink P2P).  Once attached
+ * (pyn_comm_set_peer) the all-reduces of <= 7 scalars become a one-warp kernel that stores the rank's partial into
+ * every peer's slot and sums the slots in rank order, and the halo exchange packs straight into the neighbour's
+ * mailbox and hands over with an epoch flag -- no NCCL launch on the Krylov iteration's critical path.  The caller
+ * gathers the 64-byte handles of all ranks (rank-major) with its rendezvous layer. */
+typedef struct pyn_peer pyn_peer;
+int pyn_peer_create(int rank, int world, int64_t mailbox_doubles, pyn_peer** out);
+int pyn_peer_handle(const pyn_peer* p, char* handle64);
+int pyn_peer_open(pyn_peer* p, const char* handles /* [world][64] */);
+int pyn_peer_destroy(pyn_peer* p);
+int pyn_comm_set_peer(pyn_comm* c, pyn_peer* p);
 /* d_vec: local vector with ncomp (1..3) dofs per node; ghost entries are overwritten with their owners' values */
 int pyn_halo_exchange(const pyn_halo* h, double* d_vec, int ncomp, void* stream);
 int64_t pyn_halo_bytes(const pyn_halo* h, int ncomp);

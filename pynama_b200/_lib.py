@@ -103,6 +103,11 @@ _SIGNATURES = {
     "pyn_comm_destroy": (C.c_int, [c_vp]),
     "pyn_comm_info": (C.c_int, [c_vp, P(C.c_int), P(C.c_int), P(C.c_int)]),
     "pyn_comm_allreduce_sum": (C.c_int, [c_vp, c_vp, C.c_int, c_vp]),
+    "pyn_peer_create": (C.c_int, [C.c_int, C.c_int, c_i64, P(c_vp)]),
+    "pyn_peer_handle": (C.c_int, [c_vp, c_vp]),
+    "pyn_peer_open": (C.c_int, [c_vp, c_vp]),
+    "pyn_peer_destroy": (C.c_int, [c_vp]),
+    "pyn_comm_set_peer": (C.c_int, [c_vp, c_vp]),
     "pyn_halo_create": (C.c_int, [c_vp, C.c_int, P(c_i32), P(c_i64), P(c_vp), P(c_i64), P(c_vp), P(c_vp)]),
     "pyn_halo_destroy": (C.c_int, [c_vp]),
     "pyn_halo_exchange": (C.c_int, [c_vp, c_vp, C.c_int, c_vp]),

@@ -420,8 +420,7 @@ int enqueue_cg_iteration(const pyn_ksp* k, cudaStream_t st) {
     if (rc) return rc;
   }
   if (dist) {
-    cg_reduce_kernel<<<1, 32, 0, st>>>(npw, k->B.part_a, nullptr, k->gsum);
-    int rc = pyn::comm_allreduce_sum(k->comm, k->gsum, 1, st);
+    int rc = pyn::comm_reduce_allreduce(k->comm, npw, k->B.part_a, 0, nullptr, k->gsum, st);
     if (rc) return rc;
   }
   if (k->mg) {   // z = V-cycle(r): r -= a w, the cycle's launches, then the Jacobi rows + the two dot products
@@ -432,8 +431,7 @@ int enqueue_cg_iteration(const pyn_ksp* k, cudaStream_t st) {
   } else
   cg_update_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, npw, k->B, k->pzz, k->pzr, g);
   if (dist) {
-    cg_reduce_kernel<<<1, 32, 0, st>>>(k->vgrid, k->pzz, k->pzr, k->gsum + 1);
-    int rc = pyn::comm_allreduce_sum(k->comm, k->gsum + 1, 2, st);
+    int rc = pyn::comm_reduce_allreduce(k->comm, k->vgrid, k->pzz, k->vgrid, k->pzr, k->gsum + 1, st);
     if (rc) return rc;
   }
   cg_scalar_kernel<<<1, 32, 0, st>>>(npw, k->vgrid, k->B, k->pzz, k->pzr, k->opts.atol, k->opts.dtol,
@@ -454,7 +452,7 @@ int pyn_ksp_create(int64_t nrows, const int64_t* d_ptr, const int32_t* d_ind, co
   pyn_ksp* k = new pyn_ksp();
   memset(k, 0, sizeof(*k));
   k->n = nrows; k->nnz = nnz; k->ptr = d_ptr; k->ind = d_ind; k->val = d_val; k->opts = *opts;
-  if (k->opts.check_every <= 0) k->opts.check_every = opts->pc == 2 ? 2 : 16;
+  if (k->opts.check_every <= 0) k->opts.check_every = opts->pc == 2 ? 1 : 16;   // a V-cycle iteration is ~10^4 x a host poll
   if (k->opts.max_it <= 0) k->opts.max_it = 10000;
   k->vgrid = pyn::grid_for(nrows, BLK, 8);
   {

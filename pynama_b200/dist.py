@@ -6,6 +6,7 @@ all-reduce of the Krylov / time-step scalars) goes through the library's own com
 can issue them from inside its captured iteration graph.  In the reference these are PETSc's VecScatter and
 MPI_Allreduce."""
 import ctypes as C
+import os
 
 import numpy as np
 import torch
@@ -54,6 +55,41 @@ class DistContext(object):
         self._halo = C.c_void_p()
         call("pyn_halo_create", self._comm, n, nbr, scnt, sidx, rcnt, ridx, C.byref(self._halo))
         self._scal = be.empty(4)
+        self._peer = None
+        self.peer_memory = False
+        if self.world > 1 and os.environ.get("PYN_P2P", "1") not in ("0", "false", "off"):
+            self._attach_peer_memory(max([len(r) for _, _, r in lists] + [len(s) for _, s, _ in lists] + [1]))
+
+    def _attach_peer_memory(self, max_nodes):
+        """Map every rank's exchange region over NVLink (CUDA IPC) and route the Krylov scalars' all-reduces and the
+        halo exchanges through it (csrc/dist.cu, peer-memory path).  Collective.  Falls back to NCCL -- on every rank
+        alike -- when any rank cannot map its peers."""
+        import torch.distributed as dist
+        cap = torch.tensor([int(max_nodes) * 3], dtype=torch.int64, device=self.owned.device)
+        dist.all_reduce(cap, op=dist.ReduceOp.MAX)
+        ok, peer = 1, C.c_void_p()
+        try:
+            call("pyn_peer_create", self.rank, self.world, int(cap[0]), C.byref(peer))
+            h = C.create_string_buffer(64)
+            call("pyn_peer_handle", peer, h)
+            mine = bytes(h.raw)
+        except _lib.PynamaError:
+            ok, mine = 0, b"\0" * 64
+        handles = [None] * self.world
+        dist.all_gather_object(handles, mine)
+        if ok:
+            try:
+                call("pyn_peer_open", peer, C.create_string_buffer(b"".join(handles), 64 * self.world))
+            except _lib.PynamaError:
+                ok = 0
+        flag = torch.tensor([ok], dtype=torch.int64, device=self.owned.device)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if int(flag[0]) == 1:
+            call("pyn_comm_set_peer", self._comm, peer)
+            self._peer, self.peer_memory = peer, True
+        elif peer:
+            _lib.load().pyn_peer_destroy(peer)
+        dist.barrier()
 
     def owned_rows(self, ncomp):
         """uint8 per dof (node*ncomp + c): 1 when the node is owned."""
@@ -113,6 +149,10 @@ class DistContext(object):
         if getattr(self, "_halo", None):
             lib.pyn_halo_destroy(self._halo)
             self._halo = None
+        if getattr(self, "_peer", None):
+            lib.pyn_comm_set_peer(self._comm, None)
+            lib.pyn_peer_destroy(self._peer)
+            self._peer = None
         if getattr(self, "_comm", None):
             lib.pyn_comm_destroy(self._comm)
             self._comm = None
