@@ -347,6 +347,7 @@ def run_native(a):
     if rank == 0:
         out["clocks"] = sampler.stop()
     out["setup"] = prob.setup
+    out["parity_checks"] = parity_checks(prob, be, torch, world, nx, n, dof_total)
     if not a.no_time_loop:
         tl = time_loop_phase(a, prob, be, torch, peak, barrier, world)
         out["time_loop"] = tl
@@ -599,6 +600,36 @@ def run_percell(a):
         "gpu_launches": int(launches), "clocks": clocks,
     }
     print(json.dumps(out), flush=True)
+
+
+def parity_checks(prob, be, torch, world, nx, ngl, dof_total):
+    """Size-independent invariants evaluated on every rank in the measured run (tests/test_fullsize_gpu.py holds the
+    full set): the owned rows of all ranks add up to the serial system, and a constant velocity field is in the
+    null space of K - Krhs on every owned row ((K - Krhs) t = 0: rigid translations carry no strain), which
+    fails if any element contribution, boundary class or ghost/owner decision is wrong."""
+    import torch.distributed as dist
+    K, Krhs = prob.mats["K"], prob.mats["Krhs"]
+    N = prob.dom.getTotalNodes()
+    res = 0.0
+    for comp in (0, 1):
+        t = be.zeros(2 * N)
+        t[comp::2] = 1.0
+        y, y2 = be.empty(2 * N), be.empty(2 * N)
+        K.mult(t, y, planned=False)
+        Krhs.mult(t, y2, planned=False)
+        scale = float(y.abs().max())
+        res = max(res, float((y - y2).abs().max()) / max(scale, 1e-300))
+    serial_dofs = 2 * (nx * (ngl - 1) + 1) ** 2
+    nnz_owned = torch.tensor([float(K.nnz), res], dtype=torch.float64, device="cuda")
+    if world > 1:
+        mx = nnz_owned.clone()
+        dist.all_reduce(nnz_owned, op=dist.ReduceOp.SUM)
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        res = float(mx[1])
+    return {"owned_dofs_sum_equals_serial": int(dof_total) == serial_dofs, "serial_dofs": serial_dofs,
+            "nnz_K_sum_over_ranks": int(nnz_owned[0]), "nullspace_residual_max_over_ranks": res,
+            "nullspace_ok": bool(res < 1e-12),
+            "peer_memory": bool(getattr(prob.fem.comm.dist, "peer_memory", False)) if world > 1 else None}
 
 
 def load_traffic(kernel_substr):

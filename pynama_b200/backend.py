@@ -89,15 +89,15 @@ class ElemKernels:
         call("pyn_elem_kle", self._h, ptr(coords), ne, ptr(K), ptr(Rw), ptr(Rd), stream())
         return K, Rw, Rd
 
-    def affine_coef(self, coords):
+    def affine_coef(self, coords, check=True):
         """coords (ne,4,2) -> (coef (ne,18) on device, number of non-affine elements): the closed-form coefficients
-        of csrc/elem_affine.cuh.  Synchronises (one scalar)."""
+        of csrc/elem_affine.cuh.  Synchronises (one scalar) unless check=False (caller knows the cells are affine)."""
         coords = coords.contiguous()
         ne = coords.numel() // 8
         coef = empty(ne * 18).view(ne, 18)
         bad = C.c_int64()
-        call("pyn_elem_affine_coef", self._h, ptr(coords), ne, ptr(coef), C.byref(bad), stream())
-        return coef, bad.value
+        call("pyn_elem_affine_coef", self._h, ptr(coords), ne, ptr(coef), C.byref(bad) if check else None, stream())
+        return coef, (bad.value if check else 0)
 
     def kle_affine(self, coef, want_rd=True):
         """Materialised K, Rw, Rd of affine elements from their coefficients (same layout as kle())."""

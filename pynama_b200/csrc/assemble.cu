@@ -33,14 +33,15 @@ struct DescView {
   int which;             // 0 K (2x2 blocks), 1 Rw, 2 Rd (2x1 blocks)
 };
 
-// element block (rows of local node lr, columns of local node l) of element e from the affine closed form
+// element block (rows of local node lr, columns of local node l) of one element from the affine closed form:
+// cf = the element's coefficients, rec = the product record of the pair (lr, l)
 template <int RD, int CD>
-__device__ __forceinline__ void affine_entry(const DescView& d, const pyn::AffTables& T, const double* __restrict__ cf,
-                                             int lr, int l, double (&v)[RD][CD]) {
+__device__ __forceinline__ void affine_entry(const DescView& d, const double* __restrict__ cf,
+                                             const double* __restrict__ rec, double (&v)[RD][CD]) {
   if constexpr (RD == 2 && CD == 2) {
-    pyn::affine_block_K(T, cf, lr, l, v);
+    pyn::affine_block_K(cf, rec, v);
   } else if constexpr (RD == 2 && CD == 1) {
-    pyn::affine_block_R(T, cf, d.which, lr, l, v);
+    pyn::affine_block_R(cf + 13, rec, d.which, d.aff.alpha_w, d.aff.alpha_d, v);
   }
 }
 
@@ -98,7 +99,9 @@ asm_gather_kernel(pyn::TopoView t, DescView d, const int* __restrict__ list, int
           if (l != 0xFF) {
             if constexpr (AFF) {
               double blk[RD][CD];
-              affine_entry<RD, CD>(d, d.aff, d.coef + (int64_t)e * PYN_AFF_NCOEF, lr, l, blk);
+              const double* rec = CD == 2 ? d.aff.pairK + (int64_t)(lr * t.nn + l) * pyn::PYN_AFF_PK
+                                          : d.aff.pairR + (int64_t)(lr * t.nn + l) * pyn::PYN_AFF_PR;
+              affine_entry<RD, CD>(d, d.coef + (int64_t)e * PYN_AFF_NCOEF, rec, blk);
 #pragma unroll
               for (int a = 0; a < RD; ++a)
 #pragma unroll
@@ -270,41 +273,52 @@ asm_interior_kernel(pyn::TopoView t, DescView d, const int64_t* __restrict__ ind
 }
 
 // ---- fused integrate-and-assemble, interior nodes, affine elements --------------------------------------------------
-// Same batching and the same order of additions as asm_interior_kernel (ascending cell order per entry), but the
-// element entries are EVALUATED from the element's 17 coefficients and the six 1-D matrices held in shared memory
-// (elem_affine.cuh) instead of being read from a materialised element matrix: the only HBM traffic left is the CSR rows
+// The element entries are EVALUATED -- from the element's coefficients (staged per batch in shared memory) and the
+// product record of the local node pair (elem_affine.cuh; the table sits in shared memory when it fits, else it is read
+// through L1) -- instead of being read from a materialised element matrix: the only HBM traffic left is the CSR rows
 // written once, the row pointers, 1 B per (adjacency slot, incident element) of the inverse position map and 144 B of
-// coefficients per element.  A lane keeps up to AFF_Q adjacency positions of its node in registers and walks the
-// node's elements in the outer loop, so the coefficients are loaded once per (node, element).
-constexpr int AFF_Q = 4;   // adjacency positions per lane and pass (128 per warp)
+// coefficients per element.
+//
+// A CTA takes ASM_NB consecutive nodes and its threads share the FLAT list of their adjacency slots (the nodes' slots
+// are contiguous in the adjacency CSR, and so are their output rows): one RD x CD output block per thread and step,
+// whatever the row lengths -- no per-node loop, no idle lanes on short rows.  A thread adds the contributions of the
+// node's elements in ASCENDING cell order (the reference's cell loop: same order of additions per entry as
+// asm_interior_kernel, hence the same bits).
+constexpr int AFF_KC = 4;    // incident elements per node whose coefficients are staged (more: read from global)
+constexpr int AFF_SLOTS = 4096;   // adjacency slots of a batch with a slot -> node table (longer batches: binary search)
 
-template <int CD>
-__global__ void __launch_bounds__(256)
+template <int CD, bool TSM>
+__global__ void __launch_bounds__(256, TSM ? 3 : 4)
 asm_interior_affine_kernel(pyn::TopoView t, DescView d, const int64_t* __restrict__ indptr, int* __restrict__ indices,
                            double* __restrict__ data) {
   constexpr int RD = 2;
-  __shared__ int64_t s_adj[ASM_NB + 1], s_inv[ASM_NB + 1], s_base[ASM_NB * RD];
+  constexpr int NC = CD == 2 ? 13 : 4, C0 = CD == 2 ? 0 : 13;     // coefficients used by this block shape
+  constexpr int PR = CD == 2 ? pyn::PYN_AFF_PK : pyn::PYN_AFF_PR;
+  extern __shared__ __align__(16) double s_tab[];                  // [nn*nn][PR] when TSM
+  __shared__ int64_t s_inv[ASM_NB + 1], s_base[ASM_NB * RD];
+  __shared__ int s_adj[ASM_NB + 1];                                // adjacency offsets relative to the batch
   __shared__ int s_el[ASM_NB * ASM_MAXDEG], s_lr[ASM_NB * ASM_MAXDEG];
   __shared__ __align__(16) uint8_t s_ivb[ASM_IVCAP + 32];
   __shared__ int s_n2e[ASM_NB + 1];
   __shared__ uint8_t s_flag[ASM_NB];
-  __shared__ double s_tab[6 * PYN_MAX_NGL * PYN_MAX_NGL];
-  __shared__ int s_perm[PYN_MAX_NGL * PYN_MAX_NGL];
-  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-  const int n2 = d.aff.n * d.aff.n;
-  for (int i = tid; i < 6 * n2; i += 256) s_tab[i] = d.aff.SF[i];   // SF MF CF SG MG CG are contiguous
-  for (int i = tid; i < n2; i += 256) s_perm[i] = d.aff.perm[i];
-  pyn::AffTables T = d.aff;
-  T.SF = s_tab; T.MF = s_tab + n2; T.CF = s_tab + 2 * n2; T.SG = s_tab + 3 * n2; T.MG = s_tab + 4 * n2;
-  T.CG = s_tab + 5 * n2; T.perm = s_perm;
+  __shared__ double s_cf[ASM_NB * AFF_KC * NC];
+  __shared__ uint8_t s_q2j[AFF_SLOTS];                             // adjacency slot of the batch -> node of the batch
+  const int tid = threadIdx.x;
+  const int nn = t.nn;
+  const double* gtab = CD == 2 ? d.aff.pairK : d.aff.pairR;
+  if (TSM) {
+    const int len = nn * nn * PR;
+    for (int i = tid * 2; i < len; i += 512) *reinterpret_cast<double2*>(s_tab + i) = *reinterpret_cast<const double2*>(gtab + i);
+  }
+  const double* tab = TSM ? s_tab : gtab;
   const int64_t nbatch = (t.nnodes + ASM_NB - 1) / ASM_NB;
   for (int64_t batch = blockIdx.x; batch < nbatch; batch += gridDim.x) {
     const int64_t r0 = batch * ASM_NB;
     const int nb = (int)min((int64_t)ASM_NB, t.nnodes - r0);
-    const int64_t e0 = t.n2e_ptr[r0];
+    const int64_t e0 = t.n2e_ptr[r0], a0 = t.adj_ptr[r0];
     __syncthreads();
     if (tid <= nb) {
-      s_adj[tid] = t.adj_ptr[r0 + tid];
+      s_adj[tid] = (int)(t.adj_ptr[r0 + tid] - a0);
       s_n2e[tid] = (int)(t.n2e_ptr[r0 + tid] - e0);
       s_inv[tid] = t.inv_ptr[r0 + tid];
     }
@@ -329,73 +343,88 @@ asm_interior_affine_kernel(pyn::TopoView t, DescView d, const int64_t* __restric
       }
     }
     __syncthreads();
-    for (int j = w; j < nb; j += 8) {  // one warp per node
+    if (data) {  // coefficients of the first AFF_KC elements of every node: independent loads, issued back to back
+      constexpr int PER = (ASM_NB * AFF_KC * NC + 255) / 256;
+      double tmp[PER];
+#pragma unroll
+      for (int u = 0; u < PER; ++u) {
+        const int i = tid + u * 256;
+        const int j = i / (AFF_KC * NC), rem = i - j * (AFF_KC * NC), k = rem / NC, c = rem - k * NC;
+        const bool ok = j < nb && !s_flag[j] && k < s_n2e[j + 1] - s_n2e[j];
+        tmp[u] = ok ? __ldg(d.coef + (int64_t)s_el[j * ASM_MAXDEG + k] * PYN_AFF_NCOEF + C0 + c) : 0.0;
+      }
+#pragma unroll
+      for (int u = 0; u < PER; ++u) {
+        const int i = tid + u * 256;
+        if (i < ASM_NB * AFF_KC * NC) s_cf[i] = tmp[u];
+      }
+    }
+    const int total = s_adj[nb];
+    const bool table = total <= AFF_SLOTS;
+    if (table) {   // slot -> node: 8 threads per node fill the node's range
+      const int j = tid >> 3;
+      if (j < nb)
+        for (int q = s_adj[j] + (tid & 7); q < s_adj[j + 1]; q += 8) s_q2j[q] = (uint8_t)j;
+    }
+    __syncthreads();
+    for (int q = tid; q < total; q += 256) {   // one output block per thread: adjacency slot q of the batch
+      int j = 0;                               // its node: largest j with s_adj[j] <= q
+      if (table) {
+        j = s_q2j[q];
+      } else {
+#pragma unroll
+        for (int step = ASM_NB / 2; step > 0; step >>= 1)
+          if (j + step < nb && s_adj[j + step] <= q) j += step;
+      }
       if (s_flag[j]) continue;
-      const int L = (int)(s_adj[j + 1] - s_adj[j]), deg = s_n2e[j + 1] - s_n2e[j];
-      const uint8_t* ivj = staged ? s_ivb + mis + (int)(s_inv[j] - s_inv[0]) : t.inv + s_inv[j];
+      const int p = q - s_adj[j], L = s_adj[j + 1] - s_adj[j], deg = s_n2e[j + 1] - s_n2e[j];
       if (data) {
-        for (int pc = 0; pc < L; pc += 32 * AFF_Q) {
-          double v[AFF_Q][RD][CD];
+        const uint8_t* ivj = staged ? s_ivb + mis + (int)(s_inv[j] - s_inv[0]) : t.inv + s_inv[j];
+        double v[RD][CD];
 #pragma unroll
-          for (int q = 0; q < AFF_Q; ++q)
+        for (int a = 0; a < RD; ++a)
 #pragma unroll
-            for (int a = 0; a < RD; ++a)
+          for (int b = 0; b < CD; ++b) v[a][b] = 0.0;
+        for (int k = 0; k < deg; ++k) {        // ascending cell order
+          const int l = ivj[k * L + p];
+          if (l == 0xFF) continue;
+          const double* rp = tab + ((int64_t)s_lr[j * ASM_MAXDEG + k] * nn + l) * PR;
+          double rec[PR];
 #pragma unroll
-              for (int b = 0; b < CD; ++b) v[q][a][b] = 0.0;
-          for (int k = 0; k < deg; ++k) {  // ascending cell order
-            const int lr = s_lr[j * ASM_MAXDEG + k];
-            const double* cg = d.coef + (int64_t)s_el[j * ASM_MAXDEG + k] * PYN_AFF_NCOEF;
-            double cf[PYN_AFF_NCOEF];
-            if (CD == 2) {
-#pragma unroll
-              for (int i = 0; i < 13; ++i) cf[i] = __ldg(cg + i);
-            } else {
-#pragma unroll
-              for (int i = 13; i < 17; ++i) cf[i] = __ldg(cg + i);
-            }
-#pragma unroll
-            for (int q = 0; q < AFF_Q; ++q) {
-              const int p = pc + q * 32 + lane;
-              if (p < L) {
-                const int l = ivj[k * L + p];
-                if (l != 0xFF) {
-                  double blk[RD][CD];
-                  affine_entry<RD, CD>(d, T, cf, lr, l, blk);
-#pragma unroll
-                  for (int a = 0; a < RD; ++a)
-#pragma unroll
-                    for (int b = 0; b < CD; ++b) v[q][a][b] += d.sign * blk[a][b];
-                }
-              }
-            }
+          for (int i = 0; i < PR; i += 2) {
+            const double2 x = TSM ? *reinterpret_cast<const double2*>(rp + i) : __ldg(reinterpret_cast<const double2*>(rp + i));
+            rec[i] = x.x;
+            rec[i + 1] = x.y;
+          }
+          double blk[RD][CD];
+          if (k < AFF_KC) {
+            affine_entry<RD, CD>(d, s_cf + (j * AFF_KC + k) * NC - C0, rec, blk);
+          } else {
+            affine_entry<RD, CD>(d, d.coef + (int64_t)s_el[j * ASM_MAXDEG + k] * PYN_AFF_NCOEF, rec, blk);
           }
 #pragma unroll
-          for (int q = 0; q < AFF_Q; ++q) {
-            const int p = pc + q * 32 + lane;
-            if (p < L) {
+          for (int a = 0; a < RD; ++a)
 #pragma unroll
-              for (int a = 0; a < RD; ++a) {
-                const int64_t base = s_base[j * RD + a];
-                double* o = data + base + p * CD;
-                if (CD == 2 && ((base & 1) == 0)) {
-                  *reinterpret_cast<double2*>(o) = make_double2(v[q][a][0], v[q][a][CD - 1]);
-                } else {
+            for (int b = 0; b < CD; ++b) v[a][b] += d.sign * blk[a][b];
+        }
 #pragma unroll
-                  for (int b = 0; b < CD; ++b) o[b] = v[q][a][b];
-                }
-              }
-            }
+        for (int a = 0; a < RD; ++a) {
+          const int64_t base = s_base[j * RD + a];
+          double* o = data + base + p * CD;
+          if (CD == 2 && ((base & 1) == 0)) {
+            *reinterpret_cast<double2*>(o) = make_double2(v[a][0], v[a][CD - 1]);
+          } else {
+#pragma unroll
+            for (int b = 0; b < CD; ++b) o[b] = v[a][b];
           }
         }
       }
       if (indices) {
-        for (int p = lane; p < L; p += 32) {
-          const int c = t.adj_cols[s_adj[j] + p];
+        const int c = t.adj_cols[a0 + q];
 #pragma unroll
-          for (int a = 0; a < RD; ++a)
+        for (int a = 0; a < RD; ++a)
 #pragma unroll
-            for (int b = 0; b < CD; ++b) indices[s_base[j * RD + a] + p * CD + b] = c * CD + b;
-        }
+          for (int b = 0; b < CD; ++b) indices[s_base[j * RD + a] + p * CD + b] = c * CD + b;
       }
     }
   }
@@ -791,8 +820,24 @@ static int launch_interior(const pyn_topo* t, const DescView& dv, const int64_t*
   const int grid = pyn::grid_for((t->nnodes + ASM_NB - 1) / ASM_NB * 256, 256, 8);
   if (dv.coef) {
     PYN_REQUIRE(tv.nn == dv.aff.n * dv.aff.n, "affine assembly: element handle of another order");
-    if (dv.cdof == 2) asm_interior_affine_kernel<2><<<grid, 256, 0, st>>>(tv, dv, indptr, indices, data);
-    else asm_interior_affine_kernel<1><<<grid, 256, 0, st>>>(tv, dv, indptr, indices, data);
+    // The product table is read through L1 (4 CTAs of 64 registers per SM: 6.1 ms for K at 707^2 x ngl 5); holding it
+    // in shared memory instead costs a CTA per SM and measured 7.2 ms (PYN_AFF_TSM=1: A/B switch).
+    const size_t tbytes = sizeof(double) * (size_t)tv.nn * tv.nn * (dv.cdof == 2 ? pyn::PYN_AFF_PK : pyn::PYN_AFF_PR);
+    static const int tsm_env = getenv("PYN_AFF_TSM") ? atoi(getenv("PYN_AFF_TSM")) : 0;
+    const bool tsm = tsm_env != 0 && tbytes <= 160 * 1024;
+    const size_t dyn = tsm ? tbytes : 0;
+#define PYN_AFF_LAUNCH(C, T)                                                                                         \
+    {                                                                                                                  \
+      PYN_CHECK_CUDA(cudaFuncSetAttribute(asm_interior_affine_kernel<C, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                          (int)dyn));                                                                  \
+      asm_interior_affine_kernel<C, T><<<grid, 256, dyn, st>>>(tv, dv, indptr, indices, data);                         \
+    }
+    if (dv.cdof == 2) {
+      if (tsm) PYN_AFF_LAUNCH(2, true) else PYN_AFF_LAUNCH(2, false)
+    } else {
+      if (tsm) PYN_AFF_LAUNCH(1, true) else PYN_AFF_LAUNCH(1, false)
+    }
+#undef PYN_AFF_LAUNCH
     PYN_CHECK_LAUNCH();
     return PYN_OK;
   }

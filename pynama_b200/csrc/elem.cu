@@ -306,20 +306,21 @@ elem_affine_coef_kernel(int64_t ne, const double* __restrict__ coords, double aw
   if (!ok) atomicAdd(nonaffine, 1ull);
 }
 
+// product records of every local node pair (once per element order)
+__global__ void elem_pair_tables_kernel(pyn::AffTables T, double* __restrict__ pairK, double* __restrict__ pairR) {
+  const int nn = T.n * T.n;
+  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < nn * nn; idx += gridDim.x * blockDim.x) {
+    const int i = idx / nn, j = idx - i * nn;
+    pyn::affine_pair_products_K(T, i, j, pairK + (int64_t)idx * pyn::PYN_AFF_PK);
+    pyn::affine_pair_products_R(T, i, j, pairR + (int64_t)idx * pyn::PYN_AFF_PR);
+  }
+}
+
 // materialised K_e / Rw_e / Rd_e from the coefficients: one thread per (element, local node pair)
 __global__ void __launch_bounds__(256)
 elem_kle_affine_kernel(pyn::AffTables T, const double* __restrict__ coef, int64_t ne, double* __restrict__ Kout,
                        double* __restrict__ Rwout, double* __restrict__ Rdout) {
-  extern __shared__ double sm[];
-  const int n = T.n, nn = n * n, n2 = n * n;
-  double* tab = sm;
-  int* perm = (int*)(tab + 6 * n2);
-  for (int i = threadIdx.x; i < 6 * n2; i += blockDim.x) tab[i] = T.SF[i];   // the six matrices are contiguous
-  for (int i = threadIdx.x; i < nn; i += blockDim.x) perm[i] = T.perm[i];
-  __syncthreads();
-  pyn::AffTables S = T;
-  S.SF = tab; S.MF = tab + n2; S.CF = tab + 2 * n2; S.SG = tab + 3 * n2; S.MG = tab + 4 * n2; S.CG = tab + 5 * n2;
-  S.perm = perm;
+  const int nn = T.n * T.n;
   const int64_t tot = ne * (int64_t)nn * nn;
   for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < tot; idx += (int64_t)gridDim.x * blockDim.x) {
     const int64_t e = idx / (nn * nn);
@@ -327,21 +328,21 @@ elem_kle_affine_kernel(pyn::AffTables T, const double* __restrict__ coef, int64_
     const double* cf = coef + e * PYN_AFF_NCOEF;
     if (Kout) {
       double v[2][2];
-      pyn::affine_block_K(S, cf, i, j, v);
+      pyn::affine_block_K(cf, T.pairK + (int64_t)ij * pyn::PYN_AFF_PK, v);
       double* row0 = Kout + e * (int64_t)(4 * nn) * nn + (int64_t)(2 * i) * (2 * nn) + 2 * j;
       *reinterpret_cast<double2*>(row0) = make_double2(v[0][0], v[0][1]);
       *reinterpret_cast<double2*>(row0 + 2 * nn) = make_double2(v[1][0], v[1][1]);
     }
     if (Rwout) {
       double v[2][1];
-      pyn::affine_block_R(S, cf, 1, i, j, v);
+      pyn::affine_block_R(cf + 13, T.pairR + (int64_t)ij * pyn::PYN_AFF_PR, 1, T.alpha_w, T.alpha_d, v);
       double* o = Rwout + e * (int64_t)(2 * nn) * nn + (int64_t)(2 * i) * nn + j;
       o[0] = v[0][0];
       o[nn] = v[1][0];
     }
     if (Rdout) {
       double v[2][1];
-      pyn::affine_block_R(S, cf, 2, i, j, v);
+      pyn::affine_block_R(cf + 13, T.pairR + (int64_t)ij * pyn::PYN_AFF_PR, 2, T.alpha_w, T.alpha_d, v);
       double* o = Rdout + e * (int64_t)(2 * nn) * nn + (int64_t)(2 * i) * nn + j;
       o[0] = v[0][0];
       o[nn] = v[1][0];
@@ -415,6 +416,15 @@ int pyn_elem_create(int ngl, int nqF, const double* hF, const double* dF, const 
     delete[] a;
   }
   if (err == cudaSuccess) err = cudaMalloc(&e->d_count, sizeof(unsigned long long));
+  {
+    const size_t np = (size_t)n * n * n * n;
+    if (err == cudaSuccess) err = cudaMalloc(&e->d_pairK, sizeof(double) * np * pyn::PYN_AFF_PK);
+    if (err == cudaSuccess) err = cudaMalloc(&e->d_pairR, sizeof(double) * np * pyn::PYN_AFF_PR);
+    if (err == cudaSuccess) {
+      elem_pair_tables_kernel<<<(int)((np + 255) / 256), 256>>>(pyn::aff_tables(e), e->d_pairK, e->d_pairR);
+      err = cudaDeviceSynchronize();
+    }
+  }
   if (err != cudaSuccess) {
     pyn::set_error("pyn_elem_create: %s", cudaGetErrorString(err));
     delete e;
@@ -429,6 +439,8 @@ int pyn_elem_destroy(pyn_elem* e) {
   cudaFree(e->d_tab);
   cudaFree(e->d_perm);
   cudaFree(e->d_aff);
+  cudaFree(e->d_pairK);
+  cudaFree(e->d_pairR);
   cudaFree(e->d_count);
   delete e;
   return PYN_OK;
@@ -496,10 +508,9 @@ int pyn_elem_kle_affine(const pyn_elem* e, const double* d_coef, int64_t ne, dou
   PYN_REQUIRE(e && d_coef && ne >= 0, "bad arguments");
   if (ne == 0) return PYN_OK;
   const int nn = e->n * e->n;
-  const size_t smem = sizeof(double) * 6 * nn + sizeof(int) * nn;
   const int64_t tot = ne * (int64_t)nn * nn;
-  elem_kle_affine_kernel<<<pyn::grid_for(tot, 256, 16), 256, smem, pyn::as_stream(stream)>>>(pyn::aff_tables(e), d_coef, ne,
-                                                                                            d_K, d_Rw, d_Rd);
+  elem_kle_affine_kernel<<<pyn::grid_for(tot, 256, 16), 256, 0, pyn::as_stream(stream)>>>(pyn::aff_tables(e), d_coef, ne, d_K,
+                                                                                       d_Rw, d_Rd);
   PYN_CHECK_LAUNCH();
   return PYN_OK;
 }

@@ -10,6 +10,8 @@ struct pyn_elem {
   int* d_perm;    // nn
   int off_hF, off_dF, off_wF, off_xF, off_hG, off_dG, off_wG, off_xG, off_D, off_wO, off_xO, tab_len;
   double* d_aff;  // [6][n*n] SF MF CF SG MG CG: 1-D matrices of the affine closed form (elem_affine.cuh)
+  double* d_pairK;  // [nn*nn][PYN_AFF_PK] products of the 1-D matrices per local node pair
+  double* d_pairR;  // [nn*nn][PYN_AFF_PR]
   unsigned long long* d_count;  // scratch counter (non-affine elements)
 };
 
@@ -20,6 +22,7 @@ static inline AffTables aff_tables(const pyn_elem* e) {
   T.SF = e->d_aff; T.MF = e->d_aff + n2; T.CF = e->d_aff + 2 * n2;
   T.SG = e->d_aff + 3 * n2; T.MG = e->d_aff + 4 * n2; T.CG = e->d_aff + 5 * n2;
   T.perm = e->d_perm; T.n = e->n; T.alpha_w = e->alpha_w; T.alpha_d = e->alpha_d;
+  T.pairK = e->d_pairK; T.pairR = e->d_pairR;
   return T;
 }
 }  // namespace pyn

@@ -24,6 +24,8 @@ struct AffTables {   // device pointers (or shared-memory copies) of the six n x
   const int* perm;   // [nn]: element-local node -> a*n+b
   int n;
   double alpha_w, alpha_d;
+  const double* pairK;   // [nn*nn][PYN_AFF_PK] product records (device)
+  const double* pairR;   // [nn*nn][PYN_AFF_PR]
 };
 
 // coefficients of one element from its corner coordinates (closure order); returns false when the element is not
@@ -62,20 +64,44 @@ __device__ __forceinline__ bool affine_coefficients(const double* __restrict__ c
 __device__ __forceinline__ double aff_mul(double a, double b) { return __dmul_rn(a, b); }
 __device__ __forceinline__ double aff_fma(double a, double b, double c) { return __fma_rn(a, b, c); }
 
-// 2 x 2 block of K_e between local nodes i (rows) and j (columns): [[uu, uv], [vu, vv]]
-__device__ __forceinline__ void affine_block_K(const AffTables& T, const double* __restrict__ cf, int i, int j,
-                                               double (&v)[2][2]) {
+constexpr int PYN_AFF_PK = 8;   // doubles per local node pair in the K product table (7 used; 64-byte records)
+constexpr int PYN_AFF_PR = 4;   // ... in the Rw / Rd product table
+
+// The element-independent half of an entry: products of the 1-D matrices for the local node pair (i, j).  They are
+// tabulated once per element order (pyn_elem.d_pairK / d_pairR, [nn*nn] records) so that an assembly thread evaluates an
+// entry from one 64-byte (32-byte) record and the element's coefficients -- no index arithmetic, no divisions.
+__device__ __forceinline__ void affine_pair_products_K(const AffTables& T, int i, int j, double* __restrict__ pr) {
   const int n = T.n, pi = T.perm[i], pj = T.perm[j];
   const int a = pi / n, b = pi - a * n, c = pj / n, d = pj - c * n;
   const int ac = a * n + c, ca = c * n + a, bd = b * n + d, db = d * n + b;
-  // full rule: the vector Laplacian part, identical on uu and vv; the mixed pair is summed un-fused (bitwise symmetric)
-  const double cfca = T.CF[ca], cfbd = T.CF[bd], cfac = T.CF[ac], cfdb = T.CF[db];
-  double gr = aff_mul(cf[0], aff_mul(T.SF[ac], T.MF[bd]));
-  gr = aff_fma(cf[1], __dadd_rn(aff_mul(cfca, cfbd), aff_mul(cfac, cfdb)), gr);
-  gr = aff_fma(cf[2], aff_mul(T.MF[ac], T.SF[bd]), gr);
+  pr[0] = aff_mul(T.SF[ac], T.MF[bd]);
+  pr[1] = __dadd_rn(aff_mul(T.CF[ca], T.CF[bd]), aff_mul(T.CF[ac], T.CF[db]));   // un-fused pair: bitwise symmetric
+  pr[2] = aff_mul(T.MF[ac], T.SF[bd]);
+  pr[3] = aff_mul(T.SG[ac], T.MG[bd]);
+  pr[4] = aff_mul(T.CG[ca], T.CG[bd]);
+  pr[5] = aff_mul(T.CG[ac], T.CG[db]);
+  pr[6] = aff_mul(T.MG[ac], T.SG[bd]);
+  pr[7] = 0.0;
+}
+__device__ __forceinline__ void affine_pair_products_R(const AffTables& T, int i, int j, double* __restrict__ pr) {
+  const int n = T.n, pi = T.perm[i], pj = T.perm[j];
+  const int a = pi / n, b = pi - a * n, c = pj / n, d = pj - c * n;
+  const int ac = a * n + c, ca = c * n + a, bd = b * n + d, db = d * n + b;
+  pr[0] = aff_mul(T.CF[ac], T.MF[bd]);   // test phi, trial gradient
+  pr[1] = aff_mul(T.MF[ac], T.CF[bd]);
+  pr[2] = aff_mul(T.CG[ca], T.MG[bd]);   // test gradient, trial phi
+  pr[3] = aff_mul(T.MG[ac], T.CG[db]);
+}
+
+// 2 x 2 block of K_e between two local nodes from their product record: [[uu, uv], [vu, vv]]
+__device__ __forceinline__ void affine_block_K(const double* __restrict__ cf, const double* __restrict__ pr,
+                                               double (&v)[2][2]) {
+  // full rule: the vector Laplacian part, identical on uu and vv
+  double gr = aff_mul(cf[0], pr[0]);
+  gr = aff_fma(cf[1], pr[1], gr);
+  gr = aff_fma(cf[2], pr[2], gr);
   // reduced rule: penalty terms
-  const double sm = aff_mul(T.SG[ac], T.MG[bd]), ms = aff_mul(T.MG[ac], T.SG[bd]);
-  const double c1 = aff_mul(T.CG[ca], T.CG[bd]), c2 = aff_mul(T.CG[ac], T.CG[db]);
+  const double sm = pr[3], c1 = pr[4], c2 = pr[5], ms = pr[6];
   const double cs = __dadd_rn(c1, c2);
   double kuu = aff_mul(cf[3], sm);
   kuu = aff_fma(cf[4], cs, kuu);
@@ -83,8 +109,8 @@ __device__ __forceinline__ void affine_block_K(const AffTables& T, const double*
   double kvv = aff_mul(cf[6], sm);
   kvv = aff_fma(cf[7], cs, kvv);
   kvv = aff_fma(cf[8], ms, kvv);
-  // uv and vu = uv^T: the same four products with the two mixed coefficients exchanged; the mixed pair is again
-  // summed un-fused so that K_e[i][j] (uv) and K_e[j][i] (vu seen from the other node) carry the same bits
+  // uv and vu = uv^T: the same four products with the two mixed coefficients exchanged; the mixed pair is summed
+  // un-fused so that K_e[i][j] (uv) and K_e[j][i] (vu seen from the other node) carry the same bits
   double kuv = aff_mul(cf[9], sm);
   kuv = __dadd_rn(kuv, __dadd_rn(aff_mul(cf[10], c1), aff_mul(cf[11], c2)));
   kuv = aff_fma(cf[12], ms, kuv);
@@ -97,22 +123,17 @@ __device__ __forceinline__ void affine_block_K(const AffTables& T, const double*
   v[1][1] = __dadd_rn(gr, kvv);
 }
 
-// 2 x 1 block of Rw_e (which == 1) or Rd_e (which == 2) between local nodes i (velocity rows) and j (scalar column)
-__device__ __forceinline__ void affine_block_R(const AffTables& T, const double* __restrict__ cf, int which, int i,
-                                               int j, double (&v)[2][1]) {
-  const int n = T.n, pi = T.perm[i], pj = T.perm[j];
-  const int a = pi / n, b = pi - a * n, c = pj / n, d = pj - c * n;
-  const int ac = a * n + c, ca = c * n + a, bd = b * n + d, db = d * n + b;
-  const double f1 = aff_mul(T.CF[ac], T.MF[bd]), f2 = aff_mul(T.MF[ac], T.CF[bd]);   // test phi, trial gradient
-  const double g1 = aff_mul(T.CG[ca], T.MG[bd]), g2 = aff_mul(T.MG[ac], T.CG[db]);   // test gradient, trial phi
-  const double Ax = aff_fma(cf[14], f2, aff_mul(cf[13], f1)), Ay = aff_fma(cf[16], f2, aff_mul(cf[15], f1));
-  const double Cx = aff_fma(cf[14], g2, aff_mul(cf[13], g1)), Cy = aff_fma(cf[16], g2, aff_mul(cf[15], g1));
+// 2 x 1 block of Rw_e (which == 1) or Rd_e (which == 2); cf = the element's coefficients 13..16
+__device__ __forceinline__ void affine_block_R(const double* __restrict__ cf, const double* __restrict__ pr, int which,
+                                               double alpha_w, double alpha_d, double (&v)[2][1]) {
+  const double Ax = aff_fma(cf[1], pr[1], aff_mul(cf[0], pr[0])), Ay = aff_fma(cf[3], pr[1], aff_mul(cf[2], pr[0]));
+  const double Cx = aff_fma(cf[1], pr[3], aff_mul(cf[0], pr[2])), Cy = aff_fma(cf[3], pr[3], aff_mul(cf[2], pr[2]));
   if (which == 1) {        // Rw = int dv . curl(w) + alpha_w int curl(dv) w      (spectral.py:140-147)
-    v[0][0] = aff_fma(-T.alpha_w, Cy, Ay);
-    v[1][0] = aff_fma(T.alpha_w, Cx, -Ax);
+    v[0][0] = aff_fma(-alpha_w, Cy, Ay);
+    v[1][0] = aff_fma(alpha_w, Cx, -Ax);
   } else {                 // Rd = - int dv . grad(D) + alpha_d int div(dv) D
-    v[0][0] = aff_fma(T.alpha_d, Cx, -Ax);
-    v[1][0] = aff_fma(T.alpha_d, Cy, -Ay);
+    v[0][0] = aff_fma(alpha_d, Cx, -Ax);
+    v[1][0] = aff_fma(alpha_d, Cy, -Ay);
   }
 }
 

@@ -184,6 +184,24 @@ cg_spmv_dot_kernel(pyn::SpmvPlanView P, const int* __restrict__ ind, const doubl
   if (threadIdx.x == 0) B.part_a[blockIdx.x] = dot;
 }
 
+// bulk-copy (TMA) variant of the same kernel: spmv.cuh spmv_bulk_loop
+__global__ void __launch_bounds__(pyn::SB_BLK, 2)
+cg_spmv_dot_bulk_kernel(pyn::SpmvPlanView P, const int* __restrict__ ind, const double* __restrict__ val, CgBuffers B) {
+  extern __shared__ __align__(16) unsigned char sb_raw[];
+  __shared__ double red[pyn::SB_BLK / 32];
+  if (B.st->done) return;
+  pyn::SbSmem& sm = *reinterpret_cast<pyn::SbSmem*>(sb_raw);
+  double dot = 0.0;
+  CgDotEpi epi{B.w, B.p, &dot};
+  pyn::spmv_bulk_loop(P, ind, val, B.p, blockIdx.x, gridDim.x, P.nblk - 1, sm, epi);
+  if (blockIdx.x == gridDim.x - 1) {
+    pyn::SpmvSmem& old = *reinterpret_cast<pyn::SpmvSmem*>(sb_raw);
+    pyn::spmv_stream_chunk(P, ind, val, B.p, P.nblk - 1, old, epi);
+  }
+  dot = pyn::block_sum<pyn::SB_BLK>(dot, red);
+  if (threadIdx.x == 0) B.part_a[blockIdx.x] = dot;
+}
+
 // the same product through the element operator (tmat.cuh): phase 1 is pyn::tmat_apply on p; here phase 2 (gather
 // per un-flagged node, one thread each) and the flagged rows from the CSR, both with the p.w partials fused
 template <int RD>
@@ -403,6 +421,9 @@ int enqueue_cg_product(const pyn_ksp* k, cudaStream_t st, int* npw_out) {
     else if (k->tmat->rdof == 1) cg_tmat_interior_kernel<1><<<gi, 256, 0, st>>>(tv, k->B);
     else cg_tmat_interior_kernel<3><<<gi, 256, 0, st>>>(tv, k->B);
     npw = gi;
+  } else if (k->bulk) {
+    npw = k->plan->bulk_grid;
+    cg_spmv_dot_bulk_kernel<<<npw, pyn::SB_BLK, sizeof(pyn::SbSmem), st>>>(pyn::view_of(k->plan), k->ind, k->val, k->B);
   } else {
     cg_spmv_dot_kernel<<<k->sgrid, pyn::SP_BLK, 0, st>>>(pyn::view_of(k->plan), k->ind, k->val, k->B);
   }
@@ -462,9 +483,14 @@ int pyn_ksp_create(int64_t nrows, const int64_t* d_ptr, const int32_t* d_ind, co
     PYN_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, cg_spmv_dot_kernel, pyn::SP_BLK, 0));
     const int64_t cap = (int64_t)pyn::sm_count() * (occ > 0 ? occ : 1);
     k->sgrid = (int)(k->plan->nblk < cap ? k->plan->nblk : cap);
+    k->bulk = k->plan->bulk_ok && ((reinterpret_cast<uintptr_t>(d_ind) | reinterpret_cast<uintptr_t>(d_val)) & 15) == 0;
+    if (k->bulk)
+      PYN_CHECK_CUDA(cudaFuncSetAttribute(cg_spmv_dot_bulk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)sizeof(pyn::SbSmem)));
   }
   double* pool = nullptr;
   size_t nparts = (size_t)(k->vgrid > k->sgrid ? k->vgrid : k->sgrid);
+  if (nparts < (size_t)k->plan->bulk_grid) nparts = (size_t)k->plan->bulk_grid;
   if (nparts < (size_t)pyn::sm_count() * 16) nparts = (size_t)pyn::sm_count() * 16;   // room for the template operator's grids
   const size_t ld = ((size_t)nrows + 1) & ~(size_t)1;   // even stride: every work vector stays 16-byte aligned
   PYN_CHECK_CUDA(cudaMalloc(&pool, sizeof(double) * (6 * ld + 4 * nparts)));

@@ -27,6 +27,7 @@ struct pyn_ksp {
   double *pzz, *pzr;
   KspState* h_state;  // pinned
   int vgrid, sgrid;
+  int bulk;   // w = A p through the bulk-copy (TMA) CSR stream
   pyn_spmv_plan* plan;
   cudaGraphExec_t graph;
   int graph_iters;

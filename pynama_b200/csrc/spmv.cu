@@ -1,4 +1,6 @@
 // y = A x with fused epilogues (see include/pynama_b200.h: pyn_spmv).
+#include <stdlib.h>
+
 #include "spmv.cuh"
 
 namespace {
@@ -78,6 +80,27 @@ spmv_stream_kernel(pyn::SpmvPlanView P, const int* __restrict__ ind, const doubl
   for (int b = blockIdx.x; b < P.nblk; b += gridDim.x) pyn::spmv_stream_chunk(P, ind, val, x, b, sm, epi);
 }
 
+// bulk-copy variant (spmv.cuh): all chunks but the last through the TMA pipeline, the last through the register path
+__global__ void __launch_bounds__(pyn::SB_BLK, 2)
+spmv_bulk_kernel(pyn::SpmvPlanView P, const int* __restrict__ ind, const double* __restrict__ val,
+                 const double* __restrict__ x, ModeEpi epi) {
+  extern __shared__ __align__(16) unsigned char sb_raw[];
+  pyn::SbSmem& sm = *reinterpret_cast<pyn::SbSmem*>(sb_raw);
+  pyn::spmv_bulk_loop(P, ind, val, x, blockIdx.x, gridDim.x, P.nblk - 1, sm, epi);
+  if (blockIdx.x == gridDim.x - 1) {
+    pyn::SpmvSmem& old = *reinterpret_cast<pyn::SpmvSmem*>(sb_raw);   // the pipeline is drained: reuse its memory
+    pyn::spmv_stream_chunk(P, ind, val, x, P.nblk - 1, old, epi);
+  }
+}
+
+__global__ void plan_p0_kernel(int nblk, const int64_t* __restrict__ ptr, const int* __restrict__ blk_row,
+                               long long* __restrict__ blk_p0, int cap, int* __restrict__ too_big) {
+  for (int b = blockIdx.x * blockDim.x + threadIdx.x; b <= nblk; b += gridDim.x * blockDim.x) {
+    blk_p0[b] = ptr[blk_row[b]];
+    if (b < nblk && ptr[blk_row[b + 1]] - ptr[blk_row[b]] > cap) atomicExch(too_big, 1);
+  }
+}
+
 __global__ void plan_maxrow_kernel(int64_t nrows, const int64_t* __restrict__ ptr, int* __restrict__ out) {
   int m = 0;
   for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < nrows; r += (int64_t)gridDim.x * blockDim.x) {
@@ -132,6 +155,25 @@ extern "C" int pyn_spmv_plan_create(int64_t nrows, const int64_t* d_ptr, int64_t
   PYN_CHECK_CUDA(cudaMalloc(&p->blk_row, sizeof(int) * (nb + 1)));
   plan_rows_kernel<<<pyn::grid_for(nb + 1, 256), 256, 0, st>>>(nrows, d_ptr, chunk, p->nblk, p->blk_row);
   PYN_CHECK_LAUNCH();
+  {  // bulk-copy pipeline: first non-zero of every chunk, and whether every chunk fits a stage
+    PYN_CHECK_CUDA(cudaMalloc(&p->blk_p0, sizeof(long long) * (nb + 1)));
+    int* d_big = nullptr;
+    int big = 0;
+    PYN_CHECK_CUDA(cudaMalloc(&d_big, sizeof(int)));
+    PYN_CHECK_CUDA(cudaMemsetAsync(d_big, 0, sizeof(int), st));
+    plan_p0_kernel<<<pyn::grid_for(nb + 1, 256), 256, 0, st>>>(p->nblk, d_ptr, p->blk_row, p->blk_p0, pyn::SB_CAP, d_big);
+    PYN_CHECK_LAUNCH();
+    PYN_CHECK_CUDA(cudaMemcpyAsync(&big, d_big, sizeof(int), cudaMemcpyDeviceToHost, st));
+    PYN_CHECK_CUDA(cudaStreamSynchronize(st));
+    cudaFree(d_big);
+    static const bool off = getenv("PYN_SPMV_NO_BULK") != nullptr;
+    p->bulk_ok = !big && !off && p->nblk >= 2 && (reinterpret_cast<uintptr_t>(d_ptr) & 15) == 0;
+    PYN_CHECK_CUDA(cudaFuncSetAttribute(spmv_bulk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(pyn::SbSmem)));
+    int occb = 0;
+    PYN_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occb, spmv_bulk_kernel, pyn::SB_BLK, sizeof(pyn::SbSmem)));
+    const int64_t capb = (int64_t)pyn::sm_count() * (occb > 0 ? occb : 1);
+    p->bulk_grid = (int)(nb < capb ? nb : capb);
+  }
   int occ = 0;  // persistent grid: exactly the CTAs that are resident at once
   PYN_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, spmv_stream_kernel, pyn::SP_BLK, 0));
   const int64_t cap = (int64_t)pyn::sm_count() * (occ > 0 ? occ : 1);
@@ -144,6 +186,7 @@ extern "C" int pyn_spmv_plan_create(int64_t nrows, const int64_t* d_ptr, int64_t
 extern "C" int pyn_spmv_plan_destroy(pyn_spmv_plan* p) {
   if (!p) return PYN_OK;
   cudaFree(p->blk_row);
+  cudaFree(p->blk_p0);
   delete p;
   return PYN_OK;
 }
@@ -155,7 +198,11 @@ extern "C" int pyn_spmv_planned(const pyn_spmv_plan* p, const int32_t* d_ind, co
   PYN_REQUIRE(mode != PYN_SPMV_SRT_VTENSV || (d_aux != nullptr && p->nrows % 3 == 0),
               "SRT_VTENSV needs aux and 3 rows per node");
   ModeEpi epi{d_y, mode, p0, p1, d_aux};
-  spmv_stream_kernel<<<p->grid, pyn::SP_BLK, 0, pyn::as_stream(stream)>>>(pyn::view_of(p), d_ind, d_val, d_x, epi);
+  if (p->bulk_ok && ((reinterpret_cast<uintptr_t>(d_ind) | reinterpret_cast<uintptr_t>(d_val)) & 15) == 0)
+    spmv_bulk_kernel<<<p->bulk_grid, pyn::SB_BLK, sizeof(pyn::SbSmem), pyn::as_stream(stream)>>>(pyn::view_of(p), d_ind, d_val,
+                                                                                                d_x, epi);
+  else
+    spmv_stream_kernel<<<p->grid, pyn::SP_BLK, 0, pyn::as_stream(stream)>>>(pyn::view_of(p), d_ind, d_val, d_x, epi);
   PYN_CHECK_LAUNCH();
   return PYN_OK;
 }

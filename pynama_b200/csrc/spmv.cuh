@@ -57,6 +57,7 @@ struct SpmvPlanView {
   int64_t nrows, nnz;
   const int64_t* ptr;
   const int* blk_row;  // [nblk+1] first row of each chunk
+  const long long* blk_p0;   // [nblk+1] ptr[blk_row[b]]: first non-zero of each chunk (bulk-copy producer)
   int nblk;
 };
 
@@ -127,16 +128,172 @@ __device__ __forceinline__ void spmv_stream_chunk(const SpmvPlanView& P, const i
 
 }  // namespace pyn
 
+// ---------------------------------------------------------------------------------------------------------------
+// "CSR-stream, bulk copy": the same chunks, the same products and the same row sums as spmv_stream_chunk (bit-identical
+// results), but the value / index / row-pointer slices of a chunk are brought into shared memory by the TMA unit --
+// 1-D `cp.async.bulk.shared::cluster.global` completing on an mbarrier (UBLKCP in SASS) -- issued by one thread
+// SB_STAGES-1 chunks ahead of the consumers.  The bytes in flight per SM no longer depend on registers or on resident
+// warps (two CTAs keep ~100 kB on the wire), which is what bounded the register-staged kernel at 0.71 of the HBM peak
+// (DESIGN.md section 3).  Products overwrite the staged values in place; the stage is handed back to the producer
+// by the CTA barrier that already separates the row sums of consecutive chunks.
+// ---------------------------------------------------------------------------------------------------------------
+namespace pyn {
+
+constexpr int SB_BLK = 256;
+constexpr int SB_STAGES = 3;
+constexpr int SB_CAP = 2304;      // non-zeros per stage (a plan chunk is <= 2048 by construction when rows are < 1 k long)
+constexpr int SB_RCAP = 512;      // row pointers staged per chunk (more rows in a chunk: read from global)
+
+struct SbStage {
+  double val[SB_CAP + 2];               // 16-byte aligned superset of the chunk's values; products in place
+  int ind[SB_CAP + 4];
+  long long ptr[SB_RCAP + 4];           // row pointers r0 .. r0+nr (aligned superset)
+};
+struct SbSmem {
+  SbStage st[SB_STAGES];
+  unsigned long long full[SB_STAGES];   // mbarriers
+  int r0[SB_STAGES], nr[SB_STAGES], cnt[SB_STAGES], vo[SB_STAGES], io[SB_STAGES], po[SB_STAGES];
+  long long p0[SB_STAGES];
+};
+
+__device__ __forceinline__ unsigned smem_addr(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned bytes, unsigned long long* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_addr(dst)),
+               "l"(src), "r"(bytes), "r"(smem_addr(bar))
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity) {
+  unsigned ok;
+  do {
+    asm volatile(
+        "{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+        : "=r"(ok)
+        : "r"(smem_addr(bar)), "r"(parity)
+        : "memory");
+  } while (!ok);
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// producer side (one thread): describe chunk b in stage s and start its three bulk copies
+__device__ __forceinline__ void sb_issue(const SpmvPlanView& P, const int* __restrict__ ind, const double* __restrict__ val,
+                                         int b, SbSmem& sm, int s) {
+  const int r0 = P.blk_row[b], r1 = P.blk_row[b + 1];
+  const long long p0 = P.blk_p0[b], p1 = P.blk_p0[b + 1];
+  const int nr = r1 - r0, cnt = (int)(p1 - p0);
+  sm.r0[s] = r0; sm.nr[s] = nr; sm.cnt[s] = cnt; sm.p0[s] = p0;
+  unsigned bytes = 0;
+  if (nr > 0 && cnt > 0) {
+    // aligned supersets: 16-byte boundaries of the global arrays (all three are 16-byte aligned allocations); the
+    // over-read at the upper end stays inside the arrays except in the last chunk, which the caller keeps off this path
+    const long long va = p0 & ~1ll, ve = (p1 + 1) & ~1ll;
+    const long long ia = p0 & ~3ll, ie = (p1 + 3) & ~3ll;
+    sm.vo[s] = (int)(p0 - va); sm.io[s] = (int)(p0 - ia);
+    const unsigned vb = (unsigned)(ve - va) * 8u, ib = (unsigned)(ie - ia) * 4u;
+    unsigned pb = 0;
+    if (nr <= SB_RCAP) {
+      const long long ra = r0 & ~1ll, re = ((long long)r1 + 2) & ~1ll;   // rows r0 .. r1 inclusive
+      sm.po[s] = (int)(r0 - ra);
+      pb = (unsigned)(re - ra) * 8u;
+    }
+    bytes = vb + ib + pb;
+    mbar_expect_tx(&sm.full[s], bytes);
+    bulk_g2s(sm.st[s].val, val + va, vb, &sm.full[s]);
+    bulk_g2s(sm.st[s].ind, ind + ia, ib, &sm.full[s]);
+    if (pb) bulk_g2s(sm.st[s].ptr, P.ptr + (r0 & ~1ll), pb, &sm.full[s]);
+  } else {
+    mbar_expect_tx(&sm.full[s], 0);
+  }
+}
+
+// All chunks of this CTA (b = first, first + stride, ...).  epi(row, sum) once per row from exactly one thread.
+// Requires: every chunk holds <= SB_CAP non-zeros (plan->bulk_ok) and the last chunk of the matrix is excluded
+// (nblk_bulk = nblk - 1: its aligned over-read could leave the arrays).
+template <class Epi>
+__device__ __forceinline__ void spmv_bulk_loop(const SpmvPlanView& P, const int* __restrict__ ind,
+                                               const double* __restrict__ val, const double* __restrict__ x, int first,
+                                               int stride, int nblk_bulk, SbSmem& sm, Epi&& epi) {
+  const int tid = threadIdx.x;
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < SB_STAGES; ++s) mbar_init(&sm.full[s], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  const int nmine = first < nblk_bulk ? (nblk_bulk - first + stride - 1) / stride : 0;
+  if (tid == 0)
+    for (int i = 0; i < SB_STAGES - 1 && i < nmine; ++i) sb_issue(P, ind, val, first + i * stride, sm, i);
+  for (int i = 0; i < nmine; ++i) {
+    const int s = i % SB_STAGES;
+    if (tid == 0 && i + SB_STAGES - 1 < nmine) {
+      fence_proxy_async();   // the stage was last touched by generic-proxy stores (products of chunk i - 1)
+      sb_issue(P, ind, val, first + (i + SB_STAGES - 1) * stride, sm, (i + SB_STAGES - 1) % SB_STAGES);
+    }
+    mbar_wait(&sm.full[s], (unsigned)((i / SB_STAGES) & 1));
+    const int nr = sm.nr[s], cnt = sm.cnt[s], r0 = sm.r0[s];
+    if (nr > 0 && cnt > 0) {
+      double* pv = sm.st[s].val + sm.vo[s];
+      const int* pi = sm.st[s].ind + sm.io[s];
+      for (int base = 0; base < cnt; base += SP_U * SB_BLK) {   // SP_U independent gathers of x in flight per thread
+        double vv[SP_U];
+        int cc[SP_U];
+#pragma unroll
+        for (int u = 0; u < SP_U; ++u) {
+          const int k = base + u * SB_BLK + tid;
+          const bool ok = k < cnt;
+          cc[u] = ok ? pi[k] : -1;
+          vv[u] = ok ? pv[k] : 0.0;
+        }
+#pragma unroll
+        for (int u = 0; u < SP_U; ++u)
+          if (cc[u] >= 0) vv[u] *= x[cc[u]];
+#pragma unroll
+        for (int u = 0; u < SP_U; ++u)
+          if (cc[u] >= 0) pv[base + u * SB_BLK + tid] = vv[u];
+      }
+      __syncthreads();
+      const bool staged = nr <= SB_RCAP;
+      const long long* pp = sm.st[s].ptr + sm.po[s];
+      const long long p0 = sm.p0[s];
+      int lpr = 32;
+      while (lpr > 1 && lpr * nr > SB_BLK) lpr >>= 1;
+      const int rpp = SB_BLK / lpr, sub = tid & (lpr - 1), slot = tid / lpr;
+      for (int rb = 0; rb < nr; rb += rpp) {
+        const int r = rb + slot;
+        const bool active = r < nr;
+        double acc = 0.0;
+        if (active) {
+          const int lo = (int)((staged ? pp[r] : P.ptr[r0 + r]) - p0);
+          const int hi = (int)((staged ? pp[r + 1] : P.ptr[r0 + r + 1]) - p0);
+          for (int j = lo + sub; j < hi; j += lpr) acc += pv[j];
+        }
+        for (int o = lpr >> 1; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o, lpr);
+        if (active && sub == 0) epi((int64_t)r0 + r, acc);
+      }
+    }
+    __syncthreads();   // every thread is done with stage s: the producer may refill it
+  }
+}
+
+}  // namespace pyn
+
 struct pyn_spmv_plan {
   int64_t nrows, nnz;
   const int64_t* ptr;  // borrowed
   int* blk_row;
+  long long* blk_p0;
   int nblk, chunk, grid;
+  int bulk_ok, bulk_grid;   // every chunk fits a bulk stage; persistent grid of the bulk-copy kernels
 };
 namespace pyn {
 static inline SpmvPlanView view_of(const pyn_spmv_plan* p) {
   SpmvPlanView v;
-  v.nrows = p->nrows; v.nnz = p->nnz; v.ptr = p->ptr; v.blk_row = p->blk_row; v.nblk = p->nblk;
+  v.nrows = p->nrows; v.nnz = p->nnz; v.ptr = p->ptr; v.blk_row = p->blk_row; v.blk_p0 = p->blk_p0; v.nblk = p->nblk;
   return v;
 }
 }  // namespace pyn

@@ -16,7 +16,7 @@ post-assembly loops; the assembly kernel evaluates it for the whole mesh in one 
 import numpy as np
 
 from .. import backend as be
-from .mat_generator import FREE, SET, TANGENT, Mat, rowClasses, templatesWanted
+from .mat_generator import FREE, SET, TANGENT, Mat, fusedWanted, rowClasses, templatesWanted
 
 # name: (cdof, element matrix, kept (row class, column class) pairs, classes whose diagonal entry is stored,
 #        value added on that diagonal per class, sign)
@@ -116,7 +116,8 @@ class MatNS(Mat):
         self.prepareBoundaryMaps(dom, classes, rowClassesDev)
         if corners is None:
             corners = dom.deviceTemplateCorners()
-        Ke, Rwe, Rde = elemType.getElemKLEMatricesDevice(corners, want_rd=True)
+        # cell 0 of a box mesh is a rectangle: closed-form element matrices (unless -mat_fused 0)
+        Ke, Rwe, Rde = elemType.getElemKLEMatricesDevice(corners, want_rd=True, affine=fusedWanted())
         E = {"K": Ke, "Rw": Rwe, "Rd": Rde}
         with be.assembly_batch(topo):     # boundary-list kernels of all matrices overlap the interior streams
             for name in (names or NS_DESCRIPTORS):

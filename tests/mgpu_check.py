@@ -97,6 +97,9 @@ def main():
     assert rel(vals, vel_o[dofs]) < 1e-10, rel(vals, vel_o[dofs])
     l2g2 = (part.local_to_global()[:, None] * 2 + np.arange(2)).reshape(-1)
     assert rel(fem.vel.getArray(), vel_o[l2g2]) < 1e-10, "ghost entries of the solution are not the owners' values"
+    if os.environ.get("MGPU_DUMP"):        # peer-memory path vs NCCL path: compared by tests/test_multigpu.py
+        np.save(f"{os.environ['MGPU_DUMP']}.{rank}.npy", np.concatenate([[fem.solver.its, fem.solverFS.its],
+                                                                          fem.vel.getArray()]))
     f = fem.vort.duplicate()
     fem.evalRHS(fem.ts, 0.0, w, f)
     f_o = o.eval_rhs_from_vel(ops, vel_o, fem.rho, fem.mu)
@@ -168,7 +171,7 @@ def main():
     assert rel(vals, w_ex[dofs]) < 0.05
     torch.cuda.synchronize()
     dist.barrier()
-    print(f"MGPU_OK {rank} (halo bytes/exchange vel: {dc.halo_bytes(2)})", flush=True)
+    print(f"MGPU_OK {rank} (halo bytes/exchange vel: {dc.halo_bytes(2)}, peer_memory={dc.peer_memory})", flush=True)
     sys.stdout.flush()
     # leave without running destructors: NCCL communicators captured in CUDA graphs are not torn down rank by rank
     os._exit(0)

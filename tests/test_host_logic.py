@@ -236,3 +236,30 @@ def test_oracle_cavity_stored_entry_counts(nx):
     for name, cnt in brute.items():
         assert mats[name].nnz == cnt, (name, mats[name].nnz, cnt)
     assert (mats["Rw"].nnz, mats["Rwfs"].nnz) == SURVEY_RW_COUNTS[nx]
+
+
+def test_multigrid_level_sequence_and_oracle_cycle():
+    """`-pc_type mg`: the product's level sequence equals the oracle's, and the oracle's restated V-cycle
+    is a symmetric preconditioner under which CG reproduces the direct solve in a fraction of Jacobi's iterations."""
+    import kle_oracle as o
+    from pynama_b200.solver.multigrid import coarsening_sequence
+    for args in ((1024, 1024, 5, 1024), (32, 32, 5, 64), (30, 30, 3, 64), (707, 707, 5, 1024), (8, 9, 3, 16), (6, 8, 4, 1024)):
+        assert coarsening_sequence(*args) == o.mg_coarsening_sequence(*args)
+    assert coarsening_sequence(1024, 1024, 5) == [(1024, 1024, 5), (1024, 1024, 3), (1024, 1024, 2), (512, 512, 2),
+                                                  (256, 256, 2), (128, 128, 2), (64, 64, 2), (32, 32, 2)]
+    nx, n = 12, 4
+    m = o.BoxMesh([nx, nx], [0, 0], [1, 1], n)
+    mats = o.assemble_noslip(m)
+    for kind in ("K", "KFS"):
+        A = mats["K"] if kind == "K" else o.mat_add(mats["K"], mats["Kfs"])
+        pc = o.MultigridPC(nx, nx, n, kind, coarse_cells=16)
+        rng = np.random.default_rng(4)
+        r, s = rng.standard_normal(A.shape[0]), rng.standard_normal(A.shape[0])
+        a, b = pc(r) @ s, pc(s) @ r
+        assert abs(a - b) < 1e-10 * max(abs(a), abs(b)) and pc(r) @ r > 0
+        rhs = rng.standard_normal(A.shape[0])
+        x, its, reason, _ = o.ksp_cg_jacobi(A, rhs, rtol=1e-12, pc=pc)
+        _, its_j, _, _ = o.ksp_cg_jacobi(A, rhs, rtol=1e-12)
+        assert reason == 2 and its * 4 < its_j
+        xd = o.direct_solve(A, rhs)
+        assert np.abs(x - xd).max() < 1e-9 * np.abs(xd).max()
