@@ -370,6 +370,78 @@ class BoxMesh:
 
 
 # --------------------------------------------------------------------------------------------------------
+# 8f-2  unstructured quadrilateral mesh (gmsh): the numbering rule of pynama_b200/domain/quadmesh.py restated
+# (DMPlex createFromCellList + interpolation + setFemIndexing, src/domain/dmplex.py:22-23,42-61; PETSc-internal and
+# un-pinned by any reference test: "parity unpinned")
+# --------------------------------------------------------------------------------------------------------
+class QuadMesh:
+    """points [nv,2], quads [nc,4] (0-based, any orientation).  Same surface as BoxMesh for the assembly functions."""
+
+    def __init__(self, points, quads, ngl):
+        self.points = np.asarray(points, float)
+        q = np.array(quads, dtype=np.int64)
+        for c in range(len(q)):                      # counter-clockwise cells
+            p = self.points[q[c]]
+            if (p[1, 0] - p[0, 0]) * (p[2, 1] - p[0, 1]) - (p[1, 1] - p[0, 1]) * (p[2, 0] - p[0, 0]) < 0:
+                q[c] = q[c][::-1]
+        self.quads, self.ngl = q, int(ngl)
+        self.ncell, self.nvert = len(q), len(self.points)
+        edge_id, self.edges, self.cell_edges, self.cell_rev, count = {}, [], [], [], []
+        for c in range(self.ncell):                  # edges in order of first appearance: sides v0v1, v1v2, v2v3, v3v0
+            ce, cr = [], []
+            for i in range(4):
+                a, b = int(q[c, i]), int(q[c, (i + 1) % 4])
+                key = (min(a, b), max(a, b))
+                if key not in edge_id:
+                    edge_id[key] = len(self.edges)
+                    self.edges.append((a, b))
+                    count.append(0)
+                e = edge_id[key]
+                count[e] += 1
+                ce.append(e)
+                cr.append(self.edges[e][0] != a)
+            self.cell_edges.append(ce)
+            self.cell_rev.append(cr)
+        self.edge_count = np.array(count)
+        m = self.ngl - 2
+        self.off_vert = self.ncell * m * m
+        self.off_edge = self.off_vert + self.nvert
+        self.nnodes = self.off_edge + len(self.edges) * m
+
+    def cell_corner_coords(self, cells=None):
+        cells = np.arange(self.ncell) if cells is None else np.asarray(cells)
+        return self.points[self.quads[cells]]
+
+    def cell_nodes(self, cells=None):
+        cells = np.arange(self.ncell) if cells is None else np.asarray(cells)
+        m = self.ngl - 2
+        out = []
+        for c in cells:
+            row = [self.off_vert + int(v) for v in self.quads[c]]
+            for i in range(4):
+                ks = range(m - 1, -1, -1) if self.cell_rev[c][i] else range(m)
+                row += [self.off_edge + self.cell_edges[c][i] * m + k for k in ks]
+            row += [int(c) * m * m + k for k in range(m * m)]
+            out.append(row)
+        return np.array(out, dtype=np.int64)
+
+    def node_coords(self):
+        t = tables(self.ngl)
+        xy = np.einsum("kc,ecd->ekd", t.coo_op.H, self.cell_corner_coords())
+        out = np.zeros((self.nnodes, 2))
+        out[self.cell_nodes().reshape(-1)] = xy.reshape(-1, 2)
+        return out
+
+    def boundary_nodes(self):
+        m = self.ngl - 2
+        nodes = []
+        for e in np.flatnonzero(self.edge_count == 1):
+            a, b = self.edges[e]
+            nodes += [self.off_vert + a, self.off_vert + b] + [self.off_edge + e * m + k for k in range(m)]
+        return np.unique(np.array(nodes, dtype=np.int64))
+
+
+# --------------------------------------------------------------------------------------------------------
 # deterministic COO -> CSR (PETSc MatSetValues(ADD_VALUES)+MatAssembly semantics, serial)
 # --------------------------------------------------------------------------------------------------------
 def coo_to_csr(rows, cols, vals, shape):
@@ -518,9 +590,12 @@ def mat_add(A, B):
 # --------------------------------------------------------------------------------------------------------
 # A3  buildOperators / Operators.assembleAll      base_problem.py:132-140, mat_generator.py:157-190
 # --------------------------------------------------------------------------------------------------------
-def assemble_operators(mesh):
+def assemble_operators(mesh, per_cell=False):
+    """per_cell=False: cell 0's element operators for every cell, as the reference does (base_problem.py:133-137);
+    per_cell=True: every cell's own -- what a non-uniform mesh needs."""
     nodes = mesh.cell_nodes()
-    SrTe, Dive, Curle, We = elem_kle_operators(mesh.ngl, mesh.cell_corner_coords([0]))   # cell 0 only (:133)
+    cc = mesh.cell_corner_coords() if per_cell else mesh.cell_corner_coords([0])
+    SrTe, Dive, Curle, We = elem_kle_operators(mesh.ngl, cc)
     N = mesh.nnodes
     v, w, s = _expand(nodes, 2), nodes, _expand(nodes, 3)
     tv, tw, ts = np.ones_like(v, bool), np.ones_like(w, bool), np.ones_like(s, bool)
@@ -529,7 +604,7 @@ def assemble_operators(mesh):
     Div = coo_to_csr(*_block_coo(v, s, Dive, tv, ts), (2 * N, 3 * N))
     W = np.zeros(N)
     for e in range(nodes.shape[0]):                 # VecSetValues(ADD) in cell order (mat_generator.py:168-170)
-        W[nodes[e]] += We[0]
+        W[nodes[e]] += We[e if per_cell else 0]
     rW = 1.0 / W                                    # VecReciprocal (:175,180,185)
 
     def lscale(M, ncomp):

@@ -96,7 +96,12 @@ class BaseProblem(object):
             else:
                 self.dom = DMPlexDom(boxMesh=domain.get('box-mesh'), **self.opts)
         elif "gmsh-file" in domain:
-            raise Exception("gmsh meshes are outside the B200 hot path (SURVEY.md 8f item 2)")
+            # unstructured quadrilaterals (the reference's createFromFile, src/domain/dmplex.py:22-23)
+            from ..domain.quadmesh import QuadMeshDom
+            if self.comm.size > 1:
+                raise Exception("gmsh meshes run on one GPU (the strip partition needs a box mesh)")
+            self.meshType = "gmsh"
+            self.dom = QuadMeshDom(fileName=domain["gmsh-file"], comm=None)
         self.dim = self.dom.getDimension()
         self.dim_w = 1 if self.dim == 2 else 3
         self.dim_s = 3 if self.dim == 2 else 6
@@ -136,6 +141,9 @@ class BaseProblem(object):
             self.nelem = domain['box-mesh']['nelem']
             self.lower = domain['box-mesh']['lower']
             self.upper = domain['box-mesh']['upper']
+        elif "gmsh-file" in domain:
+            self.nelem = [0, 0]            # 2-D; the cell count comes from the file
+            self.lower = self.upper = None
         else:
             raise Exception("No Gmsh Implemented")
         self.dim = len(self.nelem)

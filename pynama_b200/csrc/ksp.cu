@@ -184,8 +184,9 @@ cg_spmv_dot_kernel(pyn::SpmvPlanView P, const int* __restrict__ ind, const doubl
   if (threadIdx.x == 0) B.part_a[blockIdx.x] = dot;
 }
 
-// bulk-copy (TMA) variant of the same kernel: spmv.cuh spmv_bulk_loop
-__global__ void __launch_bounds__(pyn::SB_BLK, 2)
+// bulk-copy (TMA) variant of the same kernel: spmv.cuh spmv_bulk_loop; partial gridDim.x - ... see enqueue_cg_product:
+// the last chunk of the matrix is summed by cg_spmv_dot_tail_kernel into the partial after the bulk grid's
+__global__ void __launch_bounds__(pyn::SB_THREADS, 2)
 cg_spmv_dot_bulk_kernel(pyn::SpmvPlanView P, const int* __restrict__ ind, const double* __restrict__ val, CgBuffers B) {
   extern __shared__ __align__(16) unsigned char sb_raw[];
   __shared__ double red[pyn::SB_BLK / 32];
@@ -194,12 +195,29 @@ cg_spmv_dot_bulk_kernel(pyn::SpmvPlanView P, const int* __restrict__ ind, const 
   double dot = 0.0;
   CgDotEpi epi{B.w, B.p, &dot};
   pyn::spmv_bulk_loop(P, ind, val, B.p, blockIdx.x, gridDim.x, P.nblk - 1, sm, epi);
-  if (blockIdx.x == gridDim.x - 1) {
-    pyn::SpmvSmem& old = *reinterpret_cast<pyn::SpmvSmem*>(sb_raw);
-    pyn::spmv_stream_chunk(P, ind, val, B.p, P.nblk - 1, old, epi);
+  if (threadIdx.x >= pyn::SB_BLK) return;             // producer warp
+  // consumer warps only: named barrier over the 256 consumer threads
+  dot = pyn::warp_sum(dot);
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  if (lane == 0) red[w] = dot;
+  asm volatile("bar.sync 1, %0;" ::"n"(pyn::SB_BLK) : "memory");
+  if (w == 0) {
+    double r = (lane < pyn::SB_BLK / 32) ? red[lane] : 0.0;
+    r = pyn::warp_sum(r);
+    if (lane == 0) B.part_a[blockIdx.x] = r;
   }
-  dot = pyn::block_sum<pyn::SB_BLK>(dot, red);
-  if (threadIdx.x == 0) B.part_a[blockIdx.x] = dot;
+}
+__global__ void __launch_bounds__(pyn::SP_BLK)
+cg_spmv_dot_tail_kernel(pyn::SpmvPlanView P, const int* __restrict__ ind, const double* __restrict__ val, CgBuffers B,
+                        int slot) {
+  __shared__ pyn::SpmvSmem sm;
+  __shared__ double red[pyn::SP_BLK / 32];
+  if (B.st->done) return;
+  double dot = 0.0;
+  CgDotEpi epi{B.w, B.p, &dot};
+  pyn::spmv_stream_chunk(P, ind, val, B.p, P.nblk - 1, sm, epi);
+  dot = pyn::block_sum<pyn::SP_BLK>(dot, red);
+  if (threadIdx.x == 0) B.part_a[slot] = dot;
 }
 
 // the same product through the element operator (tmat.cuh): phase 1 is pyn::tmat_apply on p; here phase 2 (gather
@@ -422,8 +440,10 @@ int enqueue_cg_product(const pyn_ksp* k, cudaStream_t st, int* npw_out) {
     else cg_tmat_interior_kernel<3><<<gi, 256, 0, st>>>(tv, k->B);
     npw = gi;
   } else if (k->bulk) {
-    npw = k->plan->bulk_grid;
-    cg_spmv_dot_bulk_kernel<<<npw, pyn::SB_BLK, sizeof(pyn::SbSmem), st>>>(pyn::view_of(k->plan), k->ind, k->val, k->B);
+    const int g = k->plan->bulk_grid;
+    cg_spmv_dot_bulk_kernel<<<g, pyn::SB_THREADS, sizeof(pyn::SbSmem), st>>>(pyn::view_of(k->plan), k->ind, k->val, k->B);
+    cg_spmv_dot_tail_kernel<<<1, pyn::SP_BLK, 0, st>>>(pyn::view_of(k->plan), k->ind, k->val, k->B, g);
+    npw = g + 1;
   } else {
     cg_spmv_dot_kernel<<<k->sgrid, pyn::SP_BLK, 0, st>>>(pyn::view_of(k->plan), k->ind, k->val, k->B);
   }
@@ -490,7 +510,7 @@ int pyn_ksp_create(int64_t nrows, const int64_t* d_ptr, const int32_t* d_ind, co
   }
   double* pool = nullptr;
   size_t nparts = (size_t)(k->vgrid > k->sgrid ? k->vgrid : k->sgrid);
-  if (nparts < (size_t)k->plan->bulk_grid) nparts = (size_t)k->plan->bulk_grid;
+  if (nparts < (size_t)k->plan->bulk_grid + 1) nparts = (size_t)k->plan->bulk_grid + 1;
   if (nparts < (size_t)pyn::sm_count() * 16) nparts = (size_t)pyn::sm_count() * 16;   // room for the template operator's grids
   const size_t ld = ((size_t)nrows + 1) & ~(size_t)1;   // even stride: every work vector stays 16-byte aligned
   PYN_CHECK_CUDA(cudaMalloc(&pool, sizeof(double) * (6 * ld + 4 * nparts)));

@@ -80,17 +80,20 @@ spmv_stream_kernel(pyn::SpmvPlanView P, const int* __restrict__ ind, const doubl
   for (int b = blockIdx.x; b < P.nblk; b += gridDim.x) pyn::spmv_stream_chunk(P, ind, val, x, b, sm, epi);
 }
 
-// bulk-copy variant (spmv.cuh): all chunks but the last through the TMA pipeline, the last through the register path
-__global__ void __launch_bounds__(pyn::SB_BLK, 2)
+// bulk-copy variant (spmv.cuh): all chunks but the last through the TMA pipeline; the last chunk (whose aligned
+// over-read could leave the arrays) goes through the register path in a one-CTA launch of spmv_tail_kernel
+__global__ void __launch_bounds__(pyn::SB_THREADS, 2)
 spmv_bulk_kernel(pyn::SpmvPlanView P, const int* __restrict__ ind, const double* __restrict__ val,
                  const double* __restrict__ x, ModeEpi epi) {
   extern __shared__ __align__(16) unsigned char sb_raw[];
   pyn::SbSmem& sm = *reinterpret_cast<pyn::SbSmem*>(sb_raw);
   pyn::spmv_bulk_loop(P, ind, val, x, blockIdx.x, gridDim.x, P.nblk - 1, sm, epi);
-  if (blockIdx.x == gridDim.x - 1) {
-    pyn::SpmvSmem& old = *reinterpret_cast<pyn::SpmvSmem*>(sb_raw);   // the pipeline is drained: reuse its memory
-    pyn::spmv_stream_chunk(P, ind, val, x, P.nblk - 1, old, epi);
-  }
+}
+__global__ void __launch_bounds__(pyn::SP_BLK)
+spmv_tail_kernel(pyn::SpmvPlanView P, const int* __restrict__ ind, const double* __restrict__ val,
+                 const double* __restrict__ x, ModeEpi epi) {
+  __shared__ pyn::SpmvSmem sm;
+  pyn::spmv_stream_chunk(P, ind, val, x, P.nblk - 1, sm, epi);
 }
 
 __global__ void plan_p0_kernel(int nblk, const int64_t* __restrict__ ptr, const int* __restrict__ blk_row,
@@ -170,7 +173,7 @@ extern "C" int pyn_spmv_plan_create(int64_t nrows, const int64_t* d_ptr, int64_t
     p->bulk_ok = !big && !off && p->nblk >= 2 && (reinterpret_cast<uintptr_t>(d_ptr) & 15) == 0;
     PYN_CHECK_CUDA(cudaFuncSetAttribute(spmv_bulk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(pyn::SbSmem)));
     int occb = 0;
-    PYN_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occb, spmv_bulk_kernel, pyn::SB_BLK, sizeof(pyn::SbSmem)));
+    PYN_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occb, spmv_bulk_kernel, pyn::SB_THREADS, sizeof(pyn::SbSmem)));
     const int64_t capb = (int64_t)pyn::sm_count() * (occb > 0 ? occb : 1);
     p->bulk_grid = (int)(nb < capb ? nb : capb);
   }
@@ -198,10 +201,12 @@ extern "C" int pyn_spmv_planned(const pyn_spmv_plan* p, const int32_t* d_ind, co
   PYN_REQUIRE(mode != PYN_SPMV_SRT_VTENSV || (d_aux != nullptr && p->nrows % 3 == 0),
               "SRT_VTENSV needs aux and 3 rows per node");
   ModeEpi epi{d_y, mode, p0, p1, d_aux};
-  if (p->bulk_ok && ((reinterpret_cast<uintptr_t>(d_ind) | reinterpret_cast<uintptr_t>(d_val)) & 15) == 0)
-    spmv_bulk_kernel<<<p->bulk_grid, pyn::SB_BLK, sizeof(pyn::SbSmem), pyn::as_stream(stream)>>>(pyn::view_of(p), d_ind, d_val,
-                                                                                                d_x, epi);
-  else
+  if (p->bulk_ok && ((reinterpret_cast<uintptr_t>(d_ind) | reinterpret_cast<uintptr_t>(d_val)) & 15) == 0) {
+    spmv_bulk_kernel<<<p->bulk_grid, pyn::SB_THREADS, sizeof(pyn::SbSmem), pyn::as_stream(stream)>>>(pyn::view_of(p), d_ind,
+                                                                                                    d_val, d_x, epi);
+    pyn::count_launch();
+    spmv_tail_kernel<<<1, pyn::SP_BLK, 0, pyn::as_stream(stream)>>>(pyn::view_of(p), d_ind, d_val, d_x, epi);
+  } else
     spmv_stream_kernel<<<p->grid, pyn::SP_BLK, 0, pyn::as_stream(stream)>>>(pyn::view_of(p), d_ind, d_val, d_x, epi);
   PYN_CHECK_LAUNCH();
   return PYN_OK;

@@ -151,7 +151,8 @@ struct SbStage {
 };
 struct SbSmem {
   SbStage st[SB_STAGES];
-  unsigned long long full[SB_STAGES];   // mbarriers
+  unsigned long long full[SB_STAGES];
+  unsigned long long empty[SB_STAGES];   // mbarriers: bytes landed / all consumer warps done
   int r0[SB_STAGES], nr[SB_STAGES], cnt[SB_STAGES], vo[SB_STAGES], io[SB_STAGES], po[SB_STAGES];
   long long p0[SB_STAGES];
 };
@@ -177,6 +178,9 @@ __device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned pari
         : "r"(smem_addr(bar)), "r"(parity)
         : "memory");
   } while (!ok);
+}
+__device__ __forceinline__ void mbar_arrive(unsigned long long* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_addr(bar)) : "memory");
 }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
@@ -214,6 +218,15 @@ __device__ __forceinline__ void sb_issue(const SpmvPlanView& P, const int* __res
 // All chunks of this CTA (b = first, first + stride, ...).  epi(row, sum) once per row from exactly one thread.
 // Requires: every chunk holds <= SB_CAP non-zeros (plan->bulk_ok) and the last chunk of the matrix is excluded
 // (nblk_bulk = nblk - 1: its aligned over-read could leave the arrays).
+//
+// SB_BLK consumer threads + one producer warp (launch with SB_THREADS).  The pipeline is warp-asynchronous: a consumer
+// warp waits for a stage to be full, takes an eighth of the chunk's rows -- a contiguous range of entries --, forms the
+// products of that range in place (every x gather independent, SP_U per lane in flight), sums its rows with the
+// sub-warp width spmv_stream_chunk would use for the chunk (same order of additions: bit-identical results), arrives
+// on the stage's `empty` barrier and moves on; the producer refills a stage as soon as all eight warps have left it.
+// No CTA-wide barrier inside the loop.
+constexpr int SB_THREADS = SB_BLK + 32;
+
 template <class Epi>
 __device__ __forceinline__ void spmv_bulk_loop(const SpmvPlanView& P, const int* __restrict__ ind,
                                                const double* __restrict__ val, const double* __restrict__ x, int first,
@@ -221,62 +234,79 @@ __device__ __forceinline__ void spmv_bulk_loop(const SpmvPlanView& P, const int*
   const int tid = threadIdx.x;
   if (tid == 0) {
 #pragma unroll
-    for (int s = 0; s < SB_STAGES; ++s) mbar_init(&sm.full[s], 1);
+    for (int s = 0; s < SB_STAGES; ++s) {
+      mbar_init(&sm.full[s], 1);
+      mbar_init(&sm.empty[s], SB_BLK / 32);
+    }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
   const int nmine = first < nblk_bulk ? (nblk_bulk - first + stride - 1) / stride : 0;
-  if (tid == 0)
-    for (int i = 0; i < SB_STAGES - 1 && i < nmine; ++i) sb_issue(P, ind, val, first + i * stride, sm, i);
+  if (tid >= SB_BLK) {   // ---- producer warp (one lane issues) ----
+    if (tid == SB_BLK) {
+      for (int i = 0; i < nmine; ++i) {
+        const int s = i % SB_STAGES;
+        if (i >= SB_STAGES) mbar_wait(&sm.empty[s], (unsigned)(((i / SB_STAGES) - 1) & 1));
+        sb_issue(P, ind, val, first + i * stride, sm, s);
+      }
+    }
+    return;
+  }
+  const int lane = tid & 31, w = tid >> 5;
+  constexpr int NW = SB_BLK / 32;
   for (int i = 0; i < nmine; ++i) {
     const int s = i % SB_STAGES;
-    if (tid == 0 && i + SB_STAGES - 1 < nmine) {
-      fence_proxy_async();   // the stage was last touched by generic-proxy stores (products of chunk i - 1)
-      sb_issue(P, ind, val, first + (i + SB_STAGES - 1) * stride, sm, (i + SB_STAGES - 1) % SB_STAGES);
-    }
     mbar_wait(&sm.full[s], (unsigned)((i / SB_STAGES) & 1));
     const int nr = sm.nr[s], cnt = sm.cnt[s], r0 = sm.r0[s];
     if (nr > 0 && cnt > 0) {
       double* pv = sm.st[s].val + sm.vo[s];
       const int* pi = sm.st[s].ind + sm.io[s];
-      for (int base = 0; base < cnt; base += SP_U * SB_BLK) {   // SP_U independent gathers of x in flight per thread
-        double vv[SP_U];
-        int cc[SP_U];
-#pragma unroll
-        for (int u = 0; u < SP_U; ++u) {
-          const int k = base + u * SB_BLK + tid;
-          const bool ok = k < cnt;
-          cc[u] = ok ? pi[k] : -1;
-          vv[u] = ok ? pv[k] : 0.0;
-        }
-#pragma unroll
-        for (int u = 0; u < SP_U; ++u)
-          if (cc[u] >= 0) vv[u] *= x[cc[u]];
-#pragma unroll
-        for (int u = 0; u < SP_U; ++u)
-          if (cc[u] >= 0) pv[base + u * SB_BLK + tid] = vv[u];
-      }
-      __syncthreads();
       const bool staged = nr <= SB_RCAP;
       const long long* pp = sm.st[s].ptr + sm.po[s];
       const long long p0 = sm.p0[s];
-      int lpr = 32;
-      while (lpr > 1 && lpr * nr > SB_BLK) lpr >>= 1;
-      const int rpp = SB_BLK / lpr, sub = tid & (lpr - 1), slot = tid / lpr;
-      for (int rb = 0; rb < nr; rb += rpp) {
-        const int r = rb + slot;
-        const bool active = r < nr;
-        double acc = 0.0;
-        if (active) {
-          const int lo = (int)((staged ? pp[r] : P.ptr[r0 + r]) - p0);
-          const int hi = (int)((staged ? pp[r + 1] : P.ptr[r0 + r + 1]) - p0);
-          for (int j = lo + sub; j < hi; j += lpr) acc += pv[j];
+      // this warp's rows [ra, rb) and their (contiguous) entries [ea, eb)
+      const int ra = (w * nr) / NW, rb = ((w + 1) * nr) / NW;
+      if (rb > ra) {
+        const int ea = (int)((staged ? pp[ra] : P.ptr[r0 + ra]) - p0), eb = (int)((staged ? pp[rb] : P.ptr[r0 + rb]) - p0);
+        // products in place: every gather of the warp's range is independent, SP_U per lane in flight
+        for (int base = ea; base < eb; base += SP_U * 32) {
+          double vv[SP_U];
+          int cc[SP_U];
+#pragma unroll
+          for (int u = 0; u < SP_U; ++u) {
+            const int k = base + u * 32 + lane;
+            const bool ok = k < eb;
+            cc[u] = ok ? pi[k] : -1;
+            vv[u] = ok ? pv[k] : 0.0;
+          }
+#pragma unroll
+          for (int u = 0; u < SP_U; ++u)
+            if (cc[u] >= 0) vv[u] = __dmul_rn(vv[u], x[cc[u]]);
+#pragma unroll
+          for (int u = 0; u < SP_U; ++u)
+            if (cc[u] >= 0) pv[base + u * 32 + lane] = vv[u];
         }
-        for (int o = lpr >> 1; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o, lpr);
-        if (active && sub == 0) epi((int64_t)r0 + r, acc);
+        __syncwarp();
+        // row sums with the sub-warp width spmv_stream_chunk uses for a chunk of nr rows (same order of additions)
+        int lpr = 32;
+        while (lpr > 1 && lpr * nr > SB_BLK) lpr >>= 1;
+        const int rpp = 32 / lpr, sub = lane & (lpr - 1), slot = lane / lpr;
+        for (int rr = ra; rr < rb; rr += rpp) {
+          const int r = rr + slot;
+          const bool active = r < rb;
+          double acc = 0.0;
+          if (active) {
+            const int lo = (int)((staged ? pp[r] : P.ptr[r0 + r]) - p0);
+            const int hi = (int)((staged ? pp[r + 1] : P.ptr[r0 + r + 1]) - p0);
+            for (int j = lo + sub; j < hi; j += lpr) acc += pv[j];
+          }
+          for (int o = lpr >> 1; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o, lpr);
+          if (active && sub == 0) epi((int64_t)r0 + r, acc);
+        }
       }
     }
-    __syncthreads();   // every thread is done with stage s: the producer may refill it
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&sm.empty[s]);   // this warp is done with stage s
   }
 }
 

@@ -25,9 +25,15 @@ from .indices import IndicesManager
 
 
 class DMPlexDom(object):
+    def __new__(cls, **kwargs):
+        if 'boxMesh' not in kwargs and 'fileName' in kwargs:       # dmplex.py:22-23: createFromFile
+            from .quadmesh import QuadMeshDom
+            return QuadMeshDom(**kwargs)
+        return super().__new__(cls)
+
     def __init__(self, **kwargs):
         if 'boxMesh' not in kwargs:
-            raise Exception("gmsh meshes are outside the B200 hot path (SURVEY.md 8f item 2): boxMesh required")
+            raise Exception("DMPlexDom needs boxMesh={...} or fileName=<gmsh v2 ASCII file>")
         meshData = kwargs['boxMesh']
         lower = kwargs['lower'] if 'lower' in kwargs else meshData.get('lower')
         upper = kwargs['upper'] if 'upper' in kwargs else meshData.get('upper')
@@ -62,6 +68,10 @@ class DMPlexDom(object):
 
     def getDimension(self):
         return self.dim
+
+    def isUniform(self):
+        """Every cell is a copy of cell 0 (box mesh): one element matrix / operator set serves all cells."""
+        return True
 
     # -- numbering --------------------------------------------------------------------------------------------
     def setFemIndexing(self, ngl):

@@ -249,7 +249,11 @@ class Operators(Mat):
         `self.spmv[...]` always holds zero-squeezed copies, which is what the time loop multiplies with."""
         topo = dom.topology()
         N = dom.getTotalNodes()
-        S, D, C, W = elemType.getElemKLEOperatorsDevice(dom.deviceTemplateCorners())
+        # a non-uniform mesh integrates the operators of every cell (SURVEY 8f-2); a box mesh uses cell 0's for all
+        # cells like the reference (base_problem.py:133-137)
+        perCell = not getattr(dom, "isUniform", lambda: True)()
+        S, D, C, W = elemType.getElemKLEOperatorsDevice(dom.deviceCellCorners(0, None) if perCell
+                                                        else dom.deviceTemplateCorners())
         Wg = be.assemble_weights(topo, W)
         self.weights = Wg
         rW = Wg.reciprocal()

@@ -263,3 +263,34 @@ def test_multigrid_level_sequence_and_oracle_cycle():
         assert reason == 2 and its * 4 < its_j
         xd = o.direct_solve(A, rhs)
         assert np.abs(x - xd).max() < 1e-9 * np.abs(xd).max()
+
+
+def test_gmsh_reader_and_unstructured_numbering(tmp_path):
+    """gmsh v2 ASCII -> QuadMeshDom; numbering equals the oracle's restatement, shared edges are traversed
+    consistently (every cell reproduces the coordinates of the nodes it shares), boundary = one-cell edges."""
+    import kle_oracle as o
+    from quadmesh_util import skewed_square, write_msh
+    from pynama_b200.domain.quadmesh import QuadMeshDom, read_msh
+    from pynama_b200.elements.spectral import Spectral
+    P, Q = skewed_square(6)
+    path = str(tmp_path / "skew.msh")
+    write_msh(path, P, Q)
+    pts, quads = read_msh(path)
+    np.testing.assert_array_equal(pts, P)
+    np.testing.assert_array_equal(quads, Q)
+    for ngl in (2, 3, 5):
+        dom = QuadMeshDom(fileName=path)
+        dom.setFemIndexing(ngl)
+        m = o.QuadMesh(P, Q, ngl)
+        assert dom.getTotalNodes() == m.nnodes == (6 * (ngl - 1) + 1) ** 2
+        np.testing.assert_array_equal(dom.cellNodesArray(), m.cell_nodes())
+        np.testing.assert_array_equal(dom.cellCornersArray(), m.cell_corner_coords())
+        np.testing.assert_array_equal(dom.borderNodesArray(), m.boundary_nodes())
+        assert len(m.boundary_nodes()) == 4 * 6 * (ngl - 1)
+        s = Spectral(ngl, 2)
+        xy_e = np.einsum("kc,ecd->ekd", np.array(s.HCooOp), dom.cellCornersArray())
+        xy = m.node_coords()
+        assert np.abs(xy[dom.cellNodesArray()] - xy_e).max() < 1e-14       # shared nodes: same point from every cell
+        cc = dom.cellCornersArray()                                         # all cells counter-clockwise
+        area2 = (cc[:, 1, 0] - cc[:, 0, 0]) * (cc[:, 2, 1] - cc[:, 0, 1]) - (cc[:, 1, 1] - cc[:, 0, 1]) * (cc[:, 2, 0] - cc[:, 0, 0])
+        assert (area2 > 0).all()
