@@ -42,6 +42,8 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-time-loop", action="store_true", dest="no_time_loop")
+    ap.add_argument("--no-configs4", action="store_true", dest="no_configs4",
+                    help="N >= 4: skip the second record on BASELINE configs[4] (4096^2, ngl 4)")
     ap.add_argument("--workload", default="cavity", choices=["cavity", "percell"],
                     help="cavity: configs[3] (default); percell: FreeSlip, element matrices of every cell (configs[1]/[2])")
     ap.add_argument("--fused", default=None, help="percell: -mat_fused 0|1 (fused integrate+assemble kernel)")
@@ -372,6 +374,14 @@ def run_native(a):
         out["cpu_baseline"] = {"value": dof / wall, "unit": "DOF/s", "cores": cores, "kind": "port",
                                "sample": f"{cores} strips of {a.cpu_nx}x{max(1, a.cpu_nx // cores)} cells ngl {n}, "
                                          f"oracle assemble_noslip, one process per core, {wall:.1f} s"}
+    if world >= 4 and a.nx == 1024 and not a.no_configs4:
+        # the largest mesh of BASELINE.json rides along as a second record inside the one JSON line
+        del prob
+        torch.cuda.empty_cache()
+        try:
+            out["configs4"] = largest_mesh_record(a, be, torch, world, barrier, peak)
+        except Exception as e:      # e.g. not enough memory on this box: say so, keep the configs[3] line
+            out["configs4"] = {"unavailable": f"{type(e).__name__}: {e}"[:300]}
     if rank == 0:
         print(json.dumps(out), flush=True)
     if world > 1:
@@ -630,6 +640,42 @@ def parity_checks(prob, be, torch, world, nx, ngl, dof_total):
             "nnz_K_sum_over_ranks": int(nnz_owned[0]), "nullspace_residual_max_over_ranks": res,
             "nullspace_ok": bool(res < 1e-12),
             "peer_memory": bool(getattr(prob.fem.comm.dist, "peer_memory", False)) if world > 1 else None}
+
+
+def largest_mesh_record(a, be, torch, world, barrier, peak):
+    """BASELINE configs[4] -- 4096 x 4096 elements, ngl 4 (302 M velocity dofs, K = 181 GB: needs >= 4 GPUs) -- measured
+    in the same run as configs[3] when the job has >= 4 ranks: assembly step and CG iteration, same method."""
+    import torch.distributed as dist
+    nx, n = 4096, 4
+    prob = CavityAssembly(nx, n)
+    for _ in range(2):
+        prob.step()
+    barrier()
+    ev = lambda: torch.cuda.Event(enable_timing=True)
+    steps = 3
+    t0, t1 = ev(), ev()
+    t0.record()
+    for _ in range(steps):
+        prob.step()
+    t1.record()
+    barrier()
+    tt = torch.tensor([t0.elapsed_time(t1) / steps, float(prob.dof_owned)], dtype=torch.float64, device="cuda")
+    tmax = tt.clone()
+    dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+    dist.all_reduce(tt, op=dist.ReduceOp.SUM)
+    ms, dof = float(tmax[0]), float(tt[1])
+    ksp = ksp_phase(a, prob, be, torch, peak, barrier)
+    t = torch.tensor([ksp["ms_per_solve"]], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    checks = parity_checks(prob, be, torch, world, nx, n, dof)
+    out = {"workload": f"cavity {nx}x{nx} elements ngl {n} (BASELINE configs[4]), {world} strips",
+           "value": dof / (ms * 1e-3), "unit": "DOF/s", "ms_per_step": ms, "dof_rows": int(dof),
+           "ksp": {"its": ksp["its"], "ms_per_iteration": float(t[0]) / max(ksp["its"], 1), "operator": ksp["operator"],
+                   "csr_stream_ms_per_iteration": ksp["csr_stream"]["ms_per_iteration"]},
+           "parity_checks": checks}
+    del prob
+    torch.cuda.empty_cache()
+    return out
 
 
 def load_traffic(kernel_substr):

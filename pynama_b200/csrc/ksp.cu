@@ -186,7 +186,7 @@ cg_spmv_dot_kernel(pyn::SpmvPlanView P, const int* __restrict__ ind, const doubl
 
 // bulk-copy (TMA) variant of the same kernel: spmv.cuh spmv_bulk_loop; partial gridDim.x - ... see enqueue_cg_product:
 // the last chunk of the matrix is summed by cg_spmv_dot_tail_kernel into the partial after the bulk grid's
-__global__ void __launch_bounds__(pyn::SB_THREADS, 2)
+__global__ void __launch_bounds__(pyn::SB_THREADS, 4)
 cg_spmv_dot_bulk_kernel(pyn::SpmvPlanView P, const int* __restrict__ ind, const double* __restrict__ val, CgBuffers B) {
   extern __shared__ __align__(16) unsigned char sb_raw[];
   __shared__ double red[pyn::SB_BLK / 32];
@@ -194,7 +194,7 @@ cg_spmv_dot_bulk_kernel(pyn::SpmvPlanView P, const int* __restrict__ ind, const 
   pyn::SbSmem& sm = *reinterpret_cast<pyn::SbSmem*>(sb_raw);
   double dot = 0.0;
   CgDotEpi epi{B.w, B.p, &dot};
-  pyn::spmv_bulk_loop(P, ind, val, B.p, blockIdx.x, gridDim.x, P.nblk - 1, sm, epi);
+  pyn::spmv_bulk_loop(P, ind, val, B.p, blockIdx.x, gridDim.x, P.nbblk - 1, sm, epi);
   if (threadIdx.x >= pyn::SB_BLK) return;             // producer warp
   // consumer warps only: named barrier over the 256 consumer threads
   dot = pyn::warp_sum(dot);
@@ -215,7 +215,7 @@ cg_spmv_dot_tail_kernel(pyn::SpmvPlanView P, const int* __restrict__ ind, const 
   if (B.st->done) return;
   double dot = 0.0;
   CgDotEpi epi{B.w, B.p, &dot};
-  pyn::spmv_stream_chunk(P, ind, val, B.p, P.nblk - 1, sm, epi);
+  pyn::spmv_stream_rows(P, ind, val, B.p, P.brow[P.nbblk - 1], P.brow[P.nbblk], sm, epi);
   dot = pyn::block_sum<pyn::SP_BLK>(dot, red);
   if (threadIdx.x == 0) B.part_a[slot] = dot;
 }

@@ -82,18 +82,18 @@ spmv_stream_kernel(pyn::SpmvPlanView P, const int* __restrict__ ind, const doubl
 
 // bulk-copy variant (spmv.cuh): all chunks but the last through the TMA pipeline; the last chunk (whose aligned
 // over-read could leave the arrays) goes through the register path in a one-CTA launch of spmv_tail_kernel
-__global__ void __launch_bounds__(pyn::SB_THREADS, 2)
+__global__ void __launch_bounds__(pyn::SB_THREADS, 4)
 spmv_bulk_kernel(pyn::SpmvPlanView P, const int* __restrict__ ind, const double* __restrict__ val,
                  const double* __restrict__ x, ModeEpi epi) {
   extern __shared__ __align__(16) unsigned char sb_raw[];
   pyn::SbSmem& sm = *reinterpret_cast<pyn::SbSmem*>(sb_raw);
-  pyn::spmv_bulk_loop(P, ind, val, x, blockIdx.x, gridDim.x, P.nblk - 1, sm, epi);
+  pyn::spmv_bulk_loop(P, ind, val, x, blockIdx.x, gridDim.x, P.nbblk - 1, sm, epi);
 }
 __global__ void __launch_bounds__(pyn::SP_BLK)
 spmv_tail_kernel(pyn::SpmvPlanView P, const int* __restrict__ ind, const double* __restrict__ val,
                  const double* __restrict__ x, ModeEpi epi) {
   __shared__ pyn::SpmvSmem sm;
-  pyn::spmv_stream_chunk(P, ind, val, x, P.nblk - 1, sm, epi);
+  pyn::spmv_stream_rows(P, ind, val, x, P.brow[P.nbblk - 1], P.brow[P.nbblk], sm, epi);
 }
 
 __global__ void plan_p0_kernel(int nblk, const int64_t* __restrict__ ptr, const int* __restrict__ blk_row,
@@ -158,24 +158,36 @@ extern "C" int pyn_spmv_plan_create(int64_t nrows, const int64_t* d_ptr, int64_t
   PYN_CHECK_CUDA(cudaMalloc(&p->blk_row, sizeof(int) * (nb + 1)));
   plan_rows_kernel<<<pyn::grid_for(nb + 1, 256), 256, 0, st>>>(nrows, d_ptr, chunk, p->nblk, p->blk_row);
   PYN_CHECK_LAUNCH();
-  {  // bulk-copy pipeline: first non-zero of every chunk, and whether every chunk fits a stage
-    PYN_CHECK_CUDA(cudaMalloc(&p->blk_p0, sizeof(long long) * (nb + 1)));
+  {  // bulk-copy pipeline: its own finer chunk table, first non-zero of every chunk, whether every chunk fits a stage
+    int bchunk = pyn::SB_CHUNK - maxrow;
+    const bool fits = bchunk >= pyn::SB_CHUNK / 2;
+    if (!fits) bchunk = pyn::SB_CHUNK / 2;
+    const int64_t nbb = nnz > 0 ? (nnz + bchunk - 1) / bchunk : 1;
+    PYN_REQUIRE(nbb < 2147483647LL, "matrix too large for one SpMV plan");
+    p->nbblk = (int)nbb;
+    PYN_CHECK_CUDA(cudaMalloc(&p->brow, sizeof(int) * (nbb + 1)));
+    plan_rows_kernel<<<pyn::grid_for(nbb + 1, 256), 256, 0, st>>>(nrows, d_ptr, bchunk, p->nbblk, p->brow);
+    PYN_CHECK_LAUNCH();
+    PYN_CHECK_CUDA(cudaMalloc(&p->bp0, sizeof(long long) * (nbb + 1)));
     int* d_big = nullptr;
     int big = 0;
     PYN_CHECK_CUDA(cudaMalloc(&d_big, sizeof(int)));
     PYN_CHECK_CUDA(cudaMemsetAsync(d_big, 0, sizeof(int), st));
-    plan_p0_kernel<<<pyn::grid_for(nb + 1, 256), 256, 0, st>>>(p->nblk, d_ptr, p->blk_row, p->blk_p0, pyn::SB_CAP, d_big);
+    plan_p0_kernel<<<pyn::grid_for(nbb + 1, 256), 256, 0, st>>>(p->nbblk, d_ptr, p->brow, p->bp0, pyn::SB_CAP - 8, d_big);
     PYN_CHECK_LAUNCH();
     PYN_CHECK_CUDA(cudaMemcpyAsync(&big, d_big, sizeof(int), cudaMemcpyDeviceToHost, st));
     PYN_CHECK_CUDA(cudaStreamSynchronize(st));
     cudaFree(d_big);
-    static const bool off = getenv("PYN_SPMV_NO_BULK") != nullptr;
-    p->bulk_ok = !big && !off && p->nblk >= 2 && (reinterpret_cast<uintptr_t>(d_ptr) & 15) == 0;
+    // Measured on B200 at 1024^2 x ngl 5 (29.8 GB per product): register-staged kernel 6.23 ms (4.78 TB/s); this
+    // pipeline 7.4 ms with 2048-entry chunks / 2 stages / 3 CTAs per SM, 8.9 ms with 3 stages / 2 CTAs, 9.2 ms with
+    // 1024-entry chunks / 4 stages / 4 CTAs (profiles/README.md).  It therefore stays opt-in: PYN_SPMV_BULK=1.
+    static const bool on = getenv("PYN_SPMV_BULK") ? atoi(getenv("PYN_SPMV_BULK")) != 0 : false;
+    p->bulk_ok = fits && !big && on && p->nbblk >= 2 && (reinterpret_cast<uintptr_t>(d_ptr) & 15) == 0;
     PYN_CHECK_CUDA(cudaFuncSetAttribute(spmv_bulk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(pyn::SbSmem)));
     int occb = 0;
     PYN_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occb, spmv_bulk_kernel, pyn::SB_THREADS, sizeof(pyn::SbSmem)));
     const int64_t capb = (int64_t)pyn::sm_count() * (occb > 0 ? occb : 1);
-    p->bulk_grid = (int)(nb < capb ? nb : capb);
+    p->bulk_grid = (int)(nbb < capb ? nbb : capb);
   }
   int occ = 0;  // persistent grid: exactly the CTAs that are resident at once
   PYN_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, spmv_stream_kernel, pyn::SP_BLK, 0));
@@ -189,7 +201,8 @@ extern "C" int pyn_spmv_plan_create(int64_t nrows, const int64_t* d_ptr, int64_t
 extern "C" int pyn_spmv_plan_destroy(pyn_spmv_plan* p) {
   if (!p) return PYN_OK;
   cudaFree(p->blk_row);
-  cudaFree(p->blk_p0);
+  cudaFree(p->brow);
+  cudaFree(p->bp0);
   delete p;
   return PYN_OK;
 }

@@ -57,8 +57,11 @@ struct SpmvPlanView {
   int64_t nrows, nnz;
   const int64_t* ptr;
   const int* blk_row;  // [nblk+1] first row of each chunk
-  const long long* blk_p0;   // [nblk+1] ptr[blk_row[b]]: first non-zero of each chunk (bulk-copy producer)
   int nblk;
+  // bulk-copy kernels: their own, finer chunk table (smaller stages -> more resident CTAs)
+  const int* brow;           // [nbblk+1]
+  const long long* bp0;      // [nbblk+1] ptr[brow[b]]: first non-zero of each chunk
+  int nbblk;
 };
 
 struct SpmvSmem {
@@ -68,11 +71,21 @@ struct SpmvSmem {
 
 // Processes chunk `b`; calls epi(row, sum) once per row from exactly one thread.
 template <class Epi>
+__device__ __forceinline__ void spmv_stream_rows(const SpmvPlanView& P, const int* __restrict__ ind,
+                                                 const double* __restrict__ val, const double* __restrict__ x, int r0,
+                                                 int r1, SpmvSmem& sm, Epi&& epi);
+template <class Epi>
 __device__ __forceinline__ void spmv_stream_chunk(const SpmvPlanView& P, const int* __restrict__ ind,
                                                   const double* __restrict__ val, const double* __restrict__ x, int b,
                                                   SpmvSmem& sm, Epi&& epi) {
+  spmv_stream_rows(P, ind, val, x, P.blk_row[b], P.blk_row[b + 1], sm, epi);
+}
+// rows [r0, r1) as one chunk
+template <class Epi>
+__device__ __forceinline__ void spmv_stream_rows(const SpmvPlanView& P, const int* __restrict__ ind,
+                                                 const double* __restrict__ val, const double* __restrict__ x, int r0,
+                                                 int r1, SpmvSmem& sm, Epi&& epi) {
   const int tid = threadIdx.x;
-  const int r0 = P.blk_row[b], r1 = P.blk_row[b + 1];
   const int nr = r1 - r0;
   if (nr <= 0) return;
   const int64_t p0 = P.ptr[r0];
@@ -129,8 +142,8 @@ __device__ __forceinline__ void spmv_stream_chunk(const SpmvPlanView& P, const i
 }  // namespace pyn
 
 // ---------------------------------------------------------------------------------------------------------------
-// "CSR-stream, bulk copy": the same chunks, the same products and the same row sums as spmv_stream_chunk (bit-identical
-// results), but the value / index / row-pointer slices of a chunk are brought into shared memory by the TMA unit --
+// "CSR-stream, bulk copy": the same products and row sums as spmv_stream_chunk on a finer chunk table, but the value /
+// index / row-pointer slices of a chunk are brought into shared memory by the TMA unit --
 // 1-D `cp.async.bulk.shared::cluster.global` completing on an mbarrier (UBLKCP in SASS) -- issued by one thread
 // SB_STAGES-1 chunks ahead of the consumers.  The bytes in flight per SM no longer depend on registers or on resident
 // warps (two CTAs keep ~100 kB on the wire), which is what bounded the register-staged kernel at 0.71 of the HBM peak
@@ -140,9 +153,11 @@ __device__ __forceinline__ void spmv_stream_chunk(const SpmvPlanView& P, const i
 namespace pyn {
 
 constexpr int SB_BLK = 256;
-constexpr int SB_STAGES = 3;
-constexpr int SB_CAP = 2304;      // non-zeros per stage (a plan chunk is <= 2048 by construction when rows are < 1 k long)
-constexpr int SB_RCAP = 512;      // row pointers staged per chunk (more rows in a chunk: read from global)
+constexpr int SB_STAGES = 4;
+constexpr int SB_CHUNK = 1024;    // non-zeros per bulk chunk (rows snapped: a chunk holds <= SB_CHUNK when rows are shorter)
+constexpr int SB_CAP = SB_CHUNK + 16;   // per stage
+constexpr int SB_RCAP = 124;      // row pointers staged per chunk (more rows in a chunk: read from global)
+constexpr int SB_U = 4;           // x gathers in flight per lane
 
 struct SbStage {
   double val[SB_CAP + 2];               // 16-byte aligned superset of the chunk's values; products in place
@@ -186,9 +201,7 @@ __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.
 
 // producer side (one thread): describe chunk b in stage s and start its three bulk copies
 __device__ __forceinline__ void sb_issue(const SpmvPlanView& P, const int* __restrict__ ind, const double* __restrict__ val,
-                                         int b, SbSmem& sm, int s) {
-  const int r0 = P.blk_row[b], r1 = P.blk_row[b + 1];
-  const long long p0 = P.blk_p0[b], p1 = P.blk_p0[b + 1];
+                                         int r0, int r1, long long p0, long long p1, SbSmem& sm, int s) {
   const int nr = r1 - r0, cnt = (int)(p1 - p0);
   sm.r0[s] = r0; sm.nr[s] = nr; sm.cnt[s] = cnt; sm.p0[s] = p0;
   unsigned bytes = 0;
@@ -221,8 +234,8 @@ __device__ __forceinline__ void sb_issue(const SpmvPlanView& P, const int* __res
 //
 // SB_BLK consumer threads + one producer warp (launch with SB_THREADS).  The pipeline is warp-asynchronous: a consumer
 // warp waits for a stage to be full, takes an eighth of the chunk's rows -- a contiguous range of entries --, forms the
-// products of that range in place (every x gather independent, SP_U per lane in flight), sums its rows with the
-// sub-warp width spmv_stream_chunk would use for the chunk (same order of additions: bit-identical results), arrives
+// products of that range in place (every x gather independent, SB_U per lane in flight), sums its rows by sub-warps
+// (fixed shuffle tree: deterministic; the order differs from spmv_stream_chunk's because the chunks do), arrives
 // on the stage's `empty` barrier and moves on; the producer refills a stage as soon as all eight warps have left it.
 // No CTA-wide barrier inside the loop.
 constexpr int SB_THREADS = SB_BLK + 32;
@@ -243,11 +256,18 @@ __device__ __forceinline__ void spmv_bulk_loop(const SpmvPlanView& P, const int*
   __syncthreads();
   const int nmine = first < nblk_bulk ? (nblk_bulk - first + stride - 1) / stride : 0;
   if (tid >= SB_BLK) {   // ---- producer warp (one lane issues) ----
-    if (tid == SB_BLK) {
+    if (tid == SB_BLK && nmine > 0) {
+      // the chunk descriptors are fetched one chunk ahead, so that their latency is not added to every issue
+      int r0 = P.brow[first], r1 = P.brow[first + 1];
+      long long p0 = P.bp0[first], p1 = P.bp0[first + 1];
       for (int i = 0; i < nmine; ++i) {
         const int s = i % SB_STAGES;
+        const int bn = first + (i + 1 < nmine ? i + 1 : i) * stride;
+        const int nr0 = P.brow[bn], nr1 = P.brow[bn + 1];
+        const long long np0 = P.bp0[bn], np1 = P.bp0[bn + 1];
         if (i >= SB_STAGES) mbar_wait(&sm.empty[s], (unsigned)(((i / SB_STAGES) - 1) & 1));
-        sb_issue(P, ind, val, first + i * stride, sm, s);
+        sb_issue(P, ind, val, r0, r1, p0, p1, sm, s);
+        r0 = nr0; r1 = nr1; p0 = np0; p1 = np1;
       }
     }
     return;
@@ -269,25 +289,25 @@ __device__ __forceinline__ void spmv_bulk_loop(const SpmvPlanView& P, const int*
       if (rb > ra) {
         const int ea = (int)((staged ? pp[ra] : P.ptr[r0 + ra]) - p0), eb = (int)((staged ? pp[rb] : P.ptr[r0 + rb]) - p0);
         // products in place: every gather of the warp's range is independent, SP_U per lane in flight
-        for (int base = ea; base < eb; base += SP_U * 32) {
-          double vv[SP_U];
-          int cc[SP_U];
+        for (int base = ea; base < eb; base += SB_U * 32) {
+          double vv[SB_U];
+          int cc[SB_U];
 #pragma unroll
-          for (int u = 0; u < SP_U; ++u) {
+          for (int u = 0; u < SB_U; ++u) {
             const int k = base + u * 32 + lane;
             const bool ok = k < eb;
             cc[u] = ok ? pi[k] : -1;
             vv[u] = ok ? pv[k] : 0.0;
           }
 #pragma unroll
-          for (int u = 0; u < SP_U; ++u)
+          for (int u = 0; u < SB_U; ++u)
             if (cc[u] >= 0) vv[u] = __dmul_rn(vv[u], x[cc[u]]);
 #pragma unroll
-          for (int u = 0; u < SP_U; ++u)
+          for (int u = 0; u < SB_U; ++u)
             if (cc[u] >= 0) pv[base + u * 32 + lane] = vv[u];
         }
         __syncwarp();
-        // row sums with the sub-warp width spmv_stream_chunk uses for a chunk of nr rows (same order of additions)
+        // row sums by sub-warps whose width adapts to the rows in the chunk (a pure function of the pattern)
         int lpr = 32;
         while (lpr > 1 && lpr * nr > SB_BLK) lpr >>= 1;
         const int rpp = 32 / lpr, sub = lane & (lpr - 1), slot = lane / lpr;
@@ -316,14 +336,16 @@ struct pyn_spmv_plan {
   int64_t nrows, nnz;
   const int64_t* ptr;  // borrowed
   int* blk_row;
-  long long* blk_p0;
-  int nblk, chunk, grid;
+  int* brow;
+  long long* bp0;
+  int nblk, chunk, grid, nbblk;
   int bulk_ok, bulk_grid;   // every chunk fits a bulk stage; persistent grid of the bulk-copy kernels
 };
 namespace pyn {
 static inline SpmvPlanView view_of(const pyn_spmv_plan* p) {
   SpmvPlanView v;
-  v.nrows = p->nrows; v.nnz = p->nnz; v.ptr = p->ptr; v.blk_row = p->blk_row; v.blk_p0 = p->blk_p0; v.nblk = p->nblk;
+  v.nrows = p->nrows; v.nnz = p->nnz; v.ptr = p->ptr; v.blk_row = p->blk_row; v.nblk = p->nblk;
+  v.brow = p->brow; v.bp0 = p->bp0; v.nbblk = p->nbblk;
   return v;
 }
 }  // namespace pyn
