@@ -463,10 +463,18 @@ int pyn_elem_kle(const pyn_elem* e, const double* d_coords, int64_t ne, double* 
     return PYN_ERR_LIMIT;
   }
   PYN_CHECK_CUDA(cudaFuncSetAttribute(elem_kle_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  const int ctas_per_sm = (int)((227 * 1024) / (smem + 1024));
-  int grid = pyn::sm_count() * (ctas_per_sm < 1 ? 1 : (ctas_per_sm > 8 ? 8 : ctas_per_sm));
-  if (grid > ne) grid = (int)ne;
-  elem_kle_kernel<<<grid, 256, smem, pyn::as_stream(stream)>>>(*e, d_coords, ne, d_K, d_Rw, d_Rd);
+  // one CTA per element, sized to the element: nn^2 (i, j) pairs of work per phase -- 32 threads at ngl 2 ... 256 from
+  // ngl 4 on -- and as many CTAs per SM as threads and shared memory allow (ngl 2: 32, ngl 5: 8)
+  const int nn2 = e->n * e->n * e->n * e->n;
+  int threads = ((nn2 + 31) / 32) * 32;
+  if (threads > 256) threads = 256;
+  int ctas_per_sm = (int)((227 * 1024) / (smem + 1024));
+  if (ctas_per_sm > 2048 / threads) ctas_per_sm = 2048 / threads;
+  if (ctas_per_sm > 32) ctas_per_sm = 32;
+  if (ctas_per_sm < 1) ctas_per_sm = 1;
+  int64_t grid = (int64_t)pyn::sm_count() * ctas_per_sm;
+  if (grid > ne) grid = ne;
+  elem_kle_kernel<<<(int)grid, threads, smem, pyn::as_stream(stream)>>>(*e, d_coords, ne, d_K, d_Rw, d_Rd);
   PYN_CHECK_LAUNCH();
   return PYN_OK;
 }

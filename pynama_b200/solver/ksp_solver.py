@@ -106,9 +106,14 @@ class KspSolver(object):
         if ksp_type == "preonly":
             if pc not in ("lu", "cholesky"):
                 raise Exception(f"KSP preonly with PC {pc} is not available on the device path")
-            self.logger.info("preonly+lu requested: served by device CG+Jacobi to rtol %g (no sparse direct "
-                             "factorisation on the device path)", self.DIRECT_RTOL)
-            ksp_type, pc, rtol, max_it = "cg", "jacobi", self.DIRECT_RTOL, self.DIRECT_MAX_IT
+            self.logger.info("preonly+lu requested: served by device CG (multigrid or Jacobi) to rtol %g + iterative "
+                             "refinement (no sparse direct factorisation on the device path)", self.DIRECT_RTOL)
+            # one GPU: the multigrid V-cycle makes "solve to round-off" affordable (tens of iterations instead of tens
+            # of thousands); it needs the case's mesh, which the case layer supplies right after createSolver
+            # (setUpMultigrid) -- a solver used on its own falls back to Jacobi at the first solve
+            dist_ = getattr(self.comm, "dist", None)
+            pc = "mg" if dist_ is None and Options().getString("pc_direct_standin", "mg") == "mg" else "jacobi"
+            ksp_type, rtol, max_it = "cg", self.DIRECT_RTOL, self.DIRECT_MAX_IT
             self._direct = True
         if ksp_type not in be.Ksp.TYPES:
             raise Exception(f"KSP type {ksp_type} is not available on the device path (cg, gmres)")
@@ -147,6 +152,14 @@ class KspSolver(object):
         self.setUp()
 
     def solve(self, b, x):
+        if self.wantsMultigrid():      # -pc_type mg (or the direct stand-in) without a hierarchy: Jacobi instead
+            self.logger.warning("multigrid hierarchy not set up for this solver (no case attached): using Jacobi")
+            self._pc = "jacobi"
+            Options.setValue("pc_direct_standin", "jacobi")
+            try:
+                self.setUp()
+            finally:
+                Options.setValue("pc_direct_standin", "mg")
         r = self._ksp.solve(b.data, x.data)
         if self._direct and r.reason > 0:
             csr = self._ksp.A
