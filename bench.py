@@ -599,7 +599,10 @@ def run_percell(a):
                    "fused_integrate_assemble": fused,
                    "l2": "outputs exceed the 126 MB L2; no flush needed"},
         "phases_ms": phase,
-        "integration": {"kernel": "elem_kle_kernel (K_e, Rw_e of every cell)", "ms": phase["elem"], "flop": fl,
+        "integration": {"kernel": "elem_affine_coef_kernel: 17 closed-form coefficients per cell, entries evaluated inside "
+                                  "the assembly kernels (flop / tflops below do not apply)", "ms": phase["elem"],
+                        "bytes": elem_bytes + 144 * ne} if fused else
+                       {"kernel": "elem_kle_kernel (K_e, Rw_e of every cell)", "ms": phase["elem"], "flop": fl,
                         "tflops": fl / (phase["elem"] * 1e-3) / 1e12 if phase["elem"] > 0 else None,
                         "bytes": elem_bytes, "gbs": elem_bytes / (phase["elem"] * 1e-3) / 1e9 if phase["elem"] > 0 else None,
                         "hbm_frac": elem_bytes / (phase["elem"] * 1e-3) / 1e9 / peak if phase["elem"] > 0 else None,
