@@ -294,3 +294,61 @@ def test_gmsh_reader_and_unstructured_numbering(tmp_path):
         cc = dom.cellCornersArray()                                         # all cells counter-clockwise
         area2 = (cc[:, 1, 0] - cc[:, 0, 0]) * (cc[:, 2, 1] - cc[:, 0, 1]) - (cc[:, 1, 1] - cc[:, 0, 1]) * (cc[:, 2, 0] - cc[:, 0, 0])
         assert (area2 > 0).all()
+
+
+def test_paraview_xdmf_output(tmp_path, monkeypatch):
+    """viewer/paraviewer.py + xml_generator.py (reference: src/viewer/paraviewer.py:18-73, xml_generator.py:32-97): the
+    XDMF index has the reference's structure and its heavy-data items point at files holding exactly the saved values."""
+    import xml.etree.ElementTree as ET
+    from pynama_b200.viewer.paraviewer import Paraviewer
+
+    class HostVec:                              # the slice of the Vec surface the viewer uses (no GPU needed)
+        def __init__(self, a, name):
+            self.a, self.name = np.asarray(a, float), name
+        def getArray(self): return self.a
+        def getSize(self): return self.a.size
+        def getName(self): return self.name
+        def setName(self, n): self.name = n
+
+    monkeypatch.setenv("PYNAMA_SAVE", "1")
+    n = 7
+    coords = HostVec(np.arange(2 * n) * 0.5, "coords")
+    vel, vort = HostVec(np.arange(2 * n) + 100.0, "velocity"), HostVec(np.arange(n) - 3.0, "vorticity")
+    v = Paraviewer(2, None, str(tmp_path / "out"))
+    v.saveMesh(coords)
+    for step, t in ((0, 0.0), (1, 0.25)):
+        v.saveData(step, t, vel, vort)
+        v.writeXmf("cavity")
+    root = ET.parse(tmp_path / "out" / "cavity.xmf").getroot()
+    assert root.tag == "Xdmf" and root.get("Version") == "2.0"
+    coll = root.find("Domain/Grid")
+    assert coll.get("GridType") == "Collection" and coll.get("CollectionType") == "Temporal"
+    grids = coll.findall("Grid")
+    assert [g.find("Time").get("Value") for g in grids] == ["0.0", "0.25"]
+    g = grids[1]
+    assert g.find("Topology").get("TopologyType") == "Polyvertex" and g.find("Topology").get("Dimensions") == str(n)
+    assert g.find("Geometry").get("GeometryType") == "XY"
+    attrs = {a.get("Name"): a for a in g.findall("Attribute")}
+    assert attrs["velocity"].get("AttributeType") == "Vector" and attrs["vorticity"].get("AttributeType") == "Scalar"
+    assert attrs["velocity"].find("DataItem").get("Function") == "JOIN($0, $1)"
+    slabs = attrs["velocity"].find("DataItem").findall("DataItem")
+    assert [s.find("DataItem").text for s in slabs] == [f"0 2 {n}", f"1 2 {n}"]
+    item = attrs["vorticity"].find("DataItem")
+    if item.get("Format") == "Binary":
+        got = np.fromfile(tmp_path / "out" / item.text.strip(), dtype="<f8")
+        mesh = np.fromfile(tmp_path / "out" / g.find("Geometry/DataItem").text.strip(), dtype="<f8")
+        velf = np.fromfile(tmp_path / "out" / slabs[0].findall("DataItem")[1].text.strip(), dtype="<f8")
+    else:
+        import h5py
+        f, ds = item.text.strip().split(":")
+        got = h5py.File(tmp_path / "out" / f)[ds][...]
+        mesh = h5py.File(tmp_path / "out" / "mesh.h5")["/fields/mesh"][...]
+        velf = h5py.File(tmp_path / "out" / f)["/fields/velocity"][...]
+    np.testing.assert_array_equal(got, vort.a)
+    np.testing.assert_array_equal(mesh, coords.a)
+    np.testing.assert_array_equal(velf, vel.a)
+    # off by default: nothing is written without PYNAMA_SAVE
+    monkeypatch.delenv("PYNAMA_SAVE")
+    q = Paraviewer(2, None, str(tmp_path / "none"))
+    q.saveMesh(coords); q.saveData(0, 0.0, vel); q.writeXmf("x")
+    assert not (tmp_path / "none").exists()
