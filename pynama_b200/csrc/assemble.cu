@@ -858,12 +858,38 @@ static int launch_interior(const pyn_topo* t, const DescView& dv, const int64_t*
   return PYN_ERR_ARG;
 }
 
+static bool g_defer_join = false;    // pyn_asm_defer_join(1): a batch of fills joins the side stream once (pyn_asm_join)
+
 // values-only assembly of the interior nodes through row templates (needs signatures and one element matrix)
 static int launch_templates(const pyn_topo* t, const DescView& dv, const int64_t* indptr, double* data, cudaStream_t st) {
   const pyn::TopoView tv = pyn::view_of(t);
   pyn_topo* tm = const_cast<pyn_topo*>(t);   // scratch owned by the handle (one host thread per handle)
   if (!tm->sig_tmpl) PYN_CHECK_CUDA(cudaMalloc(&tm->sig_tmpl, sizeof(double) * (size_t)t->sig_slots * 9));
   double* T = tm->sig_tmpl;
+  cudaStream_t tst = st;          // stream of the template kernel
+  int ring = -1;
+  static const bool no_overlap = getenv("PYN_ASM_NO_OVERLAP") != nullptr;
+  if (g_defer_join && !no_overlap) {   // inside a batch: templates on the second side stream (topo.cuh)
+    if (!tm->side2) {
+      PYN_CHECK_CUDA(cudaStreamCreateWithFlags(&tm->side2, cudaStreamNonBlocking));
+      PYN_CHECK_CUDA(cudaEventCreateWithFlags(&tm->ev_batch, cudaEventDisableTiming));
+      for (int i = 0; i < 4; ++i) {
+        PYN_CHECK_CUDA(cudaEventCreateWithFlags(&tm->ev_tmpl[i], cudaEventDisableTiming));
+        PYN_CHECK_CUDA(cudaMalloc(&tm->sig_ring[i], sizeof(double) * (size_t)t->sig_slots * 9));
+      }
+    }
+    if (!tm->batch_forked) {   // once per batch: the element matrices are ready at this point of the caller's stream
+      PYN_CHECK_CUDA(cudaEventRecord(tm->ev_batch, st));
+      PYN_CHECK_CUDA(cudaStreamWaitEvent(tm->side2, tm->ev_batch, 0));
+      tm->batch_forked = 1;
+      tm->ring_next = 0;
+    }
+    if (tm->ring_next < 4) {   // more than four template matrices in one batch: the rest stay on the caller's stream
+      ring = tm->ring_next++;
+      T = tm->sig_ring[ring];
+      tst = tm->side2;
+    }
+  }
   const int tgrid = (t->nsig + 3) / 4;
   // One CTA per batch, NOT a persistent grid: CTAs are dispatched in batch order and start staggered, so the stores in
   // flight sweep the array like a plain fill.  Persistent CTAs stay in lock-step at addresses one batch stride apart and
@@ -880,8 +906,12 @@ static int launch_templates(const pyn_topo* t, const DescView& dv, const int64_t
   (void)warp_only_set;
 #define PYN_ASM_CASE(R, C)                                                                        \
   if (!done && dv.rdof == R && dv.cdof == C) {                                                    \
-    asm_template_kernel<R, C><<<tgrid, 128, 0, st>>>(tv, dv, T);                                  \
+    asm_template_kernel<R, C><<<tgrid, 128, 0, tst>>>(tv, dv, T);                                 \
     pyn::count_launch();                                                                          \
+    if (ring >= 0) {                                                                              \
+      cudaEventRecord(tm->ev_tmpl[ring], tst);                                                    \
+      cudaStreamWaitEvent(st, tm->ev_tmpl[ring], 0);                                              \
+    }                                                                                             \
     asm_stream_kernel<R, C><<<sgrid, 256, 0, st>>>(tv, dv, indptr, T, data);                      \
     pyn::count_launch();                                                                          \
     done = true;                                                                                  \
@@ -902,7 +932,6 @@ static int launch_templates(const pyn_topo* t, const DescView& dv, const int64_t
 }
 
 // the interior fast path applies when a map is given and class-0 rows carry no forced diagonal
-static bool g_defer_join = false;    // pyn_asm_defer_join(1): a batch of fills joins the side stream once (pyn_asm_join)
 static bool g_no_templates = false;  // pyn_asm_set_templates(0): force the generic gather kernel (tests, comparisons)
 static inline bool use_map(const pyn_asm_desc* desc) { return desc->bcmap != nullptr && !(desc->diag_classes & 1u); }
 
@@ -1007,6 +1036,7 @@ static int fork_boundary(const pyn_topo* t, const DescView& dv, const int* list,
 int pyn_asm_join(const pyn_topo* t, void* stream) {
   PYN_REQUIRE(t, "topo is NULL");
   pyn_topo* tm = const_cast<pyn_topo*>(t);
+  tm->batch_forked = 0;   // the next batch forks its template stream again (its element matrices are new)
   if (tm->pending) {
     PYN_CHECK_CUDA(cudaStreamWaitEvent(pyn::as_stream(stream), tm->ev_join, 0));
     tm->pending = 0;

@@ -524,6 +524,12 @@ int pyn_topo_destroy(pyn_topo* t) {
   cudaFree(t->n2e_ptr); cudaFree(t->n2e_elem); cudaFree(t->n2e_loc); cudaFree(t->adj_ptr); cudaFree(t->adj_cols); cudaFree(t->inv_ptr); cudaFree(t->inv);
   cudaFree(t->sig_id); cudaFree(t->sig_rep); cudaFree(t->sig_ptr); cudaFree(t->sig_tmpl);
   if (t->side) { cudaStreamSynchronize(t->side); cudaStreamDestroy(t->side); cudaEventDestroy(t->ev_fork); cudaEventDestroy(t->ev_join); }
+  if (t->side2) {
+    cudaStreamSynchronize(t->side2);
+    cudaStreamDestroy(t->side2);
+    cudaEventDestroy(t->ev_batch);
+    for (int i = 0; i < 4; ++i) { cudaEventDestroy(t->ev_tmpl[i]); cudaFree(t->sig_ring[i]); }
+  }
   delete t;
   return PYN_OK;
 }

@@ -30,6 +30,13 @@ struct pyn_topo {
   cudaStream_t side;
   cudaEvent_t ev_fork, ev_join;
   int pending;
+  // Inside a batch of fills (pyn_asm_defer_join) the row-template kernels of the later matrices run on a second side
+  // stream, forked once per batch after the element matrices exist, so that they overlap the store stream of the
+  // previous matrix instead of sitting between two stream kernels; a ring of template buffers keeps them apart.
+  cudaStream_t side2;
+  cudaEvent_t ev_batch, ev_tmpl[4];
+  double* sig_ring[4];
+  int batch_forked, ring_next;
 };
 
 struct pyn_bcmap {
