@@ -48,7 +48,7 @@ def parse_args():
                     help="cavity: configs[3] (default); percell: FreeSlip, element matrices of every cell (configs[1]/[2])")
     ap.add_argument("--fused", default=None, help="percell: -mat_fused 0|1 (fused integrate+assemble kernel)")
     ap.add_argument("--pc", default=None, help="-pc_type of the converged solves in the time-loop phase "
-                                               "(default: mg on one GPU, jacobi on a partitioned mesh)")
+                                               "(default: mg)")
     return ap.parse_args()
 
 
@@ -273,7 +273,7 @@ def run_native(a):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     if a.pc is None:
-        a.pc = "mg" if world == 1 else "jacobi"      # the V-cycle runs on one GPU (solver/multigrid.py)
+        a.pc = "mg"
     from pynama_b200 import backend as be
     ev = lambda: torch.cuda.Event(enable_timing=True)
 

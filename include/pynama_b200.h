@@ -305,6 +305,8 @@ int pyn_mg_set_coarse_inverse(pyn_mg* g, const double* d_Ainv);   /* [n_c][n_c],
 int pyn_mg_apply(pyn_mg* g, const double* d_r, double* d_z, void* stream);   /* z = V(r); 0 on prescribed dofs */
 int pyn_mg_destroy(pyn_mg* g);
 int pyn_ksp_set_mg(pyn_ksp* k, pyn_mg* g);
+/* Partitioned mesh: level 0 is this rank's strip (halo exchange before every fine product, restricted residual summed
+ * over the ranks); all coarser levels are replicated on every rank.  Declared after the multi-GPU section below. */
 
 /* ------------------------------------------------------------------------------------------------------
  * Multi-GPU: one process per GPU, the mesh cut into strips of cell rows (the reference: DMPlex.distribute(),
@@ -341,6 +343,7 @@ int pyn_comm_set_peer(pyn_comm* c, pyn_peer* p);
 int pyn_halo_exchange(const pyn_halo* h, double* d_vec, int ncomp, void* stream);
 int64_t pyn_halo_bytes(const pyn_halo* h, int ncomp);
 int pyn_ksp_set_dist(pyn_ksp* k, const pyn_comm* comm, const pyn_halo* halo, int ncomp, const uint8_t* d_owned_rows);
+int pyn_mg_set_dist(pyn_mg* g, const pyn_comm* comm, const pyn_halo* halo, int ncomp);
 
 #ifdef __cplusplus
 }

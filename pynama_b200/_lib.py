@@ -125,6 +125,7 @@ _SIGNATURES = {
     "pyn_mg_apply": (C.c_int, [c_vp, c_vp, c_vp, c_vp]),
     "pyn_mg_destroy": (C.c_int, [c_vp]),
     "pyn_ksp_set_mg": (C.c_int, [c_vp, c_vp]),
+    "pyn_mg_set_dist": (C.c_int, [c_vp, c_vp, c_vp, C.c_int]),
     "pyn_ksp_set_dist": (C.c_int, [c_vp, c_vp, c_vp, C.c_int, c_vp]),
 }
 

@@ -35,9 +35,11 @@ SPMV_SET, SPMV_ADD, SPMV_SCALE, SPMV_SRT_VTENSV = 0, 1, 2, 3
 class _Comm(object):
     """Stand-in for MPI.COMM_WORLD: rank/size of the torch.distributed job when there is one, else a single rank."""
 
-    def __init__(self):
+    def __init__(self, serial=False):
         self.rank, self.size = 0, 1
         self.dist = None            # pynama_b200.dist.DistContext once the mesh has been partitioned
+        if serial:                  # a case replicated on every rank (the coarse levels of the multigrid hierarchy)
+            return
         try:
             import torch.distributed as dist
             if dist.is_available() and dist.is_initialized():
@@ -54,7 +56,7 @@ class _Comm(object):
 
 class BaseProblem(object):
     def __init__(self, config, **kwargs):
-        self.comm = _Comm()
+        self.comm = _Comm(serial=bool(kwargs.pop("serial", False)))
         self.timerTotal = Timer()
         self.timerTotal.tic()
         self.timer = Timer()

@@ -309,28 +309,30 @@ __global__ void cg_update_kernel(int64_t n, int nparts_in, CgBuffers B, double* 
 }
 
 // ---- CG with a general (multigrid) preconditioner: z = M^-1 r is a sequence of launches between these kernels ----
-// r = b, x = 0, p = 0
-__global__ void cg_mg_init_kernel(int64_t n, const double* __restrict__ b, CgBuffers B) {
+// r = b (0 on rows owned by another rank), x = 0, p = 0
+__global__ void cg_mg_init_kernel(int64_t n, const double* __restrict__ b, CgBuffers B,
+                                  const uint8_t* __restrict__ owned) {
   for (int64_t i = blockIdx.x * (int64_t)BLK + threadIdx.x; i < n; i += (int64_t)gridDim.x * BLK) {
-    B.r[i] = b[i];
+    B.r[i] = (owned && !owned[i]) ? 0.0 : b[i];
     B.x[i] = 0.0;
     B.p[i] = 0.0;
   }
 }
 // nonzero initial guess, with p = x0 and w = A p:  r = b - w, x = x0
-__global__ void cg_mg_init_guess_kernel(int64_t n, const double* __restrict__ b, CgBuffers B) {
+__global__ void cg_mg_init_guess_kernel(int64_t n, const double* __restrict__ b, CgBuffers B,
+                                        const uint8_t* __restrict__ owned) {
   for (int64_t i = blockIdx.x * (int64_t)BLK + threadIdx.x; i < n; i += (int64_t)gridDim.x * BLK) {
-    B.r[i] = b[i] - B.w[i];
+    B.r[i] = (owned && !owned[i]) ? 0.0 : b[i] - B.w[i];
     B.x[i] = B.p[i];
   }
 }
 // a = beta / (p.w) ; r -= a w
-__global__ void cg_mg_rupdate_kernel(int64_t n, int nparts_in, CgBuffers B) {
+__global__ void cg_mg_rupdate_kernel(int64_t n, int nparts_in, CgBuffers B, const double* __restrict__ g) {
   __shared__ double s_a;
   const KspState* s = B.st;
   if (s->done) return;
   if (threadIdx.x < 32) {
-    const double dpi = pyn::reduce_partials(B.part_a, nparts_in);
+    const double dpi = g ? g[0] : pyn::reduce_partials(B.part_a, nparts_in);
     if (threadIdx.x == 0) s_a = (dpi > 0.0) ? s->beta / dpi : 0.0;
   }
   __syncthreads();
@@ -410,6 +412,12 @@ __global__ void cg_finish_kernel(int64_t n, CgBuffers B, double* __restrict__ ds
   }
 }
 
+__global__ void copy_masked_kernel(int64_t n, const double* __restrict__ src, double* __restrict__ dst,
+                                   const uint8_t* __restrict__ owned) {
+  for (int64_t i = blockIdx.x * (int64_t)BLK + threadIdx.x; i < n; i += (int64_t)gridDim.x * BLK)
+    dst[i] = (owned && !owned[i]) ? 0.0 : src[i];
+}
+
 __global__ void copy_kernel(int64_t n, const double* __restrict__ src, double* __restrict__ dst) {
   for (int64_t i = blockIdx.x * (int64_t)BLK + threadIdx.x; i < n; i += (int64_t)gridDim.x * BLK) dst[i] = src[i];
 }
@@ -465,7 +473,7 @@ int enqueue_cg_iteration(const pyn_ksp* k, cudaStream_t st) {
     if (rc) return rc;
   }
   if (k->mg) {   // z = V-cycle(r): r -= a w, the cycle's launches, then the Jacobi rows + the two dot products
-    cg_mg_rupdate_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, npw, k->B);
+    cg_mg_rupdate_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, npw, k->B, g);
     int rc = pyn::mg_apply(k->mg, k->B.r, k->B.z, st);
     if (rc) return rc;
     cg_mg_zdot_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, k->mg->L[0].dinv, k->B.r, k->B, k->pzz, k->pzr);
@@ -538,7 +546,7 @@ int pyn_ksp_solve(pyn_ksp* k, const double* d_b, double* d_x, pyn_ksp_result* re
   int64_t launches = 0;
   const bool dist = k->comm && k->comm->world > 1;
   const bool guess = k->opts.nonzero_guess != 0;
-  if (k->mg) PYN_REQUIRE(!dist, "the multigrid preconditioner runs on one GPU (use -pc_type jacobi on a partitioned mesh)");
+  if (k->mg && dist) PYN_REQUIRE(k->mg->comm == k->comm, "multigrid hierarchy of a partitioned mesh: attach the communicator (pyn_mg_set_dist)");
   if (guess) {   // r0 = b - A x0 with the contents of d_x (KSPSetInitialGuessNonzero)
     cg_reset_kernel<<<1, 1, 0, st>>>(k->B.st);
     copy_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, d_x, k->B.p);
@@ -546,10 +554,11 @@ int pyn_ksp_solve(pyn_ksp* k, const double* d_b, double* d_x, pyn_ksp_result* re
     int rc = enqueue_cg_product(k, st, &npw);
     if (rc) return rc;
     if (k->mg) {   // |M^-1 b| first (KSPConvergedDefault's reference norm), then z = M^-1 r0
-      rc = pyn::mg_apply(k->mg, d_b, k->B.z, st);
+      copy_masked_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, d_b, k->B.r, dist ? k->owned : nullptr);   // b on owned rows
+      rc = pyn::mg_apply(k->mg, k->B.r, k->B.z, st);
       if (rc) return rc;
-      cg_mg_zdot_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, k->mg->L[0].dinv, d_b, k->B, k->pzz, nullptr);
-      cg_mg_init_guess_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, d_b, k->B);
+      cg_mg_zdot_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, k->mg->L[0].dinv, k->B.r, k->B, k->pzz, nullptr);
+      cg_mg_init_guess_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, d_b, k->B, dist ? k->owned : nullptr);
       rc = pyn::mg_apply(k->mg, k->B.r, k->B.z, st);
       if (rc) return rc;
       cg_mg_zdot_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, k->mg->L[0].dinv, k->B.r, k->B, k->B.part_a, k->B.part_b);
@@ -557,7 +566,7 @@ int pyn_ksp_solve(pyn_ksp* k, const double* d_b, double* d_x, pyn_ksp_result* re
     cg_init_guess_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, d_b, k->B, dist ? k->owned : nullptr, k->pzz);
     launches += 4;
   } else if (k->mg) {
-    cg_mg_init_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, d_b, k->B);
+    cg_mg_init_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, d_b, k->B, dist ? k->owned : nullptr);
     int rc = pyn::mg_apply(k->mg, k->B.r, k->B.z, st);
     if (rc) return rc;
     cg_mg_zdot_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, k->mg->L[0].dinv, k->B.r, k->B, k->B.part_a, k->B.part_b);

@@ -66,7 +66,13 @@ __global__ void mg_dense_kernel(int n, const double* __restrict__ Ainv, const do
   if (lane == 0) x[row] = s;
 }
 
-int apply_op(const MgLevel& L, const double* x, double* y, cudaStream_t st) {
+// y = A_l x.  On a partitioned fine level the ghost entries of x are refreshed from their owners first (x is one of
+// the level's work vectors: only its ghost entries change).
+int apply_op(const pyn_mg* g, const MgLevel& L, double* x, double* y, cudaStream_t st) {
+  if (g->halo && &L == &g->L[0]) {
+    int rc = pyn::halo_exchange(g->halo, x, g->halo_comp, st);
+    if (rc) return rc;
+  }
   if (L.tmat) return pyn_tmat_mult(L.tmat, x, y, PYN_SPMV_SET, 0.0, 0.0, nullptr, st);
   return pyn_spmv_planned(L.plan, L.ind, L.val, x, y, PYN_SPMV_SET, 0.0, 0.0, nullptr, st);
 }
@@ -81,7 +87,7 @@ int smooth(const pyn_mg* g, MgLevel& L, const double* b, double* x, bool fresh, 
                                            (fresh && b != L.r) ? 1 : 0);
   PYN_CHECK_LAUNCH();
   for (int k = 1; k < g->degree; ++k) {
-    int rc = apply_op(L, L.d, L.w, st);
+    int rc = apply_op(g, L, L.d, L.w, st);
     if (rc) return rc;
     const double rho_new = 1.0 / (2.0 * sigma - rho);
     mg_step_kernel<<<L.vgrid, BLK, 0, st>>>(L.n, L.w, L.dinv, rho_new * rho, 2.0 * rho_new / delta, L.r, L.d, x);
@@ -89,7 +95,7 @@ int smooth(const pyn_mg* g, MgLevel& L, const double* b, double* x, bool fresh, 
     rho = rho_new;
   }
   if (want_resid) {
-    int rc = apply_op(L, L.d, L.w, st);
+    int rc = apply_op(g, L, L.d, L.w, st);
     if (rc) return rc;
     mg_resid_kernel<<<L.vgrid, BLK, 0, st>>>(L.n, L.w, L.r, nullptr, nullptr);
     PYN_CHECK_LAUNCH();
@@ -113,11 +119,16 @@ int cycle(pyn_mg* g, int l, const double* b, double* x, cudaStream_t st) {
   MgLevel& C = g->L[l + 1];
   rc = pyn_spmv_planned(L.Rplan, L.Rind, L.Rval, L.r, C.r, PYN_SPMV_SET, 0.0, 0.0, nullptr, st);
   if (rc) return rc;
+  if (l == 0 && g->comm && g->comm->world > 1) {   // every rank restricted its own strip: sum, then all run the same coarse cycle
+    PYN_REQUIRE(C.n < 2147483647LL, "coarse level too large for one all-reduce");
+    rc = pyn::comm_allreduce_sum(g->comm, C.r, (int)C.n, st);
+    if (rc) return rc;
+  }
   rc = cycle(g, l + 1, C.r, C.x, st);
   if (rc) return rc;
   rc = pyn_spmv_planned(L.Pplan, L.Pind, L.Pval, C.x, L.d, PYN_SPMV_SET, 0.0, 0.0, nullptr, st);
   if (rc) return rc;
-  rc = apply_op(L, L.d, L.w, st);
+  rc = apply_op(g, L, L.d, L.w, st);
   if (rc) return rc;
   mg_resid_kernel<<<L.vgrid, BLK, 0, st>>>(L.n, L.w, L.r, L.d, x);
   PYN_CHECK_LAUNCH();
@@ -191,6 +202,13 @@ int pyn_mg_set_coarse_inverse(pyn_mg* g, const double* d_Ainv) {
   PYN_REQUIRE(g, "mg is NULL");
   PYN_REQUIRE(!d_Ainv || g->L[g->nlev - 1].n < (1 << 15), "coarsest level too large for a dense inverse");
   g->Ainv = d_Ainv;
+  return PYN_OK;
+}
+
+int pyn_mg_set_dist(pyn_mg* g, const pyn_comm* comm, const pyn_halo* halo, int ncomp) {
+  PYN_REQUIRE(g && comm, "bad arguments");
+  PYN_REQUIRE(comm->world == 1 || (halo && ncomp >= 1 && ncomp <= PYN_HALO_MAX_COMP), "halo plan required for world > 1");
+  g->comm = comm; g->halo = comm->world > 1 ? halo : nullptr; g->halo_comp = ncomp;
   return PYN_OK;
 }
 

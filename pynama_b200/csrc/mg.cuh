@@ -1,5 +1,6 @@
 // Geometric p/h-multigrid V-cycle used as the preconditioner of CG (`-pc_type mg`): see mg.cu.
 #pragma once
+#include "dist.cuh"
 #include "spmv.cuh"
 #include "tmat.cuh"
 
@@ -29,6 +30,12 @@ struct pyn_mg {
   int nlev, degree;
   double ratio;               // Chebyshev interval [lmax / ratio, lmax]
   MgLevel L[PYN_MG_MAX_LEVELS];
+  // Partitioned fine level (multi-GPU): level 0 lives on this rank's strip -- its operator needs the ghost entries of
+  // the input refreshed (halo) and the restricted residual is summed over the ranks (comm) -- while every coarser
+  // level is REPLICATED: each rank runs the same coarse cycle on the whole mesh and interpolates to its own strip.
+  const pyn_comm* comm;
+  const pyn_halo* halo;
+  int halo_comp;
   const double* Ainv;         // dense inverse of the coarsest operator on its unknowns, [n_c][n_c] (borrowed)
   double* pool;               // owned: all work vectors
   int64_t launches_per_apply;

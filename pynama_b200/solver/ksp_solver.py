@@ -108,11 +108,10 @@ class KspSolver(object):
                 raise Exception(f"KSP preonly with PC {pc} is not available on the device path")
             self.logger.info("preonly+lu requested: served by device CG (multigrid or Jacobi) to rtol %g + iterative "
                              "refinement (no sparse direct factorisation on the device path)", self.DIRECT_RTOL)
-            # one GPU: the multigrid V-cycle makes "solve to round-off" affordable (tens of iterations instead of tens
-            # of thousands); it needs the case's mesh, which the case layer supplies right after createSolver
+            # the multigrid V-cycle makes "solve to round-off" affordable (tens of iterations instead of tens of
+            # thousands); it needs the case's mesh, which the case layer supplies right after createSolver
             # (setUpMultigrid) -- a solver used on its own falls back to Jacobi at the first solve
-            dist_ = getattr(self.comm, "dist", None)
-            pc = "mg" if dist_ is None and Options().getString("pc_direct_standin", "mg") == "mg" else "jacobi"
+            pc = "mg" if Options().getString("pc_direct_standin", "mg") == "mg" else "jacobi"
             ksp_type, rtol, max_it = "cg", self.DIRECT_RTOL, self.DIRECT_MAX_IT
             self._direct = True
         if ksp_type not in be.Ksp.TYPES:

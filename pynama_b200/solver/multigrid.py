@@ -84,21 +84,28 @@ class Hierarchy(object):
     kind "KFS": the free-slip stage K + Kfs (unknowns = FREE and TANGENT dofs)."""
 
     def __init__(self, fem, kind, csr, degree=3, ratio=10.0, coarse_cells=1024, power_its=30):
-        if fem.dom.partition is not None:
-            raise Exception("-pc_type mg runs on one GPU; use -pc_type jacobi on a partitioned mesh")
+        if getattr(fem.dom, "nx", None) is None:
+            raise Exception("-pc_type mg needs a box mesh (coarse meshes are generated, not read)")
         self.kind, self.degree, self.ratio = kind, int(degree), float(ratio)
         self.levels = []
-        seq = coarsening_sequence(fem.dom.nx, fem.dom.ny, fem.dom.getNGL(), coarse_cells)
+        # Partitioned mesh: level 0 is this rank's strip (halo exchange before each fine product, restricted residual
+        # summed over the ranks); the coarse levels are REPLICATED -- every rank builds them on the whole mesh and
+        # runs the same coarse cycle (a 2-D coarse hierarchy is a few per cent of the fine level's work and memory).
+        self.dist = fem.comm.dist if fem.dom.partition is not None else None
+        seq = coarsening_sequence(fem.dom.nx, fem.dom.ny_global, fem.dom.getNGL(), coarse_cells)
         self.sequence = seq
         for i, (nx, ny, ngl) in enumerate(seq):
             L = _Level()
             if i == 0:
+                self._fine = L
                 L.fem, L.csr = fem, csr
             else:
                 L.fem = self._coarse_case(fem, nx, ny, ngl)
                 L.csr = self._coarse_operator(L.fem)
             cls = L.fem.mat.dofClasses
             L.free = (cls == 0) if kind == "K" else (cls < 2)
+            if i == 0 and self.dist is not None:       # unknowns of this rank: owned rows only
+                L.free = L.free & self.dist.owned_rows(fem.dim).bool()
             L.n = int(cls.numel())
             diag = L.csr.diagonal()
             L.dinv = torch.where(L.free, 1.0 / diag, torch.zeros_like(diag)).contiguous()
@@ -118,6 +125,8 @@ class Hierarchy(object):
             call("pyn_mg_set_transfer", self._h, i, L.P.plan(), be.ptr(L.P.indices), be.ptr(L.P.data), L.R.plan(),
                  be.ptr(L.R.indices), be.ptr(L.R.data))
         call("pyn_mg_set_coarse_inverse", self._h, be.ptr(self.Ainv))
+        if self.dist is not None:
+            call("pyn_mg_set_dist", self._h, self.dist._comm, self.dist._halo, int(fem.dim))
 
     def __del__(self):
         try:
@@ -140,6 +149,7 @@ class Hierarchy(object):
                 cfg["domain"]["box-mesh"][k] = fem.opts[k]
         opts = {k: v for k, v in fem.opts.items() if k not in ("ngl", "nelem", "chart", "lower", "upper")}
         opts["case"] = fem.case
+        opts["serial"] = True          # never partitioned: on N ranks every rank holds the whole coarse level
         c = type(fem)(cfg, **opts)
         c.setUpGeneral()
         c.setUpBoundaryConditions()
@@ -166,12 +176,23 @@ class Hierarchy(object):
         g = torch.Generator(device=L.dinv.device).manual_seed(20260)
         x = torch.randn(L.n, dtype=torch.float64, device=L.dinv.device, generator=g) * L.free
         y = torch.empty_like(x)
+        dist_ = self.dist if L is self._fine else None     # partitioned fine level: ghosts refreshed, norms all-reduced
+
+        def norm(v):
+            s2 = float((v * v).sum())
+            if dist_ is not None:
+                s2 = dist_.allreduce_sum([s2])[0]
+            return s2 ** 0.5
+
         lam = 1.0
         for _ in range(its):
+            if dist_ is not None:
+                dist_.exchange(x, L.fem.dim)
             L.csr.mult(x, y)
             y *= L.dinv
-            lam = float(torch.linalg.vector_norm(y) / torch.linalg.vector_norm(x))
-            x = y / torch.linalg.vector_norm(y)
+            ny_ = norm(y)
+            lam = ny_ / norm(x * L.free)
+            x = y / ny_
         return 1.1 * lam
 
     def _transfer(self, Lf, Lc):

@@ -121,6 +121,44 @@ def main():
     dofs, vals = dc.gather_owned(fem.vort, 1)
     assert rel(vals, w_o[dofs]) < 1e-8, rel(vals, w_o[dofs])
 
+    # ---- -pc_type mg on the partitioned mesh: distributed fine level, replicated coarse levels --------------------
+    Options.clear()
+    for k, v in dict(ksp_type="cg", pc_type="mg", ksp_rtol=1e-12, ksp_max_it=500, pc_mg_coarse_cells=16).items():
+        Options.setValue(k, v)
+    nxm, nm = 16, 5
+    cm = copy.deepcopy(cfg("cavity"))
+    cm["domain"]["box-mesh"]["nelem"] = [nxm, nxm]
+    cm["domain"]["ngl"] = nm
+    cm["material-properties"] = {"rho": 1.0, "mu": 0.01}
+    fm_ = Cavity(cm, case="cavity")
+    fm_.setUp()
+    fm_.setUpSolver()
+    partm, dcm = fm_.dom.partition, fm_.comm.dist
+    mm = o.BoxMesh([nxm, nxm], [0, 0], [1, 1], nm)
+    matsm, opsm = o.assemble_noslip(mm), o.assemble_operators(mm)
+    hK = fm_.solver._ksp._mg
+    assert hK.sequence == o.mg_coarsening_sequence(nxm, nxm, nm, 16)
+    pcK = o.MultigridPC(nxm, nxm, nm, "K", coarse_cells=16, lmax=[L.lmax for L in hK.levels])
+    bglob = np.random.default_rng(21).standard_normal(2 * mm.nnodes)
+    x_o, its_o, reason_o, _ = o.ksp_cg_jacobi(matsm["K"], bglob, rtol=1e-12, pc=pcK)
+    l2g2m = (partm.local_to_global()[:, None] * 2 + np.arange(2)).reshape(-1)
+    from pynama_b200 import backend as be
+    xl = be.empty(len(l2g2m))
+    res = fm_.solver._ksp.solve(be.to_device(bglob[l2g2m]), xl)
+    assert res.reason == reason_o == 2 and abs(res.its - its_o) <= 1, (res.its, its_o)
+    dofs, vals = dcm.gather_owned(xl, 2)
+    assert rel(vals, x_o[dofs]) < 1e-10, rel(vals, x_o[dofs])
+    vbm, fdm, fvm = o.cavity_wall_vectors(mm)
+    vortm = np.random.default_rng(5).standard_normal(mm.nnodes)
+    velm_o, _, _ = o.solve_kle_noslip(matsm, opsm, vbm, fdm, fvm, vortm)
+    wm = fm_.vort.duplicate()
+    wm.setArray(vortm[partm.local_to_global()] * partm.owned_mask())
+    fm_.solveKLE(0.0, wm)
+    assert fm_.solver.reason > 0 and fm_.solverFS.reason > 0 and fm_.solver.its < 150 and fm_.solverFS.its < 150
+    dofs, vals = dcm.gather_owned(fm_.vel, 2)
+    assert rel(vals, velm_o[dofs]) < 1e-10, rel(vals, velm_o[dofs])
+    del fm_
+
     # ---- Taylor-Green, adaptive time step (the error norm is all-reduced) -----------------------------------------
     Options.clear()
     for k, v in dict(ksp_type="cg", pc_type="jacobi", ksp_rtol=1e-12, ksp_max_it=50000, ts_dt=0.01).items():
