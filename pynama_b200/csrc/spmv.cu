@@ -114,8 +114,10 @@ __global__ void plan_maxrow_kernel(int64_t nrows, const int64_t* __restrict__ pt
   if ((threadIdx.x & 31) == 0 && m > 0) atomicMax(out, m);
 }
 
-// blk_row[b] = first row whose first non-zero lies at or after b*chunk
-__global__ void plan_rows_kernel(int64_t nrows, const int64_t* __restrict__ ptr, int chunk, int nblk,
+// Chunks are cut by WEIGHT: a stored entry counts 1, a row counts `w`, so that a chunk holds at most `chunk` entries
+// AND at most chunk / w rows -- a run of empty rows (boundary-only matrices, the restriction of one strip) is spread over
+// many CTAs instead of landing in one.  blk_row[b] = first row whose weight offset ptr[r] + r w is >= b * chunk.
+__global__ void plan_rows_kernel(int64_t nrows, const int64_t* __restrict__ ptr, int chunk, int w, int nblk,
                                  int* __restrict__ blk_row) {
   for (int b = blockIdx.x * blockDim.x + threadIdx.x; b <= nblk; b += gridDim.x * blockDim.x) {
     if (b == nblk) { blk_row[b] = (int)nrows; continue; }
@@ -123,7 +125,7 @@ __global__ void plan_rows_kernel(int64_t nrows, const int64_t* __restrict__ ptr,
     int64_t lo = 0, hi = nrows;
     while (lo < hi) {
       const int64_t mid = (lo + hi) >> 1;
-      if (ptr[mid] < key) lo = mid + 1; else hi = mid;
+      if (ptr[mid] + mid * w < key) lo = mid + 1; else hi = mid;
     }
     blk_row[b] = (int)lo;
   }
@@ -152,21 +154,23 @@ extern "C" int pyn_spmv_plan_create(int64_t nrows, const int64_t* d_ptr, int64_t
   int chunk = pass - maxrow;
   if (chunk < pass / 2) chunk = pass / 2;
   p->chunk = chunk;
-  const int64_t nb = nnz > 0 ? (nnz + chunk - 1) / chunk : 1;
+  const int roww = chunk / pyn::SP_RCAP > 1 ? chunk / pyn::SP_RCAP : 1;       // rows per chunk <= SP_RCAP
+  const int64_t nb = (nnz + nrows * roww + chunk - 1) / chunk;
   PYN_REQUIRE(nb < 2147483647LL, "matrix too large for one SpMV plan");
   p->nblk = (int)nb;
   PYN_CHECK_CUDA(cudaMalloc(&p->blk_row, sizeof(int) * (nb + 1)));
-  plan_rows_kernel<<<pyn::grid_for(nb + 1, 256), 256, 0, st>>>(nrows, d_ptr, chunk, p->nblk, p->blk_row);
+  plan_rows_kernel<<<pyn::grid_for(nb + 1, 256), 256, 0, st>>>(nrows, d_ptr, chunk, roww, p->nblk, p->blk_row);
   PYN_CHECK_LAUNCH();
   {  // bulk-copy pipeline: its own finer chunk table, first non-zero of every chunk, whether every chunk fits a stage
     int bchunk = pyn::SB_CHUNK - maxrow;
     const bool fits = bchunk >= pyn::SB_CHUNK / 2;
     if (!fits) bchunk = pyn::SB_CHUNK / 2;
-    const int64_t nbb = nnz > 0 ? (nnz + bchunk - 1) / bchunk : 1;
+    const int broww = bchunk / pyn::SB_RCAP > 1 ? bchunk / pyn::SB_RCAP : 1;
+    const int64_t nbb = (nnz + nrows * broww + bchunk - 1) / bchunk;
     PYN_REQUIRE(nbb < 2147483647LL, "matrix too large for one SpMV plan");
     p->nbblk = (int)nbb;
     PYN_CHECK_CUDA(cudaMalloc(&p->brow, sizeof(int) * (nbb + 1)));
-    plan_rows_kernel<<<pyn::grid_for(nbb + 1, 256), 256, 0, st>>>(nrows, d_ptr, bchunk, p->nbblk, p->brow);
+    plan_rows_kernel<<<pyn::grid_for(nbb + 1, 256), 256, 0, st>>>(nrows, d_ptr, bchunk, broww, p->nbblk, p->brow);
     PYN_CHECK_LAUNCH();
     PYN_CHECK_CUDA(cudaMalloc(&p->bp0, sizeof(long long) * (nbb + 1)));
     int* d_big = nullptr;

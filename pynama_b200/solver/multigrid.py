@@ -204,6 +204,8 @@ class Hierarchy(object):
         keep = Lf.free[r2] & Lc.free[c2]
         r2, c2, v2 = r2[keep].to(torch.int32).contiguous(), c2[keep].to(torch.int32).contiguous(), v2[keep].contiguous()
         Lf.P = be.coo_to_csr(r2, c2, v2, (Lf.n, Lc.n), "P")
+        # (R of a strip has no entries in the rows of coarse dofs outside the strip; the SpMV plan cuts its chunks by
+        # rows as well as by stored entries, so those runs of empty rows are spread over many CTAs)
         Lf.R = be.coo_to_csr(c2, r2, v2, (Lc.n, Lf.n), "R")
 
     def _coarse_inverse(self, L):
