@@ -191,16 +191,20 @@ __device__ __forceinline__ void cp_async_zfill(double* smem_dst, const double* g
   asm volatile("cp.async.ca.shared.global [%0], [%1], %2, %3;" ::"r"(d), "l"(gsrc), "n"(BYTES), "r"(n) : "memory");
 }
 
-template <int CD, int PMAX, int MB>
-__global__ void __launch_bounds__(EM_W * 32, 3)
+// AG: the A fragments stay in global memory and are read through L1/L2 (element matrices of ngl 8-9: 135-220 kB of
+// fragments + the warps' X buffers do not fit in shared memory together; the re-reads cost ne/16 x |A| ~ 1.5 GB of L2
+// traffic per product at 16 M dofs, against 30+ GB of the CSR stream these orders used before).
+template <int CD, int PMAX, int MB, bool AG = false>
+__global__ void __launch_bounds__(EM_W * 32, AG ? 1 : 3)
 eop_apply_mma_kernel(pyn::TmatView m, const double* __restrict__ x, const int* __restrict__ done, int RB, int KB) {
   extern __shared__ __align__(16) double sm[];
   if (done && *done) return;
   const int NR = m.NR, NC = m.NC, NCP = m.NCP, nn = m.nn;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  double* Af = sm;                                                // [RB][KB][32]
-  double* Xw = sm + RB * KB * 32 + warp * (2 * EM_NE * NCP);      // this warp's [2][EM_NE][NCP]
-  for (int i = tid; i < RB * KB * 32; i += EM_W * 32) Af[i] = m.Et[i];
+  const double* Af = AG ? m.Et : sm;                              // [RB][KB][32]
+  double* Xw = sm + (AG ? 0 : RB * KB * 32) + warp * (2 * EM_NE * NCP);      // this warp's [2][EM_NE][NCP]
+  if (!AG)
+    for (int i = tid; i < RB * KB * 32; i += EM_W * 32) sm[i] = m.Et[i];
   for (int i = lane; i < 2 * EM_NE * (NCP - NC); i += 32) {        // pad columns of X: zero for the life of the CTA
     const int el = i / (NCP - NC);
     Xw[el * NCP + NC + (i - el * (NCP - NC))] = 0.0;
@@ -272,7 +276,7 @@ eop_apply_mma_kernel(pyn::TmatView m, const double* __restrict__ x, const int* _
         for (int nb = 0; nb < EM_NBW; ++nb) b[nb] = bp[nb * 8 * NCP + kb * 4];
         double a[MB];
 #pragma unroll
-        for (int i = 0; i < MB; ++i) a[i] = (rb0 + i < RB) ? ap[(i * KB + kb) * 32] : 0.0;
+        for (int i = 0; i < MB; ++i) a[i] = (rb0 + i < RB) ? (AG ? __ldg(ap + (i * KB + kb) * 32) : ap[(i * KB + kb) * 32]) : 0.0;
 #pragma unroll
         for (int i = 0; i < MB; ++i)
 #pragma unroll
@@ -359,7 +363,9 @@ struct MmaShape {
   int RB, KB, NCP, MB, P;
   size_t smem;
   bool ok;
+  bool ag;     // A fragments from L1/L2 (they do not fit in shared memory next to the X buffers)
 };
+constexpr int EM_PMAX_AG = 48;
 MmaShape mma_shape(int nn, int NR, int NC) {
   MmaShape s;
   s.RB = (NR + 7) / 8;
@@ -375,24 +381,35 @@ MmaShape mma_shape(int nn, int NR, int NC) {
   s.P = (EM_NE * nn + 31) / 32;
   s.smem = sizeof(double) * ((size_t)s.RB * s.KB * 32 + (size_t)EM_W * 2 * EM_NE * s.NCP);
   s.ok = s.smem <= EO_SMEM_MAX && s.P <= EM_PMAX;
+  s.ag = false;
+  if (!s.ok) {   // large element matrices: X buffers only in shared memory, MB in {4, 7}
+    const size_t xs = sizeof(double) * (size_t)EM_W * 2 * EM_NE * s.NCP;
+    if (xs <= EO_SMEM_MAX && s.P <= EM_PMAX_AG) {
+      s.ok = s.ag = true;
+      s.smem = xs;
+      const int w4 = (s.RB + 3) / 4 * 4 - s.RB, w7 = (s.RB + 6) / 7 * 7 - s.RB;
+      s.MB = w7 <= w4 ? 7 : 4;
+    }
+  }
   return s;
 }
-template <int CD, int PMAX, int MB>
+template <int CD, int PMAX, int MB, bool AG = false>
 int mma_launch(const pyn_tmat* m, const double* d_x, const int* d_done, cudaStream_t st) {
-  eop_apply_mma_kernel<CD, PMAX, MB><<<m->grid_apply, 32 * EM_W, m->smem, st>>>(pyn::view_of(m), d_x, d_done, m->RB,
-                                                                                 m->KB);
+  eop_apply_mma_kernel<CD, PMAX, MB, AG><<<m->grid_apply, 32 * EM_W, m->smem, st>>>(pyn::view_of(m), d_x, d_done, m->RB,
+                                                                                     m->KB);
   PYN_CHECK_LAUNCH();
   return PYN_OK;
 }
-template <int CD, int PMAX, int MB>
+template <int CD, int PMAX, int MB, bool AG = false>
 int mma_prepare(pyn_tmat* m) {
   int occ = 0;
-  PYN_CHECK_CUDA(cudaFuncSetAttribute(eop_apply_mma_kernel<CD, PMAX, MB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  PYN_CHECK_CUDA(cudaFuncSetAttribute(eop_apply_mma_kernel<CD, PMAX, MB, AG>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       (int)EO_SMEM_MAX));
-  PYN_CHECK_CUDA(cudaFuncSetAttribute(eop_apply_mma_kernel<CD, PMAX, MB>,
-                                      cudaFuncAttributePreferredSharedMemoryCarveout,
-                                      (int)cudaSharedmemCarveoutMaxShared));
-  PYN_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, eop_apply_mma_kernel<CD, PMAX, MB>, 32 * EM_W,
+  if (!AG)   // the AG variant keeps what shared memory it does not need as L1 for the A fragments
+    PYN_CHECK_CUDA(cudaFuncSetAttribute(eop_apply_mma_kernel<CD, PMAX, MB, AG>,
+                                        cudaFuncAttributePreferredSharedMemoryCarveout,
+                                        (int)cudaSharedmemCarveoutMaxShared));
+  PYN_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, eop_apply_mma_kernel<CD, PMAX, MB, AG>, 32 * EM_W,
                                                                m->smem));
   const int64_t nstages = (m->topo->ne + EM_NE - 1) / EM_NE;
   const int64_t need = (nstages + EM_W - 1) / EM_W;
@@ -442,8 +459,21 @@ int eop_prepare_any(pyn_tmat* m) { PYN_EO_DISPATCH(eop_prepare, m); }
     case 6: return FN<CDV, PV, 6>(__VA_ARGS__);                                      \
     default: return FN<CDV, PV, 7>(__VA_ARGS__);                                     \
   }
+#define PYN_EM_AG_CASE(FN, CDV, ...)                                                 \
+  if (m->P <= 32) {                                                                  \
+    if (m->MB == 4) return FN<CDV, 32, 4, true>(__VA_ARGS__);                        \
+    return FN<CDV, 32, 7, true>(__VA_ARGS__);                                        \
+  } else {                                                                           \
+    if (m->MB == 4) return FN<CDV, 48, 4, true>(__VA_ARGS__);                        \
+    return FN<CDV, 48, 7, true>(__VA_ARGS__);                                        \
+  }
 #define PYN_EM_DISPATCH(FN, ...)                                                     \
   do {                                                                               \
+    if (m->ag) {                                                                     \
+      if (m->cdof == 1) { PYN_EM_AG_CASE(FN, 1, __VA_ARGS__) }                       \
+      if (m->cdof == 2) { PYN_EM_AG_CASE(FN, 2, __VA_ARGS__) }                       \
+      PYN_EM_AG_CASE(FN, 3, __VA_ARGS__)                                             \
+    }                                                                                \
     if (m->P <= 8) {                                                                 \
       if (m->cdof == 1) { PYN_EM_CASE(FN, 1, 8, __VA_ARGS__) }                       \
       if (m->cdof == 2) { PYN_EM_CASE(FN, 2, 8, __VA_ARGS__) }                       \
@@ -469,7 +499,10 @@ int tmat_init(pyn_tmat* m, const double* d_E, double sign, cudaStream_t st) {
   const pyn_topo* t = m->topo;
   m->NR = m->rdof * t->nn; m->NC = m->cdof * t->nn;
   const MmaShape ms = mma_shape(t->nn, m->NR, m->NC);
-  m->mma = ms.ok && !getenv("PYN_EO_SIMT");      // PYN_EO_SIMT=1: keep the DFMA kernel (A/B measurements)
+  // the L2-fed DMMA variant only where the DFMA kernel does not fit either (ngl 8-9); PYN_EO_SIMT=1: A/B measurements
+  const bool simt_fits = eop_shape(m->NR, m->NC).smem <= EO_SMEM_MAX;
+  m->mma = ms.ok && (!ms.ag || !simt_fits) && !(getenv("PYN_EO_SIMT") && simt_fits);
+  m->ag = m->mma && ms.ag;
   {
     // Row map of Ye: one dense array per node kind for square 2-D elements in the reference's local order (4 vertices,
     // 4 x (n-2) edge nodes, (n-2)^2 interior nodes); anything else, or PYN_EO_AOS=1, keeps element-major records.

@@ -26,6 +26,7 @@ struct pyn_tmat {
   int rdof, cdof;
   int NR, NC, NRP, NCP;      // element matrix rows / cols; rows padded to a multiple of R, cols to 2*odd
   int R, W;                  // rows per register block (8 | 10), warps per CTA of phase 1
+  int ag;                    // DMMA variant with the A fragments read through L1/L2 instead of shared memory (ngl 8-9)
   int mma, RB, KB, MB, P;    // DMMA variant of phase 1: 8-row blocks, 4-column blocks (Et then holds the fragments),
                              // row blocks per pass, gathered pairs per lane and stage
   double* Et;                // owned: sign * E transposed, [NCP][NRP], zero padded

@@ -223,7 +223,7 @@ def test_template_assembly_is_bit_identical(be, nx, ny, n):
     np.testing.assert_array_equal(B.data.cpu().numpy(), A.data.cpu().numpy())
 
 
-@pytest.mark.parametrize("nx,ny,n", [(8, 8, 3), (6, 7, 5), (9, 6, 2), (13, 11, 4), (4, 5, 7)])
+@pytest.mark.parametrize("nx,ny,n", [(8, 8, 3), (6, 7, 5), (9, 6, 2), (13, 11, 4), (4, 5, 7), (5, 4, 8), (4, 3, 9)])
 def test_template_operator_matches_csr(be, nx, ny, n):
     """y = A x through the element operator (element products + per-node gather on interior nodes, CSR rows of the
     boundary-affected nodes) equals the CSR-stream product to round-off, for every matrix shape of the path, in every epilogue mode; and CG
