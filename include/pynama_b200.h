@@ -343,7 +343,9 @@ int pyn_comm_set_peer(pyn_comm* c, pyn_peer* p);
 int pyn_halo_exchange(const pyn_halo* h, double* d_vec, int ncomp, void* stream);
 int64_t pyn_halo_bytes(const pyn_halo* h, int ncomp);
 int pyn_ksp_set_dist(pyn_ksp* k, const pyn_comm* comm, const pyn_halo* halo, int ncomp, const uint8_t* d_owned_rows);
-int pyn_mg_set_dist(pyn_mg* g, const pyn_comm* comm, const pyn_halo* halo, int ncomp);
+int pyn_mg_set_dist(pyn_mg* g, const pyn_comm* comm, const pyn_halo* halo, int ncomp);   /* level 0 */
+/* levels 0 .. k (the fine mesh at decreasing order) may each be partitioned with their own halo plan; the rest is replicated */
+int pyn_mg_set_level_dist(pyn_mg* g, int level, const pyn_comm* comm, const pyn_halo* halo, int ncomp);
 
 #ifdef __cplusplus
 }

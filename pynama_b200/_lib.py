@@ -126,6 +126,7 @@ _SIGNATURES = {
     "pyn_mg_destroy": (C.c_int, [c_vp]),
     "pyn_ksp_set_mg": (C.c_int, [c_vp, c_vp]),
     "pyn_mg_set_dist": (C.c_int, [c_vp, c_vp, c_vp, C.c_int]),
+    "pyn_mg_set_level_dist": (C.c_int, [c_vp, C.c_int, c_vp, c_vp, C.c_int]),
     "pyn_ksp_set_dist": (C.c_int, [c_vp, c_vp, c_vp, C.c_int, c_vp]),
 }
 

@@ -546,7 +546,7 @@ int pyn_ksp_solve(pyn_ksp* k, const double* d_b, double* d_x, pyn_ksp_result* re
   int64_t launches = 0;
   const bool dist = k->comm && k->comm->world > 1;
   const bool guess = k->opts.nonzero_guess != 0;
-  if (k->mg && dist) PYN_REQUIRE(k->mg->comm == k->comm, "multigrid hierarchy of a partitioned mesh: attach the communicator (pyn_mg_set_dist)");
+  if (k->mg && dist) PYN_REQUIRE(k->mg->L[0].comm == k->comm, "multigrid hierarchy of a partitioned mesh: attach the communicator (pyn_mg_set_dist)");
   if (guess) {   // r0 = b - A x0 with the contents of d_x (KSPSetInitialGuessNonzero)
     cg_reset_kernel<<<1, 1, 0, st>>>(k->B.st);
     copy_kernel<<<k->vgrid, BLK, 0, st>>>(k->n, d_x, k->B.p);

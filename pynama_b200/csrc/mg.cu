@@ -69,8 +69,9 @@ __global__ void mg_dense_kernel(int n, const double* __restrict__ Ainv, const do
 // y = A_l x.  On a partitioned fine level the ghost entries of x are refreshed from their owners first (x is one of
 // the level's work vectors: only its ghost entries change).
 int apply_op(const pyn_mg* g, const MgLevel& L, double* x, double* y, cudaStream_t st) {
-  if (g->halo && &L == &g->L[0]) {
-    int rc = pyn::halo_exchange(g->halo, x, g->halo_comp, st);
+  (void)g;
+  if (L.halo) {
+    int rc = pyn::halo_exchange(L.halo, x, L.halo_comp, st);
     if (rc) return rc;
   }
   if (L.tmat) return pyn_tmat_mult(L.tmat, x, y, PYN_SPMV_SET, 0.0, 0.0, nullptr, st);
@@ -117,15 +118,23 @@ int cycle(pyn_mg* g, int l, const double* b, double* x, cudaStream_t st) {
   int rc = smooth(g, L, b, x, true, true, st);
   if (rc) return rc;
   MgLevel& C = g->L[l + 1];
+  if (L.halo && C.halo) {   // strip -> strip: R gathers the residual of every local fine node, ghosts included
+    rc = pyn::halo_exchange(L.halo, L.r, L.halo_comp, st);
+    if (rc) return rc;
+  }
   rc = pyn_spmv_planned(L.Rplan, L.Rind, L.Rval, L.r, C.r, PYN_SPMV_SET, 0.0, 0.0, nullptr, st);
   if (rc) return rc;
-  if (l == 0 && g->comm && g->comm->world > 1) {   // every rank restricted its own strip: sum, then all run the same coarse cycle
+  if (L.halo && !C.halo) {   // strip -> replicated: every rank restricted its own strip: sum, then all run the same cycle
     PYN_REQUIRE(C.n < 2147483647LL, "coarse level too large for one all-reduce");
-    rc = pyn::comm_allreduce_sum(g->comm, C.r, (int)C.n, st);
+    rc = pyn::comm_allreduce_sum(L.comm, C.r, (int)C.n, st);
     if (rc) return rc;
   }
   rc = cycle(g, l + 1, C.r, C.x, st);
   if (rc) return rc;
+  if (C.halo) {              // P reads the coarse correction at every local coarse node, ghosts included
+    rc = pyn::halo_exchange(C.halo, C.x, C.halo_comp, st);
+    if (rc) return rc;
+  }
   rc = pyn_spmv_planned(L.Pplan, L.Pind, L.Pval, C.x, L.d, PYN_SPMV_SET, 0.0, 0.0, nullptr, st);
   if (rc) return rc;
   rc = apply_op(g, L, L.d, L.w, st);
@@ -205,11 +214,16 @@ int pyn_mg_set_coarse_inverse(pyn_mg* g, const double* d_Ainv) {
   return PYN_OK;
 }
 
-int pyn_mg_set_dist(pyn_mg* g, const pyn_comm* comm, const pyn_halo* halo, int ncomp) {
-  PYN_REQUIRE(g && comm, "bad arguments");
+int pyn_mg_set_level_dist(pyn_mg* g, int l, const pyn_comm* comm, const pyn_halo* halo, int ncomp) {
+  PYN_REQUIRE(g && comm && l >= 0 && l < g->nlev, "bad arguments");
   PYN_REQUIRE(comm->world == 1 || (halo && ncomp >= 1 && ncomp <= PYN_HALO_MAX_COMP), "halo plan required for world > 1");
-  g->comm = comm; g->halo = comm->world > 1 ? halo : nullptr; g->halo_comp = ncomp;
+  PYN_REQUIRE(l == 0 || g->L[l - 1].halo || comm->world == 1, "partitioned levels must be the first ones of the hierarchy");
+  g->L[l].comm = comm; g->L[l].halo = comm->world > 1 ? halo : nullptr; g->L[l].halo_comp = ncomp;
   return PYN_OK;
+}
+
+int pyn_mg_set_dist(pyn_mg* g, const pyn_comm* comm, const pyn_halo* halo, int ncomp) {
+  return pyn_mg_set_level_dist(g, 0, comm, halo, ncomp);
 }
 
 int pyn_mg_apply(pyn_mg* g, const double* d_r, double* d_z, void* stream) {

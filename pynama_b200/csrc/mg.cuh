@@ -24,18 +24,20 @@ struct MgLevel {
   const double* Rval;
   double *x, *r, *d, *w;      // owned work vectors (x of level 0 is the caller's z)
   int vgrid;
+  // Partitioned level (multi-GPU): the level lives on this rank's strip -- its operator needs the ghost entries of its
+  // input refreshed (halo); NULL: the level is replicated (every rank holds and computes all of it)
+  const pyn_comm* comm;
+  const pyn_halo* halo;
+  int halo_comp;
 };
 
 struct pyn_mg {
   int nlev, degree;
   double ratio;               // Chebyshev interval [lmax / ratio, lmax]
   MgLevel L[PYN_MG_MAX_LEVELS];
-  // Partitioned fine level (multi-GPU): level 0 lives on this rank's strip -- its operator needs the ghost entries of
-  // the input refreshed (halo) and the restricted residual is summed over the ranks (comm) -- while every coarser
-  // level is REPLICATED: each rank runs the same coarse cycle on the whole mesh and interpolates to its own strip.
-  const pyn_comm* comm;
-  const pyn_halo* halo;
-  int halo_comp;
+  // Multi-GPU: the first levels (the fine mesh at every order) keep the strip partition; from the first h-coarsened
+  // level on the hierarchy is REPLICATED: the restricted residual is summed over the ranks, every rank runs the same
+  // coarse cycle on the whole mesh and interpolates to its own strip.
   const double* Ainv;         // dense inverse of the coarsest operator on its unknowns, [n_c][n_c] (borrowed)
   double* pool;               // owned: all work vectors
   int64_t launches_per_apply;

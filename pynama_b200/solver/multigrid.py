@@ -61,10 +61,12 @@ def node_interpolation(dom_c, dom_f):
     lo, up = dom_c.lower, dom_c.upper
     hx, hy = (up[0] - lo[0]) / dom_c.nx, (up[1] - lo[1]) / dom_c.ny_global
     fx = torch.clamp(torch.floor((xy[:, 0] - lo[0]) / hx - 1e-9).to(torch.int64), 0, dom_c.nx - 1)
-    fy = torch.clamp(torch.floor((xy[:, 1] - lo[1]) / hy - 1e-9).to(torch.int64), 0, dom_c.ny - 1)
+    # dom_c may be a strip (its cell rows start at global row fy0): cells are addressed in its local numbering
+    fy0 = int(getattr(dom_c, "fy0", 0))
+    fy = torch.clamp(torch.floor((xy[:, 1] - lo[1]) / hy - 1e-9).to(torch.int64) - fy0, 0, dom_c.ny - 1)
     # element map of the reference: x = x0 + (1 - r) hx / 2  (SURVEY 8a'), r ascending with the 1-D node index
     r = 1.0 - 2.0 * (xy[:, 0] - (lo[0] + hx * fx)) / hx
-    s = 1.0 - 2.0 * (xy[:, 1] - (lo[1] + hy * fy)) / hy
+    s = 1.0 - 2.0 * (xy[:, 1] - (lo[1] + hy * (fy + fy0))) / hy
     nodes1d, _ = lobattoPoints(n)
     hr, hs = _lagrange(nodes1d, r), _lagrange(nodes1d, s)
     order = torch.as_tensor(localNodeOrder(n), device=xy.device)
@@ -83,7 +85,7 @@ class Hierarchy(object):
     """V-cycle levels of one solve of a case.  kind "K": the no-slip / Dirichlet solve (unknowns = FREE dofs);
     kind "KFS": the free-slip stage K + Kfs (unknowns = FREE and TANGENT dofs)."""
 
-    def __init__(self, fem, kind, csr, degree=3, ratio=10.0, coarse_cells=1024, power_its=30):
+    def __init__(self, fem, kind, csr, degree=3, ratio=10.0, coarse_cells=1024, power_its=30, partition_p_levels=True):
         if getattr(fem.dom, "nx", None) is None:
             raise Exception("-pc_type mg needs a box mesh (coarse meshes are generated, not read)")
         self.kind, self.degree, self.ratio = kind, int(degree), float(ratio)
@@ -96,16 +98,22 @@ class Hierarchy(object):
         self.sequence = seq
         for i, (nx, ny, ngl) in enumerate(seq):
             L = _Level()
+            # the fine mesh at lower orders keeps the strip partition of level 0 (same cell rows per rank, its own halo
+            # plan); the h-coarsened levels are replicated
+            same_mesh = (nx, ny) == (fem.dom.nx, fem.dom.ny_global)
             if i == 0:
                 self._fine = L
-                L.fem, L.csr = fem, csr
+                L.fem, L.csr, L.dist = fem, csr, self.dist
             else:
-                L.fem = self._coarse_case(fem, nx, ny, ngl)
+                part = self.dist is not None and same_mesh and partition_p_levels and i + 1 < len(seq)   # coarsest: dense, replicated
+                L.fem = self._coarse_case(fem, nx, ny, ngl, serial=not part)
                 L.csr = self._coarse_operator(L.fem)
+                L.dist = L.fem.comm.dist if part else None
             cls = L.fem.mat.dofClasses
-            L.free = (cls == 0) if kind == "K" else (cls < 2)
-            if i == 0 and self.dist is not None:       # unknowns of this rank: owned rows only
-                L.free = L.free & self.dist.owned_rows(fem.dim).bool()
+            L.bc = (cls == 0) if kind == "K" else (cls < 2)       # not prescribed (ghost entries included)
+            L.free = L.bc
+            if L.dist is not None:                     # unknowns of this rank: owned rows only
+                L.free = L.bc & L.dist.owned_rows(fem.dim).bool()
             L.n = int(cls.numel())
             diag = L.csr.diagonal()
             L.dinv = torch.where(L.free, 1.0 / diag, torch.zeros_like(diag)).contiguous()
@@ -125,8 +133,9 @@ class Hierarchy(object):
             call("pyn_mg_set_transfer", self._h, i, L.P.plan(), be.ptr(L.P.indices), be.ptr(L.P.data), L.R.plan(),
                  be.ptr(L.R.indices), be.ptr(L.R.data))
         call("pyn_mg_set_coarse_inverse", self._h, be.ptr(self.Ainv))
-        if self.dist is not None:
-            call("pyn_mg_set_dist", self._h, self.dist._comm, self.dist._halo, int(fem.dim))
+        for i, L in enumerate(self.levels):
+            if L.dist is not None:
+                call("pyn_mg_set_level_dist", self._h, i, L.dist._comm, L.dist._halo, int(fem.dim))
 
     def __del__(self):
         try:
@@ -139,7 +148,7 @@ class Hierarchy(object):
 
     # -- levels ---------------------------------------------------------------------------------------------------
     @staticmethod
-    def _coarse_case(fem, nx, ny, ngl):
+    def _coarse_case(fem, nx, ny, ngl, serial=True):
         import copy
         cfg = copy.deepcopy(fem.config)
         cfg["domain"]["ngl"] = ngl
@@ -149,7 +158,7 @@ class Hierarchy(object):
                 cfg["domain"]["box-mesh"][k] = fem.opts[k]
         opts = {k: v for k, v in fem.opts.items() if k not in ("ngl", "nelem", "chart", "lower", "upper")}
         opts["case"] = fem.case
-        opts["serial"] = True          # never partitioned: on N ranks every rank holds the whole coarse level
+        opts["serial"] = serial        # replicated level: on N ranks every rank holds the whole coarse level
         c = type(fem)(cfg, **opts)
         c.setUpGeneral()
         c.setUpBoundaryConditions()
@@ -176,7 +185,7 @@ class Hierarchy(object):
         g = torch.Generator(device=L.dinv.device).manual_seed(20260)
         x = torch.randn(L.n, dtype=torch.float64, device=L.dinv.device, generator=g) * L.free
         y = torch.empty_like(x)
-        dist_ = self.dist if L is self._fine else None     # partitioned fine level: ghosts refreshed, norms all-reduced
+        dist_ = L.dist                                     # partitioned level: ghosts refreshed, norms all-reduced
 
         def norm(v):
             s2 = float((v * v).sum())
@@ -201,11 +210,21 @@ class Hierarchy(object):
         r2 = (rows[:, None] * dim + torch.arange(dim, device=rows.device)).reshape(-1)
         c2 = (cols[:, None] * dim + torch.arange(dim, device=rows.device)).reshape(-1)
         v2 = vals[:, None].expand(-1, dim).reshape(-1)
+        i32 = lambda t: t.to(torch.int32).contiguous()
+        if Lc.dist is not None:
+            # strip -> strip: both operators GATHER over every local node of the other level, ghost entries included
+            # (refreshed by a halo exchange first), and write the rank's own unknowns: globally R is still P^T
+            kp = Lf.free[r2] & Lc.bc[c2]
+            kr = Lc.free[c2] & Lf.bc[r2]
+            Lf.P = be.coo_to_csr(i32(r2[kp]), i32(c2[kp]), v2[kp].contiguous(), (Lf.n, Lc.n), "P")
+            Lf.R = be.coo_to_csr(i32(c2[kr]), i32(r2[kr]), v2[kr].contiguous(), (Lc.n, Lf.n), "R")
+            return
         keep = Lf.free[r2] & Lc.free[c2]
-        r2, c2, v2 = r2[keep].to(torch.int32).contiguous(), c2[keep].to(torch.int32).contiguous(), v2[keep].contiguous()
+        r2, c2, v2 = i32(r2[keep]), i32(c2[keep]), v2[keep].contiguous()
         Lf.P = be.coo_to_csr(r2, c2, v2, (Lf.n, Lc.n), "P")
-        # (R of a strip has no entries in the rows of coarse dofs outside the strip; the SpMV plan cuts its chunks by
-        # rows as well as by stored entries, so those runs of empty rows are spread over many CTAs)
+        # (strip -> replicated: R of a strip has no entries in the rows of coarse dofs outside the strip; the SpMV plan
+        # cuts its chunks by rows as well as by stored entries, so those runs of empty rows are spread over many CTAs;
+        # the partial results of the ranks are then summed)
         Lf.R = be.coo_to_csr(c2, r2, v2, (Lc.n, Lf.n), "R")
 
     def _coarse_inverse(self, L):
