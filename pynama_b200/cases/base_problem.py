@@ -111,9 +111,10 @@ class BaseProblem(object):
         self.dom.setFemIndexing(self.ngl)
         if self.dom.partition is not None:
             from ..dist import DistContext
-            self.comm.dist = DistContext(self.dom.partition)
-            from .. import petsc_like
-            petsc_like.set_dist(self.comm.dist)      # Vec.norm / Vec.dot become global (owned entries, all-reduced)
+            self.comm.dist = DistContext(self.dom.partition, parent=self.opts.get("dist_parent"))
+            if self.opts.get("dist_parent") is None:     # (a coarse level of a multigrid hierarchy leaves the case's own)
+                from .. import petsc_like
+                petsc_like.set_dist(self.comm.dist)      # Vec.norm / Vec.dot become global (owned entries, all-reduced)
             self.logger.info(self.dom.partition.describe())
         if not self.comm.rank:
             self.logger.info("DMPlex dom created")

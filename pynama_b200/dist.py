@@ -26,19 +26,26 @@ def world_info():
 
 
 class DistContext(object):
-    def __init__(self, partition: StripPartition):
+    def __init__(self, partition: StripPartition, parent=None):
+        """parent: another context of the same job whose communicator and peer region this one shares (same strips at
+        another element order: the coarse levels of the multigrid hierarchy) -- only the halo plan is its own."""
         import torch.distributed as dist
         self.part = partition
         self.rank, self.world = partition.rank, partition.world
-        ident = C.create_string_buffer(128)
-        if self.world > 1:
-            if self.rank == 0:
-                call("pyn_comm_unique_id", ident)
-            box = [bytes(ident.raw)]
-            dist.broadcast_object_list(box, src=0)
-            ident = C.create_string_buffer(box[0], 128)
-        self._comm = C.c_void_p()
-        call("pyn_comm_create", ident, self.rank, self.world, C.byref(self._comm))
+        self._parent = parent
+        if parent is not None:
+            assert (parent.rank, parent.world) == (self.rank, self.world)
+            self._comm = parent._comm
+        else:
+            ident = C.create_string_buffer(128)
+            if self.world > 1:
+                if self.rank == 0:
+                    call("pyn_comm_unique_id", ident)
+                box = [bytes(ident.raw)]
+                dist.broadcast_object_list(box, src=0)
+                ident = C.create_string_buffer(box[0], 128)
+            self._comm = C.c_void_p()
+            call("pyn_comm_create", ident, self.rank, self.world, C.byref(self._comm))
         own = partition.owned_mask()
         self.n_owned = int(own.sum())
         self.owned = be.to_device(own.astype(np.uint8))
@@ -57,7 +64,9 @@ class DistContext(object):
         self._scal = be.empty(4)
         self._peer = None
         self.peer_memory = False
-        if self.world > 1 and os.environ.get("PYN_P2P", "1") not in ("0", "false", "off"):
+        if parent is not None:          # the parent's mailboxes were sized for its (finer) interface: large enough
+            self.peer_memory = parent.peer_memory
+        elif self.world > 1 and os.environ.get("PYN_P2P", "1") not in ("0", "false", "off"):
             self._attach_peer_memory(max([len(r) for _, _, r in lists] + [len(s) for _, s, _ in lists] + [1]))
 
     def _attach_peer_memory(self, max_nodes):
@@ -153,6 +162,6 @@ class DistContext(object):
             lib.pyn_comm_set_peer(self._comm, None)
             lib.pyn_peer_destroy(self._peer)
             self._peer = None
-        if getattr(self, "_comm", None):
+        if getattr(self, "_comm", None) and self._parent is None:
             lib.pyn_comm_destroy(self._comm)
-            self._comm = None
+        self._comm = None

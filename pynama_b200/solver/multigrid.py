@@ -156,9 +156,11 @@ class Hierarchy(object):
         for k in ("lower", "upper"):                       # keyword overrides of the fine case become the coarse config
             if k in fem.opts:
                 cfg["domain"]["box-mesh"][k] = fem.opts[k]
-        opts = {k: v for k, v in fem.opts.items() if k not in ("ngl", "nelem", "chart", "lower", "upper")}
+        opts = {k: v for k, v in fem.opts.items() if k not in ("ngl", "nelem", "chart", "lower", "upper", "dist_parent")}
         opts["case"] = fem.case
         opts["serial"] = serial        # replicated level: on N ranks every rank holds the whole coarse level
+        if not serial:
+            opts["dist_parent"] = fem.comm.dist       # same strips: share the communicator and the peer region
         c = type(fem)(cfg, **opts)
         c.setUpGeneral()
         c.setUpBoundaryConditions()
