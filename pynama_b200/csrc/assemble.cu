@@ -6,6 +6,8 @@
 // the node's sorted adjacency list, then writes the rows out compacted by the boundary-condition masks.  The
 // summation order is therefore exactly the reference's serial cell loop (base_problem.py:337,504,135) and the
 // result is bitwise reproducible run to run.
+#include <vector>
+
 #include <cub/cub.cuh>
 
 #include "common.cuh"
@@ -31,6 +33,9 @@ struct DescView {
   const double* coef;    // [ne][PYN_AFF_NCOEF]
   pyn::AffTables aff;
   int which;             // 0 K (2x2 blocks), 1 Rw, 2 Rd (2x1 blocks)
+  // signature tiles of the boundary map (structured meshes; NULL: not available)
+  const int *sig_nodes, *tile_sig, *tile_start, *tile_cnt;
+  int64_t ntiles;
 };
 
 // element block (rows of local node lr, columns of local node l) of one element from the affine closed form:
@@ -430,6 +435,122 @@ asm_interior_affine_kernel(pyn::TopoView t, DescView d, const int64_t* __restric
   }
 }
 
+// ---- fused integrate-and-assemble on a STRUCTURED mesh: nodes grouped by row signature ---------------------------------
+// The flat kernel above spends most of its instructions on finding out, per output block, which node it belongs to and
+// which of the node's elements contribute (and its element loop diverges).  On a structured mesh that information is the
+// same for every node of a row signature (topo.cuh: byte-identical incidence local indices and inverse maps).  Here a
+// WARP takes a tile of 32 nodes of ONE signature, one node per lane: the signature's contribution list -- read from its
+// representative node -- is uniform across the warp (no look-ups per lane, no divergence), the only per-lane data are
+// the node's row bases and the 13 (4) coefficients of its <= 4 elements, staged in shared memory lane-major
+// (conflict-free).  The lanes' blocks of AFF_PT consecutive positions go through a shared-memory tile so that the rows
+// leave as 64-byte (32-byte) segments instead of 32 scattered 16-byte stores.  Same order of additions per entry as
+// every other assembly kernel (ascending cell order): same bits.
+constexpr int SIG_W = 4;       // warps (= tiles) per CTA
+constexpr int SIG_PT = 4;      // adjacency positions per pass
+constexpr int SIG_KMAX = 4;    // incident elements per node (quadrilateral meshes; larger valence: flat kernel)
+
+template <int CD>
+__global__ void __launch_bounds__(SIG_W * 32)
+asm_sig_affine_kernel(pyn::TopoView t, DescView d, const int64_t* __restrict__ indptr, double* __restrict__ data) {
+  constexpr int RD = 2;
+  constexpr int NC = CD == 2 ? 13 : 4, C0 = CD == 2 ? 0 : 13;
+  constexpr int PR = CD == 2 ? pyn::PYN_AFF_PK : pyn::PYN_AFF_PR;
+  constexpr int AW = RD * CD;
+  extern __shared__ __align__(16) double sg_dyn[];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  double* s_cf = sg_dyn + (size_t)w * (SIG_KMAX * NC * 32);                              // [k][c][lane]
+  double* s_out = sg_dyn + (size_t)SIG_W * (SIG_KMAX * NC * 32) + (size_t)w * (32 * SIG_PT * AW);   // [lane][q][AW]
+  long long* s_base = reinterpret_cast<long long*>(sg_dyn + (size_t)SIG_W * (SIG_KMAX * NC * 32 + 32 * SIG_PT * AW)) + w * 64;
+  const int64_t tile = (int64_t)blockIdx.x * SIG_W + w;
+  if (tile >= d.ntiles) return;
+  const int sig = d.tile_sig[tile], start = d.tile_start[tile], cnt = d.tile_cnt[tile];
+  const int rep = t.sig_rep[sig];
+  const int L = (int)(t.adj_ptr[rep + 1] - t.adj_ptr[rep]);
+  const int64_t rb0 = t.n2e_ptr[rep];
+  const int deg = (int)(t.n2e_ptr[rep + 1] - rb0);
+  const uint8_t* ivrep = t.inv + t.inv_ptr[rep];
+  const double* gtab = CD == 2 ? d.aff.pairK : d.aff.pairR;
+  const bool mine = lane < cnt;
+  const int j = mine ? d.sig_nodes[start + lane] : d.sig_nodes[start];
+  {
+    const int64_t b0 = t.n2e_ptr[j];
+    for (int k = 0; k < deg; ++k) {
+      const double* cg = d.coef + (int64_t)t.n2e_elem[b0 + k] * PYN_AFF_NCOEF + C0;
+#pragma unroll
+      for (int c = 0; c < NC; ++c) s_cf[(k * NC + c) * 32 + lane] = __ldg(cg + c);
+    }
+    s_base[lane] = indptr[(int64_t)j * RD];
+    s_base[32 + lane] = indptr[(int64_t)j * RD + 1];
+  }
+  __syncwarp();
+  for (int p0 = 0; p0 < L; p0 += SIG_PT) {
+    double v[SIG_PT][RD][CD];
+#pragma unroll
+    for (int q = 0; q < SIG_PT; ++q)
+#pragma unroll
+      for (int a = 0; a < RD; ++a)
+#pragma unroll
+        for (int b = 0; b < CD; ++b) v[q][a][b] = 0.0;
+#pragma unroll
+    for (int q = 0; q < SIG_PT; ++q) {
+      const int p = p0 + q;
+      if (p < L) {                           // uniform
+        for (int k = 0; k < deg; ++k) {      // ascending cell order; uniform trip count and branch
+          const int l = ivrep[k * L + p];
+          if (l == 0xFF) continue;
+          const double* rp = gtab + ((int64_t)t.n2e_loc[rb0 + k] * t.nn + l) * PR;   // the same record for every lane
+          double rec[PR];
+#pragma unroll
+          for (int i = 0; i < PR; i += 2) {
+            const double2 x = __ldg(reinterpret_cast<const double2*>(rp + i));
+            rec[i] = x.x;
+            rec[i + 1] = x.y;
+          }
+          double cf[13 + 4];
+#pragma unroll
+          for (int c = 0; c < NC; ++c) cf[C0 + c] = s_cf[(k * NC + c) * 32 + lane];
+          double blk[RD][CD];
+          affine_entry<RD, CD>(d, cf, rec, blk);
+#pragma unroll
+          for (int a = 0; a < RD; ++a)
+#pragma unroll
+            for (int b = 0; b < CD; ++b) v[q][a][b] += d.sign * blk[a][b];
+        }
+      }
+    }
+    // transpose through shared memory: lane (node n, row a, position q) writes one CD-wide piece of a row
+#pragma unroll
+    for (int q = 0; q < SIG_PT; ++q)
+#pragma unroll
+      for (int a = 0; a < RD; ++a)
+#pragma unroll
+        for (int b = 0; b < CD; ++b) s_out[(lane * SIG_PT + q) * AW + a * CD + b] = v[q][a][b];
+    __syncwarp();
+    const int nl = lane >> 3, a = (lane >> 2) & 1, q = lane & 3;
+    const int p = p0 + q;
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+      const int n = it * 4 + nl;
+      if (n < cnt && p < L) {
+        const long long base = s_base[a * 32 + n];
+        double* o = data + base + (int64_t)p * CD;
+        const double* src = s_out + (n * SIG_PT + q) * AW + a * CD;
+        if (CD == 2) {
+          if ((base & 1) == 0) {
+            *reinterpret_cast<double2*>(o) = *reinterpret_cast<const double2*>(src);
+          } else {
+            o[0] = src[0];
+            o[1] = src[1];
+          }
+        } else {
+          o[0] = src[0];
+        }
+      }
+    }
+    __syncwarp();
+  }
+}
+
 // ---- uniform-mesh fast path: one template per row signature, streamed to every node that carries it ----------------
 // With ONE element matrix for all cells (E_stride == 0: the reference integrates cell 0 only, base_problem.py:333,133)
 // the rows of an interior node depend only on its signature (topo.cuh).  asm_template_kernel computes the RD x (L*CD)
@@ -769,6 +890,7 @@ int make_desc(const pyn_asm_desc* desc, DescView* v) {
   v->sign = desc->sign; v->E = desc->d_E; v->E_stride = desc->E_stride; v->rowscale = desc->d_rowscale;
   v->flags = desc->bcmap ? desc->bcmap->flags : nullptr;
   v->coef = nullptr; v->which = 0;
+  v->sig_nodes = v->tile_sig = v->tile_start = v->tile_cnt = nullptr; v->ntiles = 0;
   memset(&v->aff, 0, sizeof(v->aff));
   if (desc->d_coef) {   // fused integrate-and-assemble on affine elements
     PYN_REQUIRE(desc->elem != nullptr, "affine assembly: element handle missing");
@@ -818,6 +940,22 @@ static int launch_interior(const pyn_topo* t, const DescView& dv, const int64_t*
                            cudaStream_t st) {
   const pyn::TopoView tv = pyn::view_of(t);
   const int grid = pyn::grid_for((t->nnodes + ASM_NB - 1) / ASM_NB * 256, 256, 8);
+  if (dv.coef && !indices && data && dv.tile_sig) {   // structured mesh, values only: signature-grouped kernel
+    PYN_REQUIRE(tv.nn == dv.aff.n * dv.aff.n, "affine assembly: element handle of another order");
+    const int nc = dv.cdof == 2 ? 13 : 4, aw = 2 * dv.cdof;
+    const size_t dyn = sizeof(double) * (size_t)SIG_W * (SIG_KMAX * nc * 32 + 32 * SIG_PT * aw) + sizeof(long long) * SIG_W * 64;
+    const int64_t g = (dv.ntiles + SIG_W - 1) / SIG_W;
+    PYN_REQUIRE(g < 0x7fffffff, "affine assembly: too many signature tiles");
+    if (dv.cdof == 2) {
+      PYN_CHECK_CUDA(cudaFuncSetAttribute(asm_sig_affine_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
+      asm_sig_affine_kernel<2><<<(int)g, SIG_W * 32, dyn, st>>>(tv, dv, indptr, data);
+    } else {
+      PYN_CHECK_CUDA(cudaFuncSetAttribute(asm_sig_affine_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
+      asm_sig_affine_kernel<1><<<(int)g, SIG_W * 32, dyn, st>>>(tv, dv, indptr, data);
+    }
+    PYN_CHECK_LAUNCH();
+    return PYN_OK;
+  }
   if (dv.coef) {
     PYN_REQUIRE(tv.nn == dv.aff.n * dv.aff.n, "affine assembly: element handle of another order");
     // The product table is read through L1 (4 CTAs of 64 registers per SM: 6.1 ms for K at 707^2 x ngl 5); holding it
@@ -931,6 +1069,78 @@ static int launch_templates(const pyn_topo* t, const DescView& dv, const int64_t
   return PYN_OK;
 }
 
+// ---- signature tiles of a boundary map (lazy; see topo.cuh) ----------------------------------------------------------
+namespace {
+struct NotFlag {
+  __host__ __device__ __forceinline__ uint8_t operator()(const uint8_t& f) const { return f ? 0 : 1; }
+};
+__global__ void sig_keys_kernel(int64_t n, const int* __restrict__ nodes, const int* __restrict__ sig_id,
+                                int* __restrict__ keys, int* __restrict__ counts) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int s = sig_id[nodes[i]];
+    keys[i] = s;
+    atomicAdd(&counts[s], 1);
+  }
+}
+}  // namespace
+
+static int ensure_sig_tiles(const pyn_topo* t, const pyn_bcmap* mc, cudaStream_t st) {
+  pyn_bcmap* m = const_cast<pyn_bcmap*>(mc);   // cache owned by the handle (one host thread per handle)
+  if (m->tiles_state != 0) return PYN_OK;
+  m->tiles_state = -1;
+  // Measured slower than the flat kernel at every order but 2 (profiles/r02_ncu_fused_assembly.md, structure v5):
+  // kept as an opt-in structure, PYN_AFF_SIG=1.
+  static const bool off = getenv("PYN_AFF_SIG") == nullptr;
+  if (off || t->nsig <= 0 || t->max_valence > SIG_KMAX || t->nn > 255) return PYN_OK;
+  const int64_t n = t->nnodes, nint = t->nnodes - m->nlist;
+  if (nint <= 0 || nint >= 0x7fffffff) return PYN_OK;
+  int *nodes = nullptr, *keys = nullptr, *keys2 = nullptr, *counts = nullptr;
+  int64_t* d_n = nullptr;
+  void* tmp = nullptr;
+  size_t b1 = 0, b2 = 0;
+  PYN_CHECK_CUDA(cudaMalloc(&nodes, sizeof(int) * nint));
+  PYN_CHECK_CUDA(cudaMalloc(&m->sig_nodes, sizeof(int) * nint));
+  PYN_CHECK_CUDA(cudaMalloc(&keys, sizeof(int) * nint));
+  PYN_CHECK_CUDA(cudaMalloc(&keys2, sizeof(int) * nint));
+  PYN_CHECK_CUDA(cudaMalloc(&counts, sizeof(int) * t->nsig));
+  PYN_CHECK_CUDA(cudaMalloc(&d_n, sizeof(int64_t)));
+  PYN_CHECK_CUDA(cudaMemsetAsync(counts, 0, sizeof(int) * t->nsig, st));
+  cub::CountingInputIterator<int> ids(0);
+  cub::TransformInputIterator<uint8_t, NotFlag, const uint8_t*> keep(m->flags, NotFlag());
+  PYN_CHECK_CUDA(cub::DeviceSelect::Flagged(nullptr, b1, ids, keep, nodes, d_n, n, st));
+  int end_bit = 1;
+  while ((1 << end_bit) < t->nsig) ++end_bit;
+  PYN_CHECK_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, b2, keys, keys2, nodes, m->sig_nodes, nint, 0, end_bit, st));
+  PYN_CHECK_CUDA(cudaMalloc(&tmp, b1 > b2 ? b1 : b2));
+  PYN_CHECK_CUDA(cub::DeviceSelect::Flagged(tmp, b1, ids, keep, nodes, d_n, n, st));      // ascending node ids
+  sig_keys_kernel<<<pyn::grid_for(nint, 256), 256, 0, st>>>(nint, nodes, t->sig_id, keys, counts);
+  PYN_CHECK_CUDA(cub::DeviceRadixSort::SortPairs(tmp, b2, keys, keys2, nodes, m->sig_nodes, nint, 0, end_bit, st));   // stable
+  pyn::count_launch(3);
+  std::vector<int> h_counts((size_t)t->nsig);
+  PYN_CHECK_CUDA(cudaMemcpyAsync(h_counts.data(), counts, sizeof(int) * t->nsig, cudaMemcpyDeviceToHost, st));
+  PYN_CHECK_CUDA(cudaStreamSynchronize(st));
+  cudaFree(nodes); cudaFree(keys); cudaFree(keys2); cudaFree(counts); cudaFree(d_n); cudaFree(tmp);
+  std::vector<int> ts, tb, tc;
+  int64_t off_ = 0;
+  for (int s = 0; s < t->nsig; ++s) {
+    for (int c = 0; c < h_counts[s]; c += 32) {
+      ts.push_back(s); tb.push_back((int)(off_ + c)); tc.push_back(h_counts[s] - c < 32 ? h_counts[s] - c : 32);
+    }
+    off_ += h_counts[s];
+  }
+  if (off_ != nint || ts.empty()) return PYN_OK;
+  m->ntiles = (int64_t)ts.size();
+  PYN_CHECK_CUDA(cudaMalloc(&m->tile_sig, sizeof(int) * ts.size()));
+  PYN_CHECK_CUDA(cudaMalloc(&m->tile_start, sizeof(int) * ts.size()));
+  PYN_CHECK_CUDA(cudaMalloc(&m->tile_cnt, sizeof(int) * ts.size()));
+  PYN_CHECK_CUDA(cudaMemcpyAsync(m->tile_sig, ts.data(), sizeof(int) * ts.size(), cudaMemcpyHostToDevice, st));
+  PYN_CHECK_CUDA(cudaMemcpyAsync(m->tile_start, tb.data(), sizeof(int) * ts.size(), cudaMemcpyHostToDevice, st));
+  PYN_CHECK_CUDA(cudaMemcpyAsync(m->tile_cnt, tc.data(), sizeof(int) * ts.size(), cudaMemcpyHostToDevice, st));
+  PYN_CHECK_CUDA(cudaStreamSynchronize(st));
+  m->tiles_state = 1;
+  return PYN_OK;
+}
+
 // the interior fast path applies when a map is given and class-0 rows carry no forced diagonal
 static bool g_no_templates = false;  // pyn_asm_set_templates(0): force the generic gather kernel (tests, comparisons)
 static inline bool use_map(const pyn_asm_desc* desc) { return desc->bcmap != nullptr && !(desc->diag_classes & 1u); }
@@ -982,6 +1192,7 @@ int pyn_bcmap_destroy(pyn_bcmap* m) {
   if (!m) return PYN_OK;
   cudaFreeAsync(m->flags, m->st);   // stream-ordered: no device-wide synchronisation, the pool keeps the memory
   cudaFreeAsync(m->list, m->st);
+  cudaFree(m->sig_nodes); cudaFree(m->tile_sig); cudaFree(m->tile_start); cudaFree(m->tile_cnt);
   delete m;
   return PYN_OK;
 }
@@ -1068,6 +1279,14 @@ int pyn_asm_fill(const pyn_topo* t, const pyn_asm_desc* desc, const int64_t* d_i
       if (overlap) {
         rc = fork_boundary(t, dv, desc->bcmap->list, desc->bcmap->nlist, d_indptr, d_data, st);
         if (rc) return rc;
+      }
+      if (dv.coef && d_data && !d_indices) {   // structured mesh: the signature-grouped fused kernel
+        rc = ensure_sig_tiles(t, desc->bcmap, st);
+        if (rc) return rc;
+        if (desc->bcmap->tiles_state == 1) {
+          dv.sig_nodes = desc->bcmap->sig_nodes; dv.tile_sig = desc->bcmap->tile_sig;
+          dv.tile_start = desc->bcmap->tile_start; dv.tile_cnt = desc->bcmap->tile_cnt; dv.ntiles = desc->bcmap->ntiles;
+        }
       }
       rc = tmpl ? launch_templates(t, dv, d_indptr, d_data, st) : launch_interior(t, dv, d_indptr, d_indices, d_data, st);
       if (rc) return rc;

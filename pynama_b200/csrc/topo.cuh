@@ -44,6 +44,13 @@ struct pyn_bcmap {
   uint8_t* flags;  // [nnodes] 1 = boundary-affected node
   int* list;       // the flagged nodes, ascending
   cudaStream_t st; // stream the buffers were allocated on (stream-ordered allocator) and are released on
+  // Signature tiles (lazy, structured meshes only): the un-flagged nodes grouped by row signature (ascending node id
+  // inside a group) and cut into tiles of <= 32 nodes of ONE signature: tile i = nodes sig_nodes[tile_start[i] ..
+  // + tile_cnt[i]) of signature tile_sig[i].  Used by the signature-grouped fused assembly kernel (assemble.cu).
+  int* sig_nodes;
+  int *tile_sig, *tile_start, *tile_cnt;
+  int64_t ntiles;
+  int tiles_state;   // 0 not built, 1 built, -1 unavailable
 };
 
 namespace pyn {

@@ -5,6 +5,10 @@ of FreeSlip.buildKLEMats (src/cases/base_problem.py:499-552) without materialise
   * fused assembly bit-identical to "materialise with the same closed form, then gather"
   * assembled K, Krhs, Rw vs the oracle's per-cell assembly: pattern bit-exact, values 1e-12
   * a mesh with one non-affine cell falls back to the general kernels (and still matches the oracle)"""
+import os
+import subprocess
+import sys
+
 import numpy as np
 import pytest
 import yaml
@@ -134,3 +138,13 @@ def test_fused_rd_blocks(be):
     assert bool((A.data == B.data).all()) and bool((A.indices == B.indices).all())
     _, _, Rdo = o.elem_kle_matrices(ngl, m.cell_corner_coords())
     assert rel_err(Rde.cpu().numpy(), Rdo) < 1e-12
+
+
+@pytest.mark.skipif(os.environ.get("PYN_AFF_SIG") is not None, reason="already inside the opt-in run")
+def test_signature_tile_structure_is_bit_identical_too():
+    """The opt-in structure of the fused kernel (PYN_AFF_SIG=1: tiles of one row signature, one node per lane) is read
+    once per process, so the parity cases above are re-run in a child process with it switched on."""
+    env = dict(os.environ, PYN_AFF_SIG="1")
+    r = subprocess.run([sys.executable, "-m", "pytest", __file__, "-q", "-x", "-k", "fused_assembly_vs_oracle or rd_blocks"],
+                       env=env, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
