@@ -245,6 +245,15 @@ int pyn_vec_maxpy(int64_t n, int m, const double* h_coef, const double* const* h
                   double* d_y, void* stream);                          /* y = y0 + sum c_j x_j ; y0 NULL = 0 */
 int pyn_vec_dot(int64_t n, const double* d_x, const double* d_y, double* h_out, void* stream); /* synchronises */
 int pyn_vec_norm(int64_t n, const double* d_x, int kind /*2: l2, 3: inf*/, double* h_out, void* stream);
+/* pyn_vec_dot for callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).
+ * No counterpart in the reference.  Bit-identical to pyn_vec_dot, but the
+ * per-CTA partial sums live in a file-scope device array of PYN_VEC_DOT_NOALLOC_MAX_PARTS doubles (16 KiB, held by every
+ * GPU that loads the library) and the result is written to the caller's DEVICE double d_out; the call allocates and
+ * frees nothing and does not synchronise.  n > PYN_VEC_DOT_NOALLOC_MAX_N is rejected (PYN_ERR_ARG).  All calls share the
+ * array: calls that overlap on the GPU (different streams) race. */
+#define PYN_VEC_DOT_NOALLOC_MAX_PARTS 2048
+#define PYN_VEC_DOT_NOALLOC_MAX_N ((int64_t)1 << 28)
+int pyn_vec_dot_noalloc(int64_t n, const double* d_x, const double* d_y, double* d_out, void* stream);
 int pyn_vec_scatter_set(int64_t nidx, const int64_t* d_idx, const double* d_vals, double* d_x, void* stream);
 int pyn_vec_scatter_const(int64_t nidx, const int64_t* d_idx, double val, double* d_x, void* stream);
 int pyn_vtensv(int64_t nnodes, const double* d_vel, double* d_out, void* stream);  /* base_problem.py:234-252 */

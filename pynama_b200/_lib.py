@@ -87,6 +87,7 @@ _SIGNATURES = {
     "pyn_vec_maxpy": (C.c_int, [c_i64, C.c_int, P(c_f64), P(c_vp), c_vp, c_vp, c_vp]),
     "pyn_vec_dot": (C.c_int, [c_i64, c_vp, c_vp, P(c_f64), c_vp]),
     "pyn_vec_norm": (C.c_int, [c_i64, c_vp, C.c_int, P(c_f64), c_vp]),
+    "pyn_vec_dot_noalloc": (C.c_int, [c_i64, c_vp, c_vp, c_vp, c_vp]),
     "pyn_vec_scatter_set": (C.c_int, [c_i64, c_vp, c_vp, c_vp, c_vp]),
     "pyn_vec_scatter_const": (C.c_int, [c_i64, c_vp, c_f64, c_vp, c_vp]),
     "pyn_vtensv": (C.c_int, [c_i64, c_vp, c_vp, c_vp]),

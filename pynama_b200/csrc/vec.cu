@@ -1,4 +1,6 @@
 // FP64 vector kernels (the PETSc Vec calls of the hot path).  Grid-stride, two-pass deterministic reductions.
+#include <mutex>
+
 #include "common.cuh"
 
 namespace {
@@ -203,4 +205,68 @@ int pyn_vec_wrms(int64_t n, const double* e, const double* y, const double* yn, 
   *h_out = sqrt(*g_s.h_out / (double)n);
   return PYN_OK;
 }
+}  // extern "C"
+
+// ---- pyn_vec_dot_noalloc: the dot product for callers that must not allocate ----------------------------------------
+// Same two kernels, same grid and same order of additions as pyn_vec_dot (bit-identical result), but the per-CTA partial
+// sums go to a file-scope device array instead of cudaMalloc'ed scratch and the result is left in the caller's DEVICE
+// buffer: no cudaMalloc / cudaMallocHost / cudaFree, no synchronisation, nothing but two launches on the stream.
+// Every GPU that loads the library holds the 16 KiB array until exit.  All calls share it: nothing in it has to start at
+// zero (a call overwrites the grid entries it then reads), but two calls that overlap on the GPU (different streams)
+// race on it.
+static __device__ __align__(256) double g_noalloc_part[PYN_VEC_DOT_NOALLOC_MAX_PARTS];
+
+namespace {
+constexpr int NOALLOC_MAX_DEV = 64;
+struct NoallocDev {
+  double* part;   // device address of g_noalloc_part on this device (the symbol itself is a host-side stand-in)
+  int sms;
+};
+NoallocDev g_noalloc_dev[NOALLOC_MAX_DEV];
+std::mutex g_noalloc_mu;
+
+// once per device, with that device current
+int noalloc_setup(NoallocDev** out) {
+  int dev = -1;
+  PYN_CHECK_CUDA(cudaGetDevice(&dev));
+  PYN_REQUIRE(dev >= 0 && dev < NOALLOC_MAX_DEV, "pyn_vec_dot_noalloc: device ordinal out of range");
+  std::lock_guard<std::mutex> lock(g_noalloc_mu);
+  NoallocDev& d = g_noalloc_dev[dev];
+  if (!d.part) {
+    double* ptr = nullptr;
+    int sms = 0;
+    PYN_CHECK_CUDA(cudaGetSymbolAddress((void**)&ptr, g_noalloc_part));
+    PYN_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    PYN_REQUIRE(ptr && sms > 0, "pyn_vec_dot_noalloc: no device address for the scratch array");
+    d.sms = sms;
+    d.part = ptr;
+  }
+  *out = &d;
+  return PYN_OK;
+}
+}  // namespace
+
+extern "C" int pyn_vec_dot_noalloc(int64_t n, const double* x, const double* y, double* d_out, void* stream) {
+  PYN_REQUIRE(n > 0 && x && y && d_out, "bad arguments");
+  if (n > PYN_VEC_DOT_NOALLOC_MAX_N) {
+    pyn::set_error("pyn_vec_dot_noalloc: n = %lld exceeds the maximum of %lld entries", (long long)n,
+                   (long long)PYN_VEC_DOT_NOALLOC_MAX_N);
+    return PYN_ERR_ARG;
+  }
+  NoallocDev* d = nullptr;
+  const int rc = noalloc_setup(&d);
+  if (rc) return rc;
+  int64_t g = (n + BLK - 1) / BLK;                       // the grid of pyn_vec_dot (grid_for(n, BLK, 8))
+  if (g > (int64_t)d->sms * 8) g = (int64_t)d->sms * 8;
+  if (g > PYN_VEC_DOT_NOALLOC_MAX_PARTS) {
+    pyn::set_error("pyn_vec_dot_noalloc: %lld partial sums exceed the scratch array of %d", (long long)g,
+                   PYN_VEC_DOT_NOALLOC_MAX_PARTS);
+    return PYN_ERR_ARG;
+  }
+  cudaStream_t st = pyn::as_stream(stream);
+  reduce1_kernel<0><<<(int)g, BLK, 0, st>>>(n, x, y, d->part);
+  PYN_CHECK_LAUNCH();
+  reduce2_kernel<0><<<1, BLK, 0, st>>>((int)g, d->part, d_out);
+  PYN_CHECK_LAUNCH();
+  return PYN_OK;
 }
