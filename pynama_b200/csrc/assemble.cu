@@ -6,6 +6,7 @@
 // the node's sorted adjacency list, then writes the rows out compacted by the boundary-condition masks.  The
 // summation order is therefore exactly the reference's serial cell loop (base_problem.py:337,504,135) and the
 // result is bitwise reproducible run to run.
+#include <algorithm>
 #include <vector>
 
 #include <cub/cub.cuh>
@@ -36,6 +37,7 @@ struct DescView {
   // signature tiles of the boundary map (structured meshes; NULL: not available)
   const int *sig_nodes, *tile_sig, *tile_start, *tile_cnt;
   int64_t ntiles;
+  int64_t tile_class_end[3];
 };
 
 // element block (rows of local node lr, columns of local node l) of one element from the affine closed form:
@@ -439,104 +441,129 @@ asm_interior_affine_kernel(pyn::TopoView t, DescView d, const int64_t* __restric
 // The flat kernel above spends most of its instructions on finding out, per output block, which node it belongs to and
 // which of the node's elements contribute (and its element loop diverges).  On a structured mesh that information is the
 // same for every node of a row signature (topo.cuh: byte-identical incidence local indices and inverse maps).  Here a
-// WARP takes a tile of 32 nodes of ONE signature, one node per lane: the signature's contribution list -- read from its
-// representative node -- is uniform across the warp (no look-ups per lane, no divergence), the only per-lane data are
-// the node's row bases and the 13 (4) coefficients of its <= 4 elements, staged in shared memory lane-major
-// (conflict-free).  The lanes' blocks of AFF_PT consecutive positions go through a shared-memory tile so that the rows
-// leave as 64-byte (32-byte) segments instead of 32 scattered 16-byte stores.  Same order of additions per entry as
-// every other assembly kernel (ascending cell order): same bits.
+// WARP takes a tile of 32 nodes of ONE signature, one node per lane:
+//   * the 13 (4) coefficients of the node's <= DEG elements live in REGISTERS for the whole row (DEG is a template
+//     parameter: the tiles are sorted by valence class and each class gets its own launch);
+//   * per pass of SIG_PT adjacency positions the signature's contribution list (the representative node's inverse map)
+//     is read by the lanes (k, q) and the product records it names are staged in shared memory, so the evaluation loop
+//     has no global loads and no look-ups: a warp-uniform test per (position, element), broadcast LDS.128 of the
+//     record, the closed form, one store of the block into the warp's output tile;
+//   * the output tile is flushed row-major: 8 lanes write one 128-byte (64-byte for 2x1 blocks) piece of one row.
+// Same order of additions per entry as every other assembly kernel (ascending cell order): same bits.
 constexpr int SIG_W = 4;       // warps (= tiles) per CTA
-constexpr int SIG_PT = 4;      // adjacency positions per pass
+constexpr int SIG_PT = 8;      // adjacency positions per pass
 constexpr int SIG_KMAX = 4;    // incident elements per node (quadrilateral meshes; larger valence: flat kernel)
 
 template <int CD>
+struct SigSmem {
+  static constexpr int RD = 2;
+  static constexpr int PR = CD == 2 ? pyn::PYN_AFF_PK : pyn::PYN_AFF_PR;
+  static constexpr int OSTR = RD * SIG_PT * CD + CD;                 // doubles per lane in the output tile (padded)
+  static constexpr int per_warp(int deg) { return 32 * OSTR + deg * SIG_PT * PR + RD * 32; }   // in 8-byte words
+};
+
+template <int CD, int DEG>
 __global__ void __launch_bounds__(SIG_W * 32)
-asm_sig_affine_kernel(pyn::TopoView t, DescView d, const int64_t* __restrict__ indptr, double* __restrict__ data) {
-  constexpr int RD = 2;
+asm_sig_affine_kernel(pyn::TopoView t, DescView d, const int64_t* __restrict__ indptr, double* __restrict__ data,
+                      int64_t tile0, int64_t tile1) {
+  using S = SigSmem<CD>;
+  constexpr int RD = 2, PT = SIG_PT;
   constexpr int NC = CD == 2 ? 13 : 4, C0 = CD == 2 ? 0 : 13;
-  constexpr int PR = CD == 2 ? pyn::PYN_AFF_PK : pyn::PYN_AFF_PR;
-  constexpr int AW = RD * CD;
+  constexpr int PR = S::PR, OSTR = S::OSTR;
   extern __shared__ __align__(16) double sg_dyn[];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  double* s_cf = sg_dyn + (size_t)w * (SIG_KMAX * NC * 32);                              // [k][c][lane]
-  double* s_out = sg_dyn + (size_t)SIG_W * (SIG_KMAX * NC * 32) + (size_t)w * (32 * SIG_PT * AW);   // [lane][q][AW]
-  long long* s_base = reinterpret_cast<long long*>(sg_dyn + (size_t)SIG_W * (SIG_KMAX * NC * 32 + 32 * SIG_PT * AW)) + w * 64;
-  const int64_t tile = (int64_t)blockIdx.x * SIG_W + w;
-  if (tile >= d.ntiles) return;
+  double* s_out = sg_dyn + (size_t)w * S::per_warp(DEG);             // [lane][a][q][b]
+  double* s_rec = s_out + 32 * OSTR;                                 // [k][q][PR]
+  double** s_ptr = reinterpret_cast<double**>(s_rec + DEG * PT * PR);   // [a][lane]: start of the lane's row a
+  const int64_t tile = tile0 + (int64_t)blockIdx.x * SIG_W + w;
+  if (tile >= tile1) return;                                         // warps are independent: no CTA-wide barrier below
   const int sig = d.tile_sig[tile], start = d.tile_start[tile], cnt = d.tile_cnt[tile];
   const int rep = t.sig_rep[sig];
   const int L = (int)(t.adj_ptr[rep + 1] - t.adj_ptr[rep]);
   const int64_t rb0 = t.n2e_ptr[rep];
-  const int deg = (int)(t.n2e_ptr[rep + 1] - rb0);
+  const int deg = min((int)(t.n2e_ptr[rep + 1] - rb0), DEG);
   const uint8_t* ivrep = t.inv + t.inv_ptr[rep];
   const double* gtab = CD == 2 ? d.aff.pairK : d.aff.pairR;
-  const bool mine = lane < cnt;
-  const int j = mine ? d.sig_nodes[start + lane] : d.sig_nodes[start];
+  const int j = d.sig_nodes[start + (lane < cnt ? lane : 0)];
+  double cf[DEG][NC];
   {
     const int64_t b0 = t.n2e_ptr[j];
-    for (int k = 0; k < deg; ++k) {
-      const double* cg = d.coef + (int64_t)t.n2e_elem[b0 + k] * PYN_AFF_NCOEF + C0;
 #pragma unroll
-      for (int c = 0; c < NC; ++c) s_cf[(k * NC + c) * 32 + lane] = __ldg(cg + c);
+    for (int k = 0; k < DEG; ++k) {
+      const double* cg = d.coef + (int64_t)t.n2e_elem[b0 + (k < deg ? k : 0)] * PYN_AFF_NCOEF + C0;
+#pragma unroll
+      for (int c = 0; c < NC; ++c) cf[k][c] = __ldg(cg + c);
     }
-    s_base[lane] = indptr[(int64_t)j * RD];
-    s_base[32 + lane] = indptr[(int64_t)j * RD + 1];
+    s_ptr[lane] = data + indptr[(int64_t)j * RD];
+    s_ptr[32 + lane] = data + indptr[(int64_t)j * RD + 1];
   }
-  __syncwarp();
-  for (int p0 = 0; p0 < L; p0 += SIG_PT) {
-    double v[SIG_PT][RD][CD];
+  // this lane's share of the staging: element kk of the signature, position qq of the pass
+  const int kk = lane / PT, qq = lane % PT;
+  const int64_t lrow = kk < deg ? (int64_t)t.n2e_loc[rb0 + kk] * t.nn : 0;
+  const double sign = d.sign;
+  for (int p0 = 0; p0 < L; p0 += PT) {
+    const int wch = min(PT, L - p0);
+    int l = 0xFF;
+    if (kk < deg && qq < wch) l = ivrep[kk * L + p0 + qq];
+    if (l != 0xFF) {
+      const double2* rp = reinterpret_cast<const double2*>(gtab + (lrow + l) * PR);
+      double2* dst = reinterpret_cast<double2*>(s_rec + (kk * PT + qq) * PR);
 #pragma unroll
-    for (int q = 0; q < SIG_PT; ++q)
+      for (int i = 0; i < PR / 2; ++i) dst[i] = __ldg(rp + i);
+    }
+    __syncwarp();
+#pragma unroll 2
+    for (int q = 0; q < wch; ++q) {
+      double v[RD][CD];
 #pragma unroll
       for (int a = 0; a < RD; ++a)
 #pragma unroll
-        for (int b = 0; b < CD; ++b) v[q][a][b] = 0.0;
+        for (int b = 0; b < CD; ++b) v[a][b] = 0.0;
 #pragma unroll
-    for (int q = 0; q < SIG_PT; ++q) {
-      const int p = p0 + q;
-      if (p < L) {                           // uniform
-        for (int k = 0; k < deg; ++k) {      // ascending cell order; uniform trip count and branch
-          const int l = ivrep[k * L + p];
-          if (l == 0xFF) continue;
-          const double* rp = gtab + ((int64_t)t.n2e_loc[rb0 + k] * t.nn + l) * PR;   // the same record for every lane
+      for (int k = 0; k < DEG; ++k) {          // ascending cell order; the test is uniform across the warp
+        const int lk = __shfl_sync(0xffffffffu, l, k * PT + q);
+        if (lk != 0xFF) {
+          const double2* rs = reinterpret_cast<const double2*>(s_rec + (k * PT + q) * PR);
           double rec[PR];
 #pragma unroll
-          for (int i = 0; i < PR; i += 2) {
-            const double2 x = __ldg(reinterpret_cast<const double2*>(rp + i));
-            rec[i] = x.x;
-            rec[i + 1] = x.y;
+          for (int i = 0; i < PR / 2; ++i) {
+            const double2 x = rs[i];
+            rec[2 * i] = x.x;
+            rec[2 * i + 1] = x.y;
           }
-          double cf[13 + 4];
-#pragma unroll
-          for (int c = 0; c < NC; ++c) cf[C0 + c] = s_cf[(k * NC + c) * 32 + lane];
           double blk[RD][CD];
-          affine_entry<RD, CD>(d, cf, rec, blk);
+          if constexpr (CD == 2) {
+            pyn::affine_block_K(cf[k], rec, blk);
+          } else {
+            pyn::affine_block_R(cf[k], rec, d.which, d.aff.alpha_w, d.aff.alpha_d, blk);
+          }
 #pragma unroll
           for (int a = 0; a < RD; ++a)
 #pragma unroll
-            for (int b = 0; b < CD; ++b) v[q][a][b] += d.sign * blk[a][b];
+            for (int b = 0; b < CD; ++b) v[a][b] += sign * blk[a][b];
+        }
+      }
+#pragma unroll
+      for (int a = 0; a < RD; ++a) {
+        double* o = s_out + lane * OSTR + (a * PT + q) * CD;
+        if constexpr (CD == 2) {
+          *reinterpret_cast<double2*>(o) = make_double2(v[a][0], v[a][1]);
+        } else {
+          o[0] = v[a][0];
         }
       }
     }
-    // transpose through shared memory: lane (node n, row a, position q) writes one CD-wide piece of a row
-#pragma unroll
-    for (int q = 0; q < SIG_PT; ++q)
-#pragma unroll
-      for (int a = 0; a < RD; ++a)
-#pragma unroll
-        for (int b = 0; b < CD; ++b) s_out[(lane * SIG_PT + q) * AW + a * CD + b] = v[q][a][b];
     __syncwarp();
-    const int nl = lane >> 3, a = (lane >> 2) & 1, q = lane & 3;
-    const int p = p0 + q;
-#pragma unroll
-    for (int it = 0; it < 8; ++it) {
-      const int n = it * 4 + nl;
-      if (n < cnt && p < L) {
-        const long long base = s_base[a * 32 + n];
-        double* o = data + base + (int64_t)p * CD;
-        const double* src = s_out + (n * SIG_PT + q) * AW + a * CD;
-        if (CD == 2) {
-          if ((base & 1) == 0) {
+    // flush: 2^s lanes per row piece (s = ceil log2 of the positions of this pass), 32 >> (s + 1) nodes per step
+    const int s = wch > 4 ? 3 : (wch > 2 ? 2 : wch - 1);
+    const int fq = lane & ((1 << s) - 1), fa = (lane >> s) & 1, fn = lane >> (s + 1), npi = 32 >> (s + 1);
+    if (fq < wch) {
+#pragma unroll 4
+      for (int n = fn; n < cnt; n += npi) {
+        double* o = s_ptr[fa * 32 + n] + (int64_t)(p0 + fq) * CD;
+        const double* src = s_out + n * OSTR + (fa * PT + fq) * CD;
+        if constexpr (CD == 2) {
+          if ((reinterpret_cast<uintptr_t>(o) & 15) == 0) {
             *reinterpret_cast<double2*>(o) = *reinterpret_cast<const double2*>(src);
           } else {
             o[0] = src[0];
@@ -942,18 +969,28 @@ static int launch_interior(const pyn_topo* t, const DescView& dv, const int64_t*
   const int grid = pyn::grid_for((t->nnodes + ASM_NB - 1) / ASM_NB * 256, 256, 8);
   if (dv.coef && !indices && data && dv.tile_sig) {   // structured mesh, values only: signature-grouped kernel
     PYN_REQUIRE(tv.nn == dv.aff.n * dv.aff.n, "affine assembly: element handle of another order");
-    const int nc = dv.cdof == 2 ? 13 : 4, aw = 2 * dv.cdof;
-    const size_t dyn = sizeof(double) * (size_t)SIG_W * (SIG_KMAX * nc * 32 + 32 * SIG_PT * aw) + sizeof(long long) * SIG_W * 64;
-    const int64_t g = (dv.ntiles + SIG_W - 1) / SIG_W;
-    PYN_REQUIRE(g < 0x7fffffff, "affine assembly: too many signature tiles");
-    if (dv.cdof == 2) {
-      PYN_CHECK_CUDA(cudaFuncSetAttribute(asm_sig_affine_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
-      asm_sig_affine_kernel<2><<<(int)g, SIG_W * 32, dyn, st>>>(tv, dv, indptr, data);
-    } else {
-      PYN_CHECK_CUDA(cudaFuncSetAttribute(asm_sig_affine_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
-      asm_sig_affine_kernel<1><<<(int)g, SIG_W * 32, dyn, st>>>(tv, dv, indptr, data);
+    int64_t c0 = 0;
+#define PYN_SIG_CASE(C, DG, cls)                                                                                        \
+    if (dv.cdof == C && dv.tile_class_end[cls] > c0) {                                                                  \
+      const int64_t c1 = dv.tile_class_end[cls], g = (c1 - c0 + SIG_W - 1) / SIG_W;                                    \
+      const size_t dyn = sizeof(double) * (size_t)SIG_W * SigSmem<C>::per_warp(DG);                                    \
+      PYN_REQUIRE(g < 0x7fffffff, "affine assembly: too many signature tiles");                                        \
+      PYN_CHECK_CUDA(cudaFuncSetAttribute(asm_sig_affine_kernel<C, DG>, cudaFuncAttributeMaxDynamicSharedMemorySize,   \
+                                          (int)dyn));                                                                  \
+      asm_sig_affine_kernel<C, DG><<<(int)g, SIG_W * 32, dyn, st>>>(tv, dv, indptr, data, c0, c1);                     \
+      pyn::count_launch();                                                                                             \
     }
-    PYN_CHECK_LAUNCH();
+    PYN_SIG_CASE(2, 1, 0) PYN_SIG_CASE(1, 1, 0)
+    c0 = dv.tile_class_end[0];
+    PYN_SIG_CASE(2, 2, 1) PYN_SIG_CASE(1, 2, 1)
+    c0 = dv.tile_class_end[1];
+    PYN_SIG_CASE(2, 4, 2) PYN_SIG_CASE(1, 4, 2)
+#undef PYN_SIG_CASE
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) {
+      pyn::set_error("signature-tile assembly: %s", cudaGetErrorString(e));
+      return PYN_ERR_CUDA;
+    }
     return PYN_OK;
   }
   if (dv.coef) {
@@ -1082,6 +1119,14 @@ __global__ void sig_keys_kernel(int64_t n, const int* __restrict__ nodes, const 
     atomicAdd(&counts[s], 1);
   }
 }
+__global__ void tile_first_kernel(int64_t nt, const int* __restrict__ start, const int* __restrict__ sig_nodes,
+                                  const int64_t* __restrict__ n2e_ptr, int* __restrict__ first, int* __restrict__ deg) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < nt; i += (int64_t)gridDim.x * blockDim.x) {
+    const int j = sig_nodes[start[i]];
+    first[i] = j;
+    deg[i] = (int)(n2e_ptr[j + 1] - n2e_ptr[j]);
+  }
+}
 }  // namespace
 
 static int ensure_sig_tiles(const pyn_topo* t, const pyn_bcmap* mc, cudaStream_t st) {
@@ -1129,6 +1174,41 @@ static int ensure_sig_tiles(const pyn_topo* t, const pyn_bcmap* mc, cudaStream_t
     off_ += h_counts[s];
   }
   if (off_ != nint || ts.empty()) return PYN_OK;
+  {  // order of execution: valence class (one launch each), then first node -- tiles that write neighbouring rows run
+     // at about the same time, so the partial lines of a row meet in L2
+    const size_t nt = ts.size();
+    int *d_start = nullptr, *d_first = nullptr, *d_deg = nullptr;
+    PYN_CHECK_CUDA(cudaMalloc(&d_start, sizeof(int) * nt));
+    PYN_CHECK_CUDA(cudaMalloc(&d_first, sizeof(int) * nt));
+    PYN_CHECK_CUDA(cudaMalloc(&d_deg, sizeof(int) * nt));
+    PYN_CHECK_CUDA(cudaMemcpyAsync(d_start, tb.data(), sizeof(int) * nt, cudaMemcpyHostToDevice, st));
+    tile_first_kernel<<<pyn::grid_for((int64_t)nt, 256), 256, 0, st>>>((int64_t)nt, d_start, m->sig_nodes, t->n2e_ptr,
+                                                                        d_first, d_deg);
+    pyn::count_launch();
+    std::vector<int> first(nt), dg(nt);
+    PYN_CHECK_CUDA(cudaMemcpyAsync(first.data(), d_first, sizeof(int) * nt, cudaMemcpyDeviceToHost, st));
+    PYN_CHECK_CUDA(cudaMemcpyAsync(dg.data(), d_deg, sizeof(int) * nt, cudaMemcpyDeviceToHost, st));
+    PYN_CHECK_CUDA(cudaStreamSynchronize(st));
+    cudaFree(d_start); cudaFree(d_first); cudaFree(d_deg);
+    std::vector<int64_t> key(nt);
+    std::vector<int> order(nt);
+    for (size_t i = 0; i < nt; ++i) {
+      const int cls = dg[i] <= 1 ? 0 : (dg[i] == 2 ? 1 : 2);
+      key[i] = ((int64_t)cls << 40) | (int64_t)first[i];
+      order[i] = (int)i;
+    }
+    std::sort(order.begin(), order.end(), [&](int a, int b) { return key[a] < key[b]; });
+    std::vector<int> ts2(nt), tb2(nt), tc2(nt);
+    m->tile_class_end[0] = m->tile_class_end[1] = m->tile_class_end[2] = 0;
+    for (size_t i = 0; i < nt; ++i) {
+      const int o = order[i];
+      ts2[i] = ts[o]; tb2[i] = tb[o]; tc2[i] = tc[o];
+      m->tile_class_end[key[o] >> 40] = (int64_t)i + 1;
+    }
+    if (m->tile_class_end[1] < m->tile_class_end[0]) m->tile_class_end[1] = m->tile_class_end[0];
+    if (m->tile_class_end[2] < m->tile_class_end[1]) m->tile_class_end[2] = m->tile_class_end[1];
+    ts.swap(ts2); tb.swap(tb2); tc.swap(tc2);
+  }
   m->ntiles = (int64_t)ts.size();
   PYN_CHECK_CUDA(cudaMalloc(&m->tile_sig, sizeof(int) * ts.size()));
   PYN_CHECK_CUDA(cudaMalloc(&m->tile_start, sizeof(int) * ts.size()));
@@ -1286,6 +1366,7 @@ int pyn_asm_fill(const pyn_topo* t, const pyn_asm_desc* desc, const int64_t* d_i
         if (desc->bcmap->tiles_state == 1) {
           dv.sig_nodes = desc->bcmap->sig_nodes; dv.tile_sig = desc->bcmap->tile_sig;
           dv.tile_start = desc->bcmap->tile_start; dv.tile_cnt = desc->bcmap->tile_cnt; dv.ntiles = desc->bcmap->ntiles;
+          for (int c = 0; c < 3; ++c) dv.tile_class_end[c] = desc->bcmap->tile_class_end[c];
         }
       }
       rc = tmpl ? launch_templates(t, dv, d_indptr, d_data, st) : launch_interior(t, dv, d_indptr, d_indices, d_data, st);

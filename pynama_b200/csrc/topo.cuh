@@ -50,6 +50,7 @@ struct pyn_bcmap {
   int* sig_nodes;
   int *tile_sig, *tile_start, *tile_cnt;
   int64_t ntiles;
+  int64_t tile_class_end[3];   // tiles are sorted by valence class (1, 2, <= 4 incident elements), then by first node
   int tiles_state;   // 0 not built, 1 built, -1 unavailable
 };
 
