@@ -444,37 +444,38 @@ asm_interior_affine_kernel(pyn::TopoView t, DescView d, const int64_t* __restric
 // WARP takes a tile of 32 nodes of ONE signature, one node per lane:
 //   * the 13 (4) coefficients of the node's <= DEG elements live in REGISTERS for the whole row (DEG is a template
 //     parameter: the tiles are sorted by valence class and each class gets its own launch);
-//   * per pass of SIG_PT adjacency positions the signature's contribution list (the representative node's inverse map)
-//     is read by the lanes (k, q) and the product records it names are staged in shared memory, so the evaluation loop
-//     has no global loads and no look-ups: a warp-uniform test per (position, element), broadcast LDS.128 of the
-//     record, the closed form, one store of the block into the warp's output tile;
-//   * the output tile is flushed row-major: 8 lanes write one 128-byte (64-byte for 2x1 blocks) piece of one row.
+//   * the row is produced in passes of PT adjacency positions (128 bytes of every row).  The signature's contribution
+//     list (the representative node's inverse map) is read by the lanes (element k, position q) TWO passes ahead and
+//     the product records it names ONE pass ahead, into registers; they are put in shared memory when their pass
+//     begins, so the evaluation has no global loads and no look-ups: a warp-uniform bit test per (position, element),
+//     broadcast LDS.128 of the record, the closed form, one STS.128 into the warp's output tile;
+//   * the output tile is flushed row-major: 8 lanes write one 128-byte piece of one row.
 // Same order of additions per entry as every other assembly kernel (ascending cell order): same bits.
 constexpr int SIG_W = 4;       // warps (= tiles) per CTA
-constexpr int SIG_PT = 8;      // adjacency positions per pass
 constexpr int SIG_KMAX = 4;    // incident elements per node (quadrilateral meshes; larger valence: flat kernel)
 
 template <int CD>
-struct SigSmem {
+struct SigShape {
   static constexpr int RD = 2;
+  static constexpr int PT = 16 / CD;                                 // adjacency positions per pass: 16 doubles per row
   static constexpr int PR = CD == 2 ? pyn::PYN_AFF_PK : pyn::PYN_AFF_PR;
-  static constexpr int OSTR = RD * SIG_PT * CD + CD;                 // doubles per lane in the output tile (padded)
-  static constexpr int per_warp(int deg) { return 32 * OSTR + deg * SIG_PT * PR + RD * 32; }   // in 8-byte words
+  static constexpr int OSTR = RD * 16 + 2;                           // doubles per lane in the output tile (padded)
+  static constexpr int rounds(int deg) { return (deg * PT + 31) / 32; }   // staging rounds of 32 (k, q) pairs
+  static constexpr int per_warp(int deg) { return 32 * OSTR + rounds(deg) * 32 * PR + RD * 32; }   // 8-byte words
 };
 
 template <int CD, int DEG>
-__global__ void __launch_bounds__(SIG_W * 32)
+__global__ void __launch_bounds__(SIG_W * 32, DEG == 4 ? 3 : (DEG == 2 ? 4 : 5))
 asm_sig_affine_kernel(pyn::TopoView t, DescView d, const int64_t* __restrict__ indptr, double* __restrict__ data,
                       int64_t tile0, int64_t tile1) {
-  using S = SigSmem<CD>;
-  constexpr int RD = 2, PT = SIG_PT;
+  using S = SigShape<CD>;
+  constexpr int RD = 2, PT = S::PT, PR = S::PR, OSTR = S::OSTR, R = S::rounds(DEG);
   constexpr int NC = CD == 2 ? 13 : 4, C0 = CD == 2 ? 0 : 13;
-  constexpr int PR = S::PR, OSTR = S::OSTR;
   extern __shared__ __align__(16) double sg_dyn[];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  double* s_out = sg_dyn + (size_t)w * S::per_warp(DEG);             // [lane][a][q][b]
-  double* s_rec = s_out + 32 * OSTR;                                 // [k][q][PR]
-  double** s_ptr = reinterpret_cast<double**>(s_rec + DEG * PT * PR);   // [a][lane]: start of the lane's row a
+  double* s_out = sg_dyn + (size_t)w * S::per_warp(DEG);             // [lane][a][16 doubles of the pass]
+  double* s_rec = s_out + 32 * OSTR;                                 // [k * PT + q][PR]
+  double** s_ptr = reinterpret_cast<double**>(s_rec + R * 32 * PR);  // [a][lane]: start of the lane's row a
   const int64_t tile = tile0 + (int64_t)blockIdx.x * SIG_W + w;
   if (tile >= tile1) return;                                         // warps are independent: no CTA-wide barrier below
   const int sig = d.tile_sig[tile], start = d.tile_start[tile], cnt = d.tile_cnt[tile];
@@ -484,6 +485,25 @@ asm_sig_affine_kernel(pyn::TopoView t, DescView d, const int64_t* __restrict__ i
   const int deg = min((int)(t.n2e_ptr[rep + 1] - rb0), DEG);
   const uint8_t* ivrep = t.inv + t.inv_ptr[rep];
   const double* gtab = CD == 2 ? d.aff.pairK : d.aff.pairR;
+  // this lane's share of the staging: pair idx = r * 32 + lane = element kk, position qq of the pass
+  int kk[R], qq[R];
+  int64_t lrow[R];
+  const uint8_t* ivk[R];
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    const int idx = r * 32 + lane;
+    kk[r] = idx / PT;
+    qq[r] = idx % PT;
+    lrow[r] = kk[r] < deg ? (int64_t)t.n2e_loc[rb0 + kk[r]] * t.nn : 0;
+    ivk[r] = ivrep + kk[r] * L + qq[r];
+  }
+  int l0[R], l1[R];
+  double2 rg[R][PR / 2];
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    l0[r] = (kk[r] < deg && qq[r] < L) ? ivk[r][0] : 0xFF;
+    l1[r] = (kk[r] < deg && PT + qq[r] < L) ? ivk[r][PT] : 0xFF;
+  }
   const int j = d.sig_nodes[start + (lane < cnt ? lane : 0)];
   double cf[DEG][NC];
   {
@@ -497,80 +517,111 @@ asm_sig_affine_kernel(pyn::TopoView t, DescView d, const int64_t* __restrict__ i
     s_ptr[lane] = data + indptr[(int64_t)j * RD];
     s_ptr[32 + lane] = data + indptr[(int64_t)j * RD + 1];
   }
-  // this lane's share of the staging: element kk of the signature, position qq of the pass
-  const int kk = lane / PT, qq = lane % PT;
-  const int64_t lrow = kk < deg ? (int64_t)t.n2e_loc[rb0 + kk] * t.nn : 0;
+#pragma unroll
+  for (int r = 0; r < R; ++r)
+    if (l0[r] != 0xFF) {
+      const double2* rp = reinterpret_cast<const double2*>(gtab + (lrow[r] + l0[r]) * PR);
+#pragma unroll
+      for (int i = 0; i < PR / 2; ++i) rg[r][i] = __ldg(rp + i);
+    }
   const double sign = d.sign;
   for (int p0 = 0; p0 < L; p0 += PT) {
     const int wch = min(PT, L - p0);
-    int l = 0xFF;
-    if (kk < deg && qq < wch) l = ivrep[kk * L + p0 + qq];
-    if (l != 0xFF) {
-      const double2* rp = reinterpret_cast<const double2*>(gtab + (lrow + l) * PR);
-      double2* dst = reinterpret_cast<double2*>(s_rec + (kk * PT + qq) * PR);
+    // (A) the records of this pass (fetched during the previous one) go to shared memory; which (k, q) exist
+    unsigned mask[R];
 #pragma unroll
-      for (int i = 0; i < PR / 2; ++i) dst[i] = __ldg(rp + i);
+    for (int r = 0; r < R; ++r) {
+      const bool on = l0[r] != 0xFF;
+      if (on) {
+        double2* dst = reinterpret_cast<double2*>(s_rec + (r * 32 + lane) * PR);
+#pragma unroll
+        for (int i = 0; i < PR / 2; ++i) dst[i] = rg[r][i];
+      }
+      mask[r] = __ballot_sync(0xffffffffu, on);
     }
     __syncwarp();
-#pragma unroll 2
-    for (int q = 0; q < wch; ++q) {
-      double v[RD][CD];
+    // (B) fetch ahead: records of the next pass, contribution list of the one after
 #pragma unroll
-      for (int a = 0; a < RD; ++a)
+    for (int r = 0; r < R; ++r) {
+      l0[r] = l1[r];
+      if (l0[r] != 0xFF) {
+        const double2* rp = reinterpret_cast<const double2*>(gtab + (lrow[r] + l0[r]) * PR);
 #pragma unroll
-        for (int b = 0; b < CD; ++b) v[a][b] = 0.0;
+        for (int i = 0; i < PR / 2; ++i) rg[r][i] = __ldg(rp + i);
+      }
+      l1[r] = (kk[r] < deg && p0 + 2 * PT + qq[r] < L) ? ivk[r][p0 + 2 * PT] : 0xFF;
+    }
+    // (C) evaluation: 16 doubles of each of the lane's two rows, in units of one double2 per row
+    constexpr int NU = 8;                       // units per pass; a unit = 1 position (2x2 blocks) or 2 (2x1 blocks)
+    const int nu = (wch * CD + 1) / 2;
+    auto eval_unit = [&](int u) {
+      double v[2 / CD][RD][CD];
 #pragma unroll
-      for (int k = 0; k < DEG; ++k) {          // ascending cell order; the test is uniform across the warp
-        const int lk = __shfl_sync(0xffffffffu, l, k * PT + q);
-        if (lk != 0xFF) {
-          const double2* rs = reinterpret_cast<const double2*>(s_rec + (k * PT + q) * PR);
-          double rec[PR];
+      for (int h = 0; h < 2 / CD; ++h) {
+        const int q = u * (2 / CD) + h;
 #pragma unroll
-          for (int i = 0; i < PR / 2; ++i) {
-            const double2 x = rs[i];
-            rec[2 * i] = x.x;
-            rec[2 * i + 1] = x.y;
+        for (int a = 0; a < RD; ++a)
+#pragma unroll
+          for (int b = 0; b < CD; ++b) v[h][a][b] = 0.0;
+#pragma unroll
+        for (int k = 0; k < DEG; ++k) {          // ascending cell order; the test is uniform across the warp
+          const int bit = k * PT + q;            // < R * 32
+          const bool on = (CD == 2 && DEG == 1) ? true : (((R == 1 || bit < 32 ? mask[0] : mask[R - 1]) >> (bit & 31)) & 1u);
+          if (on) {
+            const double2* rs = reinterpret_cast<const double2*>(s_rec + bit * PR);
+            double rec[PR];
+#pragma unroll
+            for (int i = 0; i < PR / 2; ++i) {
+              const double2 x = rs[i];
+              rec[2 * i] = x.x;
+              rec[2 * i + 1] = x.y;
+            }
+            double blk[RD][CD];
+            if constexpr (CD == 2) {
+              pyn::affine_block_K(cf[k], rec, blk);
+            } else {
+              pyn::affine_block_R(cf[k], rec, d.which, d.aff.alpha_w, d.aff.alpha_d, blk);
+            }
+#pragma unroll
+            for (int a = 0; a < RD; ++a)
+#pragma unroll
+              for (int b = 0; b < CD; ++b) v[h][a][b] += sign * blk[a][b];
           }
-          double blk[RD][CD];
-          if constexpr (CD == 2) {
-            pyn::affine_block_K(cf[k], rec, blk);
-          } else {
-            pyn::affine_block_R(cf[k], rec, d.which, d.aff.alpha_w, d.aff.alpha_d, blk);
-          }
-#pragma unroll
-          for (int a = 0; a < RD; ++a)
-#pragma unroll
-            for (int b = 0; b < CD; ++b) v[a][b] += sign * blk[a][b];
         }
       }
 #pragma unroll
       for (int a = 0; a < RD; ++a) {
-        double* o = s_out + lane * OSTR + (a * PT + q) * CD;
+        double2* o = reinterpret_cast<double2*>(s_out + lane * OSTR + a * 16 + 2 * u);
         if constexpr (CD == 2) {
-          *reinterpret_cast<double2*>(o) = make_double2(v[a][0], v[a][1]);
+          *o = make_double2(v[0][a][0], v[0][a][1]);
         } else {
-          o[0] = v[a][0];
+          *o = make_double2(v[0][a][0], v[2 / CD - 1][a][0]);
         }
       }
+    };
+    if (nu == NU) {
+#pragma unroll (DEG == 1 ? 4 : 2)
+      for (int u = 0; u < NU; ++u) eval_unit(u);
+    } else {
+      for (int u = 0; u < nu; ++u) eval_unit(u);
     }
     __syncwarp();
-    // flush: 2^s lanes per row piece (s = ceil log2 of the positions of this pass), 32 >> (s + 1) nodes per step
-    const int s = wch > 4 ? 3 : (wch > 2 ? 2 : wch - 1);
-    const int fq = lane & ((1 << s) - 1), fa = (lane >> s) & 1, fn = lane >> (s + 1), npi = 32 >> (s + 1);
-    if (fq < wch) {
+    // (D) flush: 8 lanes per 128-byte piece of a row, 2 nodes per step
+    {
+      const int nd = wch * CD;                  // valid doubles of every piece
+      const int u2 = (lane & 7) * 2, fa = (lane >> 3) & 1;
+      const bool full = u2 + 1 < nd, any = u2 < nd;
+      if (any) {
 #pragma unroll 4
-      for (int n = fn; n < cnt; n += npi) {
-        double* o = s_ptr[fa * 32 + n] + (int64_t)(p0 + fq) * CD;
-        const double* src = s_out + n * OSTR + (fa * PT + fq) * CD;
-        if constexpr (CD == 2) {
-          if ((reinterpret_cast<uintptr_t>(o) & 15) == 0) {
+        for (int n = lane >> 4; n < cnt; n += 2) {
+          double* o = s_ptr[fa * 32 + n] + (int64_t)p0 * CD + u2;
+          const double* src = s_out + n * OSTR + fa * 16 + u2;
+          if (full && (reinterpret_cast<uintptr_t>(o) & 15) == 0) {
             *reinterpret_cast<double2*>(o) = *reinterpret_cast<const double2*>(src);
           } else {
             o[0] = src[0];
-            o[1] = src[1];
+            if (full) o[1] = src[1];
           }
-        } else {
-          o[0] = src[0];
         }
       }
     }
@@ -973,7 +1024,7 @@ static int launch_interior(const pyn_topo* t, const DescView& dv, const int64_t*
 #define PYN_SIG_CASE(C, DG, cls)                                                                                        \
     if (dv.cdof == C && dv.tile_class_end[cls] > c0) {                                                                  \
       const int64_t c1 = dv.tile_class_end[cls], g = (c1 - c0 + SIG_W - 1) / SIG_W;                                    \
-      const size_t dyn = sizeof(double) * (size_t)SIG_W * SigSmem<C>::per_warp(DG);                                    \
+      const size_t dyn = sizeof(double) * (size_t)SIG_W * SigShape<C>::per_warp(DG);                                    \
       PYN_REQUIRE(g < 0x7fffffff, "affine assembly: too many signature tiles");                                        \
       PYN_CHECK_CUDA(cudaFuncSetAttribute(asm_sig_affine_kernel<C, DG>, cudaFuncAttributeMaxDynamicSharedMemorySize,   \
                                           (int)dyn));                                                                  \
