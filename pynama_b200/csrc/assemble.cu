@@ -35,7 +35,7 @@ struct DescView {
   pyn::AffTables aff;
   int which;             // 0 K (2x2 blocks), 1 Rw, 2 Rd (2x1 blocks)
   // signature tiles of the boundary map (structured meshes; NULL: not available)
-  const int *sig_nodes, *tile_sig, *tile_start, *tile_cnt;
+  const int *tile_desc, *tile_slot;
   int64_t ntiles;
   int64_t tile_class_end[3];
 };
@@ -454,6 +454,19 @@ asm_interior_affine_kernel(pyn::TopoView t, DescView d, const int64_t* __restric
 constexpr int SIG_W = 4;       // warps (= tiles) per CTA
 constexpr int SIG_KMAX = 4;    // incident elements per node (quadrilateral meshes; larger valence: flat kernel)
 
+// v2 store when the address is 16-byte aligned, else one or two scalar stores -- predicated, no branches
+__device__ __forceinline__ void sig_store(double* o, double2 x, bool v2, bool lo, bool hi) {
+  asm volatile(
+      "{\n\t.reg .pred p2, pl, ph;\n\t"
+      "setp.ne.b32 p2, %3, 0;\n\tsetp.ne.b32 pl, %4, 0;\n\tsetp.ne.b32 ph, %5, 0;\n\t"
+      "@p2 st.global.v2.f64 [%0], {%1, %2};\n\t"
+      "@pl st.global.f64 [%0], %1;\n\t"
+      "@ph st.global.f64 [%0+8], %2;\n\t}"
+      :
+      : "l"(o), "d"(x.x), "d"(x.y), "r"((int)v2), "r"((int)lo), "r"((int)hi)
+      : "memory");
+}
+
 template <int CD>
 struct SigShape {
   static constexpr int RD = 2;
@@ -478,12 +491,12 @@ asm_sig_affine_kernel(pyn::TopoView t, DescView d, const int64_t* __restrict__ i
   double** s_ptr = reinterpret_cast<double**>(s_rec + R * 32 * PR);  // [a][lane]: start of the lane's row a
   const int64_t tile = tile0 + (int64_t)blockIdx.x * SIG_W + w;
   if (tile >= tile1) return;                                         // warps are independent: no CTA-wide barrier below
-  const int sig = d.tile_sig[tile], start = d.tile_start[tile], cnt = d.tile_cnt[tile];
-  const int rep = t.sig_rep[sig];
-  const int L = (int)(t.adj_ptr[rep + 1] - t.adj_ptr[rep]);
-  const int64_t rb0 = t.n2e_ptr[rep];
-  const int deg = min((int)(t.n2e_ptr[rep + 1] - rb0), DEG);
-  const uint8_t* ivrep = t.inv + t.inv_ptr[rep];
+  const int4 td0 = __ldg(reinterpret_cast<const int4*>(d.tile_desc) + tile * 2);
+  const int2 td1 = __ldg(reinterpret_cast<const int2*>(d.tile_desc) + tile * 4 + 2);
+  const int2 slot = __ldg(reinterpret_cast<const int2*>(d.tile_slot) + tile * 32 + lane);
+  const int cnt = td0.x, L = td0.y, deg = min(td0.z, DEG);
+  const unsigned lrp = (unsigned)td0.w;
+  const uint8_t* ivrep = t.inv + (((int64_t)td1.y << 32) | (int64_t)(unsigned)td1.x);
   const double* gtab = CD == 2 ? d.aff.pairK : d.aff.pairR;
   // this lane's share of the staging: pair idx = r * 32 + lane = element kk, position qq of the pass
   int kk[R], qq[R];
@@ -494,7 +507,7 @@ asm_sig_affine_kernel(pyn::TopoView t, DescView d, const int64_t* __restrict__ i
     const int idx = r * 32 + lane;
     kk[r] = idx / PT;
     qq[r] = idx % PT;
-    lrow[r] = kk[r] < deg ? (int64_t)t.n2e_loc[rb0 + kk[r]] * t.nn : 0;
+    lrow[r] = (int64_t)((lrp >> (8 * kk[r])) & 255u) * t.nn;
     ivk[r] = ivrep + kk[r] * L + qq[r];
   }
   int l0[R], l1[R];
@@ -504,10 +517,10 @@ asm_sig_affine_kernel(pyn::TopoView t, DescView d, const int64_t* __restrict__ i
     l0[r] = (kk[r] < deg && qq[r] < L) ? ivk[r][0] : 0xFF;
     l1[r] = (kk[r] < deg && PT + qq[r] < L) ? ivk[r][PT] : 0xFF;
   }
-  const int j = d.sig_nodes[start + (lane < cnt ? lane : 0)];
+  const int j = slot.x;
   double cf[DEG][NC];
   {
-    const int64_t b0 = t.n2e_ptr[j];
+    const int64_t b0 = slot.y;
 #pragma unroll
     for (int k = 0; k < DEG; ++k) {
       const double* cg = d.coef + (int64_t)t.n2e_elem[b0 + (k < deg ? k : 0)] * PYN_AFF_NCOEF + C0;
@@ -606,16 +619,35 @@ asm_sig_affine_kernel(pyn::TopoView t, DescView d, const int64_t* __restrict__ i
       for (int u = 0; u < nu; ++u) eval_unit(u);
     }
     __syncwarp();
-    // (D) flush: 8 lanes per 128-byte piece of a row, 2 nodes per step
+    // (D) flush: 8 lanes per 128-byte piece of a row, 2 nodes per step; 4 steps in flight (pointers, then data, then
+    // predicated stores: no branches, nothing serialised on a register)
     {
       const int nd = wch * CD;                  // valid doubles of every piece
       const int u2 = (lane & 7) * 2, fa = (lane >> 3) & 1;
       const bool full = u2 + 1 < nd, any = u2 < nd;
-      if (any) {
-#pragma unroll 4
+      double* const* sp = s_ptr + fa * 32;
+      const double* sb = s_out + fa * 16 + u2;
+      const int64_t off = (int64_t)p0 * CD + u2;
+      if (wch == PT && cnt == 32) {             // whole pieces of a whole tile (nearly all of them): one predicate left
+#pragma unroll
+        for (int n0 = 0; n0 < 32; n0 += 8) {
+          const int nb = n0 + (lane >> 4);
+          double* o[4];
+          double2 x[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) o[i] = sp[nb + 2 * i] + off;
+#pragma unroll
+          for (int i = 0; i < 4; ++i) x[i] = *reinterpret_cast<const double2*>(sb + (nb + 2 * i) * OSTR);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const bool al = (reinterpret_cast<uintptr_t>(o[i]) & 15) == 0;
+            sig_store(o[i], x[i], al, !al, !al);
+          }
+        }
+      } else if (any) {
         for (int n = lane >> 4; n < cnt; n += 2) {
-          double* o = s_ptr[fa * 32 + n] + (int64_t)p0 * CD + u2;
-          const double* src = s_out + n * OSTR + fa * 16 + u2;
+          double* o = sp[n] + off;
+          const double* src = sb + n * OSTR;
           if (full && (reinterpret_cast<uintptr_t>(o) & 15) == 0) {
             *reinterpret_cast<double2*>(o) = *reinterpret_cast<const double2*>(src);
           } else {
@@ -968,7 +1000,7 @@ int make_desc(const pyn_asm_desc* desc, DescView* v) {
   v->sign = desc->sign; v->E = desc->d_E; v->E_stride = desc->E_stride; v->rowscale = desc->d_rowscale;
   v->flags = desc->bcmap ? desc->bcmap->flags : nullptr;
   v->coef = nullptr; v->which = 0;
-  v->sig_nodes = v->tile_sig = v->tile_start = v->tile_cnt = nullptr; v->ntiles = 0;
+  v->tile_desc = v->tile_slot = nullptr; v->ntiles = 0;
   memset(&v->aff, 0, sizeof(v->aff));
   if (desc->d_coef) {   // fused integrate-and-assemble on affine elements
     PYN_REQUIRE(desc->elem != nullptr, "affine assembly: element handle missing");
@@ -1018,7 +1050,7 @@ static int launch_interior(const pyn_topo* t, const DescView& dv, const int64_t*
                            cudaStream_t st) {
   const pyn::TopoView tv = pyn::view_of(t);
   const int grid = pyn::grid_for((t->nnodes + ASM_NB - 1) / ASM_NB * 256, 256, 8);
-  if (dv.coef && !indices && data && dv.tile_sig) {   // structured mesh, values only: signature-grouped kernel
+  if (dv.coef && !indices && data && dv.tile_desc) {   // structured mesh, values only: signature-grouped kernel
     PYN_REQUIRE(tv.nn == dv.aff.n * dv.aff.n, "affine assembly: element handle of another order");
     int64_t c0 = 0;
 #define PYN_SIG_CASE(C, DG, cls)                                                                                        \
@@ -1178,6 +1210,34 @@ __global__ void tile_first_kernel(int64_t nt, const int* __restrict__ start, con
     deg[i] = (int)(n2e_ptr[j + 1] - n2e_ptr[j]);
   }
 }
+__global__ void tile_build_kernel(pyn::TopoView t, int64_t nt, const int* __restrict__ tile_sig,
+                                  const int* __restrict__ tile_start, const int* __restrict__ tile_cnt,
+                                  const int* __restrict__ sig_nodes, int* __restrict__ desc, int* __restrict__ slot) {
+  const int lane = threadIdx.x & 31;
+  const int64_t w0 = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5, nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t i = w0; i < nt; i += nw) {
+    const int start = tile_start[i], cnt = tile_cnt[i];
+    const int j = sig_nodes[start + (lane < cnt ? lane : 0)];
+    slot[(i * 32 + lane) * 2] = j;
+    slot[(i * 32 + lane) * 2 + 1] = (int)t.n2e_ptr[j];
+    if (lane == 0) {
+      const int rep = t.sig_rep[tile_sig[i]];
+      const int64_t rb0 = t.n2e_ptr[rep];
+      const int deg = (int)(t.n2e_ptr[rep + 1] - rb0);
+      unsigned lr = 0;
+      for (int k = 0; k < deg && k < 4; ++k) lr |= (unsigned)(t.n2e_loc[rb0 + k] & 255) << (8 * k);
+      const int64_t io = t.inv_ptr[rep];
+      int* o = desc + i * 8;
+      o[0] = cnt;
+      o[1] = (int)(t.adj_ptr[rep + 1] - t.adj_ptr[rep]);
+      o[2] = deg;
+      o[3] = (int)lr;
+      o[4] = (int)(io & 0xffffffffll);
+      o[5] = (int)(io >> 32);
+      o[6] = o[7] = 0;
+    }
+  }
+}
 }  // namespace
 
 static int ensure_sig_tiles(const pyn_topo* t, const pyn_bcmap* mc, cudaStream_t st) {
@@ -1189,7 +1249,7 @@ static int ensure_sig_tiles(const pyn_topo* t, const pyn_bcmap* mc, cudaStream_t
   static const bool off = getenv("PYN_AFF_SIG") == nullptr;
   if (off || t->nsig <= 0 || t->max_valence > SIG_KMAX || t->nn > 255) return PYN_OK;
   const int64_t n = t->nnodes, nint = t->nnodes - m->nlist;
-  if (nint <= 0 || nint >= 0x7fffffff) return PYN_OK;
+  if (nint <= 0 || nint >= 0x7fffffff || (int64_t)t->ne * t->nn >= 0x7fffffff) return PYN_OK;
   int *nodes = nullptr, *keys = nullptr, *keys2 = nullptr, *counts = nullptr;
   int64_t* d_n = nullptr;
   void* tmp = nullptr;
@@ -1268,6 +1328,15 @@ static int ensure_sig_tiles(const pyn_topo* t, const pyn_bcmap* mc, cudaStream_t
   PYN_CHECK_CUDA(cudaMemcpyAsync(m->tile_start, tb.data(), sizeof(int) * ts.size(), cudaMemcpyHostToDevice, st));
   PYN_CHECK_CUDA(cudaMemcpyAsync(m->tile_cnt, tc.data(), sizeof(int) * ts.size(), cudaMemcpyHostToDevice, st));
   PYN_CHECK_CUDA(cudaStreamSynchronize(st));
+  PYN_CHECK_CUDA(cudaMalloc(&m->tile_desc, sizeof(int) * 8 * ts.size()));
+  PYN_CHECK_CUDA(cudaMalloc(&m->tile_slot, sizeof(int) * 64 * ts.size()));
+  tile_build_kernel<<<pyn::grid_for((int64_t)ts.size() * 32, 256), 256, 0, st>>>(
+      pyn::view_of(t), (int64_t)ts.size(), m->tile_sig, m->tile_start, m->tile_cnt, m->sig_nodes, m->tile_desc,
+      m->tile_slot);
+  PYN_CHECK_LAUNCH();
+  PYN_CHECK_CUDA(cudaStreamSynchronize(st));
+  cudaFree(m->sig_nodes); cudaFree(m->tile_sig); cudaFree(m->tile_start); cudaFree(m->tile_cnt);
+  m->sig_nodes = m->tile_sig = m->tile_start = m->tile_cnt = nullptr;
   m->tiles_state = 1;
   return PYN_OK;
 }
@@ -1324,6 +1393,7 @@ int pyn_bcmap_destroy(pyn_bcmap* m) {
   cudaFreeAsync(m->flags, m->st);   // stream-ordered: no device-wide synchronisation, the pool keeps the memory
   cudaFreeAsync(m->list, m->st);
   cudaFree(m->sig_nodes); cudaFree(m->tile_sig); cudaFree(m->tile_start); cudaFree(m->tile_cnt);
+  cudaFree(m->tile_desc); cudaFree(m->tile_slot);
   delete m;
   return PYN_OK;
 }
@@ -1415,8 +1485,7 @@ int pyn_asm_fill(const pyn_topo* t, const pyn_asm_desc* desc, const int64_t* d_i
         rc = ensure_sig_tiles(t, desc->bcmap, st);
         if (rc) return rc;
         if (desc->bcmap->tiles_state == 1) {
-          dv.sig_nodes = desc->bcmap->sig_nodes; dv.tile_sig = desc->bcmap->tile_sig;
-          dv.tile_start = desc->bcmap->tile_start; dv.tile_cnt = desc->bcmap->tile_cnt; dv.ntiles = desc->bcmap->ntiles;
+          dv.tile_desc = desc->bcmap->tile_desc; dv.tile_slot = desc->bcmap->tile_slot; dv.ntiles = desc->bcmap->ntiles;
           for (int c = 0; c < 3; ++c) dv.tile_class_end[c] = desc->bcmap->tile_class_end[c];
         }
       }
