@@ -441,21 +441,22 @@ asm_interior_affine_kernel(pyn::TopoView t, DescView d, const int64_t* __restric
 // The flat kernel above spends most of its instructions on finding out, per output block, which node it belongs to and
 // which of the node's elements contribute (and its element loop diverges).  On a structured mesh that information is the
 // same for every node of a row signature (topo.cuh: byte-identical incidence local indices and inverse maps).  Here a
-// WARP takes a tile of 32 nodes of ONE signature, one node per lane:
-//   * the 13 (4) coefficients of the node's <= DEG elements live in REGISTERS for the whole row (DEG is a template
-//     parameter: the tiles are sorted by valence class and each class gets its own launch);
-//   * the row is produced in passes of PT adjacency positions (128 bytes of every row).  The signature's contribution
-//     list (the representative node's inverse map) is read by the lanes (element k, position q) TWO passes ahead and
-//     the product records it names ONE pass ahead, into registers; they are put in shared memory when their pass
-//     begins, so the evaluation has no global loads and no look-ups: a warp-uniform bit test per (position, element),
-//     broadcast LDS.128 of the record, the closed form, one STS.128 into the warp's output tile;
-//   * the output tile is flushed row-major: 8 lanes write one 128-byte piece of one row.
-// Same order of additions per entry as every other assembly kernel (ascending cell order): same bits.
+// WARP takes a tile of 32 nodes of ONE signature and walks their rows in passes of 128 bytes (PT adjacency positions):
+//   * 8 lanes share a node and split the positions of the pass, 4 nodes per step, 8 steps per pass.  A lane's position
+//     is fixed during a pass, so the product records it needs (one per incident element: the representative node's
+//     inverse map says which) sit in its REGISTERS for all 32 nodes -- fetched one pass ahead, the inverse-map bytes two
+//     passes ahead;
+//   * what changes from step to step is the node: the 13 (4) coefficients of its <= DEG elements are staged once per
+//     tile in shared memory and read as broadcast LDS.128 (4 distinct nodes per warp, distinct banks);
+//   * the 8 lanes of a node store 128 consecutive bytes of each of its two rows straight from registers: no output
+//     tile, no transposition, no barrier after the coefficients are staged, every step independent of the others.
+// DEG (incident elements per node) is a template parameter: the tiles are sorted by valence class and each class gets
+// its own launch.  Same order of additions per entry as every other assembly kernel (ascending cell order): same bits.
 constexpr int SIG_W = 4;       // warps (= tiles) per CTA
 constexpr int SIG_KMAX = 4;    // incident elements per node (quadrilateral meshes; larger valence: flat kernel)
 
 // v2 store when the address is 16-byte aligned, else one or two scalar stores -- predicated, no branches
-__device__ __forceinline__ void sig_store(double* o, double2 x, bool v2, bool lo, bool hi) {
+__device__ __forceinline__ void sig_store(double* o, double x0, double x1, bool v2, bool lo, bool hi) {
   asm volatile(
       "{\n\t.reg .pred p2, pl, ph;\n\t"
       "setp.ne.b32 p2, %3, 0;\n\tsetp.ne.b32 pl, %4, 0;\n\tsetp.ne.b32 ph, %5, 0;\n\t"
@@ -463,32 +464,32 @@ __device__ __forceinline__ void sig_store(double* o, double2 x, bool v2, bool lo
       "@pl st.global.f64 [%0], %1;\n\t"
       "@ph st.global.f64 [%0+8], %2;\n\t}"
       :
-      : "l"(o), "d"(x.x), "d"(x.y), "r"((int)v2), "r"((int)lo), "r"((int)hi)
+      : "l"(o), "d"(x0), "d"(x1), "r"((int)v2), "r"((int)lo), "r"((int)hi)
       : "memory");
 }
 
 template <int CD>
 struct SigShape {
   static constexpr int RD = 2;
-  static constexpr int PT = 16 / CD;                                 // adjacency positions per pass: 16 doubles per row
+  static constexpr int NP = 2 / CD;                                  // adjacency positions per lane and pass
+  static constexpr int PT = 8 * NP;                                  // ... per pass: 16 doubles of every row
   static constexpr int PR = CD == 2 ? pyn::PYN_AFF_PK : pyn::PYN_AFF_PR;
-  static constexpr int OSTR = RD * 16 + 2;                           // doubles per lane in the output tile (padded)
-  static constexpr int rounds(int deg) { return (deg * PT + 31) / 32; }   // staging rounds of 32 (k, q) pairs
-  static constexpr int per_warp(int deg) { return 32 * OSTR + rounds(deg) * 32 * PR + RD * 32; }   // 8-byte words
+  static constexpr int NC = CD == 2 ? 13 : 4, NCP = CD == 2 ? 14 : 4;   // coefficients per element (padded to 16 B)
+  static constexpr int per_warp(int deg) { return 32 * deg * NCP + 32 * RD; }   // 8-byte words of shared memory
 };
 
 template <int CD, int DEG>
-__global__ void __launch_bounds__(SIG_W * 32, DEG == 4 ? 3 : (DEG == 2 ? 4 : 5))
+__global__ void __launch_bounds__(SIG_W * 32, DEG == 4 ? 3 : 4)
 asm_sig_affine_kernel(pyn::TopoView t, DescView d, const int64_t* __restrict__ indptr, double* __restrict__ data,
                       int64_t tile0, int64_t tile1) {
   using S = SigShape<CD>;
-  constexpr int RD = 2, PT = S::PT, PR = S::PR, OSTR = S::OSTR, R = S::rounds(DEG);
-  constexpr int NC = CD == 2 ? 13 : 4, C0 = CD == 2 ? 0 : 13;
+  constexpr int RD = 2, PT = S::PT, PR = S::PR, NP = S::NP, NC = S::NC, NCP = S::NCP;
+  constexpr int C0 = CD == 2 ? 0 : 13;
+  constexpr bool DBL = DEG <= 2;                                     // records double-buffered in registers
   extern __shared__ __align__(16) double sg_dyn[];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  double* s_out = sg_dyn + (size_t)w * S::per_warp(DEG);             // [lane][a][16 doubles of the pass]
-  double* s_rec = s_out + 32 * OSTR;                                 // [k * PT + q][PR]
-  double** s_ptr = reinterpret_cast<double**>(s_rec + R * 32 * PR);  // [a][lane]: start of the lane's row a
+  double* s_cf = sg_dyn + (size_t)w * S::per_warp(DEG);              // [node][k][NCP]
+  double** s_ptr = reinterpret_cast<double**>(s_cf + 32 * DEG * NCP);   // [node][a]: start of row a of the node
   const int64_t tile = tile0 + (int64_t)blockIdx.x * SIG_W + w;
   if (tile >= tile1) return;                                         // warps are independent: no CTA-wide barrier below
   const int4 td0 = __ldg(reinterpret_cast<const int4*>(d.tile_desc) + tile * 2);
@@ -498,166 +499,149 @@ asm_sig_affine_kernel(pyn::TopoView t, DescView d, const int64_t* __restrict__ i
   const unsigned lrp = (unsigned)td0.w;
   const uint8_t* ivrep = t.inv + (((int64_t)td1.y << 32) | (int64_t)(unsigned)td1.x);
   const double* gtab = CD == 2 ? d.aff.pairK : d.aff.pairR;
-  // this lane's share of the staging: pair idx = r * 32 + lane = element kk, position qq of the pass
-  int kk[R], qq[R];
-  int64_t lrow[R];
-  const uint8_t* ivk[R];
+  const int nn = t.nn;
+  // geometry of the pass that starts at position p: 2^s lanes per node (8 unless the pass is a narrow tail)
+  auto lanes_log2 = [&](int p) {
+    const int nu = (min(PT, L - p) + NP - 1) / NP;                   // units (double2 per row) of the pass
+    return nu > 4 ? 3 : (nu > 2 ? 2 : (nu > 1 ? 1 : 0));
+  };
+  // inverse-map bytes of this lane's positions in the pass that starts at p (0xFF: no contribution / no position)
+  auto load_l = [&](int p, int (&l)[DEG][NP]) {
+    const int s = p < L ? lanes_log2(p) : 0;
+    const int u = lane & ((1 << s) - 1);
 #pragma unroll
-  for (int r = 0; r < R; ++r) {
-    const int idx = r * 32 + lane;
-    kk[r] = idx / PT;
-    qq[r] = idx % PT;
-    lrow[r] = (int64_t)((lrp >> (8 * kk[r])) & 255u) * t.nn;
-    ivk[r] = ivrep + kk[r] * L + qq[r];
-  }
-  int l0[R], l1[R];
-  double2 rg[R][PR / 2];
+    for (int k = 0; k < DEG; ++k)
 #pragma unroll
-  for (int r = 0; r < R; ++r) {
-    l0[r] = (kk[r] < deg && qq[r] < L) ? ivk[r][0] : 0xFF;
-    l1[r] = (kk[r] < deg && PT + qq[r] < L) ? ivk[r][PT] : 0xFF;
-  }
-  const int j = slot.x;
-  double cf[DEG][NC];
-  {
+      for (int h = 0; h < NP; ++h) {
+        const int q = p + u * NP + h;
+        l[k][h] = (k < deg && q < L) ? (int)ivrep[k * L + q] : 0xFF;
+      }
+  };
+  auto load_rec = [&](const int (&l)[DEG][NP], double (&rec)[DEG][NP][PR]) {
+#pragma unroll
+    for (int k = 0; k < DEG; ++k)
+#pragma unroll
+      for (int h = 0; h < NP; ++h)
+        if (l[k][h] != 0xFF) {
+          const double2* rp =
+              reinterpret_cast<const double2*>(gtab + ((int64_t)((lrp >> (8 * k)) & 255u) * nn + l[k][h]) * PR);
+#pragma unroll
+          for (int i = 0; i < PR / 2; ++i) {
+            const double2 x = __ldg(rp + i);
+            rec[k][h][2 * i] = x.x;
+            rec[k][h][2 * i + 1] = x.y;
+          }
+        }
+  };
+  int l0[DEG][NP], l1[DEG][NP];
+  double rec[DEG][NP][PR], recn[DBL ? DEG : 1][NP][PR];
+#pragma unroll
+  for (int k = 0; k < DEG; ++k)
+#pragma unroll
+    for (int h = 0; h < NP; ++h)
+#pragma unroll
+      for (int i = 0; i < PR; ++i) {
+        rec[k][h][i] = 0.0;
+        if (DBL) recn[k][h][i] = 0.0;
+      }
+  load_l(0, l0);
+  load_l(PT, l1);
+  {  // coefficients and row starts of this lane's node -> shared memory
+    const int j = slot.x;
     const int64_t b0 = slot.y;
 #pragma unroll
     for (int k = 0; k < DEG; ++k) {
       const double* cg = d.coef + (int64_t)t.n2e_elem[b0 + (k < deg ? k : 0)] * PYN_AFF_NCOEF + C0;
+      double c[NC];
 #pragma unroll
-      for (int c = 0; c < NC; ++c) cf[k][c] = __ldg(cg + c);
+      for (int i = 0; i < NC; ++i) c[i] = __ldg(cg + i);
+#pragma unroll
+      for (int i = 0; i < NC; ++i) s_cf[(lane * DEG + k) * NCP + i] = c[i];
     }
-    s_ptr[lane] = data + indptr[(int64_t)j * RD];
-    s_ptr[32 + lane] = data + indptr[(int64_t)j * RD + 1];
+    s_ptr[lane * RD] = data + indptr[(int64_t)j * RD];
+    s_ptr[lane * RD + 1] = data + indptr[(int64_t)j * RD + 1];
   }
-#pragma unroll
-  for (int r = 0; r < R; ++r)
-    if (l0[r] != 0xFF) {
-      const double2* rp = reinterpret_cast<const double2*>(gtab + (lrow[r] + l0[r]) * PR);
-#pragma unroll
-      for (int i = 0; i < PR / 2; ++i) rg[r][i] = __ldg(rp + i);
-    }
+  load_rec(l0, rec);
+  __syncwarp();
   const double sign = d.sign;
   for (int p0 = 0; p0 < L; p0 += PT) {
     const int wch = min(PT, L - p0);
-    // (A) the records of this pass (fetched during the previous one) go to shared memory; which (k, q) exist
-    unsigned mask[R];
+    const int s = lanes_log2(p0);
+    const int u = lane & ((1 << s) - 1), grp = lane >> s, npg = 32 >> s;
+    // fetch ahead: records of the next pass, inverse-map bytes of the one after
+    if constexpr (DBL) load_rec(l1, recn);
+    int l2[DEG][NP];
+    load_l(p0 + 2 * PT, l2);
+    bool on[DEG][NP], anyk[DEG];
 #pragma unroll
-    for (int r = 0; r < R; ++r) {
-      const bool on = l0[r] != 0xFF;
-      if (on) {
-        double2* dst = reinterpret_cast<double2*>(s_rec + (r * 32 + lane) * PR);
+    for (int k = 0; k < DEG; ++k) {
 #pragma unroll
-        for (int i = 0; i < PR / 2; ++i) dst[i] = rg[r][i];
-      }
-      mask[r] = __ballot_sync(0xffffffffu, on);
+      for (int h = 0; h < NP; ++h) on[k][h] = l0[k][h] != 0xFF;
+      anyk[k] = __any_sync(0xffffffffu, on[k][0] || on[k][NP - 1]);
     }
-    __syncwarp();
-    // (B) fetch ahead: records of the next pass, contribution list of the one after
+    const bool act = u * NP < wch;                           // this lane has a unit (double2 of each row) in this pass
+    const bool second = CD == 2 || u * NP + 1 < wch;         // ... and the unit's second double exists
+    const int64_t off = (int64_t)(p0 + u * NP) * CD;
+#pragma unroll 2
+    for (int st = 0; st < (1 << s); ++st) {                  // npg nodes per step
+      const int n = st * npg + grp;
+      const double* cfn = s_cf + n * (DEG * NCP);
+      const longlong2 pp = *reinterpret_cast<const longlong2*>(s_ptr + n * RD);
+      double v[NP][RD][CD];
 #pragma unroll
-    for (int r = 0; r < R; ++r) {
-      l0[r] = l1[r];
-      if (l0[r] != 0xFF) {
-        const double2* rp = reinterpret_cast<const double2*>(gtab + (lrow[r] + l0[r]) * PR);
-#pragma unroll
-        for (int i = 0; i < PR / 2; ++i) rg[r][i] = __ldg(rp + i);
-      }
-      l1[r] = (kk[r] < deg && p0 + 2 * PT + qq[r] < L) ? ivk[r][p0 + 2 * PT] : 0xFF;
-    }
-    // (C) evaluation: 16 doubles of each of the lane's two rows, in units of one double2 per row
-    constexpr int NU = 8;                       // units per pass; a unit = 1 position (2x2 blocks) or 2 (2x1 blocks)
-    const int nu = (wch * CD + 1) / 2;
-    auto eval_unit = [&](int u) {
-      double v[2 / CD][RD][CD];
-#pragma unroll
-      for (int h = 0; h < 2 / CD; ++h) {
-        const int q = u * (2 / CD) + h;
+      for (int h = 0; h < NP; ++h)
 #pragma unroll
         for (int a = 0; a < RD; ++a)
 #pragma unroll
           for (int b = 0; b < CD; ++b) v[h][a][b] = 0.0;
 #pragma unroll
-        for (int k = 0; k < DEG; ++k) {          // ascending cell order; the test is uniform across the warp
-          const int bit = k * PT + q;            // < R * 32
-          const bool on = (CD == 2 && DEG == 1) ? true : (((R == 1 || bit < 32 ? mask[0] : mask[R - 1]) >> (bit & 31)) & 1u);
-          if (on) {
-            const double2* rs = reinterpret_cast<const double2*>(s_rec + bit * PR);
-            double rec[PR];
+      for (int k = 0; k < DEG; ++k) {                        // ascending cell order
+        if (DEG == 1 || anyk[k]) {                           // uniform: some lane of the warp takes element k
+          double cf[NCP];
 #pragma unroll
-            for (int i = 0; i < PR / 2; ++i) {
-              const double2 x = rs[i];
-              rec[2 * i] = x.x;
-              rec[2 * i + 1] = x.y;
-            }
+          for (int i = 0; i < NCP / 2; ++i) {
+            const double2 x = *reinterpret_cast<const double2*>(cfn + k * NCP + 2 * i);
+            cf[2 * i] = x.x;
+            cf[2 * i + 1] = x.y;
+          }
+#pragma unroll
+          for (int h = 0; h < NP; ++h) {
             double blk[RD][CD];
             if constexpr (CD == 2) {
-              pyn::affine_block_K(cf[k], rec, blk);
+              pyn::affine_block_K(cf, rec[k][h], blk);
             } else {
-              pyn::affine_block_R(cf[k], rec, d.which, d.aff.alpha_w, d.aff.alpha_d, blk);
+              pyn::affine_block_R(cf, rec[k][h], d.which, d.aff.alpha_w, d.aff.alpha_d, blk);
             }
+            if (on[k][h]) {
 #pragma unroll
-            for (int a = 0; a < RD; ++a)
+              for (int a = 0; a < RD; ++a)
 #pragma unroll
-              for (int b = 0; b < CD; ++b) v[h][a][b] += sign * blk[a][b];
+                for (int b = 0; b < CD; ++b) v[h][a][b] += sign * blk[a][b];
+            }
           }
         }
       }
+      const bool ok = act && n < cnt;
 #pragma unroll
       for (int a = 0; a < RD; ++a) {
-        double2* o = reinterpret_cast<double2*>(s_out + lane * OSTR + a * 16 + 2 * u);
-        if constexpr (CD == 2) {
-          *o = make_double2(v[0][a][0], v[0][a][1]);
-        } else {
-          *o = make_double2(v[0][a][0], v[2 / CD - 1][a][0]);
-        }
-      }
-    };
-    if (nu == NU) {
-#pragma unroll (DEG == 1 ? 4 : 2)
-      for (int u = 0; u < NU; ++u) eval_unit(u);
-    } else {
-      for (int u = 0; u < nu; ++u) eval_unit(u);
-    }
-    __syncwarp();
-    // (D) flush: 8 lanes per 128-byte piece of a row, 2 nodes per step; 4 steps in flight (pointers, then data, then
-    // predicated stores: no branches, nothing serialised on a register)
-    {
-      const int nd = wch * CD;                  // valid doubles of every piece
-      const int u2 = (lane & 7) * 2, fa = (lane >> 3) & 1;
-      const bool full = u2 + 1 < nd, any = u2 < nd;
-      double* const* sp = s_ptr + fa * 32;
-      const double* sb = s_out + fa * 16 + u2;
-      const int64_t off = (int64_t)p0 * CD + u2;
-      if (wch == PT && cnt == 32) {             // whole pieces of a whole tile (nearly all of them): one predicate left
-#pragma unroll
-        for (int n0 = 0; n0 < 32; n0 += 8) {
-          const int nb = n0 + (lane >> 4);
-          double* o[4];
-          double2 x[4];
-#pragma unroll
-          for (int i = 0; i < 4; ++i) o[i] = sp[nb + 2 * i] + off;
-#pragma unroll
-          for (int i = 0; i < 4; ++i) x[i] = *reinterpret_cast<const double2*>(sb + (nb + 2 * i) * OSTR);
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const bool al = (reinterpret_cast<uintptr_t>(o[i]) & 15) == 0;
-            sig_store(o[i], x[i], al, !al, !al);
-          }
-        }
-      } else if (any) {
-        for (int n = lane >> 4; n < cnt; n += 2) {
-          double* o = sp[n] + off;
-          const double* src = sb + n * OSTR;
-          if (full && (reinterpret_cast<uintptr_t>(o) & 15) == 0) {
-            *reinterpret_cast<double2*>(o) = *reinterpret_cast<const double2*>(src);
-          } else {
-            o[0] = src[0];
-            if (full) o[1] = src[1];
-          }
-        }
+        double* o = reinterpret_cast<double*>(a == 0 ? pp.x : pp.y) + off;
+        const bool al = ok && second && (reinterpret_cast<uintptr_t>(o) & 15) == 0;
+        sig_store(o, v[0][a][0], CD == 2 ? v[0][a][CD - 1] : v[NP - 1][a][0], al, ok && !al, ok && !al && second);
       }
     }
-    __syncwarp();
+    // rotate the look-ahead
+#pragma unroll
+    for (int k = 0; k < DEG; ++k)
+#pragma unroll
+      for (int h = 0; h < NP; ++h) {
+        l0[k][h] = l1[k][h];
+        l1[k][h] = l2[k][h];
+        if constexpr (DBL) {
+#pragma unroll
+          for (int i = 0; i < PR; ++i) rec[k][h][i] = recn[k][h][i];
+        }
+      }
+    if constexpr (!DBL) load_rec(l0, rec);
   }
 }
 
