@@ -37,7 +37,7 @@ struct DescView {
   // signature tiles of the boundary map (structured meshes; NULL: not available)
   const int *tile_desc, *tile_slot;
   int64_t ntiles;
-  int64_t tile_class_end[3];
+  int64_t tile_class_end[3], tile_slot_base[3];
 };
 
 // element block (rows of local node lr, columns of local node l) of one element from the affine closed form:
@@ -441,7 +441,7 @@ asm_interior_affine_kernel(pyn::TopoView t, DescView d, const int64_t* __restric
 // The flat kernel above spends most of its instructions on finding out, per output block, which node it belongs to and
 // which of the node's elements contribute (and its element loop diverges).  On a structured mesh that information is the
 // same for every node of a row signature (topo.cuh: byte-identical incidence local indices and inverse maps).  Here a
-// WARP takes a tile of 32 nodes of ONE signature and walks their rows in passes of 128 bytes (PT adjacency positions):
+// WARP takes tiles of 32 nodes of ONE signature and walks their rows in passes of 128 bytes (PT adjacency positions):
 //   * 8 lanes share a node and split the positions of the pass, 4 nodes per step, 8 steps per pass.  A lane's position
 //     is fixed during a pass, so the product records it needs (one per incident element: the representative node's
 //     inverse map says which) sit in its REGISTERS for all 32 nodes -- fetched one pass ahead, the inverse-map bytes two
@@ -449,10 +449,14 @@ asm_interior_affine_kernel(pyn::TopoView t, DescView d, const int64_t* __restric
 //   * what changes from step to step is the node: the 13 (4) coefficients of its <= DEG elements are staged once per
 //     tile in shared memory and read as broadcast LDS.128 (4 distinct nodes per warp, distinct banks);
 //   * the 8 lanes of a node store 128 consecutive bytes of each of its two rows straight from registers: no output
-//     tile, no transposition, no barrier after the coefficients are staged, every step independent of the others.
+//     tile, no transposition, every step independent of the others;
+//   * the warps are persistent and the tiles pipelined: while tile i is evaluated, the coefficients of tile i+1 arrive
+//     in the other half of the shared buffer (cp.async: no registers), its row starts and first inverse-map bytes in
+//     registers, and the descriptor and node slots of tile i+2 are on their way -- the three dependent loads that
+//     precede a tile's first pass are off the critical path (they were 17-37 % of the stall samples).
 // DEG (incident elements per node) is a template parameter: the tiles are sorted by valence class and each class gets
 // its own launch.  Same order of additions per entry as every other assembly kernel (ascending cell order): same bits.
-constexpr int SIG_W = 4;       // warps (= tiles) per CTA
+constexpr int SIG_W = 4;       // warps per CTA
 constexpr int SIG_KMAX = 4;    // incident elements per node (quadrilateral meshes; larger valence: flat kernel)
 
 // v2 store when the address is 16-byte aligned, else one or two scalar stores -- predicated, no branches
@@ -467,64 +471,105 @@ __device__ __forceinline__ void sig_store(double* o, double x0, double x1, bool 
       : "l"(o), "d"(x0), "d"(x1), "r"((int)v2), "r"((int)lo), "r"((int)hi)
       : "memory");
 }
+template <int BYTES>
+__device__ __forceinline__ void sig_cp_async(void* smem_dst, const void* gsrc) {
+  const unsigned dst = (unsigned)__cvta_generic_to_shared(smem_dst);
+  if constexpr (BYTES == 16) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(dst), "l"(gsrc) : "memory");
+  } else {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;\n" ::"r"(dst), "l"(gsrc) : "memory");
+  }
+}
+__device__ __forceinline__ void sig_cp_async_wait() { asm volatile("cp.async.wait_all;\n" ::: "memory"); }
 
-template <int CD>
+template <int CD, int DEG>
 struct SigShape {
   static constexpr int RD = 2;
   static constexpr int NP = 2 / CD;                                  // adjacency positions per lane and pass
   static constexpr int PT = 8 * NP;                                  // ... per pass: 16 doubles of every row
   static constexpr int PR = CD == 2 ? pyn::PYN_AFF_PK : pyn::PYN_AFF_PR;
   static constexpr int NC = CD == 2 ? 13 : 4, NCP = CD == 2 ? 14 : 4;   // coefficients per element (padded to 16 B)
-  static constexpr int per_warp(int deg) { return 32 * deg * NCP + 32 * RD; }   // 8-byte words of shared memory
+  static constexpr int NB = DEG <= 2 ? 2 : 1;                        // coefficient buffers (2: next tile lands early)
+  static constexpr int SL = DEG == 1 ? 2 : (DEG == 2 ? 4 : 8);       // ints per node slot
+  static constexpr int CFW = 32 * DEG * NCP;                         // doubles of one coefficient buffer
+  static constexpr int per_warp = NB * CFW + 32 * RD;                // 8-byte words of shared memory per warp
+};
+
+struct SigTile {   // what a warp knows about a tile: unpacked descriptor
+  int cnt, L, deg;
+  unsigned lrp;
+  const uint8_t* iv;
 };
 
 template <int CD, int DEG>
 __global__ void __launch_bounds__(SIG_W * 32, DEG == 4 ? 3 : 4)
 asm_sig_affine_kernel(pyn::TopoView t, DescView d, const int64_t* __restrict__ indptr, double* __restrict__ data,
-                      int64_t tile0, int64_t tile1) {
-  using S = SigShape<CD>;
-  constexpr int RD = 2, PT = S::PT, PR = S::PR, NP = S::NP, NC = S::NC, NCP = S::NCP;
+                      int64_t tile0, int64_t tile1, const int* __restrict__ slots) {
+  using S = SigShape<CD, DEG>;
+  constexpr int RD = 2, PT = S::PT, PR = S::PR, NP = S::NP, NC = S::NC, NCP = S::NCP, NB = S::NB, SL = S::SL;
   constexpr int C0 = CD == 2 ? 0 : 13;
-  constexpr bool DBL = DEG <= 2;                                     // records double-buffered in registers
+  constexpr bool PIPE = NB == 2;                                     // next tile's coefficients land during this one
+  constexpr bool DBL = DEG == 1;                                     // records double-buffered in registers
   extern __shared__ __align__(16) double sg_dyn[];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  double* s_cf = sg_dyn + (size_t)w * S::per_warp(DEG);              // [node][k][NCP]
-  double** s_ptr = reinterpret_cast<double**>(s_cf + 32 * DEG * NCP);   // [node][a]: start of row a of the node
-  const int64_t tile = tile0 + (int64_t)blockIdx.x * SIG_W + w;
+  double* s_cf = sg_dyn + (size_t)w * S::per_warp;                   // [buffer][node][k][NCP]
+  double** s_ptr = reinterpret_cast<double**>(s_cf + NB * S::CFW);   // [node][a]: start of row a of the node
+  const int64_t stride = (int64_t)gridDim.x * SIG_W;
+  int64_t tile = tile0 + (int64_t)blockIdx.x * SIG_W + w;
   if (tile >= tile1) return;                                         // warps are independent: no CTA-wide barrier below
-  const int4 td0 = __ldg(reinterpret_cast<const int4*>(d.tile_desc) + tile * 2);
-  const int2 td1 = __ldg(reinterpret_cast<const int2*>(d.tile_desc) + tile * 4 + 2);
-  const int2 slot = __ldg(reinterpret_cast<const int2*>(d.tile_slot) + tile * 32 + lane);
-  const int cnt = td0.x, L = td0.y, deg = min(td0.z, DEG);
-  const unsigned lrp = (unsigned)td0.w;
-  const uint8_t* ivrep = t.inv + (((int64_t)td1.y << 32) | (int64_t)(unsigned)td1.x);
   const double* gtab = CD == 2 ? d.aff.pairK : d.aff.pairR;
   const int nn = t.nn;
+  const double sign = d.sign;
+
+  auto load_l1 = [&](int64_t tl, int4& dd, int (&sl)[1 + DEG]) {     // level 1: descriptor and this lane's node slot
+    dd = __ldg(reinterpret_cast<const int4*>(d.tile_desc) + tl);
+    const int* sp = slots + ((tl - tile0) * 32 + lane) * SL;
+    if constexpr (SL == 2) {
+      const int2 x = __ldg(reinterpret_cast<const int2*>(sp));
+      sl[0] = x.x; sl[1] = x.y;
+    } else {
+      const int4 x = __ldg(reinterpret_cast<const int4*>(sp));
+      sl[0] = x.x; sl[1] = x.y; sl[2] = x.z;
+      if constexpr (SL == 8) {
+        sl[3] = x.w;
+        sl[4] = __ldg(sp + 4);
+      }
+    }
+  };
+  auto unpack = [&](const int4& dd) {
+    SigTile g;
+    g.cnt = dd.x & 255;
+    g.deg = min((dd.x >> 8) & 255, DEG);
+    g.L = (int)((unsigned)dd.x >> 16);
+    g.lrp = (unsigned)dd.y;
+    g.iv = t.inv + (((int64_t)dd.w << 32) | (int64_t)(unsigned)dd.z);
+    return g;
+  };
   // geometry of the pass that starts at position p: 2^s lanes per node (8 unless the pass is a narrow tail)
-  auto lanes_log2 = [&](int p) {
-    const int nu = (min(PT, L - p) + NP - 1) / NP;                   // units (double2 per row) of the pass
+  auto lanes_log2 = [&](const SigTile& g, int p) {
+    const int nu = (min(PT, g.L - p) + NP - 1) / NP;                 // units (double2 per row) of the pass
     return nu > 4 ? 3 : (nu > 2 ? 2 : (nu > 1 ? 1 : 0));
   };
   // inverse-map bytes of this lane's positions in the pass that starts at p (0xFF: no contribution / no position)
-  auto load_l = [&](int p, int (&l)[DEG][NP]) {
-    const int s = p < L ? lanes_log2(p) : 0;
+  auto load_l = [&](const SigTile& g, int p, int (&l)[DEG][NP]) {
+    const int s = p < g.L ? lanes_log2(g, p) : 0;
     const int u = lane & ((1 << s) - 1);
 #pragma unroll
     for (int k = 0; k < DEG; ++k)
 #pragma unroll
       for (int h = 0; h < NP; ++h) {
         const int q = p + u * NP + h;
-        l[k][h] = (k < deg && q < L) ? (int)ivrep[k * L + q] : 0xFF;
+        l[k][h] = (k < g.deg && q < g.L) ? (int)g.iv[k * g.L + q] : 0xFF;
       }
   };
-  auto load_rec = [&](const int (&l)[DEG][NP], double (&rec)[DEG][NP][PR]) {
+  auto load_rec = [&](const SigTile& g, const int (&l)[DEG][NP], double (&rec)[DEG][NP][PR]) {
 #pragma unroll
     for (int k = 0; k < DEG; ++k)
 #pragma unroll
       for (int h = 0; h < NP; ++h)
         if (l[k][h] != 0xFF) {
           const double2* rp =
-              reinterpret_cast<const double2*>(gtab + ((int64_t)((lrp >> (8 * k)) & 255u) * nn + l[k][h]) * PR);
+              reinterpret_cast<const double2*>(gtab + ((int64_t)((g.lrp >> (8 * k)) & 255u) * nn + l[k][h]) * PR);
 #pragma unroll
           for (int i = 0; i < PR / 2; ++i) {
             const double2 x = __ldg(rp + i);
@@ -533,7 +578,37 @@ asm_sig_affine_kernel(pyn::TopoView t, DescView d, const int64_t* __restrict__ i
           }
         }
   };
+  // level 2 of a tile: coefficients of the lane's node -> shared buffer `buf` (asynchronous), its row starts and the
+  // inverse-map bytes of the first two passes -> registers
+  auto stage2 = [&](const SigTile& g, const int (&sl)[1 + DEG], int buf, int64_t (&q)[RD], int (&la)[DEG][NP],
+                    int (&lb)[DEG][NP]) {
+#pragma unroll
+    for (int k = 0; k < DEG; ++k) {
+      const double* cg = d.coef + (int64_t)sl[1 + k] * PYN_AFF_NCOEF + C0;
+      double* dst = s_cf + buf * S::CFW + (lane * DEG + k) * NCP;
+      if constexpr (CD == 2) {
+#pragma unroll
+        for (int i = 0; i < NCP / 2; ++i) sig_cp_async<16>(dst + 2 * i, cg + 2 * i);
+      } else {
+#pragma unroll
+        for (int i = 0; i < NC; ++i) sig_cp_async<8>(dst + i, cg + i);
+      }
+    }
+    q[0] = indptr[(int64_t)sl[0] * RD];
+    q[1] = indptr[(int64_t)sl[0] * RD + 1];
+    load_l(g, 0, la);
+    load_l(g, PT, lb);
+  };
+
+  int4 dd;
+  int sl[1 + DEG];
+  load_l1(tile, dd, sl);
+  SigTile g = unpack(dd);
+  int64_t q[RD];
   int l0[DEG][NP], l1[DEG][NP];
+  stage2(g, sl, 0, q, l0, l1);
+  bool has_n = tile + stride < tile1;
+  if (has_n) load_l1(tile + stride, dd, sl);                         // level 1 of the next tile
   double rec[DEG][NP][PR], recn[DBL ? DEG : 1][NP][PR];
 #pragma unroll
   for (int k = 0; k < DEG; ++k)
@@ -544,104 +619,125 @@ asm_sig_affine_kernel(pyn::TopoView t, DescView d, const int64_t* __restrict__ i
         rec[k][h][i] = 0.0;
         if (DBL) recn[k][h][i] = 0.0;
       }
-  load_l(0, l0);
-  load_l(PT, l1);
-  {  // coefficients and row starts of this lane's node -> shared memory
-    const int j = slot.x;
-    const int64_t b0 = slot.y;
-#pragma unroll
-    for (int k = 0; k < DEG; ++k) {
-      const double* cg = d.coef + (int64_t)t.n2e_elem[b0 + (k < deg ? k : 0)] * PYN_AFF_NCOEF + C0;
-      double c[NC];
-#pragma unroll
-      for (int i = 0; i < NC; ++i) c[i] = __ldg(cg + i);
-#pragma unroll
-      for (int i = 0; i < NC; ++i) s_cf[(lane * DEG + k) * NCP + i] = c[i];
+  int buf = 0;
+  for (;;) {
+    __syncwarp();                                                    // everybody is done with the previous tile
+    sig_cp_async_wait();
+    s_ptr[lane * RD] = data + q[0];
+    s_ptr[lane * RD + 1] = data + q[1];
+    load_rec(g, l0, rec);
+    __syncwarp();
+    // the tiles behind this one
+    SigTile gn = g;
+    int64_t qn[RD] = {0, 0};
+    int ln0[DEG][NP], ln1[DEG][NP];
+    const bool has_nn = tile + 2 * stride < tile1;
+    if (has_n) {
+      gn = unpack(dd);
+      if constexpr (PIPE) {
+        stage2(gn, sl, buf ^ 1, qn, ln0, ln1);
+        if (has_nn) load_l1(tile + 2 * stride, dd, sl);
+      }
     }
-    s_ptr[lane * RD] = data + indptr[(int64_t)j * RD];
-    s_ptr[lane * RD + 1] = data + indptr[(int64_t)j * RD + 1];
-  }
-  load_rec(l0, rec);
-  __syncwarp();
-  const double sign = d.sign;
-  for (int p0 = 0; p0 < L; p0 += PT) {
-    const int wch = min(PT, L - p0);
-    const int s = lanes_log2(p0);
-    const int u = lane & ((1 << s) - 1), grp = lane >> s, npg = 32 >> s;
-    // fetch ahead: records of the next pass, inverse-map bytes of the one after
-    if constexpr (DBL) load_rec(l1, recn);
-    int l2[DEG][NP];
-    load_l(p0 + 2 * PT, l2);
-    bool on[DEG][NP], anyk[DEG];
+    const double* cfb = s_cf + buf * S::CFW;
+    for (int p0 = 0; p0 < g.L; p0 += PT) {
+      const int wch = min(PT, g.L - p0);
+      const int s = lanes_log2(g, p0);
+      const int u = lane & ((1 << s) - 1), grp = lane >> s, npg = 32 >> s;
+      // fetch ahead: records of the next pass, inverse-map bytes of the one after
+      if constexpr (DBL) load_rec(g, l1, recn);
+      int l2[DEG][NP];
+      load_l(g, p0 + 2 * PT, l2);
+      bool on[DEG][NP], anyk[DEG];
 #pragma unroll
-    for (int k = 0; k < DEG; ++k) {
+      for (int k = 0; k < DEG; ++k) {
 #pragma unroll
-      for (int h = 0; h < NP; ++h) on[k][h] = l0[k][h] != 0xFF;
-      anyk[k] = __any_sync(0xffffffffu, on[k][0] || on[k][NP - 1]);
-    }
-    const bool act = u * NP < wch;                           // this lane has a unit (double2 of each row) in this pass
-    const bool second = CD == 2 || u * NP + 1 < wch;         // ... and the unit's second double exists
-    const int64_t off = (int64_t)(p0 + u * NP) * CD;
+        for (int h = 0; h < NP; ++h) on[k][h] = l0[k][h] != 0xFF;
+        anyk[k] = __any_sync(0xffffffffu, on[k][0] || on[k][NP - 1]);
+      }
+      const bool act = u * NP < wch;                         // this lane has a unit (double2 of each row) in this pass
+      const bool second = CD == 2 || u * NP + 1 < wch;       // ... and the unit's second double exists
+      const int64_t off = (int64_t)(p0 + u * NP) * CD;
 #pragma unroll 2
-    for (int st = 0; st < (1 << s); ++st) {                  // npg nodes per step
-      const int n = st * npg + grp;
-      const double* cfn = s_cf + n * (DEG * NCP);
-      const longlong2 pp = *reinterpret_cast<const longlong2*>(s_ptr + n * RD);
-      double v[NP][RD][CD];
+      for (int st = 0; st < (1 << s); ++st) {                // npg nodes per step
+        const int n = st * npg + grp;
+        const double* cfn = cfb + n * (DEG * NCP);
+        const longlong2 pp = *reinterpret_cast<const longlong2*>(s_ptr + n * RD);
+        double v[NP][RD][CD];
 #pragma unroll
-      for (int h = 0; h < NP; ++h)
+        for (int h = 0; h < NP; ++h)
 #pragma unroll
-        for (int a = 0; a < RD; ++a)
+          for (int a = 0; a < RD; ++a)
 #pragma unroll
-          for (int b = 0; b < CD; ++b) v[h][a][b] = 0.0;
+            for (int b = 0; b < CD; ++b) v[h][a][b] = 0.0;
 #pragma unroll
-      for (int k = 0; k < DEG; ++k) {                        // ascending cell order
-        if (DEG == 1 || anyk[k]) {                           // uniform: some lane of the warp takes element k
-          double cf[NCP];
+        for (int k = 0; k < DEG; ++k) {                      // ascending cell order
+          if (DEG == 1 || anyk[k]) {                         // uniform: some lane of the warp takes element k
+            double cf[NCP];
 #pragma unroll
-          for (int i = 0; i < NCP / 2; ++i) {
-            const double2 x = *reinterpret_cast<const double2*>(cfn + k * NCP + 2 * i);
-            cf[2 * i] = x.x;
-            cf[2 * i + 1] = x.y;
-          }
-#pragma unroll
-          for (int h = 0; h < NP; ++h) {
-            double blk[RD][CD];
-            if constexpr (CD == 2) {
-              pyn::affine_block_K(cf, rec[k][h], blk);
-            } else {
-              pyn::affine_block_R(cf, rec[k][h], d.which, d.aff.alpha_w, d.aff.alpha_d, blk);
+            for (int i = 0; i < NCP / 2; ++i) {
+              const double2 x = *reinterpret_cast<const double2*>(cfn + k * NCP + 2 * i);
+              cf[2 * i] = x.x;
+              cf[2 * i + 1] = x.y;
             }
-            if (on[k][h]) {
 #pragma unroll
-              for (int a = 0; a < RD; ++a)
+            for (int h = 0; h < NP; ++h) {
+              double blk[RD][CD];
+              if constexpr (CD == 2) {
+                pyn::affine_block_K(cf, rec[k][h], blk);
+              } else {
+                pyn::affine_block_R(cf, rec[k][h], d.which, d.aff.alpha_w, d.aff.alpha_d, blk);
+              }
+              if (on[k][h]) {
 #pragma unroll
-                for (int b = 0; b < CD; ++b) v[h][a][b] += sign * blk[a][b];
+                for (int a = 0; a < RD; ++a)
+#pragma unroll
+                  for (int b = 0; b < CD; ++b) v[h][a][b] += sign * blk[a][b];
+              }
             }
           }
         }
-      }
-      const bool ok = act && n < cnt;
+        const bool ok = act && n < g.cnt;
 #pragma unroll
-      for (int a = 0; a < RD; ++a) {
-        double* o = reinterpret_cast<double*>(a == 0 ? pp.x : pp.y) + off;
-        const bool al = ok && second && (reinterpret_cast<uintptr_t>(o) & 15) == 0;
-        sig_store(o, v[0][a][0], CD == 2 ? v[0][a][CD - 1] : v[NP - 1][a][0], al, ok && !al, ok && !al && second);
+        for (int a = 0; a < RD; ++a) {
+          double* o = reinterpret_cast<double*>(a == 0 ? pp.x : pp.y) + off;
+          const bool al = ok && second && (reinterpret_cast<uintptr_t>(o) & 15) == 0;
+          sig_store(o, v[0][a][0], CD == 2 ? v[0][a][CD - 1] : v[NP - 1][a][0], al, ok && !al, ok && !al && second);
+        }
       }
+      // rotate the look-ahead
+#pragma unroll
+      for (int k = 0; k < DEG; ++k)
+#pragma unroll
+        for (int h = 0; h < NP; ++h) {
+          l0[k][h] = l1[k][h];
+          l1[k][h] = l2[k][h];
+          if constexpr (DBL) {
+#pragma unroll
+            for (int i = 0; i < PR; ++i) rec[k][h][i] = recn[k][h][i];
+          }
+        }
+      if constexpr (!DBL) load_rec(g, l0, rec);
     }
-    // rotate the look-ahead
+    if (!has_n) break;
+    if constexpr (!PIPE) {                                   // one buffer: the next tile is staged after this one
+      __syncwarp();
+      stage2(gn, sl, buf, qn, ln0, ln1);
+      if (has_nn) load_l1(tile + 2 * stride, dd, sl);
+    }
+    g = gn;
+    q[0] = qn[0];
+    q[1] = qn[1];
 #pragma unroll
     for (int k = 0; k < DEG; ++k)
 #pragma unroll
       for (int h = 0; h < NP; ++h) {
-        l0[k][h] = l1[k][h];
-        l1[k][h] = l2[k][h];
-        if constexpr (DBL) {
-#pragma unroll
-          for (int i = 0; i < PR; ++i) rec[k][h][i] = recn[k][h][i];
-        }
+        l0[k][h] = ln0[k][h];
+        l1[k][h] = ln1[k][h];
       }
-    if constexpr (!DBL) load_rec(l0, rec);
+    tile += stride;
+    has_n = has_nn;
+    if constexpr (PIPE) buf ^= 1;
   }
 }
 
@@ -1039,12 +1135,22 @@ static int launch_interior(const pyn_topo* t, const DescView& dv, const int64_t*
     int64_t c0 = 0;
 #define PYN_SIG_CASE(C, DG, cls)                                                                                        \
     if (dv.cdof == C && dv.tile_class_end[cls] > c0) {                                                                  \
-      const int64_t c1 = dv.tile_class_end[cls], g = (c1 - c0 + SIG_W - 1) / SIG_W;                                    \
-      const size_t dyn = sizeof(double) * (size_t)SIG_W * SigShape<C>::per_warp(DG);                                    \
-      PYN_REQUIRE(g < 0x7fffffff, "affine assembly: too many signature tiles");                                        \
-      PYN_CHECK_CUDA(cudaFuncSetAttribute(asm_sig_affine_kernel<C, DG>, cudaFuncAttributeMaxDynamicSharedMemorySize,   \
-                                          (int)dyn));                                                                  \
-      asm_sig_affine_kernel<C, DG><<<(int)g, SIG_W * 32, dyn, st>>>(tv, dv, indptr, data, c0, c1);                     \
+      using Sh = SigShape<C, DG>;                                                                                      \
+      const int64_t c1 = dv.tile_class_end[cls];                                                                       \
+      const size_t dyn = sizeof(double) * (size_t)SIG_W * Sh::per_warp;                                                \
+      static int resident = 0;   /* CTAs per SM of this variant (persistent warps: one wave) */                        \
+      if (!resident) {                                                                                                 \
+        PYN_CHECK_CUDA(cudaFuncSetAttribute(asm_sig_affine_kernel<C, DG>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                            (int)dyn));                                                                \
+        PYN_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&resident, asm_sig_affine_kernel<C, DG>,          \
+                                                                     SIG_W * 32, dyn));                                \
+        if (resident < 1) resident = 1;                                                                                \
+      }                                                                                                                \
+      int64_t g = (c1 - c0 + SIG_W - 1) / SIG_W;                                                                       \
+      const int64_t cap = (int64_t)pyn::sm_count() * resident;                                                         \
+      if (g > cap) g = cap;                                                                                            \
+      asm_sig_affine_kernel<C, DG><<<(int)g, SIG_W * 32, dyn, st>>>(tv, dv, indptr, data, c0, c1,                      \
+                                                                    dv.tile_slot + dv.tile_slot_base[cls]);            \
       pyn::count_launch();                                                                                             \
     }
     PYN_SIG_CASE(2, 1, 0) PYN_SIG_CASE(1, 1, 0)
@@ -1194,16 +1300,26 @@ __global__ void tile_first_kernel(int64_t nt, const int* __restrict__ start, con
     deg[i] = (int)(n2e_ptr[j + 1] - n2e_ptr[j]);
   }
 }
-__global__ void tile_build_kernel(pyn::TopoView t, int64_t nt, const int* __restrict__ tile_sig,
+struct TileClasses {
+  int64_t end[3];    // tiles of valence class c: [end[c-1], end[c])
+  int64_t base[3];   // first int of the class in the slot table
+};
+__global__ void tile_build_kernel(pyn::TopoView t, int64_t nt, TileClasses tc, const int* __restrict__ tile_sig,
                                   const int* __restrict__ tile_start, const int* __restrict__ tile_cnt,
                                   const int* __restrict__ sig_nodes, int* __restrict__ desc, int* __restrict__ slot) {
   const int lane = threadIdx.x & 31;
   const int64_t w0 = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5, nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
   for (int64_t i = w0; i < nt; i += nw) {
+    const int cls = i < tc.end[0] ? 0 : (i < tc.end[1] ? 1 : 2);
+    const int sl = 2 << cls, dmax = cls == 2 ? 4 : cls + 1;          // ints per slot, elements per node of the class
+    const int64_t c0 = cls == 0 ? 0 : tc.end[cls - 1];
     const int start = tile_start[i], cnt = tile_cnt[i];
     const int j = sig_nodes[start + (lane < cnt ? lane : 0)];
-    slot[(i * 32 + lane) * 2] = j;
-    slot[(i * 32 + lane) * 2 + 1] = (int)t.n2e_ptr[j];
+    const int64_t b0 = t.n2e_ptr[j];
+    const int dj = (int)(t.n2e_ptr[j + 1] - b0);
+    int* sp = slot + tc.base[cls] + ((i - c0) * 32 + lane) * sl;
+    sp[0] = j;
+    for (int k = 0; k < sl - 1; ++k) sp[1 + k] = k < dmax ? t.n2e_elem[b0 + (k < dj ? k : 0)] : 0;
     if (lane == 0) {
       const int rep = t.sig_rep[tile_sig[i]];
       const int64_t rb0 = t.n2e_ptr[rep];
@@ -1211,14 +1327,12 @@ __global__ void tile_build_kernel(pyn::TopoView t, int64_t nt, const int* __rest
       unsigned lr = 0;
       for (int k = 0; k < deg && k < 4; ++k) lr |= (unsigned)(t.n2e_loc[rb0 + k] & 255) << (8 * k);
       const int64_t io = t.inv_ptr[rep];
-      int* o = desc + i * 8;
-      o[0] = cnt;
-      o[1] = (int)(t.adj_ptr[rep + 1] - t.adj_ptr[rep]);
-      o[2] = deg;
-      o[3] = (int)lr;
-      o[4] = (int)(io & 0xffffffffll);
-      o[5] = (int)(io >> 32);
-      o[6] = o[7] = 0;
+      const int L = (int)(t.adj_ptr[rep + 1] - t.adj_ptr[rep]);
+      int* o = desc + i * 4;
+      o[0] = cnt | (deg << 8) | (L << 16);
+      o[1] = (int)lr;
+      o[2] = (int)(io & 0xffffffffll);
+      o[3] = (int)(io >> 32);
     }
   }
 }
@@ -1231,7 +1345,8 @@ static int ensure_sig_tiles(const pyn_topo* t, const pyn_bcmap* mc, cudaStream_t
   // Measured slower than the flat kernel at every order but 2 (profiles/r02_ncu_fused_assembly.md, structure v5):
   // kept as an opt-in structure, PYN_AFF_SIG=1.
   static const bool off = getenv("PYN_AFF_SIG") == nullptr;
-  if (off || t->nsig <= 0 || t->max_valence > SIG_KMAX || t->nn > 255) return PYN_OK;
+  if (off || t->nsig <= 0 || t->max_valence > SIG_KMAX || t->nn > 255 || (int64_t)t->nn * SIG_KMAX >= 32768)
+    return PYN_OK;   // (a row holds at most max_valence * nn column nodes: L fits the descriptor's 15 bits)
   const int64_t n = t->nnodes, nint = t->nnodes - m->nlist;
   if (nint <= 0 || nint >= 0x7fffffff || (int64_t)t->ne * t->nn >= 0x7fffffff) return PYN_OK;
   int *nodes = nullptr, *keys = nullptr, *keys2 = nullptr, *counts = nullptr;
@@ -1312,10 +1427,18 @@ static int ensure_sig_tiles(const pyn_topo* t, const pyn_bcmap* mc, cudaStream_t
   PYN_CHECK_CUDA(cudaMemcpyAsync(m->tile_start, tb.data(), sizeof(int) * ts.size(), cudaMemcpyHostToDevice, st));
   PYN_CHECK_CUDA(cudaMemcpyAsync(m->tile_cnt, tc.data(), sizeof(int) * ts.size(), cudaMemcpyHostToDevice, st));
   PYN_CHECK_CUDA(cudaStreamSynchronize(st));
-  PYN_CHECK_CUDA(cudaMalloc(&m->tile_desc, sizeof(int) * 8 * ts.size()));
-  PYN_CHECK_CUDA(cudaMalloc(&m->tile_slot, sizeof(int) * 64 * ts.size()));
+  TileClasses tcl;
+  for (int c = 0; c < 3; ++c) {
+    tcl.end[c] = m->tile_class_end[c];
+    const int64_t before = c == 0 ? 0 : tcl.end[c - 1] - (c == 1 ? 0 : tcl.end[c - 2]);
+    tcl.base[c] = c == 0 ? 0 : tcl.base[c - 1] + before * 32 * (2 << (c - 1));
+    m->tile_slot_base[c] = tcl.base[c];
+  }
+  const int64_t slot_ints = tcl.base[2] + (tcl.end[2] - tcl.end[1]) * 32 * 8;
+  PYN_CHECK_CUDA(cudaMalloc(&m->tile_desc, sizeof(int) * 4 * ts.size()));
+  PYN_CHECK_CUDA(cudaMalloc(&m->tile_slot, sizeof(int) * (slot_ints > 0 ? slot_ints : 1)));
   tile_build_kernel<<<pyn::grid_for((int64_t)ts.size() * 32, 256), 256, 0, st>>>(
-      pyn::view_of(t), (int64_t)ts.size(), m->tile_sig, m->tile_start, m->tile_cnt, m->sig_nodes, m->tile_desc,
+      pyn::view_of(t), (int64_t)ts.size(), tcl, m->tile_sig, m->tile_start, m->tile_cnt, m->sig_nodes, m->tile_desc,
       m->tile_slot);
   PYN_CHECK_LAUNCH();
   PYN_CHECK_CUDA(cudaStreamSynchronize(st));
@@ -1470,7 +1593,10 @@ int pyn_asm_fill(const pyn_topo* t, const pyn_asm_desc* desc, const int64_t* d_i
         if (rc) return rc;
         if (desc->bcmap->tiles_state == 1) {
           dv.tile_desc = desc->bcmap->tile_desc; dv.tile_slot = desc->bcmap->tile_slot; dv.ntiles = desc->bcmap->ntiles;
-          for (int c = 0; c < 3; ++c) dv.tile_class_end[c] = desc->bcmap->tile_class_end[c];
+          for (int c = 0; c < 3; ++c) {
+            dv.tile_class_end[c] = desc->bcmap->tile_class_end[c];
+            dv.tile_slot_base[c] = desc->bcmap->tile_slot_base[c];
+          }
         }
       }
       rc = tmpl ? launch_templates(t, dv, d_indptr, d_data, st) : launch_interior(t, dv, d_indptr, d_indices, d_data, st);

@@ -49,12 +49,14 @@ struct pyn_bcmap {
   // + tile_cnt[i]) of signature tile_sig[i].  Used by the signature-grouped fused assembly kernel (assemble.cu).
   int* sig_nodes;
   int *tile_sig, *tile_start, *tile_cnt;
-  // What the kernel reads (built from the above, which are then released): per tile 8 ints {cnt, L, deg, local row
-  // index of the representative in its elements (4 bytes), offset of its inverse map (2 ints), 0, 0}; per tile and lane
-  // {node, first entry of the node's incidence list} (lanes beyond cnt repeat lane 0)
+  // What the kernel reads (built from the above, which are then released): per tile 4 ints {cnt | deg << 8 | L << 16,
+  // local row index of the representative in its elements (4 bytes), offset of its inverse map (2 ints)}; per tile and
+  // lane a slot {node, its elements} of 2 / 4 / 8 ints for the valence classes 1 / 2 / <= 4 (lanes beyond cnt repeat
+  // lane 0); class c starts at int tile_slot_base[c] of the slot table
   int* tile_desc;
   int* tile_slot;
   int64_t ntiles;
+  int64_t tile_slot_base[3];
   int64_t tile_class_end[3];   // tiles are sorted by valence class (1, 2, <= 4 incident elements), then by first node
   int tiles_state;   // 0 not built, 1 built, -1 unavailable
 };
