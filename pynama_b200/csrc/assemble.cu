@@ -482,14 +482,14 @@ __device__ __forceinline__ void sig_cp_async(void* smem_dst, const void* gsrc) {
 }
 __device__ __forceinline__ void sig_cp_async_wait() { asm volatile("cp.async.wait_all;\n" ::: "memory"); }
 
-template <int CD, int DEG>
+template <int CD, int DEG, int UL, bool PIPEF>
 struct SigShape {
   static constexpr int RD = 2;
-  static constexpr int NP = 2 / CD;                                  // adjacency positions per lane and pass
-  static constexpr int PT = 8 * NP;                                  // ... per pass: 16 doubles of every row
+  static constexpr int NP = UL * 2 / CD;                             // adjacency positions per lane and pass
+  static constexpr int PT = 16 / CD;                                 // ... per pass: 16 doubles (8 units) of every row
   static constexpr int PR = CD == 2 ? pyn::PYN_AFF_PK : pyn::PYN_AFF_PR;
   static constexpr int NC = CD == 2 ? 13 : 4, NCP = CD == 2 ? 14 : 4;   // coefficients per element (padded to 16 B)
-  static constexpr int NB = DEG <= 2 ? 2 : 1;                        // coefficient buffers (2: next tile lands early)
+  static constexpr int NB = PIPEF ? 2 : 1;                           // coefficient buffers (2: next tile lands early)
   static constexpr int SL = DEG == 1 ? 2 : (DEG == 2 ? 4 : 8);       // ints per node slot
   static constexpr int CFW = 32 * DEG * NCP;                         // doubles of one coefficient buffer
   static constexpr int per_warp = NB * CFW + 32 * RD;                // 8-byte words of shared memory per warp
@@ -501,15 +501,16 @@ struct SigTile {   // what a warp knows about a tile: unpacked descriptor
   const uint8_t* iv;
 };
 
-template <int CD, int DEG>
+template <int CD, int DEG, int UL, bool PIPEF, bool DBL>
 __global__ void __launch_bounds__(SIG_W * 32, DEG == 4 ? 3 : 4)
 asm_sig_affine_kernel(pyn::TopoView t, DescView d, const int64_t* __restrict__ indptr, double* __restrict__ data,
-                      int64_t tile0, int64_t tile1, const int* __restrict__ slots) {
-  using S = SigShape<CD, DEG>;
+                      int64_t tile0, int64_t tile1, const int* __restrict__ slots, int dbg_align) {
+  using S = SigShape<CD, DEG, UL, PIPEF>;
   constexpr int RD = 2, PT = S::PT, PR = S::PR, NP = S::NP, NC = S::NC, NCP = S::NCP, NB = S::NB, SL = S::SL;
   constexpr int C0 = CD == 2 ? 0 : 13;
-  constexpr bool PIPE = NB == 2;                                     // next tile's coefficients land during this one
-  constexpr bool DBL = DEG == 1;                                     // records double-buffered in registers
+  constexpr int PPU = 2 / CD;                                        // positions per unit (double2 of a row)
+  static_assert(UL == 1, "one unit per lane");
+  constexpr bool PIPE = PIPEF;                                       // next tile's coefficients land during this one
   extern __shared__ __align__(16) double sg_dyn[];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   double* s_cf = sg_dyn + (size_t)w * S::per_warp;                   // [buffer][node][k][NCP]
@@ -545,21 +546,23 @@ asm_sig_affine_kernel(pyn::TopoView t, DescView d, const int64_t* __restrict__ i
     g.iv = t.inv + (((int64_t)dd.w << 32) | (int64_t)(unsigned)dd.z);
     return g;
   };
-  // geometry of the pass that starts at position p: 2^s lanes per node (8 unless the pass is a narrow tail)
-  auto lanes_log2 = [&](const SigTile& g, int p) {
-    const int nu = (min(PT, g.L - p) + NP - 1) / NP;                 // units (double2 per row) of the pass
-    return nu > 4 ? 3 : (nu > 2 ? 2 : (nu > 1 ? 1 : 0));
-  };
-  // inverse-map bytes of this lane's positions in the pass that starts at p (0xFF: no contribution / no position)
-  auto load_l = [&](const SigTile& g, int p, int (&l)[DEG][NP]) {
-    const int s = p < g.L ? lanes_log2(g, p) : 0;
+  // Passes: a row of nut units (a unit = one double2 = PPU adjacency positions) is cut into passes whose widths are
+  // the powers of two of nut's binary expansion, largest first, at most 32 units: 2^s lanes per node, one unit per
+  // lane, 32 >> s nodes per step -- every lane busy whatever the row length, and the pieces stored by one instruction
+  // are as long as the row allows (512 contiguous bytes when 2^s = 32).
+  auto width_log2 = [&](int left) { return min(5, 31 - __clz(left)); };   // left >= 1 units remain
+  auto units_of = [&](const SigTile& g) { return (g.L + PPU - 1) / PPU; };
+  // inverse-map bytes of this lane's unit in the pass that starts at unit pu (0xFF: no contribution / no position)
+  auto load_l = [&](const SigTile& g, int pu, int (&l)[DEG][NP]) {
+    const int nut = units_of(g);
+    const int s = pu < nut ? width_log2(nut - pu) : 0;
     const int u = lane & ((1 << s) - 1);
 #pragma unroll
     for (int k = 0; k < DEG; ++k)
 #pragma unroll
       for (int h = 0; h < NP; ++h) {
-        const int q = p + u * NP + h;
-        l[k][h] = (k < g.deg && q < g.L) ? (int)g.iv[k * g.L + q] : 0xFF;
+        const int q = (pu + u) * PPU + h;
+        l[k][h] = (pu < nut && k < g.deg && q < g.L) ? (int)g.iv[k * g.L + q] : 0xFF;
       }
   };
   auto load_rec = [&](const SigTile& g, const int (&l)[DEG][NP], double (&rec)[DEG][NP][PR]) {
@@ -597,7 +600,7 @@ asm_sig_affine_kernel(pyn::TopoView t, DescView d, const int64_t* __restrict__ i
     q[0] = indptr[(int64_t)sl[0] * RD];
     q[1] = indptr[(int64_t)sl[0] * RD + 1];
     load_l(g, 0, la);
-    load_l(g, PT, lb);
+    load_l(g, 1 << width_log2(units_of(g)), lb);
   };
 
   int4 dd;
@@ -640,24 +643,30 @@ asm_sig_affine_kernel(pyn::TopoView t, DescView d, const int64_t* __restrict__ i
       }
     }
     const double* cfb = s_cf + buf * S::CFW;
-    for (int p0 = 0; p0 < g.L; p0 += PT) {
-      const int wch = min(PT, g.L - p0);
-      const int s = lanes_log2(g, p0);
+    const int nut = units_of(g);
+    int sn = width_log2(nut);
+    for (int pu = 0; pu < nut;) {
+      const int s = sn;
       const int u = lane & ((1 << s) - 1), grp = lane >> s, npg = 32 >> s;
+      const int pu1 = pu + (1 << s);                         // the next pass, and the one after
+      sn = pu1 < nut ? width_log2(nut - pu1) : 0;
+      const int pu2 = pu1 + (1 << sn);
       // fetch ahead: records of the next pass, inverse-map bytes of the one after
       if constexpr (DBL) load_rec(g, l1, recn);
       int l2[DEG][NP];
-      load_l(g, p0 + 2 * PT, l2);
+      load_l(g, pu2, l2);
       bool on[DEG][NP], anyk[DEG];
 #pragma unroll
       for (int k = 0; k < DEG; ++k) {
 #pragma unroll
         for (int h = 0; h < NP; ++h) on[k][h] = l0[k][h] != 0xFF;
-        anyk[k] = __any_sync(0xffffffffu, on[k][0] || on[k][NP - 1]);
+        bool some = false;
+#pragma unroll
+        for (int h = 0; h < NP; ++h) some = some || on[k][h];
+        anyk[k] = __any_sync(0xffffffffu, some);
       }
-      const bool act = u * NP < wch;                         // this lane has a unit (double2 of each row) in this pass
-      const bool second = CD == 2 || u * NP + 1 < wch;       // ... and the unit's second double exists
-      const int64_t off = (int64_t)(p0 + u * NP) * CD;
+      const bool second = CD == 2 || (pu + u) * PPU + 1 < g.L;   // the unit's second double exists
+      const int64_t off = (int64_t)(pu + u) * 2;
 #pragma unroll 2
       for (int st = 0; st < (1 << s); ++st) {                // npg nodes per step
         const int n = st * npg + grp;
@@ -697,10 +706,11 @@ asm_sig_affine_kernel(pyn::TopoView t, DescView d, const int64_t* __restrict__ i
             }
           }
         }
-        const bool ok = act && n < g.cnt;
 #pragma unroll
         for (int a = 0; a < RD; ++a) {
           double* o = reinterpret_cast<double*>(a == 0 ? pp.x : pp.y) + off;
+          if (dbg_align) o = reinterpret_cast<double*>((reinterpret_cast<uintptr_t>(o - 2 * u) & ~(uintptr_t)127)) + 2 * u;   // EXPERIMENT ONLY: wrong addresses, line-aligned pieces
+          const bool ok = n < g.cnt;
           const bool al = ok && second && (reinterpret_cast<uintptr_t>(o) & 15) == 0;
           sig_store(o, v[0][a][0], CD == 2 ? v[0][a][CD - 1] : v[NP - 1][a][0], al, ok && !al, ok && !al && second);
         }
@@ -718,6 +728,7 @@ asm_sig_affine_kernel(pyn::TopoView t, DescView d, const int64_t* __restrict__ i
           }
         }
       if constexpr (!DBL) load_rec(g, l0, rec);
+      pu = pu1;
     }
     if (!has_n) break;
     if constexpr (!PIPE) {                                   // one buffer: the next tile is staged after this one
@@ -1133,31 +1144,51 @@ static int launch_interior(const pyn_topo* t, const DescView& dv, const int64_t*
   if (dv.coef && !indices && data && dv.tile_desc) {   // structured mesh, values only: signature-grouped kernel
     PYN_REQUIRE(tv.nn == dv.aff.n * dv.aff.n, "affine assembly: element handle of another order");
     int64_t c0 = 0;
-#define PYN_SIG_CASE(C, DG, cls)                                                                                        \
-    if (dv.cdof == C && dv.tile_class_end[cls] > c0) {                                                                  \
-      using Sh = SigShape<C, DG>;                                                                                      \
+#define PYN_SIG_LAUNCH(C, DG, U, P, B, cls)                                                                             \
+    {                                                                                                                  \
+      using Sh = SigShape<C, DG, U, P>;                                                                                \
       const int64_t c1 = dv.tile_class_end[cls];                                                                       \
       const size_t dyn = sizeof(double) * (size_t)SIG_W * Sh::per_warp;                                                \
       static int resident = 0;   /* CTAs per SM of this variant (persistent warps: one wave) */                        \
       if (!resident) {                                                                                                 \
-        PYN_CHECK_CUDA(cudaFuncSetAttribute(asm_sig_affine_kernel<C, DG>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
-                                            (int)dyn));                                                                \
-        PYN_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&resident, asm_sig_affine_kernel<C, DG>,          \
+        PYN_CHECK_CUDA(cudaFuncSetAttribute(asm_sig_affine_kernel<C, DG, U, P, B>,                                     \
+                                            cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));                   \
+        PYN_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&resident, asm_sig_affine_kernel<C, DG, U, P, B>, \
                                                                      SIG_W * 32, dyn));                                \
         if (resident < 1) resident = 1;                                                                                \
       }                                                                                                                \
       int64_t g = (c1 - c0 + SIG_W - 1) / SIG_W;                                                                       \
       const int64_t cap = (int64_t)pyn::sm_count() * resident;                                                         \
-      if (g > cap) g = cap;                                                                                            \
-      asm_sig_affine_kernel<C, DG><<<(int)g, SIG_W * 32, dyn, st>>>(tv, dv, indptr, data, c0, c1,                      \
-                                                                    dv.tile_slot + dv.tile_slot_base[cls]);            \
+      if (g > cap && getenv("PYN_SIG_PERSIST")) g = cap;                                                               \
+      asm_sig_affine_kernel<C, DG, U, P, B><<<(int)g, SIG_W * 32, dyn, st>>>(tv, dv, indptr, data, c0, c1,             \
+                                                                             dv.tile_slot + dv.tile_slot_base[cls],   \
+                                                                             getenv("PYN_SIG_DBG_ALIGN") ? 1 : 0);    \
       pyn::count_launch();                                                                                             \
     }
+    // variant = units per lane (1, 2) | tiles pipelined (+4) | records double-buffered (+8); PYN_SIG_VARIANT: A/B switch
+#define PYN_SIG_CASE(C, DG, cls)                                                                                        \
+    if (dv.cdof == C && dv.tile_class_end[cls] > c0) {                                                                  \
+      /* what the registers allow: 2 units per lane and double-buffered records for valence 1 only (and not both),     \
+         pipelined tiles up to valence 2 */                                                                            \
+      int var = sig_variant;                                                                                           \
+      if (DG != 1) var = (var & ~(3 | 8)) | 1;                                                                         \
+      if (DG == 4) var &= ~4;                                                                                          \
+      if ((var & 3) == 2) var &= ~8;                                                                                   \
+      switch (var) {                                                                                                   \
+        case 1: PYN_SIG_LAUNCH(C, DG, 1, false, false, cls) break;                                                     \
+        case 5: PYN_SIG_LAUNCH(C, DG, 1, (DG <= 2), false, cls) break;                                                 \
+        case 9: PYN_SIG_LAUNCH(C, DG, 1, false, (DG == 1), cls) break;                                                 \
+        case 13: PYN_SIG_LAUNCH(C, DG, 1, (DG == 1), (DG == 1), cls) break;                                            \
+        default: PYN_REQUIRE(false, "PYN_SIG_VARIANT: 1, 2 (+4 pipelined tiles, +8 double-buffered records)");        \
+      }                                                                                                                \
+    }
+    static const int sig_variant = getenv("PYN_SIG_VARIANT") ? atoi(getenv("PYN_SIG_VARIANT")) : 9;
     PYN_SIG_CASE(2, 1, 0) PYN_SIG_CASE(1, 1, 0)
     c0 = dv.tile_class_end[0];
     PYN_SIG_CASE(2, 2, 1) PYN_SIG_CASE(1, 2, 1)
     c0 = dv.tile_class_end[1];
     PYN_SIG_CASE(2, 4, 2) PYN_SIG_CASE(1, 4, 2)
+#undef PYN_SIG_LAUNCH
 #undef PYN_SIG_CASE
     const cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
