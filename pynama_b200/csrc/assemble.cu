@@ -441,22 +441,24 @@ asm_interior_affine_kernel(pyn::TopoView t, DescView d, const int64_t* __restric
 // The flat kernel above spends most of its instructions on finding out, per output block, which node it belongs to and
 // which of the node's elements contribute (and its element loop diverges).  On a structured mesh that information is the
 // same for every node of a row signature (topo.cuh: byte-identical incidence local indices and inverse maps).  Here a
-// WARP takes tiles of 32 nodes of ONE signature and walks their rows in passes of 128 bytes (PT adjacency positions):
-//   * 8 lanes share a node and split the positions of the pass, 4 nodes per step, 8 steps per pass.  A lane's position
-//     is fixed during a pass, so the product records it needs (one per incident element: the representative node's
-//     inverse map says which) sit in its REGISTERS for all 32 nodes -- fetched one pass ahead, the inverse-map bytes two
-//     passes ahead;
+// WARP takes a tile of 32 nodes of ONE signature and walks their rows in passes:
+//   * a row of nut units (a unit = one double2 of each of the node's two rows = 1 adjacency position of a 2x2-block
+//     matrix, 2 positions of a 2x1-block one) is cut into passes whose widths are the powers of two of nut's binary
+//     expansion, largest first, at most 32: 2^s lanes share a node, one unit per lane, 32 >> s nodes per step, 2^s
+//     steps per pass.  Every lane is busy whatever the row length and one store instruction writes pieces as long as
+//     the row allows (512 contiguous bytes when 2^s = 32);
+//   * a lane's unit is fixed during a pass, so the product records it needs (one per incident element: the
+//     representative node's inverse map says which) sit in its REGISTERS for all 32 nodes -- the inverse-map bytes are
+//     fetched two passes ahead and, where the registers allow (valence 1), the records one pass ahead;
 //   * what changes from step to step is the node: the 13 (4) coefficients of its <= DEG elements are staged once per
-//     tile in shared memory and read as broadcast LDS.128 (4 distinct nodes per warp, distinct banks);
-//   * the 8 lanes of a node store 128 consecutive bytes of each of its two rows straight from registers: no output
-//     tile, no transposition, every step independent of the others;
-//   * the warps are persistent and the tiles pipelined: while tile i is evaluated, the coefficients of tile i+1 arrive
-//     in the other half of the shared buffer (cp.async: no registers), its row starts and first inverse-map bytes in
-//     registers, and the descriptor and node slots of tile i+2 are on their way -- the three dependent loads that
-//     precede a tile's first pass are off the critical path (they were 17-37 % of the stall samples).
-// DEG (incident elements per node) is a template parameter: the tiles are sorted by valence class and each class gets
-// its own launch.  Same order of additions per entry as every other assembly kernel (ascending cell order): same bits.
-constexpr int SIG_W = 4;       // warps per CTA
+//     tile in shared memory (cp.async) and read as broadcast LDS.128;
+//   * the lanes of a node store consecutive double2 of each of its two rows straight from registers: no output tile,
+//     no transposition, every step independent of the others.
+// Per tile the kernel reads a 16-byte descriptor and one slot per lane {node, its elements} (topo.cuh), so two dependent
+// loads precede the first pass.  DEG (incident elements per node) is a template parameter: the tiles are sorted by
+// valence class and each class gets its own launch.  Same order of additions per entry as every other assembly kernel
+// (ascending cell order): same bits.
+constexpr int SIG_W = 4;       // warps (= tiles) per CTA
 constexpr int SIG_KMAX = 4;    // incident elements per node (quadrilateral meshes; larger valence: flat kernel)
 
 // v2 store when the address is 16-byte aligned, else one or two scalar stores -- predicated, no branches
@@ -482,49 +484,39 @@ __device__ __forceinline__ void sig_cp_async(void* smem_dst, const void* gsrc) {
 }
 __device__ __forceinline__ void sig_cp_async_wait() { asm volatile("cp.async.wait_all;\n" ::: "memory"); }
 
-template <int CD, int DEG, int UL, bool PIPEF>
+template <int CD, int DEG>
 struct SigShape {
   static constexpr int RD = 2;
-  static constexpr int NP = UL * 2 / CD;                             // adjacency positions per lane and pass
-  static constexpr int PT = 16 / CD;                                 // ... per pass: 16 doubles (8 units) of every row
+  static constexpr int NP = 2 / CD;                                  // adjacency positions per unit
   static constexpr int PR = CD == 2 ? pyn::PYN_AFF_PK : pyn::PYN_AFF_PR;
   static constexpr int NC = CD == 2 ? 13 : 4, NCP = CD == 2 ? 14 : 4;   // coefficients per element (padded to 16 B)
-  static constexpr int NB = PIPEF ? 2 : 1;                           // coefficient buffers (2: next tile lands early)
   static constexpr int SL = DEG == 1 ? 2 : (DEG == 2 ? 4 : 8);       // ints per node slot
-  static constexpr int CFW = 32 * DEG * NCP;                         // doubles of one coefficient buffer
-  static constexpr int per_warp = NB * CFW + 32 * RD;                // 8-byte words of shared memory per warp
+  static constexpr int per_warp = 32 * DEG * NCP + 32 * RD;          // 8-byte words of shared memory per warp
+  static constexpr bool DBL = DEG == 1;                              // records double-buffered in registers
 };
 
-struct SigTile {   // what a warp knows about a tile: unpacked descriptor
-  int cnt, L, deg;
-  unsigned lrp;
-  const uint8_t* iv;
-};
-
-template <int CD, int DEG, int UL, bool PIPEF, bool DBL>
+template <int CD, int DEG>
 __global__ void __launch_bounds__(SIG_W * 32, DEG == 4 ? 3 : 4)
 asm_sig_affine_kernel(pyn::TopoView t, DescView d, const int64_t* __restrict__ indptr, double* __restrict__ data,
-                      int64_t tile0, int64_t tile1, const int* __restrict__ slots, int dbg_align) {
-  using S = SigShape<CD, DEG, UL, PIPEF>;
-  constexpr int RD = 2, PT = S::PT, PR = S::PR, NP = S::NP, NC = S::NC, NCP = S::NCP, NB = S::NB, SL = S::SL;
+                      int64_t tile0, int64_t tile1, const int* __restrict__ slots) {
+  using S = SigShape<CD, DEG>;
+  constexpr int RD = 2, PR = S::PR, NP = S::NP, NC = S::NC, NCP = S::NCP, SL = S::SL;
   constexpr int C0 = CD == 2 ? 0 : 13;
-  constexpr int PPU = 2 / CD;                                        // positions per unit (double2 of a row)
-  static_assert(UL == 1, "one unit per lane");
-  constexpr bool PIPE = PIPEF;                                       // next tile's coefficients land during this one
+  constexpr bool DBL = S::DBL;
   extern __shared__ __align__(16) double sg_dyn[];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  double* s_cf = sg_dyn + (size_t)w * S::per_warp;                   // [buffer][node][k][NCP]
-  double** s_ptr = reinterpret_cast<double**>(s_cf + NB * S::CFW);   // [node][a]: start of row a of the node
-  const int64_t stride = (int64_t)gridDim.x * SIG_W;
-  int64_t tile = tile0 + (int64_t)blockIdx.x * SIG_W + w;
+  double* s_cf = sg_dyn + (size_t)w * S::per_warp;                   // [node][k][NCP]
+  double** s_ptr = reinterpret_cast<double**>(s_cf + 32 * DEG * NCP);   // [node][a]: start of row a of the node
+  const int64_t tile = tile0 + (int64_t)blockIdx.x * SIG_W + w;
   if (tile >= tile1) return;                                         // warps are independent: no CTA-wide barrier below
   const double* gtab = CD == 2 ? d.aff.pairK : d.aff.pairR;
   const int nn = t.nn;
   const double sign = d.sign;
-
-  auto load_l1 = [&](int64_t tl, int4& dd, int (&sl)[1 + DEG]) {     // level 1: descriptor and this lane's node slot
-    dd = __ldg(reinterpret_cast<const int4*>(d.tile_desc) + tl);
-    const int* sp = slots + ((tl - tile0) * 32 + lane) * SL;
+  // level 1: the tile's descriptor and this lane's node slot
+  const int4 dd = __ldg(reinterpret_cast<const int4*>(d.tile_desc) + tile);
+  int sl[1 + DEG];
+  {
+    const int* sp = slots + ((tile - tile0) * 32 + lane) * SL;
     if constexpr (SL == 2) {
       const int2 x = __ldg(reinterpret_cast<const int2*>(sp));
       sl[0] = x.x; sl[1] = x.y;
@@ -536,43 +528,32 @@ asm_sig_affine_kernel(pyn::TopoView t, DescView d, const int64_t* __restrict__ i
         sl[4] = __ldg(sp + 4);
       }
     }
-  };
-  auto unpack = [&](const int4& dd) {
-    SigTile g;
-    g.cnt = dd.x & 255;
-    g.deg = min((dd.x >> 8) & 255, DEG);
-    g.L = (int)((unsigned)dd.x >> 16);
-    g.lrp = (unsigned)dd.y;
-    g.iv = t.inv + (((int64_t)dd.w << 32) | (int64_t)(unsigned)dd.z);
-    return g;
-  };
-  // Passes: a row of nut units (a unit = one double2 = PPU adjacency positions) is cut into passes whose widths are
-  // the powers of two of nut's binary expansion, largest first, at most 32 units: 2^s lanes per node, one unit per
-  // lane, 32 >> s nodes per step -- every lane busy whatever the row length, and the pieces stored by one instruction
-  // are as long as the row allows (512 contiguous bytes when 2^s = 32).
+  }
+  const int cnt = dd.x & 255, deg = min((dd.x >> 8) & 255, DEG), L = (int)((unsigned)dd.x >> 16);
+  const unsigned lrp = (unsigned)dd.y;
+  const uint8_t* iv = t.inv + (((int64_t)dd.w << 32) | (int64_t)(unsigned)dd.z);
+  const int nut = (L + NP - 1) / NP;                                 // units of a row
   auto width_log2 = [&](int left) { return min(5, 31 - __clz(left)); };   // left >= 1 units remain
-  auto units_of = [&](const SigTile& g) { return (g.L + PPU - 1) / PPU; };
   // inverse-map bytes of this lane's unit in the pass that starts at unit pu (0xFF: no contribution / no position)
-  auto load_l = [&](const SigTile& g, int pu, int (&l)[DEG][NP]) {
-    const int nut = units_of(g);
+  auto load_l = [&](int pu, int (&l)[DEG][NP]) {
     const int s = pu < nut ? width_log2(nut - pu) : 0;
     const int u = lane & ((1 << s) - 1);
 #pragma unroll
     for (int k = 0; k < DEG; ++k)
 #pragma unroll
       for (int h = 0; h < NP; ++h) {
-        const int q = (pu + u) * PPU + h;
-        l[k][h] = (pu < nut && k < g.deg && q < g.L) ? (int)g.iv[k * g.L + q] : 0xFF;
+        const int q = (pu + u) * NP + h;
+        l[k][h] = (pu < nut && k < deg && q < L) ? (int)iv[k * L + q] : 0xFF;
       }
   };
-  auto load_rec = [&](const SigTile& g, const int (&l)[DEG][NP], double (&rec)[DEG][NP][PR]) {
+  auto load_rec = [&](const int (&l)[DEG][NP], double (&rec)[DEG][NP][PR]) {
 #pragma unroll
     for (int k = 0; k < DEG; ++k)
 #pragma unroll
       for (int h = 0; h < NP; ++h)
         if (l[k][h] != 0xFF) {
           const double2* rp =
-              reinterpret_cast<const double2*>(gtab + ((int64_t)((g.lrp >> (8 * k)) & 255u) * nn + l[k][h]) * PR);
+              reinterpret_cast<const double2*>(gtab + ((int64_t)((lrp >> (8 * k)) & 255u) * nn + l[k][h]) * PR);
 #pragma unroll
           for (int i = 0; i < PR / 2; ++i) {
             const double2 x = __ldg(rp + i);
@@ -581,37 +562,24 @@ asm_sig_affine_kernel(pyn::TopoView t, DescView d, const int64_t* __restrict__ i
           }
         }
   };
-  // level 2 of a tile: coefficients of the lane's node -> shared buffer `buf` (asynchronous), its row starts and the
-  // inverse-map bytes of the first two passes -> registers
-  auto stage2 = [&](const SigTile& g, const int (&sl)[1 + DEG], int buf, int64_t (&q)[RD], int (&la)[DEG][NP],
-                    int (&lb)[DEG][NP]) {
+  // level 2: coefficients of the lane's node -> shared memory (asynchronous), its row starts, the inverse-map bytes of
+  // the first two passes
 #pragma unroll
-    for (int k = 0; k < DEG; ++k) {
-      const double* cg = d.coef + (int64_t)sl[1 + k] * PYN_AFF_NCOEF + C0;
-      double* dst = s_cf + buf * S::CFW + (lane * DEG + k) * NCP;
-      if constexpr (CD == 2) {
+  for (int k = 0; k < DEG; ++k) {
+    const double* cg = d.coef + (int64_t)sl[1 + k] * PYN_AFF_NCOEF + C0;
+    double* dst = s_cf + (lane * DEG + k) * NCP;
+    if constexpr (CD == 2) {
 #pragma unroll
-        for (int i = 0; i < NCP / 2; ++i) sig_cp_async<16>(dst + 2 * i, cg + 2 * i);
-      } else {
+      for (int i = 0; i < NCP / 2; ++i) sig_cp_async<16>(dst + 2 * i, cg + 2 * i);
+    } else {
 #pragma unroll
-        for (int i = 0; i < NC; ++i) sig_cp_async<8>(dst + i, cg + i);
-      }
+      for (int i = 0; i < NC; ++i) sig_cp_async<8>(dst + i, cg + i);
     }
-    q[0] = indptr[(int64_t)sl[0] * RD];
-    q[1] = indptr[(int64_t)sl[0] * RD + 1];
-    load_l(g, 0, la);
-    load_l(g, 1 << width_log2(units_of(g)), lb);
-  };
-
-  int4 dd;
-  int sl[1 + DEG];
-  load_l1(tile, dd, sl);
-  SigTile g = unpack(dd);
-  int64_t q[RD];
+  }
+  const int64_t q0 = indptr[(int64_t)sl[0] * RD], q1 = indptr[(int64_t)sl[0] * RD + 1];
   int l0[DEG][NP], l1[DEG][NP];
-  stage2(g, sl, 0, q, l0, l1);
-  bool has_n = tile + stride < tile1;
-  if (has_n) load_l1(tile + stride, dd, sl);                         // level 1 of the next tile
+  load_l(0, l0);
+  load_l(1 << width_log2(nut), l1);
   double rec[DEG][NP][PR], recn[DBL ? DEG : 1][NP][PR];
 #pragma unroll
   for (int k = 0; k < DEG; ++k)
@@ -622,133 +590,96 @@ asm_sig_affine_kernel(pyn::TopoView t, DescView d, const int64_t* __restrict__ i
         rec[k][h][i] = 0.0;
         if (DBL) recn[k][h][i] = 0.0;
       }
-  int buf = 0;
-  for (;;) {
-    __syncwarp();                                                    // everybody is done with the previous tile
-    sig_cp_async_wait();
-    s_ptr[lane * RD] = data + q[0];
-    s_ptr[lane * RD + 1] = data + q[1];
-    load_rec(g, l0, rec);
-    __syncwarp();
-    // the tiles behind this one
-    SigTile gn = g;
-    int64_t qn[RD] = {0, 0};
-    int ln0[DEG][NP], ln1[DEG][NP];
-    const bool has_nn = tile + 2 * stride < tile1;
-    if (has_n) {
-      gn = unpack(dd);
-      if constexpr (PIPE) {
-        stage2(gn, sl, buf ^ 1, qn, ln0, ln1);
-        if (has_nn) load_l1(tile + 2 * stride, dd, sl);
+  s_ptr[lane * RD] = data + q0;
+  s_ptr[lane * RD + 1] = data + q1;
+  load_rec(l0, rec);                                                 // level 3
+  sig_cp_async_wait();
+  __syncwarp();
+
+  int sn = width_log2(nut);
+  for (int pu = 0; pu < nut;) {
+    const int s = sn;
+    const int u = lane & ((1 << s) - 1), grp = lane >> s, npg = 32 >> s;
+    const int pu1 = pu + (1 << s);                           // the next pass, and the one after
+    sn = pu1 < nut ? width_log2(nut - pu1) : 0;
+    const int pu2 = pu1 + (1 << sn);
+    if constexpr (DBL) load_rec(l1, recn);
+    int l2[DEG][NP];
+    load_l(pu2, l2);
+    bool on[DEG][NP], anyk[DEG];
+#pragma unroll
+    for (int k = 0; k < DEG; ++k) {
+      bool some = false;
+#pragma unroll
+      for (int h = 0; h < NP; ++h) {
+        on[k][h] = l0[k][h] != 0xFF;
+        some = some || on[k][h];
       }
+      anyk[k] = __any_sync(0xffffffffu, some);
     }
-    const double* cfb = s_cf + buf * S::CFW;
-    const int nut = units_of(g);
-    int sn = width_log2(nut);
-    for (int pu = 0; pu < nut;) {
-      const int s = sn;
-      const int u = lane & ((1 << s) - 1), grp = lane >> s, npg = 32 >> s;
-      const int pu1 = pu + (1 << s);                         // the next pass, and the one after
-      sn = pu1 < nut ? width_log2(nut - pu1) : 0;
-      const int pu2 = pu1 + (1 << sn);
-      // fetch ahead: records of the next pass, inverse-map bytes of the one after
-      if constexpr (DBL) load_rec(g, l1, recn);
-      int l2[DEG][NP];
-      load_l(g, pu2, l2);
-      bool on[DEG][NP], anyk[DEG];
-#pragma unroll
-      for (int k = 0; k < DEG; ++k) {
-#pragma unroll
-        for (int h = 0; h < NP; ++h) on[k][h] = l0[k][h] != 0xFF;
-        bool some = false;
-#pragma unroll
-        for (int h = 0; h < NP; ++h) some = some || on[k][h];
-        anyk[k] = __any_sync(0xffffffffu, some);
-      }
-      const bool second = CD == 2 || (pu + u) * PPU + 1 < g.L;   // the unit's second double exists
-      const int64_t off = (int64_t)(pu + u) * 2;
+    const bool second = CD == 2 || (pu + u) * NP + 1 < L;    // the unit's second double exists
+    const int64_t off = (int64_t)(pu + u) * 2;
 #pragma unroll 2
-      for (int st = 0; st < (1 << s); ++st) {                // npg nodes per step
-        const int n = st * npg + grp;
-        const double* cfn = cfb + n * (DEG * NCP);
-        const longlong2 pp = *reinterpret_cast<const longlong2*>(s_ptr + n * RD);
-        double v[NP][RD][CD];
+    for (int st = 0; st < (1 << s); ++st) {                  // npg nodes per step
+      const int n = st * npg + grp;
+      const double* cfn = s_cf + n * (DEG * NCP);
+      const longlong2 pp = *reinterpret_cast<const longlong2*>(s_ptr + n * RD);
+      double v[NP][RD][CD];
 #pragma unroll
-        for (int h = 0; h < NP; ++h)
+      for (int h = 0; h < NP; ++h)
 #pragma unroll
-          for (int a = 0; a < RD; ++a)
+        for (int a = 0; a < RD; ++a)
 #pragma unroll
-            for (int b = 0; b < CD; ++b) v[h][a][b] = 0.0;
+          for (int b = 0; b < CD; ++b) v[h][a][b] = 0.0;
 #pragma unroll
-        for (int k = 0; k < DEG; ++k) {                      // ascending cell order
-          if (DEG == 1 || anyk[k]) {                         // uniform: some lane of the warp takes element k
-            double cf[NCP];
+      for (int k = 0; k < DEG; ++k) {                        // ascending cell order
+        if (DEG == 1 || anyk[k]) {                           // uniform: some lane of the warp takes element k
+          double cf[NCP];
 #pragma unroll
-            for (int i = 0; i < NCP / 2; ++i) {
-              const double2 x = *reinterpret_cast<const double2*>(cfn + k * NCP + 2 * i);
-              cf[2 * i] = x.x;
-              cf[2 * i + 1] = x.y;
+          for (int i = 0; i < NCP / 2; ++i) {
+            const double2 x = *reinterpret_cast<const double2*>(cfn + k * NCP + 2 * i);
+            cf[2 * i] = x.x;
+            cf[2 * i + 1] = x.y;
+          }
+#pragma unroll
+          for (int h = 0; h < NP; ++h) {
+            double blk[RD][CD];
+            if constexpr (CD == 2) {
+              pyn::affine_block_K(cf, rec[k][h], blk);
+            } else {
+              pyn::affine_block_R(cf, rec[k][h], d.which, d.aff.alpha_w, d.aff.alpha_d, blk);
             }
+            if (on[k][h]) {
 #pragma unroll
-            for (int h = 0; h < NP; ++h) {
-              double blk[RD][CD];
-              if constexpr (CD == 2) {
-                pyn::affine_block_K(cf, rec[k][h], blk);
-              } else {
-                pyn::affine_block_R(cf, rec[k][h], d.which, d.aff.alpha_w, d.aff.alpha_d, blk);
-              }
-              if (on[k][h]) {
+              for (int a = 0; a < RD; ++a)
 #pragma unroll
-                for (int a = 0; a < RD; ++a)
-#pragma unroll
-                  for (int b = 0; b < CD; ++b) v[h][a][b] += sign * blk[a][b];
-              }
+                for (int b = 0; b < CD; ++b) v[h][a][b] += sign * blk[a][b];
             }
           }
-        }
-#pragma unroll
-        for (int a = 0; a < RD; ++a) {
-          double* o = reinterpret_cast<double*>(a == 0 ? pp.x : pp.y) + off;
-          if (dbg_align) o = reinterpret_cast<double*>((reinterpret_cast<uintptr_t>(o - 2 * u) & ~(uintptr_t)127)) + 2 * u;   // EXPERIMENT ONLY: wrong addresses, line-aligned pieces
-          const bool ok = n < g.cnt;
-          const bool al = ok && second && (reinterpret_cast<uintptr_t>(o) & 15) == 0;
-          sig_store(o, v[0][a][0], CD == 2 ? v[0][a][CD - 1] : v[NP - 1][a][0], al, ok && !al, ok && !al && second);
         }
       }
-      // rotate the look-ahead
+      const bool ok = n < cnt;
 #pragma unroll
-      for (int k = 0; k < DEG; ++k)
-#pragma unroll
-        for (int h = 0; h < NP; ++h) {
-          l0[k][h] = l1[k][h];
-          l1[k][h] = l2[k][h];
-          if constexpr (DBL) {
-#pragma unroll
-            for (int i = 0; i < PR; ++i) rec[k][h][i] = recn[k][h][i];
-          }
-        }
-      if constexpr (!DBL) load_rec(g, l0, rec);
-      pu = pu1;
+      for (int a = 0; a < RD; ++a) {
+        double* o = reinterpret_cast<double*>(a == 0 ? pp.x : pp.y) + off;
+        const bool al = ok && second && (reinterpret_cast<uintptr_t>(o) & 15) == 0;
+        sig_store(o, v[0][a][0], CD == 2 ? v[0][a][CD - 1] : v[NP - 1][a][0], al, ok && !al, ok && !al && second);
+      }
     }
-    if (!has_n) break;
-    if constexpr (!PIPE) {                                   // one buffer: the next tile is staged after this one
-      __syncwarp();
-      stage2(gn, sl, buf, qn, ln0, ln1);
-      if (has_nn) load_l1(tile + 2 * stride, dd, sl);
-    }
-    g = gn;
-    q[0] = qn[0];
-    q[1] = qn[1];
+    // rotate the look-ahead
 #pragma unroll
     for (int k = 0; k < DEG; ++k)
 #pragma unroll
       for (int h = 0; h < NP; ++h) {
-        l0[k][h] = ln0[k][h];
-        l1[k][h] = ln1[k][h];
+        l0[k][h] = l1[k][h];
+        l1[k][h] = l2[k][h];
+        if constexpr (DBL) {
+#pragma unroll
+          for (int i = 0; i < PR; ++i) rec[k][h][i] = recn[k][h][i];
+        }
       }
-    tile += stride;
-    has_n = has_nn;
-    if constexpr (PIPE) buf ^= 1;
+    if constexpr (!DBL) load_rec(l0, rec);
+    pu = pu1;
   }
 }
 
@@ -1144,51 +1075,22 @@ static int launch_interior(const pyn_topo* t, const DescView& dv, const int64_t*
   if (dv.coef && !indices && data && dv.tile_desc) {   // structured mesh, values only: signature-grouped kernel
     PYN_REQUIRE(tv.nn == dv.aff.n * dv.aff.n, "affine assembly: element handle of another order");
     int64_t c0 = 0;
-#define PYN_SIG_LAUNCH(C, DG, U, P, B, cls)                                                                             \
-    {                                                                                                                  \
-      using Sh = SigShape<C, DG, U, P>;                                                                                \
-      const int64_t c1 = dv.tile_class_end[cls];                                                                       \
-      const size_t dyn = sizeof(double) * (size_t)SIG_W * Sh::per_warp;                                                \
-      static int resident = 0;   /* CTAs per SM of this variant (persistent warps: one wave) */                        \
-      if (!resident) {                                                                                                 \
-        PYN_CHECK_CUDA(cudaFuncSetAttribute(asm_sig_affine_kernel<C, DG, U, P, B>,                                     \
-                                            cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));                   \
-        PYN_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&resident, asm_sig_affine_kernel<C, DG, U, P, B>, \
-                                                                     SIG_W * 32, dyn));                                \
-        if (resident < 1) resident = 1;                                                                                \
-      }                                                                                                                \
-      int64_t g = (c1 - c0 + SIG_W - 1) / SIG_W;                                                                       \
-      const int64_t cap = (int64_t)pyn::sm_count() * resident;                                                         \
-      if (g > cap && getenv("PYN_SIG_PERSIST")) g = cap;                                                               \
-      asm_sig_affine_kernel<C, DG, U, P, B><<<(int)g, SIG_W * 32, dyn, st>>>(tv, dv, indptr, data, c0, c1,             \
-                                                                             dv.tile_slot + dv.tile_slot_base[cls],   \
-                                                                             getenv("PYN_SIG_DBG_ALIGN") ? 1 : 0);    \
-      pyn::count_launch();                                                                                             \
-    }
-    // variant = units per lane (1, 2) | tiles pipelined (+4) | records double-buffered (+8); PYN_SIG_VARIANT: A/B switch
 #define PYN_SIG_CASE(C, DG, cls)                                                                                        \
     if (dv.cdof == C && dv.tile_class_end[cls] > c0) {                                                                  \
-      /* what the registers allow: 2 units per lane and double-buffered records for valence 1 only (and not both),     \
-         pipelined tiles up to valence 2 */                                                                            \
-      int var = sig_variant;                                                                                           \
-      if (DG != 1) var = (var & ~(3 | 8)) | 1;                                                                         \
-      if (DG == 4) var &= ~4;                                                                                          \
-      if ((var & 3) == 2) var &= ~8;                                                                                   \
-      switch (var) {                                                                                                   \
-        case 1: PYN_SIG_LAUNCH(C, DG, 1, false, false, cls) break;                                                     \
-        case 5: PYN_SIG_LAUNCH(C, DG, 1, (DG <= 2), false, cls) break;                                                 \
-        case 9: PYN_SIG_LAUNCH(C, DG, 1, false, (DG == 1), cls) break;                                                 \
-        case 13: PYN_SIG_LAUNCH(C, DG, 1, (DG == 1), (DG == 1), cls) break;                                            \
-        default: PYN_REQUIRE(false, "PYN_SIG_VARIANT: 1, 2 (+4 pipelined tiles, +8 double-buffered records)");        \
-      }                                                                                                                \
+      const int64_t c1 = dv.tile_class_end[cls], g = (c1 - c0 + SIG_W - 1) / SIG_W;                                    \
+      const size_t dyn = sizeof(double) * (size_t)SIG_W * SigShape<C, DG>::per_warp;                                   \
+      PYN_REQUIRE(g < 0x7fffffff, "affine assembly: too many signature tiles");                                        \
+      PYN_CHECK_CUDA(cudaFuncSetAttribute(asm_sig_affine_kernel<C, DG>, cudaFuncAttributeMaxDynamicSharedMemorySize,   \
+                                          (int)dyn));                                                                  \
+      asm_sig_affine_kernel<C, DG><<<(int)g, SIG_W * 32, dyn, st>>>(tv, dv, indptr, data, c0, c1,                      \
+                                                                    dv.tile_slot + dv.tile_slot_base[cls]);            \
+      pyn::count_launch();                                                                                             \
     }
-    static const int sig_variant = getenv("PYN_SIG_VARIANT") ? atoi(getenv("PYN_SIG_VARIANT")) : 9;
     PYN_SIG_CASE(2, 1, 0) PYN_SIG_CASE(1, 1, 0)
     c0 = dv.tile_class_end[0];
     PYN_SIG_CASE(2, 2, 1) PYN_SIG_CASE(1, 2, 1)
     c0 = dv.tile_class_end[1];
     PYN_SIG_CASE(2, 4, 2) PYN_SIG_CASE(1, 4, 2)
-#undef PYN_SIG_LAUNCH
 #undef PYN_SIG_CASE
     const cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
@@ -1373,9 +1275,9 @@ static int ensure_sig_tiles(const pyn_topo* t, const pyn_bcmap* mc, cudaStream_t
   pyn_bcmap* m = const_cast<pyn_bcmap*>(mc);   // cache owned by the handle (one host thread per handle)
   if (m->tiles_state != 0) return PYN_OK;
   m->tiles_state = -1;
-  // Measured slower than the flat kernel at every order but 2 (profiles/r02_ncu_fused_assembly.md, structure v5):
-  // kept as an opt-in structure, PYN_AFF_SIG=1.
-  static const bool off = getenv("PYN_AFF_SIG") == nullptr;
+  // default on structured meshes; PYN_AFF_NO_SIG=1 keeps the flat kernel (A/B switch, and what the parity test uses to
+  // cover both)
+  static const bool off = getenv("PYN_AFF_NO_SIG") != nullptr;
   if (off || t->nsig <= 0 || t->max_valence > SIG_KMAX || t->nn > 255 || (int64_t)t->nn * SIG_KMAX >= 32768)
     return PYN_OK;   // (a row holds at most max_valence * nn column nodes: L fits the descriptor's 15 bits)
   const int64_t n = t->nnodes, nint = t->nnodes - m->nlist;

@@ -140,11 +140,12 @@ def test_fused_rd_blocks(be):
     assert rel_err(Rde.cpu().numpy(), Rdo) < 1e-12
 
 
-@pytest.mark.skipif(os.environ.get("PYN_AFF_SIG") is not None, reason="already inside the opt-in run")
-def test_signature_tile_structure_is_bit_identical_too():
-    """The opt-in structure of the fused kernel (PYN_AFF_SIG=1: tiles of one row signature, one node per lane) is read
-    once per process, so the parity cases above are re-run in a child process with it switched on."""
-    env = dict(os.environ, PYN_AFF_SIG="1")
+@pytest.mark.skipif(os.environ.get("PYN_AFF_NO_SIG") is not None, reason="already inside the flat-kernel run")
+def test_flat_kernel_is_bit_identical_too():
+    """On a structured mesh the fused assembly takes the signature-tile kernel (asm_sig_affine_kernel); the slot-flat
+    kernel (asm_interior_affine_kernel: meshes without row signatures, valence > 4) is selected once per process with
+    PYN_AFF_NO_SIG=1, so the parity cases above are re-run in a child process with it."""
+    env = dict(os.environ, PYN_AFF_NO_SIG="1")
     r = subprocess.run([sys.executable, "-m", "pytest", __file__, "-q", "-x", "-k", "fused_assembly_vs_oracle or rd_blocks"],
                        env=env, capture_output=True, text=True, timeout=900)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
