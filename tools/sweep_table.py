@@ -1,9 +1,12 @@
-"""profiles/r02_order_sweep_percell.md from the two order-sweep .jsonl files (tools/order_sweep.py --fused 1|0)."""
+"""profiles/r02_order_sweep_percell.md from the order-sweep .jsonl files: tools/order_sweep.py --fused 1, --fused 0 and
+(optional) --fused 1 under PYN_AFF_NO_SIG=1 (the slot-flat kernel)."""
 import json
 import sys
 
-fused, mat = {}, {}
-for path, dst in ((sys.argv[1], fused), (sys.argv[2], mat)):
+fused, mat, flat = {}, {}, {}
+for path, dst in ((sys.argv[1], fused), (sys.argv[2], mat), (sys.argv[3] if len(sys.argv) > 3 else None, flat)):
+    if path is None:
+        continue
     for l in open(path):
         if l.startswith("{"):
             d = json.loads(l)
@@ -21,12 +24,19 @@ for n in sorted(mat):
     print(f"| {n} | {c['cells']:,} | {c['nnz']['K']:,} | {d['ms_per_step']:.2f} | {p['elem']:.2f} | {i['tflops']:.2f} | "
           f"{i['fp64_frac']:.3f} | {i['gbs']:.0f} | {i['flop_per_byte']:.1f} | {p['K']:.2f} | {d['roofline']['frac']:.2f} | "
           f"{d['value'] / 1e9:.2f} |")
-print("\n## fused integrate-and-assemble (default on parallelogram cells)\n")
-print("| ngl | step ms | coefficients ms | K ms | K frac of HBM | Rw ms | G DOF/s | speed-up of the step |\n|---|---|---|---|---|---|---|---|")
-for n in sorted(fused):
-    d = fused[n]; p = d["phases_ms"]
-    print(f"| {n} | {d['ms_per_step']:.2f} | {p['elem']:.2f} | {p['K']:.2f} | {d['roofline']['frac']:.2f} | {p['Rw']:.2f} | "
-          f"{d['value'] / 1e9:.2f} | {mat[n]['ms_per_step'] / d['ms_per_step']:.1f}x |")
+def fused_table(rows):
+    print("| ngl | step ms | coefficients ms | K ms | K frac of HBM | Rw ms | G DOF/s | speed-up of the step |\n|---|---|---|---|---|---|---|---|")
+    for n in sorted(rows):
+        d = rows[n]; p = d["phases_ms"]
+        print(f"| {n} | {d['ms_per_step']:.2f} | {p['elem']:.2f} | {p['K']:.2f} | {d['roofline']['frac']:.2f} | {p['Rw']:.2f} | "
+              f"{d['value'] / 1e9:.2f} | {mat[n]['ms_per_step'] / d['ms_per_step']:.1f}x |")
+
+
+print("\n## fused integrate-and-assemble, signature-tile kernel (default on structured meshes of parallelogram cells)\n")
+fused_table(fused)
+if flat:
+    print("\n## fused integrate-and-assemble, slot-flat kernel (`PYN_AFF_NO_SIG=1`; meshes without row signatures)\n")
+    fused_table(flat)
 print("""
 Reading.  The arithmetic intensity of the sum-factorised integration (its flops / the `64 n^4` B of element matrices it
 writes) crosses the machine balance of the B200 (37 TFLOP/s FP64 / 6.5 TB/s = 5.7 flop/B) at **ngl 4**: below it an
@@ -35,7 +45,11 @@ of the FP64 pipe) and 0.08 of the HBM bandwidth; ncu (`r02_ncu_elem_kle.md`) sho
 stalls are CTA barriers (eight per element) and a fifth shared-memory operand latency (every multiply-add takes two
 operands from shared memory), at ngl 2 instruction fetch (a long kernel run by one warp per 8x8 matrix).  On general
 quads the integration therefore dominates the per-cell step 5-10x at every order.  The closed form on parallelogram
-cells removes the contraction and the element matrices altogether: the step becomes the CSR store stream plus ~60
-instructions per 2x2 block, 3.7-6.7x faster, issue-bound at 0.1-0.3 of the HBM roofline
-(`r02_ncu_fused_assembly.md`); its cost per stored entry is flat in ngl, so this path has no crossover -- it is
-designed to be HBM-bound at every order once the instruction overhead is gone.""")
+cells removes the contraction and the element matrices altogether: the step becomes the CSR store stream plus the
+evaluation of the entries from 13 coefficients and a 64-byte product record per 2x2 block.  The slot-flat kernel pays
+~350 instructions per 32 blocks for look-ups and is issue-bound at 0.1-0.3 of the HBM roofline; the signature-tile
+kernel (`r02_ncu_fused_assembly.md`) brings that to ~80 and reaches **0.44-0.74** for ngl >= 4 -- highest where the rows
+are whole 32-byte sectors or 128-byte lines (even ngl: 0.49 / 0.67 / 0.74 at ngl 4 / 6 / 8; odd ngl, rows of 16 * odd
+bytes: 0.44 / 0.51 / 0.49 at ngl 5 / 7 / 9), lowest for the short rows of ngl 2-3 (9-25 column nodes: the per-tile
+set-up is not amortised).  Its cost per stored entry is flat in ngl, so this path has no crossover: it is a store
+stream at every order.""")
