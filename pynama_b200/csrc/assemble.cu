@@ -531,7 +531,7 @@ asm_sig_affine_kernel(pyn::TopoView t, DescView d, const int64_t* __restrict__ i
   }
   const int cnt = dd.x & 255, deg = min((dd.x >> 8) & 255, DEG), L = (int)((unsigned)dd.x >> 16);
   const unsigned lrp = (unsigned)dd.y;
-  const uint8_t* iv = t.inv + (((int64_t)dd.w << 32) | (int64_t)(unsigned)dd.z);
+  const uint8_t* iv = t.inv + (((int64_t)(dd.w & 0xffffff) << 32) | (int64_t)(unsigned)dd.z);   // (top byte: row offsets)
   const int nut = (L + NP - 1) / NP;                                 // units of a row
   auto width_log2 = [&](int left) { return min(5, 31 - __clz(left)); };   // left >= 1 units remain
   // inverse-map bytes of this lane's unit in the pass that starts at unit pu (0xFF: no contribution / no position)
@@ -679,6 +679,224 @@ asm_sig_affine_kernel(pyn::TopoView t, DescView d, const int64_t* __restrict__ i
         }
       }
     if constexpr (!DBL) load_rec(l0, rec);
+    pu = pu1;
+  }
+}
+
+// ---- the same with LINE-ALIGNED stores ---------------------------------------------------------------------------------
+// The rows of a CSR matrix start wherever the previous row ended: 16 bytes into a 32-byte sector every second time when a
+// row holds an odd number of 2x2 blocks, 8 bytes off for 2x1 blocks.  Measured on the kernel above (pieces rounded down
+// to 128-byte lines, wrong addresses): the misaligned pieces cost 20 % (K) to 35 % (Rw) of the launch.  Here the tiles
+// are grouped by (signature, offset of the node's first row inside a 128-byte line) -- ensure_sig_tiles sorts by both, the
+// second row's offset follows from the row length -- and a lane's pair of doubles is fixed in LINE coordinates: pair y
+// of row a is the row's double y - tau_a, so the 2^s lanes of a node always cover whole, aligned 16-byte units and a
+// 32-lane pass writes four whole lines.  The price: the two rows of a node are evaluated at DIFFERENT column positions
+// (tau_0 != tau_1), each from its own product record (twice the record registers) with the row-wise closed form
+// (affine_row_K / affine_row_R: the same operations per entry as the block form, so the same bits).
+template <int CD, int DEG>
+struct SigRowShape {
+  static constexpr int NP = 2 / CD;                                  // adjacency positions per pair of doubles
+  static constexpr int PR = CD == 2 ? pyn::PYN_AFF_PK : pyn::PYN_AFF_PR;
+  static constexpr int NC = CD == 2 ? 13 : 4, NCP = CD == 2 ? 14 : 4;
+  static constexpr int SL = DEG == 1 ? 2 : (DEG == 2 ? 4 : 8);
+  static constexpr int per_warp = 32 * DEG * NCP + 32 * 2;           // 8-byte words of shared memory per warp
+};
+
+template <int CD, int DEG>
+__global__ void __launch_bounds__(SIG_W * 32, DEG == 1 ? 4 : 3)
+asm_sigrow_affine_kernel(pyn::TopoView t, DescView d, const int64_t* __restrict__ indptr, double* __restrict__ data,
+                         int64_t tile0, int64_t tile1, const int* __restrict__ slots) {
+  using S = SigRowShape<CD, DEG>;
+  constexpr int RD = 2, PR = S::PR, NP = S::NP, NC = S::NC, NCP = S::NCP, SL = S::SL;
+  constexpr int C0 = CD == 2 ? 0 : 13;
+  extern __shared__ __align__(16) double sg_dyn[];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  double* s_cf = sg_dyn + (size_t)w * S::per_warp;                   // [node][k][NCP]
+  double** s_ptr = reinterpret_cast<double**>(s_cf + 32 * DEG * NCP);   // [node][a]: start of row a of the node
+  const int64_t tile = tile0 + (int64_t)blockIdx.x * SIG_W + w;
+  if (tile >= tile1) return;
+  const double* gtab = CD == 2 ? d.aff.pairK : d.aff.pairR;
+  const int nn = t.nn;
+  const double sign = d.sign;
+  const int4 dd = __ldg(reinterpret_cast<const int4*>(d.tile_desc) + tile);
+  int sl[1 + DEG];
+  {
+    const int* sp = slots + ((tile - tile0) * 32 + lane) * SL;
+    if constexpr (SL == 2) {
+      const int2 x = __ldg(reinterpret_cast<const int2*>(sp));
+      sl[0] = x.x; sl[1] = x.y;
+    } else {
+      const int4 x = __ldg(reinterpret_cast<const int4*>(sp));
+      sl[0] = x.x; sl[1] = x.y; sl[2] = x.z;
+      if constexpr (SL == 8) {
+        sl[3] = x.w;
+        sl[4] = __ldg(sp + 4);
+      }
+    }
+  }
+  const int cnt = dd.x & 255, deg = min((dd.x >> 8) & 255, DEG), L = (int)((unsigned)dd.x >> 16);
+  const unsigned lrp = (unsigned)dd.y;
+  const uint8_t* iv = t.inv + (((int64_t)(dd.w & 0xffffff) << 32) | (int64_t)(unsigned)dd.z);
+  // offsets of the two rows inside a line, in doubles (2x2 blocks: rounded down to a whole block -- a row that starts on
+  // an odd double keeps its scalar stores)
+  int tau[RD] = {(dd.w >> 24) & 15, (int)((unsigned)dd.w >> 28)};
+  if (CD == 2) {
+    tau[0] &= ~1;
+    tau[1] &= ~1;
+  }
+  const int rowlen = L * CD;
+  const int nuy = (max(tau[0], tau[1]) + rowlen + 1) / 2;            // pairs of a row in line coordinates
+  auto width_log2 = [&](int left) { return min(5, 31 - __clz(left)); };
+  auto load_l = [&](int pu, int (&l)[RD][DEG][NP]) {
+    const int s = pu < nuy ? width_log2(nuy - pu) : 0;
+    const int u = lane & ((1 << s) - 1);
+#pragma unroll
+    for (int a = 0; a < RD; ++a) {
+      const int tt = 2 * (pu + u) - tau[a];                          // row-relative double of the pair's first entry
+#pragma unroll
+      for (int k = 0; k < DEG; ++k)
+#pragma unroll
+        for (int h = 0; h < NP; ++h) {
+          const int q = CD == 2 ? (tt >> 1) : tt + h;
+          const bool ok = pu < nuy && k < deg && (CD == 2 ? tt >= 0 : q >= 0) && q < L;
+          l[a][k][h] = ok ? (int)iv[k * L + q] : 0xFF;
+        }
+    }
+  };
+  auto load_rec = [&](const int (&l)[RD][DEG][NP], double (&rec)[RD][DEG][NP][PR]) {
+#pragma unroll
+    for (int a = 0; a < RD; ++a)
+#pragma unroll
+      for (int k = 0; k < DEG; ++k)
+#pragma unroll
+        for (int h = 0; h < NP; ++h)
+          if (l[a][k][h] != 0xFF) {
+            const double2* rp =
+                reinterpret_cast<const double2*>(gtab + ((int64_t)((lrp >> (8 * k)) & 255u) * nn + l[a][k][h]) * PR);
+#pragma unroll
+            for (int i = 0; i < PR / 2; ++i) {
+              const double2 x = __ldg(rp + i);
+              rec[a][k][h][2 * i] = x.x;
+              rec[a][k][h][2 * i + 1] = x.y;
+            }
+          }
+  };
+#pragma unroll
+  for (int k = 0; k < DEG; ++k) {
+    const double* cg = d.coef + (int64_t)sl[1 + k] * PYN_AFF_NCOEF + C0;
+    double* dst = s_cf + (lane * DEG + k) * NCP;
+    if constexpr (CD == 2) {
+#pragma unroll
+      for (int i = 0; i < NCP / 2; ++i) sig_cp_async<16>(dst + 2 * i, cg + 2 * i);
+    } else {
+#pragma unroll
+      for (int i = 0; i < NC; ++i) sig_cp_async<8>(dst + i, cg + i);
+    }
+  }
+  const int64_t q0 = indptr[(int64_t)sl[0] * RD], q1 = indptr[(int64_t)sl[0] * RD + 1];
+  int l0[RD][DEG][NP], l1[RD][DEG][NP];
+  load_l(0, l0);
+  load_l(1 << width_log2(nuy), l1);
+  double rec[RD][DEG][NP][PR];
+#pragma unroll
+  for (int a = 0; a < RD; ++a)
+#pragma unroll
+    for (int k = 0; k < DEG; ++k)
+#pragma unroll
+      for (int h = 0; h < NP; ++h)
+#pragma unroll
+        for (int i = 0; i < PR; ++i) rec[a][k][h][i] = 0.0;
+  // row starts in line coordinates: pair y of row a sits at s_ptr[a] + 2 y
+  s_ptr[lane * RD] = data + q0 - tau[0];
+  s_ptr[lane * RD + 1] = data + q1 - tau[1];
+  load_rec(l0, rec);
+  sig_cp_async_wait();
+  __syncwarp();
+
+  int sn = width_log2(nuy);
+  for (int pu = 0; pu < nuy;) {
+    const int s = sn;
+    const int u = lane & ((1 << s) - 1), grp = lane >> s, npg = 32 >> s;
+    const int pu1 = pu + (1 << s);
+    sn = pu1 < nuy ? width_log2(nuy - pu1) : 0;
+    int l2[RD][DEG][NP];
+    load_l(pu1 + (1 << sn), l2);
+    bool on[RD][DEG][NP], anyk[DEG], first[RD], second[RD];
+#pragma unroll
+    for (int k = 0; k < DEG; ++k) {
+      bool some = false;
+#pragma unroll
+      for (int a = 0; a < RD; ++a)
+#pragma unroll
+        for (int h = 0; h < NP; ++h) {
+          on[a][k][h] = l0[a][k][h] != 0xFF;
+          some = some || on[a][k][h];
+        }
+      anyk[k] = __any_sync(0xffffffffu, some);
+    }
+#pragma unroll
+    for (int a = 0; a < RD; ++a) {                           // which doubles of the pair exist in row a
+      const int tt = 2 * (pu + u) - tau[a];
+      first[a] = tt >= 0 && tt < rowlen;
+      second[a] = tt + 1 >= 0 && tt + 1 < rowlen;
+    }
+    const int64_t off = (int64_t)(pu + u) * 2;
+#pragma unroll 2
+    for (int st = 0; st < (1 << s); ++st) {
+      const int n = st * npg + grp;
+      const double* cfn = s_cf + n * (DEG * NCP);
+      const longlong2 pp = *reinterpret_cast<const longlong2*>(s_ptr + n * RD);
+      double v[RD][2];
+#pragma unroll
+      for (int a = 0; a < RD; ++a) v[a][0] = v[a][1] = 0.0;
+#pragma unroll
+      for (int k = 0; k < DEG; ++k) {                        // ascending cell order
+        if (DEG == 1 || anyk[k]) {
+          double cf[NCP];
+#pragma unroll
+          for (int i = 0; i < NCP / 2; ++i) {
+            const double2 x = *reinterpret_cast<const double2*>(cfn + k * NCP + 2 * i);
+            cf[2 * i] = x.x;
+            cf[2 * i + 1] = x.y;
+          }
+#pragma unroll
+          for (int a = 0; a < RD; ++a) {
+            if constexpr (CD == 2) {
+              double r2[2];
+              pyn::affine_row_K(cf, rec[a][k][0], a, r2);
+              if (on[a][k][0]) {
+                v[a][0] += sign * r2[0];
+                v[a][1] += sign * r2[1];
+              }
+            } else {
+#pragma unroll
+              for (int h = 0; h < NP; ++h) {
+                const double r1 = pyn::affine_row_R(cf, rec[a][k][h], d.which, d.aff.alpha_w, d.aff.alpha_d, a);
+                if (on[a][k][h]) v[a][h] += sign * r1;
+              }
+            }
+          }
+        }
+      }
+      const bool okn = n < cnt;
+#pragma unroll
+      for (int a = 0; a < RD; ++a) {
+        double* o = reinterpret_cast<double*>(a == 0 ? pp.x : pp.y) + off;
+        const bool f = okn && first[a], g2 = okn && second[a];
+        const bool al = f && g2 && (reinterpret_cast<uintptr_t>(o) & 15) == 0;
+        sig_store(o, v[a][0], v[a][1], al, f && !al, g2 && !al);
+      }
+    }
+#pragma unroll
+    for (int a = 0; a < RD; ++a)
+#pragma unroll
+      for (int k = 0; k < DEG; ++k)
+#pragma unroll
+        for (int h = 0; h < NP; ++h) {
+          l0[a][k][h] = l1[a][k][h];
+          l1[a][k][h] = l2[a][k][h];
+        }
+    load_rec(l0, rec);
     pu = pu1;
   }
 }
@@ -1075,22 +1293,31 @@ static int launch_interior(const pyn_topo* t, const DescView& dv, const int64_t*
   if (dv.coef && !indices && data && dv.tile_desc) {   // structured mesh, values only: signature-grouped kernel
     PYN_REQUIRE(tv.nn == dv.aff.n * dv.aff.n, "affine assembly: element handle of another order");
     int64_t c0 = 0;
-#define PYN_SIG_CASE(C, DG, cls)                                                                                        \
+#define PYN_SIG_CASE(C, DG, cls, KERNEL, SHAPE)                                                                         \
     if (dv.cdof == C && dv.tile_class_end[cls] > c0) {                                                                  \
       const int64_t c1 = dv.tile_class_end[cls], g = (c1 - c0 + SIG_W - 1) / SIG_W;                                    \
-      const size_t dyn = sizeof(double) * (size_t)SIG_W * SigShape<C, DG>::per_warp;                                   \
+      const size_t dyn = sizeof(double) * (size_t)SIG_W * SHAPE<C, DG>::per_warp;                                      \
       PYN_REQUIRE(g < 0x7fffffff, "affine assembly: too many signature tiles");                                        \
-      PYN_CHECK_CUDA(cudaFuncSetAttribute(asm_sig_affine_kernel<C, DG>, cudaFuncAttributeMaxDynamicSharedMemorySize,   \
-                                          (int)dyn));                                                                  \
-      asm_sig_affine_kernel<C, DG><<<(int)g, SIG_W * 32, dyn, st>>>(tv, dv, indptr, data, c0, c1,                      \
-                                                                    dv.tile_slot + dv.tile_slot_base[cls]);            \
+      PYN_CHECK_CUDA(cudaFuncSetAttribute(KERNEL<C, DG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));      \
+      KERNEL<C, DG><<<(int)g, SIG_W * 32, dyn, st>>>(tv, dv, indptr, data, c0, c1,                                     \
+                                                     dv.tile_slot + dv.tile_slot_base[cls]);                           \
       pyn::count_launch();                                                                                             \
     }
-    PYN_SIG_CASE(2, 1, 0) PYN_SIG_CASE(1, 1, 0)
-    c0 = dv.tile_class_end[0];
-    PYN_SIG_CASE(2, 2, 1) PYN_SIG_CASE(1, 2, 1)
+    // valence 1 and 2: line-aligned rows; valence 4 (two record sets of 4 elements do not fit the registers): row-relative
+    static const bool unaligned = getenv("PYN_SIG_UNALIGNED") != nullptr;   // A/B switch
+    if (unaligned) {
+      PYN_SIG_CASE(2, 1, 0, asm_sig_affine_kernel, SigShape) PYN_SIG_CASE(1, 1, 0, asm_sig_affine_kernel, SigShape)
+      c0 = dv.tile_class_end[0];
+      PYN_SIG_CASE(2, 2, 1, asm_sig_affine_kernel, SigShape) PYN_SIG_CASE(1, 2, 1, asm_sig_affine_kernel, SigShape)
+    } else {
+      PYN_SIG_CASE(2, 1, 0, asm_sigrow_affine_kernel, SigRowShape)
+      PYN_SIG_CASE(1, 1, 0, asm_sigrow_affine_kernel, SigRowShape)
+      c0 = dv.tile_class_end[0];
+      PYN_SIG_CASE(2, 2, 1, asm_sigrow_affine_kernel, SigRowShape)
+      PYN_SIG_CASE(1, 2, 1, asm_sigrow_affine_kernel, SigRowShape)
+    }
     c0 = dv.tile_class_end[1];
-    PYN_SIG_CASE(2, 4, 2) PYN_SIG_CASE(1, 4, 2)
+    PYN_SIG_CASE(2, 4, 2, asm_sig_affine_kernel, SigShape) PYN_SIG_CASE(1, 4, 2, asm_sig_affine_kernel, SigShape)
 #undef PYN_SIG_CASE
     const cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
@@ -1217,10 +1444,14 @@ namespace {
 struct NotFlag {
   __host__ __device__ __forceinline__ uint8_t operator()(const uint8_t& f) const { return f ? 0 : 1; }
 };
+// group key of an un-flagged node: its row signature and where its first row starts inside a 128-byte line (in
+// doubles: the rows of a signature have one length, so the second row's offset follows)
 __global__ void sig_keys_kernel(int64_t n, const int* __restrict__ nodes, const int* __restrict__ sig_id,
-                                int* __restrict__ keys, int* __restrict__ counts) {
+                                const int64_t* __restrict__ indptr, int rdof, int* __restrict__ keys,
+                                int* __restrict__ counts) {
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-    const int s = sig_id[nodes[i]];
+    const int j = nodes[i];
+    const int s = sig_id[j] * 16 + (int)(indptr[(int64_t)j * rdof] & 15);
     keys[i] = s;
     atomicAdd(&counts[s], 1);
   }
@@ -1239,7 +1470,8 @@ struct TileClasses {
 };
 __global__ void tile_build_kernel(pyn::TopoView t, int64_t nt, TileClasses tc, const int* __restrict__ tile_sig,
                                   const int* __restrict__ tile_start, const int* __restrict__ tile_cnt,
-                                  const int* __restrict__ sig_nodes, int* __restrict__ desc, int* __restrict__ slot) {
+                                  const int* __restrict__ sig_nodes, const int64_t* __restrict__ indptr,
+                                  int* __restrict__ desc, int* __restrict__ slot) {
   const int lane = threadIdx.x & 31;
   const int64_t w0 = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5, nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
   for (int64_t i = w0; i < nt; i += nw) {
@@ -1254,7 +1486,7 @@ __global__ void tile_build_kernel(pyn::TopoView t, int64_t nt, TileClasses tc, c
     sp[0] = j;
     for (int k = 0; k < sl - 1; ++k) sp[1 + k] = k < dmax ? t.n2e_elem[b0 + (k < dj ? k : 0)] : 0;
     if (lane == 0) {
-      const int rep = t.sig_rep[tile_sig[i]];
+      const int rep = t.sig_rep[tile_sig[i] >> 4];
       const int64_t rb0 = t.n2e_ptr[rep];
       const int deg = (int)(t.n2e_ptr[rep + 1] - rb0);
       unsigned lr = 0;
@@ -1265,20 +1497,27 @@ __global__ void tile_build_kernel(pyn::TopoView t, int64_t nt, TileClasses tc, c
       o[0] = cnt | (deg << 8) | (L << 16);
       o[1] = (int)lr;
       o[2] = (int)(io & 0xffffffffll);
-      o[3] = (int)(io >> 32);
+      const int tau0 = (int)(indptr[(int64_t)j * 2] & 15), tau1 = (int)(indptr[(int64_t)j * 2 + 1] & 15);
+      o[3] = (int)((io >> 32) & 0xffffff) | (tau0 << 24) | (tau1 << 28);   // (inverse maps stay far below 2^56 bytes)
     }
   }
 }
 }  // namespace
 
-static int ensure_sig_tiles(const pyn_topo* t, const pyn_bcmap* mc, cudaStream_t st) {
+static int ensure_sig_tiles(const pyn_topo* t, const pyn_bcmap* mc, const int64_t* indptr, cudaStream_t st) {
   pyn_bcmap* m = const_cast<pyn_bcmap*>(mc);   // cache owned by the handle (one host thread per handle)
-  if (m->tiles_state != 0) return PYN_OK;
+  if (m->tiles_state < 0 || (m->tiles_state == 1 && m->tiles_indptr == indptr)) return PYN_OK;
+  if (m->tiles_state == 1) {   // the tiles follow the row starts of ONE matrix: another one came along with this map
+    cudaFree(m->tile_desc); cudaFree(m->tile_slot);
+    m->tile_desc = m->tile_slot = nullptr;
+  }
+  m->tiles_indptr = indptr;
   m->tiles_state = -1;
   // default on structured meshes; PYN_AFF_NO_SIG=1 keeps the flat kernel (A/B switch, and what the parity test uses to
   // cover both)
   static const bool off = getenv("PYN_AFF_NO_SIG") != nullptr;
-  if (off || t->nsig <= 0 || t->max_valence > SIG_KMAX || t->nn > 255 || (int64_t)t->nn * SIG_KMAX >= 32768)
+  if (off || t->nsig <= 0 || t->max_valence > SIG_KMAX || t->nn > 255 || (int64_t)t->nn * SIG_KMAX >= 32768 ||
+      t->nsig >= (1 << 26))
     return PYN_OK;   // (a row holds at most max_valence * nn column nodes: L fits the descriptor's 15 bits)
   const int64_t n = t->nnodes, nint = t->nnodes - m->nlist;
   if (nint <= 0 || nint >= 0x7fffffff || (int64_t)t->ne * t->nn >= 0x7fffffff) return PYN_OK;
@@ -1290,27 +1529,28 @@ static int ensure_sig_tiles(const pyn_topo* t, const pyn_bcmap* mc, cudaStream_t
   PYN_CHECK_CUDA(cudaMalloc(&m->sig_nodes, sizeof(int) * nint));
   PYN_CHECK_CUDA(cudaMalloc(&keys, sizeof(int) * nint));
   PYN_CHECK_CUDA(cudaMalloc(&keys2, sizeof(int) * nint));
-  PYN_CHECK_CUDA(cudaMalloc(&counts, sizeof(int) * t->nsig));
+  const int ngroups = t->nsig * 16;
+  PYN_CHECK_CUDA(cudaMalloc(&counts, sizeof(int) * ngroups));
   PYN_CHECK_CUDA(cudaMalloc(&d_n, sizeof(int64_t)));
-  PYN_CHECK_CUDA(cudaMemsetAsync(counts, 0, sizeof(int) * t->nsig, st));
+  PYN_CHECK_CUDA(cudaMemsetAsync(counts, 0, sizeof(int) * ngroups, st));
   cub::CountingInputIterator<int> ids(0);
   cub::TransformInputIterator<uint8_t, NotFlag, const uint8_t*> keep(m->flags, NotFlag());
   PYN_CHECK_CUDA(cub::DeviceSelect::Flagged(nullptr, b1, ids, keep, nodes, d_n, n, st));
   int end_bit = 1;
-  while ((1 << end_bit) < t->nsig) ++end_bit;
+  while ((1 << end_bit) < ngroups) ++end_bit;
   PYN_CHECK_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, b2, keys, keys2, nodes, m->sig_nodes, nint, 0, end_bit, st));
   PYN_CHECK_CUDA(cudaMalloc(&tmp, b1 > b2 ? b1 : b2));
   PYN_CHECK_CUDA(cub::DeviceSelect::Flagged(tmp, b1, ids, keep, nodes, d_n, n, st));      // ascending node ids
-  sig_keys_kernel<<<pyn::grid_for(nint, 256), 256, 0, st>>>(nint, nodes, t->sig_id, keys, counts);
+  sig_keys_kernel<<<pyn::grid_for(nint, 256), 256, 0, st>>>(nint, nodes, t->sig_id, indptr, 2, keys, counts);
   PYN_CHECK_CUDA(cub::DeviceRadixSort::SortPairs(tmp, b2, keys, keys2, nodes, m->sig_nodes, nint, 0, end_bit, st));   // stable
   pyn::count_launch(3);
-  std::vector<int> h_counts((size_t)t->nsig);
-  PYN_CHECK_CUDA(cudaMemcpyAsync(h_counts.data(), counts, sizeof(int) * t->nsig, cudaMemcpyDeviceToHost, st));
+  std::vector<int> h_counts((size_t)ngroups);
+  PYN_CHECK_CUDA(cudaMemcpyAsync(h_counts.data(), counts, sizeof(int) * ngroups, cudaMemcpyDeviceToHost, st));
   PYN_CHECK_CUDA(cudaStreamSynchronize(st));
   cudaFree(nodes); cudaFree(keys); cudaFree(keys2); cudaFree(counts); cudaFree(d_n); cudaFree(tmp);
   std::vector<int> ts, tb, tc;
   int64_t off_ = 0;
-  for (int s = 0; s < t->nsig; ++s) {
+  for (int s = 0; s < ngroups; ++s) {
     for (int c = 0; c < h_counts[s]; c += 32) {
       ts.push_back(s); tb.push_back((int)(off_ + c)); tc.push_back(h_counts[s] - c < 32 ? h_counts[s] - c : 32);
     }
@@ -1371,8 +1611,8 @@ static int ensure_sig_tiles(const pyn_topo* t, const pyn_bcmap* mc, cudaStream_t
   PYN_CHECK_CUDA(cudaMalloc(&m->tile_desc, sizeof(int) * 4 * ts.size()));
   PYN_CHECK_CUDA(cudaMalloc(&m->tile_slot, sizeof(int) * (slot_ints > 0 ? slot_ints : 1)));
   tile_build_kernel<<<pyn::grid_for((int64_t)ts.size() * 32, 256), 256, 0, st>>>(
-      pyn::view_of(t), (int64_t)ts.size(), tcl, m->tile_sig, m->tile_start, m->tile_cnt, m->sig_nodes, m->tile_desc,
-      m->tile_slot);
+      pyn::view_of(t), (int64_t)ts.size(), tcl, m->tile_sig, m->tile_start, m->tile_cnt, m->sig_nodes, indptr,
+      m->tile_desc, m->tile_slot);
   PYN_CHECK_LAUNCH();
   PYN_CHECK_CUDA(cudaStreamSynchronize(st));
   cudaFree(m->sig_nodes); cudaFree(m->tile_sig); cudaFree(m->tile_start); cudaFree(m->tile_cnt);
@@ -1521,8 +1761,8 @@ int pyn_asm_fill(const pyn_topo* t, const pyn_asm_desc* desc, const int64_t* d_i
         rc = fork_boundary(t, dv, desc->bcmap->list, desc->bcmap->nlist, d_indptr, d_data, st);
         if (rc) return rc;
       }
-      if (dv.coef && d_data && !d_indices) {   // structured mesh: the signature-grouped fused kernel
-        rc = ensure_sig_tiles(t, desc->bcmap, st);
+      if (dv.coef && d_data && !d_indices && dv.rdof == 2) {   // structured mesh: the signature-grouped fused kernel
+        rc = ensure_sig_tiles(t, desc->bcmap, d_indptr, st);
         if (rc) return rc;
         if (desc->bcmap->tiles_state == 1) {
           dv.tile_desc = desc->bcmap->tile_desc; dv.tile_slot = desc->bcmap->tile_slot; dv.ntiles = desc->bcmap->ntiles;

@@ -137,4 +137,43 @@ __device__ __forceinline__ void affine_block_R(const double* __restrict__ cf, co
   }
 }
 
+// Row a of the same blocks, entry by entry the same operations as affine_block_K / affine_block_R (same bits): the
+// signature-tile assembly evaluates the two rows of a node at DIFFERENT column positions when it aligns its stores.
+__device__ __forceinline__ void affine_row_K(const double* __restrict__ cf, const double* __restrict__ pr, int a,
+                                             double (&v)[2]) {
+  double gr = aff_mul(cf[0], pr[0]);
+  gr = aff_fma(cf[1], pr[1], gr);
+  gr = aff_fma(cf[2], pr[2], gr);
+  const double sm = pr[3], c1 = pr[4], c2 = pr[5], ms = pr[6];
+  const double cs = __dadd_rn(c1, c2);
+  if (a == 0) {
+    double kuu = aff_mul(cf[3], sm);
+    kuu = aff_fma(cf[4], cs, kuu);
+    kuu = aff_fma(cf[5], ms, kuu);
+    double kuv = aff_mul(cf[9], sm);
+    kuv = __dadd_rn(kuv, __dadd_rn(aff_mul(cf[10], c1), aff_mul(cf[11], c2)));
+    kuv = aff_fma(cf[12], ms, kuv);
+    v[0] = __dadd_rn(gr, kuu);
+    v[1] = kuv;
+  } else {
+    double kvv = aff_mul(cf[6], sm);
+    kvv = aff_fma(cf[7], cs, kvv);
+    kvv = aff_fma(cf[8], ms, kvv);
+    double kvu = aff_mul(cf[9], sm);
+    kvu = __dadd_rn(kvu, __dadd_rn(aff_mul(cf[11], c1), aff_mul(cf[10], c2)));
+    kvu = aff_fma(cf[12], ms, kvu);
+    v[0] = kvu;
+    v[1] = __dadd_rn(gr, kvv);
+  }
+}
+__device__ __forceinline__ double affine_row_R(const double* __restrict__ cf, const double* __restrict__ pr, int which,
+                                               double alpha_w, double alpha_d, int a) {
+  // the x pair feeds row 1 of Rw and row 0 of Rd, the y pair the other two
+  const bool usex = (which == 1) == (a == 1);
+  const double c0 = usex ? cf[0] : cf[2], c1 = usex ? cf[1] : cf[3];
+  const double A = aff_fma(c1, pr[1], aff_mul(c0, pr[0])), Cc = aff_fma(c1, pr[3], aff_mul(c0, pr[2]));
+  if (which == 1) return a == 0 ? aff_fma(-alpha_w, Cc, A) : aff_fma(alpha_w, Cc, -A);
+  return aff_fma(alpha_d, Cc, -A);
+}
+
 }  // namespace pyn

@@ -59,6 +59,7 @@ struct pyn_bcmap {
   int64_t tile_slot_base[3];
   int64_t tile_class_end[3];   // tiles are sorted by valence class (1, 2, <= 4 incident elements), then by first node
   int tiles_state;   // 0 not built, 1 built, -1 unavailable
+  const int64_t* tiles_indptr;   // the matrix whose row starts the tiles were grouped by
 };
 
 namespace pyn {
