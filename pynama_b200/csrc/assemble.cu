@@ -37,7 +37,7 @@ struct DescView {
   // signature tiles of the boundary map (structured meshes; NULL: not available)
   const int *tile_desc, *tile_slot;
   int64_t ntiles;
-  int64_t tile_class_end[3], tile_slot_base[3];
+  int64_t tile_class_end[5], tile_slot_base[5];
 };
 
 // element block (rows of local node lr, columns of local node l) of one element from the affine closed form:
@@ -1303,21 +1303,27 @@ static int launch_interior(const pyn_topo* t, const DescView& dv, const int64_t*
                                                      dv.tile_slot + dv.tile_slot_base[cls]);                           \
       pyn::count_launch();                                                                                             \
     }
-    // valence 1 and 2: line-aligned rows; valence 4 (two record sets of 4 elements do not fit the registers): row-relative
-    static const bool unaligned = getenv("PYN_SIG_UNALIGNED") != nullptr;   // A/B switch
+    // classes 0 / 2 / 4: valence 1 / 2 / <= 4, row-relative pieces; 1 / 3: valence 1 / 2 with line-aligned rows
+    static const bool unaligned = getenv("PYN_SIG_UNALIGNED") != nullptr;   // A/B switch: row-relative pieces everywhere
+    PYN_SIG_CASE(2, 1, 0, asm_sig_affine_kernel, SigShape) PYN_SIG_CASE(1, 1, 0, asm_sig_affine_kernel, SigShape)
+    c0 = dv.tile_class_end[0];
     if (unaligned) {
-      PYN_SIG_CASE(2, 1, 0, asm_sig_affine_kernel, SigShape) PYN_SIG_CASE(1, 1, 0, asm_sig_affine_kernel, SigShape)
-      c0 = dv.tile_class_end[0];
-      PYN_SIG_CASE(2, 2, 1, asm_sig_affine_kernel, SigShape) PYN_SIG_CASE(1, 2, 1, asm_sig_affine_kernel, SigShape)
+      PYN_SIG_CASE(2, 1, 1, asm_sig_affine_kernel, SigShape) PYN_SIG_CASE(1, 1, 1, asm_sig_affine_kernel, SigShape)
     } else {
-      PYN_SIG_CASE(2, 1, 0, asm_sigrow_affine_kernel, SigRowShape)
-      PYN_SIG_CASE(1, 1, 0, asm_sigrow_affine_kernel, SigRowShape)
-      c0 = dv.tile_class_end[0];
-      PYN_SIG_CASE(2, 2, 1, asm_sigrow_affine_kernel, SigRowShape)
-      PYN_SIG_CASE(1, 2, 1, asm_sigrow_affine_kernel, SigRowShape)
+      PYN_SIG_CASE(2, 1, 1, asm_sigrow_affine_kernel, SigRowShape)
+      PYN_SIG_CASE(1, 1, 1, asm_sigrow_affine_kernel, SigRowShape)
     }
     c0 = dv.tile_class_end[1];
-    PYN_SIG_CASE(2, 4, 2, asm_sig_affine_kernel, SigShape) PYN_SIG_CASE(1, 4, 2, asm_sig_affine_kernel, SigShape)
+    PYN_SIG_CASE(2, 2, 2, asm_sig_affine_kernel, SigShape) PYN_SIG_CASE(1, 2, 2, asm_sig_affine_kernel, SigShape)
+    c0 = dv.tile_class_end[2];
+    if (unaligned) {
+      PYN_SIG_CASE(2, 2, 3, asm_sig_affine_kernel, SigShape) PYN_SIG_CASE(1, 2, 3, asm_sig_affine_kernel, SigShape)
+    } else {
+      PYN_SIG_CASE(2, 2, 3, asm_sigrow_affine_kernel, SigRowShape)
+      PYN_SIG_CASE(1, 2, 3, asm_sigrow_affine_kernel, SigRowShape)
+    }
+    c0 = dv.tile_class_end[3];
+    PYN_SIG_CASE(2, 4, 4, asm_sig_affine_kernel, SigShape) PYN_SIG_CASE(1, 4, 4, asm_sig_affine_kernel, SigShape)
 #undef PYN_SIG_CASE
     const cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
@@ -1444,30 +1450,43 @@ namespace {
 struct NotFlag {
   __host__ __device__ __forceinline__ uint8_t operator()(const uint8_t& f) const { return f ? 0 : 1; }
 };
+constexpr int SIG_CLASSES = 5;   // 2 * valence index + aligned; valence 4 (index 2) has no aligned variant
+struct TileClasses {
+  int64_t end[SIG_CLASSES];    // tiles of class c: [end[c-1], end[c])
+  int64_t base[SIG_CLASSES];   // first int of the class in the slot table
+};
+__host__ __device__ inline int sig_valence_index(int cls) { return cls >> 1; }
+// A tile takes the line-aligned kernel when its rows are long enough for the extra work to pay (measured: from 25 column
+// nodes on) and hold an ODD number of column nodes: then every second row of a 2x2-block matrix starts 16 bytes into a
+// sector and every second row of a 2x1-block matrix on an odd double (scalar stores).  Rows with an even number of
+// column nodes lose with it (ngl 6, Rw: 1.42 -> 1.63 ms).
+__host__ __device__ inline bool sig_wants_alignment(int deg, int L, int /*cdof*/) {
+  return deg <= 2 && L >= 25 && (L & 1) != 0;
+}
 // group key of an un-flagged node: its row signature and where its first row starts inside a 128-byte line (in
 // doubles: the rows of a signature have one length, so the second row's offset follows)
-__global__ void sig_keys_kernel(int64_t n, const int* __restrict__ nodes, const int* __restrict__ sig_id,
-                                const int64_t* __restrict__ indptr, int rdof, int* __restrict__ keys,
+__global__ void sig_keys_kernel(pyn::TopoView t, int64_t n, const int* __restrict__ nodes,
+                                const int64_t* __restrict__ indptr, int rdof, int cdof, int* __restrict__ keys,
                                 int* __restrict__ counts) {
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     const int j = nodes[i];
-    const int s = sig_id[j] * 16 + (int)(indptr[(int64_t)j * rdof] & 15);
+    const int deg = (int)(t.n2e_ptr[j + 1] - t.n2e_ptr[j]), L = (int)(t.adj_ptr[j + 1] - t.adj_ptr[j]);
+    const int cls = sig_wants_alignment(deg, L, cdof) ? (int)(indptr[(int64_t)j * rdof] & 15) : 0;
+    const int s = t.sig_id[j] * 16 + cls;
     keys[i] = s;
     atomicAdd(&counts[s], 1);
   }
 }
-__global__ void tile_first_kernel(int64_t nt, const int* __restrict__ start, const int* __restrict__ sig_nodes,
-                                  const int64_t* __restrict__ n2e_ptr, int* __restrict__ first, int* __restrict__ deg) {
+__global__ void tile_first_kernel(pyn::TopoView t, int64_t nt, const int* __restrict__ start,
+                                  const int* __restrict__ sig_nodes, int* __restrict__ first, int* __restrict__ deg,
+                                  int* __restrict__ len) {
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < nt; i += (int64_t)gridDim.x * blockDim.x) {
     const int j = sig_nodes[start[i]];
     first[i] = j;
-    deg[i] = (int)(n2e_ptr[j + 1] - n2e_ptr[j]);
+    deg[i] = (int)(t.n2e_ptr[j + 1] - t.n2e_ptr[j]);
+    len[i] = (int)(t.adj_ptr[j + 1] - t.adj_ptr[j]);
   }
 }
-struct TileClasses {
-  int64_t end[3];    // tiles of valence class c: [end[c-1], end[c])
-  int64_t base[3];   // first int of the class in the slot table
-};
 __global__ void tile_build_kernel(pyn::TopoView t, int64_t nt, TileClasses tc, const int* __restrict__ tile_sig,
                                   const int* __restrict__ tile_start, const int* __restrict__ tile_cnt,
                                   const int* __restrict__ sig_nodes, const int64_t* __restrict__ indptr,
@@ -1475,8 +1494,10 @@ __global__ void tile_build_kernel(pyn::TopoView t, int64_t nt, TileClasses tc, c
   const int lane = threadIdx.x & 31;
   const int64_t w0 = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5, nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
   for (int64_t i = w0; i < nt; i += nw) {
-    const int cls = i < tc.end[0] ? 0 : (i < tc.end[1] ? 1 : 2);
-    const int sl = 2 << cls, dmax = cls == 2 ? 4 : cls + 1;          // ints per slot, elements per node of the class
+    int cls = 0;
+    while (cls < SIG_CLASSES - 1 && i >= tc.end[cls]) ++cls;
+    const int vi = sig_valence_index(cls);
+    const int sl = 2 << vi, dmax = vi == 2 ? 4 : vi + 1;             // ints per slot, elements per node of the class
     const int64_t c0 = cls == 0 ? 0 : tc.end[cls - 1];
     const int start = tile_start[i], cnt = tile_cnt[i];
     const int j = sig_nodes[start + (lane < cnt ? lane : 0)];
@@ -1504,7 +1525,7 @@ __global__ void tile_build_kernel(pyn::TopoView t, int64_t nt, TileClasses tc, c
 }
 }  // namespace
 
-static int ensure_sig_tiles(const pyn_topo* t, const pyn_bcmap* mc, const int64_t* indptr, cudaStream_t st) {
+static int ensure_sig_tiles(const pyn_topo* t, const pyn_bcmap* mc, const int64_t* indptr, int cdof, cudaStream_t st) {
   pyn_bcmap* m = const_cast<pyn_bcmap*>(mc);   // cache owned by the handle (one host thread per handle)
   if (m->tiles_state < 0 || (m->tiles_state == 1 && m->tiles_indptr == indptr)) return PYN_OK;
   if (m->tiles_state == 1) {   // the tiles follow the row starts of ONE matrix: another one came along with this map
@@ -1541,7 +1562,7 @@ static int ensure_sig_tiles(const pyn_topo* t, const pyn_bcmap* mc, const int64_
   PYN_CHECK_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, b2, keys, keys2, nodes, m->sig_nodes, nint, 0, end_bit, st));
   PYN_CHECK_CUDA(cudaMalloc(&tmp, b1 > b2 ? b1 : b2));
   PYN_CHECK_CUDA(cub::DeviceSelect::Flagged(tmp, b1, ids, keep, nodes, d_n, n, st));      // ascending node ids
-  sig_keys_kernel<<<pyn::grid_for(nint, 256), 256, 0, st>>>(nint, nodes, t->sig_id, indptr, 2, keys, counts);
+  sig_keys_kernel<<<pyn::grid_for(nint, 256), 256, 0, st>>>(pyn::view_of(t), nint, nodes, indptr, 2, cdof, keys, counts);
   PYN_CHECK_CUDA(cub::DeviceRadixSort::SortPairs(tmp, b2, keys, keys2, nodes, m->sig_nodes, nint, 0, end_bit, st));   // stable
   pyn::count_launch(3);
   std::vector<int> h_counts((size_t)ngroups);
@@ -1560,36 +1581,39 @@ static int ensure_sig_tiles(const pyn_topo* t, const pyn_bcmap* mc, const int64_
   {  // order of execution: valence class (one launch each), then first node -- tiles that write neighbouring rows run
      // at about the same time, so the partial lines of a row meet in L2
     const size_t nt = ts.size();
-    int *d_start = nullptr, *d_first = nullptr, *d_deg = nullptr;
+    int *d_start = nullptr, *d_first = nullptr, *d_deg = nullptr, *d_len = nullptr;
     PYN_CHECK_CUDA(cudaMalloc(&d_start, sizeof(int) * nt));
     PYN_CHECK_CUDA(cudaMalloc(&d_first, sizeof(int) * nt));
     PYN_CHECK_CUDA(cudaMalloc(&d_deg, sizeof(int) * nt));
+    PYN_CHECK_CUDA(cudaMalloc(&d_len, sizeof(int) * nt));
     PYN_CHECK_CUDA(cudaMemcpyAsync(d_start, tb.data(), sizeof(int) * nt, cudaMemcpyHostToDevice, st));
-    tile_first_kernel<<<pyn::grid_for((int64_t)nt, 256), 256, 0, st>>>((int64_t)nt, d_start, m->sig_nodes, t->n2e_ptr,
-                                                                        d_first, d_deg);
+    tile_first_kernel<<<pyn::grid_for((int64_t)nt, 256), 256, 0, st>>>(pyn::view_of(t), (int64_t)nt, d_start, m->sig_nodes,
+                                                                        d_first, d_deg, d_len);
     pyn::count_launch();
-    std::vector<int> first(nt), dg(nt);
+    std::vector<int> first(nt), dg(nt), ln(nt);
     PYN_CHECK_CUDA(cudaMemcpyAsync(first.data(), d_first, sizeof(int) * nt, cudaMemcpyDeviceToHost, st));
     PYN_CHECK_CUDA(cudaMemcpyAsync(dg.data(), d_deg, sizeof(int) * nt, cudaMemcpyDeviceToHost, st));
+    PYN_CHECK_CUDA(cudaMemcpyAsync(ln.data(), d_len, sizeof(int) * nt, cudaMemcpyDeviceToHost, st));
     PYN_CHECK_CUDA(cudaStreamSynchronize(st));
-    cudaFree(d_start); cudaFree(d_first); cudaFree(d_deg);
+    cudaFree(d_start); cudaFree(d_first); cudaFree(d_deg); cudaFree(d_len);
     std::vector<int64_t> key(nt);
     std::vector<int> order(nt);
     for (size_t i = 0; i < nt; ++i) {
-      const int cls = dg[i] <= 1 ? 0 : (dg[i] == 2 ? 1 : 2);
+      const int vi = dg[i] <= 1 ? 0 : (dg[i] == 2 ? 1 : 2);
+      const int cls = 2 * vi + (sig_wants_alignment(dg[i], ln[i], cdof) ? 1 : 0);
       key[i] = ((int64_t)cls << 40) | (int64_t)first[i];
       order[i] = (int)i;
     }
     std::sort(order.begin(), order.end(), [&](int a, int b) { return key[a] < key[b]; });
     std::vector<int> ts2(nt), tb2(nt), tc2(nt);
-    m->tile_class_end[0] = m->tile_class_end[1] = m->tile_class_end[2] = 0;
+    for (int c = 0; c < SIG_CLASSES; ++c) m->tile_class_end[c] = 0;
     for (size_t i = 0; i < nt; ++i) {
       const int o = order[i];
       ts2[i] = ts[o]; tb2[i] = tb[o]; tc2[i] = tc[o];
       m->tile_class_end[key[o] >> 40] = (int64_t)i + 1;
     }
-    if (m->tile_class_end[1] < m->tile_class_end[0]) m->tile_class_end[1] = m->tile_class_end[0];
-    if (m->tile_class_end[2] < m->tile_class_end[1]) m->tile_class_end[2] = m->tile_class_end[1];
+    for (int c = 1; c < SIG_CLASSES; ++c)
+      if (m->tile_class_end[c] < m->tile_class_end[c - 1]) m->tile_class_end[c] = m->tile_class_end[c - 1];
     ts.swap(ts2); tb.swap(tb2); tc.swap(tc2);
   }
   m->ntiles = (int64_t)ts.size();
@@ -1601,13 +1625,12 @@ static int ensure_sig_tiles(const pyn_topo* t, const pyn_bcmap* mc, const int64_
   PYN_CHECK_CUDA(cudaMemcpyAsync(m->tile_cnt, tc.data(), sizeof(int) * ts.size(), cudaMemcpyHostToDevice, st));
   PYN_CHECK_CUDA(cudaStreamSynchronize(st));
   TileClasses tcl;
-  for (int c = 0; c < 3; ++c) {
+  int64_t slot_ints = 0;
+  for (int c = 0; c < SIG_CLASSES; ++c) {
     tcl.end[c] = m->tile_class_end[c];
-    const int64_t before = c == 0 ? 0 : tcl.end[c - 1] - (c == 1 ? 0 : tcl.end[c - 2]);
-    tcl.base[c] = c == 0 ? 0 : tcl.base[c - 1] + before * 32 * (2 << (c - 1));
-    m->tile_slot_base[c] = tcl.base[c];
+    tcl.base[c] = m->tile_slot_base[c] = slot_ints;
+    slot_ints += (tcl.end[c] - (c ? tcl.end[c - 1] : 0)) * 32 * (2 << sig_valence_index(c));
   }
-  const int64_t slot_ints = tcl.base[2] + (tcl.end[2] - tcl.end[1]) * 32 * 8;
   PYN_CHECK_CUDA(cudaMalloc(&m->tile_desc, sizeof(int) * 4 * ts.size()));
   PYN_CHECK_CUDA(cudaMalloc(&m->tile_slot, sizeof(int) * (slot_ints > 0 ? slot_ints : 1)));
   tile_build_kernel<<<pyn::grid_for((int64_t)ts.size() * 32, 256), 256, 0, st>>>(
@@ -1762,11 +1785,11 @@ int pyn_asm_fill(const pyn_topo* t, const pyn_asm_desc* desc, const int64_t* d_i
         if (rc) return rc;
       }
       if (dv.coef && d_data && !d_indices && dv.rdof == 2) {   // structured mesh: the signature-grouped fused kernel
-        rc = ensure_sig_tiles(t, desc->bcmap, d_indptr, st);
+        rc = ensure_sig_tiles(t, desc->bcmap, d_indptr, dv.cdof, st);
         if (rc) return rc;
         if (desc->bcmap->tiles_state == 1) {
           dv.tile_desc = desc->bcmap->tile_desc; dv.tile_slot = desc->bcmap->tile_slot; dv.ntiles = desc->bcmap->ntiles;
-          for (int c = 0; c < 3; ++c) {
+          for (int c = 0; c < SIG_CLASSES; ++c) {
             dv.tile_class_end[c] = desc->bcmap->tile_class_end[c];
             dv.tile_slot_base[c] = desc->bcmap->tile_slot_base[c];
           }

@@ -56,8 +56,10 @@ struct pyn_bcmap {
   int* tile_desc;
   int* tile_slot;
   int64_t ntiles;
-  int64_t tile_slot_base[3];
-  int64_t tile_class_end[3];   // tiles are sorted by valence class (1, 2, <= 4 incident elements), then by first node
+  // tiles are sorted by class, then by first node.  Class = 2 * valence index (1, 2, <= 4 incident elements) + 1 when the
+  // tile takes the line-aligned kernel (rows long enough and not whole sectors; never for valence 4): PYN_SIG_CLASSES = 5
+  int64_t tile_slot_base[5];
+  int64_t tile_class_end[5];
   int tiles_state;   // 0 not built, 1 built, -1 unavailable
   const int64_t* tiles_indptr;   // the matrix whose row starts the tiles were grouped by
 };
