@@ -42,6 +42,8 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-time-loop", action="store_true", dest="no_time_loop")
+    ap.add_argument("--no-percell", action="store_true", dest="no_percell",
+                    help="skip the per-cell record (configs[2] at the headline order) of the default single-GPU line")
     ap.add_argument("--no-configs4", action="store_true", dest="no_configs4",
                     help="N >= 4: skip the second record on BASELINE configs[4] (4096^2, ngl 4)")
     ap.add_argument("--workload", default="cavity", choices=["cavity", "percell"],
@@ -385,6 +387,14 @@ def run_native(a):
             out["configs4"] = largest_mesh_record(a, be, torch, world, barrier, peak)
         except Exception as e:      # e.g. not enough memory on this box: say so, keep the configs[3] line
             out["configs4"] = {"unavailable": f"{type(e).__name__}: {e}"[:300]}
+    if world == 1 and a.nx == 1024 and not a.no_percell:
+        # the per-cell path (BASELINE configs[1]/[2]) as a second record inside the one JSON line
+        prob = None
+        torch.cuda.empty_cache()
+        try:
+            out["percell"] = percell_record(a, torch)
+        except Exception as e:
+            out["percell"] = {"unavailable": f"{type(e).__name__}: {e}"[:300]}
     if rank == 0:
         print(json.dumps(out), flush=True)
     if world > 1:
@@ -526,7 +536,7 @@ def elem_flops(n):
     return step1 + step2_k + step2_r
 
 
-def run_percell(a):
+def run_percell(a, emit=True):
     """One step = integrate K_e, Rw_e of every cell from its corner coordinates + assemble K, Krhs, Rw (values on the
     prebuilt pattern) through the reference's case class (CustomFuncCase -> FreeSlip.buildKLEMats)."""
     import torch
@@ -615,7 +625,22 @@ def run_percell(a):
                      "traffic": None},
         "gpu_launches": int(launches), "clocks": clocks,
     }
-    print(json.dumps(out), flush=True)
+    if emit:
+        print(json.dumps(out), flush=True)
+    return out
+
+
+def percell_record(a, torch):
+    """BASELINE configs[2] at the order of the headline case riding along in the default line: the per-cell path
+    (FreeSlip.buildKLEMats, every cell integrated) at ~16 M velocity dofs, compressed to its timings and roofline."""
+    import copy
+    b = copy.copy(a)
+    b.nx, b.steps, b.warmup, b.fused = round(2828 / (a.ngl - 1)), 5, 3, None
+    r = run_percell(b, emit=False)
+    return {"workload": r["config"]["workload"], "dof_rows": r["config"]["dof_rows"], "cells": r["config"]["cells"],
+            "nnz_K": r["config"]["nnz"]["K"], "fused_integrate_assemble": r["config"]["fused_integrate_assemble"],
+            "value": r["value"], "unit": r["unit"], "ms_per_step": r["ms_per_step"], "steps": r["steps"],
+            "phases_ms": r["phases_ms"], "roofline": r["roofline"], "gpu_launches": r["gpu_launches"]}
 
 
 def parity_checks(prob, be, torch, world, nx, ngl, dof_total):
