@@ -292,18 +292,33 @@ elem_ops_kernel(pyn_elem E, const double* __restrict__ coords, int64_t ne, doubl
 }
 
 // ---- affine elements: closed form (elem_affine.cuh) ---------------------------------------------------------------
-__global__ void __launch_bounds__(256)
+// One thread per element; corners in and coefficients out go through shared memory so that both global streams are
+// coalesced (64 B and 144 B per element: read and written directly they touch a sector per lane and instruction).
+constexpr int AFC_T = 128;                   // elements (= threads) per CTA
+constexpr int AFC_SI = 9, AFC_SO = PYN_AFF_NCOEF + 1;   // padded strides: 2-way bank conflicts at most
+__global__ void __launch_bounds__(AFC_T)
 elem_affine_coef_kernel(int64_t ne, const double* __restrict__ coords, double aw, double ad, double* __restrict__ coef,
                         unsigned long long* __restrict__ nonaffine) {
-  const int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  if (e >= ne) return;
-  double c[8], out[PYN_AFF_NCOEF];
+  __shared__ double s_in[AFC_T * AFC_SI], s_out[AFC_T * AFC_SO];
+  const int tid = threadIdx.x;
+  const int64_t e0 = blockIdx.x * (int64_t)AFC_T;
+  const int nb = (int)min((int64_t)AFC_T, ne - e0);
+  for (int i = tid; i < nb * 8; i += AFC_T) s_in[(i >> 3) * AFC_SI + (i & 7)] = coords[e0 * 8 + i];
+  __syncthreads();
+  if (tid < nb) {
+    double c[8], out[PYN_AFF_NCOEF];
 #pragma unroll
-  for (int k = 0; k < 8; ++k) c[k] = coords[e * 8 + k];
-  const bool ok = pyn::affine_coefficients(c, aw, ad, out);
+    for (int k = 0; k < 8; ++k) c[k] = s_in[tid * AFC_SI + k];
+    const bool ok = pyn::affine_coefficients(c, aw, ad, out);
 #pragma unroll
-  for (int k = 0; k < PYN_AFF_NCOEF; ++k) coef[e * PYN_AFF_NCOEF + k] = out[k];
-  if (!ok) atomicAdd(nonaffine, 1ull);
+    for (int k = 0; k < PYN_AFF_NCOEF; ++k) s_out[tid * AFC_SO + k] = out[k];
+    if (!ok) atomicAdd(nonaffine, 1ull);
+  }
+  __syncthreads();
+  for (int i = tid; i < nb * PYN_AFF_NCOEF; i += AFC_T) {
+    const int e = i / PYN_AFF_NCOEF;
+    coef[e0 * PYN_AFF_NCOEF + i] = s_out[e * AFC_SO + (i - e * PYN_AFF_NCOEF)];
+  }
 }
 
 // product records of every local node pair (once per element order)
@@ -499,8 +514,8 @@ int pyn_elem_affine_coef(const pyn_elem* e, const double* d_coords, int64_t ne, 
   if (h_nonaffine) *h_nonaffine = 0;
   if (ne == 0) return PYN_OK;
   PYN_CHECK_CUDA(cudaMemsetAsync(e->d_count, 0, sizeof(unsigned long long), st));
-  elem_affine_coef_kernel<<<(unsigned)((ne + 255) / 256), 256, 0, st>>>(ne, d_coords, e->alpha_w, e->alpha_d, d_coef,
-                                                                          e->d_count);
+  elem_affine_coef_kernel<<<(unsigned)((ne + AFC_T - 1) / AFC_T), AFC_T, 0, st>>>(ne, d_coords, e->alpha_w, e->alpha_d,
+                                                                                    d_coef, e->d_count);
   PYN_CHECK_LAUNCH();
   if (h_nonaffine) {   // the caller decides the path from this count: one scalar read-back
     unsigned long long c = 0;
