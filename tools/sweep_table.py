@@ -48,9 +48,9 @@ quads the integration therefore dominates the per-cell step 5-10x at every order
 cells removes the contraction and the element matrices altogether: the step becomes the CSR store stream plus the
 evaluation of the entries from 13 coefficients and a 64-byte product record per 2x2 block.  The slot-flat kernel pays
 ~350 instructions per 32 blocks for look-ups and is issue-bound at 0.1-0.3 of the HBM roofline; the signature-tile
-kernels (`r02_ncu_fused_assembly.md`) bring that to 80-120 and reach **0.48-0.74** for ngl >= 4: 0.49 / 0.68 / 0.74 at
+kernels (`r02_ncu_fused_assembly.md`) bring that to 80-120 and reach **0.48-0.75** for ngl >= 4: 0.51 / 0.68 / 0.75 at
 ngl 4 / 6 / 8, whose rows are whole 32-byte sectors or 128-byte lines, and 0.48 / 0.58 / 0.57 at ngl 5 / 7 / 9, where
 every second row starts mid-sector and the line-aligned variant of the kernel is used (0.44 / 0.51 / 0.49 without
-it); lowest for the short rows of ngl 2-3 (9-25 column nodes: the per-tile set-up is not amortised).  Its cost per
+it); lowest for the short rows of ngl 2-3 (0.19 / 0.30; 9-25 column nodes: the per-tile set-up is not amortised).  Its cost per
 stored entry is flat in ngl, so this path has no crossover: it is a store
 stream at every order.""")
