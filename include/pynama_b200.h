@@ -234,6 +234,24 @@ int64_t pyn_tmat_bytes(const pyn_tmat* m);
 int pyn_tmat_supported(int nn, int rdof, int cdof);
 
 /* ------------------------------------------------------------------------------------------------------
+ * Immersed-boundary coupling (ImmersedBoundaryStatic / Dynamic, src/cases/immersed_boundary.py)
+ * ------------------------------------------------------------------------------------------------------
+ * pyn_ibm_collect replaces collectNodes + computeClose + computeDirac (immersed_boundary.py:258-277, 318-338 and, for
+ * mode 1, :391-402): for every Lagrangian node (d_lagxy [nlag][2]) the candidate Euler nodes (d_cand, ascending ids into
+ * d_nodexy [nnodes][2]) that are "close" -- mode 0: |dx / dl| < 3 and |dy / dl| < 3; mode 1: |dx / dl| < 2 and
+ * |dy| < 1 + 2 dl -- with the discrete delta value prod_r phi(|r| / h) / h (immersed_body.py:259-264; delta_kind 0
+ * fourGrid, 1 threeGrid, 2 linear, :398-421).  Two passes: d_ptr == NULL writes the counts [nlag] into
+ * d_count_or_nodes; with the prefix sums d_ptr [nlag + 1] it writes the node ids and delta values (ascending node id).
+ * pyn_ibm_gram replaces H.matMult(S) of buildIBMMatrix (:246): the Lagrangian system matrix for one velocity
+ * component, entry (i, j) = sum over the common Euler nodes e, ascending, of (d_i(e) a)(d_j(e) b) with a = h^2 and
+ * b = dl h the scale factors of H and S (:243-245); same two-pass protocol (counts [nlag], then columns j and values). */
+int pyn_ibm_collect(int64_t nlag, const double* d_lagxy, int64_t ncand, const int32_t* d_cand, const double* d_nodexy,
+                    double dl, double h, int mode, int delta_kind, const int64_t* d_ptr, int32_t* d_count_or_nodes,
+                    double* d_dirac, void* stream);
+int pyn_ibm_gram(int64_t nlag, const int64_t* d_ptr, const int32_t* d_nodes, const double* d_dirac, double a, double b,
+                 const int64_t* d_aptr, int32_t* d_count_or_cols, double* d_avals, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------
  * Vectors (PETSc Vec calls of the path: base_problem.py:222-230,234-252; cavity.py:53-81; custom_func.py:76-83)
  * ---------------------------------------------------------------------------------------------------- */
 int pyn_vec_set(int64_t n, double a, double* d_x, void* stream);

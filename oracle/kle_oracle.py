@@ -1055,3 +1055,137 @@ def ksp_gmres(A, b, rtol=1e-5, atol=1e-50, dtol=1e4, max_it=10000, restart=30, j
         for i in range(k):
             x = x + y[i] * V[i]
     return x, its, reason, hist
+
+
+# ======================================================================================================================
+# Immersed-boundary velocity correction.  PARITY UNPINNED: the reference's immersed_boundary.py and
+# immersed_body.py import petsc4py / DMPlex and have no tests; what follows restates their arithmetic line by line and is
+# pinned only through the properties of the discrete delta functions (tests/test_host_logic.py).
+# ======================================================================================================================
+def ibm_phi(kind, r):
+    """Discrete delta functions of src/domain/immersed_body.py:398-421: 'four' (fourGrid, the default of
+    ImmersedBody.__init__, :136), 'three' (threeGrid), 'linear'.  r = |distance| / h."""
+    if kind == "four":
+        if r <= 1:
+            return (3 - 2 * r + math.sqrt(1 + 4 * r - 4 * r ** 2)) / 8
+        elif r <= 2:
+            return (5 - 2 * r - math.sqrt(-7 + 12 * r - 4 * r ** 2)) / 8
+        return 0.0
+    if kind == "three":
+        if r <= 0.5:
+            return (1 + math.sqrt(-3 * r ** 2 + 1)) / 3
+        elif r <= 1.5:
+            return (5 - 3 * r - math.sqrt(-3 * (1 - r) ** 2 + 1)) / 6
+        return 0.0
+    if kind == "linear":
+        return (1 - r) if r < 1 else 0.0
+    raise ValueError(kind)
+
+
+def ibm_dirac(kind, dist, h):
+    """ImmersedBody.getDiracs (immersed_body.py:259-264): per direction multiply by phi, then divide by h."""
+    d = 1.0
+    for r in dist:
+        d *= ibm_phi(kind, abs(r) / h)
+        d /= h
+    return d
+
+
+def ibm_close(mode, dist, dl):
+    """computeClose of the static (immersed_boundary.py:325-336, mode 0) and dynamic (:391-402, mode 1) cases."""
+    ex, ey = dist[0] / dl, dist[1] / dl
+    if mode == 0:
+        return abs(ex) < 3 and abs(ey) < 3
+    return abs(ex) < 2 and abs(ey * dl) < (1 + 2 * dl)
+
+
+def ibm_circle(radius, h, center=(0.0, 0.0)):
+    """Circle.generateBody (immersed_body.py:371-389) + the centre displacement of getNodeCoordinates (:240-243):
+    ((npoints, 2) coordinates, dl)."""
+    long_total = 2 * math.pi * radius
+    points = math.ceil(long_total / h)
+    start = math.pi / 1000
+    angles = np.linspace(0, 2 * math.pi, points, endpoint=False)
+    xy = np.stack([radius * np.cos(angles + start), radius * np.sin(angles + start)], 1)
+    dl = 2 * math.pi * radius / points
+    return xy + np.asarray(center, dtype=float), dl
+
+
+def ibm_line(dl, length=2.0, center=(0.0, 0.0)):
+    """Line.generateBody (immersed_body.py:294-307)."""
+    div = math.ceil(length / dl)
+    xy = np.stack([np.linspace(0, length, div), np.zeros(div)], 1)
+    return xy + np.asarray(center, dtype=float), dl
+
+
+def ibm_open_box(dl, length=1.0, center=(0.0, 0.0)):
+    """OpenBox.generateBody (immersed_body.py:316-345): the diamond (0,L) -> (-L,0) -> (0,-L) -> (L,0)."""
+    div = math.ceil(math.sqrt(2) / dl)
+    pts = [(0, length), (-length, 0), (0, -length), (length, 0), (0, length)]
+    xs = np.concatenate([np.linspace(pts[i][0], pts[i + 1][0], div, endpoint=False) for i in range(4)])
+    ys = np.concatenate([np.linspace(pts[i][1], pts[i + 1][1], div, endpoint=False) for i in range(4)])
+    return np.stack([xs, ys], 1) + np.asarray(center, dtype=float), dl
+
+
+def ibm_collect(lagxy, cand, nodexy, dl, h, mode=0, kind="four"):
+    """collectNodes + computeDirac (immersed_boundary.py:258-277, 318-323): per Lagrangian node the close Euler nodes
+    (ascending id) and their delta values."""
+    out = []
+    cand = np.asarray(cand)
+    for X in lagxy:
+        nodes, dirac = [], []
+        for e in cand:
+            dist = nodexy[e] - X
+            if ibm_close(mode, dist, dl):
+                nodes.append(int(e))
+                dirac.append(ibm_dirac(kind, dist, h))
+        if not nodes:
+            raise Exception("Lag Node without Euler")
+        out.append((np.array(nodes, dtype=np.int64), np.array(dirac)))
+    return out
+
+
+def ibm_matrices(collected, n_euler_nodes, dl, h, dim=2):
+    """buildIBMMatrix (immersed_boundary.py:222-251): H (2 rows per Lagrangian node, columns 2 per Euler node),
+    S = H^T dl h, H scaled by h^2 afterwards, A = H S.  A is accumulated over the common Euler nodes in ascending
+    order, the order of a sorted-row sparse product."""
+    nlag = len(collected)
+    rows, cols, vals = [], [], []
+    for l, (nodes, dirac) in enumerate(collected):
+        for dof in range(dim):
+            rows += [l * dim + dof] * len(nodes)
+            cols += list(nodes * dim + dof)
+            vals += list(dirac)
+    H0 = sp.csr_matrix((vals, (rows, cols)), shape=(nlag * dim, n_euler_nodes * dim))
+    H0.sort_indices()
+    S = sp.csr_matrix(H0.T)
+    S.sort_indices()
+    S.data = S.data * (dl * h)
+    H = H0.copy()
+    H.data = H.data * (h ** 2)
+    a, b = h ** 2, dl * h
+    ar, ac, av = [], [], []
+    for i, (ni, di) in enumerate(collected):
+        for j, (nj, dj) in enumerate(collected):
+            common, pi, pj = np.intersect1d(ni, nj, assume_unique=True, return_indices=True)
+            if len(common) == 0:
+                continue
+            s = 0.0
+            for p, q in zip(pi, pj):
+                s = s + (di[p] * a) * (dj[q] * b)
+            for dof in range(dim):
+                ar.append(i * dim + dof)
+                ac.append(j * dim + dof)
+                av.append(s)
+    A = sp.csr_matrix((av, (ar, ac)), shape=(nlag * dim, nlag * dim))
+    A.sort_indices()
+    return H, S, A
+
+
+def ibm_velocity_correction(H, S, A, vel, body_vel):
+    """computeVelocityCorrection (immersed_boundary.py:205-211): rhs = H v - V_body; A q = -rhs; v += S q.  Returns
+    (corrected velocity, virtual flux q)."""
+    import scipy.sparse.linalg as spla
+    rhs = H @ vel - body_vel
+    q = spla.spsolve(sp.csc_matrix(A), -rhs)
+    return vel + S @ q, q

@@ -79,6 +79,8 @@ _SIGNATURES = {
     "pyn_spmv_plan_create": (C.c_int, [c_i64, c_vp, c_i64, c_vp, P(c_vp)]),
     "pyn_spmv_plan_destroy": (C.c_int, [c_vp]),
     "pyn_spmv_planned": (C.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, C.c_int, c_f64, c_f64, c_vp, c_vp]),
+    "pyn_ibm_collect": (C.c_int, [c_i64, c_vp, c_i64, c_vp, c_vp, c_f64, c_f64, C.c_int, C.c_int, c_vp, c_vp, c_vp, c_vp]),
+    "pyn_ibm_gram": (C.c_int, [c_i64, c_vp, c_vp, c_vp, c_f64, c_f64, c_vp, c_vp, c_vp, c_vp]),
     "pyn_vec_set": (C.c_int, [c_i64, c_f64, c_vp, c_vp]),
     "pyn_vec_scale": (C.c_int, [c_i64, c_f64, c_vp, c_vp]),
     "pyn_vec_axpy": (C.c_int, [c_i64, c_f64, c_vp, c_vp, c_vp]),

@@ -501,6 +501,58 @@ def coo_to_csr(rows, cols, vals, shape, name=""):
 
 
 # ---------------------------------------------------------------------------------------------------------
+# Immersed-boundary coupling (csrc/ibm.cu; reference src/cases/immersed_boundary.py:222-277, 318-338)
+IBM_DELTA = {"four": 0, "three": 1, "linear": 2}
+
+
+def _two_pass(entry, head, tail, n):
+    """count pass -> prefix sums on device -> fill pass of one of the pyn_ibm_* entry points."""
+    counts = empty(n, I32)
+    call(entry, *head, None, ptr(counts), None, *tail)
+    p = zeros(n + 1, I64)
+    torch.cumsum(counts, 0, out=p[1:])
+    total = int(p[-1])                       # one scalar read-back: the size of the output arrays
+    ids, vals = empty(total, I32), empty(total)
+    call(entry, *head, ptr(p), ptr(ids), ptr(vals), *tail)
+    return p, ids, vals
+
+
+def ibm_collect(lagxy, cand, nodexy, dl, h, mode=0, kind="four"):
+    """Per Lagrangian node the close candidate Euler nodes (ascending) and their delta values:
+    (ptr [nlag+1] int64, nodes int32, dirac f64)."""
+    nlag = lagxy.numel() // 2
+    head = (nlag, ptr(lagxy), int(cand.numel()), ptr(cand), ptr(nodexy), float(dl), float(h), int(mode), IBM_DELTA[kind])
+    return _two_pass("pyn_ibm_collect", head, (stream(),), nlag)
+
+
+def ibm_gram(p, nodes, dirac, a, b):
+    """One velocity component of A = H S: (ptr [nlag+1], partner Lagrangian nodes j, values)."""
+    nlag = p.numel() - 1
+    head = (nlag, ptr(p), ptr(nodes), ptr(dirac), float(a), float(b))
+    return _two_pass("pyn_ibm_gram", head, (stream(),), nlag)
+
+
+def dof_blocked_csr(p, ids, vals, ncols_nodes, dim, name=""):
+    """CSR with `dim` rows per list and the columns ids * dim + dof: row l * dim + dof holds list l on component dof
+    (H of buildIBMMatrix: setValues(lagNode * dim + dof, eulerIndices[dof::dim], dirac), immersed_boundary.py:234-235).
+    Index arithmetic only (allocator-side plumbing)."""
+    n = p.numel() - 1
+    cnt = p[1:] - p[:-1]
+    indptr = zeros(n * dim + 1, I64)
+    rowlen = cnt.repeat_interleave(dim)
+    torch.cumsum(rowlen, 0, out=indptr[1:])
+    owner = torch.repeat_interleave(torch.arange(n, device=ids.device), cnt)        # list of every entry
+    pos = torch.arange(ids.numel(), device=ids.device) - p[:-1][owner]             # position inside its list
+    indices = empty(ids.numel() * dim, I32)
+    data = empty(ids.numel() * dim)
+    for dof in range(dim):
+        at = indptr[owner * dim + dof] + pos
+        indices[at] = ids * dim + dof
+        data[at] = vals
+    return CSR((n * dim, ncols_nodes * dim), indptr, indices, data, name)
+
+
+# ---------------------------------------------------------------------------------------------------------
 class Ksp:
     """Device Krylov solver handle (pyn_ksp_*)."""
     TYPES = {"cg": 0, "gmres": 1}

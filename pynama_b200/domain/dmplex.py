@@ -212,6 +212,13 @@ class DMPlexDom(object):
         return self.fullCoordVec.getValues(indices).reshape((floor(len(indices) / dim), dim))
 
     # -- device tables ----------------------------------------------------------------------------------------
+    def getBoundingBox(self):
+        """(lower, upper) corners of the mesh (DMPlex.getBoundingBox, used by immersed_boundary.py:50)."""
+        return list(self.lower), list(self.upper)
+
+    def getTotalCells(self):
+        return self.ncell
+
     def deviceCellNodes(self):
         from .. import backend as be
         if "e2n" not in self._dev:

@@ -148,6 +148,12 @@ class QuadMeshDom(object):
     def cellCornersArray(self):
         return self.points[self.quads]                       # (nc, 4, 2), closure order = the cell's vertex order
 
+    def getBoundingBox(self):
+        return list(self.lower), list(self.upper)
+
+    def getTotalCells(self):
+        return self.ncell
+
     def deviceCellNodes(self):
         from .. import backend as be
         if "e2n" not in self._dev:

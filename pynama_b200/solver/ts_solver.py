@@ -316,5 +316,12 @@ class TsSolver(object):
     def getSolution(self):
         return self.vec_sol
 
+    def setSolution(self, u):
+        """TSSetSolution: the caller edited the state outside the integrator (the immersed-boundary loop replaces the
+        vorticity by the curl of the corrected velocity, immersed_boundary.py:102-106), so the saved first stage is
+        stale."""
+        self.vec_sol = u
+        self.restart()
+
     def destroy(self):
         self._work = None

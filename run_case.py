@@ -30,6 +30,10 @@ elif case == 'uniform':
     from pynama_b200.cases.uniform import UniformFlow as FemProblem
 elif case == 'cavity':
     from pynama_b200.cases.cavity import Cavity as FemProblem
+elif case == 'ibm-static':
+    from pynama_b200.cases.immersed_boundary import ImmersedBoundaryStatic as FemProblem
+elif case == 'ibm-dynamic':
+    from pynama_b200.cases.immersed_boundary import ImmersedBoundaryDynamic as FemProblem
 else:
     print("Case not defined unabled to import")
     sys.exit()

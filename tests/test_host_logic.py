@@ -352,3 +352,43 @@ def test_paraview_xdmf_output(tmp_path, monkeypatch):
     q = Paraviewer(2, None, str(tmp_path / "none"))
     q.saveMesh(coords); q.saveData(0, 0.0, vel); q.writeXmf("x")
     assert not (tmp_path / "none").exists()
+
+
+# ---- immersed-boundary coupling (parity unpinned: the reference's IBM code has no tests) ------------------
+def test_ibm_delta_functions_are_discrete_deltas():
+    """What pins the restated delta functions (src/domain/immersed_body.py:398-421): on any grid offset they sum to one
+    and have a vanishing first moment; the 4-point one also satisfies Peskin's sum-of-squares condition (3/8)."""
+    from pynama_b200.domain import immersed_body as ib
+    for kind, host in (("four", ib.fourGrid), ("three", ib.threeGrid), ("linear", ib.linear)):
+        for x in np.linspace(0.0, 1.0, 11):
+            w = [o.ibm_phi(kind, abs(x - j)) for j in range(-3, 5)]
+            assert abs(sum(w) - 1.0) < 1e-14, (kind, x)
+            assert abs(sum((x - j) * wj for j, wj in zip(range(-3, 5), w))) < 1e-14, (kind, x)
+            assert all(host(abs(x - j)) == o.ibm_phi(kind, abs(x - j)) for j in range(-3, 5))
+            if kind == "four":
+                assert abs(sum(wj * wj for wj in w) - 3.0 / 8.0) < 1e-14
+    assert o.ibm_dirac("four", [0.01, -0.02], 0.06) == ib.Circle([0, 0], [0, 0], 0.5).getDiracs([0.01, -0.02], 0.06)
+
+
+def test_ibm_bodies_and_matrices_oracle():
+    """Circle of the reference's ibm-static case (radius 0.5, h = 6/50/2: 53 markers); H, S, A of a small box mesh:
+    A = H S as matrices, symmetric positive definite; the correction makes the interpolated velocity the body's."""
+    xy, dl = o.ibm_circle(0.5, 6 / 50 / 2)
+    assert len(xy) == 53 and abs(dl - 2 * np.pi * 0.5 / 53) < 1e-16
+    assert np.allclose(np.hypot(xy[:, 0], xy[:, 1]), 0.5, atol=1e-15)
+    assert len(o.ibm_open_box(0.1)[0]) == 4 * 15 and len(o.ibm_line(0.1)[0]) == 20
+    n, h = 26, 0.12                      # node spacing 3 / 25 = h
+    gx = np.linspace(-1.5, 1.5, n)
+    nodexy = np.stack(np.meshgrid(gx, gx, indexing="xy"), -1).reshape(-1, 2)
+    lag, dl = o.ibm_circle(0.5, h)
+    col = o.ibm_collect(lag, np.arange(len(nodexy)), nodexy, dl, h, mode=0, kind="four")
+    H, S, A = o.ibm_matrices(col, len(nodexy), dl, h)
+    assert abs(A - H @ S).max() < 1e-15 * abs(A).max()
+    assert abs(A - A.T).max() < 1e-15 * abs(A).max()
+    assert np.linalg.eigvalsh(A.toarray()).min() > 0
+    rng = np.random.default_rng(0)
+    vel, vbody = rng.standard_normal(2 * len(nodexy)), np.tile([0.3, -0.1], len(lag))
+    vnew, q = o.ibm_velocity_correction(H, S, A, vel, vbody)
+    assert np.abs(H @ vnew - vbody).max() < 1e-12
+    # every marker sees the full weight of the delta function: sum_e delta h^2 = 1
+    assert np.allclose(np.asarray(H[0::2].sum(axis=1)).ravel(), 1.0, atol=1e-13)
