@@ -240,11 +240,15 @@ int pyn_tmat_supported(int nn, int rdof, int cdof);
  * mode 1, :391-402): for every Lagrangian node (d_lagxy [nlag][2]) the candidate Euler nodes (d_cand, ascending ids into
  * d_nodexy [nnodes][2]) that are "close" -- mode 0: |dx / dl| < 3 and |dy / dl| < 3; mode 1: |dx / dl| < 2 and
  * |dy| < 1 + 2 dl -- with the discrete delta value prod_r phi(|r| / h) / h (immersed_body.py:259-264; delta_kind 0
- * fourGrid, 1 threeGrid, 2 linear, :398-421).  Two passes: d_ptr == NULL writes the counts [nlag] into
- * d_count_or_nodes; with the prefix sums d_ptr [nlag + 1] it writes the node ids and delta values (ascending node id).
+ * fourGrid, 1 threeGrid, 2 linear, :398-421).  Two passes over (marker, chunk) pairs, marker-major, with nchunks =
+ * pyn_ibm_chunks(ncand, NULL) chunks of the candidate list per marker: d_ptr == NULL writes the counts [nlag * nchunks]
+ * into d_count_or_nodes; with their prefix sums d_ptr [nlag * nchunks + 1] it writes the node ids and delta values
+ * (ascending node id; the list of marker l starts at d_ptr[l * nchunks]).
  * pyn_ibm_gram replaces H.matMult(S) of buildIBMMatrix (:246): the Lagrangian system matrix for one velocity
  * component, entry (i, j) = sum over the common Euler nodes e, ascending, of (d_i(e) a)(d_j(e) b) with a = h^2 and
- * b = dl h the scale factors of H and S (:243-245); same two-pass protocol (counts [nlag], then columns j and values). */
+ * b = dl h the scale factors of H and S (:243-245); the same two-pass protocol over (marker, block of 32 partner
+ * markers) pairs: counts [nlag * ceil(nlag / 32)], then the partner indices j and the values at their prefix sums. */
+int pyn_ibm_chunks(int64_t n, int64_t* chunk);
 int pyn_ibm_collect(int64_t nlag, const double* d_lagxy, int64_t ncand, const int32_t* d_cand, const double* d_nodexy,
                     double dl, double h, int mode, int delta_kind, const int64_t* d_ptr, int32_t* d_count_or_nodes,
                     double* d_dirac, void* stream);

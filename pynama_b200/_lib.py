@@ -80,6 +80,7 @@ _SIGNATURES = {
     "pyn_spmv_plan_destroy": (C.c_int, [c_vp]),
     "pyn_spmv_planned": (C.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, C.c_int, c_f64, c_f64, c_vp, c_vp]),
     "pyn_ibm_collect": (C.c_int, [c_i64, c_vp, c_i64, c_vp, c_vp, c_f64, c_f64, C.c_int, C.c_int, c_vp, c_vp, c_vp, c_vp]),
+    "pyn_ibm_chunks": (C.c_int, [c_i64, c_vp]),
     "pyn_ibm_gram": (C.c_int, [c_i64, c_vp, c_vp, c_vp, c_f64, c_f64, c_vp, c_vp, c_vp, c_vp]),
     "pyn_vec_set": (C.c_int, [c_i64, c_f64, c_vp, c_vp]),
     "pyn_vec_scale": (C.c_int, [c_i64, c_f64, c_vp, c_vp]),

@@ -505,31 +505,32 @@ def coo_to_csr(rows, cols, vals, shape, name=""):
 IBM_DELTA = {"four": 0, "three": 1, "linear": 2}
 
 
-def _two_pass(entry, head, tail, n):
-    """count pass -> prefix sums on device -> fill pass of one of the pyn_ibm_* entry points."""
-    counts = empty(n, I32)
+def _two_pass(entry, head, tail, n, pieces):
+    """count pass over (list, piece) pairs -> prefix sums on device -> fill pass of one of the pyn_ibm_* entry points.
+    Returns (ptr [n + 1] of the lists, ids, values)."""
+    counts = empty(n * pieces, I32)
     call(entry, *head, None, ptr(counts), None, *tail)
-    p = zeros(n + 1, I64)
+    p = zeros(n * pieces + 1, I64)
     torch.cumsum(counts, 0, out=p[1:])
     total = int(p[-1])                       # one scalar read-back: the size of the output arrays
     ids, vals = empty(total, I32), empty(total)
     call(entry, *head, ptr(p), ptr(ids), ptr(vals), *tail)
-    return p, ids, vals
+    return p[::pieces].contiguous(), ids, vals
 
 
 def ibm_collect(lagxy, cand, nodexy, dl, h, mode=0, kind="four"):
     """Per Lagrangian node the close candidate Euler nodes (ascending) and their delta values:
     (ptr [nlag+1] int64, nodes int32, dirac f64)."""
-    nlag = lagxy.numel() // 2
-    head = (nlag, ptr(lagxy), int(cand.numel()), ptr(cand), ptr(nodexy), float(dl), float(h), int(mode), IBM_DELTA[kind])
-    return _two_pass("pyn_ibm_collect", head, (stream(),), nlag)
+    nlag, ncand = lagxy.numel() // 2, int(cand.numel())
+    head = (nlag, ptr(lagxy), ncand, ptr(cand), ptr(nodexy), float(dl), float(h), int(mode), IBM_DELTA[kind])
+    return _two_pass("pyn_ibm_collect", head, (stream(),), nlag, int(_lib.load().pyn_ibm_chunks(ncand, None)))
 
 
 def ibm_gram(p, nodes, dirac, a, b):
     """One velocity component of A = H S: (ptr [nlag+1], partner Lagrangian nodes j, values)."""
     nlag = p.numel() - 1
     head = (nlag, ptr(p), ptr(nodes), ptr(dirac), float(a), float(b))
-    return _two_pass("pyn_ibm_gram", head, (stream(),), nlag)
+    return _two_pass("pyn_ibm_gram", head, (stream(),), nlag, (nlag + 31) // 32)
 
 
 def dof_blocked_csr(p, ids, vals, ncols_nodes, dim, name=""):

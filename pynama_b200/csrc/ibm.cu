@@ -5,11 +5,11 @@
 // src/domain/immersed_body.py:259-264, 398-421.  The reference loops over the Lagrangian nodes in Python and, for the
 // dynamic case, does so again every time step (rebuildMatrix, :416-433).  Here both steps are kernels:
 //
-//   ibm_collect_kernel  one warp per Lagrangian node scans the candidate Euler nodes (ascending node id) and keeps the
-//                       close ones with their delta value: ballot + prefix, so the lists come out sorted and the
-//                       result does not depend on the launch geometry;
-//   ibm_gram_kernel     the Lagrangian system matrix A = H S (S = H^T dl h, H scaled by h^2): one warp per row node,
-//                       one partner node per lane, a two-pointer merge of the two sorted lists -- terms added in
+//   ibm_collect_kernel  one warp per (Lagrangian node, chunk of the candidate Euler nodes, ascending node id) keeps the
+//                       close ones with their delta value: ballot + prefix inside the warp, prefix sums of the chunk
+//                       counts between them, so the lists come out sorted whatever the launch geometry;
+//   ibm_gram_kernel     the Lagrangian system matrix A = H S (S = H^T dl h, H scaled by h^2): one warp per (row node,
+//                       32 partner nodes), one partner per lane, a two-pointer merge of the two sorted lists -- terms added in
 //                       ascending Euler node order (what a row-times-column product over sorted CSR rows does).
 //
 // Both run as count / fill pairs on the caller's prefix sums.  Every floating-point operation is an explicit
@@ -65,23 +65,28 @@ __device__ __forceinline__ bool ibm_close(int mode, double dx, double dy, double
   return fabs(ex) < 2.0 && fabs(__dmul_rn(ey, dl)) < __dadd_rn(1.0, __dmul_rn(2.0, dl));
 }
 
+// One warp per (marker, chunk of the candidate list): the counts of the chunks, marker-major, are prefix-summed by the
+// caller, which gives every warp the place of its (ascending) piece of the marker's list.
 template <bool FILL>
 __global__ void __launch_bounds__(256)
 ibm_collect_kernel(int64_t nlag, const double* __restrict__ lagxy, int64_t ncand, const int* __restrict__ cand,
-                   const double* __restrict__ nodexy, double dl, double h, int mode, int kind,
-                   const int64_t* __restrict__ ptr, int* __restrict__ count_or_nodes, double* __restrict__ dirac) {
+                   const double* __restrict__ nodexy, double dl, double h, int mode, int kind, int nchunks,
+                   int64_t chunk, const int64_t* __restrict__ ptr, int* __restrict__ count_or_nodes,
+                   double* __restrict__ dirac) {
   const int lane = threadIdx.x & 31;
-  const int64_t l = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
-  if (l >= nlag) return;
+  const int64_t wid = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  if (wid >= nlag * nchunks) return;
+  const int64_t l = wid / nchunks, ck = wid - l * nchunks;
   const double lx = lagxy[2 * l], ly = lagxy[2 * l + 1];
-  int64_t at = FILL ? ptr[l] : 0;
+  const int64_t cbeg = ck * chunk, cend = min(ncand, cbeg + chunk);
+  int64_t at = FILL ? ptr[wid] : 0;
   int found = 0;
-  for (int64_t c0 = 0; c0 < ncand; c0 += 32) {
+  for (int64_t c0 = cbeg; c0 < cend; c0 += 32) {
     const int64_t c = c0 + lane;
     int node = 0;
     double dx = 0.0, dy = 0.0;
     bool close = false;
-    if (c < ncand) {
+    if (c < cend) {
       node = cand[c];
       dx = __dsub_rn(nodexy[2 * (int64_t)node], lx);        // coords - coordBodyNode
       dy = __dsub_rn(nodexy[2 * (int64_t)node + 1], ly);
@@ -96,7 +101,7 @@ ibm_collect_kernel(int64_t nlag, const double* __restrict__ lagxy, int64_t ncand
     at += __popc(m);
     found += __popc(m);
   }
-  if (!FILL && lane == 0) count_or_nodes[l] = found;
+  if (!FILL && lane == 0) count_or_nodes[wid] = found;
 }
 
 // A = H S restricted to one velocity component (the two components carry the same numbers on the rows 2i+d / columns
@@ -104,50 +109,55 @@ ibm_collect_kernel(int64_t nlag, const double* __restrict__ lagxy, int64_t ncand
 template <bool FILL>
 __global__ void __launch_bounds__(256)
 ibm_gram_kernel(int64_t nlag, const int64_t* __restrict__ ptr, const int* __restrict__ nodes,
-                const double* __restrict__ dirac, double a, double b, const int64_t* __restrict__ aptr,
+                const double* __restrict__ dirac, double a, double b, int nblk, const int64_t* __restrict__ aptr,
                 int* __restrict__ count_or_cols, double* __restrict__ avals) {
   const int lane = threadIdx.x & 31;
-  const int64_t i = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
-  if (i >= nlag) return;
+  const int64_t wid = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;   // (row marker i, block of 32 partners)
+  if (wid >= nlag * nblk) return;
+  const int64_t i = wid / nblk, j = (wid - i * nblk) * 32 + lane;
   const int64_t i0 = ptr[i], i1 = ptr[i + 1];
-  int64_t at = FILL ? aptr[i] : 0;
-  int found = 0;
-  for (int64_t j0 = 0; j0 < nlag; j0 += 32) {
-    const int64_t j = j0 + lane;
-    bool hit = false;
-    double s = 0.0;
-    if (j < nlag) {
-      int64_t p = i0, q = ptr[j];
-      const int64_t q1 = ptr[j + 1];
-      while (p < i1 && q < q1) {
-        const int np_ = nodes[p], nq = nodes[q];
-        if (np_ == nq) {
-          hit = true;
-          s = __dadd_rn(s, __dmul_rn(__dmul_rn(dirac[p], a), __dmul_rn(dirac[q], b)));
-          ++p;
-          ++q;
-        } else if (np_ < nq) {
-          ++p;
-        } else {
-          ++q;
-        }
+  bool hit = false;
+  double s = 0.0;
+  if (j < nlag) {
+    int64_t p = i0, q = ptr[j];
+    const int64_t q1 = ptr[j + 1];
+    while (p < i1 && q < q1) {
+      const int np_ = nodes[p], nq = nodes[q];
+      if (np_ == nq) {
+        hit = true;
+        s = __dadd_rn(s, __dmul_rn(__dmul_rn(dirac[p], a), __dmul_rn(dirac[q], b)));
+        ++p;
+        ++q;
+      } else if (np_ < nq) {
+        ++p;
+      } else {
+        ++q;
       }
     }
-    const unsigned m = __ballot_sync(0xffffffffu, hit);
-    if (FILL && hit) {
-      const int64_t o = at + __popc(m & ((1u << lane) - 1u));
-      count_or_cols[o] = (int)j;
-      avals[o] = s;
-    }
-    at += __popc(m);
-    found += __popc(m);
   }
-  if (!FILL && lane == 0) count_or_cols[i] = found;
+  const unsigned m = __ballot_sync(0xffffffffu, hit);
+  if (FILL && hit) {
+    const int64_t o = aptr[wid] + __popc(m & ((1u << lane) - 1u));
+    count_or_cols[o] = (int)j;
+    avals[o] = s;
+  }
+  if (!FILL && lane == 0) count_or_cols[wid] = __popc(m);
 }
 
 }  // namespace
 
 extern "C" {
+
+int pyn_ibm_chunks(int64_t n, int64_t* chunk) {
+  // pieces a list of n candidates is cut into (one warp each per marker): about 4096 candidates, whole warps
+  int64_t nchunks = (n + 4095) / 4096;
+  if (nchunks < 1) nchunks = 1;
+  int64_t c = (n + nchunks - 1) / nchunks;
+  c = (c + 31) / 32 * 32;
+  if (c < 32) c = 32;
+  if (chunk) *chunk = c;
+  return (int)((n + c - 1) / c > 0 ? (n + c - 1) / c : 1);
+}
 
 int pyn_ibm_collect(int64_t nlag, const double* d_lagxy, int64_t ncand, const int32_t* d_cand, const double* d_nodexy,
                     double dl, double h, int mode, int delta_kind, const int64_t* d_ptr, int32_t* d_count_or_nodes,
@@ -158,13 +168,17 @@ int pyn_ibm_collect(int64_t nlag, const double* d_lagxy, int64_t ncand, const in
   PYN_REQUIRE(!d_ptr || d_dirac, "fill pass without an output array for the delta values");
   if (nlag == 0) return PYN_OK;
   cudaStream_t st = pyn::as_stream(stream);
-  const unsigned grid = (unsigned)((nlag * 32 + 255) / 256);
+  int64_t chunk = 0;
+  const int nchunks = pyn_ibm_chunks(ncand, &chunk);
+  const int64_t nwarps = nlag * nchunks;
+  PYN_REQUIRE(nwarps * 32 / 256 < 0x7fffffff, "too many (marker, chunk) pairs");
+  const unsigned grid = (unsigned)((nwarps * 32 + 255) / 256);
   if (d_ptr)
-    ibm_collect_kernel<true><<<grid, 256, 0, st>>>(nlag, d_lagxy, ncand, d_cand, d_nodexy, dl, h, mode, delta_kind, d_ptr,
-                                                   d_count_or_nodes, d_dirac);
+    ibm_collect_kernel<true><<<grid, 256, 0, st>>>(nlag, d_lagxy, ncand, d_cand, d_nodexy, dl, h, mode, delta_kind,
+                                                   nchunks, chunk, d_ptr, d_count_or_nodes, d_dirac);
   else
     ibm_collect_kernel<false><<<grid, 256, 0, st>>>(nlag, d_lagxy, ncand, d_cand, d_nodexy, dl, h, mode, delta_kind,
-                                                    nullptr, d_count_or_nodes, nullptr);
+                                                    nchunks, chunk, nullptr, d_count_or_nodes, nullptr);
   PYN_CHECK_LAUNCH();
   return PYN_OK;
 }
@@ -175,11 +189,14 @@ int pyn_ibm_gram(int64_t nlag, const int64_t* d_ptr, const int32_t* d_nodes, con
   PYN_REQUIRE(!d_aptr || d_avals, "fill pass without an output array for the values");
   if (nlag == 0) return PYN_OK;
   cudaStream_t st = pyn::as_stream(stream);
-  const unsigned grid = (unsigned)((nlag * 32 + 255) / 256);
+  const int nblk = (int)((nlag + 31) / 32);
+  const unsigned grid = (unsigned)((nlag * nblk * 32 + 255) / 256);
   if (d_aptr)
-    ibm_gram_kernel<true><<<grid, 256, 0, st>>>(nlag, d_ptr, d_nodes, d_dirac, a, b, d_aptr, d_count_or_cols, d_avals);
+    ibm_gram_kernel<true><<<grid, 256, 0, st>>>(nlag, d_ptr, d_nodes, d_dirac, a, b, nblk, d_aptr, d_count_or_cols,
+                                                d_avals);
   else
-    ibm_gram_kernel<false><<<grid, 256, 0, st>>>(nlag, d_ptr, d_nodes, d_dirac, a, b, nullptr, d_count_or_cols, nullptr);
+    ibm_gram_kernel<false><<<grid, 256, 0, st>>>(nlag, d_ptr, d_nodes, d_dirac, a, b, nblk, nullptr, d_count_or_cols,
+                                                 nullptr);
   PYN_CHECK_LAUNCH();
   return PYN_OK;
 }
