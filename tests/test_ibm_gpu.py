@@ -138,3 +138,37 @@ def test_dynamic_case_rebuilds_where_the_body_is(be):
     vbody = fem.body.getVelocity().getArray()
     assert np.allclose(vbody[1::2], 2 * np.pi * 0.3 * np.cos(2 * np.pi * 0.37) / (5 / fem.U_ref))
     assert np.abs(H @ fem.vel.getArray() - vbody).max() < 1e-9 * max(fem.U_ref, np.abs(vbody).max())
+
+
+def test_two_bodies_share_one_system(be):
+    """The reference's two-cylinder set-up (commented in ibm-static.yaml): markers of both bodies in one H / S / A,
+    global marker numbers body after body (BodiesContainer.mapGlobToLocal, immersed_body.py:50-67)."""
+    from pynama_b200.cases import immersed_boundary as ib
+    from pynama_b200.common.options import Options
+    Options.clear()
+    for k, v in dict(ksp_type="cg", pc_type="jacobi", ksp_rtol=1e-12, ksp_max_it=20000).items():
+        Options.setValue(k, v)
+    with open(f"{ROOT}/pynama_b200/cases/ibm-static.yaml") as f:
+        cfg = yaml.load(f, Loader=yaml.Loader)
+    cfg["domain"]["box-mesh"]["nelem"] = [32, 32]
+    cfg["bodies"].append({"type": "circle", "vel": "static", "radius": 0.5, "center": [0, -1.5]})
+    fem = ib.ImmersedBoundaryStatic(cfg, case="ibm-static")
+    fem.setUp()
+    fem.setUpSolver()
+    n1 = fem.body.bodies[0].getTotalNodes()
+    assert fem.body.getTotalNodes() == 2 * n1 and fem.H.getSize()[0] == 4 * n1
+    assert fem.body.mapGlobToLocal(n1 + 3) == (3, 1) and fem.body.mapGlobToLocal(n1 - 1) == (n1 - 1, 0)
+    np.testing.assert_allclose(fem.body.getNodeCoordinates(n1 + 3),
+                               fem.body.bodies[1].getNodeCoordinates(3), rtol=0, atol=0)
+    H, S, A = _oracle_matrices(fem, 0)
+    for mine, ref in ((fem.H, H), (fem.A, A)):
+        ip, ix, dv = mine.getValuesCSR()
+        np.testing.assert_array_equal(ip, ref.indptr)
+        np.testing.assert_array_equal(ix, ref.indices)
+        assert rel_err(dv, ref.data) < 1e-15
+    fem.vort.set(0.0)
+    fem.solveKLE(0.0, fem.vort)
+    fem.computeVelocityCorrection()
+    assert np.abs(H @ fem.vel.getArray()).max() < 1e-9 * fem.U_ref
+    fx, fy = fem.computeDragForce(0.1)
+    assert len(fx) == 2 and len(fy) == 2
