@@ -42,6 +42,8 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-time-loop", action="store_true", dest="no_time_loop")
+    ap.add_argument("--mg", default="", help="multigrid tuning for the time-loop solves: degree[,ratio] of the "
+                    "Chebyshev smoother (-pc_mg_degree, -pc_mg_ratio; default 3,10)")
     ap.add_argument("--no-percell", action="store_true", dest="no_percell",
                     help="skip the per-cell record (configs[2] at the headline order) of the default single-GPU line")
     ap.add_argument("--no-configs4", action="store_true", dest="no_configs4",
@@ -287,7 +289,14 @@ def run_native(a):
     nx, n = a.nx, a.ngl
     # strong scaling: the fixed nx x nx mesh is cut into `world` strips of cell rows, one per GPU; a rank assembles the
     # rows of the nodes it owns (complete thanks to one ghost row of cells: no matrix entry crosses NVLink)
-    prob = CavityAssembly(nx, n, pc_type=a.pc, ksp_max_it=200000, **({"ksp_check_every": 50} if a.pc == "jacobi" else {}))
+    mg_opts = {}
+    if a.mg:
+        parts = a.mg.split(",")
+        mg_opts["pc_mg_degree"] = int(parts[0])
+        if len(parts) > 1:
+            mg_opts["pc_mg_ratio"] = float(parts[1])
+    prob = CavityAssembly(nx, n, pc_type=a.pc, ksp_max_it=200000, **mg_opts,
+                          **({"ksp_check_every": 50} if a.pc == "jacobi" else {}))
     prob.step()
     barrier()
     nnz = {k: v.nnz for k, v in prob.mats.items()}

@@ -726,7 +726,7 @@ class MultigridPC:
     rediscretised, exact coarsest solve; Jacobi on the prescribed dofs (identity rows).  kind: "K" | "KFS" for the
     cavity (assemble_noslip), "freeslip" for the all-Dirichlet cases (assemble_freeslip)."""
 
-    def __init__(self, nx, ny, ngl, kind="K", lower=(0, 0), upper=(1, 1), degree=3, ratio=10.0, coarse_cells=1024,
+    def __init__(self, nx, ny, ngl, kind="K", lower=(0, 0), upper=(1, 1), degree=3, ratio=30.0, coarse_cells=1024,
                  power_its=30, fine=None, lmax=None):
         """fine: use this matrix as the level-0 operator; lmax: per-level spectral bounds to use instead of this
         class's own power iteration (its start vector differs from the device's, so the bounds agree to ~1e-3 only)."""

@@ -91,7 +91,7 @@ class KspSolver(object):
         self.guess_nonzero = o.getBool("ksp_initial_guess_nonzero", self.guess_nonzero)
         self.error_if_not_converged = o.getBool("ksp_error_if_not_converged", self.error_if_not_converged)
         self.mg_degree = o.getInt("pc_mg_degree", 3)                 # Chebyshev smoother degree
-        self.mg_ratio = o.getReal("pc_mg_ratio", 10.0)               # ... on [lmax / ratio, lmax]
+        self.mg_ratio = o.getReal("pc_mg_ratio", 30.0)               # ... on [lmax / ratio, lmax]; 30: see profiles/README.md
         self.mg_coarse_cells = o.getInt("pc_mg_coarse_cells", 1024)  # coarsest mesh: dense inverse
 
     def setOperators(self, mat):

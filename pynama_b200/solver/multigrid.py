@@ -85,7 +85,7 @@ class Hierarchy(object):
     """V-cycle levels of one solve of a case.  kind "K": the no-slip / Dirichlet solve (unknowns = FREE dofs);
     kind "KFS": the free-slip stage K + Kfs (unknowns = FREE and TANGENT dofs)."""
 
-    def __init__(self, fem, kind, csr, degree=3, ratio=10.0, coarse_cells=1024, power_its=30, partition_p_levels=True):
+    def __init__(self, fem, kind, csr, degree=3, ratio=30.0, coarse_cells=1024, power_its=30, partition_p_levels=True):
         if getattr(fem.dom, "nx", None) is None:
             raise Exception("-pc_type mg needs a box mesh (coarse meshes are generated, not read)")
         self.kind, self.degree, self.ratio = kind, int(degree), float(ratio)
