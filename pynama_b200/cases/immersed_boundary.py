@@ -28,6 +28,8 @@ class ImmersedBoundaryStatic(FreeSlip):
     closeMode = 0      # computeClose of the static case (immersed_boundary.py:325-336)
 
     def setUp(self):
+        if self.comm.size > 1:
+            raise Exception("immersed-boundary cases run on one GPU (the markers are not partitioned)")
         super().setUp()
         self.setUpBodies()
         cells = self.getAffectedCells(10)
