@@ -1058,9 +1058,11 @@ def ksp_gmres(A, b, rtol=1e-5, atol=1e-50, dtol=1e4, max_it=10000, restart=30, j
 
 
 # ======================================================================================================================
-# Immersed-boundary velocity correction.  PARITY UNPINNED: the reference's immersed_boundary.py and
-# immersed_body.py import petsc4py / DMPlex and have no tests; what follows restates their arithmetic line by line and is
-# pinned only through the properties of the discrete delta functions (tests/test_host_logic.py).
+# Immersed-boundary velocity correction.  PARTLY PINNED: the discrete delta functions, getDiracs and the
+# marker coordinates of the bodies are checked bit for bit against the UNMODIFIED src/domain/immersed_body.py (golden
+# vectors tests/golden/ibm_ref.npz from oracle/gen_golden_ibm.py; live where /root/reference exists).  The closeness
+# rule, the matrices H, S, A and the correction step (src/cases/immersed_boundary.py, which needs PETSc and has no
+# tests) are restated line by line: PARITY UNPINNED for those, beyond the properties tests/test_host_logic.py checks.
 # ======================================================================================================================
 def ibm_phi(kind, r):
     """Discrete delta functions of src/domain/immersed_body.py:398-421: 'four' (fourGrid, the default of

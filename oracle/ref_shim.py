@@ -39,3 +39,22 @@ def import_reference_elements():
     from elements.spectral import Spectral  # noqa: E402  (reference code)
     from elements import utilities  # noqa: E402
     return Spectral, utilities
+
+
+def import_reference_immersed_body():
+    """The reference's src/domain/immersed_body.py, imported unmodified.  It imports petsc4py at module level (the
+    bodies are stored as 1-D DMPlex objects) but its discrete delta functions (threeGrid / linear / fourGrid, :398-421),
+    ImmersedBody.getDiracs (:259-264) and the generateBody methods of Line / OpenBox / Circle (:293-389) are plain
+    Python + NumPy: an empty petsc4py stand-in is enough to reach them."""
+    if not reference_available():
+        raise RuntimeError("reference tree not present (expected only in the build container)")
+    if "petsc4py" not in sys.modules:
+        stub = types.ModuleType("petsc4py")
+        stub.PETSc = types.SimpleNamespace()
+        stub.init = lambda *a, **k: None
+        sys.modules["petsc4py"] = stub
+    if REFERENCE_SRC not in sys.path:
+        sys.path.insert(0, REFERENCE_SRC)
+    import domain.immersed_body as ib  # noqa: E402  (reference code)
+    return ib
+

@@ -1,12 +1,13 @@
 """CPU tests: the oracle (oracle/kle_oracle.py) and the product's host tables against the golden vectors made by the
 UNMODIFIED reference (oracle/gen_golden.py) and against the reference's own known answers."""
 import math
+import os
 
 import numpy as np
 import pytest
 
 import kle_oracle as o
-from conftest import rel_err
+from conftest import GOLDEN, rel_err
 
 
 # ---- closed-form rules pinned by the reference (src/tests/test_element.py:181-229) -----------------------
@@ -198,3 +199,45 @@ def test_cg_initial_guess_nonzero_semantics():
     assert o.ksp_cg_jacobi(K, b, rtol=1e-6, x0=xs)[1:3] == (0, 2)
     xb, itb, rb, hb = o.ksp_cg_jacobi(K, np.zeros_like(b), rtol=1e-6, x0=x0)
     assert rb == 2 and itb > 0 and hb[-1] <= 1e-6 * hb[0] and np.abs(xb).max() < 1e-4 * np.abs(x0).max()
+
+
+# ---- immersed bodies: the reference's own delta functions and marker coordinates (src/domain/immersed_body.py) ---------
+def test_ibm_oracle_vs_reference_golden():
+    """tests/golden/ibm_ref.npz holds outputs of the UNMODIFIED reference module (oracle/gen_golden_ibm.py): the three
+    discrete delta functions on 501 radii, ImmersedBody.getDiracs on 400 offsets, the markers of Circle / Line /
+    OpenBox.  The oracle -- and the host functions of the product -- reproduce them bit for bit."""
+    from pynama_b200.domain import immersed_body as ib
+    g = np.load(os.path.join(GOLDEN, "ibm_ref.npz"))
+    for kind, name, host in (("four", "fourGrid", ib.fourGrid), ("three", "threeGrid", ib.threeGrid),
+                             ("linear", "linear", ib.linear)):
+        np.testing.assert_array_equal([o.ibm_phi(kind, r) for r in g["r"]], g[f"phi_{name}"])
+        np.testing.assert_array_equal([float(host(r)) for r in g["r"]], g[f"phi_{name}"])
+    h = float(g["dirac_h"])
+    np.testing.assert_array_equal([o.ibm_dirac("four", d, h) for d in g["dirac_dist"]], g["dirac"])
+    for i in range(3):
+        radius, hh = g[f"circle{i}_args"]
+        xy, dl = o.ibm_circle(radius, hh)
+        np.testing.assert_array_equal(xy, g[f"circle{i}_xy"])
+        assert dl == float(g[f"circle{i}_dl"])
+    for i in range(2):
+        np.testing.assert_array_equal(o.ibm_line(float(g[f"line{i}_args"][0]))[0], g[f"line{i}_xy"])
+        np.testing.assert_array_equal(o.ibm_open_box(float(g[f"box{i}_args"][0]))[0], g[f"box{i}_xy"])
+
+
+def test_ibm_oracle_vs_live_reference():
+    """Where /root/reference exists (the build container): the same comparison against the module itself."""
+    import ref_shim
+    if not ref_shim.reference_available():
+        pytest.skip("reference tree not present")
+    ref = ref_shim.import_reference_immersed_body()
+    rng = np.random.default_rng(5)
+    for r in rng.uniform(0, 2.5, 200):
+        assert o.ibm_phi("four", r) == ref.fourGrid(r) and o.ibm_phi("three", r) == ref.threeGrid(r)
+        assert o.ibm_phi("linear", r) == ref.linear(r)
+    body = ref.Circle(vel=[0, 0], center=[0, 0], radius=0.5)
+    for d in rng.uniform(-0.2, 0.2, (50, 2)):
+        assert o.ibm_dirac("four", d, 0.07) == body.getDiracs(d, 0.07)
+    coords, _, dl = ref.Circle(vel=[0, 0], center=[0, 0], radius=0.41).generateBody(0.033)
+    xy, dl2 = o.ibm_circle(0.41, 0.033)
+    np.testing.assert_array_equal(xy, np.array(coords))
+    assert dl == dl2
