@@ -172,3 +172,23 @@ def test_two_bodies_share_one_system(be):
     assert np.abs(H @ fem.vel.getArray()).max() < 1e-9 * fem.U_ref
     fx, fy = fem.computeDragForce(0.1)
     assert len(fx) == 2 and len(fy) == 2
+
+
+@pytest.mark.parametrize("tag,mode", [("static", 0), ("dynamic", 1)])
+def test_device_matrices_vs_reference_golden(be, tag, mode):
+    """The device lists and matrices against what the UNMODIFIED reference case code produced for the same markers and
+    Euler nodes (tests/golden/ibm_ref.npz, oracle/gen_golden_ibm.py): patterns exact, values to 1e-15."""
+    import os
+    from conftest import GOLDEN
+    g = np.load(os.path.join(GOLDEN, "ibm_ref.npz"))
+    nodexy, lag, dl, h = g["case_nodexy"], g["case_lag"], float(g["case_dl"]), float(g["case_h"])
+    p, nodes, dirac = be.ibm_collect(be.to_device(lag.reshape(-1)), be.to_device(g["case_cand"].astype(np.int32)),
+                                     be.to_device(nodexy.reshape(-1)), dl, h, mode=mode, kind="four")
+    H = be.dof_blocked_csr(p, nodes, dirac * (h ** 2), len(nodexy), 2)
+    ap, aj, av = be.ibm_gram(p, nodes, dirac, h ** 2, dl * h)
+    A = be.dof_blocked_csr(ap, aj, av, len(lag), 2)
+    for nm, M in (("H", H), ("A", A)):
+        ip, ix, dv = M.getValuesCSR()
+        np.testing.assert_array_equal(ip, g[f"{tag}_{nm}_indptr"])
+        np.testing.assert_array_equal(ix, g[f"{tag}_{nm}_indices"])
+        assert rel_err(dv, g[f"{tag}_{nm}_data"]) < 1e-15
