@@ -1058,11 +1058,13 @@ def ksp_gmres(A, b, rtol=1e-5, atol=1e-50, dtol=1e4, max_it=10000, restart=30, j
 
 
 # ======================================================================================================================
-# Immersed-boundary velocity correction.  PARTLY PINNED: the discrete delta functions, getDiracs and the
-# marker coordinates of the bodies are checked bit for bit against the UNMODIFIED src/domain/immersed_body.py (golden
-# vectors tests/golden/ibm_ref.npz from oracle/gen_golden_ibm.py; live where /root/reference exists).  The closeness
-# rule, the matrices H, S, A and the correction step (src/cases/immersed_boundary.py, which needs PETSc and has no
-# tests) are restated line by line: PARITY UNPINNED for those, beyond the properties tests/test_host_logic.py checks.
+# Immersed-boundary velocity correction.  PINNED against the reference's own code: the delta functions,
+# getDiracs and marker coordinates against the UNMODIFIED src/domain/immersed_body.py, and the lists, H, S, A, the
+# corrected velocity and the virtual flux against the UNMODIFIED collectNodes / computeClose / computeDirac /
+# buildIBMMatrix / computeVelocityCorrection of src/cases/immersed_boundary.py run on scipy stand-ins for PETSc's Mat and
+# Vec (oracle/ref_shim.run_reference_ibm) -- bit for bit; golden vectors tests/golden/ibm_ref.npz from
+# oracle/gen_golden_ibm.py, live comparison where /root/reference exists (tests/test_oracle_golden.py).  What the
+# stand-ins assume of PETSc: INSERT_VALUES setValues, sorted AIJ rows, MatMatMult accumulating along the left row.
 # ======================================================================================================================
 def ibm_phi(kind, r):
     """Discrete delta functions of src/domain/immersed_body.py:398-421: 'four' (fourGrid, the default of
