@@ -12,12 +12,23 @@ oracle/gen_golden.py):
   * element layer (quadrature, tabulation, element K/Rw/Rd, SrT/DivSrT/Curl/W): PINNED against the
     reference's own code imported unmodified in the build container (tests/golden/elem_*.npz) and against the
     closed-form points/weights of src/tests/test_element.py:181-229.
-  * numbering / assembly / KSP / TS: the arithmetic lives in PETSc (petsc4py; un-vendored, version not pinned,
-    absent from this image).  Pinned only through the reference tests that survive at that boundary:
+  * assembly loops, operators, right-hand-side chain, two-stage solveKLE, immersed-boundary coupling: PINNED against the
+    reference's own case-layer code run UNMODIFIED in the build container on stand-ins for PETSc's Mat / Vec and for the
+    mesh queries (oracle/ref_shim.py: run_reference_build_kle_mats, run_reference_operators_and_rhs,
+    run_reference_cavity_solve_kle, run_reference_ibm): NoSlipFreeSlip.buildKLEMats and FreeSlip.buildKLEMats
+    (src/cases/base_problem.py:329-454, 499-552) with MatNS / Mat.assembleAll / setIndices2One, buildOperators with
+    Operators.setValues / assembleAll (mat_generator.py:157-190), evalRHS + computeVtensV (:212-252), solveKLE with
+    Cavity.applyBoundaryConditions[FS] and NoSlipWalls (:321-327, cavity.py:53-81), the IBM case code
+    (immersed_boundary.py:205-277, 318-338, 391-402).  Golden vectors: tests/golden/asm_ref.npz, ibm_ref.npz
+    (oracle/gen_golden_asm.py, gen_golden_ibm.py): stored patterns (explicit zeros included) bit-exact, values to the
+    round-off of the element matrices.  What the stand-ins assume of PETSc: serial AIJ keeps every inserted entry,
+    ADD_VALUES accumulate in call order, INSERT replaces, MatMult / MatMatMult walk sorted rows.
+  * numbering / KSP / TS: the arithmetic lives in PETSc (petsc4py; un-vendored, version not pinned, absent from this
+    image).  Pinned only through the reference tests that survive at that boundary:
     src/tests/test_domain.py:22-78,187-201 (cell range, corner order, border/node counts, ngl=2 numbering) and
     src/tests/test_solver.py:20-37,66-87 (uniform flow 1e-12, Taylor-Green 2x2/ngl 11 < 2e-8, VtensV).
-    Everything else at that layer (edge/interior numbering for ngl>2, assembled values, cavity two-stage
-    solve, RK tableau/adaptor) is "PARITY UNPINNED" -- restated from PETSc's documented semantics.
+    The rest of that layer (edge/interior numbering for ngl>2 -- which the stand-ins take from this oracle's BoxMesh --,
+    the CG recurrence, RK tableau/adaptor) is "PARITY UNPINNED": restated from PETSc's documented semantics.
 """
 from __future__ import annotations
 

@@ -234,3 +234,314 @@ def run_reference_ibm(nodexy, candidate_nodes, lagxy, dl, h, dynamic, vel, body_
     cib.ImmersedBoundaryStatic.computeVelocityCorrection(fem)
     return fem.H.csr, fem.S.csr, fem.ksp.A.csr, fem.vel.a, fem.virtualFlux.a
 
+
+
+# ---- the reference's buildKLEMats loops (A1 / A2 of SURVEY 8) on stand-ins -------------------------------------------
+class _FakeAijMat(object):
+    """MatSetValues / MatAssembly of a serial AIJ matrix: every (row, col) ever set is stored -- explicit zeros included
+    --, ADD_VALUES accumulate in call order, INSERT_VALUES replace."""
+
+    def __init__(self, shape, name=""):
+        self.shape, self.name, self.entries = shape, name, {}
+
+    def setValues(self, rows, cols, vals, addv=False):
+        import numpy as np
+        rows, cols = np.atleast_1d(np.asarray(rows, dtype=np.int64)), np.atleast_1d(np.asarray(cols, dtype=np.int64))
+        vals = np.asarray(vals, dtype=float)
+        if vals.ndim == 0:
+            vals = np.full((len(rows), len(cols)), float(vals))
+        vals = vals.reshape(len(rows), len(cols))
+        for i, r in enumerate(rows):
+            for j, c in enumerate(cols):
+                k = (int(r), int(c))
+                if addv and k in self.entries:
+                    self.entries[k] = self.entries[k] + vals[i, j]
+                else:
+                    self.entries[k] = float(vals[i, j])
+
+    def assemble(self):
+        pass
+
+    def getName(self):
+        return self.name
+
+    def to_csr(self):
+        import numpy as np
+        import scipy.sparse as sp
+        keys = sorted(self.entries)
+        indptr = np.zeros(self.shape[0] + 1, dtype=np.int64)
+        for r, _ in keys:
+            indptr[r + 1] += 1
+        return sp.csr_matrix((np.array([self.entries[k] for k in keys]), np.array([k[1] for k in keys], dtype=np.int32),
+                              np.cumsum(indptr)), shape=self.shape)
+
+
+def run_reference_build_kle_mats(mesh, noslip):
+    """NoSlipFreeSlip.buildKLEMats (src/cases/base_problem.py:329-454) or FreeSlip.buildKLEMats (:499-552), UNMODIFIED,
+    on a bare case instance: the element layer is the reference's own Spectral, the matrix container its own MatNS / Mat
+    (assembleAll, setIndices2One), the PETSc matrices are _FakeAijMat, and the mesh queries (cell nodes, corner
+    coordinates, border nodes with their wall normal: src/domain/dmplex.py:245-261) are answered from the oracle's
+    BoxMesh `mesh`.  Every decision about which dof is free / tangential / set in a cell, the thirteen setValues calls
+    and the post-assembly loops are the reference's.  Returns {name: scipy CSR}."""
+    import logging
+    import numpy as np
+    Spectral, _ = import_reference_elements()
+    _install_petsc_stub()
+    if REFERENCE_SRC not in sys.path:
+        sys.path.insert(0, REFERENCE_SRC)
+    import cases.base_problem as cbp  # noqa: E402  (reference code)
+    from matrices.mat_generator import Mat  # noqa: E402
+    from matrices.mat_ns import MatNS  # noqa: E402
+    cell_nodes = mesh.cell_nodes()
+    corner = mesh.cell_corner_coords()
+    names = ["down", "right", "up", "left"]                      # dmplex.py:38
+    face_nodes = {nm: set(int(n) for n in mesh.border_nodes(nm)) for nm in names}
+    normal = {"down": 1, "up": 1, "left": 0, "right": 0}         # |normal| of the face (computeCellGeometryFVM)
+    boundary = set(int(n) for n in mesh.boundary_nodes())
+
+    class Dom(object):
+        cellStart, cellEnd = 0, len(cell_nodes)
+
+        def getCellCornersCoords(self, cell):
+            return corner[cell].reshape(-1).copy()
+
+        def getGlobalNodesFromCell(self, cell, shared):
+            return [int(n) for n in cell_nodes[cell]]
+
+        def getVelocityIndex(self, nodes):
+            return [n * 2 + d for n in nodes for d in range(2)]
+
+        def getVorticityIndex(self, nodes):
+            return [n for n in nodes]
+
+        def getNodesFromLabel(self, label, shared=False):
+            assert label == "External Boundary"
+            return set(boundary)
+
+        def getBorderNodesWithNormal(self, cell, intersect):
+            nodes, normals = [], []
+            mine = [int(n) for n in cell_nodes[cell]]
+            for nm in names:
+                on_face = [n for n in mine if n in face_nodes[nm]]
+                # (a cell of a box mesh that touches a border does so with a whole side)
+                if len(on_face) >= mesh.ngl and not (set(on_face) - intersect):
+                    normals.append(normal[nm])
+                    nodes.append(on_face)
+            return nodes, normals
+
+    N = mesh.nnodes
+    comm = types.SimpleNamespace(rank=0, size=1)
+    mat = (MatNS if noslip else Mat).__new__(MatNS if noslip else Mat)
+    mat.dim, mat.dim_w, mat.dim_s, mat.comm = 2, 1, 3, comm
+    mat.logger = logging.getLogger("reference-mat")
+    sq, rc = (2 * N, 2 * N), (2 * N, N)
+    for nm, shape in (("K", sq), ("Krhs", sq), ("Rw", rc), ("Rd", rc), ("Kfs", sq), ("Krhsfs", sq), ("Rwfs", rc),
+                      ("Rdfs", rc)):
+        setattr(mat, nm, _FakeAijMat(shape, nm))
+    mat.mats = [mat.K, mat.Rw, mat.Rd, mat.Krhs]
+    if noslip:
+        mat.globalIndicesNS, mat.globalIndicesDIR = set(boundary), set()
+    else:
+        mat.globalIndicesDIR = set(2 * n + d for n in boundary for d in range(2))
+    base = cbp.NoSlipFreeSlip if noslip else cbp.FreeSlip
+
+    class Bare(base):
+        def __init__(self):
+            pass
+
+    fem = Bare()
+    fem.dim, fem.dom, fem.mat, fem.comm = 2, Dom(), mat, comm
+    fem.elemType = Spectral(mesh.ngl, 2)
+    fem.logger = logging.getLogger("reference-case")
+    fem.buildKLEMats()
+    keep = ("K", "Krhs", "Rw", "Rd", "Kfs", "Krhsfs", "Rwfs", "Rdfs") if noslip else ("K", "Krhs", "Rw")
+    return {nm: getattr(mat, nm).to_csr() for nm in keep}
+
+
+# ---- buildOperators / Operators.assembleAll (A3) and the evalRHS chain (R2 / R3) on stand-ins --------------------------
+class _FakeNpVec(object):
+    """PETSc.Vec calls of mat_generator.py:157-190 and base_problem.py:212-252 on a NumPy array."""
+
+    def __init__(self, n=0, arr=None):
+        import numpy as np
+        self.a = np.zeros(n) if arr is None else np.array(arr, dtype=float)
+
+    def setValues(self, idx, vals, addv=False):
+        import numpy as np
+        idx = np.asarray(idx, dtype=np.int64).reshape(-1)
+        vals = np.broadcast_to(np.asarray(vals, dtype=float).reshape(-1), idx.shape)
+        if addv:
+            for i, v in zip(idx, vals):          # sequential: the order of the ADD_VALUES stash
+                self.a[i] += v
+        else:
+            self.a[idx] = vals
+
+    def assemble(self):
+        pass
+
+    def destroy(self):
+        pass
+
+    def reciprocal(self):
+        self.a = 1.0 / self.a
+
+    def getArray(self):
+        return self.a
+
+    def duplicate(self):
+        return _FakeNpVec(len(self.a))
+
+    def scale(self, alpha):
+        self.a = self.a * alpha
+
+    def axpy(self, alpha, x):
+        self.a = self.a + alpha * x.a
+
+    def __imul__(self, alpha):
+        self.a = self.a * alpha
+        return self
+
+
+def _aij_extras():
+    """diagonalScale / mult / getOwnershipRange for _FakeAijMat (kept apart from the assembly stand-in above)."""
+    import numpy as np
+
+    def diagonalScale(self, L=None, R=None):
+        assert R is None
+        for (r, c) in self.entries:
+            self.entries[(r, c)] = L.a[r] * self.entries[(r, c)]
+
+    def mult(self, x, y):
+        y.a = self.to_csr() @ np.asarray(x.a)
+
+    def getOwnershipRange(self):
+        return 0, self.shape[0]
+
+    _FakeAijMat.diagonalScale, _FakeAijMat.mult, _FakeAijMat.getOwnershipRange = diagonalScale, mult, getOwnershipRange
+
+
+def run_reference_operators_and_rhs(mesh, vel, rho, mu):
+    """BaseProblem.buildOperators (src/cases/base_problem.py:132-140) with Operators.setValues / assembleAll
+    (src/matrices/mat_generator.py:157-190), then evalRHS (:212-232, computeVtensV :234-252) on a given velocity --
+    UNMODIFIED, solveKLE replaced by a no-op.  Returns ({SrT, DivSrT, Curl: scipy CSR}, f)."""
+    import logging
+    import numpy as np
+    Spectral, _ = import_reference_elements()
+    _install_petsc_stub()
+    _aij_extras()
+    if REFERENCE_SRC not in sys.path:
+        sys.path.insert(0, REFERENCE_SRC)
+    import cases.base_problem as cbp  # noqa: E402  (reference code)
+    from matrices.mat_generator import Operators  # noqa: E402
+    cell_nodes, corner, N = mesh.cell_nodes(), mesh.cell_corner_coords(), mesh.nnodes
+
+    class Dom(object):
+        cellStart, cellEnd = 0, len(cell_nodes)
+
+        def getCellCornersCoords(self, cell):
+            return corner[cell].reshape(-1).copy()
+
+        def getGlobalNodesFromCell(self, cell, shared):
+            return [int(n) for n in cell_nodes[cell]]
+
+    op = Operators.__new__(Operators)
+    op.dim, op.dim_w, op.dim_s = 2, 1, 3
+    op.Curl, op.SrT, op.DivSrT = (_FakeAijMat((N, 2 * N), "Curl"), _FakeAijMat((3 * N, 2 * N), "SrT"),
+                                  _FakeAijMat((2 * N, 3 * N), "DivSrT"))
+    op.weigCurl, op.weigSrT, op.weigDivSrT = _FakeNpVec(N), _FakeNpVec(3 * N), _FakeNpVec(2 * N)
+
+    class Bare(cbp.BaseProblem):
+        def __init__(self):
+            pass
+
+        def solveKLE(self, t, vort):
+            pass
+
+    fem = Bare()
+    fem.dim, fem.dim_w, fem.dim_s = 2, 1, 3
+    fem.dom, fem.operator, fem.comm = Dom(), op, types.SimpleNamespace(rank=0, size=1)
+    fem.elemType, fem.logger = Spectral(mesh.ngl, 2), logging.getLogger("reference-case")
+    fem.buildOperators()
+    fem.rho, fem.mu = rho, mu
+    fem.mat = types.SimpleNamespace(K=_FakeAijMat((2 * N, 2 * N)))
+    fem.vel = _FakeNpVec(arr=vel)
+    fem._VtensV, fem._Aux1 = _FakeNpVec(3 * N), _FakeNpVec(3 * N)
+    f = _FakeNpVec(N)
+    fem.evalRHS(None, 0.0, None, f)
+    return {nm: getattr(op, nm).to_csr() for nm in ("SrT", "DivSrT", "Curl")}, np.array(f.a)
+
+
+# ---- Cavity.solveKLE (R1) on stand-ins -----------------------------------------------------------------------------
+def run_reference_cavity_solve_kle(mesh, vort, no_slip={"up": [1, 0]}):
+    """NoSlipFreeSlip.solveKLE (src/cases/base_problem.py:321-327) with Cavity.applyBoundaryConditions /
+    applyBoundaryConditionsFS (src/cases/cavity.py:53-81) and the reference's own NoSlipWalls (src/common/nswalls.py),
+    UNMODIFIED, on the matrices its own buildKLEMats / buildOperators produced (the stand-ins above); the two KSP solves
+    are SuperLU, the stand-in for the reference's default preonly + lu.  Returns (velocity, free-slip velocity)."""
+    import logging
+    import numpy as np
+    import scipy.sparse as sp
+    import scipy.sparse.linalg as spla
+    Spectral, _ = import_reference_elements()
+    _install_petsc_stub()
+    _aij_extras()
+    if REFERENCE_SRC not in sys.path:
+        sys.path.insert(0, REFERENCE_SRC)
+    import cases.base_problem as cbp  # noqa: E402  (reference code)
+    import cases.cavity as ccav  # noqa: E402
+    from matrices.mat_generator import Operators  # noqa: E402
+    from matrices.mat_ns import MatNS  # noqa: E402
+    N = mesh.nnodes
+    mats = run_reference_build_kle_mats(mesh, True)
+    ops, _ = run_reference_operators_and_rhs(mesh, np.zeros(2 * N), 1.0, 1.0)
+
+    class M(object):                      # Mat * Vec and Mat + Mat of petsc4py on an assembled matrix
+        def __init__(self, csr):
+            self.csr = csr
+
+        def __mul__(self, v):
+            return V(self.csr @ v.a)
+
+        def __add__(self, other):         # MatAXPY(1.0, DIFFERENT_NONZERO_PATTERN): union pattern
+            A, B = self.csr.tocoo(), other.csr.tocoo()
+            import kle_oracle as o
+            return M(o.coo_to_csr(np.concatenate([A.row, B.row]), np.concatenate([A.col, B.col]),
+                                  np.concatenate([A.data, B.data]), A.shape))
+
+    class V(_FakeNpVec):
+        def __init__(self, arr):
+            super().__init__(arr=arr)
+
+        def __add__(self, other):
+            return V(self.a + other.a)
+
+        def set(self, value):
+            self.a[:] = value
+
+    def lu(A):
+        fac = spla.splu(sp.csc_matrix(A.csr))
+
+        def solve(b, x):
+            x.a = fac.solve(b.a)
+        return solve
+
+    border = {nm: [int(n) for n in mesh.border_nodes(nm)] for nm in ("down", "right", "up", "left")}
+
+    class Dom(object):
+        def getBorderNodes(self, name):
+            return border[name]
+
+    class Bare(ccav.Cavity):
+        def __init__(self):
+            pass
+
+    fem = Bare()
+    fem.dim, fem.dom, fem.comm = 2, Dom(), types.SimpleNamespace(rank=0, size=1)
+    fem.logger = logging.getLogger("reference-case")
+    fem.lower, fem.upper = list(mesh.lower), list(mesh.upper)
+    fem.readBoundaryCondition({"no-slip": dict(no_slip)})
+    fem.mat = types.SimpleNamespace(**{k: M(v) for k, v in mats.items()})
+    fem.operator = types.SimpleNamespace(**{k: M(v) for k, v in ops.items()})
+    fem.solver, fem.solverFS = lu(fem.mat.K), lu(fem.mat.K + fem.mat.Kfs)
+    fem.vel, fem.velFS = V(np.zeros(2 * N)), V(np.zeros(2 * N))
+    fem.solveKLE(0.0, V(np.asarray(vort, dtype=float)))
+    return np.array(fem.vel.a), np.array(fem.velFS.a)

@@ -276,3 +276,67 @@ def test_ibm_case_code_vs_live_reference():
     np.testing.assert_array_equal(A.indices, g["static_A_indices"])
     np.testing.assert_array_equal(A.data, g["static_A_data"])
     np.testing.assert_array_equal(vnew, g["static_vel"])
+
+
+# ---- the assembly loops themselves: the reference's buildKLEMats run unmodified on stand-ins ---------------------------
+def test_assembly_oracle_vs_reference_golden():
+    """tests/golden/asm_ref.npz: every matrix that NoSlipFreeSlip.buildKLEMats / FreeSlip.buildKLEMats of the UNMODIFIED
+    reference (src/cases/base_problem.py:329-454, 499-552) produce on three box meshes, with PETSc's AIJ matrices and
+    the mesh queries replaced by stand-ins (oracle/ref_shim.run_reference_build_kle_mats, oracle/gen_golden_asm.py).
+    The oracle's vectorised restatement has the same stored pattern -- explicit zeros included -- and the same values up
+    to the round-off of its own element matrices (1e-13)."""
+    g = np.load(os.path.join(GOLDEN, "asm_ref.npz"))
+    for nx, ny, n in g["meshes"]:
+        m = o.BoxMesh([int(nx), int(ny)], [0, 0], [1.0, 0.7], int(n))
+        for tag, mats in (("ns", o.assemble_noslip(m)), ("fs", o.assemble_freeslip(m))):
+            names = ("K", "Krhs", "Rw", "Rd", "Kfs", "Krhsfs", "Rwfs", "Rdfs") if tag == "ns" else ("K", "Krhs", "Rw")
+            for nm in names:
+                key = f"{tag}_{nx}x{ny}_{n}_{nm}"
+                A = mats[nm]
+                np.testing.assert_array_equal(A.indptr, g[key + "_indptr"], err_msg=key)
+                np.testing.assert_array_equal(A.indices, g[key + "_indices"], err_msg=key)
+                assert rel_err(A.data, g[key + "_data"]) < 1e-13, key
+
+
+@pytest.mark.parametrize("nx", [8, 16, 30])
+def test_cavity_stored_entry_counts_are_the_reference_codes(nx):
+    """The stored-entry counts of the cavity at the sizes SURVEY.md 8(c) quotes, as the reference's own loops produce
+    them (K 12 228 / 56 900 / 213 924 ...): the survey's K-family figures (10 064 ...) were counts of numerically
+    non-zero entries."""
+    g = np.load(os.path.join(GOLDEN, "asm_ref.npz"))
+    mats = o.assemble_noslip(o.BoxMesh([nx, nx], [0, 0], [1, 1], 3))
+    assert [mats[k].nnz for k in ("K", "Kfs", "Krhs", "Krhsfs", "Rw", "Rwfs")] == list(g[f"cavity_counts_{nx}"])
+
+
+def test_assembly_oracle_vs_live_reference():
+    import ref_shim
+    if not ref_shim.reference_available():
+        pytest.skip("reference tree not present")
+    m = o.BoxMesh([4, 5], [0, 0], [2.0, 0.9], 4)
+    for noslip, mine in ((True, o.assemble_noslip(m)), (False, o.assemble_freeslip(m))):
+        for nm, A in ref_shim.run_reference_build_kle_mats(m, noslip).items():
+            np.testing.assert_array_equal(mine[nm].indptr, A.indptr, err_msg=nm)
+            np.testing.assert_array_equal(mine[nm].indices, A.indices, err_msg=nm)
+            assert rel_err(mine[nm].data, A.data) < 1e-13, nm
+
+
+@pytest.mark.parametrize("nx,ny,n", [(4, 3, 3), (3, 4, 5)])
+def test_operators_rhs_chain_and_solve_kle_vs_reference_golden(nx, ny, n):
+    """buildOperators + Operators.assembleAll, the evalRHS chain and the cavity's two-stage solveKLE of the UNMODIFIED
+    reference (src/cases/base_problem.py:132-140, 212-252, 321-327; src/matrices/mat_generator.py:157-190;
+    src/cases/cavity.py:53-81; src/common/nswalls.py) on stand-ins for PETSc (oracle/ref_shim.py): same operator
+    patterns, values / right-hand side / velocities to round-off."""
+    g = np.load(os.path.join(GOLDEN, "asm_ref.npz"))
+    m = o.BoxMesh([nx, ny], [0, 0], [1.0, 0.7], n)
+    ops = o.assemble_operators(m)
+    key = f"ops_{nx}x{ny}_{n}"
+    for nm in ("SrT", "DivSrT", "Curl"):
+        np.testing.assert_array_equal(ops[nm].indptr, g[f"{key}_{nm}_indptr"])
+        np.testing.assert_array_equal(ops[nm].indices, g[f"{key}_{nm}_indices"])
+        assert rel_err(ops[nm].data, g[f"{key}_{nm}_data"]) < 1e-13
+    assert rel_err(o.eval_rhs_from_vel(ops, g[f"{key}_vel"], 0.5, 0.01), g[f"{key}_rhs"]) < 1e-13
+    mc = o.BoxMesh([nx, ny], [0, 0], [1.0, 1.0], n)
+    vb, fd, fv = o.cavity_wall_vectors(mc)
+    vel, velfs, _ = o.solve_kle_noslip(o.assemble_noslip(mc), o.assemble_operators(mc), vb, fd, fv,
+                                       g[f"kle_{nx}x{ny}_{n}_vort"])
+    assert rel_err(vel, g[f"kle_{nx}x{ny}_{n}_vel"]) < 1e-12 and rel_err(velfs, g[f"kle_{nx}x{ny}_{n}_velfs"]) < 1e-12
