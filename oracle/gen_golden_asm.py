@@ -17,7 +17,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, HERE)
 import kle_oracle as o  # noqa: E402
 from ref_shim import (run_reference_build_kle_mats, run_reference_cavity_solve_kle,  # noqa: E402
-                      run_reference_operators_and_rhs)
+                      run_reference_operators_and_rhs, run_reference_taylor_green_solve_kle)
 
 OUT = os.path.join(HERE, "..", "tests", "golden", "asm_ref.npz")
 MESHES = ((4, 3, 3), (5, 5, 2), (3, 4, 5))         # (nx, ny, ngl) on [0, 1] x [0, 0.7]
@@ -48,6 +48,10 @@ def main():
         vort = np.random.default_rng(3).standard_normal(mc.nnodes)
         v, vfs = run_reference_cavity_solve_kle(mc, vort)
         out[f"kle_{nx}x{ny}_{n}_vort"], out[f"kle_{nx}x{ny}_{n}_vel"], out[f"kle_{nx}x{ny}_{n}_velfs"] = vort, v, vfs
+    for nx, n in ((4, 3), (2, 7)):               # Taylor-Green (configs[1]'s case): FreeSlip.solveKLE from the exact vorticity
+        m = o.BoxMesh([nx, nx], [0, 0], [1.0, 1.0], n)
+        v, ve, we = run_reference_taylor_green_solve_kle(m, 0.02, 0.3)
+        out[f"tg_{nx}_{n}_vel"], out[f"tg_{nx}_{n}_exact_vel"], out[f"tg_{nx}_{n}_exact_vort"] = v, ve, we
     np.savez_compressed(OUT, **out)
     print("wrote", OUT)
 

@@ -545,3 +545,78 @@ def run_reference_cavity_solve_kle(mesh, vort, no_slip={"up": [1, 0]}):
     fem.vel, fem.velFS = V(np.zeros(2 * N)), V(np.zeros(2 * N))
     fem.solveKLE(0.0, V(np.asarray(vort, dtype=float)))
     return np.array(fem.vel.a), np.array(fem.velFS.a)
+
+
+# ---- CustomFuncCase (Taylor-Green): boundary data and FreeSlip.solveKLE on stand-ins -----------------------------------
+def run_reference_taylor_green_solve_kle(mesh, nu, t):
+    """FreeSlip.solveKLE (src/cases/base_problem.py:479-481) with CustomFuncCase.applyBoundaryConditions /
+    generateExactVecs (src/cases/custom_func.py:62-83) and the Taylor-Green functions (:173-193), DMPlexDom's
+    applyFunctionVecToVec (src/domain/dmplex.py:263-272) included, UNMODIFIED, on the matrices the reference's own
+    FreeSlip.buildKLEMats produced; the solve is SuperLU.  Returns (velocity from the exact vorticity, exact velocity,
+    exact vorticity)."""
+    import logging
+    import numpy as np
+    import scipy.sparse as sp
+    import scipy.sparse.linalg as spla
+    import_reference_elements()
+    _install_petsc_stub()
+    _aij_extras()
+    if REFERENCE_SRC not in sys.path:
+        sys.path.insert(0, REFERENCE_SRC)
+    import cases.custom_func as ccf  # noqa: E402  (reference code)
+    from domain.dmplex import DMPlexDom  # noqa: E402
+    N = mesh.nnodes
+    mats = run_reference_build_kle_mats(mesh, False)
+    xy = mesh.node_coords()
+
+    class V(_FakeNpVec):
+        def __init__(self, arr):
+            super().__init__(arr=arr)
+
+        def __add__(self, other):
+            return V(self.a + other.a)
+
+        def set(self, value):
+            self.a[:] = value
+
+        def setName(self, name):
+            pass
+
+    class M(object):
+        def __init__(self, csr, ncols):
+            self.csr, self.ncols = csr, ncols
+
+        def __mul__(self, v):
+            return V(self.csr @ v.a)
+
+        def createVecRight(self):
+            return V(np.zeros(self.ncols))
+
+    class Dom(object):
+        applyFunctionVecToVec = DMPlexDom.applyFunctionVecToVec      # the reference's own method, unbound
+
+        def getNodesCoordinates(self, nodes):
+            return np.array([xy[int(n)] for n in nodes])
+
+        def getAllNodes(self):
+            return list(range(N))
+
+    class Bare(ccf.CustomFuncCase):
+        def __init__(self):
+            pass
+
+    fem = Bare()
+    fem.dim, fem.dim_w, fem.dom, fem.nu, fem.caseName = 2, 1, Dom(), nu, "taylor-green"
+    fem.comm, fem.logger = types.SimpleNamespace(rank=0, size=1), logging.getLogger("reference-case")
+    fem.velFunction, fem.vortFunction = fem.taylorGreenVel_2D, fem.taylorGreenVort_2D
+    fem.bcNodes = set(int(n) for n in mesh.boundary_nodes())
+    fem.mat = types.SimpleNamespace(K=M(mats["K"], 2 * N), Krhs=M(mats["Krhs"], 2 * N), Rw=M(mats["Rw"], N))
+    fac = spla.splu(sp.csc_matrix(mats["K"]))
+
+    def solver(b, x):
+        x.a = fac.solve(b.a)
+    fem.solver = solver
+    fem.vel, fem.vort = V(np.zeros(2 * N)), V(np.zeros(N))
+    exactVel, exactVort = fem.generateExactVecs(t)
+    fem.solveKLE(t, exactVort)
+    return np.array(fem.vel.a), np.array(exactVel.a), np.array(exactVort.a)

@@ -340,3 +340,19 @@ def test_operators_rhs_chain_and_solve_kle_vs_reference_golden(nx, ny, n):
     vel, velfs, _ = o.solve_kle_noslip(o.assemble_noslip(mc), o.assemble_operators(mc), vb, fd, fv,
                                        g[f"kle_{nx}x{ny}_{n}_vort"])
     assert rel_err(vel, g[f"kle_{nx}x{ny}_{n}_vel"]) < 1e-12 and rel_err(velfs, g[f"kle_{nx}x{ny}_{n}_velfs"]) < 1e-12
+
+
+@pytest.mark.parametrize("nx,n", [(4, 3), (2, 7)])
+def test_taylor_green_solve_kle_vs_reference_golden(nx, n):
+    """CustomFuncCase (src/cases/custom_func.py:62-83, 173-193) + FreeSlip.solveKLE (base_problem.py:479-481) of the
+    UNMODIFIED reference on stand-ins: exact fields bit for bit, the velocity recovered from the exact vorticity to
+    round-off."""
+    g = np.load(os.path.join(GOLDEN, "asm_ref.npz"))
+    m = o.BoxMesh([nx, nx], [0, 0], [1.0, 1.0], n)
+    ve, we = o.taylor_green(m.node_coords(), 0.02, 0.3)
+    np.testing.assert_array_equal(ve.reshape(-1), g[f"tg_{nx}_{n}_exact_vel"])
+    np.testing.assert_array_equal(we, g[f"tg_{nx}_{n}_exact_vort"])
+    mats = o.assemble_freeslip(m)
+    vb = np.zeros(2 * m.nnodes)
+    vb.reshape(-1, 2)[mats["bc_nodes"]] = ve[mats["bc_nodes"]]
+    assert rel_err(o.solve_kle_freeslip(mats, vb, we), g[f"tg_{nx}_{n}_vel"]) < 1e-12
