@@ -17,7 +17,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, HERE)
 import kle_oracle as o  # noqa: E402
 from ref_shim import (run_reference_build_kle_mats, run_reference_cavity_solve_kle,  # noqa: E402
-                      run_reference_operators_and_rhs, run_reference_taylor_green_solve_kle)
+                      run_reference_cell_nodes, run_reference_operators_and_rhs,
+                      run_reference_taylor_green_solve_kle)
 
 OUT = os.path.join(HERE, "..", "tests", "golden", "asm_ref.npz")
 MESHES = ((4, 3, 3), (5, 5, 2), (3, 4, 5))         # (nx, ny, ngl) on [0, 1] x [0, 0.7]
@@ -52,6 +53,8 @@ def main():
         m = o.BoxMesh([nx, nx], [0, 0], [1.0, 1.0], n)
         v, ve, we = run_reference_taylor_green_solve_kle(m, 0.02, 0.3)
         out[f"tg_{nx}_{n}_vel"], out[f"tg_{nx}_{n}_exact_vel"], out[f"tg_{nx}_{n}_exact_vort"] = v, ve, we
+    for nx, ny, n in ((2, 2, 2), (3, 2, 3), (4, 3, 5), (2, 5, 8)):     # IndicesManager over DMPlex-style closures
+        out[f"cellnodes_{nx}x{ny}_{n}"] = run_reference_cell_nodes(o.BoxMesh([nx, ny], [0, 0], [1, 1], n))
     np.savez_compressed(OUT, **out)
     print("wrote", OUT)
 

@@ -15,7 +15,9 @@ oracle/gen_golden.py):
   * assembly loops, operators, right-hand-side chain, two-stage solveKLE, immersed-boundary coupling: PINNED against the
     reference's own case-layer code run UNMODIFIED in the build container on stand-ins for PETSc's Mat / Vec and for the
     mesh queries (oracle/ref_shim.py: run_reference_build_kle_mats, run_reference_operators_and_rhs,
-    run_reference_cavity_solve_kle, run_reference_ibm): NoSlipFreeSlip.buildKLEMats and FreeSlip.buildKLEMats
+    run_reference_cavity_solve_kle, run_reference_taylor_green_solve_kle, run_reference_cell_nodes,
+    run_reference_ibm): IndicesManager.mapEntitiesToNodes (src/domain/indices.py:66-118) over DMPlex-style closures,
+    CustomFuncCase + FreeSlip.solveKLE (custom_func.py:62-83,173-193), NoSlipFreeSlip.buildKLEMats and FreeSlip.buildKLEMats
     (src/cases/base_problem.py:329-454, 499-552) with MatNS / Mat.assembleAll / setIndices2One, buildOperators with
     Operators.setValues / assembleAll (mat_generator.py:157-190), evalRHS + computeVtensV (:212-252), solveKLE with
     Cavity.applyBoundaryConditions[FS] and NoSlipWalls (:321-327, cavity.py:53-81), the IBM case code

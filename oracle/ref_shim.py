@@ -620,3 +620,46 @@ def run_reference_taylor_green_solve_kle(mesh, nu, t):
     exactVel, exactVort = fem.generateExactVecs(t)
     fem.solveKLE(t, exactVort)
     return np.array(fem.vel.a), np.array(exactVel.a), np.array(exactVort.a)
+
+
+# ---- node numbering: the reference's IndicesManager over a DMPlex-style closure (D2 / D3) --------------------------------
+def run_reference_cell_nodes(mesh):
+    """IndicesManager.mapEntitiesToNodes / getGlobalNodes / getSectionOffset / reorderEntities2D of the UNMODIFIED
+    src/domain/indices.py on every cell of `mesh`.  What PETSc would supply is stated here: the transitive closure of a
+    cell of DMPlexCreateBoxMesh -- [cell, bottom, right, top, left edge, 4 vertices counter-clockwise from (x0, y0)],
+    top and left edges with a negative orientation -- and the section of setFemIndexing (src/domain/dmplex.py:42-61:
+    (ngl-2)^2 nodes per cell, 1 per vertex, ngl-2 per edge, offsets in point order).  Returns (ncell, ngl^2) node ids."""
+    import numpy as np
+    import_reference_elements()
+    _install_petsc_stub()
+    if REFERENCE_SRC not in sys.path:
+        sys.path.insert(0, REFERENCE_SRC)
+    from domain.indices import IndicesManager  # noqa: E402  (reference code)
+    nx, ny, m = mesh.nx, mesh.ny, mesh.ngl - 2
+    nc, nv = nx * ny, (nx + 1) * (ny + 1)
+    nxe = nx * (ny + 1)
+
+    class Section(object):
+        def getDof(self, p):
+            return m * m if p < nc else (1 if p < nc + nv else m)
+
+        def getOffset(self, p):
+            if p < nc:
+                return p * m * m
+            if p < nc + nv:
+                return nc * m * m + (p - nc)
+            return nc * m * m + nv + (p - nc - nv) * m
+
+    im = IndicesManager(2, mesh.ngl, types.SimpleNamespace(rank=0, size=1))
+    im.setGlobalIndicesSection(Section())
+    out = []
+    for c in range(nc):
+        fx, fy = c % nx, c // nx
+        vert = lambda vx, vy: nc + vy * (nx + 1) + vx                    # noqa: E731
+        xedge = lambda ex, vy: nc + nv + vy * nx + ex                    # noqa: E731
+        yedge = lambda vx, ey: nc + nv + nxe + vx * ny + ey              # noqa: E731
+        closure = np.array([c, xedge(fx, fy), yedge(fx + 1, fy), xedge(fx, fy + 1), yedge(fx, fy),
+                            vert(fx, fy), vert(fx + 1, fy), vert(fx + 1, fy + 1), vert(fx, fy + 1)])
+        orient = np.array([0, 0, 0, -1, -1, 0, 0, 0, 0])
+        out.append(im.mapEntitiesToNodes(closure, orient, True))
+    return np.array(out, dtype=np.int64)

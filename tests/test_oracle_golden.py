@@ -356,3 +356,20 @@ def test_taylor_green_solve_kle_vs_reference_golden(nx, n):
     vb = np.zeros(2 * m.nnodes)
     vb.reshape(-1, 2)[mats["bc_nodes"]] = ve[mats["bc_nodes"]]
     assert rel_err(o.solve_kle_freeslip(mats, vb, we), g[f"tg_{nx}_{n}_vel"]) < 1e-12
+
+
+@pytest.mark.parametrize("nx,ny,n", [(2, 2, 2), (3, 2, 3), (4, 3, 5), (2, 5, 8)])
+def test_cell_node_numbering_vs_reference_indices_manager(nx, ny, n):
+    """The element-local node order of every cell as the UNMODIFIED IndicesManager (src/domain/indices.py:66-118)
+    produces it from a DMPlex-style closure and the section of setFemIndexing (oracle/ref_shim.run_reference_cell_nodes;
+    the closure convention itself -- PETSc's -- is stated there, pinned by src/tests/test_domain.py for ngl 2)."""
+    g = np.load(os.path.join(GOLDEN, "asm_ref.npz"))
+    np.testing.assert_array_equal(o.BoxMesh([nx, ny], [0, 0], [1, 1], n).cell_nodes(), g[f"cellnodes_{nx}x{ny}_{n}"])
+    from pynama_b200.domain.dmplex import DMPlexDom  # the product's host numbering: the same table
+    try:
+        dom = DMPlexDom(boxMesh={"nelem": [nx, ny], "lower": [0, 0], "upper": [1, 1]})
+        dom.setFemIndexing(n)
+        got = np.array([dom.getGlobalNodesFromCell(c, shared=True) for c in range(nx * ny)])
+    except Exception as e:              # (a device is needed for some of the domain's tables)
+        pytest.skip(f"domain object needs the device: {e}")
+    np.testing.assert_array_equal(got, g[f"cellnodes_{nx}x{ny}_{n}"])
