@@ -373,3 +373,30 @@ def test_cell_node_numbering_vs_reference_indices_manager(nx, ny, n):
     except Exception as e:              # (a device is needed for some of the domain's tables)
         pytest.skip(f"domain object needs the device: {e}")
     np.testing.assert_array_equal(got, g[f"cellnodes_{nx}x{ny}_{n}"])
+
+
+def test_noslip_walls_vs_live_reference():
+    """The product's NoSlipWalls (pynama_b200/common/nswalls.py) against the reference's own class
+    (src/common/nswalls.py), where /root/reference exists: wall names, moving / static walls, wall velocities and
+    their tangential dofs, static dofs."""
+    import sys
+    import ref_shim
+    if not ref_shim.reference_available():
+        pytest.skip("reference tree not present")
+    ref_shim.import_reference_elements()
+    ref_shim._install_petsc_stub()
+    if ref_shim.REFERENCE_SRC not in sys.path:
+        sys.path.insert(0, ref_shim.REFERENCE_SRC)
+    from common.nswalls import NoSlipWalls as RefWalls
+    from pynama_b200.common.nswalls import NoSlipWalls as MyWalls
+    for excl, moving in (([], "up"), (["left"], "right"), (["down", "up"], "right")):
+        a, b = RefWalls([0, 0], [1, 2], exclude=excl), MyWalls([0, 0], [1, 2], exclude=excl)
+        a.setWallVelocity(moving, [0.5, 2])
+        b.setWallVelocity(moving, [0.5, 2])
+        assert list(a.getWallsNames()) == list(b.getWallsNames())
+        assert a.getWallsWithVelocity() == b.getWallsWithVelocity() and a.getStaticWalls() == b.getStaticWalls()
+        for wname in a.getWallsWithVelocity():
+            (va, da), (vb, db) = a.getWallVelocity(wname), b.getWallVelocity(wname)
+            assert list(np.atleast_1d(va)) == list(np.atleast_1d(vb)) and list(da) == list(db)
+        for wname in a.getStaticWalls():
+            assert list(a.getStaticDofsByName(wname)) == list(b.getStaticDofsByName(wname))
